@@ -1,0 +1,142 @@
+"""Pins the CPU oracle (oracle/fs3_oracle.c) -- CPU only, no GPU.
+
+1. against tests/golden/ (generated from the unmodified reference by tests/golden/make_golden.py):
+   known-answer table (SURVEY.md Appendix C format), full 16^3 states, per-stage 24^3 outputs;
+2. against the reference itself (oracle/_ref/libfs3ref.so) when it is present, bit for bit.
+"""
+import json
+import os
+import numpy as np
+import pytest
+from oracle_lib import Oracle, RefSim, cellhash, have_ref
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def same(a, b):
+    return np.array_equal(bits(a), bits(b))
+
+
+@pytest.mark.parametrize("n", [16, 32])
+def test_known_answers(n):
+    rows = [r for r in json.load(open(os.path.join(G, "kat.json"))) if r["n"] == n]
+    sim = Oracle(n)
+    done = 0
+    for r in sorted(rows, key=lambda r: r["step"]):
+        while done < r["step"]:
+            sim.step()
+            done += 1
+        p = sim.get_particles()
+        u, v, w = sim.get_velocity()
+        assert p.shape[0] == r["particles"]
+        assert cellhash(p, n) == r["cellhash"], (n, r["step"])
+        cnt = sim.get_cell_counts()
+        assert int(cnt.max()) == r["max_per_cell"] and int((cnt > 0).sum()) == r["occupied"]
+        assert float(u.astype(np.float64).sum()) == r["sumU"]
+        assert float(v.astype(np.float64).sum()) == r["sumV"]
+        assert float(w.astype(np.float64).sum()) == r["sumW"]
+        if r["step"] > 0:
+            phi = sim.get_phi()
+            assert float(phi.astype(np.float64).sum()) == r["sumPhi"]
+            assert int((phi < 0).sum()) == r["nFluid"]
+
+
+def test_survey_appendix_c_values():
+    # values printed in SURVEY.md Appendix C (from the survey's own probe of the reference)
+    rows = {(r["n"], r["step"]): r for r in json.load(open(os.path.join(G, "kat.json")))}
+    assert rows[(16, 0)]["cellhash"] == "0efe9b91839040a3"
+    assert rows[(16, 1)]["cellhash"] == "ab6ac3b3fa6c1ac5" and rows[(16, 1)]["nFluid"] == 1760
+    assert rows[(32, 10)]["cellhash"] == "967a06013f4d5efd" and rows[(32, 10)]["nFluid"] == 16165
+    assert rows[(32, 100)]["cellhash"] == "ca7e91625df945ab" and rows[(32, 100)]["max_per_cell"] == 235
+
+
+def test_full_state_16():
+    sim = Oracle(16)
+    for step in (1, 2, 3):
+        sim.step()
+        f = os.path.join(G, "ref16_step%d.npz" % step)
+        if not os.path.exists(f):
+            continue
+        g = np.load(f)
+        u, v, w = sim.get_velocity()
+        assert same(sim.get_particles(), g["particles"])
+        assert same(u, g["u"]) and same(v, g["v"]) and same(w, g["w"]) and same(sim.get_phi(), g["phi"])
+
+
+def test_stages_24():
+    g = np.load(os.path.join(G, "ref24_stages.npz"))
+    sim = Oracle(24)
+    sim.set_particles(g["p0"]); sim.set_velocity(g["u0"], g["v0"], g["w0"]); sim.set_phi(g["phi0"])
+    sim.advect(); assert same(sim.get_particles(), g["p_advect"])
+    sim.levelset(); assert same(sim.get_phi(), g["phi_levelset"])
+    sim.p2g(); u, v, w = sim.get_velocity()
+    assert same(u, g["u_p2g"]) and same(v, g["v_p2g"]) and same(w, g["w_p2g"])
+    sim.bodyforces(); sim.project(); u, v, w = sim.get_velocity()
+    assert same(u, g["u_proj"]) and same(v, g["v_proj"]) and same(w, g["w_proj"])
+
+
+def test_reset_counts():
+    for n in (8, 16, 20):
+        sim = Oracle(n)
+        assert sim.num_particles == 8 * (n - 2) ** 2 * (n - 1 - n // 2)
+
+
+def test_residual_history_32():
+    # ||r||_2 at 32^3, step 1, iterations 1/10/100
+    sim = Oracle(32)
+    sim.set_record_residuals(True)
+    sim.step()
+    l2, li = sim.get_residuals()
+    assert len(l2) == 100
+    assert abs(l2[0] - 4.803260e+04) / 4.8e4 < 1e-6
+    assert abs(l2[9] - 1.737042e+04) / 1.7e4 < 1e-6
+    assert abs(l2[99] - 1.524452e+00) / 1.5 < 1e-6
+    b, d = sim.get_rhs_diag()
+    phi = sim.get_phi()
+    assert abs(np.sqrt((b[phi < 0] ** 2).sum()) - 3.707655e+04) / 3.7e4 < 1e-6
+
+
+def test_project_fp32_drift_is_small():
+    a, b = Oracle(16), Oracle(16)
+    for s in (a, b):
+        s.advect(); s.levelset(); s.p2g(); s.bodyforces()
+    a.project(); b.project_f32()
+    for x, y in zip(a.get_velocity(), b.get_velocity()):
+        assert np.abs(x - y).max() < 1e-5 * max(1.0, np.abs(x).max())
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built (reference sources absent)")
+@pytest.mark.parametrize("n", [16, 20])
+def test_against_reference_bitexact(n):
+    r, o = RefSim(n), Oracle(n)
+    for step in range(6):
+        assert same(r.get_particles(), o.get_particles()), step
+        for a, b in zip(r.get_velocity(), o.get_velocity()):
+            assert same(a, b), step
+        if step:
+            assert same(r.get_phi(), o.get_phi()), step
+        r.step(); o.step()
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
+def test_extrapolate_against_reference():
+    rng = np.random.default_rng(3)
+    r, o = RefSim(8), Oracle(8)
+    for dims in ((9, 8, 8), (8, 9, 8), (5, 7, 6)):
+        nn = dims[0] * dims[1] * dims[2]
+        src = rng.standard_normal(nn).astype(np.float32)
+        valid = (rng.random(nn) < 0.05).astype(np.uint8)
+        valid[0] = 1
+        assert same(r.extrapolate(src, valid, *dims), o.extrapolate(src, valid, *dims))
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
+def test_interpolate_against_reference():
+    rng = np.random.default_rng(5)
+    r, o = RefSim(8), Oracle(8)
+    for q in rng.uniform(-2, 10, (200, 3)).astype(np.float32):
+        assert same(r.interpolate(*q), o.interpolate(*q))
