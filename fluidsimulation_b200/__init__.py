@@ -1,0 +1,6 @@
+"""fluidsimulation_b200: B200-native (sm_100a CUDA) replacement for the reference CPU solver FluidSim3.
+
+The product is the C-ABI shared library libfluidsim3_b200.so (include/fs3.h); `FluidSim3` here is the
+host-side mirror of the reference class over that ABI.
+"""
+from .sim import FluidSim3, Fs3Error, Fs3Params, load_library, LIB_PATH, ABI_SYMBOLS, STAGE_NAMES  # noqa: F401

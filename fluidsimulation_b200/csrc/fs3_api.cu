@@ -1,0 +1,270 @@
+// C ABI of libfluidsim3_b200.so (include/fs3.h): lifecycle, state access, step orchestration.
+// Mirrors FluidSim3's surface (Simulation3D.h:18-24,160-162); no CPU fallback anywhere.
+#include "fs3_internal.cuh"
+#include <cstring>
+#include <cmath>
+#include <new>
+
+static std::string g_create_error;
+
+#define ENTER(s)                                                       \
+	if (!(s)) return FS3_ERR_INVALID;                                  \
+	do {                                                               \
+		cudaError_t e0_ = cudaSetDevice((s)->device);                  \
+		if (e0_ != cudaSuccess) { (s)->err = cudaGetErrorString(e0_); return FS3_ERR_CUDA; } \
+	} while (0)
+
+static int fail(fs3_sim* s, int code, const char* msg) { s->err = msg; return code; }
+
+static int ensure_particle_capacity(fs3_sim* s, long long count) {
+	if (count <= s->cap) return FS3_OK;
+	for (int k = 0; k < 2; k++) {
+		if (s->pos[k]) cudaFree(s->pos[k]); if (s->vel[k]) cudaFree(s->vel[k]);
+		s->pos[k] = s->vel[k] = nullptr;
+	}
+	if (s->cellid) cudaFree(s->cellid); if (s->tmp_id) cudaFree(s->tmp_id);
+	s->cellid = nullptr; s->tmp_id = nullptr;
+	size_t n = (size_t)count;
+	for (int k = 0; k < 2; k++) { FS3_CUDA(cudaMalloc((void**)&s->pos[k], n * sizeof(float4))); FS3_CUDA(cudaMalloc((void**)&s->vel[k], n * sizeof(float4))); }
+	FS3_CUDA(cudaMalloc((void**)&s->cellid, n * sizeof(uint32_t)));
+	FS3_CUDA(cudaMalloc((void**)&s->tmp_id, n * sizeof(int)));
+	s->cap = count;
+	return FS3_OK;
+}
+
+// device scratch for AoS staging at the boundary, owned by the handle
+int fs3i_staging(fs3_sim* s, size_t bytes) {
+	if (bytes <= s->stage_bytes) return FS3_OK;
+	if (s->stage_ptr) cudaFree(s->stage_ptr);
+	s->stage_ptr = nullptr; s->stage_bytes = 0;
+	FS3_CUDA(cudaMalloc(&s->stage_ptr, bytes));
+	s->stage_bytes = bytes;
+	return FS3_OK;
+}
+
+static int check_flags(fs3_sim* s) {
+	int h[1] = {0};
+	FS3_CUDA(cudaMemcpyAsync(h, s->dev_flags, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	if (h[0]) {
+		FS3_CUDA(cudaMemsetAsync(s->dev_flags, 0, sizeof(int), s->stream));
+		return fail(s, FS3_ERR_PARTICLE, "a particle lay outside the grid when binned (positions must be inside the Advect clamp box)");
+	}
+	return FS3_OK;
+}
+
+extern "C" {
+
+const char* fs3_last_error(const fs3_sim* s) { return s ? s->err.c_str() : g_create_error.c_str(); }
+
+int fs3_create(int nx, int ny, int nz, float cpm, int device, fs3_sim** out) {
+	if (!out) return FS3_ERR_INVALID;
+	*out = nullptr;
+	if (nx < 4 || nx != ny || ny != nz || cpm != (float)nx) {
+		g_create_error = "only cubic grids with cells_per_meter == nx (>= 4) are supported, as the reference's own results are only defined there";
+		return FS3_ERR_INVALID;
+	}
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || device < 0 || device >= ndev) {
+		g_create_error = std::string("no usable CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "ordinal out of range");
+		return FS3_ERR_CUDA;
+	}
+	cudaDeviceProp prop;
+	cudaGetDeviceProperties(&prop, device);
+	if (prop.major != 10) {
+		g_create_error = std::string("device is not sm_100-class (found ") + prop.name + "); this library contains sm_100a code only";
+		return FS3_ERR_CUDA;
+	}
+	fs3_sim* s = new (std::nothrow) fs3_sim();
+	if (!s) return FS3_ERR_INVALID;
+	memset((void*)&s->prm, 0, sizeof(s->prm));
+	s->device = device; s->nx = nx; s->ny = ny; s->nz = nz; s->cpm = cpm;
+	s->prm.sor_iterations = 100; s->prm.omega = 0; s->prm.precision = 0; s->prm.force_dt_0_01 = 1; s->prm.record_residuals = 0;
+	s->prm.rho = 1000.0f; s->prm.gravity_y = -9.81f; s->prm.nu = 8.90f * 1e-4f / 1000.0f; s->prm.particle_radius = 1.0f;  // S3D.h:135-145
+	s->prm.record_stage_times = 0;
+	s->nU = (size_t)(nx + 1) * ny * nz; s->nV = (size_t)nx * (ny + 1) * nz; s->nW = (size_t)nx * ny * (nz + 1); s->nC = (size_t)nx * ny * nz;
+	s->launches = 0; s->np = 0; s->cap = 0; s->cur = 0; s->sorted = false; s->closest_valid = false; s->system_valid = false;
+	s->alloc_precision = -1; s->res_cap = 4096; s->res_count = 0; s->stage_ptr = nullptr; s->stage_bytes = 0;
+	for (int k = 0; k < FS3_T_COUNT; k++) s->stage_ms[k] = 0.f;
+#define CK(call)                                                                                  \
+	do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { g_create_error = std::string(#call) + ": " + cudaGetErrorString(e_); fs3_destroy(s); return FS3_ERR_CUDA; } } while (0)
+	CK(cudaSetDevice(device));
+	CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+	for (int k = 0; k < FS3_T_COUNT + 2; k++) CK(cudaEventCreate(&s->ev[k]));
+	size_t nmax = s->nW > s->nU ? s->nW : s->nU;
+	if (s->nV > nmax) nmax = s->nV;
+	CK(cudaMalloc((void**)&s->U, s->nU * 4)); CK(cudaMalloc((void**)&s->V, s->nV * 4)); CK(cudaMalloc((void**)&s->W, s->nW * 4));
+	CK(cudaMalloc((void**)&s->oU, s->nU * 4)); CK(cudaMalloc((void**)&s->oV, s->nV * 4)); CK(cudaMalloc((void**)&s->oW, s->nW * 4));
+	CK(cudaMalloc((void**)&s->phi, s->nC * 4));
+	CK(cudaMemsetAsync(s->phi, 0, s->nC * 4, s->stream));  // the reference leaves m_Phi uninitialised; every cell is written by the first level set
+	CK(cudaMalloc((void**)&s->cell_count, (s->nC + 1) * 4)); CK(cudaMalloc((void**)&s->cell_start, (s->nC + 1) * 4));
+	CK(cudaMalloc((void**)&s->cell_fill, s->nC * 4));
+	s->scan_block_cap = (s->nC + 1) / 4096 + 2;
+	CK(cudaMalloc((void**)&s->scan_block, s->scan_block_cap * 4));
+	CK(cudaMalloc((void**)&s->ls_rec, s->nC * sizeof(float4))); CK(cudaMalloc((void**)&s->closest, s->nC * 4));
+	for (int k = 0; k < 3; k++) { CK(cudaMalloc((void**)&s->cdv[k], nmax * 4)); CK(cudaMalloc((void**)&s->orderv[k], nmax * 4)); }
+	s->bucket_cap = nx + ny + nz + 8;
+	CK(cudaMalloc((void**)&s->bucket, 3 * (3 * (size_t)s->bucket_cap + 2) * 4));
+	CK(cudaMallocHost((void**)&s->h_bucket, 3 * ((size_t)s->bucket_cap + 1) * 4));
+	CK(cudaMalloc((void**)&s->res, sizeof(double) * 2 * s->res_cap));
+	CK(cudaMalloc((void**)&s->dev_flags, 4 * sizeof(int)));
+	CK(cudaMemsetAsync(s->dev_flags, 0, 4 * sizeof(int), s->stream));
+#undef CK
+	long long np = 8LL * (nz - 2) * (ny - 2) * (nx - 1 - nx / 2);
+	int rc = ensure_particle_capacity(s, np > 0 ? np : 1);
+	if (!rc) rc = fs3i_alloc_pressure(s);
+	if (!rc) rc = fs3i_reset(s);
+	if (rc) { g_create_error = s->err; fs3_destroy(s); return rc; }
+	*out = s;
+	return FS3_OK;
+}
+
+int fs3_destroy(fs3_sim* s) {
+	if (!s) return FS3_OK;
+	cudaSetDevice(s->device);
+	if (s->stream) cudaStreamSynchronize(s->stream);
+	void* ptrs[] = {s->U, s->V, s->W, s->oU, s->oV, s->oW, s->phi, s->pos[0], s->pos[1], s->vel[0], s->vel[1], s->cellid, s->cell_count,
+	                s->cell_start, s->cell_fill, s->tmp_id, s->scan_block, s->ls_rec, s->closest, s->cdv[0], s->cdv[1], s->cdv[2], s->orderv[0],
+	                s->orderv[1], s->orderv[2], s->bucket, s->p[0], s->p[1], s->b[0], s->b[1], s->dg[0], s->dg[1], s->mask[0], s->mask[1],
+	                s->res, s->dev_flags};
+	for (void* p : ptrs) if (p) cudaFree(p);
+	if (s->h_bucket) cudaFreeHost(s->h_bucket);
+	if (s->stage_ptr) cudaFree(s->stage_ptr);
+	for (int k = 0; k < FS3_T_COUNT + 2; k++) if (s->ev[k]) cudaEventDestroy(s->ev[k]);
+	if (s->stream) cudaStreamDestroy(s->stream);
+	delete s;
+	return FS3_OK;
+}
+
+int fs3_reset(fs3_sim* s) {
+	ENTER(s);
+	long long np = 8LL * (s->nz - 2) * (s->ny - 2) * (s->nx - 1 - s->nx / 2);
+	int rc = ensure_particle_capacity(s, np > 0 ? np : 1);
+	if (rc) return rc;
+	return fs3i_reset(s);
+}
+
+int fs3_sync(fs3_sim* s) {
+	ENTER(s);
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	return check_flags(s);
+}
+
+void* fs3_stream(fs3_sim* s) { return s ? (void*)s->stream : nullptr; }
+long long fs3_kernel_launches(const fs3_sim* s) { return s ? s->launches : 0; }
+long long fs3_num_particles(const fs3_sim* s) { return s ? s->np : 0; }
+
+static float flip_alpha(const fs3_sim* s, float dt) {
+	float a = 6 * dt * s->prm.nu * s->cpm * s->cpm;   // S3D.cpp:114
+	return a < 0.0f ? 0.0f : (a > 1.0f ? 1.0f : a);
+}
+static float effective_dt(const fs3_sim* s, float dt) {
+	dt = dt < 0.0f ? 0.0f : (dt > 1.0f / 15.0f ? 1.0f / 15.0f : dt);   // S3D.cpp:103
+	if (s->prm.force_dt_0_01) dt = 0.01f;                              // S3D.cpp:104
+	return dt;
+}
+
+// FluidSim3::Simulate (S3D.cpp:101-188)
+int fs3_step(fs3_sim* s, float dt) {
+	ENTER(s);
+	if (s->np <= 272) return fail(s, FS3_ERR_STATE, "Simulate needs more than 272 particles (the reference reads particles[272], Simulation3D.cpp:198-199)");
+	dt = effective_dt(s, dt);
+	const bool T = s->prm.record_stage_times != 0;
+	int rc;
+	if (T) cudaEventRecord(s->ev[FS3_T_ADVECT], s->stream);
+	if ((rc = fs3i_advect(s, dt))) return rc;
+	if (T) cudaEventRecord(s->ev[FS3_T_BIN], s->stream);
+	if ((rc = fs3i_bin(s))) return rc;
+	if ((rc = fs3i_levelset(s))) return rc;            // records LEVELSET_SEED / LEVELSET_SWEEP
+	if ((rc = fs3i_p2g(s))) return rc;                 // records P2G / EXTRAPOLATE
+	if ((rc = fs3i_project(s, dt, true, true))) return rc;  // records PROJECT_SETUP / SOR / TOVEL; gravity folded in
+	if (T) cudaEventRecord(s->ev[FS3_T_FLIP_APPLY], s->stream);
+	float alpha = flip_alpha(s, dt);
+	if ((rc = fs3i_flip_combine(s, alpha))) return rc;
+	if ((rc = fs3i_g2p(s, alpha))) return rc;
+	if (T) cudaEventRecord(s->ev[FS3_T_TOTAL], s->stream);
+	return FS3_OK;
+}
+
+int fs3_stage_times(fs3_sim* s, float* ms, int cap) {
+	ENTER(s);
+	if (!ms || cap < FS3_T_COUNT) return FS3_ERR_INVALID;
+	if (!s->prm.record_stage_times) return fail(s, FS3_ERR_STATE, "record_stage_times is off");
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	for (int k = 0; k < FS3_T_TOTAL; k++) FS3_CUDA(cudaEventElapsedTime(&ms[k], s->ev[k], s->ev[k + 1]));
+	FS3_CUDA(cudaEventElapsedTime(&ms[FS3_T_TOTAL], s->ev[0], s->ev[FS3_T_TOTAL]));
+	return FS3_OK;
+}
+
+// ---- state access -------------------------------------------------------------------------------------
+int fs3_get_particles(fs3_sim* s, fs3_particle* host) {
+	ENTER(s);
+	if (!host) return FS3_ERR_INVALID;
+	if (s->np <= 0) return FS3_OK;
+	int rc = fs3i_staging(s, (size_t)s->np * sizeof(fs3_particle));
+	if (rc) return rc;
+	if ((rc = fs3i_unsort_particles(s, (fs3_particle*)s->stage_ptr))) return rc;
+	FS3_CUDA(cudaMemcpyAsync(host, s->stage_ptr, (size_t)s->np * sizeof(fs3_particle), cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	return FS3_OK;
+}
+int fs3_set_particles(fs3_sim* s, const fs3_particle* host, long long count) {
+	ENTER(s);
+	if (count < 0 || (count > 0 && !host) || count > 0x7fffffffLL) return FS3_ERR_INVALID;
+	int rc = ensure_particle_capacity(s, count > 0 ? count : 1);
+	if (rc) return rc;
+	if ((rc = fs3i_staging(s, (size_t)(count > 0 ? count : 1) * sizeof(fs3_particle)))) return rc;
+	if (count > 0) FS3_CUDA(cudaMemcpyAsync(s->stage_ptr, host, (size_t)count * sizeof(fs3_particle), cudaMemcpyHostToDevice, s->stream));
+	rc = fs3i_load_particles(s, (const fs3_particle*)s->stage_ptr, count);
+	if (rc) return rc;
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	return FS3_OK;
+}
+int fs3_get_velocity(fs3_sim* s, float* U, float* V, float* W) {
+	ENTER(s);
+	if (U) FS3_CUDA(cudaMemcpyAsync(U, s->U, s->nU * 4, cudaMemcpyDeviceToHost, s->stream));
+	if (V) FS3_CUDA(cudaMemcpyAsync(V, s->V, s->nV * 4, cudaMemcpyDeviceToHost, s->stream));
+	if (W) FS3_CUDA(cudaMemcpyAsync(W, s->W, s->nW * 4, cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	return FS3_OK;
+}
+int fs3_set_velocity(fs3_sim* s, const float* U, const float* V, const float* W) {
+	ENTER(s);
+	if (U) FS3_CUDA(cudaMemcpyAsync(s->U, U, s->nU * 4, cudaMemcpyHostToDevice, s->stream));
+	if (V) FS3_CUDA(cudaMemcpyAsync(s->V, V, s->nV * 4, cudaMemcpyHostToDevice, s->stream));
+	if (W) FS3_CUDA(cudaMemcpyAsync(s->W, W, s->nW * 4, cudaMemcpyHostToDevice, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	return FS3_OK;
+}
+int fs3_get_phi(fs3_sim* s, float* phi) {
+	ENTER(s);
+	if (!phi) return FS3_ERR_INVALID;
+	FS3_CUDA(cudaMemcpyAsync(phi, s->phi, s->nC * 4, cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	return FS3_OK;
+}
+int fs3_set_phi(fs3_sim* s, const float* phi) {
+	ENTER(s);
+	if (!phi) return FS3_ERR_INVALID;
+	FS3_CUDA(cudaMemcpyAsync(s->phi, phi, s->nC * 4, cudaMemcpyHostToDevice, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	return FS3_OK;
+}
+int fs3_get_params(const fs3_sim* s, fs3_params* p) {
+	if (!s || !p) return FS3_ERR_INVALID;
+	*p = s->prm;
+	return FS3_OK;
+}
+int fs3_set_params(fs3_sim* s, const fs3_params* p) {
+	ENTER(s);
+	if (!p) return FS3_ERR_INVALID;
+	if (p->sor_iterations < 0 || p->sor_iterations > s->res_cap) return fail(s, FS3_ERR_INVALID, "sor_iterations out of range [0,4096]");
+	if (p->omega >= 2.0) return fail(s, FS3_ERR_INVALID, "omega must be < 2");
+	if (!(p->rho > 0.0f)) return fail(s, FS3_ERR_INVALID, "rho must be positive");
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	s->prm = *p;
+	return fs3i_alloc_pressure(s);
+}
+
+}  // extern "C"

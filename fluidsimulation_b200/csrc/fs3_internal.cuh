@@ -1,0 +1,172 @@
+// Internal state and helpers shared by the sm_100a kernels of libfluidsim3_b200.so.
+// Reference citations "S3D.cpp:a-b" / "S3D.h:a-b" are FluidSimulationDemo/Simulation3D.{cpp,h}.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include "../../include/fs3.h"
+
+#define FS3_INF_CD 1000000000  // ExtrapolateValues' "inf" (S3D.cpp:632)
+
+// ---- red-black ("colour-split") storage of the pressure system ---------------------------------
+// Cells with (x+y+z)&1 == c live in colour array c at  xh + hp*(y + ny*(z+1)),  xh = x>>1.
+// hp (half-row pitch) is a multiple of 4 so that every row starts 16-byte aligned for fp32 and fp64;
+// one ghost plane below z=0 and one above z=nz-1 make the 7-point stencil branch-free (and are the
+// z-slab halos in the multi-GPU layout).
+struct RBLayout {
+	int nx, ny, nz;
+	int hx;            // colour cells per row = (nx+1)/2
+	int hp;            // pitch
+	size_t plane;      // hp*ny
+	size_t total;      // plane*(nz+2)
+	__host__ __device__ size_t at(int xh, int y, int z) const { return (size_t)xh + (size_t)hp * ((size_t)y + (size_t)ny * (size_t)(z + 1)); }
+};
+
+struct fs3_sim {
+	int device;
+	int nx, ny, nz;
+	float cpm;
+	fs3_params prm;
+	cudaStream_t stream;
+	std::string err;
+	long long launches;
+
+	// MAC grids.  cur = field seen by Advect / returned by get_velocity (the projected field);
+	// old = target of P2G, kept as "old grid" for FLIP (S3D.cpp:123-156).
+	size_t nU, nV, nW, nC;
+	float *U, *V, *W;
+	float *oU, *oV, *oW;
+	float* phi;
+
+	// particles, SoA of two float4: pos = (X,Y,Z, bits(creation id)), vel = (uX,uY,uZ,0); double-buffered for the sort
+	long long np;
+	long long cap;
+	float4 *pos[2], *vel[2];
+	int cur;                 // which buffer holds the live particles
+	bool sorted;             // live buffer is cell-sorted and cell_start is valid
+	uint32_t* cellid;        // per particle (live order), cell index
+	uint32_t* cell_count;    // nC+1
+	uint32_t* cell_start;    // nC+1 exclusive scan
+	uint32_t* cell_fill;     // nC cursor
+	int* tmp_id;             // per sorted slot: creation id (ranking key)
+	uint32_t* scan_block;    // block sums for the scan
+	size_t scan_block_cap;
+
+	// level set
+	float4* ls_rec;          // per cell: closest particle (n*X, n*Y, n*Z, bits(id)); id<0 = none
+	int* closest;            // per cell creation id (exported)
+	bool closest_valid;
+
+	// extrapolation scratch (sized for the largest face grid)
+	int* cdv[3];             // L1 distance, one slot per face grid
+	int* orderv[3];          // nodes with cd>0 bucketed by distance
+	uint32_t* bucket;        // per slot: histogram / starts / cursors (3*bucket_cap+2 words)
+	int bucket_cap;
+	uint32_t* h_bucket;      // pinned host copy of the starts, (bucket_cap+1) words per slot
+
+	// pressure system
+	RBLayout rb;
+	void *p[2], *b[2], *dg[2]; // colour arrays, double or float according to prm.precision
+	int alloc_precision;
+	unsigned char* mask[2];     // bit0..5: x-,x+,y-,y+,z-,z+ neighbour is fluid; bit6: cell is fluid
+	bool system_valid;
+	double* res;               // device: [2*i] sum r^2, [2*i+1] max |r| (as double bits)
+	int res_cap, res_count;
+
+	int* dev_flags;            // [0] particle-outside flag
+	void* stage_ptr;           // device staging for AoS / hook transfers at the boundary
+	size_t stage_bytes;
+	cudaEvent_t ev[FS3_T_COUNT + 2];
+	float stage_ms[FS3_T_COUNT];
+};
+
+#define FS3_CUDA(call)                                                                           \
+	do {                                                                                         \
+		cudaError_t e_ = (call);                                                                 \
+		if (e_ != cudaSuccess) {                                                                 \
+			s->err = std::string(#call) + ": " + cudaGetErrorString(e_);                         \
+			return FS3_ERR_CUDA;                                                                 \
+		}                                                                                        \
+	} while (0)
+
+#define FS3_LAUNCH_CHECK()                                                                       \
+	do {                                                                                         \
+		s->launches++;                                                                           \
+		cudaError_t e_ = cudaGetLastError();                                                     \
+		if (e_ != cudaSuccess) {                                                                 \
+			s->err = std::string("kernel launch: ") + cudaGetErrorString(e_);                    \
+			return FS3_ERR_CUDA;                                                                 \
+		}                                                                                        \
+	} while (0)
+
+static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// ---- device helpers common to the particle kernels ---------------------------------------------
+struct GridDims {
+	int nx, ny, nz;
+};
+
+__device__ __forceinline__ float fs3_clamp(float x, float lo, float hi) { return x < lo ? lo : (x > hi ? hi : x); }  // MathHelper.h:49-53
+__device__ __forceinline__ float fs3_lerp(float a, float b, float t) { return __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), t)); }  // MathHelper.h:43-47, never fused
+
+// One axis of InterpolateMACCell (S3D.h:61-82): clamp, floor, step back from the last node, fraction.
+__device__ __forceinline__ void fs3_split(float c, float hi, int last, int& i0, float& f) {
+	float cc = fs3_clamp(c, 0.0f, hi);
+	int i = (int)floorf(cc);
+	if (i == last) i--;
+	i0 = i;
+	f = __fsub_rn(cc, (float)i);
+}
+
+__device__ __forceinline__ float fs3_tri(const float* __restrict__ g, size_t base, int sy, size_t sz, float fx, float fy, float fz) {
+	// x lerps first, then y, then z (S3D.h:87-97)
+	float a00 = fs3_lerp(__ldg(g + base), __ldg(g + base + 1), fx);
+	float a10 = fs3_lerp(__ldg(g + base + sy), __ldg(g + base + sy + 1), fx);
+	float a01 = fs3_lerp(__ldg(g + base + sz), __ldg(g + base + sz + 1), fx);
+	float a11 = fs3_lerp(__ldg(g + base + sz + sy), __ldg(g + base + sz + sy + 1), fx);
+	return fs3_lerp(fs3_lerp(a00, a10, fy), fs3_lerp(a01, a11, fy), fz);
+}
+
+// InterpolateMACCell (S3D.h:55-123) at index-space point (i,j,k).
+__device__ __forceinline__ float3 fs3_interp(const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W,
+                                             GridDims d, float i, float j, float k) {
+	int iI, iJ, iK, eI, eJ, eK;
+	float fI, fJ, fK, gI, gJ, gK;
+	fs3_split(i, (float)d.nx - 1.0f, d.nx - 1, iI, fI);
+	fs3_split(j, (float)d.ny - 1.0f, d.ny - 1, iJ, fJ);
+	fs3_split(k, (float)d.nz - 1.0f, d.nz - 1, iK, fK);
+	fs3_split(__fadd_rn(i, 0.5f), (float)d.nx, d.nx, eI, gI);
+	fs3_split(__fadd_rn(j, 0.5f), (float)d.ny, d.ny, eJ, gJ);
+	fs3_split(__fadd_rn(k, 0.5f), (float)d.nz, d.nz, eK, gK);
+	float3 r;
+	r.x = fs3_tri(U, (size_t)eI + (size_t)(d.nx + 1) * ((size_t)iJ + (size_t)d.ny * iK), d.nx + 1, (size_t)(d.nx + 1) * d.ny, gI, fJ, fK);
+	r.y = fs3_tri(V, (size_t)iI + (size_t)d.nx * ((size_t)eJ + (size_t)(d.ny + 1) * iK), d.nx, (size_t)d.nx * (d.ny + 1), fI, gJ, fK);
+	r.z = fs3_tri(W, (size_t)iI + (size_t)d.nx * ((size_t)iJ + (size_t)d.ny * eK), d.nx, (size_t)d.nx * d.ny, fI, fJ, gK);
+	return r;
+}
+
+// cell of a particle: (int)roundf(n*X) per axis (S3D.cpp:283-288)
+__device__ __forceinline__ int fs3_cell_axis(float p, float n) { return (int)roundf(__fmul_rn(p, n)); }
+
+// ---- host-side launchers implemented in the .cu files -------------------------------------------
+int fs3i_reset(fs3_sim* s);
+int fs3i_advect(fs3_sim* s, float dt);
+int fs3i_bin(fs3_sim* s);
+int fs3i_unsort_particles(fs3_sim* s, fs3_particle* dev_out);              // creation order AoS into device buffer
+int fs3i_load_particles(fs3_sim* s, const fs3_particle* dev_in, long long count);
+int fs3i_cell_indices(fs3_sim* s, int* dev_out);                            // creation order
+int fs3i_levelset(fs3_sim* s);
+int fs3i_p2g(fs3_sim* s);
+int fs3i_extrapolate(fs3_sim* s, float* grid, int xs, int ys, int zs);          // uses slot 0 (cdv[0] initialised)
+int fs3i_cd_from_valid(fs3_sim* s, const unsigned char* dev_valid, size_t n);
+int fs3i_bodyforces(fs3_sim* s, float dt);
+int fs3i_project(fs3_sim* s, float dt, bool from_old, bool with_gravity);
+int fs3i_sor_loop(fs3_sim* s, int iters);
+int fs3i_clear_pressure(fs3_sim* s);
+int fs3i_export_pressure(fs3_sim* s, double* dev_p, double* dev_b, double* dev_dg);
+int fs3i_flip_combine(fs3_sim* s, float alpha);                             // old <- cur - (1-alpha) old
+int fs3i_g2p(fs3_sim* s, float alpha);
+int fs3i_alloc_pressure(fs3_sim* s);
+int fs3i_staging(fs3_sim* s, size_t bytes);
+int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs);
+int fs3i_extrap_fill(fs3_sim* s, int slot, float* grid, int xs, int ys, int zs);

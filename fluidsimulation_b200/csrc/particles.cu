@@ -1,0 +1,349 @@
+// Particle-side kernels: reset (closed-form LCG skip-ahead), RK3 advection, counting sort by cell,
+// PIC/FLIP grid-to-particle blend.  sm_100a; compiled with -fmad=false (the reference build never
+// contracts a*b+c).  All kernels are particle-parallel, 128-bit loads/stores on the
+// float4 SoA arrays; particles are kept physically sorted by cell so that the grid gathers of one
+// warp hit a handful of neighbouring cache lines.
+#include "fs3_internal.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// ResetSimulation (S3D.cpp:41-99).  std::default_random_engine(0) is minstd_rand0 in libstdc++:
+// x_k = 16807^k mod (2^31-1) with x_0 = 1, one draw per value, so draw k is computable independently.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t lcg_state(unsigned long long k) {
+	const unsigned long long M = 2147483647ull;
+	unsigned long long r = 1, a = 16807ull;
+	while (k) {
+		if (k & 1) r = (r * a) % M;
+		a = (a * a) % M;
+		k >>= 1;
+	}
+	return (uint32_t)r;
+}
+// uniform_real_distribution<float>(-0.25f, 0.25f) of draw k >= 1 (libstdc++ generate_canonical<float,24>)
+__device__ __forceinline__ float lcg_uniform(unsigned long long k) {
+	uint32_t x = lcg_state(k);
+	float r = (float)(x - 1u) / 2147483648.0f;
+	if (r >= 1.0f) r = 0.99999994f;  // nextafterf(1,0)
+	return __fadd_rn(__fmul_rn(r, 0.5f), -0.25f);
+}
+
+__global__ void k_reset_grids(float* __restrict__ U, float* __restrict__ V, float* __restrict__ W, size_t nU, size_t nV, size_t nW) {
+	size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	size_t tot = nU + nV + nW;
+	for (; q < tot; q += (size_t)gridDim.x * blockDim.x) {
+		float r = lcg_uniform(q + 1);
+		if (q < nU) U[q] = r;
+		else if (q < nU + nV) V[q - nU] = r;
+		else W[q - nU - nV] = r;
+	}
+}
+
+__global__ void k_reset_particles(float4* __restrict__ pos, float4* __restrict__ vel, long long np, GridDims d, float cpm,
+                                  const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W,
+                                  unsigned long long draw0) {
+	long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (j >= np) return;
+	int c = (int)(j & 1), b = (int)((j >> 1) & 1), a = (int)((j >> 2) & 1);
+	long long cellj = j >> 3;
+	int xc = d.nx - 1 - d.nx / 2, yc = d.ny - 2;
+	int x = d.nx / 2 + (int)(cellj % xc);
+	int y = 1 + (int)((cellj / xc) % yc);
+	int z = 1 + (int)(cellj / ((long long)xc * yc));
+	float dd = 0.5f / cpm;
+	unsigned long long k = draw0 + 3ull * (unsigned long long)j;
+	float m1 = __fadd_rn(__fadd_rn(((float)x - 0.25f) / cpm, __fmul_rn((float)a, dd)), lcg_uniform(k) / cpm);
+	float m2 = __fadd_rn(__fadd_rn(((float)y - 0.25f) / cpm, __fmul_rn((float)b, dd)), lcg_uniform(k + 1) / cpm);
+	float m3 = __fadd_rn(__fadd_rn(((float)z - 0.25f) / cpm, __fmul_rn((float)c, dd)), lcg_uniform(k + 2) / cpm);
+	float3 u = fs3_interp(U, V, W, d, __fmul_rn((float)d.nx, m1), __fmul_rn((float)d.ny, m2), __fmul_rn((float)d.nz, m3));
+	pos[j] = make_float4(m1, m2, m3, __int_as_float((int)j));
+	vel[j] = make_float4(u.x, u.y, u.z, 0.0f);
+}
+
+int fs3i_reset(fs3_sim* s) {
+	size_t tot = s->nU + s->nV + s->nW;
+	k_reset_grids<<<cdiv((long long)tot, 256 * 4), 256, 0, s->stream>>>(s->U, s->V, s->W, s->nU, s->nV, s->nW);
+	FS3_LAUNCH_CHECK();
+	long long np = 8LL * (s->nz - 2) * (s->ny - 2) * (s->nx - 1 - s->nx / 2);
+	s->np = np;
+	s->cur = 0;
+	s->sorted = false;
+	s->closest_valid = false;
+	s->system_valid = false;
+	GridDims d{s->nx, s->ny, s->nz};
+	k_reset_particles<<<cdiv(np, 256), 256, 0, s->stream>>>(s->pos[0], s->vel[0], np, d, s->cpm, s->U, s->V, s->W,
+	                                                         (unsigned long long)tot + 1ull);
+	FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Advect (S3D.cpp:190-232): Ralston RK3 through the grid, clamp into the box.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_advect(float4* __restrict__ pos, long long np, GridDims d, float dt,
+                                                const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	float4 p = pos[i];
+	float fx = (float)d.nx, fy = (float)d.ny, fz = (float)d.nz;
+	float3 k1 = fs3_interp(U, V, W, d, __fmul_rn(fx, p.x), __fmul_rn(fy, p.y), __fmul_rn(fz, p.z));
+	float h = __fmul_rn(0.5f, dt);
+	float3 k2 = fs3_interp(U, V, W, d, __fmul_rn(fx, __fadd_rn(p.x, __fmul_rn(h, k1.x))), __fmul_rn(fy, __fadd_rn(p.y, __fmul_rn(h, k1.y))),
+	                       __fmul_rn(fz, __fadd_rn(p.z, __fmul_rn(h, k1.z))));
+	float t = __fmul_rn(0.75f, dt);
+	float3 k3 = fs3_interp(U, V, W, d, __fmul_rn(fx, __fadd_rn(p.x, __fmul_rn(t, k2.x))), __fmul_rn(fy, __fadd_rn(p.y, __fmul_rn(t, k2.y))),
+	                       __fmul_rn(fz, __fadd_rn(p.z, __fmul_rn(t, k2.z))));
+	const float c1 = 2.0f / 9.0f, c2 = 3.0f / 9.0f, c3 = 4.0f / 9.0f;
+	float vx = __fadd_rn(__fadd_rn(__fmul_rn(c1, k1.x), __fmul_rn(c2, k2.x)), __fmul_rn(c3, k3.x));
+	float vy = __fadd_rn(__fadd_rn(__fmul_rn(c1, k1.y), __fmul_rn(c2, k2.y)), __fmul_rn(c3, k3.y));
+	float vz = __fadd_rn(__fadd_rn(__fmul_rn(c1, k1.z), __fmul_rn(c2, k2.z)), __fmul_rn(c3, k3.z));
+	p.x = __fadd_rn(p.x, __fmul_rn(dt, vx));
+	p.y = __fadd_rn(p.y, __fmul_rn(dt, vy));
+	p.z = __fadd_rn(p.z, __fmul_rn(dt, vz));
+	const float eps = 0.1f;
+	p.x = fs3_clamp(p.x, (-0.5f + eps) / fx, __fadd_rn(1.0f, (-0.5f - eps) / fx));
+	p.y = fs3_clamp(p.y, (-0.5f + eps) / fy, __fadd_rn(1.0f, (-0.5f - eps) / fy));
+	p.z = fs3_clamp(p.z, (-0.5f + eps) / fz, __fadd_rn(1.0f, (-0.5f - eps) / fz));
+	pos[i] = p;
+}
+
+int fs3i_advect(fs3_sim* s, float dt) {
+	if (s->np <= 0) return FS3_OK;
+	GridDims d{s->nx, s->ny, s->nz};
+	k_advect<<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, dt, s->U, s->V, s->W);
+	FS3_LAUNCH_CHECK();
+	s->sorted = false;
+	s->closest_valid = false;
+	return FS3_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Binning: counting sort of the particles by cell (cell = (int)roundf(n*X), S3D.cpp:286-288).
+// count -> exclusive scan -> scatter creation ids -> rank inside the cell by creation id -> gather.
+// Ranking by creation id makes the order inside a cell the reference's particle order, so the result
+// is deterministic (no dependence on atomic arrival order) and "lowest index wins" tie-breaks
+// (S3D.cpp:296) fall out of a forward scan of the cell's segment.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_bin_count(const float4* __restrict__ pos, long long np, GridDims d, uint32_t* __restrict__ cellid,
+                                                   uint32_t* __restrict__ count, int* __restrict__ flags) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	float4 p = pos[i];
+	int cx = fs3_cell_axis(p.x, (float)d.nx), cy = fs3_cell_axis(p.y, (float)d.ny), cz = fs3_cell_axis(p.z, (float)d.nz);
+	if (cx < 0 || cx >= d.nx || cy < 0 || cy >= d.ny || cz < 0 || cz >= d.nz) {
+		flags[0] = 1;  // outside the box: the reference skips such particles; Advect's clamp makes this unreachable
+		cx = min(max(cx, 0), d.nx - 1); cy = min(max(cy, 0), d.ny - 1); cz = min(max(cz, 0), d.nz - 1);
+	}
+	uint32_t c = (uint32_t)cx + (uint32_t)d.nx * ((uint32_t)cy + (uint32_t)d.ny * (uint32_t)cz);
+	cellid[i] = c;
+	atomicAdd(count + c, 1u);
+}
+
+// --- exclusive scan of uint32 (reduce / scan block sums / apply), tile = 512 threads x 8 items ----
+#define SCAN_T 512
+#define SCAN_I 8
+#define SCAN_TILE (SCAN_T * SCAN_I)
+
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total) {
+	__shared__ uint32_t wsum[SCAN_T / 32];
+	int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	uint32_t inc = v;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+		if (lane >= o) inc += t;
+	}
+	if (lane == 31) wsum[wid] = inc;
+	__syncthreads();
+	if (wid == 0) {
+		uint32_t w = lane < SCAN_T / 32 ? wsum[lane] : 0;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
+			if (lane >= o) w += t;
+		}
+		if (lane < SCAN_T / 32) wsum[lane] = w;
+	}
+	__syncthreads();
+	uint32_t base = wid ? wsum[wid - 1] : 0;
+	if (total) *total = wsum[SCAN_T / 32 - 1];
+	__syncthreads();
+	return base + inc - v;
+}
+
+__global__ void __launch_bounds__(SCAN_T) k_scan_reduce(const uint32_t* __restrict__ in, size_t n, uint32_t* __restrict__ bsum) {
+	size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_I;
+	uint32_t v = 0;
+#pragma unroll
+	for (int k = 0; k < SCAN_I; k++) if (base + k < n) v += in[base + k];
+	uint32_t tot;
+	block_excl_scan(v, &tot);
+	if (threadIdx.x == 0) bsum[blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(SCAN_T) k_scan_blocks(uint32_t* __restrict__ bsum, int nb) {
+	__shared__ uint32_t carry;
+	if (threadIdx.x == 0) carry = 0;
+	__syncthreads();
+	for (int b0 = 0; b0 < nb; b0 += SCAN_T) {
+		int i = b0 + threadIdx.x;
+		uint32_t v = i < nb ? bsum[i] : 0, tot;
+		uint32_t ex = block_excl_scan(v, &tot);
+		uint32_t c = carry;
+		if (i < nb) bsum[i] = ex + c;
+		__syncthreads();
+		if (threadIdx.x == 0) carry = c + tot;
+		__syncthreads();
+	}
+}
+__global__ void __launch_bounds__(SCAN_T) k_scan_apply(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
+                                                       const uint32_t* __restrict__ bsum) {
+	size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_I;
+	uint32_t loc[SCAN_I], v = 0;
+#pragma unroll
+	for (int k = 0; k < SCAN_I; k++) { loc[k] = base + k < n ? in[base + k] : 0; v += loc[k]; }
+	uint32_t ex = block_excl_scan(v, nullptr) + bsum[blockIdx.x];
+#pragma unroll
+	for (int k = 0; k < SCAN_I; k++) { if (base + k < n) out[base + k] = ex; ex += loc[k]; }
+}
+
+static int scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n) {
+	int nb = cdiv((long long)n, SCAN_TILE);
+	if ((size_t)nb > s->scan_block_cap) { s->err = "scan scratch too small"; return FS3_ERR_STATE; }
+	k_scan_reduce<<<nb, SCAN_T, 0, s->stream>>>(in, n, s->scan_block); FS3_LAUNCH_CHECK();
+	k_scan_blocks<<<1, SCAN_T, 0, s->stream>>>(s->scan_block, nb); FS3_LAUNCH_CHECK();
+	k_scan_apply<<<nb, SCAN_T, 0, s->stream>>>(in, out, n, s->scan_block); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+__global__ void __launch_bounds__(256) k_bin_scatter_ids(const float4* __restrict__ pos, const uint32_t* __restrict__ cellid, long long np,
+                                                         const uint32_t* __restrict__ start, uint32_t* __restrict__ fill, int* __restrict__ tmp_id) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	uint32_t c = cellid[i];
+	uint32_t slot = start[c] + atomicAdd(fill + c, 1u);
+	tmp_id[slot] = __float_as_int(pos[i].w);
+}
+
+__global__ void __launch_bounds__(256) k_bin_rank_gather(const float4* __restrict__ pin, const float4* __restrict__ vin,
+                                                         const uint32_t* __restrict__ cellid, long long np, const uint32_t* __restrict__ start,
+                                                         const int* __restrict__ tmp_id, float4* __restrict__ pout, float4* __restrict__ vout) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	float4 p = pin[i], v = vin[i];
+	uint32_t c = cellid[i];
+	uint32_t b = start[c], e = start[c + 1];
+	int id = __float_as_int(p.w);
+	uint32_t rank = 0;
+	for (uint32_t t = b; t < e; t++) rank += (__ldg(tmp_id + t) < id) ? 1u : 0u;
+	pout[b + rank] = p;
+	vout[b + rank] = v;
+}
+
+int fs3i_bin(fs3_sim* s) {
+	if (s->sorted) return FS3_OK;
+	FS3_CUDA(cudaMemsetAsync(s->cell_count, 0, (s->nC + 1) * sizeof(uint32_t), s->stream));
+	FS3_CUDA(cudaMemsetAsync(s->cell_fill, 0, s->nC * sizeof(uint32_t), s->stream));
+	if (s->np > 0) {
+		GridDims d{s->nx, s->ny, s->nz};
+		int nb = cdiv(s->np, 256);
+		k_bin_count<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, s->cellid, s->cell_count, s->dev_flags); FS3_LAUNCH_CHECK();
+		int rc = scan_u32(s, s->cell_count, s->cell_start, s->nC + 1);
+		if (rc) return rc;
+		k_bin_scatter_ids<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->cellid, s->np, s->cell_start, s->cell_fill, s->tmp_id); FS3_LAUNCH_CHECK();
+		k_bin_rank_gather<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->cellid, s->np, s->cell_start, s->tmp_id,
+		                                              s->pos[s->cur ^ 1], s->vel[s->cur ^ 1]); FS3_LAUNCH_CHECK();
+		s->cur ^= 1;
+	} else {
+		FS3_CUDA(cudaMemsetAsync(s->cell_start, 0, (s->nC + 1) * sizeof(uint32_t), s->stream));
+	}
+	s->sorted = true;
+	return FS3_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Boundary conversions: AoS Particle3 in creation order <-> internal sorted SoA
+// ------------------------------------------------------------------------------------------------
+__global__ void k_unsort(const float4* __restrict__ pos, const float4* __restrict__ vel, long long np, fs3_particle* __restrict__ out) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	float4 p = pos[i], v = vel[i];
+	fs3_particle q{p.x, p.y, p.z, v.x, v.y, v.z};
+	out[__float_as_int(p.w)] = q;
+}
+__global__ void k_load(const fs3_particle* __restrict__ in, long long np, float4* __restrict__ pos, float4* __restrict__ vel) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	fs3_particle q = in[i];
+	pos[i] = make_float4(q.X, q.Y, q.Z, __int_as_float((int)i));
+	vel[i] = make_float4(q.uX, q.uY, q.uZ, 0.0f);
+}
+__global__ void k_cell_indices(const float4* __restrict__ pos, long long np, GridDims d, int* __restrict__ out) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	float4 p = pos[i];
+	int cx = fs3_cell_axis(p.x, (float)d.nx), cy = fs3_cell_axis(p.y, (float)d.ny), cz = fs3_cell_axis(p.z, (float)d.nz);
+	bool in = cx >= 0 && cx < d.nx && cy >= 0 && cy < d.ny && cz >= 0 && cz < d.nz;
+	out[__float_as_int(p.w)] = in ? cx + d.nx * (cy + d.ny * cz) : -1;
+}
+
+int fs3i_unsort_particles(fs3_sim* s, fs3_particle* dev_out) {
+	if (s->np <= 0) return FS3_OK;
+	k_unsort<<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->np, dev_out); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+int fs3i_load_particles(fs3_sim* s, const fs3_particle* dev_in, long long count) {
+	s->np = count; s->cur = 0; s->sorted = false; s->closest_valid = false;
+	if (count <= 0) return FS3_OK;
+	k_load<<<cdiv(count, 256), 256, 0, s->stream>>>(dev_in, count, s->pos[0], s->vel[0]); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+int fs3i_cell_indices(fs3_sim* s, int* dev_out) {
+	if (s->np <= 0) return FS3_OK;
+	GridDims d{s->nx, s->ny, s->nz};
+	k_cell_indices<<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, dev_out); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// PIC/FLIP blend (S3D.cpp:148-180): old <- cur - (1-alpha)*old on the three face grids, then
+// u_p <- (1-alpha) u_p + interp(old) per particle.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_flip_combine(const float* __restrict__ cur, float* __restrict__ old, size_t n, float om) {
+	size_t q4 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	size_t n4 = n >> 2;
+	if (q4 < n4) {
+		float4 c = reinterpret_cast<const float4*>(cur)[q4];
+		float4 o = reinterpret_cast<float4*>(old)[q4];
+		o.x = __fsub_rn(c.x, __fmul_rn(om, o.x)); o.y = __fsub_rn(c.y, __fmul_rn(om, o.y));
+		o.z = __fsub_rn(c.z, __fmul_rn(om, o.z)); o.w = __fsub_rn(c.w, __fmul_rn(om, o.w));
+		reinterpret_cast<float4*>(old)[q4] = o;
+	} else if (q4 == n4) {
+		for (size_t q = n4 << 2; q < n; q++) old[q] = __fsub_rn(cur[q], __fmul_rn(om, old[q]));
+	}
+}
+int fs3i_flip_combine(fs3_sim* s, float alpha) {
+	float om = 1.0f - alpha;
+	k_flip_combine<<<cdiv((long long)(s->nU >> 2) + 1, 256), 256, 0, s->stream>>>(s->U, s->oU, s->nU, om); FS3_LAUNCH_CHECK();
+	k_flip_combine<<<cdiv((long long)(s->nV >> 2) + 1, 256), 256, 0, s->stream>>>(s->V, s->oV, s->nV, om); FS3_LAUNCH_CHECK();
+	k_flip_combine<<<cdiv((long long)(s->nW >> 2) + 1, 256), 256, 0, s->stream>>>(s->W, s->oW, s->nW, om); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+__global__ void __launch_bounds__(256) k_g2p(const float4* __restrict__ pos, float4* __restrict__ vel, long long np, GridDims d, float om,
+                                             const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	float4 p = pos[i], v = vel[i];
+	float3 g = fs3_interp(U, V, W, d, __fmul_rn((float)d.nx, p.x), __fmul_rn((float)d.ny, p.y), __fmul_rn((float)d.nz, p.z));
+	v.x = __fadd_rn(__fmul_rn(om, v.x), g.x);
+	v.y = __fadd_rn(__fmul_rn(om, v.y), g.y);
+	v.z = __fadd_rn(__fmul_rn(om, v.z), g.z);
+	if (v.x > 100000.0f) v.x = 1000000.0f;  // S3D.cpp:172-175
+	vel[i] = v;
+}
+int fs3i_g2p(fs3_sim* s, float alpha) {
+	if (s->np <= 0) return FS3_OK;
+	GridDims d{s->nx, s->ny, s->nz};
+	k_g2p<<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->np, d, 1.0f - alpha, s->oU, s->oV, s->oW);
+	FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}

@@ -1,0 +1,350 @@
+// Project (S3D.cpp:790-1093) on sm_100a: right-hand side + ghost-fluid diagonal, red-black SOR,
+// pressure-gradient update.  The pressure system is stored COLOUR-SPLIT (see RBLayout): a half sweep
+// streams one colour's p/b/diag contiguously with 128-bit accesses and reads the other colour as a
+// 7-point stencil whose y/z neighbours sit at the same index in the adjacent row/plane.  Neighbour
+// "is fluid" tests are folded into one mask byte per cell so phi is never re-read in the 200 sweeps.
+// REAL = double reproduces the reference's fp64 solve bit for bit (each half sweep is order
+// independent; same IEEE operations, no FMA contraction); REAL = float is the fast mode.
+#include "fs3_internal.cuh"
+
+template <typename T> struct Ops;
+template <> struct Ops<double> {
+	static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+	static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
+	static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+	static __device__ __forceinline__ double div(double a, double b) { return __ddiv_rn(a, b); }
+};
+template <> struct Ops<float> {
+	static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+	static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+	static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+	static __device__ __forceinline__ float div(float a, float b) { return __fdiv_rn(a, b); }
+};
+
+template <typename REAL> struct Sys {
+	REAL *p[2], *b[2], *dg[2];
+	unsigned char* mask[2];
+	RBLayout rb;
+};
+
+// ---- I. rhs, diagonal, masks (S3D.cpp:833-917); also clears p --------------------------------------
+template <typename REAL>
+__global__ void __launch_bounds__(256) k_project_setup(Sys<REAL> sy, const float* __restrict__ U, const float* __restrict__ V,
+                                                       const float* __restrict__ W, const float* __restrict__ phi, REAL scale, float gdt,
+                                                       int add_g, REAL max_ratio) {
+	typedef Ops<REAL> O;
+	const int nx = sy.rb.nx, ny = sy.rb.ny, nz = sy.rb.nz;
+	size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= (size_t)nx * ny * nz) return;
+	int x = (int)(c % nx), y = (int)((c / nx) % ny), z = (int)(c / ((size_t)nx * ny));
+	size_t iu = (size_t)x + (size_t)(nx + 1) * ((size_t)y + (size_t)ny * z);
+	size_t iv = (size_t)x + (size_t)nx * ((size_t)y + (size_t)(ny + 1) * z);
+	size_t iw = c;
+	// wall faces count as solid velocity 0 (S3D.cpp:840-845)
+	REAL xp = x == nx - 1 ? (REAL)0 : (REAL)U[iu + 1];
+	REAL xm = x == 0 ? (REAL)0 : (REAL)U[iu];
+	float vhi = V[iv + nx], vlo = V[iv];
+	if (add_g) { vhi = __fadd_rn(vhi, gdt); vlo = __fadd_rn(vlo, gdt); }   // AddBodyForces folded in (S3D.cpp:783-787)
+	REAL yp = y == ny - 1 ? (REAL)0 : (REAL)vhi;
+	REAL ym = y == 0 ? (REAL)0 : (REAL)vlo;
+	REAL zp = z == nz - 1 ? (REAL)0 : (REAL)W[iw + (size_t)nx * ny];
+	REAL zm = z == 0 ? (REAL)0 : (REAL)W[iw];
+	REAL div = O::sub(O::add(O::sub(O::add(O::sub(xp, xm), yp), ym), zp), zm);
+	REAL bval = O::mul(scale, div);
+	float pc = phi[c];
+	unsigned m = 0;
+	REAL d = 0;
+	if (pc < 0.0f) {
+		m = 64;
+		const int sY = nx, sZ = nx * ny;
+		const bool has[6] = {x != 0, x != nx - 1, y != 0, y != ny - 1, z != 0, z != nz - 1};
+		const long long off[6] = {-1, 1, -sY, sY, -(long long)sZ, (long long)sZ};
+#pragma unroll
+		for (int k = 0; k < 6; k++) {
+			if (!has[k]) continue;
+			d = O::add(d, (REAL)1);
+			float pn = phi[(long long)c + off[k]];
+			if (pn < 0.0f) m |= 1u << k;
+			if (pn > 0.0f) {
+				REAL r = O::div(-(REAL)pn, (REAL)pc);
+				r = r < (REAL)0 ? (REAL)0 : (r > max_ratio ? max_ratio : r);
+				d = O::add(d, r);
+			}
+		}
+	}
+	int col = (x + y + z) & 1;
+	size_t q = sy.rb.at(x >> 1, y, z);
+	sy.b[col][q] = bval;
+	sy.dg[col][q] = d;
+	sy.p[col][q] = (REAL)0;
+	sy.mask[col][q] = (unsigned char)m;
+}
+
+// ---- II. one colour of red-black SOR (S3D.cpp:948-1001) --------------------------------------------
+template <typename REAL, int VEC> struct VecT;
+template <> struct VecT<double, 2> { typedef double2 type; typedef unsigned short mtype; };
+template <> struct VecT<float, 4> { typedef float4 type; typedef unsigned int mtype; };
+
+template <typename REAL, int VEC>
+__global__ void __launch_bounds__(256) k_sor_half(Sys<REAL> sy, int colour, REAL omega, REAL one_minus_omega) {
+	typedef Ops<REAL> O;
+	typedef typename VecT<REAL, VEC>::type V;
+	typedef typename VecT<REAL, VEC>::mtype M;
+	const int tpr = sy.rb.hp / VEC;
+	size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	size_t rows = (size_t)sy.rb.ny * sy.rb.nz;
+	if (t >= rows * tpr) return;
+	int xv = (int)(t % tpr);
+	size_t r = t / tpr;
+	int y = (int)(r % sy.rb.ny), z = (int)(r / sy.rb.ny);
+	size_t base = sy.rb.at(xv * VEC, y, z);
+	M mm = *reinterpret_cast<const M*>(sy.mask[colour] + base);
+	M selfbits = VEC == 2 ? (M)0x4040 : (M)0x40404040u;
+	if ((mm & selfbits) == 0) return;   // no fluid cell in this vector: nothing to read or write
+	const int s = (colour + y + z) & 1;  // x parity of this colour in this row
+	const REAL* __restrict__ o = sy.p[colour ^ 1];
+	REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
+	*reinterpret_cast<V*>(own) = *reinterpret_cast<const V*>(sy.p[colour] + base);
+	*reinterpret_cast<V*>(bb) = *reinterpret_cast<const V*>(sy.b[colour] + base);
+	*reinterpret_cast<V*>(dd) = *reinterpret_cast<const V*>(sy.dg[colour] + base);
+	*reinterpret_cast<V*>(xc) = *reinterpret_cast<const V*>(o + base);
+	*reinterpret_cast<V*>(ym) = *reinterpret_cast<const V*>(o + base - sy.rb.hp);
+	*reinterpret_cast<V*>(yp) = *reinterpret_cast<const V*>(o + base + sy.rb.hp);
+	*reinterpret_cast<V*>(zm) = *reinterpret_cast<const V*>(o + base - sy.rb.plane);
+	*reinterpret_cast<V*>(zp) = *reinterpret_cast<const V*>(o + base + sy.rb.plane);
+	REAL edge = s == 0 ? o[base - 1] : o[base + VEC];
+#pragma unroll
+	for (int e = 0; e < VEC; e++) {
+		unsigned m = (unsigned)(mm >> (8 * e)) & 0xffu;
+		if (!(m & 64u)) continue;
+		// other-colour x neighbours: left at index e-1+s, right at e+s
+		REAL L = s ? xc[e] : (e == 0 ? edge : xc[e > 0 ? e - 1 : 0]);
+		REAL R = s ? (e == VEC - 1 ? edge : xc[e < VEC - 1 ? e + 1 : e]) : xc[e];
+		REAL nms = 0;                                   // neighborMinusSum, order x-,x+,y-,y+,z-,z+ (S3D.cpp:964-993)
+		if (m & 1u) nms = O::sub(nms, L);
+		if (m & 2u) nms = O::sub(nms, R);
+		if (m & 4u) nms = O::sub(nms, ym[e]);
+		if (m & 8u) nms = O::sub(nms, yp[e]);
+		if (m & 16u) nms = O::sub(nms, zm[e]);
+		if (m & 32u) nms = O::sub(nms, zp[e]);
+		// p = (1-omega) p + omega (b - nms) / diag   (S3D.cpp:996)
+		own[e] = O::add(O::mul(one_minus_omega, own[e]), O::div(O::mul(omega, O::sub(bb[e], nms)), dd[e]));
+	}
+	*reinterpret_cast<V*>(sy.p[colour] + base) = *reinterpret_cast<V*>(own);
+}
+
+// ---- residual ||b - A p|| over fluid cells (instrumentation; not in the reference) ------------------
+template <typename REAL>
+__global__ void __launch_bounds__(256) k_sor_residual(Sys<REAL> sy, double* __restrict__ out) {
+	const int nx = sy.rb.nx, ny = sy.rb.ny, nz = sy.rb.nz;
+	size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	double r2 = 0, ra = 0;
+	if (c < (size_t)nx * ny * nz) {
+		int x = (int)(c % nx), y = (int)((c / nx) % ny), z = (int)(c / ((size_t)nx * ny));
+		int col = (x + y + z) & 1, s = x & 1, xh = x >> 1;
+		size_t q = sy.rb.at(xh, y, z);
+		unsigned m = sy.mask[col][q];
+		if (m & 64u) {
+			const REAL* o = sy.p[col ^ 1];
+			double nms = 0;
+			if (m & 1u) nms -= (double)o[q - 1 + s];
+			if (m & 2u) nms -= (double)o[q + s];
+			if (m & 4u) nms -= (double)o[q - sy.rb.hp];
+			if (m & 8u) nms -= (double)o[q + sy.rb.hp];
+			if (m & 16u) nms -= (double)o[q - sy.rb.plane];
+			if (m & 32u) nms -= (double)o[q + sy.rb.plane];
+			double r = (double)sy.b[col][q] - ((double)sy.dg[col][q] * (double)sy.p[col][q] + nms);
+			r2 = r * r;
+			ra = fabs(r);
+		}
+	}
+	__shared__ double s2[8], sa[8];
+	for (int o = 16; o; o >>= 1) { r2 += __shfl_down_sync(0xffffffffu, r2, o); ra = fmax(ra, __shfl_down_sync(0xffffffffu, ra, o)); }
+	int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+	if (lane == 0) { s2[w] = r2; sa[w] = ra; }
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		for (int k = 1; k < 8; k++) { r2 += s2[k]; ra = fmax(ra, sa[k]); }
+		atomicAdd(out, r2);
+		atomicMax(reinterpret_cast<unsigned long long*>(out + 1), (unsigned long long)__double_as_longlong(ra));
+	}
+}
+
+// ---- III. pressure-gradient update, four ghost-fluid cases per face (S3D.cpp:1012-1084) -------------
+template <typename REAL>
+__device__ __forceinline__ float grad_face(float g, float plo, float phi_hi, REAL p_lo, REAL p_hi, REAL scale, REAL max_ratio) {
+	typedef Ops<REAL> O;
+	REAL lo = (REAL)plo, hi = (REAL)phi_hi;
+	if (lo < 0 && hi < 0) return (float)O::sub((REAL)g, O::mul(scale, O::sub(p_hi, p_lo)));
+	if (lo < 0 && hi >= 0) {
+		REAL r = O::div(-hi, lo); r = r < (REAL)0 ? (REAL)0 : (r > max_ratio ? max_ratio : r);
+		return (float)O::add((REAL)g, O::mul(O::mul(scale, O::add((REAL)1, r)), p_lo));
+	}
+	if (lo >= 0 && hi < 0) {
+		REAL r = O::div(-lo, hi); r = r < (REAL)0 ? (REAL)0 : (r > max_ratio ? max_ratio : r);
+		return (float)O::sub((REAL)g, O::mul(O::mul(scale, O::add((REAL)1, r)), p_hi));
+	}
+	return 0.0f;
+}
+
+template <typename REAL>
+__global__ void __launch_bounds__(256) k_project_gradient(Sys<REAL> sy, const float* __restrict__ sU, const float* __restrict__ sV,
+                                                          const float* __restrict__ sW, const float* __restrict__ phi, float* __restrict__ dU,
+                                                          float* __restrict__ dV, float* __restrict__ dW, REAL scale, float gdt, int add_g,
+                                                          REAL max_ratio) {
+	const int nx = sy.rb.nx, ny = sy.rb.ny, nz = sy.rb.nz;
+	size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= (size_t)nx * ny * nz) return;
+	int x = (int)(c % nx), y = (int)((c / nx) % ny), z = (int)(c / ((size_t)nx * ny));
+	int col = (x + y + z) & 1, s = x & 1;
+	size_t q = sy.rb.at(x >> 1, y, z);
+	REAL pc = sy.p[col][q];
+	float fc = phi[c];
+	const REAL* o = sy.p[col ^ 1];
+	size_t iu = (size_t)x + (size_t)(nx + 1) * ((size_t)y + (size_t)ny * z);
+	size_t iv = (size_t)x + (size_t)nx * ((size_t)y + (size_t)(ny + 1) * z);
+	size_t iw = c, sZ = (size_t)nx * ny;
+	// x face above this cell; wall faces are zero (SetEdgeVelocitiesToZero, S3D.cpp:1012)
+	if (x == 0) dU[iu] = 0.f;
+	dU[iu + 1] = x == nx - 1 ? 0.f : grad_face<REAL>(sU[iu + 1], fc, phi[c + 1], pc, o[q + s], scale, max_ratio);
+	if (y == 0) dV[iv] = 0.f;
+	{
+		float g = sV[iv + nx];
+		if (add_g) g = __fadd_rn(g, gdt);
+		dV[iv + nx] = y == ny - 1 ? 0.f : grad_face<REAL>(g, fc, phi[c + nx], pc, o[q + sy.rb.hp], scale, max_ratio);
+	}
+	if (z == 0) dW[iw] = 0.f;
+	dW[iw + sZ] = z == nz - 1 ? 0.f : grad_face<REAL>(sW[iw + sZ], fc, phi[c + sZ], pc, o[q + sy.rb.plane], scale, max_ratio);
+}
+
+template <typename REAL>
+__global__ void k_export_system(Sys<REAL> sy, double* __restrict__ p, double* __restrict__ b, double* __restrict__ dg) {
+	const int nx = sy.rb.nx, ny = sy.rb.ny, nz = sy.rb.nz;
+	size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= (size_t)nx * ny * nz) return;
+	int x = (int)(c % nx), y = (int)((c / nx) % ny), z = (int)(c / ((size_t)nx * ny));
+	int col = (x + y + z) & 1;
+	size_t q = sy.rb.at(x >> 1, y, z);
+	if (p) p[c] = (double)sy.p[col][q];
+	if (b) b[c] = (double)sy.b[col][q];
+	if (dg) dg[c] = (double)sy.dg[col][q];
+}
+
+template <typename REAL>
+__global__ void k_clear_p(Sys<REAL> sy) {
+	size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (q < sy.rb.total) { sy.p[0][q] = 0; sy.p[1][q] = 0; }
+}
+
+// ---- host side --------------------------------------------------------------------------------------
+template <typename REAL> static Sys<REAL> make_sys(fs3_sim* s) {
+	Sys<REAL> sy;
+	for (int c = 0; c < 2; c++) {
+		sy.p[c] = (REAL*)s->p[c]; sy.b[c] = (REAL*)s->b[c]; sy.dg[c] = (REAL*)s->dg[c]; sy.mask[c] = s->mask[c];
+	}
+	sy.rb = s->rb;
+	return sy;
+}
+
+int fs3i_alloc_pressure(fs3_sim* s) {
+	int prec = s->prm.precision ? 1 : 0;
+	if (s->p[0] && s->alloc_precision == prec) return FS3_OK;
+	for (int c = 0; c < 2; c++) {
+		if (s->p[c]) cudaFree(s->p[c]); if (s->b[c]) cudaFree(s->b[c]); if (s->dg[c]) cudaFree(s->dg[c]); if (s->mask[c]) cudaFree(s->mask[c]);
+		s->p[c] = s->b[c] = s->dg[c] = nullptr; s->mask[c] = nullptr;
+	}
+	RBLayout& rb = s->rb;
+	rb.nx = s->nx; rb.ny = s->ny; rb.nz = s->nz;
+	rb.hx = (s->nx + 1) / 2;
+	rb.hp = (rb.hx + 3) / 4 * 4;
+	rb.plane = (size_t)rb.hp * s->ny;
+	rb.total = rb.plane * (size_t)(s->nz + 2);
+	size_t es = prec ? 4 : 8;
+	for (int c = 0; c < 2; c++) {
+		FS3_CUDA(cudaMalloc(&s->p[c], rb.total * es)); FS3_CUDA(cudaMalloc(&s->b[c], rb.total * es));
+		FS3_CUDA(cudaMalloc(&s->dg[c], rb.total * es)); FS3_CUDA(cudaMalloc((void**)&s->mask[c], rb.total));
+		FS3_CUDA(cudaMemsetAsync(s->p[c], 0, rb.total * es, s->stream)); FS3_CUDA(cudaMemsetAsync(s->b[c], 0, rb.total * es, s->stream));
+		FS3_CUDA(cudaMemsetAsync(s->dg[c], 0, rb.total * es, s->stream)); FS3_CUDA(cudaMemsetAsync(s->mask[c], 0, rb.total, s->stream));
+	}
+	s->alloc_precision = prec;
+	s->system_valid = false;
+	return FS3_OK;
+}
+
+static double fs3_omega(const fs3_sim* s) { return s->prm.omega > 0 ? s->prm.omega : 2 - 3.16343 / s->nx; }  // S3D.cpp:944
+
+template <typename REAL, int VEC> static int sor_loop_t(fs3_sim* s, int iters) {
+	Sys<REAL> sy = make_sys<REAL>(s);
+	REAL omega = (REAL)fs3_omega(s);
+	if (sizeof(REAL) == 4) omega = (REAL)2 - (REAL)3.16343 / s->nx, omega = s->prm.omega > 0 ? (REAL)s->prm.omega : omega;
+	REAL omo = (REAL)1 - omega;
+	size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * s->nz;
+	int nb = cdiv((long long)threads, 256);
+	bool rec = s->prm.record_residuals != 0;
+	if (rec) {
+		if (iters > s->res_cap) { s->err = "residual buffer too small"; return FS3_ERR_STATE; }
+		FS3_CUDA(cudaMemsetAsync(s->res, 0, sizeof(double) * 2 * iters, s->stream));
+	}
+	for (int it = 0; it < iters; it++) {
+		k_sor_half<REAL, VEC><<<nb, 256, 0, s->stream>>>(sy, 0, omega, omo); FS3_LAUNCH_CHECK();
+		k_sor_half<REAL, VEC><<<nb, 256, 0, s->stream>>>(sy, 1, omega, omo); FS3_LAUNCH_CHECK();
+		if (rec) { k_sor_residual<REAL><<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(sy, s->res + 2 * it); FS3_LAUNCH_CHECK(); }
+	}
+	s->res_count = rec ? iters : 0;
+	return FS3_OK;
+}
+int fs3i_sor_loop(fs3_sim* s, int iters) {
+	return s->alloc_precision ? sor_loop_t<float, 4>(s, iters) : sor_loop_t<double, 2>(s, iters);
+}
+
+template <typename REAL> static int project_t(fs3_sim* s, float dt, bool from_old, bool with_gravity) {
+	Sys<REAL> sy = make_sys<REAL>(s);
+	const float *sU = from_old ? s->oU : s->U, *sV = from_old ? s->oV : s->V, *sW = from_old ? s->oW : s->W;
+	REAL dx = (REAL)1.0 / s->cpm;                       // S3D.cpp:834
+	REAL scale = -dx * s->prm.rho / dt;                 // S3D.cpp:835
+	float gdt = s->prm.gravity_y * dt;                  // S3D.cpp:784
+	int nb = cdiv((long long)s->nC, 256);
+	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_PROJECT_SETUP], s->stream);
+	k_project_setup<REAL><<<nb, 256, 0, s->stream>>>(sy, sU, sV, sW, s->phi, scale, gdt, with_gravity ? 1 : 0, (REAL)1000.0);
+	FS3_LAUNCH_CHECK();
+	s->system_valid = true;
+	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_PROJECT_SOR], s->stream);
+	int rc = fs3i_sor_loop(s, s->prm.sor_iterations);
+	if (rc) return rc;
+	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_PROJECT_TOVEL], s->stream);
+	REAL gscale = dt / (s->prm.rho * dx);               // S3D.cpp:1015
+	k_project_gradient<REAL><<<nb, 256, 0, s->stream>>>(sy, sU, sV, sW, s->phi, s->U, s->V, s->W, gscale, gdt, with_gravity ? 1 : 0, (REAL)1000.0);
+	FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+int fs3i_project(fs3_sim* s, float dt, bool from_old, bool with_gravity) {
+	int rc = fs3i_alloc_pressure(s);
+	if (rc) return rc;
+	return s->alloc_precision ? project_t<float>(s, dt, from_old, with_gravity) : project_t<double>(s, dt, from_old, with_gravity);
+}
+
+int fs3i_clear_pressure(fs3_sim* s) {
+	int nb = cdiv((long long)s->rb.total, 256);
+	if (s->alloc_precision) k_clear_p<float><<<nb, 256, 0, s->stream>>>(make_sys<float>(s));
+	else k_clear_p<double><<<nb, 256, 0, s->stream>>>(make_sys<double>(s));
+	FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+int fs3i_export_pressure(fs3_sim* s, double* p, double* b, double* dg) {
+	int nb = cdiv((long long)s->nC, 256);
+	if (s->alloc_precision) k_export_system<float><<<nb, 256, 0, s->stream>>>(make_sys<float>(s), p, b, dg);
+	else k_export_system<double><<<nb, 256, 0, s->stream>>>(make_sys<double>(s), p, b, dg);
+	FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+// AddBodyForces as a stand-alone stage (S3D.cpp:780-788); fs3_step folds it into the projection kernels.
+__global__ void k_bodyforces(float* __restrict__ V, size_t n, float gdt) {
+	size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (q < n) V[q] = __fadd_rn(V[q], gdt);
+}
+int fs3i_bodyforces(fs3_sim* s, float dt) {
+	k_bodyforces<<<cdiv((long long)s->nV, 256), 256, 0, s->stream>>>(s->V, s->nV, s->prm.gravity_y * dt);
+	FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}

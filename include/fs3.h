@@ -1,0 +1,121 @@
+/* fs3.h -- C ABI of libfluidsim3_b200.so: the B200-native (sm_100a CUDA) replacement for the
+ * reference CPU solver `FluidSim3` (reference: FluidSimulationDemo/Simulation3D.h:18-24,160-162).
+ *
+ * The reference has no FFI layer; its boundary is the C++ class surface used by its only caller
+ * (FluidSimDemoOld3D.cpp:65-67,115,136,234,263-269,437-439).  Each entry point below names the
+ * reference member it replaces.  include/FluidSim3Compat.hpp wraps this ABI in a class with the
+ * reference's exact names (FluidSim3(x,y,z,cpm), ResetSimulation(), Simulate(dt), m_particles).
+ *
+ * Conventions: plain pointers and sizes, caller-owned HOST buffers unless a name says `_device`;
+ * every call returns FS3_OK (0) or a negative error code and records a message retrievable with
+ * fs3_last_error().  Calls on one handle must be serialised by the caller (the reference is
+ * single-threaded and not re-entrant, Simulation3D.cpp:107).  There is no CPU fallback: every
+ * entry point fails with FS3_ERR_CUDA when no sm_100-class device is usable.
+ *
+ * Grid layouts are the reference's (Simulation3D.h:41-52), x fastest:
+ *   U[(nx+1)*ny*nz]  U(i,j,k) = U[i + (nx+1)*(j + ny*k)]      (x-faces)
+ *   V[nx*(ny+1)*nz]  V(i,j,k) = V[i + nx*(j + (ny+1)*k)]      (y-faces)
+ *   W[nx*ny*(nz+1)]  W(i,j,k) = W[i + nx*(j + ny*k)]          (z-faces)
+ *   phi[nx*ny*nz]    in cell units (Simulation3D.h:156-158)
+ */
+#ifndef FS3_H
+#define FS3_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FS3_OK 0
+#define FS3_ERR_INVALID (-1)    /* bad argument / unsupported shape            */
+#define FS3_ERR_CUDA (-2)       /* CUDA runtime error (message in last_error)  */
+#define FS3_ERR_STATE (-3)      /* call order / missing prerequisite stage     */
+#define FS3_ERR_PARTICLE (-4)   /* particle outside the simulation box         */
+
+/* Wire layout of one particle == reference `struct Particle3` (ParticleDefs.h:39-47): 24 bytes. */
+typedef struct fs3_particle {
+	float X, Y, Z;    /* metres, unit box */
+	float uX, uY, uZ; /* m/s */
+} fs3_particle;
+
+typedef struct fs3_sim fs3_sim; /* opaque handle == one FluidSim3 object */
+
+/* Runtime parameters; defaults are the reference's hard-coded values. */
+typedef struct fs3_params {
+	int sor_iterations;     /* 100   (Simulation3D.cpp:946) */
+	double omega;           /* <=0 -> fitted 2 - 3.16343/nx (Simulation3D.cpp:944) */
+	int precision;          /* 0 = fp64 pressure solve like the reference (default), 1 = fp32 fast mode */
+	int force_dt_0_01;      /* 1 = reproduce `dt = 0.01f` override (Simulation3D.cpp:104); 0 = use clamped dt */
+	int record_residuals;   /* 1 = record ||b - A p|| after every SOR iteration (instrumentation, slower) */
+	float rho, gravity_y, nu, particle_radius; /* 1000, -9.81, 8.9e-7, 1.0 (Simulation3D.h:135-145) */
+	int record_stage_times; /* 1 = bracket every stage with CUDA events (fs3_stage_times) */
+} fs3_params;
+
+/* Stage taxonomy for fs3_stage_times, named after the reference profiler marks (GPUProfiler.h:16-44). */
+enum {
+	FS3_T_ADVECT = 0, FS3_T_BIN, FS3_T_LEVELSET_SEED, FS3_T_LEVELSET_SWEEP, FS3_T_P2G, FS3_T_EXTRAPOLATE,
+	FS3_T_PROJECT_SETUP, FS3_T_PROJECT_SOR, FS3_T_PROJECT_TOVEL, FS3_T_FLIP_APPLY, FS3_T_TOTAL, FS3_T_COUNT
+};
+
+/* ---- lifecycle -------------------------------------------------------------------------- */
+/* FluidSim3::FluidSim3(x,y,z,CellsPerMeter) incl. the ResetSimulation() it runs (Simulation3D.cpp:19-31).
+ * Only cubes with cells_per_meter == nx are accepted: the reference mixes mX/mY/mZ and
+ * CellsPerMeter (Simulation3D.cpp:283-285 vs :442-444) and indexes uAmts with mZ for mY (:476),
+ * so its results are only defined there.  `device` = CUDA ordinal. */
+int fs3_create(int nx, int ny, int nz, float cells_per_meter, int device, fs3_sim** out);
+/* FluidSim3::~FluidSim3 (Simulation3D.cpp:33-39) */
+int fs3_destroy(fs3_sim* s);
+/* FluidSim3::ResetSimulation (Simulation3D.cpp:41-99); bit-identical to a libstdc++ build of the
+ * reference (minstd_rand0 seed 0, closed-form skip-ahead on the device). */
+int fs3_reset(fs3_sim* s);
+/* FluidSim3::Simulate(dt) (Simulation3D.cpp:101-188).  Asynchronous on the handle's stream. */
+int fs3_step(fs3_sim* s, float dt);
+/* Blocks until all queued work on the handle is complete and reports deferred device errors. */
+int fs3_sync(fs3_sim* s);
+const char* fs3_last_error(const fs3_sim* s); /* s may be NULL: error of the last failed fs3_create */
+
+/* ---- state access (reference: public m_particles; private m_MU/m_MV/m_MW/m_Phi) ------------ */
+long long fs3_num_particles(const fs3_sim* s);                      /* m_particles.size() */
+int fs3_get_particles(fs3_sim* s, fs3_particle* host);              /* m_particles, creation order */
+int fs3_set_particles(fs3_sim* s, const fs3_particle* host, long long count);
+int fs3_get_velocity(fs3_sim* s, float* U, float* V, float* W);     /* any may be NULL */
+int fs3_set_velocity(fs3_sim* s, const float* U, const float* V, const float* W);
+int fs3_get_phi(fs3_sim* s, float* phi);
+int fs3_set_phi(fs3_sim* s, const float* phi);
+int fs3_get_params(const fs3_sim* s, fs3_params* p);
+int fs3_set_params(fs3_sim* s, const fs3_params* p);
+
+/* ---- single stages of Simulate, in call order (parity hooks) ------------------------------ */
+int fs3_stage_advect(fs3_sim* s, float dt);       /* Advect, Simulation3D.cpp:190-232 */
+int fs3_stage_bin(fs3_sim* s);                    /* counting sort by cell (cell = roundf, :286-288) */
+int fs3_stage_levelset(fs3_sim* s);               /* ComputeLevelSet, :255-420 (runs fs3_stage_bin first) */
+int fs3_stage_p2g(fs3_sim* s);                    /* TransferParticlesToGrid incl. ExtrapolateValues, :422-778 */
+int fs3_stage_bodyforces(fs3_sim* s, float dt);   /* AddBodyForces, :780-788 */
+int fs3_stage_project(fs3_sim* s, float dt);      /* Project, :790-1093 (no gravity) */
+/* old' = new - (1-alpha) old; u = (1-alpha) u + interp(old')  (:148-180); old grids are host arrays */
+int fs3_stage_g2p(fs3_sim* s, float dt, const float* oldU, const float* oldV, const float* oldW);
+/* ExtrapolateValues on a caller-supplied grid (:614-778); `valid` is one byte per node */
+int fs3_extrapolate(fs3_sim* s, float* grid, const unsigned char* valid, int xs, int ys, int zs);
+
+/* ---- quantities the reference keeps in locals (parity / measurement hooks) ---------------- */
+int fs3_get_cell_indices(fs3_sim* s, int* cell);   /* per particle in creation order; valid after bin/levelset */
+int fs3_get_cell_counts(fs3_sim* s, int* counts);  /* per cell */
+int fs3_get_closest(fs3_sim* s, int* closest);     /* closestParticles[] after the 8 sweeps (creation-order ids) */
+int fs3_get_pressure(fs3_sim* s, double* p);       /* p[] of the last Project, natural cell order */
+int fs3_get_rhs_diag(fs3_sim* s, double* b, double* diag);
+int fs3_get_sor_residuals(fs3_sim* s, double* l2, double* linf, int cap, int* count);
+int fs3_stage_times(fs3_sim* s, float* ms, int cap); /* FS3_T_* order, last step, milliseconds */
+
+/* ---- measurement: projection microbench (BASELINE config 3) ------------------------------- */
+/* Runs `iters` red-black SOR iterations on the current b/diag/mask (from the last project setup)
+ * starting from p = 0 and returns the device time of the sweep loop. */
+int fs3_sor_bench(fs3_sim* s, int iters, float* ms_out);
+/* Makes every cell fluid (phi = -1, the reference's own debug switch Simulation3D.cpp:851-858). */
+int fs3_set_phi_all_fluid(fs3_sim* s);
+void* fs3_stream(fs3_sim* s);              /* the cudaStream_t all work is queued on */
+long long fs3_kernel_launches(const fs3_sim* s); /* number of kernels launched so far by this handle */
+
+#ifdef __cplusplus
+}
+#endif
+#endif
