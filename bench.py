@@ -1,0 +1,252 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json metric: particle-steps/s of the FluidSim3 step at 256^3 (dam break from
+ResetSimulation, ~65.5M particles), SOR sweep GB/s against the HBM roofline.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--grid 256] [--precision fp64|fp32]
+  python bench.py --impl reference ...      times the reference's own CPU FluidSim3 (oracle/_ref) instead
+
+A "step" is one FluidSim3::Simulate(dt) over the resident dam-break state.  `value` is timed with CUDA
+events on the library's stream with the state resident in HBM; `e2e` goes through the reference-facing
+calls with HOST buffers: upload m_particles from pinned memory, Simulate, read m_particles back.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+SOR_BYTES_PER_CELL_ITER = {"fp64": 48.0, "fp32": 28.0}  # p 2r+1w, b, diag, 2x phi
+
+
+def n_particles(n):
+    return 8 * (n - 2) ** 2 * (n - 1 - n // 2)
+
+
+def measured_peaks():
+    try:
+        d = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) >= 8:
+                self.rows.append(f)
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = sorted(int(float(r[1])) for r in self.rows if r[1].replace(".", "").isdigit())
+        mx = [int(float(r[2])) for r in self.rows if r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows for i in range(4) if r[4 + i].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def cpu_reference_run(n, steps, warmup):
+    """Times the reference CPU FluidSim3 (oracle/_ref, else the C port) -- single-threaded by construction."""
+    import oracle_lib
+    oracle_lib.build_oracle()
+    kind = "reference" if oracle_lib.have_ref() else "port"
+    sim = (oracle_lib.RefSim if kind == "reference" else oracle_lib.Oracle)(n)
+    for _ in range(warmup):
+        sim.step(0.01)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        sim.step(0.01)
+    dt = time.perf_counter() - t0
+    P = sim.num_particles
+    sim.close()
+    return P * steps / dt, dt, kind, P
+
+
+def pick_cpu_grid(total_steps, budget_s):
+    for n in (128, 96, 64, 48, 32):
+        if n_particles(n) / 1.0e6 * total_steps <= budget_s:
+            return n
+    return 32
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    n = pick_cpu_grid(args.steps + args.warmup, 150.0)
+    value, dt, kind, P = cpu_reference_run(n, args.steps, args.warmup)
+    sample = "%d^3 dam break (%d particles), %d Simulate(0.01) steps, 1 thread" % (n, P, args.steps)
+    line = {"impl": "reference", "metric": "particle-steps/s", "value": value, "unit": "particle-steps/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32 particles/grids, f64 pressure solve", "data": "synthetic",
+            "config": {"workload": "FluidSim3 dam-break step at %d^3 (target config: 256^3, 65.5M particles); CPU sample at %d^3, "
+                                   "throughput is linear in particle count (BASELINE.md section 2)" % (args.grid, n)},
+            "cpu_baseline": {"value": value, "unit": "particle-steps/s", "cores": 1, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": "particle-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_gpu(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from fluidsimulation_b200 import FluidSim3
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
+    n = args.grid
+    sim = FluidSim3(n, n, n, float(n), device=local_rank)
+    sim.set_params(precision=1 if args.precision == "fp32" else 0, record_stage_times=1)
+    P = sim.num_particles
+    stream = torch.cuda.ExternalStream(sim.stream, device=local_rank)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing: W warm-up + K timed steps, CUDA events on the library's stream -------
+    for _ in range(args.warmup):
+        sim.Simulate(0.01)
+    sim.sync()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = sim.kernel_launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sor_ms, stage_acc = 0.0, {}
+    e0.record(stream)
+    for _ in range(args.steps):
+        sim.Simulate(0.01)
+        st = sim.stage_times()      # waits for the step; event reads only, no extra device work
+        sor_ms += st["PROJECT_SOR"]
+        for k, v in st.items():
+            stage_acc[k] = stage_acc.get(k, 0.0) + v
+    e1.record(stream)
+    sim.sync()
+    barrier()
+    clocks = sampler.stop()
+    launches = sim.kernel_launches - launches0
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * P * args.steps / (ms * 1e-3)
+
+    # ---- end to end through the reference-facing calls with HOST buffers --------------------------------
+    # m_particles lives in pinned host memory: upload it, Simulate, read it back (Old3D.cpp:234,263-269).
+    host = torch.empty((P, 6), dtype=torch.float32, pin_memory=True)
+    hnp = host.numpy()
+    sim.get_particles(out=hnp)
+    e2e_steps = max(1, min(args.steps, 5))
+    barrier()
+    t0 = time.perf_counter()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record(stream)
+    for _ in range(e2e_steps):
+        sim.set_particles(hnp)
+        sim.Simulate(0.01)
+        sim.get_particles(out=hnp)
+    g1.record(stream)
+    sim.sync()
+    barrier()
+    e2e_ms = max(g0.elapsed_time(g1), (time.perf_counter() - t0) * 1e3)
+    if world > 1:
+        t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    e2e_value = world * P * e2e_steps / (e2e_ms * 1e-3)
+
+    # ---- roofline of the dominant kernel (one colour sweep of red-black SOR) ----------------------------
+    iters = sim.get_params().sor_iterations
+    n_launch = 2 * iters * args.steps
+    avg_launch_ms = sor_ms / n_launch
+    bytes_per_launch = SOR_BYTES_PER_CELL_ITER[args.precision] * n ** 3 / 2.0
+    peak, peak_src = measured_peaks()
+    achieved = bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_sor_half<%s>" % ("float,4" if args.precision == "fp32" else "double,2"),
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": args.traffic,
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_us": avg_launch_ms * 1e3,
+                "launches_timed": n_launch, "cell_updates_per_s": n ** 3 * iters * args.steps / (sor_ms * 1e-3),
+                "share_of_step": sor_ms / ms}
+
+    if rank == 0:
+        cpu = None
+        if not args.no_cpu_baseline:
+            cn = 128 if n >= 128 else n
+            cv, cdt, kind, cP = cpu_reference_run(cn, 2, 0)
+            cpu = {"value": cv, "unit": "particle-steps/s", "cores": 1, "kind": kind,
+                   "sample": "%d^3 dam break (%d particles), 2 Simulate(0.01) steps, %.1f s, single thread (the reference has no threads)" % (cn, cP, cdt)}
+        line = {"metric": "particle-steps/s", "value": value, "unit": "particle-steps/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32 particles/grids, %s pressure solve" % ("f32" if args.precision == "fp32" else "f64"), "data": "synthetic",
+                "config": {"workload": "FluidSim3 dam-break full step, %d^3 grid, %d particles/GPU, 100 SOR iterations, dt=0.01" % (n, P),
+                           "parallelism": "1 GPU" if world == 1 else "%d independent replicas (z-slab sharding not built yet)" % world,
+                           "l2": "working set (%.1f GB) larger than L2; no flush" % ((P * 64 + 40.0 * n ** 3) / 1e9)},
+                "e2e": {"value": e2e_value, "unit": "particle-steps/s", "h2d_bytes_per_step": P * 24, "d2h_bytes_per_step": P * 24,
+                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+                "stage_ms_per_step": {k: v / args.steps for k, v in stage_acc.items()}}
+        print(json.dumps(line), flush=True)
+    sim.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--grid", type=int, default=256)
+    ap.add_argument("--precision", choices=["fp64", "fp32"], default="fp64")
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--traffic", type=float, default=None, help="ncu dram bytes per launch of the dominant kernel (profiles/)")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_gpu(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
