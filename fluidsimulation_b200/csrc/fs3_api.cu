@@ -43,11 +43,15 @@ int fs3i_staging(fs3_sim* s, size_t bytes) {
 }
 
 static int check_flags(fs3_sim* s) {
-	int h[1] = {0};
-	FS3_CUDA(cudaMemcpyAsync(h, s->dev_flags, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+	int h[2] = {0, 0};
+	FS3_CUDA(cudaMemcpyAsync(h, s->dev_flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	if (h[1]) {
+		FS3_CUDA(cudaMemsetAsync(s->dev_flags, 0, 2 * sizeof(int), s->stream));
+		return fail(s, FS3_ERR_STATE, "level-set dataflow sweep timed out waiting for a tile dependency (results invalid)");
+	}
 	if (h[0]) {
-		FS3_CUDA(cudaMemsetAsync(s->dev_flags, 0, sizeof(int), s->stream));
+		FS3_CUDA(cudaMemsetAsync(s->dev_flags, 0, 2 * sizeof(int), s->stream));
 		return fail(s, FS3_ERR_PARTICLE, "a particle lay outside the grid when binned (positions must be inside the Advect clamp box)");
 	}
 	return FS3_OK;
@@ -98,9 +102,10 @@ int fs3_create(int nx, int ny, int nz, float cpm, int device, fs3_sim** out) {
 	CK(cudaMalloc((void**)&s->oU, s->nU * 4)); CK(cudaMalloc((void**)&s->oV, s->nV * 4)); CK(cudaMalloc((void**)&s->oW, s->nW * 4));
 	CK(cudaMalloc((void**)&s->phi, s->nC * 4));
 	CK(cudaMemsetAsync(s->phi, 0, s->nC * 4, s->stream));  // the reference leaves m_Phi uninitialised; every cell is written by the first level set
-	CK(cudaMalloc((void**)&s->cell_count, (s->nC + 1) * 4)); CK(cudaMalloc((void**)&s->cell_start, (s->nC + 1) * 4));
-	CK(cudaMalloc((void**)&s->cell_fill, s->nC * 4));
-	s->scan_block_cap = (s->nC + 1) / 4096 + 2;
+	s->nH = 8 * s->nC;
+	CK(cudaMalloc((void**)&s->cell_count, (s->nH + 1) * 4)); CK(cudaMalloc((void**)&s->cell_start, (s->nH + 1) * 4));
+	CK(cudaMalloc((void**)&s->cell_fill, s->nH * 4));
+	s->scan_block_cap = (s->nH + 1) / 4096 + 2;
 	CK(cudaMalloc((void**)&s->scan_block, s->scan_block_cap * 4));
 	CK(cudaMalloc((void**)&s->ls_rec, s->nC * sizeof(float4))); CK(cudaMalloc((void**)&s->closest, s->nC * 4));
 	for (int k = 0; k < 3; k++) { CK(cudaMalloc((void**)&s->cdv[k], nmax * 4)); CK(cudaMalloc((void**)&s->orderv[k], nmax * 4)); }
@@ -114,6 +119,7 @@ int fs3_create(int nx, int ny, int nz, float cpm, int device, fs3_sim** out) {
 	long long np = 8LL * (nz - 2) * (ny - 2) * (nx - 1 - nx / 2);
 	int rc = ensure_particle_capacity(s, np > 0 ? np : 1);
 	if (!rc) rc = fs3i_alloc_pressure(s);
+	if (!rc) rc = fs3i_levelset_init(s);
 	if (!rc) rc = fs3i_reset(s);
 	if (rc) { g_create_error = s->err; fs3_destroy(s); return rc; }
 	*out = s;
@@ -127,7 +133,7 @@ int fs3_destroy(fs3_sim* s) {
 	void* ptrs[] = {s->U, s->V, s->W, s->oU, s->oV, s->oW, s->phi, s->pos[0], s->pos[1], s->vel[0], s->vel[1], s->cellid, s->cell_count,
 	                s->cell_start, s->cell_fill, s->tmp_id, s->scan_block, s->ls_rec, s->closest, s->cdv[0], s->cdv[1], s->cdv[2], s->orderv[0],
 	                s->orderv[1], s->orderv[2], s->bucket, s->p[0], s->p[1], s->b[0], s->b[1], s->dg[0], s->dg[1], s->mask[0], s->mask[1],
-	                s->res, s->dev_flags};
+	                s->res, s->dev_flags, s->ls_order, s->ls_done, s->ls_ticket};
 	for (void* p : ptrs) if (p) cudaFree(p);
 	if (s->h_bucket) cudaFreeHost(s->h_bucket);
 	if (s->stage_ptr) cudaFree(s->stage_ptr);

@@ -21,9 +21,13 @@ __global__ void k_fill_f32(float* p, size_t n, float v) {
 	size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (q < n) p[q] = v;
 }
-__global__ void k_cell_counts(const uint32_t* __restrict__ start, size_t nc, int* __restrict__ out) {
+__global__ void k_cell_counts(const uint32_t* __restrict__ start, GridDims d, int* __restrict__ out) {
 	size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (q < nc) out[q] = (int)(start[q + 1] - start[q]);
+	if (q >= (size_t)d.nx * d.ny * d.nz) return;
+	int x = (int)(q % d.nx), y = (int)((q / d.nx) % d.ny), z = (int)(q / ((size_t)d.nx * d.ny));
+	int n = 0;
+	FS3_FOR_CELL_RANGES(start, d, x, y, z, b, e) n += (int)(e - b);
+	out[q] = n;
 }
 
 extern "C" {
@@ -97,7 +101,7 @@ int fs3_get_cell_counts(fs3_sim* s, int* counts) {
 	int rc = fs3i_bin(s);
 	if (rc) return rc;
 	if ((rc = fs3i_staging(s, s->nC * 4))) return rc;
-	k_cell_counts<<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(s->cell_start, s->nC, (int*)s->stage_ptr); FS3_LAUNCH_CHECK();
+	k_cell_counts<<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(s->cell_start, GridDims{s->nx, s->ny, s->nz}, (int*)s->stage_ptr); FS3_LAUNCH_CHECK();
 	FS3_CUDA(cudaMemcpyAsync(counts, s->stage_ptr, s->nC * 4, cudaMemcpyDeviceToHost, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	return FS3_OK;

@@ -43,11 +43,12 @@ struct fs3_sim {
 	long long cap;
 	float4 *pos[2], *vel[2];
 	int cur;                 // which buffer holds the live particles
-	bool sorted;             // live buffer is cell-sorted and cell_start is valid
+	bool sorted;             // live buffer is half-cell-sorted and cell_start is valid
+	size_t nH;               // 8*nC half-cells: the sort key is the particle's octant inside its cell, (2n)^3 grid, x fastest
 	uint32_t* cellid;        // per particle (live order), cell index
-	uint32_t* cell_count;    // nC+1
-	uint32_t* cell_start;    // nC+1 exclusive scan
-	uint32_t* cell_fill;     // nC cursor
+	uint32_t* cell_count;    // nH+1
+	uint32_t* cell_start;    // nH+1 exclusive scan
+	uint32_t* cell_fill;     // nH cursor
 	int* tmp_id;             // per sorted slot: creation id (ranking key)
 	uint32_t* scan_block;    // block sums for the scan
 	size_t scan_block_cap;
@@ -56,6 +57,12 @@ struct fs3_sim {
 	float4* ls_rec;          // per cell: closest particle (n*X, n*Y, n*Z, bits(id)); id<0 = none
 	int* closest;            // per cell creation id (exported)
 	bool closest_valid;
+	// persistent dataflow sweep: tiles in wavefront order, per-tile completion epochs, ticket counter
+	uint32_t* ls_order;      // ntiles packed (Tx | Ty<<10 | Tz<<20), sorted by Tx+Ty+Tz
+	uint32_t* ls_done;       // ntiles: epoch of the last sweep this tile completed
+	uint32_t* ls_ticket;     // 1 word
+	uint32_t ls_epoch;       // host counter: epoch of sweep m of the current call = ls_epoch + m + 1
+	int ls_ntiles, ls_blocks;
 
 	// extrapolation scratch (sized for the largest face grid)
 	int* cdv[3];             // L1 distance, one slot per face grid
@@ -147,6 +154,19 @@ __device__ __forceinline__ float3 fs3_interp(const float* __restrict__ U, const 
 
 // cell of a particle: (int)roundf(n*X) per axis (S3D.cpp:283-288)
 __device__ __forceinline__ int fs3_cell_axis(float p, float n) { return (int)roundf(__fmul_rn(p, n)); }
+// half-cell of a particle on one axis: 2*cell + (n*X >= cell centre).  Half-cell h spans [h/2 - 0.5, h/2) in
+// index space, so the support of any trilinear-hat node is exactly 4 consecutive half-cells per axis.
+__device__ __forceinline__ int fs3_halfcell_axis(float p, float n, int& cell) {
+	float q = __fmul_rn(p, n);
+	float r = roundf(q);
+	cell = (int)r;
+	return 2 * cell + (q >= r ? 1 : 0);
+}
+// particles of cell (cx,cy,cz) = 4 half-rows of 2 consecutive half-cells: visit(range begin, range end)
+#define FS3_FOR_CELL_RANGES(start, d, cx, cy, cz, B, E)                                                          \
+	for (int hr_ = 0; hr_ < 4; hr_++)                                                                            \
+		for (uint32_t hq_ = 0, B = __ldg((start) + (size_t)(2 * (cx)) + (size_t)(2 * (d).nx) * ((size_t)(2 * (cy) + (hr_ & 1)) + (size_t)(2 * (d).ny) * (2 * (cz) + (hr_ >> 1)))), \
+		              E = __ldg((start) + (size_t)(2 * (cx)) + 2 + (size_t)(2 * (d).nx) * ((size_t)(2 * (cy) + (hr_ & 1)) + (size_t)(2 * (d).ny) * (2 * (cz) + (hr_ >> 1)))); hq_ < 1; hq_++)
 
 // ---- host-side launchers implemented in the .cu files -------------------------------------------
 int fs3i_reset(fs3_sim* s);
@@ -167,6 +187,7 @@ int fs3i_export_pressure(fs3_sim* s, double* dev_p, double* dev_b, double* dev_d
 int fs3i_flip_combine(fs3_sim* s, float alpha);                             // old <- cur - (1-alpha) old
 int fs3i_g2p(fs3_sim* s, float alpha);
 int fs3i_alloc_pressure(fs3_sim* s);
+int fs3i_levelset_init(fs3_sim* s);
 int fs3i_staging(fs3_sim* s, size_t bytes);
 int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs);
 int fs3i_extrap_fill(fs3_sim* s, int slot, float* grid, int xs, int ys, int zs);

@@ -1,22 +1,16 @@
 // TransferParticlesToGrid (S3D.cpp:422-612) and ExtrapolateValues (S3D.cpp:614-778) on sm_100a.
 //
-// P2G is a deterministic GATHER over the cell-sorted particles: one thread per face node walks the
-// (2 x 3 x 3) cells whose particles can reach it with the trilinear hat, in (z,y,x) cell order and
-// creation order inside a cell, accumulating sum(w*u) and sum(w) in fp32 exactly as the reference's
-// scatter does per tap (same weights, same guards); only the order of the fp32 additions differs.
-// Normalisation, the validity test and the wall faces are fused into the same kernel, which also
-// initialises the L1-distance grid of the extrapolation.
+// P2G is a deterministic, work-optimal GATHER over the half-cell-sorted particles.  The support of a
+// trilinear-hat node is [m-1, m+1) per axis in the node's own coordinate (n*X, +0.5 on the staggered
+// axis), which is exactly 4 consecutive half-cells per axis, and half-cells are stored x fastest, so one
+// thread per face node walks 4 x 4 contiguous particle runs in which EVERY particle contributes.  The
+// weight is evaluated as 1 - |q - m|: for q in [m-1, m+1] this is bit-identical to the reference's
+// floor/alpha form (q - floor(q) and m - q are exact in fp32), and a particle whose rounded q lands on
+// the support's edge gets weight 0 where the reference has no tap.  sum(w*u) and sum(w) are accumulated
+// in fp32 per tap like the reference's scatter; only the order of the additions differs (run order
+// instead of particle-index order).  Normalisation, the validity test and the wall faces are fused in,
+// and the kernel also initialises the L1-distance grid of the extrapolation.
 #include "fs3_internal.cuh"
-
-// per-axis tap test: does the particle coordinate q (already +0.5 on the staggered axis) touch node m?
-__device__ __forceinline__ bool p2g_axis(float q, int m, float& w) {
-	float fb = floorf(q);
-	int base = (int)fb;
-	float al = __fsub_rn(q, fb);
-	if (m == base) { w = __fsub_rn(1.f, al); return true; }
-	if (m == base + 1) { w = al; return true; }
-	return false;
-}
 
 // AX = staggered axis of this face grid (0:U, 1:V, 2:W).  Grid extents (xs,ys,zs) = cells + 1 on AX.
 template <int AX>
@@ -30,27 +24,29 @@ __global__ void __launch_bounds__(128) k_p2g_gather(const float4* __restrict__ p
 	// wall planes: forced to zero and valid (S3D.cpp:578-599)
 	int m_ax = AX == 0 ? i : (AX == 1 ? j : k), n_ax = AX == 0 ? d.nx : (AX == 1 ? d.ny : d.nz);
 	if (m_ax == 0 || m_ax == n_ax) { grid[q] = 0.f; cd[q] = 0; return; }
-	// cells that can reach this node: staggered axis {m-1, m}; other axes {m-1, m, m+1}
-	int x0 = max(i - 1, 0), x1 = min(AX == 0 ? i : i + 1, d.nx - 1);
-	int y0 = max(j - 1, 0), y1 = min(AX == 1 ? j : j + 1, d.ny - 1);
-	int z0 = max(k - 1, 0), z1 = min(AX == 2 ? k : k + 1, d.nz - 1);
+	// half-cell support: staggered axis [2m-2, 2m+1], other axes [2m-1, 2m+2], clipped to the grid
+	const int HX = 2 * d.nx, HY = 2 * d.ny, HZ = 2 * d.nz;
+	int x0 = max(2 * i - (AX == 0 ? 2 : 1), 0), x1 = min(2 * i + (AX == 0 ? 1 : 2), HX - 1);
+	int y0 = max(2 * j - (AX == 1 ? 2 : 1), 0), y1 = min(2 * j + (AX == 1 ? 1 : 2), HY - 1);
+	int z0 = max(2 * k - (AX == 2 ? 2 : 1), 0), z1 = min(2 * k + (AX == 2 ? 1 : 2), HZ - 1);
+	const float fi = (float)i, fj = (float)j, fk = (float)k;
+	const float* __restrict__ vcomp = reinterpret_cast<const float*>(vel) + AX;
 	float sum = 0.f, amt = 0.f;
-	const double hx = d.nx + 0.5, hy = d.ny + 0.5, hz = d.nz + 0.5;
-	for (int cz = z0; cz <= z1; cz++)
-		for (int cy = y0; cy <= y1; cy++) {
-			size_t row = (size_t)d.nx * ((size_t)cy + (size_t)d.ny * cz);
-			uint32_t b = __ldg(start + row + x0), e = __ldg(start + row + x1 + 1);  // cells of one row are contiguous
+	for (int hz = z0; hz <= z1; hz++)
+		for (int hy = y0; hy <= y1; hy++) {
+			size_t row = (size_t)HX * ((size_t)hy + (size_t)HY * hz);
+			uint32_t b = __ldg(start + row + x0), e = __ldg(start + row + x1 + 1);
 			for (uint32_t t = b; t < e; t++) {
 				float4 p = __ldg(pos + t);
-				float px = __fmul_rn(p.x, cpm), py = __fmul_rn(p.y, cpm), pz = __fmul_rn(p.z, cpm);   // S3D.cpp:442-444
-				if ((double)px < -0.5 || (double)px > hx || (double)py < -0.5 || (double)py > hy || (double)pz < -0.5 || (double)pz > hz) continue;
-				float wx, wy, wz;
-				if (!p2g_axis(AX == 0 ? __fadd_rn(px, 0.5f) : px, i, wx)) continue;
-				if (!p2g_axis(AX == 1 ? __fadd_rn(py, 0.5f) : py, j, wy)) continue;
-				if (!p2g_axis(AX == 2 ? __fadd_rn(pz, 0.5f) : pz, k, wz)) continue;
-				float w = __fmul_rn(__fmul_rn(wx, wy), wz);
-				float4 v = __ldg(vel + t);
-				float u = AX == 0 ? v.x : (AX == 1 ? v.y : v.z);
+				float qx = __fmul_rn(p.x, cpm), qy = __fmul_rn(p.y, cpm), qz = __fmul_rn(p.z, cpm);   // S3D.cpp:442-444
+				if (AX == 0) qx = __fadd_rn(qx, 0.5f);
+				if (AX == 1) qy = __fadd_rn(qy, 0.5f);
+				if (AX == 2) qz = __fadd_rn(qz, 0.5f);
+				float wx = __fsub_rn(1.f, fabsf(__fsub_rn(qx, fi)));
+				float wy = __fsub_rn(1.f, fabsf(__fsub_rn(qy, fj)));
+				float wz = __fsub_rn(1.f, fabsf(__fsub_rn(qz, fk)));
+				float w = __fmul_rn(__fmul_rn(wx, wy), wz);                                           // S3D.cpp:472-474
+				float u = __ldg(vcomp + 4 * (size_t)t);
 				sum = __fadd_rn(sum, __fmul_rn(w, u));
 				amt = __fadd_rn(amt, w);
 			}

@@ -117,7 +117,8 @@ int fs3i_advect(fs3_sim* s, float dt) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// Binning: counting sort of the particles by cell (cell = (int)roundf(n*X), S3D.cpp:286-288).
+// Binning: counting sort of the particles by HALF-cell (cell = (int)roundf(n*X), S3D.cpp:286-288, refined by the
+// particle's octant inside the cell; key on the (2n)^3 half-cell grid, x fastest -- see fs3_halfcell_axis).
 // count -> exclusive scan -> scatter creation ids -> rank inside the cell by creation id -> gather.
 // Ranking by creation id makes the order inside a cell the reference's particle order, so the result
 // is deterministic (no dependence on atomic arrival order) and "lowest index wins" tie-breaks
@@ -128,12 +129,13 @@ __global__ void __launch_bounds__(256) k_bin_count(const float4* __restrict__ po
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	float4 p = pos[i];
-	int cx = fs3_cell_axis(p.x, (float)d.nx), cy = fs3_cell_axis(p.y, (float)d.ny), cz = fs3_cell_axis(p.z, (float)d.nz);
+	int cx, cy, cz;
+	int hx = fs3_halfcell_axis(p.x, (float)d.nx, cx), hy = fs3_halfcell_axis(p.y, (float)d.ny, cy), hz = fs3_halfcell_axis(p.z, (float)d.nz, cz);
 	if (cx < 0 || cx >= d.nx || cy < 0 || cy >= d.ny || cz < 0 || cz >= d.nz) {
 		flags[0] = 1;  // outside the box: the reference skips such particles; Advect's clamp makes this unreachable
-		cx = min(max(cx, 0), d.nx - 1); cy = min(max(cy, 0), d.ny - 1); cz = min(max(cz, 0), d.nz - 1);
+		hx = min(max(hx, 0), 2 * d.nx - 1); hy = min(max(hy, 0), 2 * d.ny - 1); hz = min(max(hz, 0), 2 * d.nz - 1);
 	}
-	uint32_t c = (uint32_t)cx + (uint32_t)d.nx * ((uint32_t)cy + (uint32_t)d.ny * (uint32_t)cz);
+	uint32_t c = (uint32_t)hx + (uint32_t)(2 * d.nx) * ((uint32_t)hy + (uint32_t)(2 * d.ny) * (uint32_t)hz);
 	cellid[i] = c;
 	atomicAdd(count + c, 1u);
 }
@@ -240,20 +242,20 @@ __global__ void __launch_bounds__(256) k_bin_rank_gather(const float4* __restric
 
 int fs3i_bin(fs3_sim* s) {
 	if (s->sorted) return FS3_OK;
-	FS3_CUDA(cudaMemsetAsync(s->cell_count, 0, (s->nC + 1) * sizeof(uint32_t), s->stream));
-	FS3_CUDA(cudaMemsetAsync(s->cell_fill, 0, s->nC * sizeof(uint32_t), s->stream));
+	FS3_CUDA(cudaMemsetAsync(s->cell_count, 0, (s->nH + 1) * sizeof(uint32_t), s->stream));
+	FS3_CUDA(cudaMemsetAsync(s->cell_fill, 0, s->nH * sizeof(uint32_t), s->stream));
 	if (s->np > 0) {
 		GridDims d{s->nx, s->ny, s->nz};
 		int nb = cdiv(s->np, 256);
 		k_bin_count<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, s->cellid, s->cell_count, s->dev_flags); FS3_LAUNCH_CHECK();
-		int rc = scan_u32(s, s->cell_count, s->cell_start, s->nC + 1);
+		int rc = scan_u32(s, s->cell_count, s->cell_start, s->nH + 1);
 		if (rc) return rc;
 		k_bin_scatter_ids<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->cellid, s->np, s->cell_start, s->cell_fill, s->tmp_id); FS3_LAUNCH_CHECK();
 		k_bin_rank_gather<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->cellid, s->np, s->cell_start, s->tmp_id,
 		                                              s->pos[s->cur ^ 1], s->vel[s->cur ^ 1]); FS3_LAUNCH_CHECK();
 		s->cur ^= 1;
 	} else {
-		FS3_CUDA(cudaMemsetAsync(s->cell_start, 0, (s->nC + 1) * sizeof(uint32_t), s->stream));
+		FS3_CUDA(cudaMemsetAsync(s->cell_start, 0, (s->nH + 1) * sizeof(uint32_t), s->stream));
 	}
 	s->sorted = true;
 	return FS3_OK;
