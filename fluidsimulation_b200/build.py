@@ -19,10 +19,12 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, extra_flags=(), suffix=""):
+    """suffix/extra_flags: instrumented side builds (tools/), e.g. suffix="_trace", extra_flags=["-DFS3_LS_TRACE"]."""
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     headers = [os.path.join(CSRC, "fs3_internal.cuh"), os.path.join(os.path.dirname(HERE), "include", "fs3.h")]
-    objdir = os.path.join(HERE, "build")
+    objdir = os.path.join(HERE, "build" + suffix)
+    lib = LIB.replace(".so", suffix + ".so")
     os.makedirs(objdir, exist_ok=True)
     objs, procs = [], []
     for src in SOURCES:
@@ -30,7 +32,7 @@ def build(force=False, verbose=False):
         op = os.path.join(objdir, src.replace(".cu", ".o"))
         objs.append(op)
         if force or _stale(op, [sp] + headers):
-            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", sp, "-o", op]
+            cmd = [nvcc] + NVCC_FLAGS + list(extra_flags) + (["-Xptxas", "-v"] if verbose else []) + ["-c", sp, "-o", op]
             procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     for src, p in procs:
         out, _ = p.communicate()
@@ -38,9 +40,9 @@ def build(force=False, verbose=False):
             sys.stderr.write(out)
         if p.returncode:
             raise RuntimeError("nvcc failed on " + src)
-    if force or procs or _stale(LIB, objs):
-        subprocess.check_call([nvcc, "-shared", "-o", LIB] + objs + ["-lcudart"])
-    return LIB
+    if force or procs or _stale(lib, objs):
+        subprocess.check_call([nvcc, "-shared", "-o", lib] + objs + ["-lcudart"])
+    return lib
 
 
 if __name__ == "__main__":

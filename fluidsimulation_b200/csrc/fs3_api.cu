@@ -89,6 +89,7 @@ int fs3_create(int nx, int ny, int nz, float cpm, int device, fs3_sim** out) {
 	s->prm.record_stage_times = 0;
 	s->nU = (size_t)(nx + 1) * ny * nz; s->nV = (size_t)nx * (ny + 1) * nz; s->nW = (size_t)nx * ny * (nz + 1); s->nC = (size_t)nx * ny * nz;
 	s->launches = 0; s->np = 0; s->cap = 0; s->cur = 0; s->sorted = false; s->closest_valid = false; s->system_valid = false;
+	s->sor_list_valid = false; s->sm_count = prop.multiProcessorCount;
 	s->alloc_precision = -1; s->res_cap = 4096; s->res_count = 0; s->stage_ptr = nullptr; s->stage_bytes = 0;
 	for (int k = 0; k < FS3_T_COUNT; k++) s->stage_ms[k] = 0.f;
 #define CK(call)                                                                                  \
@@ -133,7 +134,7 @@ int fs3_destroy(fs3_sim* s) {
 	void* ptrs[] = {s->U, s->V, s->W, s->oU, s->oV, s->oW, s->phi, s->pos[0], s->pos[1], s->vel[0], s->vel[1], s->cellid, s->cell_count,
 	                s->cell_start, s->cell_fill, s->tmp_id, s->scan_block, s->ls_rec, s->closest, s->cdv[0], s->cdv[1], s->cdv[2], s->orderv[0],
 	                s->orderv[1], s->orderv[2], s->bucket, s->p[0], s->p[1], s->b[0], s->b[1], s->dg[0], s->dg[1], s->mask[0], s->mask[1],
-	                s->res, s->dev_flags, s->ls_order, s->ls_done, s->ls_ticket};
+	                s->res, s->dev_flags, s->ls_order, s->ls_done, s->ls_ticket, s->sor_flags, s->sor_pos[0], s->sor_pos[1], s->sor_list[0], s->sor_list[1]};
 	for (void* p : ptrs) if (p) cudaFree(p);
 	if (s->h_bucket) cudaFreeHost(s->h_bucket);
 	if (s->stage_ptr) cudaFree(s->stage_ptr);

@@ -58,11 +58,12 @@ struct fs3_sim {
 	int* closest;            // per cell creation id (exported)
 	bool closest_valid;
 	// persistent dataflow sweep: tiles in wavefront order, per-tile completion epochs, ticket counter
-	uint32_t* ls_order;      // ntiles packed (Tx | Ty<<10 | Tz<<20), sorted by Tx+Ty+Tz
+	uint32_t* ls_order;      // 8*ntiles work items (Tx | Ty<<9 | Tz<<18 | sweep<<27), sorted by DAG level
 	uint32_t* ls_done;       // ntiles: epoch of the last sweep this tile completed
 	uint32_t* ls_ticket;     // 1 word
 	uint32_t ls_epoch;       // host counter: epoch of sweep m of the current call = ls_epoch + m + 1
-	int ls_ntiles, ls_blocks;
+	int ls_sleep_ns;         // cap of the poll back-off
+	int ls_ntiles, ls_blocks, ls_levels;   // ls_levels = depth of the dependency DAG (critical path in tiles)
 
 	// extrapolation scratch (sized for the largest face grid)
 	int* cdv[3];             // L1 distance, one slot per face grid
@@ -77,6 +78,13 @@ struct fs3_sim {
 	int alloc_precision;
 	unsigned char* mask[2];     // bit0..5: x-,x+,y-,y+,z-,z+ neighbour is fluid; bit6: cell is fluid
 	bool system_valid;
+	// active-vector lists of the two colours (rebuilt by every projection setup)
+	uint32_t* sor_flags;        // nvec+1
+	uint32_t* sor_pos[2];       // nvec+1: exclusive scan of the flags; [nvec] = number of active vectors
+	uint32_t* sor_list[2];      // compacted: vector index | row parity << 31
+	uint32_t* sor_count[2];     // = sor_pos[c] + nvec (device pointer to the list length)
+	bool sor_list_valid;
+	int sm_count;
 	double* res;               // device: [2*i] sum r^2, [2*i+1] max |r| (as double bits)
 	int res_cap, res_count;
 
@@ -172,6 +180,7 @@ __device__ __forceinline__ int fs3_halfcell_axis(float p, float n, int& cell) {
 int fs3i_reset(fs3_sim* s);
 int fs3i_advect(fs3_sim* s, float dt);
 int fs3i_bin(fs3_sim* s);
+int fs3i_scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n);   // exclusive scan on the handle's stream
 int fs3i_unsort_particles(fs3_sim* s, fs3_particle* dev_out);              // creation order AoS into device buffer
 int fs3i_load_particles(fs3_sim* s, const fs3_particle* dev_in, long long count);
 int fs3i_cell_indices(fs3_sim* s, int* dev_out);                            // creation order

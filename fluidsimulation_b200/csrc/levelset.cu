@@ -3,15 +3,18 @@
 //
 // In the sweep with direction signs (sx,sy,sz) a cell only reads its three upwind neighbours, after
 // they were finalised in the same sweep, and its three offers stay in x,y,z order inside one thread.
-// Any schedule that respects that partial order gives the reference's result bit for bit, so tiles of
-// 8x8x8 cells are processed in tile-hyperplane order (one launch per tile plane) and inside a tile the
-// 22 cell hyperplanes run between __syncthreads() with the tile + its upwind halo held in shared memory.
+// Any schedule that respects that partial order gives the reference's result bit for bit, so the grid is
+// cut into 8x8x4 tiles that run as a dataflow (see k_ls_sweep_dataflow) and inside a tile the 18 cell
+// hyperplanes are walked by one warp with the tile + its upwind halo held in shared memory.
 // Each cell carries its closest particle as (n*X, n*Y, n*Z, id): the candidate's position travels with
 // the index, so the dependent chain contains no global gather, and phi is recomputed from it
 // (ptDistance is symmetric in its arguments, S3D.cpp:234-236).
 #include "fs3_internal.cuh"
+#include <vector>
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 
-#define LS_T 8  // tile edge
 
 __device__ __forceinline__ float ls_dist(float cx, float cy, float cz, float4 q, float radius) {
 	float dx = __fsub_rn(cx, q.x), dy = __fsub_rn(cy, q.y), dz = __fsub_rn(cz, q.z);
@@ -43,138 +46,259 @@ __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos,
 	rec[c] = best;
 }
 
-// All 8 sweeps in ONE persistent launch, scheduled as a dataflow over 8x8x8 tiles.
-// Tiles are a fixed partition of physical space.  Work items (sweep m, tile) are handed out through a
-// ticket counter in sweep-major, tile-hyperplane order; a block that holds an item waits (polling the
-// per-tile completion epochs in L2) until
+// All 8 sweeps in ONE persistent launch, scheduled as a dataflow over 8x8x4 tiles, ONE WARP PER TILE.
+// Tiles are a fixed partition of physical space.  A work item is (sweep m, tile); the host orders all
+// 8*ntiles items by their earliest possible start level in the dependency DAG (fs3i_levelset_init), and
+// warps draw items through a ticket counter.  A warp that holds an item waits (polling per-tile
+// completion epochs in L2) until
 //   * the tile itself and its 6 face neighbours have completed sweep m-1 (RAW on its own cells, WAR on
 //     the halo cells its neighbours read in sweep m-1), and
 //   * its 3 upwind neighbours have completed sweep m (RAW on the halo),
-// all of which hold lower tickets, so some running block can always make progress (no co-residency
-// assumption, no grid-wide barrier).  Inside a tile the 22 cell hyperplanes run between
-// __syncthreads() with the tile and a one-cell halo in shared memory.  Consecutive sweeps overlap
-// wherever the dependencies allow.  Records are read/written with L2-only accesses (ld.cg / st.cg):
-// L1 is not coherent across SMs.
-__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
+// all of which hold lower tickets, so some running warp can always make progress (no co-residency
+// assumption, no grid-wide barrier), and consecutive sweeps pipeline behind each other as far as the
+// DAG allows.  The sweep is latency-bound (the DAG is ~600 tiles deep at 256^3), so the tile is shaped
+// for the shortest serial chain: 32 x-lines of 8 cells, one line per lane, 18 cell hyperplanes walked
+// with only __syncwarp() between them; the tile and its three upwind halo faces sit in the warp's
+// private shared memory in SWEEP space (index 0 = most upwind) so that one code path serves all 8
+// directions.  Candidates are first compared by squared distance (sqrt and "- radius" are monotonic,
+// so a candidate that is not closer in d^2 can never win the reference's `dist < phi` test); the full
+// reference expression decides the rest.  Records move with cp.async.cg / st.cg (L2 only: L1 is not
+// coherent across SMs).  The last sweep also writes phi and closestParticles[].
+#define LS_TX 8
+#define LS_TY 8
+#define LS_TZ 4
+#define LS_PX (LS_TX + 2)   // x pitch 10: on a hyperplane a+b+c=s the 8 lanes of a quarter warp hit 8 different 16-byte bank groups (pitch 9 puts all 32 in one)
+#define LS_PY (LS_TY + 1)
+#define LS_PZ (LS_TZ + 1)
+#define LS_STEPS (LS_TX + LS_TY + LS_TZ - 2)
+#define LS_WARPS 8
+#define LS_SMEM_BYTES (LS_WARPS * LS_SM_PER_WARP * (sizeof(float4) + sizeof(float)))
+#define LS_SM_PER_WARP (LS_PX * LS_PY * LS_PZ)
 
-__global__ void __launch_bounds__(LS_T* LS_T* LS_T) k_ls_sweep_dataflow(float4* __restrict__ rec, GridDims d, float radius,
-                                                                       const uint32_t* __restrict__ order, uint32_t* done,
-                                                                       uint32_t* ticket, int ntiles, int ntx, int nty, int ntz,
-                                                                       uint32_t epoch0, int* __restrict__ flags) {
-	const int P = LS_T + 2;
-	__shared__ float4 sm[P * P * P];
-	__shared__ uint32_t s_ticket;
-	__shared__ int s_abort;
-#define SM(i, j, k) sm[((i) + 1) + P * (((j) + 1) + P * ((k) + 1))]
-	const int tid = threadIdx.x;
-	const int lx = tid % LS_T, ly = (tid / LS_T) % LS_T, lz = tid / (LS_T * LS_T);
-	if (tid == 0) s_abort = 0;
-	for (;;) {
-		__syncthreads();  // previous item fully retired (smem reuse, s_ticket reuse)
-		if (tid == 0) s_ticket = atomicAdd(ticket, 1u);
-		__syncthreads();
-		const uint32_t t = s_ticket;
-		if (t >= 8u * (uint32_t)ntiles || s_abort) break;
-		const int m = (int)(t / (uint32_t)ntiles);
-		const uint32_t packed = order[t % (uint32_t)ntiles];
-		const int fx = m & 1, fy = (m >> 1) & 1, fz = (m >> 2) & 1;   // sweep order of S3D.cpp:306-416
-		// tile in sweep space -> physical tile
-		const int Tx = fx ? ntx - 1 - (int)(packed & 1023u) : (int)(packed & 1023u);
-		const int Ty = fy ? nty - 1 - (int)((packed >> 10) & 1023u) : (int)((packed >> 10) & 1023u);
-		const int Tz = fz ? ntz - 1 - (int)(packed >> 20) : (int)(packed >> 20);
-		const int dx = fx ? -1 : 1, dy = fy ? -1 : 1, dz = fz ? -1 : 1;   // sweep direction per axis
-		const uint32_t E = epoch0 + (uint32_t)m + 1u;
-		// ---- wait for the dependencies: threads 0..6 poll one tile each ------------------------------
-		if (tid < 7) {
-			int qx = Tx, qy = Ty, qz = Tz;
-			uint32_t need = E - 1u;
-			if (tid == 1) qx -= 1; else if (tid == 2) qx += 1; else if (tid == 3) qy -= 1; else if (tid == 4) qy += 1;
-			else if (tid == 5) qz -= 1; else if (tid == 6) qz += 1;
-			if ((tid == 1 && dx > 0) || (tid == 2 && dx < 0) || (tid == 3 && dy > 0) || (tid == 4 && dy < 0) || (tid == 5 && dz > 0) ||
-			    (tid == 6 && dz < 0))
-				need = E;   // upwind neighbour: must have finished THIS sweep
-			if (qx >= 0 && qx < ntx && qy >= 0 && qy < nty && qz >= 0 && qz < ntz) {
-				const uint32_t* f = done + ((size_t)qx + (size_t)ntx * ((size_t)qy + (size_t)nty * qz));
-				long long t0 = clock64();
-				while ((int32_t)(ld_volatile_u32(f) - need) < 0) {
-					__nanosleep(40);
-					if (clock64() - t0 > 4000000000LL) { flags[1] = 1; s_abort = 1; break; }   // ~2 s: never hang the GPU
-				}
-			}
-			__threadfence();
-		}
-		__syncthreads();
-		if (s_abort) break;
-		// ---- load the tile and its three upwind halo faces ---------------------------------------------
-		const int x0 = Tx * LS_T, y0 = Ty * LS_T, z0 = Tz * LS_T;
-		const int wx = min(LS_T, d.nx - x0), wy = min(LS_T, d.ny - y0), wz = min(LS_T, d.nz - z0);
-		const int gx = x0 + lx, gy = y0 + ly, gz = z0 + lz;
-		const bool inside = lx < wx && ly < wy && lz < wz;
-		const size_t gi = (size_t)gx + (size_t)d.nx * ((size_t)gy + (size_t)d.ny * gz);
-		float4 mine = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-		if (inside) mine = __ldcg(rec + gi);
-		SM(lx, ly, lz) = mine;
-		if (tid < 3 * LS_T * LS_T) {
-			const int f = tid / (LS_T * LS_T), a = tid % LS_T, b = (tid / LS_T) % LS_T;
-			// face f: the plane just upwind of the tile on axis f
-			int hx = f == 0 ? (dx > 0 ? -1 : wx) : a;
-			int hy = f == 1 ? (dy > 0 ? -1 : wy) : (f == 0 ? a : b);
-			int hz = f == 2 ? (dz > 0 ? -1 : wz) : b;
-			const int qx = x0 + hx, qy = y0 + hy, qz = z0 + hz;
-			float4 h = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-			if (qx >= 0 && qy >= 0 && qz >= 0 && qx < d.nx && qy < d.ny && qz < d.nz)
-				h = __ldcg(rec + ((size_t)qx + (size_t)d.nx * ((size_t)qy + (size_t)d.ny * qz)));
-			if (hx <= LS_T && hy <= LS_T && hz <= LS_T) SM(hx, hy, hz) = h;
-		}
-		__syncthreads();
-		// ---- 22 cell hyperplanes inside the tile ----------------------------------------------------------
-		const float cx = (float)gx, cy = (float)gy, cz = (float)gz;
-		int myid = __float_as_int(mine.w);
-		float myphi = myid >= 0 ? ls_dist(cx, cy, cz, mine, radius) : 0.f;
-		bool changed = false;
-		const int mystep = (dx > 0 ? lx : wx - 1 - lx) + (dy > 0 ? ly : wy - 1 - ly) + (dz > 0 ? lz : wz - 1 - lz);
-		const bool hasx = dx > 0 ? gx != 0 : gx != d.nx - 1, hasy = dy > 0 ? gy != 0 : gy != d.ny - 1, hasz = dz > 0 ? gz != 0 : gz != d.nz - 1;
-		for (int step = 0; step <= 3 * (LS_T - 1); step++) {
-			if (step == mystep && inside) {
-				// clsInner on the upwind x-, y-, z-neighbour in that order (S3D.cpp:310-315 and siblings):
-				// index <= 0 is never propagated (:242); strict `<` keeps the incumbent (:248).
-#pragma unroll
-				for (int a = 0; a < 3; a++) {
-					const bool has = a == 0 ? hasx : (a == 1 ? hasy : hasz);
-					if (!has) continue;
-					const float4 cand = a == 0 ? SM(lx - dx, ly, lz) : (a == 1 ? SM(lx, ly - dy, lz) : SM(lx, ly, lz - dz));
-					if (__float_as_int(cand.w) > 0) {
-						const float dd = ls_dist(cx, cy, cz, cand, radius);
-						if (myid < 0 || dd < myphi) { mine = cand; myid = __float_as_int(cand.w); myphi = dd; changed = true; }
-					}
-				}
-				SM(lx, ly, lz) = mine;
-			}
-			__syncthreads();
-		}
-		if (changed) __stcg(rec + gi, mine);
-		// ---- publish: all stores of the block, then the epoch -------------------------------------------
-		__threadfence();
-		__syncthreads();
-		if (tid == 0) {
-			*reinterpret_cast<volatile uint32_t*>(done + ((size_t)Tx + (size_t)ntx * ((size_t)Ty + (size_t)nty * Tz))) = E;
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+	unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+	uint32_t v;
+	asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) { asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory"); }
+
+// false = gave up (another warp aborted, or ~2 s without progress: never hang the GPU)
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+	uint32_t v;
+	asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+	return v;
+}
+// Polls with relaxed loads and a capped exponential back-off (waiting warps share the SM with the warps
+// that are computing), then takes the acquire once the epoch is there.
+__device__ __forceinline__ bool ls_wait(const uint32_t* f, uint32_t need, int* flags, unsigned sleep_max) {
+	if ((int32_t)(ld_acquire_u32(f) - need) >= 0) return true;
+	long long t0 = clock64();
+	unsigned ns = 32;
+	for (unsigned it = 1;; it++) {
+		if ((int32_t)(ld_relaxed_u32(f) - need) >= 0) break;
+		__nanosleep(ns);
+		ns = min(ns * 2, sleep_max);
+		if ((it & 255u) == 0) {
+			if (*reinterpret_cast<volatile int*>(flags + 1)) return false;
+			if (clock64() - t0 > 4000000000LL) { flags[1] = 1; return false; }
 		}
 	}
-#undef SM
+	return (int32_t)(ld_acquire_u32(f) - need) >= 0;
 }
 
-// phi and closestParticles[] from the records; cells never reached keep their previous phi, as in
-// the reference where m_Phi is only written together with closestParticles (S3D.cpp:248-251,296-299).
-__global__ void __launch_bounds__(256) k_ls_finalize(const float4* __restrict__ rec, GridDims d, float radius, float* __restrict__ phi,
-                                                     int* __restrict__ closest) {
-	size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	size_t nc = (size_t)d.nx * d.ny * d.nz;
-	if (c >= nc) return;
-	int x = (int)(c % d.nx), y = (int)((c / d.nx) % d.ny), z = (int)(c / ((size_t)d.nx * d.ny));
-	float4 r = rec[c];
-	int id = __float_as_int(r.w);
-	closest[c] = id;
-	if (id >= 0) phi[c] = ls_dist((float)x, (float)y, (float)z, r, radius);
+__device__ __forceinline__ float ls_d2(float cx, float cy, float cz, float4 q) {
+	float dx = __fsub_rn(cx, q.x), dy = __fsub_rn(cy, q.y), dz = __fsub_rn(cz, q.z);
+	return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));   // ptDistance's radicand, S3D.cpp:234-236
+}
+
+#ifdef FS3_LS_TRACE
+__device__ unsigned long long* g_ls_trace;   // 8 timestamps per work item (debug builds only, tools/ls_trace.py)
+__device__ __forceinline__ unsigned long long ls_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define LS_MARK(k) do { if (lane == 0) g_ls_trace[(size_t)t * 8 + (k)] = ls_now(); } while (0)
+#else
+#define LS_MARK(k) do { } while (0)
+#endif
+
+__global__ void __launch_bounds__(32 * LS_WARPS) k_ls_sweep_dataflow(float4* __restrict__ rec, GridDims d, float radius,
+                                                                     const uint32_t* __restrict__ items, uint32_t* done, uint32_t* ticket,
+                                                                     uint32_t nitems, int ntx, int nty, int ntz, uint32_t epoch0,
+                                                                     int* __restrict__ flags, float* __restrict__ phi, int* __restrict__ closest, unsigned sleep_max) {
+	extern __shared__ float4 ls_smem[];
+	const unsigned FULL = 0xffffffffu;
+	const int lane = threadIdx.x & 31;
+	float4* sm = ls_smem + (threadIdx.x >> 5) * LS_SM_PER_WARP;
+	float* m2s = reinterpret_cast<float*>(ls_smem + LS_WARPS * LS_SM_PER_WARP) + (threadIdx.x >> 5) * LS_SM_PER_WARP;
+#define SMI(a, b, c) (((a) + 1) + LS_PX * (((b) + 1) + LS_PY * ((c) + 1)))
+	const float4 none = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+	const size_t sY = (size_t)d.nx, sZ = (size_t)d.nx * d.ny;
+	for (;;) {
+		uint32_t t = 0;
+		if (lane == 0) t = atomicAdd(ticket, 1u);
+		t = __shfl_sync(FULL, t, 0);
+		if (t >= nitems) break;
+		LS_MARK(0);
+		const uint32_t it = __ldg(items + t);
+		const int m = (int)(it >> 27), Tx = (int)(it & 511u), Ty = (int)((it >> 9) & 511u), Tz = (int)((it >> 18) & 511u);
+		const int dx = (m & 1) ? -1 : 1, dy = (m & 2) ? -1 : 1, dz = (m & 4) ? -1 : 1;   // sweep order of S3D.cpp:306-416
+		const uint32_t E = epoch0 + (uint32_t)m + 1u;
+		const int x0 = Tx * LS_TX, y0 = Ty * LS_TY, z0 = Tz * LS_TZ;
+		const int wx = min(LS_TX, d.nx - x0), wy = min(LS_TY, d.ny - y0), wz = min(LS_TZ, d.nz - z0);
+		uint32_t* const mydone = done + ((size_t)Tx + (size_t)ntx * ((size_t)Ty + (size_t)nty * Tz));
+		// ---- own cells are final once this tile has completed sweep m-1: start their copy first ----------
+		bool ok = true;
+		if (lane == 0) ok = ls_wait(mydone, E - 1u, flags, sleep_max);
+		if (!__all_sync(FULL, ok)) break;
+		LS_MARK(1);
+		{
+			const int px = lane & 7;
+			const int a = (px < wx && dx < 0) ? wx - 1 - px : px;
+#pragma unroll
+			for (int i = 0; i < LS_TY * LS_TZ / 4; i++) {
+				const int row = (lane >> 3) + 4 * i, py = row & 7, pz = row >> 3;
+				const int b = (py < wy && dy < 0) ? wy - 1 - py : py, c = (pz < wz && dz < 0) ? wz - 1 - pz : pz;
+				if (px < wx && py < wy && pz < wz) cp_async16(sm + SMI(a, b, c), rec + ((size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)(z0 + pz)));
+				else sm[SMI(a, b, c)] = none;
+			}
+		}
+		// ---- the six neighbours: upwind ones must have finished THIS sweep, the others the previous one ---
+		if (lane >= 1 && lane <= 6) {
+			const int ax = (lane - 1) >> 1, sgn = (lane & 1) ? -1 : 1;   // lanes 1,2: x-,x+   3,4: y-,y+   5,6: z-,z+
+			const int qx = Tx + (ax == 0 ? sgn : 0), qy = Ty + (ax == 1 ? sgn : 0), qz = Tz + (ax == 2 ? sgn : 0);
+			const int dir = ax == 0 ? dx : (ax == 1 ? dy : dz);
+			if (qx >= 0 && qx < ntx && qy >= 0 && qy < nty && qz >= 0 && qz < ntz)
+				ok = ls_wait(done + ((size_t)qx + (size_t)ntx * ((size_t)qy + (size_t)nty * qz)), sgn == -dir ? E : E - 1u, flags, sleep_max);
+		}
+		if (!__all_sync(FULL, ok)) break;
+		LS_MARK(2);
+		// ---- three upwind halo faces (sweep coordinate -1 on one axis) ---------------------------------------
+		{
+			// x face: (b, c) = 8 x 4 cells, one per lane
+			const int b = lane & 7, c = lane >> 3;
+			const int qx = dx > 0 ? x0 - 1 : x0 + wx, qy = y0 + (dy > 0 ? b : wy - 1 - b), qz = z0 + (dz > 0 ? c : wz - 1 - c);
+			if (b < wy && c < wz && qx >= 0 && qx < d.nx) cp_async16(sm + SMI(-1, b, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
+			else sm[SMI(-1, b, c)] = none;
+		}
+		{
+			// y face: (a, c) = 8 x 4 cells, one per lane
+			const int a = lane & 7, c = lane >> 3;
+			const int qx = x0 + (dx > 0 ? a : wx - 1 - a), qy = dy > 0 ? y0 - 1 : y0 + wy, qz = z0 + (dz > 0 ? c : wz - 1 - c);
+			if (a < wx && c < wz && qy >= 0 && qy < d.ny) cp_async16(sm + SMI(a, -1, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
+			else sm[SMI(a, -1, c)] = none;
+		}
+#pragma unroll
+		for (int i = 0; i < 2; i++) {
+			// z face: (a, b) = 8 x 8 cells, two per lane
+			const int a = lane & 7, b = (lane >> 3) + 4 * i;
+			const int qx = x0 + (dx > 0 ? a : wx - 1 - a), qy = y0 + (dy > 0 ? b : wy - 1 - b), qz = dz > 0 ? z0 - 1 : z0 + wz;
+			if (a < wx && b < wy && qz >= 0 && qz < d.nz) cp_async16(sm + SMI(a, b, -1), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
+			else sm[SMI(a, b, -1)] = none;
+		}
+		cp_async_wait_all();
+		__syncwarp();
+		LS_MARK(3);
+		// ---- 18 cell hyperplanes; lane = line (b, c), marching along a ---------------------------------------
+		// Branch-free on the hot path: every lane runs every step on addresses that stay inside the warp's own
+		// shared-memory region (inactive lanes compute garbage and store nothing).
+		{
+			const int b = lane & 7, c = lane >> 3;
+			const bool line_in = b < wy && c < wz;
+			const int gy = y0 + (dy > 0 ? b : wy - 1 - b), gz = z0 + (dz > 0 ? c : wz - 1 - c);
+			const float cyf = (float)gy, czf = (float)gz;
+			const int li = SMI(0, b, c);
+			const int gx0 = dx > 0 ? x0 : x0 + wx - 1;
+			float4* const grow = rec + (sY * (size_t)gy + sZ * (size_t)gz);
+			// squared distance of every own cell to its current record (off the dependent chain)
+			// Quiet-tile test, fully parallel (no dependent chain): if no cell would accept any of its three
+			// upwind candidates as they stand BEFORE the sweep (q2 < m2 is necessary for acceptance), then by
+			// induction along the sweep order the Gauss-Seidel pass changes nothing and the 18 steps are skipped.
+			bool maybe = false;
+			{
+				float4 r8[LS_TX + 1];
+#pragma unroll
+				for (int a = -1; a < LS_TX; a++) r8[a + 1] = sm[li + a];
+#pragma unroll
+				for (int a = 0; a < LS_TX; a++) {
+					const float cxf = (float)(gx0 + dx * a);
+					const float4 Y = sm[li + a - LS_PX], Z = sm[li + a - LS_PX * LS_PY];
+					const float m2 = ls_d2(cxf, cyf, czf, r8[a + 1]);
+					m2s[li + a] = m2;
+					const int myid = __float_as_int(r8[a + 1].w), idX = __float_as_int(r8[a].w), idY = __float_as_int(Y.w), idZ = __float_as_int(Z.w);
+					const bool wX = idX > 0 && idX != myid && (myid < 0 || ls_d2(cxf, cyf, czf, r8[a]) < m2);
+					const bool wY = idY > 0 && idY != myid && (myid < 0 || ls_d2(cxf, cyf, czf, Y) < m2);
+					const bool wZ = idZ > 0 && idZ != myid && (myid < 0 || ls_d2(cxf, cyf, czf, Z) < m2);
+					maybe |= (a < wx) && (wX || wY || wZ);
+				}
+			}
+			const bool quiet = !__any_sync(FULL, maybe && line_in);   // (also orders the m2s stores before the loop)
+#ifdef FS3_LS_TRACE
+			if (lane == 0 && quiet) g_ls_trace[(size_t)t * 8 + 6] = 1;
+#endif
+			uint32_t chg = 0;
+			for (int s = 0; s < (quiet ? 0 : LS_STEPS); s++) {
+				const int a = s - b - c;
+				const bool act = line_in && (unsigned)a < (unsigned)wx;
+				const float4* q = sm + li + a;
+				float4 mine = q[0];
+				const float4 X = q[-1], Y = q[-LS_PX], Z = q[-LS_PX * LS_PY];
+				float m2 = m2s[li + a];
+				const int gx = gx0 + dx * a;
+				const float cxf = (float)gx;
+				int myid = __float_as_int(mine.w);
+				const int idX = __float_as_int(X.w), idY = __float_as_int(Y.w), idZ = __float_as_int(Z.w);
+				const float x2 = ls_d2(cxf, cyf, czf, X), y2 = ls_d2(cxf, cyf, czf, Y), z2 = ls_d2(cxf, cyf, czf, Z);
+				bool changed = false;
+				// clsInner on the upwind x-, y-, z-neighbour in that order (S3D.cpp:310-315 and siblings): index <= 0 is
+				// never propagated (:242); strict `<` keeps the incumbent (:248).  Same id = same record = no change.
+				// `sure`: q2 < m2 by more than 2^-21 relative with sqrt(m2) >= 0.5 implies sqrt(q2)-r < sqrt(m2)-r in
+				// fp32 (the sqrt values differ by >= 1 ulp and sqrt(m2)-1 is exact); anything closer takes the
+				// reference's full expression.
+#define LS_TRY(Q, idQ, q2)                                                                                                   \
+	{                                                                                                                        \
+		const bool valid = idQ > 0 && idQ != myid;                                                                           \
+		const bool sure = m2 >= 0.25f && q2 < __fmul_rn(m2, 0.99999905f);                                                    \
+		bool take = valid && (myid < 0 || sure);                                                                             \
+		if (valid && myid >= 0 && !sure && q2 < m2) take = __fsub_rn(sqrtf(q2), radius) < __fsub_rn(sqrtf(m2), radius);      \
+		mine.x = take ? Q.x : mine.x; mine.y = take ? Q.y : mine.y; mine.z = take ? Q.z : mine.z; mine.w = take ? Q.w : mine.w; \
+		myid = take ? idQ : myid; m2 = take ? q2 : m2; changed |= take;                                                      \
+	}
+				LS_TRY(X, idX, x2)
+				LS_TRY(Y, idY, y2)
+				LS_TRY(Z, idZ, z2)
+#undef LS_TRY
+				// global write-back is deferred past the loop: __syncwarp() orders memory, so a store in flight
+				// would put an L2 round trip into every step
+				if (act && changed) { sm[li + a] = mine; m2s[li + a] = m2; chg |= 1u << a; }
+				__syncwarp();
+			}
+#pragma unroll
+			for (int a = 0; a < LS_TX; a++)
+				if ((chg >> a) & 1u) __stcg(grow + (gx0 + dx * a), sm[li + a]);
+			if (m == 7 && line_in) {
+				// cells never reached keep their previous phi, as in the reference where m_Phi is only written
+				// together with closestParticles (S3D.cpp:248-251,296-299)
+				const size_t g0 = sY * (size_t)gy + sZ * (size_t)gz;
+#pragma unroll
+				for (int a = 0; a < LS_TX; a++) {
+					if (a < wx) {
+						const int id = __float_as_int(sm[li + a].w);
+						const size_t gi = g0 + (size_t)(gx0 + dx * a);
+						closest[gi] = id;
+						if (id >= 0) phi[gi] = __fsub_rn(sqrtf(m2s[li + a]), radius);
+					}
+				}
+			}
+		}
+		// ---- publish: the warp's stores, then the epoch (release is cumulative over the barrier) -----------
+		LS_MARK(4);
+		if (lane == 0) st_release_u32(mydone, E);
+		LS_MARK(5);
+	}
+#undef SMI
 }
 
 int fs3i_levelset(fs3_sim* s) {
@@ -186,45 +310,97 @@ int fs3i_levelset(fs3_sim* s) {
 	k_ls_seed<<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->cell_start, d, radius, s->ls_rec);
 	FS3_LAUNCH_CHECK();
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SWEEP], s->stream);
-	int ntx = cdiv(d.nx, LS_T), nty = cdiv(d.ny, LS_T), ntz = cdiv(d.nz, LS_T);
+	int ntx = cdiv(d.nx, LS_TX), nty = cdiv(d.ny, LS_TY), ntz = cdiv(d.nz, LS_TZ);
 	FS3_CUDA(cudaMemsetAsync(s->ls_ticket, 0, sizeof(uint32_t), s->stream));
-	k_ls_sweep_dataflow<<<s->ls_blocks, LS_T * LS_T * LS_T, 0, s->stream>>>(s->ls_rec, d, radius, s->ls_order, s->ls_done, s->ls_ticket,
-	                                                                         s->ls_ntiles, ntx, nty, ntz, s->ls_epoch, s->dev_flags);
+#ifdef FS3_LS_TRACE
+	static unsigned long long* trace_dev = nullptr;
+	const size_t trace_n = (size_t)8 * s->ls_ntiles * 8;
+	if (!trace_dev) { FS3_CUDA(cudaMalloc((void**)&trace_dev, trace_n * 8)); FS3_CUDA(cudaMemcpyToSymbol(g_ls_trace, &trace_dev, sizeof(trace_dev))); }
+	FS3_CUDA(cudaMemsetAsync(trace_dev, 0, trace_n * 8, s->stream));
+#endif
+	k_ls_sweep_dataflow<<<s->ls_blocks, 32 * LS_WARPS, LS_SMEM_BYTES, s->stream>>>(
+	    s->ls_rec, d, radius, s->ls_order, s->ls_done, s->ls_ticket, 8u * (uint32_t)s->ls_ntiles, ntx, nty, ntz, s->ls_epoch, s->dev_flags, s->phi,
+	    s->closest, (unsigned)s->ls_sleep_ns);
 	FS3_LAUNCH_CHECK();
 	s->ls_epoch += 8;
-	k_ls_finalize<<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(s->ls_rec, d, radius, s->phi, s->closest);
-	FS3_LAUNCH_CHECK();
 	s->closest_valid = true;
+#ifdef FS3_LS_TRACE
+	if (const char* path = getenv("FS3_LS_TRACE_FILE")) {
+		std::vector<unsigned long long> h(trace_n);
+		std::vector<uint32_t> ord((size_t)8 * s->ls_ntiles);
+		FS3_CUDA(cudaStreamSynchronize(s->stream));
+		FS3_CUDA(cudaMemcpy(h.data(), trace_dev, trace_n * 8, cudaMemcpyDeviceToHost));
+		FS3_CUDA(cudaMemcpy(ord.data(), s->ls_order, ord.size() * 4, cudaMemcpyDeviceToHost));
+		if (FILE* fp = fopen(path, "wb")) { fwrite(h.data(), 8, trace_n, fp); fwrite(ord.data(), 4, ord.size(), fp); fclose(fp); }
+	}
+#endif
 	return FS3_OK;
 }
 
-// tile order table, completion epochs and the persistent grid size (called once from fs3_create)
-#include <vector>
-#include <algorithm>
+// Work-item table, completion epochs and the persistent grid size (called once from fs3_create).
+// Items (sweep m, tile) are sorted by their level in the dependency DAG -- the earliest "time" at which the
+// item could run if every item took one unit -- which is a topological order (every dependency has a
+// strictly smaller level), so ticket order is deadlock-free, and it lets sweep m+1 start behind sweep m as
+// soon as the DAG allows instead of after it.
 int fs3i_levelset_init(fs3_sim* s) {
-	int ntx = cdiv(s->nx, LS_T), nty = cdiv(s->ny, LS_T), ntz = cdiv(s->nz, LS_T);
-	if (ntx > 1023 || nty > 1023 || ntz > 1023) { s->err = "grid too large for the level-set tile table"; return FS3_ERR_INVALID; }
-	int nt = ntx * nty * ntz;
-	std::vector<uint32_t> ord;
-	ord.reserve(nt);
-	for (int w = 0; w <= ntx + nty + ntz - 3; w++)
-		for (int tz = 0; tz < ntz; tz++)
-			for (int ty = 0; ty < nty; ty++) {
-				int tx = w - ty - tz;
-				if (tx >= 0 && tx < ntx) ord.push_back((uint32_t)tx | ((uint32_t)ty << 10) | ((uint32_t)tz << 20));
-			}
-	FS3_CUDA(cudaMalloc((void**)&s->ls_order, sizeof(uint32_t) * nt));
+	const int ntx = cdiv(s->nx, LS_TX), nty = cdiv(s->ny, LS_TY), ntz = cdiv(s->nz, LS_TZ);
+	if (ntx > 511 || nty > 511 || ntz > 511) { s->err = "grid too large for the level-set tile table"; return FS3_ERR_INVALID; }
+	const int nt = ntx * nty * ntz;
+	auto tid = [&](int x, int y, int z) { return x + ntx * (y + nty * z); };
+	std::vector<int> prev(nt, -1), cur(nt, 0);
+	std::vector<std::pair<int, uint32_t>> items;
+	items.reserve((size_t)8 * nt);
+	int maxlevel = 0;
+	for (int m = 0; m < 8; m++) {
+		const int dx = (m & 1) ? -1 : 1, dy = (m & 2) ? -1 : 1, dz = (m & 4) ? -1 : 1;
+		for (int kz = 0; kz < ntz; kz++)
+			for (int ky = 0; ky < nty; ky++)
+				for (int kx = 0; kx < ntx; kx++) {   // sweep-space order: upwind neighbours are visited first
+					const int x = dx > 0 ? kx : ntx - 1 - kx, y = dy > 0 ? ky : nty - 1 - ky, z = dz > 0 ? kz : ntz - 1 - kz;
+					int L = 0;
+					if (kx > 0) L = std::max(L, cur[tid(x - dx, y, z)] + 1);
+					if (ky > 0) L = std::max(L, cur[tid(x, y - dy, z)] + 1);
+					if (kz > 0) L = std::max(L, cur[tid(x, y, z - dz)] + 1);
+					if (m > 0) {
+						L = std::max(L, prev[tid(x, y, z)] + 1);
+						if (x > 0) L = std::max(L, prev[tid(x - 1, y, z)] + 1);
+						if (x < ntx - 1) L = std::max(L, prev[tid(x + 1, y, z)] + 1);
+						if (y > 0) L = std::max(L, prev[tid(x, y - 1, z)] + 1);
+						if (y < nty - 1) L = std::max(L, prev[tid(x, y + 1, z)] + 1);
+						if (z > 0) L = std::max(L, prev[tid(x, y, z - 1)] + 1);
+						if (z < ntz - 1) L = std::max(L, prev[tid(x, y, z + 1)] + 1);
+					}
+					cur[tid(x, y, z)] = L;
+					maxlevel = std::max(maxlevel, L);
+					items.emplace_back(L, (uint32_t)x | ((uint32_t)y << 9) | ((uint32_t)z << 18) | ((uint32_t)m << 27));
+				}
+		prev = cur;
+	}
+	std::stable_sort(items.begin(), items.end(), [](const std::pair<int, uint32_t>& a, const std::pair<int, uint32_t>& b) { return a.first < b.first; });
+	std::vector<uint32_t> ord(items.size());
+	for (size_t i = 0; i < items.size(); i++) ord[i] = items[i].second;
+	FS3_CUDA(cudaMalloc((void**)&s->ls_order, sizeof(uint32_t) * ord.size()));
 	FS3_CUDA(cudaMalloc((void**)&s->ls_done, sizeof(uint32_t) * nt));
 	FS3_CUDA(cudaMalloc((void**)&s->ls_ticket, sizeof(uint32_t)));
-	FS3_CUDA(cudaMemcpyAsync(s->ls_order, ord.data(), sizeof(uint32_t) * nt, cudaMemcpyHostToDevice, s->stream));
+	FS3_CUDA(cudaMemcpyAsync(s->ls_order, ord.data(), sizeof(uint32_t) * ord.size(), cudaMemcpyHostToDevice, s->stream));
 	FS3_CUDA(cudaMemsetAsync(s->ls_done, 0, sizeof(uint32_t) * nt, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	s->ls_ntiles = nt;
+	s->ls_levels = maxlevel + 1;
 	s->ls_epoch = 0;
 	int per_sm = 0, sms = 0;
-	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ls_sweep_dataflow, LS_T * LS_T * LS_T, 0));
+	const size_t smem = LS_SMEM_BYTES;
+	FS3_CUDA(cudaFuncSetAttribute(k_ls_sweep_dataflow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ls_sweep_dataflow, 32 * LS_WARPS, smem));
 	FS3_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
+	// Two blocks (16 warps) per SM measured best at 256^3: more resident warps only add pollers that compete
+	// with the computing warps for issue slots.  Tunables (debug): FS3_LS_BLOCKS_PER_SM, FS3_LS_SLEEP_NS.
+	const int occ = std::max(1, per_sm);   // never more than can be co-resident: waiting warps must not block ticket holders
+	per_sm = std::min(occ, 2);
+	if (const char* e = getenv("FS3_LS_BLOCKS_PER_SM")) per_sm = std::min(occ, std::max(1, atoi(e)));
+	s->ls_sleep_ns = 256;
+	if (const char* e = getenv("FS3_LS_SLEEP_NS")) s->ls_sleep_ns = std::max(20, atoi(e));
 	long long blocks = (long long)std::max(1, per_sm) * sms;
-	s->ls_blocks = (int)std::min<long long>(blocks, 8LL * nt);
+	s->ls_blocks = (int)std::min<long long>(blocks, (8LL * nt + LS_WARPS - 1) / LS_WARPS);
 	return FS3_OK;
 }

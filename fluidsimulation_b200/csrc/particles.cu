@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_apply(const uint32_t* __restric
 	for (int k = 0; k < SCAN_I; k++) { if (base + k < n) out[base + k] = ex; ex += loc[k]; }
 }
 
-static int scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n) {
+int fs3i_scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n) {
 	int nb = cdiv((long long)n, SCAN_TILE);
 	if ((size_t)nb > s->scan_block_cap) { s->err = "scan scratch too small"; return FS3_ERR_STATE; }
 	k_scan_reduce<<<nb, SCAN_T, 0, s->stream>>>(in, n, s->scan_block); FS3_LAUNCH_CHECK();
@@ -248,7 +248,7 @@ int fs3i_bin(fs3_sim* s) {
 		GridDims d{s->nx, s->ny, s->nz};
 		int nb = cdiv(s->np, 256);
 		k_bin_count<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, s->cellid, s->cell_count, s->dev_flags); FS3_LAUNCH_CHECK();
-		int rc = scan_u32(s, s->cell_count, s->cell_start, s->nH + 1);
+		int rc = fs3i_scan_u32(s, s->cell_count, s->cell_start, s->nH + 1);
 		if (rc) return rc;
 		k_bin_scatter_ids<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->cellid, s->np, s->cell_start, s->cell_fill, s->tmp_id); FS3_LAUNCH_CHECK();
 		k_bin_rank_gather<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->cellid, s->np, s->cell_start, s->tmp_id,

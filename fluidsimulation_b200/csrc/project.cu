@@ -6,6 +6,7 @@
 // REAL = double reproduces the reference's fp64 solve bit for bit (each half sweep is order
 // independent; same IEEE operations, no FMA contraction); REAL = float is the fast mode.
 #include "fs3_internal.cuh"
+#include <algorithm>
 
 template <typename T> struct Ops;
 template <> struct Ops<double> {
@@ -55,7 +56,7 @@ __global__ void __launch_bounds__(256) k_project_setup(Sys<REAL> sy, const float
 	unsigned m = 0;
 	REAL d = 0;
 	if (pc < 0.0f) {
-		m = 64;
+		m = 64 | 128;   // bit7: no air neighbour, i.e. diag == number of fluid neighbours exactly (cleared below)
 		const int sY = nx, sZ = nx * ny;
 		const bool has[6] = {x != 0, x != nx - 1, y != 0, y != ny - 1, z != 0, z != nz - 1};
 		const long long off[6] = {-1, 1, -sY, sY, -(long long)sZ, (long long)sZ};
@@ -65,6 +66,7 @@ __global__ void __launch_bounds__(256) k_project_setup(Sys<REAL> sy, const float
 			d = O::add(d, (REAL)1);
 			float pn = phi[(long long)c + off[k]];
 			if (pn < 0.0f) m |= 1u << k;
+			if (!(pn < 0.0f)) m &= ~128u;
 			if (pn > 0.0f) {
 				REAL r = O::div(-(REAL)pn, (REAL)pc);
 				r = r < (REAL)0 ? (REAL)0 : (r > max_ratio ? max_ratio : r);
@@ -85,52 +87,77 @@ template <typename REAL, int VEC> struct VecT;
 template <> struct VecT<double, 2> { typedef double2 type; typedef unsigned short mtype; };
 template <> struct VecT<float, 4> { typedef float4 type; typedef unsigned int mtype; };
 
+// The sweep runs over a compacted list of the colour's ACTIVE vectors (VEC consecutive colour cells of which
+// at least one is fluid), built once per projection (200 sweeps reuse it): every resident warp does useful
+// work, air is never touched, and consecutive list entries are consecutive in memory wherever the fluid
+// is, so accesses stay coalesced.  Entry = vector index | (x parity of the colour in that row) << 31.
+// Interior cells (mask bit7) have diag == popcount(fluid neighbours), so dg is only read near the surface.
 template <typename REAL, int VEC>
-__global__ void __launch_bounds__(256) k_sor_half(Sys<REAL> sy, int colour, REAL omega, REAL one_minus_omega) {
+__global__ void __launch_bounds__(256) k_sor_half(Sys<REAL> sy, int colour, REAL omega, REAL one_minus_omega,
+                                                  const uint32_t* __restrict__ list, const uint32_t* __restrict__ count) {
 	typedef Ops<REAL> O;
 	typedef typename VecT<REAL, VEC>::type V;
 	typedef typename VecT<REAL, VEC>::mtype M;
-	const int tpr = sy.rb.hp / VEC;
-	size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	size_t rows = (size_t)sy.rb.ny * sy.rb.nz;
-	if (t >= rows * tpr) return;
-	int xv = (int)(t % tpr);
-	size_t r = t / tpr;
-	int y = (int)(r % sy.rb.ny), z = (int)(r / sy.rb.ny);
-	size_t base = sy.rb.at(xv * VEC, y, z);
-	M mm = *reinterpret_cast<const M*>(sy.mask[colour] + base);
-	M selfbits = VEC == 2 ? (M)0x4040 : (M)0x40404040u;
-	if ((mm & selfbits) == 0) return;   // no fluid cell in this vector: nothing to read or write
-	const int s = (colour + y + z) & 1;  // x parity of this colour in this row
+	const uint32_t n = __ldg(count);
 	const REAL* __restrict__ o = sy.p[colour ^ 1];
-	REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
-	*reinterpret_cast<V*>(own) = *reinterpret_cast<const V*>(sy.p[colour] + base);
-	*reinterpret_cast<V*>(bb) = *reinterpret_cast<const V*>(sy.b[colour] + base);
-	*reinterpret_cast<V*>(dd) = *reinterpret_cast<const V*>(sy.dg[colour] + base);
-	*reinterpret_cast<V*>(xc) = *reinterpret_cast<const V*>(o + base);
-	*reinterpret_cast<V*>(ym) = *reinterpret_cast<const V*>(o + base - sy.rb.hp);
-	*reinterpret_cast<V*>(yp) = *reinterpret_cast<const V*>(o + base + sy.rb.hp);
-	*reinterpret_cast<V*>(zm) = *reinterpret_cast<const V*>(o + base - sy.rb.plane);
-	*reinterpret_cast<V*>(zp) = *reinterpret_cast<const V*>(o + base + sy.rb.plane);
-	REAL edge = s == 0 ? o[base - 1] : o[base + VEC];
+	const M nodiag = VEC == 2 ? (M)0x8080 : (M)0x80808080u;
+	for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+		const uint32_t ent = __ldg(list + t);
+		const int s = (int)(ent >> 31);   // x parity of this colour in this row
+		const size_t base = (size_t)(ent & 0x7fffffffu) * VEC;
+		const M mm = *reinterpret_cast<const M*>(sy.mask[colour] + base);
+		REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
+		*reinterpret_cast<V*>(own) = *reinterpret_cast<const V*>(sy.p[colour] + base);
+		*reinterpret_cast<V*>(bb) = *reinterpret_cast<const V*>(sy.b[colour] + base);
+		*reinterpret_cast<V*>(xc) = *reinterpret_cast<const V*>(o + base);
+		*reinterpret_cast<V*>(ym) = *reinterpret_cast<const V*>(o + base - sy.rb.hp);
+		*reinterpret_cast<V*>(yp) = *reinterpret_cast<const V*>(o + base + sy.rb.hp);
+		*reinterpret_cast<V*>(zm) = *reinterpret_cast<const V*>(o + base - sy.rb.plane);
+		*reinterpret_cast<V*>(zp) = *reinterpret_cast<const V*>(o + base + sy.rb.plane);
+		const REAL edge = s == 0 ? o[base - 1] : o[base + VEC];
+		if ((mm & nodiag) != nodiag) *reinterpret_cast<V*>(dd) = *reinterpret_cast<const V*>(sy.dg[colour] + base);
 #pragma unroll
-	for (int e = 0; e < VEC; e++) {
-		unsigned m = (unsigned)(mm >> (8 * e)) & 0xffu;
-		if (!(m & 64u)) continue;
-		// other-colour x neighbours: left at index e-1+s, right at e+s
-		REAL L = s ? xc[e] : (e == 0 ? edge : xc[e > 0 ? e - 1 : 0]);
-		REAL R = s ? (e == VEC - 1 ? edge : xc[e < VEC - 1 ? e + 1 : e]) : xc[e];
-		REAL nms = 0;                                   // neighborMinusSum, order x-,x+,y-,y+,z-,z+ (S3D.cpp:964-993)
-		if (m & 1u) nms = O::sub(nms, L);
-		if (m & 2u) nms = O::sub(nms, R);
-		if (m & 4u) nms = O::sub(nms, ym[e]);
-		if (m & 8u) nms = O::sub(nms, yp[e]);
-		if (m & 16u) nms = O::sub(nms, zm[e]);
-		if (m & 32u) nms = O::sub(nms, zp[e]);
-		// p = (1-omega) p + omega (b - nms) / diag   (S3D.cpp:996)
-		own[e] = O::add(O::mul(one_minus_omega, own[e]), O::div(O::mul(omega, O::sub(bb[e], nms)), dd[e]));
+		for (int e = 0; e < VEC; e++) {
+			const unsigned m = (unsigned)(mm >> (8 * e)) & 0xffu;
+			if (!(m & 64u)) continue;
+			// other-colour x neighbours: left at index e-1+s, right at e+s
+			const REAL L = s ? xc[e] : (e == 0 ? edge : xc[e > 0 ? e - 1 : 0]);
+			const REAL R = s ? (e == VEC - 1 ? edge : xc[e < VEC - 1 ? e + 1 : e]) : xc[e];
+			REAL nms = 0;                                   // neighborMinusSum, order x-,x+,y-,y+,z-,z+ (S3D.cpp:964-993)
+			if (m & 1u) nms = O::sub(nms, L);
+			if (m & 2u) nms = O::sub(nms, R);
+			if (m & 4u) nms = O::sub(nms, ym[e]);
+			if (m & 8u) nms = O::sub(nms, yp[e]);
+			if (m & 16u) nms = O::sub(nms, zm[e]);
+			if (m & 32u) nms = O::sub(nms, zp[e]);
+			const REAL dg = (m & 128u) ? (REAL)__popc(m & 63u) : dd[e];
+			// p = (1-omega) p + omega (b - nms) / diag   (S3D.cpp:996)
+			own[e] = O::add(O::mul(one_minus_omega, own[e]), O::div(O::mul(omega, O::sub(bb[e], nms)), dg));
+		}
+		*reinterpret_cast<V*>(sy.p[colour] + base) = *reinterpret_cast<V*>(own);
 	}
-	*reinterpret_cast<V*>(sy.p[colour] + base) = *reinterpret_cast<V*>(own);
+}
+
+// active-vector flags (+1 trailing zero so that the exclusive scan's last entry is the count) and compaction
+template <int VEC>
+__global__ void __launch_bounds__(256) k_sor_flags(const unsigned char* __restrict__ mask, size_t nvec, uint32_t* __restrict__ flags) {
+	size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (v > nvec) return;
+	uint32_t f = 0;
+	if (v < nvec) {
+		if (VEC == 2) f = (*reinterpret_cast<const unsigned short*>(mask + v * 2) & 0x4040u) != 0;
+		else f = (*reinterpret_cast<const unsigned int*>(mask + v * 4) & 0x40404040u) != 0;
+	}
+	flags[v] = f;
+}
+template <int VEC>
+__global__ void __launch_bounds__(256) k_sor_compact(const uint32_t* __restrict__ flags, const uint32_t* __restrict__ pos, size_t nvec, RBLayout rb,
+                                                     int colour, uint32_t* __restrict__ list) {
+	size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (v >= nvec || !flags[v]) return;
+	size_t row = (v * VEC) / rb.hp;   // = y + ny*(z+1)
+	int y = (int)(row % rb.ny), z = (int)(row / rb.ny) - 1;
+	list[pos[v]] = (uint32_t)v | ((uint32_t)((colour + y + z) & 1) << 31);
 }
 
 // ---- residual ||b - A p|| over fluid cells (instrumentation; not in the reference) ------------------
@@ -251,8 +278,11 @@ int fs3i_alloc_pressure(fs3_sim* s) {
 	if (s->p[0] && s->alloc_precision == prec) return FS3_OK;
 	for (int c = 0; c < 2; c++) {
 		if (s->p[c]) cudaFree(s->p[c]); if (s->b[c]) cudaFree(s->b[c]); if (s->dg[c]) cudaFree(s->dg[c]); if (s->mask[c]) cudaFree(s->mask[c]);
-		s->p[c] = s->b[c] = s->dg[c] = nullptr; s->mask[c] = nullptr;
+		if (s->sor_list[c]) cudaFree(s->sor_list[c]); if (s->sor_pos[c]) cudaFree(s->sor_pos[c]);
+		s->p[c] = s->b[c] = s->dg[c] = nullptr; s->mask[c] = nullptr; s->sor_list[c] = s->sor_pos[c] = nullptr;
 	}
+	if (s->sor_flags) cudaFree(s->sor_flags);
+	s->sor_flags = nullptr;
 	RBLayout& rb = s->rb;
 	rb.nx = s->nx; rb.ny = s->ny; rb.nz = s->nz;
 	rb.hx = (s->nx + 1) / 2;
@@ -266,8 +296,16 @@ int fs3i_alloc_pressure(fs3_sim* s) {
 		FS3_CUDA(cudaMemsetAsync(s->p[c], 0, rb.total * es, s->stream)); FS3_CUDA(cudaMemsetAsync(s->b[c], 0, rb.total * es, s->stream));
 		FS3_CUDA(cudaMemsetAsync(s->dg[c], 0, rb.total * es, s->stream)); FS3_CUDA(cudaMemsetAsync(s->mask[c], 0, rb.total, s->stream));
 	}
+	const size_t nvec = rb.total / (prec ? 4 : 2);
+	FS3_CUDA(cudaMalloc((void**)&s->sor_flags, (nvec + 1) * sizeof(uint32_t)));
+	for (int c = 0; c < 2; c++) {
+		FS3_CUDA(cudaMalloc((void**)&s->sor_list[c], nvec * sizeof(uint32_t)));
+		FS3_CUDA(cudaMalloc((void**)&s->sor_pos[c], (nvec + 1) * sizeof(uint32_t)));
+	}
+	if ((nvec + 1) / 4096 + 2 > s->scan_block_cap) { s->err = "scan scratch too small for the SOR lists"; return FS3_ERR_STATE; }
 	s->alloc_precision = prec;
 	s->system_valid = false;
+	s->sor_list_valid = false;
 	return FS3_OK;
 }
 
@@ -278,16 +316,29 @@ template <typename REAL, int VEC> static int sor_loop_t(fs3_sim* s, int iters) {
 	REAL omega = (REAL)fs3_omega(s);
 	if (sizeof(REAL) == 4) omega = (REAL)2 - (REAL)3.16343 / s->nx, omega = s->prm.omega > 0 ? (REAL)s->prm.omega : omega;
 	REAL omo = (REAL)1 - omega;
+	if (!s->sor_list_valid) {
+		// active-vector lists of both colours (flags -> exclusive scan -> compaction); count stays on the device
+		const size_t nvec = s->rb.total / VEC;
+		for (int c = 0; c < 2; c++) {
+			k_sor_flags<VEC><<<cdiv((long long)nvec + 1, 256), 256, 0, s->stream>>>(s->mask[c], nvec, s->sor_flags); FS3_LAUNCH_CHECK();
+			int rc = fs3i_scan_u32(s, s->sor_flags, s->sor_pos[c], nvec + 1);
+			if (rc) return rc;
+			k_sor_compact<VEC><<<cdiv((long long)nvec, 256), 256, 0, s->stream>>>(s->sor_flags, s->sor_pos[c], nvec, s->rb, c, s->sor_list[c]); FS3_LAUNCH_CHECK();
+			s->sor_count[c] = s->sor_pos[c] + nvec;
+		}
+		s->sor_list_valid = true;
+	}
+	// persistent grid-stride launch: enough blocks to fill the machine; the list length is read on the device
 	size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * s->nz;
-	int nb = cdiv((long long)threads, 256);
+	int nb = (int)std::min<long long>(cdiv((long long)threads, 256), (long long)s->sm_count * 8);
 	bool rec = s->prm.record_residuals != 0;
 	if (rec) {
 		if (iters > s->res_cap) { s->err = "residual buffer too small"; return FS3_ERR_STATE; }
 		FS3_CUDA(cudaMemsetAsync(s->res, 0, sizeof(double) * 2 * iters, s->stream));
 	}
 	for (int it = 0; it < iters; it++) {
-		k_sor_half<REAL, VEC><<<nb, 256, 0, s->stream>>>(sy, 0, omega, omo); FS3_LAUNCH_CHECK();
-		k_sor_half<REAL, VEC><<<nb, 256, 0, s->stream>>>(sy, 1, omega, omo); FS3_LAUNCH_CHECK();
+		k_sor_half<REAL, VEC><<<nb, 256, 0, s->stream>>>(sy, 0, omega, omo, s->sor_list[0], s->sor_count[0]); FS3_LAUNCH_CHECK();
+		k_sor_half<REAL, VEC><<<nb, 256, 0, s->stream>>>(sy, 1, omega, omo, s->sor_list[1], s->sor_count[1]); FS3_LAUNCH_CHECK();
 		if (rec) { k_sor_residual<REAL><<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(sy, s->res + 2 * it); FS3_LAUNCH_CHECK(); }
 	}
 	s->res_count = rec ? iters : 0;
@@ -308,6 +359,7 @@ template <typename REAL> static int project_t(fs3_sim* s, float dt, bool from_ol
 	k_project_setup<REAL><<<nb, 256, 0, s->stream>>>(sy, sU, sV, sW, s->phi, scale, gdt, with_gravity ? 1 : 0, (REAL)1000.0);
 	FS3_LAUNCH_CHECK();
 	s->system_valid = true;
+	s->sor_list_valid = false;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_PROJECT_SOR], s->stream);
 	int rc = fs3i_sor_loop(s, s->prm.sor_iterations);
 	if (rc) return rc;
