@@ -4,6 +4,7 @@
 #include <cstring>
 #include <cmath>
 #include <new>
+#include <algorithm>
 
 static std::string g_create_error;
 
@@ -18,6 +19,7 @@ static int fail(fs3_sim* s, int code, const char* msg) { s->err = msg; return co
 
 static int ensure_particle_capacity(fs3_sim* s, long long count) {
 	if (count <= s->cap) return FS3_OK;
+	if (s->arena) { s->err = "particle capacity of a sharded handle is fixed at creation"; return FS3_ERR_STATE; }
 	for (int k = 0; k < 2; k++) {
 		if (s->pos[k]) cudaFree(s->pos[k]); if (s->vel[k]) cudaFree(s->vel[k]);
 		s->pos[k] = s->vel[k] = nullptr;
@@ -42,18 +44,15 @@ int fs3i_staging(fs3_sim* s, size_t bytes) {
 	return FS3_OK;
 }
 
-static int check_flags(fs3_sim* s) {
-	int h[2] = {0, 0};
-	FS3_CUDA(cudaMemcpyAsync(h, s->dev_flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+int fs3i_check_flags(fs3_sim* s) {
+	int h[4] = {0, 0, 0, 0};
+	FS3_CUDA(cudaMemcpyAsync(h, s->dev_flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
-	if (h[1]) {
-		FS3_CUDA(cudaMemsetAsync(s->dev_flags, 0, 2 * sizeof(int), s->stream));
-		return fail(s, FS3_ERR_STATE, "level-set dataflow sweep timed out waiting for a tile dependency (results invalid)");
-	}
-	if (h[0]) {
-		FS3_CUDA(cudaMemsetAsync(s->dev_flags, 0, 2 * sizeof(int), s->stream));
-		return fail(s, FS3_ERR_PARTICLE, "a particle lay outside the grid when binned (positions must be inside the Advect clamp box)");
-	}
+	if (h[0] || h[1] || h[2] || h[3]) FS3_CUDA(cudaMemsetAsync(s->dev_flags, 0, 4 * sizeof(int), s->stream));
+	if (h[2]) return fail(s, FS3_ERR_STATE, "a cross-rank wait was not satisfied (peer rank missing, out of step, or timed out); results invalid");
+	if (h[3]) return fail(s, FS3_ERR_STATE, "a slab's particle, ghost-layer or migration capacity was exceeded; results invalid");
+	if (h[1]) return fail(s, FS3_ERR_STATE, "level-set dataflow sweep timed out waiting for a tile dependency (results invalid)");
+	if (h[0]) return fail(s, FS3_ERR_PARTICLE, "a particle lay outside the grid (or its rank's slab) when binned (positions must be inside the Advect clamp box)");
 	return FS3_OK;
 }
 
@@ -61,11 +60,17 @@ extern "C" {
 
 const char* fs3_last_error(const fs3_sim* s) { return s ? s->err.c_str() : g_create_error.c_str(); }
 
-int fs3_create(int nx, int ny, int nz, float cpm, int device, fs3_sim** out) {
+// Shared by fs3_create (world 1), fs3_create_sharded (one rank of a multi-process job) and fs3_group_create (all ranks in
+// this process).  A sharded handle is NOT reset here: ResetSimulation needs the peers (fs3_shard_connect / group create).
+static int create_common(int nx, int ny, int nz, float cpm, int device, int rank, int world, bool lockstep, cudaStream_t shared_stream, fs3_sim** out) {
 	if (!out) return FS3_ERR_INVALID;
 	*out = nullptr;
 	if (nx < 4 || nx != ny || ny != nz || cpm != (float)nx) {
 		g_create_error = "only cubic grids with cells_per_meter == nx (>= 4) are supported, as the reference's own results are only defined there";
+		return FS3_ERR_INVALID;
+	}
+	if (world < 1 || world > FS3_MAX_WORLD || rank < 0 || rank >= world || nz % world != 0 || (world > 1 && nz / world < 2)) {
+		g_create_error = "z-slab sharding needs 1 <= world <= 16, nz divisible by world and slabs of at least 2 cell planes";
 		return FS3_ERR_INVALID;
 	}
 	int ndev = 0;
@@ -88,42 +93,170 @@ int fs3_create(int nx, int ny, int nz, float cpm, int device, fs3_sim** out) {
 	s->prm.rho = 1000.0f; s->prm.gravity_y = -9.81f; s->prm.nu = 8.90f * 1e-4f / 1000.0f; s->prm.particle_radius = 1.0f;  // S3D.h:135-145
 	s->prm.record_stage_times = 0;
 	s->nU = (size_t)(nx + 1) * ny * nz; s->nV = (size_t)nx * (ny + 1) * nz; s->nW = (size_t)nx * ny * (nz + 1); s->nC = (size_t)nx * ny * nz;
-	s->launches = 0; s->np = 0; s->cap = 0; s->cur = 0; s->sorted = false; s->closest_valid = false; s->system_valid = false;
+	s->launches = 0; s->np = 0; s->np_in = 0; s->cap = 0; s->cur = 0; s->sorted = false; s->closest_valid = false; s->system_valid = false;
 	s->sor_list_valid = false; s->sm_count = prop.multiProcessorCount;
 	s->alloc_precision = -1; s->res_cap = 4096; s->res_count = 0; s->stage_ptr = nullptr; s->stage_bytes = 0;
+	s->rank = rank; s->world = world; s->z0 = rank * (nz / world); s->z1 = s->z0 + nz / world; s->lockstep = lockstep;
+	s->bar_epoch = 0; s->sor_epoch = 0; s->sor_e0 = 0; s->n_ipc_opened = 0; s->poff = 0; s->gcap = 0; s->mig_cap = 0;
 	for (int k = 0; k < FS3_T_COUNT; k++) s->stage_ms[k] = 0.f;
+	const long long P = std::max(1LL, 8LL * (nz - 2) * (ny - 2) * (nx - 1 - nx / 2));
+	long long cap = P;
+	if (world > 1) {
+		// a slab may hold up to twice its even share; a ghost region up to 8 average cell layers; a step's emigrants up to 4
+		const long long layer = P / (nz - 2) + 1;
+		cap = std::min(P, 2 * (P / world) + 4096);
+		s->gcap = std::min(P, 8 * layer + 4096);
+		s->mig_cap = std::min(P, 4 * layer + 4096);
+		s->poff = (size_t)s->gcap;
+	}
+	const long long ptot = cap + 2 * s->gcap;
 #define CK(call)                                                                                  \
 	do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { g_create_error = std::string(#call) + ": " + cudaGetErrorString(e_); fs3_destroy(s); return FS3_ERR_CUDA; } } while (0)
+#define CA(ptr, bytes)                                                                            \
+	do { int rc_ = fs3i_alloc(s, (void**)&(ptr), (bytes)); if (rc_) { g_create_error = s->err; fs3_destroy(s); return rc_; } } while (0)
 	CK(cudaSetDevice(device));
-	CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+	if (shared_stream) { s->stream = shared_stream; s->owns_stream = false; }
+	else { CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)); s->owns_stream = true; }
 	for (int k = 0; k < FS3_T_COUNT + 2; k++) CK(cudaEventCreate(&s->ev[k]));
+	if (world > 1) {
+		s->arena_bytes = fs3i_arena_bytes(nx, ptot, s->mig_cap, world);
+		CK(cudaMalloc((void**)&s->arena, s->arena_bytes));
+		CK(cudaMemsetAsync(s->arena, 0, s->arena_bytes, s->stream));   // epoch flags, counters and ghost planes start at zero
+		s->arena_used = 0;
+		s->peer_base[rank] = s->arena;
+	}
 	size_t nmax = s->nW > s->nU ? s->nW : s->nU;
 	if (s->nV > nmax) nmax = s->nV;
-	CK(cudaMalloc((void**)&s->U, s->nU * 4)); CK(cudaMalloc((void**)&s->V, s->nV * 4)); CK(cudaMalloc((void**)&s->W, s->nW * 4));
-	CK(cudaMalloc((void**)&s->oU, s->nU * 4)); CK(cudaMalloc((void**)&s->oV, s->nV * 4)); CK(cudaMalloc((void**)&s->oW, s->nW * 4));
-	CK(cudaMalloc((void**)&s->phi, s->nC * 4));
+	CA(s->U, s->nU * 4); CA(s->V, s->nV * 4); CA(s->W, s->nW * 4);
+	CA(s->oU, s->nU * 4); CA(s->oV, s->nV * 4); CA(s->oW, s->nW * 4);
+	CA(s->phi, s->nC * 4);
 	CK(cudaMemsetAsync(s->phi, 0, s->nC * 4, s->stream));  // the reference leaves m_Phi uninitialised; every cell is written by the first level set
 	s->nH = 8 * s->nC;
-	CK(cudaMalloc((void**)&s->cell_count, (s->nH + 1) * 4)); CK(cudaMalloc((void**)&s->cell_start, (s->nH + 1) * 4));
-	CK(cudaMalloc((void**)&s->cell_fill, s->nH * 4));
+	CA(s->cell_count, (s->nH + 1) * 4); CA(s->cell_start, (s->nH + 1) * 4);
+	CA(s->cell_fill, s->nH * 4);
 	s->scan_block_cap = (s->nH + 1) / 4096 + 2;
-	CK(cudaMalloc((void**)&s->scan_block, s->scan_block_cap * 4));
-	CK(cudaMalloc((void**)&s->ls_rec, s->nC * sizeof(float4))); CK(cudaMalloc((void**)&s->closest, s->nC * 4));
-	for (int k = 0; k < 3; k++) { CK(cudaMalloc((void**)&s->cdv[k], nmax * 4)); CK(cudaMalloc((void**)&s->orderv[k], nmax * 4)); }
+	CA(s->scan_block, s->scan_block_cap * 4);
+	CA(s->ls_rec, s->nC * sizeof(float4)); CA(s->closest, s->nC * 4);
+	for (int k = 0; k < 3; k++) { CA(s->cdv[k], nmax * 4); CA(s->orderv[k], nmax * 4); }
 	s->bucket_cap = nx + ny + nz + 8;
-	CK(cudaMalloc((void**)&s->bucket, 3 * (3 * (size_t)s->bucket_cap + 2) * 4));
+	CA(s->bucket, 3 * (3 * (size_t)s->bucket_cap + 2) * 4);
 	CK(cudaMallocHost((void**)&s->h_bucket, 3 * ((size_t)s->bucket_cap + 1) * 4));
-	CK(cudaMalloc((void**)&s->res, sizeof(double) * 2 * s->res_cap));
-	CK(cudaMalloc((void**)&s->dev_flags, 4 * sizeof(int)));
+	CA(s->res, sizeof(double) * 2 * s->res_cap);
+	CA(s->dev_flags, 4 * sizeof(int));
 	CK(cudaMemsetAsync(s->dev_flags, 0, 4 * sizeof(int), s->stream));
+	if (world > 1) {
+		for (int k = 0; k < 2; k++) { CA(s->pos[k], (size_t)ptot * sizeof(float4)); CA(s->vel[k], (size_t)ptot * sizeof(float4)); }
+		CA(s->cellid, (size_t)ptot * 4); CA(s->tmp_id, (size_t)ptot * 4);
+		s->cap = cap;
+	}
 #undef CK
-	long long np = 8LL * (nz - 2) * (ny - 2) * (nx - 1 - nx / 2);
-	int rc = ensure_particle_capacity(s, np > 0 ? np : 1);
+#undef CA
+	int rc = world > 1 ? fs3i_shard_alloc(s) : ensure_particle_capacity(s, P);
 	if (!rc) rc = fs3i_alloc_pressure(s);
 	if (!rc) rc = fs3i_levelset_init(s);
-	if (!rc) rc = fs3i_reset(s);
+	if (!rc && world == 1) rc = fs3i_reset(s);
+	if (!rc && cudaStreamSynchronize(s->stream) != cudaSuccess) { s->err = "device initialisation failed"; rc = FS3_ERR_CUDA; }
 	if (rc) { g_create_error = s->err; fs3_destroy(s); return rc; }
 	*out = s;
+	return FS3_OK;
+}
+
+int fs3_create(int nx, int ny, int nz, float cpm, int device, fs3_sim** out) { return create_common(nx, ny, nz, cpm, device, 0, 1, false, nullptr, out); }
+
+// ---- z-slab sharding: one rank of a multi-process job -----------------------------------------------------------------
+int fs3_create_sharded(int nx, int ny, int nz, float cpm, int device, int rank, int world, fs3_sim** out) {
+	if (world == 1) return fs3_create(nx, ny, nz, cpm, device, out);
+	return create_common(nx, ny, nz, cpm, device, rank, world, false, nullptr, out);
+}
+
+int fs3_shard_plan(int nz, int world, int rank, int* z0, int* z1) {
+	if (world < 1 || world > FS3_MAX_WORLD || rank < 0 || rank >= world || nz % world != 0 || (world > 1 && nz / world < 2)) return FS3_ERR_INVALID;
+	if (z0) *z0 = rank * (nz / world);
+	if (z1) *z1 = (rank + 1) * (nz / world);
+	return FS3_OK;
+}
+int fs3_shard_info(const fs3_sim* s, int* rank, int* world, int* z0, int* z1) {
+	if (!s) return FS3_ERR_INVALID;
+	if (rank) *rank = s->rank; if (world) *world = s->world; if (z0) *z0 = s->z0; if (z1) *z1 = s->z1;
+	return FS3_OK;
+}
+
+// What a rank tells its peers: the CUDA-IPC handle of its arena plus enough identity to refuse unsafe set-ups.
+struct fs3_shard_blob {
+	cudaIpcMemHandle_t mem;       // 64 bytes
+	unsigned char uuid[16];       // device the arena lives on
+	unsigned long long arena_bytes;
+	int rank, world, nx, pad;
+};
+static_assert(sizeof(fs3_shard_blob) <= FS3_SHARD_HANDLE_BYTES, "FS3_SHARD_HANDLE_BYTES too small");
+
+int fs3_shard_get_handle(fs3_sim* s, void* blob) {
+	ENTER(s);
+	if (!blob) return FS3_ERR_INVALID;
+	if (s->world < 2 || s->lockstep) return fail(s, FS3_ERR_STATE, "not a multi-process sharded handle");
+	fs3_shard_blob b;
+	memset(&b, 0, sizeof(b));
+	FS3_CUDA(cudaIpcGetMemHandle(&b.mem, s->arena));
+	cudaDeviceProp prop;
+	FS3_CUDA(cudaGetDeviceProperties(&prop, s->device));
+	memcpy(b.uuid, &prop.uuid, 16);
+	b.arena_bytes = s->arena_bytes; b.rank = s->rank; b.world = s->world; b.nx = s->nx;
+	memset(blob, 0, FS3_SHARD_HANDLE_BYTES);
+	memcpy(blob, &b, sizeof(b));
+	return FS3_OK;
+}
+
+static int run_reset_phases(fs3_sim* s) {
+	for (int ph = 0; ph < 3; ph++) { int rc = fs3i_reset_phase(s, ph); if (rc) return rc; }
+	return FS3_OK;
+}
+
+// `blobs` = world blobs of FS3_SHARD_HANDLE_BYTES each, in rank order (gathered by the caller with whatever transport
+// it has: MPI_Allgather, torch.distributed.all_gather, a file).  Collective: maps every peer's arena, then runs
+// ResetSimulation across the ranks.
+int fs3_shard_connect(fs3_sim* s, const void* blobs) {
+	ENTER(s);
+	if (!blobs) return FS3_ERR_INVALID;
+	if (s->world < 2 || s->lockstep) return fail(s, FS3_ERR_STATE, "not a multi-process sharded handle");
+	if (s->n_ipc_opened) return fail(s, FS3_ERR_STATE, "already connected");
+	fs3_shard_blob mine;
+	memcpy(&mine, (const char*)blobs + (size_t)s->rank * FS3_SHARD_HANDLE_BYTES, sizeof(mine));
+	for (int r = 0; r < s->world; r++) {
+		fs3_shard_blob b;
+		memcpy(&b, (const char*)blobs + (size_t)r * FS3_SHARD_HANDLE_BYTES, sizeof(b));
+		if (b.rank != r || b.world != s->world || b.nx != s->nx || b.arena_bytes != s->arena_bytes)
+			return fail(s, FS3_ERR_INVALID, "peer handle does not describe rank r of the same job (rank order, world size or grid differ)");
+		if (r == s->rank) continue;
+		// ranks spin on each other's flags inside kernels: two ranks on one GPU could wait on a kernel that cannot run
+		if (!memcmp(b.uuid, mine.uuid, 16)) return fail(s, FS3_ERR_INVALID, "two ranks share one GPU; every rank needs its own device");
+		void* base = nullptr;
+		cudaError_t e = cudaIpcOpenMemHandle(&base, b.mem, cudaIpcMemLazyEnablePeerAccess);
+		if (e != cudaSuccess) { s->err = std::string("cudaIpcOpenMemHandle (is peer access / IPC available between the GPUs?): ") + cudaGetErrorString(e); return FS3_ERR_CUDA; }
+		s->peer_base[r] = (char*)base;
+		s->n_ipc_opened++;
+	}
+	return run_reset_phases(s);
+}
+
+// ---- z-slab sharding: all ranks in THIS process, one stream, stepped in lockstep (single-GPU testing of the sharded path) --
+int fs3_group_create(int nx, int ny, int nz, float cpm, int device, int world, fs3_sim** out) {
+	if (!out || world < 2 || world > FS3_MAX_WORLD) return FS3_ERR_INVALID;
+	for (int r = 0; r < world; r++) out[r] = nullptr;
+	int rc = FS3_OK;
+	for (int r = 0; r < world && !rc; r++) rc = create_common(nx, ny, nz, cpm, device, r, world, true, r ? out[0]->stream : nullptr, &out[r]);
+	if (!rc) {
+		for (int r = 0; r < world; r++) for (int q = 0; q < world; q++) out[r]->peer_base[q] = out[q]->arena;
+		rc = fs3_group_reset(out, world);
+		if (rc) g_create_error = "group reset failed";
+	}
+	if (rc) { for (int r = world - 1; r >= 0; r--) if (out[r]) { fs3_destroy(out[r]); out[r] = nullptr; } }
+	return rc;
+}
+int fs3_group_reset(fs3_sim** h, int world) {
+	if (!h || world < 2 || !h[0] || world != h[0]->world) return FS3_ERR_INVALID;
+	cudaSetDevice(h[0]->device);
+	for (int ph = 0; ph < 3; ph++)
+		for (int r = 0; r < world; r++) { int rc = fs3i_reset_phase(h[r], ph); if (rc) return rc; }
 	return FS3_OK;
 }
 
@@ -131,21 +264,32 @@ int fs3_destroy(fs3_sim* s) {
 	if (!s) return FS3_OK;
 	cudaSetDevice(s->device);
 	if (s->stream) cudaStreamSynchronize(s->stream);
-	void* ptrs[] = {s->U, s->V, s->W, s->oU, s->oV, s->oW, s->phi, s->pos[0], s->pos[1], s->vel[0], s->vel[1], s->cellid, s->cell_count,
-	                s->cell_start, s->cell_fill, s->tmp_id, s->scan_block, s->ls_rec, s->closest, s->cdv[0], s->cdv[1], s->cdv[2], s->orderv[0],
-	                s->orderv[1], s->orderv[2], s->bucket, s->p[0], s->p[1], s->b[0], s->b[1], s->dg[0], s->dg[1], s->mask[0], s->mask[1],
-	                s->res, s->dev_flags, s->ls_order, s->ls_done, s->ls_ticket, s->sor_flags, s->sor_pos[0], s->sor_pos[1], s->sor_list[0], s->sor_list[1]};
-	for (void* p : ptrs) if (p) cudaFree(p);
+	if (s->arena) {
+		for (int r = 0; r < s->world; r++) if (!s->lockstep && r != s->rank && s->peer_base[r]) cudaIpcCloseMemHandle(s->peer_base[r]);
+		cudaFree(s->arena);
+		if (s->h_pin) cudaFreeHost(s->h_pin);
+	} else {
+		void* ptrs[] = {s->U, s->V, s->W, s->oU, s->oV, s->oW, s->phi, s->pos[0], s->pos[1], s->vel[0], s->vel[1], s->cellid, s->cell_count,
+		                s->cell_start, s->cell_fill, s->tmp_id, s->scan_block, s->ls_rec, s->closest, s->cdv[0], s->cdv[1], s->cdv[2], s->orderv[0],
+		                s->orderv[1], s->orderv[2], s->bucket, s->p[0], s->p[1], s->b[0], s->b[1], s->dg[0], s->dg[1], s->mask[0], s->mask[1],
+		                s->res, s->dev_flags, s->ls_order, s->ls_done, s->ls_ticket, s->sor_flags, s->sor_pos[0], s->sor_pos[1], s->sor_list[0], s->sor_list[1]};
+		for (void* p : ptrs) if (p) cudaFree(p);
+	}
 	if (s->h_bucket) cudaFreeHost(s->h_bucket);
 	if (s->stage_ptr) cudaFree(s->stage_ptr);
 	for (int k = 0; k < FS3_T_COUNT + 2; k++) if (s->ev[k]) cudaEventDestroy(s->ev[k]);
-	if (s->stream) cudaStreamDestroy(s->stream);
+	if (s->stream && s->owns_stream) cudaStreamDestroy(s->stream);
 	delete s;
 	return FS3_OK;
 }
 
 int fs3_reset(fs3_sim* s) {
 	ENTER(s);
+	if (s->world > 1) {
+		if (s->lockstep) return fail(s, FS3_ERR_STATE, "a lockstep group is reset with fs3_group_reset");
+		if (!s->n_ipc_opened) return fail(s, FS3_ERR_STATE, "sharded handle is not connected (fs3_shard_connect)");
+		return run_reset_phases(s);   // collective: every rank calls fs3_reset
+	}
 	long long np = 8LL * (s->nz - 2) * (s->ny - 2) * (s->nx - 1 - s->nx / 2);
 	int rc = ensure_particle_capacity(s, np > 0 ? np : 1);
 	if (rc) return rc;
@@ -155,12 +299,19 @@ int fs3_reset(fs3_sim* s) {
 int fs3_sync(fs3_sim* s) {
 	ENTER(s);
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
-	return check_flags(s);
+	return fs3i_check_flags(s);
 }
 
 void* fs3_stream(fs3_sim* s) { return s ? (void*)s->stream : nullptr; }
 long long fs3_kernel_launches(const fs3_sim* s) { return s ? s->launches : 0; }
-long long fs3_num_particles(const fs3_sim* s) { return s ? s->np : 0; }
+long long fs3_num_particles(const fs3_sim* s) {
+	if (!s) return 0;
+	if (s->world == 1) return s->np;
+	long long t = 0;
+	for (int r = 0; r < s->world; r++) t += s->np_all[r];
+	return t;   // m_particles.size() of the whole simulation
+}
+long long fs3_num_local_particles(const fs3_sim* s) { return s ? s->np : 0; }
 
 static float flip_alpha(const fs3_sim* s, float dt) {
 	float a = 6 * dt * s->prm.nu * s->cpm * s->cpm;   // S3D.cpp:114
@@ -175,10 +326,17 @@ static float effective_dt(const fs3_sim* s, float dt) {
 // FluidSim3::Simulate (S3D.cpp:101-188)
 int fs3_step(fs3_sim* s, float dt) {
 	ENTER(s);
-	if (s->np <= 272) return fail(s, FS3_ERR_STATE, "Simulate needs more than 272 particles (the reference reads particles[272], Simulation3D.cpp:198-199)");
+	if (s->world == 1 && s->np <= 272) return fail(s, FS3_ERR_STATE, "Simulate needs more than 272 particles (the reference reads particles[272], Simulation3D.cpp:198-199)");
 	dt = effective_dt(s, dt);
 	const bool T = s->prm.record_stage_times != 0;
 	int rc;
+	if (s->world > 1) {
+		if (s->lockstep) return fail(s, FS3_ERR_STATE, "a lockstep group is stepped with fs3_group_step");
+		if (!s->n_ipc_opened) return fail(s, FS3_ERR_STATE, "sharded handle is not connected (fs3_shard_connect)");
+		const int nph = fs3i_num_step_phases(s);
+		for (int ph = 0; ph < nph; ph++) if ((rc = fs3i_step_phase(s, ph, dt))) return rc;
+		return FS3_OK;
+	}
 	if (T) cudaEventRecord(s->ev[FS3_T_ADVECT], s->stream);
 	if ((rc = fs3i_advect(s, dt))) return rc;
 	if (T) cudaEventRecord(s->ev[FS3_T_BIN], s->stream);
@@ -191,6 +349,17 @@ int fs3_step(fs3_sim* s, float dt) {
 	if ((rc = fs3i_flip_combine(s, alpha))) return rc;
 	if ((rc = fs3i_g2p(s, alpha))) return rc;
 	if (T) cudaEventRecord(s->ev[FS3_T_TOTAL], s->stream);
+	return FS3_OK;
+}
+
+// One Simulate(dt) of a lockstep group: phase k of every rank is queued before phase k+1 of any.
+int fs3_group_step(fs3_sim** h, int world, float dt) {
+	if (!h || world < 2 || !h[0] || world != h[0]->world || !h[0]->lockstep) return FS3_ERR_INVALID;
+	cudaSetDevice(h[0]->device);
+	dt = effective_dt(h[0], dt);
+	const int nph = fs3i_num_step_phases(h[0]);
+	for (int ph = 0; ph < nph; ph++)
+		for (int r = 0; r < world; r++) { int rc = fs3i_step_phase(h[r], ph, dt); if (rc) return rc; }
 	return FS3_OK;
 }
 
@@ -208,22 +377,27 @@ int fs3_stage_times(fs3_sim* s, float* ms, int cap) {
 int fs3_get_particles(fs3_sim* s, fs3_particle* host) {
 	ENTER(s);
 	if (!host) return FS3_ERR_INVALID;
-	if (s->np <= 0) return FS3_OK;
-	int rc = fs3i_staging(s, (size_t)s->np * sizeof(fs3_particle));
+	long long total = s->np;
+	if (s->world > 1) { total = 0; for (int r = 0; r < s->world; r++) total += s->np_all[r]; }
+	if (total <= 0) return FS3_OK;
+	int rc = fs3i_staging(s, (size_t)total * sizeof(fs3_particle));
 	if (rc) return rc;
+	// sharded: records of particles owned by other ranks read back as NaN (all bits set); the caller merges the ranks
+	if (s->world > 1) FS3_CUDA(cudaMemsetAsync(s->stage_ptr, 0xff, (size_t)total * sizeof(fs3_particle), s->stream));
 	if ((rc = fs3i_unsort_particles(s, (fs3_particle*)s->stage_ptr))) return rc;
-	FS3_CUDA(cudaMemcpyAsync(host, s->stage_ptr, (size_t)s->np * sizeof(fs3_particle), cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaMemcpyAsync(host, s->stage_ptr, (size_t)total * sizeof(fs3_particle), cudaMemcpyDeviceToHost, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	return FS3_OK;
 }
 int fs3_set_particles(fs3_sim* s, const fs3_particle* host, long long count) {
 	ENTER(s);
 	if (count < 0 || (count > 0 && !host) || count > 0x7fffffffLL) return FS3_ERR_INVALID;
-	int rc = ensure_particle_capacity(s, count > 0 ? count : 1);
+	int rc = s->world > 1 ? FS3_OK : ensure_particle_capacity(s, count > 0 ? count : 1);
 	if (rc) return rc;
 	if ((rc = fs3i_staging(s, (size_t)(count > 0 ? count : 1) * sizeof(fs3_particle)))) return rc;
 	if (count > 0) FS3_CUDA(cudaMemcpyAsync(s->stage_ptr, host, (size_t)count * sizeof(fs3_particle), cudaMemcpyHostToDevice, s->stream));
-	rc = fs3i_load_particles(s, (const fs3_particle*)s->stage_ptr, count);
+	// sharded: every rank is given the same full array and keeps the particles of its slab
+	rc = s->world > 1 ? fs3i_load_particles_owned(s, (const fs3_particle*)s->stage_ptr, count) : fs3i_load_particles(s, (const fs3_particle*)s->stage_ptr, count);
 	if (rc) return rc;
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	return FS3_OK;

@@ -11,6 +11,8 @@
 	} while (0)
 
 static int fail(fs3_sim* s, int code, const char* msg) { s->err = msg; return code; }
+// stage-by-stage hooks drive one GPU; a sharded handle only steps as a whole (its stages are collective phases)
+#define SINGLE(s) if ((s)->world > 1) return fail(s, FS3_ERR_STATE, "this hook is not available on a sharded handle")
 
 static float flip_alpha(const fs3_sim* s, float dt) {
 	float a = 6 * dt * s->prm.nu * s->cpm * s->cpm;   // S3D.cpp:114
@@ -32,13 +34,14 @@ __global__ void k_cell_counts(const uint32_t* __restrict__ start, GridDims d, in
 
 extern "C" {
 
-int fs3_stage_advect(fs3_sim* s, float dt) { ENTER(s); return fs3i_advect(s, dt); }
-int fs3_stage_bin(fs3_sim* s) { ENTER(s); return fs3i_bin(s); }
-int fs3_stage_levelset(fs3_sim* s) { ENTER(s); return fs3i_levelset(s); }
+int fs3_stage_advect(fs3_sim* s, float dt) { ENTER(s); SINGLE(s); return fs3i_advect(s, dt); }
+int fs3_stage_bin(fs3_sim* s) { ENTER(s); SINGLE(s); return fs3i_bin(s); }
+int fs3_stage_levelset(fs3_sim* s) { ENTER(s); SINGLE(s); return fs3i_levelset(s); }
 
 // The stand-alone stage leaves its result in the live grids (as the reference does), so copy old -> cur.
 int fs3_stage_p2g(fs3_sim* s) {
 	ENTER(s);
+	SINGLE(s);
 	int rc = fs3i_p2g(s);
 	if (rc) return rc;
 	FS3_CUDA(cudaMemcpyAsync(s->U, s->oU, s->nU * 4, cudaMemcpyDeviceToDevice, s->stream));
@@ -46,11 +49,12 @@ int fs3_stage_p2g(fs3_sim* s) {
 	FS3_CUDA(cudaMemcpyAsync(s->W, s->oW, s->nW * 4, cudaMemcpyDeviceToDevice, s->stream));
 	return FS3_OK;
 }
-int fs3_stage_bodyforces(fs3_sim* s, float dt) { ENTER(s); return fs3i_bodyforces(s, dt); }
-int fs3_stage_project(fs3_sim* s, float dt) { ENTER(s); return fs3i_project(s, dt, false, false); }
+int fs3_stage_bodyforces(fs3_sim* s, float dt) { ENTER(s); SINGLE(s); return fs3i_bodyforces(s, dt); }
+int fs3_stage_project(fs3_sim* s, float dt) { ENTER(s); SINGLE(s); return fs3i_project(s, dt, false, false); }
 
 int fs3_stage_g2p(fs3_sim* s, float dt, const float* oldU, const float* oldV, const float* oldW) {
 	ENTER(s);
+	SINGLE(s);
 	if (!oldU || !oldV || !oldW) return FS3_ERR_INVALID;
 	FS3_CUDA(cudaMemcpyAsync(s->oU, oldU, s->nU * 4, cudaMemcpyHostToDevice, s->stream));
 	FS3_CUDA(cudaMemcpyAsync(s->oV, oldV, s->nV * 4, cudaMemcpyHostToDevice, s->stream));
@@ -66,6 +70,7 @@ int fs3_stage_g2p(fs3_sim* s, float dt, const float* oldU, const float* oldV, co
 
 int fs3_extrapolate(fs3_sim* s, float* grid, const unsigned char* valid, int xs, int ys, int zs) {
 	ENTER(s);
+	SINGLE(s);
 	if (!grid || !valid || xs < 1 || ys < 1 || zs < 1) return FS3_ERR_INVALID;
 	size_t n = (size_t)xs * ys * zs;
 	size_t nmax = s->nW > s->nU ? s->nW : s->nU;
@@ -87,17 +92,20 @@ int fs3_extrapolate(fs3_sim* s, float* grid, const unsigned char* valid, int xs,
 int fs3_get_cell_indices(fs3_sim* s, int* cell) {
 	ENTER(s);
 	if (!cell) return FS3_ERR_INVALID;
-	if (s->np <= 0) return FS3_OK;
-	int rc = fs3i_staging(s, (size_t)s->np * 4);
+	const long long total = fs3_num_particles(s);
+	if (total <= 0) return FS3_OK;
+	int rc = fs3i_staging(s, (size_t)total * 4);
 	if (rc) return rc;
+	if (s->world > 1) FS3_CUDA(cudaMemsetAsync(s->stage_ptr, 0xff, (size_t)total * 4, s->stream));   // -1 for particles of other ranks
 	if ((rc = fs3i_cell_indices(s, (int*)s->stage_ptr))) return rc;
-	FS3_CUDA(cudaMemcpyAsync(cell, s->stage_ptr, (size_t)s->np * 4, cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaMemcpyAsync(cell, s->stage_ptr, (size_t)total * 4, cudaMemcpyDeviceToHost, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	return FS3_OK;
 }
 int fs3_get_cell_counts(fs3_sim* s, int* counts) {
 	ENTER(s);
 	if (!counts) return FS3_ERR_INVALID;
+	SINGLE(s);
 	int rc = fs3i_bin(s);
 	if (rc) return rc;
 	if ((rc = fs3i_staging(s, s->nC * 4))) return rc;
@@ -147,6 +155,7 @@ int fs3_get_sor_residuals(fs3_sim* s, double* l2, double* linf, int cap, int* co
 int fs3_sor_bench(fs3_sim* s, int iters, float* ms_out) {
 	ENTER(s);
 	if (iters < 1 || !ms_out) return FS3_ERR_INVALID;
+	SINGLE(s);
 	if (!s->system_valid) return fail(s, FS3_ERR_STATE, "run a projection first: the sweep needs b, diag and the masks");
 	int rc = fs3i_clear_pressure(s);
 	if (rc) return rc;
@@ -164,6 +173,7 @@ int fs3_sor_bench(fs3_sim* s, int iters, float* ms_out) {
 
 int fs3_set_phi_all_fluid(fs3_sim* s) {
 	ENTER(s);
+	SINGLE(s);
 	k_fill_f32<<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(s->phi, s->nC, -1.0f); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }

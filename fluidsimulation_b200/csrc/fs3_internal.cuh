@@ -7,6 +7,7 @@
 #include "../../include/fs3.h"
 
 #define FS3_INF_CD 1000000000  // ExtrapolateValues' "inf" (S3D.cpp:632)
+#define FS3_MAX_WORLD 16
 
 // ---- red-black ("colour-split") storage of the pressure system ---------------------------------
 // Cells with (x+y+z)&1 == c live in colour array c at  xh + hp*(y + ny*(z+1)),  xh = x>>1.
@@ -88,7 +89,36 @@ struct fs3_sim {
 	double* res;               // device: [2*i] sum r^2, [2*i+1] max |r| (as double bits)
 	int res_cap, res_count;
 
-	int* dev_flags;            // [0] particle-outside flag
+	// ---- z-slab sharding over the GPUs of one box (world == 1: the whole grid) ------------------------------------
+	// Every rank keeps FULL-SIZE grid arrays with global indexing and works on the cells / face nodes with z in
+	// [z0, z1); particles are owned by the rank whose slab contains their cell.  All device memory of a sharded
+	// handle comes from ONE arena, so one CUDA-IPC handle per rank makes every array of every rank addressable
+	// from every rank at the same offset (fs3_peer).  Ranks exchange data with plain stores / copies into the
+	// peers' arrays over NVLink and order them with epoch flags (shard.cu).
+	int rank, world, z0, z1;
+	bool lockstep;             // all ranks live in this process, share one stream and are stepped phase by phase:
+	                           // waits are then satisfied by stream order and never spin (single-GPU testing)
+	bool owns_stream;
+	char* arena;
+	size_t arena_bytes, arena_used;
+	char* peer_base[FS3_MAX_WORLD];   // arena of rank r mapped into this process (own rank: arena)
+	int n_ipc_opened;
+	size_t poff;               // live particles sit at [poff, poff+np_in) of pos/vel; ghost layers just below / above
+	long long gcap;            // capacity of each ghost region (== poff)
+	long long np_in;           // length of the live range including dead slots (id < 0) left by emigrants; == np when sorted
+	long long np_all[FS3_MAX_WORLD];  // live particle count of every rank, tracked identically on all ranks
+	uint32_t* mig_matrix;      // world x world: [r*world+d] = particles rank r sends to rank d (row r written by rank r)
+	uint32_t* mig_ctl;         // [0,world) counts, [world,2world) cursors, [2world] number of emigrants
+	uint32_t* leaver_idx;      // indices (relative to poff) of this step's emigrants
+	float4 *mig_pos, *mig_vel; // emigrants grouped by destination
+	long long mig_cap;
+	uint32_t* h_pin;           // pinned host scratch (count matrix)
+	uint32_t* bar;             // [r] barrier epoch written by rank r; [FS3_MAX_WORLD+0/1] SOR epoch of the lower/upper neighbour
+	uint32_t bar_epoch, sor_epoch;
+	uint32_t* sor_done;        // block counter of the fused end-of-sweep signal
+	uint32_t sor_e0;           // SOR epoch of "system set up" of the current projection
+
+	int* dev_flags;            // [0] particle outside, [1] level-set wait timeout, [2] cross-rank wait failed, [3] shard capacity
 	void* stage_ptr;           // device staging for AoS / hook transfers at the boundary
 	size_t stage_bytes;
 	cudaEvent_t ev[FS3_T_COUNT + 2];
@@ -176,11 +206,41 @@ __device__ __forceinline__ int fs3_halfcell_axis(float p, float n, int& cell) {
 		for (uint32_t hq_ = 0, B = __ldg((start) + (size_t)(2 * (cx)) + (size_t)(2 * (d).nx) * ((size_t)(2 * (cy) + (hr_ & 1)) + (size_t)(2 * (d).ny) * (2 * (cz) + (hr_ >> 1)))), \
 		              E = __ldg((start) + (size_t)(2 * (cx)) + 2 + (size_t)(2 * (d).nx) * ((size_t)(2 * (cy) + (hr_ & 1)) + (size_t)(2 * (d).ny) * (2 * (cz) + (hr_ >> 1)))); hq_ < 1; hq_++)
 
+// ---- cross-rank epoch flags (system scope: the writer is another GPU) ---------------------------------
+__device__ __forceinline__ uint32_t fs3_ld_acquire_sys(const uint32_t* p) {
+	uint32_t v;
+	asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ uint32_t fs3_ld_relaxed_sys(const uint32_t* p) {
+	uint32_t v;
+	asm volatile("ld.relaxed.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void fs3_st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory"); }
+// Waits until *f has reached `need` (epochs wrap: signed difference).  Never hangs: gives up after ~4 s (or at once in
+// lockstep mode, where stream order must already have satisfied the wait) and raises flags[2].
+__device__ __forceinline__ void fs3_flag_wait(const uint32_t* f, uint32_t need, int* flags, int nospin) {
+	if ((int32_t)(fs3_ld_acquire_sys(f) - need) >= 0) return;
+	if (nospin) { flags[2] = 1; return; }
+	long long t0 = clock64();
+	for (unsigned it = 1;; it++) {
+		if ((int32_t)(fs3_ld_relaxed_sys(f) - need) >= 0) break;
+		__nanosleep(64);
+		if ((it & 1023u) == 0) {
+			if (*reinterpret_cast<volatile int*>(flags + 2)) return;
+			if (clock64() - t0 > 8000000000LL) { flags[2] = 1; return; }
+		}
+	}
+	(void)fs3_ld_acquire_sys(f);
+}
+
+
 // ---- host-side launchers implemented in the .cu files -------------------------------------------
 int fs3i_reset(fs3_sim* s);
 int fs3i_advect(fs3_sim* s, float dt);
 int fs3i_bin(fs3_sim* s);
-int fs3i_scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n);   // exclusive scan on the handle's stream
+int fs3i_scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n, uint32_t base0 = 0);   // exclusive scan (+ base0) on the handle's stream
 int fs3i_unsort_particles(fs3_sim* s, fs3_particle* dev_out);              // creation order AoS into device buffer
 int fs3i_load_particles(fs3_sim* s, const fs3_particle* dev_in, long long count);
 int fs3i_cell_indices(fs3_sim* s, int* dev_out);                            // creation order
@@ -200,3 +260,41 @@ int fs3i_levelset_init(fs3_sim* s);
 int fs3i_staging(fs3_sim* s, size_t bytes);
 int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs);
 int fs3i_extrap_fill(fs3_sim* s, int slot, float* grid, int xs, int ys, int zs);
+int fs3i_alloc(fs3_sim* s, void** p, size_t bytes);                         // arena (sharded) or cudaMalloc
+void fs3i_free(fs3_sim* s, void* p);
+int fs3i_check_flags(fs3_sim* s);
+// particles.cu (sharded pieces)
+int fs3i_reset_grids(fs3_sim* s);
+int fs3i_reset_particles_slab(fs3_sim* s);
+int fs3i_mig_mark(fs3_sim* s);                                              // emigrants of the live range (not fused with Advect)
+int fs3i_mig_pack(fs3_sim* s);
+int fs3i_load_particles_owned(fs3_sim* s, const fs3_particle* dev_in, long long count);
+// project.cu (sharded pieces)
+int fs3i_project_setup(fs3_sim* s, float dt, bool from_old, bool with_gravity);
+int fs3i_sor_prepare(fs3_sim* s);
+int fs3i_sor_half_launch(fs3_sim* s, int k);                                // half sweep k of the current projection
+int fs3i_project_gradient(fs3_sim* s, float dt, bool from_old, bool with_gravity);
+// levelset.cu / p2g.cu pieces
+int fs3i_levelset_seed(fs3_sim* s);
+int fs3i_levelset_sweeps(fs3_sim* s);
+int fs3i_p2g_gather(fs3_sim* s);
+void fs3i_p2g_range(const fs3_sim* s, int ax, size_t* q0, size_t* q1);
+int fs3i_extrapolate_all(fs3_sim* s);
+// shard.cu
+int fs3i_shard_alloc(fs3_sim* s);
+int fs3i_signal(fs3_sim* s);                                                // barrier, first half: publish my epoch to all ranks
+int fs3i_wait(fs3_sim* s);                                                  // barrier, second half: all ranks reached my epoch
+int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes);        // copy a range of one of my arrays into the same range of every peer
+int fs3i_sor_signal(fs3_sim* s);                                            // "system set up": first SOR epoch of this projection to both neighbours
+int fs3i_sor_wait(fs3_sim* s, uint32_t epoch);
+int fs3i_ghost_pull(fs3_sim* s);
+int fs3i_mig_publish(fs3_sim* s);
+int fs3i_mig_exchange(fs3_sim* s);
+int fs3i_step_phase(fs3_sim* s, int phase, float dt);
+int fs3i_reset_phase(fs3_sim* s, int phase);
+int fs3i_num_step_phases(const fs3_sim* s);
+size_t fs3i_arena_bytes(int n, long long ptot, long long mig_cap, int world);
+
+template <typename T> static inline T* fs3_peer(const fs3_sim* s, int r, T* p) {
+	return reinterpret_cast<T*>(s->peer_base[r] + (reinterpret_cast<char*>(p) - s->arena));
+}

@@ -25,10 +25,9 @@ __device__ __forceinline__ float ls_dist(float cx, float cy, float cz, float4 q,
 // Seed (S3D.cpp:281-300): minimum kernel distance over the particles of the cell (its 8 half-cells); the
 // reference's strict `phi > k` in index order keeps the lowest index on ties.
 __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos, const uint32_t* __restrict__ start, GridDims d, float radius,
-                                                 float4* __restrict__ rec) {
-	size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	size_t nc = (size_t)d.nx * d.ny * d.nz;
-	if (c >= nc) return;
+                                                 float4* __restrict__ rec, size_t c0, size_t c1) {
+	size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= c1) return;
 	int x = (int)(c % d.nx), y = (int)((c / d.nx) % d.ny), z = (int)(c / ((size_t)d.nx * d.ny));
 	float4 best = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
 	float bk = 0.f;
@@ -301,14 +300,27 @@ __global__ void __launch_bounds__(32 * LS_WARPS) k_ls_sweep_dataflow(float4* __r
 #undef SMI
 }
 
+// seed of the cells of this rank's slab (world == 1: all cells)
+int fs3i_levelset_seed(fs3_sim* s) {
+	GridDims d{s->nx, s->ny, s->nz};
+	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SEED], s->stream);
+	const size_t plane = (size_t)s->nx * s->ny, c0 = plane * s->z0, c1 = plane * s->z1;
+	k_ls_seed<<<cdiv((long long)(c1 - c0), 256), 256, 0, s->stream>>>(s->pos[s->cur], s->cell_start, d, s->prm.particle_radius, s->ls_rec, c0, c1);
+	FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
 int fs3i_levelset(fs3_sim* s) {
 	int rc = fs3i_bin(s);
 	if (rc) return rc;
+	if ((rc = fs3i_levelset_seed(s))) return rc;
+	return fs3i_levelset_sweeps(s);
+}
+
+// the 8 sweeps over the WHOLE grid (a sharded handle runs them replicated on the gathered seed records)
+int fs3i_levelset_sweeps(fs3_sim* s) {
 	GridDims d{s->nx, s->ny, s->nz};
 	float radius = s->prm.particle_radius;
-	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SEED], s->stream);
-	k_ls_seed<<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->cell_start, d, radius, s->ls_rec);
-	FS3_LAUNCH_CHECK();
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SWEEP], s->stream);
 	int ntx = cdiv(d.nx, LS_TX), nty = cdiv(d.ny, LS_TY), ntz = cdiv(d.nz, LS_TZ);
 	FS3_CUDA(cudaMemsetAsync(s->ls_ticket, 0, sizeof(uint32_t), s->stream));
@@ -379,9 +391,10 @@ int fs3i_levelset_init(fs3_sim* s) {
 	std::stable_sort(items.begin(), items.end(), [](const std::pair<int, uint32_t>& a, const std::pair<int, uint32_t>& b) { return a.first < b.first; });
 	std::vector<uint32_t> ord(items.size());
 	for (size_t i = 0; i < items.size(); i++) ord[i] = items[i].second;
-	FS3_CUDA(cudaMalloc((void**)&s->ls_order, sizeof(uint32_t) * ord.size()));
-	FS3_CUDA(cudaMalloc((void**)&s->ls_done, sizeof(uint32_t) * nt));
-	FS3_CUDA(cudaMalloc((void**)&s->ls_ticket, sizeof(uint32_t)));
+	int rc;
+	if ((rc = fs3i_alloc(s, (void**)&s->ls_order, sizeof(uint32_t) * ord.size()))) return rc;
+	if ((rc = fs3i_alloc(s, (void**)&s->ls_done, sizeof(uint32_t) * nt))) return rc;
+	if ((rc = fs3i_alloc(s, (void**)&s->ls_ticket, sizeof(uint32_t)))) return rc;
 	FS3_CUDA(cudaMemcpyAsync(s->ls_order, ord.data(), sizeof(uint32_t) * ord.size(), cudaMemcpyHostToDevice, s->stream));
 	FS3_CUDA(cudaMemsetAsync(s->ls_done, 0, sizeof(uint32_t) * nt, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));

@@ -16,10 +16,10 @@
 template <int AX>
 __global__ void __launch_bounds__(128) k_p2g_gather(const float4* __restrict__ pos, const float4* __restrict__ vel,
                                                     const uint32_t* __restrict__ start, GridDims d, float cpm, float* __restrict__ grid,
-                                                    int* __restrict__ cd) {
+                                                    int* __restrict__ cd, size_t q0, size_t q1) {
 	const int xs = d.nx + (AX == 0), ys = d.ny + (AX == 1), zs = d.nz + (AX == 2);
-	size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (q >= (size_t)xs * ys * zs) return;
+	size_t q = q0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (q >= q1) return;
 	int i = (int)(q % xs), j = (int)((q / xs) % ys), k = (int)(q / ((size_t)xs * ys));
 	// wall planes: forced to zero and valid (S3D.cpp:578-599)
 	int m_ax = AX == 0 ? i : (AX == 1 ? j : k), n_ax = AX == 0 ? d.nx : (AX == 1 ? d.ny : d.nz);
@@ -228,16 +228,39 @@ int fs3i_extrapolate(fs3_sim* s, float* grid, int xs, int ys, int zs) {
 	return fs3i_extrap_fill(s, 0, grid, xs, ys, zs);
 }
 
-int fs3i_p2g(fs3_sim* s) {
-	int rc = fs3i_bin(s);
-	if (rc) return rc;
+// Face nodes of this rank's slab: z planes [z0, z1) of every face grid, plus the top W plane on the last rank.
+void fs3i_p2g_range(const fs3_sim* s, int ax, size_t* q0, size_t* q1) {
+	const size_t plane = (size_t)(s->nx + (ax == 0)) * (s->ny + (ax == 1));
+	*q0 = plane * s->z0;
+	*q1 = plane * (s->z1 + ((ax == 2 && s->rank == s->world - 1) ? 1 : 0));
+}
+
+int fs3i_p2g_gather(fs3_sim* s) {
 	GridDims d{s->nx, s->ny, s->nz};
 	const float4 *pos = s->pos[s->cur], *vel = s->vel[s->cur];
 	// P2G writes the "old" set; the projected field is produced from it by fs3i_project (no copy, S3D.cpp:123-134)
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_P2G], s->stream);
-	k_p2g_gather<0><<<cdiv((long long)s->nU, 128), 128, 0, s->stream>>>(pos, vel, s->cell_start, d, s->cpm, s->oU, s->cdv[0]); FS3_LAUNCH_CHECK();
-	k_p2g_gather<1><<<cdiv((long long)s->nV, 128), 128, 0, s->stream>>>(pos, vel, s->cell_start, d, s->cpm, s->oV, s->cdv[1]); FS3_LAUNCH_CHECK();
-	k_p2g_gather<2><<<cdiv((long long)s->nW, 128), 128, 0, s->stream>>>(pos, vel, s->cell_start, d, s->cpm, s->oW, s->cdv[2]); FS3_LAUNCH_CHECK();
+	size_t a, b;
+	fs3i_p2g_range(s, 0, &a, &b);
+	k_p2g_gather<0><<<cdiv((long long)(b - a), 128), 128, 0, s->stream>>>(pos, vel, s->cell_start, d, s->cpm, s->oU, s->cdv[0], a, b); FS3_LAUNCH_CHECK();
+	fs3i_p2g_range(s, 1, &a, &b);
+	k_p2g_gather<1><<<cdiv((long long)(b - a), 128), 128, 0, s->stream>>>(pos, vel, s->cell_start, d, s->cpm, s->oV, s->cdv[1], a, b); FS3_LAUNCH_CHECK();
+	fs3i_p2g_range(s, 2, &a, &b);
+	k_p2g_gather<2><<<cdiv((long long)(b - a), 128), 128, 0, s->stream>>>(pos, vel, s->cell_start, d, s->cpm, s->oW, s->cdv[2], a, b); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+int fs3i_p2g(fs3_sim* s) {
+	int rc = fs3i_bin(s);
+	if (rc) return rc;
+	if ((rc = fs3i_p2g_gather(s))) return rc;
+	return fs3i_extrapolate_all(s);
+}
+
+// the three face grids over the WHOLE grid (a sharded handle runs this replicated on the gathered P2G result)
+int fs3i_extrapolate_all(fs3_sim* s) {
+	GridDims d{s->nx, s->ny, s->nz};
+	int rc;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_EXTRAPOLATE], s->stream);
 	for (int ax = 0; ax < 3; ax++) {
 		rc = fs3i_extrap_prepare(s, ax, d.nx + (ax == 0), d.ny + (ax == 1), d.nz + (ax == 2));

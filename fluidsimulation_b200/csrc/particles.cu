@@ -4,6 +4,7 @@
 // float4 SoA arrays; particles are kept physically sorted by cell so that the grid gathers of one
 // warp hit a handful of neighbouring cache lines.
 #include "fs3_internal.cuh"
+#include <algorithm>
 
 // ------------------------------------------------------------------------------------------------
 // ResetSimulation (S3D.cpp:41-99).  std::default_random_engine(0) is minstd_rand0 in libstdc++:
@@ -38,11 +39,14 @@ __global__ void k_reset_grids(float* __restrict__ U, float* __restrict__ V, floa
 	}
 }
 
-__global__ void k_reset_particles(float4* __restrict__ pos, float4* __restrict__ vel, long long np, GridDims d, float cpm,
+// creation ids [j0, j0+np) are written to pos[0..np) (a z-slab of the block generates a contiguous id range)
+__global__ void k_reset_particles(float4* __restrict__ pos, float4* __restrict__ vel, long long np, long long j0, GridDims d, float cpm,
                                   const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W,
                                   unsigned long long draw0) {
 	long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (j >= np) return;
+	pos -= j0; vel -= j0;   // slot of creation id j is j - j0
+	j += j0;
 	int c = (int)(j & 1), b = (int)((j >> 1) & 1), a = (int)((j >> 2) & 1);
 	long long cellj = j >> 3;
 	int xc = d.nx - 1 - d.nx / 2, yc = d.ny - 2;
@@ -59,31 +63,76 @@ __global__ void k_reset_particles(float4* __restrict__ pos, float4* __restrict__
 	vel[j] = make_float4(u.x, u.y, u.z, 0.0f);
 }
 
-int fs3i_reset(fs3_sim* s) {
+int fs3i_reset_grids(fs3_sim* s) {
 	size_t tot = s->nU + s->nV + s->nW;
 	k_reset_grids<<<cdiv((long long)tot, 256 * 4), 256, 0, s->stream>>>(s->U, s->V, s->W, s->nU, s->nV, s->nW);
 	FS3_LAUNCH_CHECK();
-	long long np = 8LL * (s->nz - 2) * (s->ny - 2) * (s->nx - 1 - s->nx / 2);
-	s->np = np;
 	s->cur = 0;
 	s->sorted = false;
 	s->closest_valid = false;
 	s->system_valid = false;
-	GridDims d{s->nx, s->ny, s->nz};
-	k_reset_particles<<<cdiv(np, 256), 256, 0, s->stream>>>(s->pos[0], s->vel[0], np, d, s->cpm, s->U, s->V, s->W,
-	                                                         (unsigned long long)tot + 1ull);
-	FS3_LAUNCH_CHECK();
 	return FS3_OK;
+}
+
+// Particles whose GENERATING cell lies in this rank's slab (world == 1: all of them); the generating cells of the dam-break
+// block are z in [1, nz-1), z slowest, so a slab is a contiguous range of creation ids.  A jittered particle can round into
+// the neighbouring slab: the sharded reset runs one migration afterwards.
+int fs3i_reset_particles_slab(fs3_sim* s) {
+	size_t tot = s->nU + s->nV + s->nW;
+	const long long per_layer = 8LL * (s->ny - 2) * (s->nx - 1 - s->nx / 2);
+	for (int r = 0; r < s->world; r++) {
+		int zs = s->nz / s->world, a = std::max(r * zs, 1), b = std::min((r + 1) * zs, s->nz - 1);
+		s->np_all[r] = per_layer * std::max(0, b - a);
+	}
+	const int zlo = std::max(s->z0, 1), zhi = std::min(s->z1, s->nz - 1);
+	const long long np = per_layer * std::max(0, zhi - zlo), j0 = per_layer * (zlo - 1);
+	if (np > s->cap) { s->err = "particle capacity of the slab exceeded at reset"; return FS3_ERR_STATE; }
+	s->np = s->np_in = np;
+	GridDims d{s->nx, s->ny, s->nz};
+	if (np > 0) {
+		k_reset_particles<<<cdiv(np, 256), 256, 0, s->stream>>>(s->pos[0] + s->poff, s->vel[0] + s->poff, np, j0, d, s->cpm, s->U, s->V, s->W,
+		                                                         (unsigned long long)tot + 1ull);
+		FS3_LAUNCH_CHECK();
+	}
+	return FS3_OK;
+}
+
+int fs3i_reset(fs3_sim* s) {
+	int rc = fs3i_reset_grids(s);
+	if (rc) return rc;
+	return fs3i_reset_particles_slab(s);
 }
 
 // ------------------------------------------------------------------------------------------------
 // Advect (S3D.cpp:190-232): Ralston RK3 through the grid, clamp into the box.
 // ------------------------------------------------------------------------------------------------
+// Emigrant bookkeeping of a sharded handle: destination rank = slab of the particle's cell, (int)roundf(n*Z) (S3D.cpp:288).
+struct MigArgs {
+	uint32_t* ctl;       // [0,world) per-destination counts, [world,2world) cursors, [2world] number of emigrants
+	uint32_t* leaver;    // their indices in the live range
+	uint32_t cap;
+	int rank, world, slab, nz;
+};
+__device__ __forceinline__ int mig_owner(const MigArgs& m, float z) {
+	int cz = min(max(fs3_cell_axis(z, (float)m.nz), 0), m.nz - 1);
+	return cz / m.slab;
+}
+__device__ __forceinline__ void mig_note(const MigArgs& m, long long i, float z) {
+	int dest = mig_owner(m, z);
+	if (dest != m.rank) {
+		atomicAdd(m.ctl + dest, 1u);
+		uint32_t k = atomicAdd(m.ctl + 2 * m.world, 1u);
+		if (k < m.cap) m.leaver[k] = (uint32_t)i;
+	}
+}
+
+template <bool SHARD>
 __global__ void __launch_bounds__(256) k_advect(float4* __restrict__ pos, long long np, GridDims d, float dt,
-                                                const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W) {
+                                                const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W, MigArgs mig) {
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	float4 p = pos[i];
+	if (__float_as_int(p.w) < 0) return;   // dead slot (emigrated)
 	float fx = (float)d.nx, fy = (float)d.ny, fz = (float)d.nz;
 	float3 k1 = fs3_interp(U, V, W, d, __fmul_rn(fx, p.x), __fmul_rn(fy, p.y), __fmul_rn(fz, p.z));
 	float h = __fmul_rn(0.5f, dt);
@@ -104,15 +153,70 @@ __global__ void __launch_bounds__(256) k_advect(float4* __restrict__ pos, long l
 	p.y = fs3_clamp(p.y, (-0.5f + eps) / fy, __fadd_rn(1.0f, (-0.5f - eps) / fy));
 	p.z = fs3_clamp(p.z, (-0.5f + eps) / fz, __fadd_rn(1.0f, (-0.5f - eps) / fz));
 	pos[i] = p;
+	if (SHARD) mig_note(mig, i, p.z);
+}
+
+static MigArgs mig_args(fs3_sim* s) {
+	MigArgs m;
+	m.ctl = s->mig_ctl; m.leaver = s->leaver_idx; m.cap = (uint32_t)s->mig_cap;
+	m.rank = s->rank; m.world = s->world; m.slab = s->nz / s->world; m.nz = s->nz;
+	return m;
 }
 
 int fs3i_advect(fs3_sim* s, float dt) {
-	if (s->np <= 0) return FS3_OK;
 	GridDims d{s->nx, s->ny, s->nz};
-	k_advect<<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, dt, s->U, s->V, s->W);
-	FS3_LAUNCH_CHECK();
 	s->sorted = false;
 	s->closest_valid = false;
+	if (s->world > 1) {
+		FS3_CUDA(cudaMemsetAsync(s->mig_ctl, 0, (2 * s->world + 1) * sizeof(uint32_t), s->stream));
+		if (s->np_in > 0) {
+			k_advect<true><<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->np_in, d, dt, s->U, s->V, s->W, mig_args(s));
+			FS3_LAUNCH_CHECK();
+		}
+		return FS3_OK;
+	}
+	if (s->np <= 0) return FS3_OK;
+	k_advect<false><<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, dt, s->U, s->V, s->W, MigArgs{});
+	FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+// Emigrants of the live range without moving anything (after reset / a particle upload).
+__global__ void __launch_bounds__(256) k_mig_mark(const float4* __restrict__ pos, long long np, MigArgs mig) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	float4 p = pos[i];
+	if (__float_as_int(p.w) < 0) return;
+	mig_note(mig, i, p.z);
+}
+int fs3i_mig_mark(fs3_sim* s) {
+	FS3_CUDA(cudaMemsetAsync(s->mig_ctl, 0, (2 * s->world + 1) * sizeof(uint32_t), s->stream));
+	if (s->np_in > 0) { k_mig_mark<<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->np_in, mig_args(s)); FS3_LAUNCH_CHECK(); }
+	s->sorted = false;
+	return FS3_OK;
+}
+
+// Emigrants -> outgoing buffers grouped by destination rank; their slots become dead (id = -1).
+__global__ void __launch_bounds__(256) k_mig_pack(float4* __restrict__ pos, const float4* __restrict__ vel, MigArgs mig, float4* __restrict__ opos,
+                                                  float4* __restrict__ ovel, int* __restrict__ flags) {
+	const uint32_t n = mig.ctl[2 * mig.world];
+	if (n > mig.cap) { if (blockIdx.x == 0 && threadIdx.x == 0) flags[3] = 1; return; }
+	for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+		const uint32_t i = mig.leaver[t];
+		float4 p = pos[i];
+		const int dest = mig_owner(mig, p.z);
+		uint32_t base = 0;
+		for (int r = 0; r < dest; r++) base += mig.ctl[r];
+		const uint32_t slot = base + atomicAdd(mig.ctl + mig.world + dest, 1u);
+		opos[slot] = p;
+		ovel[slot] = vel[i];
+		pos[i].w = __int_as_float(-1);
+	}
+}
+int fs3i_mig_pack(fs3_sim* s) {
+	k_mig_pack<<<std::max(1, std::min(cdiv(s->mig_cap, 256), s->sm_count * 4)), 256, 0, s->stream>>>(
+	    s->pos[s->cur] + s->poff, s->vel[s->cur] + s->poff, mig_args(s), s->mig_pos, s->mig_vel, s->dev_flags);
+	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 
@@ -124,16 +228,17 @@ int fs3i_advect(fs3_sim* s, float dt) {
 // is deterministic (no dependence on atomic arrival order) and "lowest index wins" tie-breaks
 // (S3D.cpp:296) fall out of a forward scan of the cell's segment.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_bin_count(const float4* __restrict__ pos, long long np, GridDims d, uint32_t* __restrict__ cellid,
-                                                   uint32_t* __restrict__ count, int* __restrict__ flags) {
+__global__ void __launch_bounds__(256) k_bin_count(const float4* __restrict__ pos, long long np, GridDims d, int zlo, int zhi,
+                                                   uint32_t* __restrict__ cellid, uint32_t* __restrict__ count, int* __restrict__ flags) {
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	float4 p = pos[i];
+	if (__float_as_int(p.w) < 0) { cellid[i] = 0xffffffffu; return; }   // dead slot of an emigrant
 	int cx, cy, cz;
 	int hx = fs3_halfcell_axis(p.x, (float)d.nx, cx), hy = fs3_halfcell_axis(p.y, (float)d.ny, cy), hz = fs3_halfcell_axis(p.z, (float)d.nz, cz);
-	if (cx < 0 || cx >= d.nx || cy < 0 || cy >= d.ny || cz < 0 || cz >= d.nz) {
-		flags[0] = 1;  // outside the box: the reference skips such particles; Advect's clamp makes this unreachable
-		hx = min(max(hx, 0), 2 * d.nx - 1); hy = min(max(hy, 0), 2 * d.ny - 1); hz = min(max(hz, 0), 2 * d.nz - 1);
+	if (cx < 0 || cx >= d.nx || cy < 0 || cy >= d.ny || cz < zlo || cz >= zhi) {
+		flags[0] = 1;  // outside the box (or the slab): the reference skips such particles; Advect's clamp makes this unreachable
+		hx = min(max(hx, 0), 2 * d.nx - 1); hy = min(max(hy, 0), 2 * d.ny - 1); hz = min(max(hz, 2 * zlo), 2 * zhi - 1);
 	}
 	uint32_t c = (uint32_t)hx + (uint32_t)(2 * d.nx) * ((uint32_t)hy + (uint32_t)(2 * d.ny) * (uint32_t)hz);
 	cellid[i] = c;
@@ -197,22 +302,22 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_blocks(uint32_t* __restrict__ b
 	}
 }
 __global__ void __launch_bounds__(SCAN_T) k_scan_apply(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
-                                                       const uint32_t* __restrict__ bsum) {
+                                                       const uint32_t* __restrict__ bsum, uint32_t base0) {
 	size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_I;
 	uint32_t loc[SCAN_I], v = 0;
 #pragma unroll
 	for (int k = 0; k < SCAN_I; k++) { loc[k] = base + k < n ? in[base + k] : 0; v += loc[k]; }
-	uint32_t ex = block_excl_scan(v, nullptr) + bsum[blockIdx.x];
+	uint32_t ex = block_excl_scan(v, nullptr) + bsum[blockIdx.x] + base0;
 #pragma unroll
 	for (int k = 0; k < SCAN_I; k++) { if (base + k < n) out[base + k] = ex; ex += loc[k]; }
 }
 
-int fs3i_scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n) {
+int fs3i_scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n, uint32_t base0) {
 	int nb = cdiv((long long)n, SCAN_TILE);
 	if ((size_t)nb > s->scan_block_cap) { s->err = "scan scratch too small"; return FS3_ERR_STATE; }
 	k_scan_reduce<<<nb, SCAN_T, 0, s->stream>>>(in, n, s->scan_block); FS3_LAUNCH_CHECK();
 	k_scan_blocks<<<1, SCAN_T, 0, s->stream>>>(s->scan_block, nb); FS3_LAUNCH_CHECK();
-	k_scan_apply<<<nb, SCAN_T, 0, s->stream>>>(in, out, n, s->scan_block); FS3_LAUNCH_CHECK();
+	k_scan_apply<<<nb, SCAN_T, 0, s->stream>>>(in, out, n, s->scan_block, base0); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 
@@ -221,6 +326,7 @@ __global__ void __launch_bounds__(256) k_bin_scatter_ids(const float4* __restric
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	uint32_t c = cellid[i];
+	if (c == 0xffffffffu) return;
 	uint32_t slot = start[c] + atomicAdd(fill + c, 1u);
 	tmp_id[slot] = __float_as_int(pos[i].w);
 }
@@ -230,8 +336,9 @@ __global__ void __launch_bounds__(256) k_bin_rank_gather(const float4* __restric
                                                          const int* __restrict__ tmp_id, float4* __restrict__ pout, float4* __restrict__ vout) {
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
-	float4 p = pin[i], v = vin[i];
 	uint32_t c = cellid[i];
+	if (c == 0xffffffffu) return;
+	float4 p = pin[i], v = vin[i];
 	uint32_t b = start[c], e = start[c + 1];
 	int id = __float_as_int(p.w);
 	uint32_t rank = 0;
@@ -240,23 +347,32 @@ __global__ void __launch_bounds__(256) k_bin_rank_gather(const float4* __restric
 	vout[b + rank] = v;
 }
 
+// Sorts the live range [poff, poff+np_in) of buffer `cur` (dead slots dropped) into [poff, poff+np) of the other buffer.
+// A sharded handle only owns the half-cell keys of its slab, [K0, K1): counts, scan and cursors are restricted to them and
+// cell_start holds ABSOLUTE slots (poff included), so that the neighbours' boundary layers can be spliced in below / above
+// (fs3i_ghost_pull) and the gather kernels index pos/vel from the buffer base.
 int fs3i_bin(fs3_sim* s) {
 	if (s->sorted) return FS3_OK;
-	FS3_CUDA(cudaMemsetAsync(s->cell_count, 0, (s->nH + 1) * sizeof(uint32_t), s->stream));
-	FS3_CUDA(cudaMemsetAsync(s->cell_fill, 0, s->nH * sizeof(uint32_t), s->stream));
-	if (s->np > 0) {
+	const size_t hplane = (size_t)(2 * s->nx) * (2 * s->ny);
+	const size_t K0 = hplane * (size_t)(2 * s->z0), K1 = hplane * (size_t)(2 * s->z1);
+	FS3_CUDA(cudaMemsetAsync(s->cell_count + K0, 0, (K1 - K0 + 1) * sizeof(uint32_t), s->stream));
+	FS3_CUDA(cudaMemsetAsync(s->cell_fill + K0, 0, (K1 - K0) * sizeof(uint32_t), s->stream));
+	if (s->np_in > 0) {
 		GridDims d{s->nx, s->ny, s->nz};
-		int nb = cdiv(s->np, 256);
-		k_bin_count<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, s->cellid, s->cell_count, s->dev_flags); FS3_LAUNCH_CHECK();
-		int rc = fs3i_scan_u32(s, s->cell_count, s->cell_start, s->nH + 1);
+		int nb = cdiv(s->np_in, 256);
+		const float4 *pin = s->pos[s->cur] + s->poff, *vin = s->vel[s->cur] + s->poff;
+		k_bin_count<<<nb, 256, 0, s->stream>>>(pin, s->np_in, d, s->z0, s->z1, s->cellid, s->cell_count, s->dev_flags); FS3_LAUNCH_CHECK();
+		int rc = fs3i_scan_u32(s, s->cell_count + K0, s->cell_start + K0, K1 - K0 + 1, (uint32_t)s->poff);
 		if (rc) return rc;
-		k_bin_scatter_ids<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->cellid, s->np, s->cell_start, s->cell_fill, s->tmp_id); FS3_LAUNCH_CHECK();
-		k_bin_rank_gather<<<nb, 256, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->cellid, s->np, s->cell_start, s->tmp_id,
+		k_bin_scatter_ids<<<nb, 256, 0, s->stream>>>(pin, s->cellid, s->np_in, s->cell_start, s->cell_fill, s->tmp_id); FS3_LAUNCH_CHECK();
+		k_bin_rank_gather<<<nb, 256, 0, s->stream>>>(pin, vin, s->cellid, s->np_in, s->cell_start, s->tmp_id,
 		                                              s->pos[s->cur ^ 1], s->vel[s->cur ^ 1]); FS3_LAUNCH_CHECK();
 		s->cur ^= 1;
 	} else {
-		FS3_CUDA(cudaMemsetAsync(s->cell_start, 0, (s->nH + 1) * sizeof(uint32_t), s->stream));
+		int rc = fs3i_scan_u32(s, s->cell_count + K0, s->cell_start + K0, K1 - K0 + 1, (uint32_t)s->poff);
+		if (rc) return rc;
 	}
+	s->np_in = s->np;
 	s->sorted = true;
 	return FS3_OK;
 }
@@ -268,6 +384,7 @@ __global__ void k_unsort(const float4* __restrict__ pos, const float4* __restric
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	float4 p = pos[i], v = vel[i];
+	if (__float_as_int(p.w) < 0) return;
 	fs3_particle q{p.x, p.y, p.z, v.x, v.y, v.z};
 	out[__float_as_int(p.w)] = q;
 }
@@ -282,26 +399,55 @@ __global__ void k_cell_indices(const float4* __restrict__ pos, long long np, Gri
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	float4 p = pos[i];
+	if (__float_as_int(p.w) < 0) return;
 	int cx = fs3_cell_axis(p.x, (float)d.nx), cy = fs3_cell_axis(p.y, (float)d.ny), cz = fs3_cell_axis(p.z, (float)d.nz);
 	bool in = cx >= 0 && cx < d.nx && cy >= 0 && cy < d.ny && cz >= 0 && cz < d.nz;
 	out[__float_as_int(p.w)] = in ? cx + d.nx * (cy + d.ny * cz) : -1;
 }
 
 int fs3i_unsort_particles(fs3_sim* s, fs3_particle* dev_out) {
-	if (s->np <= 0) return FS3_OK;
-	k_unsort<<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->np, dev_out); FS3_LAUNCH_CHECK();
+	if (s->np_in <= 0) return FS3_OK;
+	k_unsort<<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->vel[s->cur] + s->poff, s->np_in, dev_out); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 int fs3i_load_particles(fs3_sim* s, const fs3_particle* dev_in, long long count) {
-	s->np = count; s->cur = 0; s->sorted = false; s->closest_valid = false;
+	s->np = s->np_in = count; s->cur = 0; s->sorted = false; s->closest_valid = false;
 	if (count <= 0) return FS3_OK;
 	k_load<<<cdiv(count, 256), 256, 0, s->stream>>>(dev_in, count, s->pos[0], s->vel[0]); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
+// Sharded upload: every rank is handed the SAME full array and keeps the particles whose cell lies in its slab
+// (creation id = array index).  The per-rank counts come out of the same pass, so no communication is needed.
+__global__ void __launch_bounds__(256) k_load_owned(const fs3_particle* __restrict__ in, long long n, MigArgs mig, float4* __restrict__ pos,
+                                                    float4* __restrict__ vel, uint32_t* __restrict__ counts, uint32_t cap, int* __restrict__ flags) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	fs3_particle q = in[i];
+	const int owner = mig_owner(mig, q.Z);
+	const uint32_t k = atomicAdd(counts + owner, 1u);
+	if (owner != mig.rank) return;
+	if (k >= cap) { flags[3] = 1; return; }
+	pos[k] = make_float4(q.X, q.Y, q.Z, __int_as_float((int)i));
+	vel[k] = make_float4(q.uX, q.uY, q.uZ, 0.0f);
+}
+int fs3i_load_particles_owned(fs3_sim* s, const fs3_particle* dev_in, long long count) {
+	s->cur = 0; s->sorted = false; s->closest_valid = false;
+	FS3_CUDA(cudaMemsetAsync(s->mig_ctl, 0, (2 * s->world + 1) * sizeof(uint32_t), s->stream));
+	if (count > 0) {
+		k_load_owned<<<cdiv(count, 256), 256, 0, s->stream>>>(dev_in, count, mig_args(s), s->pos[0] + s->poff, s->vel[0] + s->poff, s->mig_ctl,
+		                                                      (uint32_t)s->cap, s->dev_flags);
+		FS3_LAUNCH_CHECK();
+	}
+	FS3_CUDA(cudaMemcpyAsync(s->h_pin, s->mig_ctl, s->world * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	for (int r = 0; r < s->world; r++) s->np_all[r] = s->h_pin[r];
+	s->np = s->np_in = std::min<long long>(s->np_all[s->rank], s->cap);
+	return fs3i_check_flags(s);
+}
 int fs3i_cell_indices(fs3_sim* s, int* dev_out) {
-	if (s->np <= 0) return FS3_OK;
+	if (s->np_in <= 0) return FS3_OK;
 	GridDims d{s->nx, s->ny, s->nz};
-	k_cell_indices<<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, dev_out); FS3_LAUNCH_CHECK();
+	k_cell_indices<<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->np_in, d, dev_out); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 
@@ -335,6 +481,7 @@ __global__ void __launch_bounds__(256) k_g2p(const float4* __restrict__ pos, flo
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	float4 p = pos[i], v = vel[i];
+	if (__float_as_int(p.w) < 0) return;
 	float3 g = fs3_interp(U, V, W, d, __fmul_rn((float)d.nx, p.x), __fmul_rn((float)d.ny, p.y), __fmul_rn((float)d.nz, p.z));
 	v.x = __fadd_rn(__fmul_rn(om, v.x), g.x);
 	v.y = __fadd_rn(__fmul_rn(om, v.y), g.y);
@@ -343,9 +490,9 @@ __global__ void __launch_bounds__(256) k_g2p(const float4* __restrict__ pos, flo
 	vel[i] = v;
 }
 int fs3i_g2p(fs3_sim* s, float alpha) {
-	if (s->np <= 0) return FS3_OK;
+	if (s->np_in <= 0) return FS3_OK;
 	GridDims d{s->nx, s->ny, s->nz};
-	k_g2p<<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->np, d, 1.0f - alpha, s->oU, s->oV, s->oW);
+	k_g2p<<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->vel[s->cur] + s->poff, s->np_in, d, 1.0f - alpha, s->oU, s->oV, s->oW);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }

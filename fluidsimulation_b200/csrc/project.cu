@@ -32,11 +32,11 @@ template <typename REAL> struct Sys {
 template <typename REAL>
 __global__ void __launch_bounds__(256) k_project_setup(Sys<REAL> sy, const float* __restrict__ U, const float* __restrict__ V,
                                                        const float* __restrict__ W, const float* __restrict__ phi, REAL scale, float gdt,
-                                                       int add_g, REAL max_ratio) {
+                                                       int add_g, REAL max_ratio, size_t c0, size_t c1) {
 	typedef Ops<REAL> O;
 	const int nx = sy.rb.nx, ny = sy.rb.ny, nz = sy.rb.nz;
-	size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (c >= (size_t)nx * ny * nz) return;
+	size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= c1) return;
 	int x = (int)(c % nx), y = (int)((c / nx) % ny), z = (int)(c / ((size_t)nx * ny));
 	size_t iu = (size_t)x + (size_t)(nx + 1) * ((size_t)y + (size_t)ny * z);
 	size_t iv = (size_t)x + (size_t)nx * ((size_t)y + (size_t)(ny + 1) * z);
@@ -92,12 +92,30 @@ template <> struct VecT<float, 4> { typedef float4 type; typedef unsigned int mt
 // work, air is never touched, and consecutive list entries are consecutive in memory wherever the fluid
 // is, so accesses stay coalesced.  Entry = vector index | (x parity of the colour in that row) << 31.
 // Interior cells (mask bit7) have diag == popcount(fluid neighbours), so dg is only read near the surface.
-template <typename REAL, int VEC>
+// Sharded sweep (SHARD): the list holds the vectors of this rank's slab.  The kernel first waits until both z-neighbours
+// have published the previous half sweep (their boundary plane of the OTHER colour was stored straight into this rank's
+// ghost planes), stores the updated vectors of its own boundary planes into the neighbours' arrays over NVLink while it
+// sweeps, and the last block to finish publishes the epoch to both neighbours: compute and halo exchange are one kernel.
+struct SorShard {
+	void* peer_p[2];          // this colour's array of the lower / upper neighbour (nullptr: no neighbour)
+	uint32_t* peer_flag[2];   // where that neighbour expects this rank's epoch
+	const uint32_t* my_flag;  // [0] written by the lower, [1] by the upper neighbour
+	uint32_t wait_epoch, signal_epoch;
+	size_t lo_begin, lo_end, hi_begin, hi_end;   // element ranges of the slab's first / last plane in a colour array
+	uint32_t* done;           // block counter
+	int* flags;
+	int nospin;
+};
+template <typename REAL, int VEC, bool SHARD>
 __global__ void __launch_bounds__(256) k_sor_half(Sys<REAL> sy, int colour, REAL omega, REAL one_minus_omega,
-                                                  const uint32_t* __restrict__ list, const uint32_t* __restrict__ count) {
+                                                  const uint32_t* __restrict__ list, const uint32_t* __restrict__ count, SorShard sh) {
 	typedef Ops<REAL> O;
 	typedef typename VecT<REAL, VEC>::type V;
 	typedef typename VecT<REAL, VEC>::mtype M;
+	if (SHARD) {
+		if (threadIdx.x < 2 && sh.peer_flag[threadIdx.x]) fs3_flag_wait(sh.my_flag + threadIdx.x, sh.wait_epoch, sh.flags, sh.nospin);
+		__syncthreads();
+	}
 	const uint32_t n = __ldg(count);
 	const REAL* __restrict__ o = sy.p[colour ^ 1];
 	const M nodiag = VEC == 2 ? (M)0x8080 : (M)0x80808080u;
@@ -135,16 +153,34 @@ __global__ void __launch_bounds__(256) k_sor_half(Sys<REAL> sy, int colour, REAL
 			own[e] = O::add(O::mul(one_minus_omega, own[e]), O::div(O::mul(omega, O::sub(bb[e], nms)), dg));
 		}
 		*reinterpret_cast<V*>(sy.p[colour] + base) = *reinterpret_cast<V*>(own);
+		if (SHARD) {
+			if (sh.peer_p[0] && base >= sh.lo_begin && base < sh.lo_end) *reinterpret_cast<V*>(reinterpret_cast<REAL*>(sh.peer_p[0]) + base) = *reinterpret_cast<V*>(own);
+			if (sh.peer_p[1] && base >= sh.hi_begin && base < sh.hi_end) *reinterpret_cast<V*>(reinterpret_cast<REAL*>(sh.peer_p[1]) + base) = *reinterpret_cast<V*>(own);
+		}
+	}
+	if (SHARD) {
+		// publish: every thread's peer stores are made visible system-wide, then the last block raises the neighbours' flags
+		__threadfence_system();
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			const uint32_t t = atomicAdd(sh.done, 1u);
+			if (t == gridDim.x - 1) {
+				*sh.done = 0;
+				__threadfence_system();
+				if (sh.peer_flag[0]) fs3_st_release_sys(sh.peer_flag[0], sh.signal_epoch);
+				if (sh.peer_flag[1]) fs3_st_release_sys(sh.peer_flag[1], sh.signal_epoch);
+			}
+		}
 	}
 }
 
 // active-vector flags (+1 trailing zero so that the exclusive scan's last entry is the count) and compaction
 template <int VEC>
-__global__ void __launch_bounds__(256) k_sor_flags(const unsigned char* __restrict__ mask, size_t nvec, uint32_t* __restrict__ flags) {
+__global__ void __launch_bounds__(256) k_sor_flags(const unsigned char* __restrict__ mask, size_t nvec, uint32_t* __restrict__ flags, size_t v0, size_t v1) {
 	size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (v > nvec) return;
 	uint32_t f = 0;
-	if (v < nvec) {
+	if (v >= v0 && v < v1) {
 		if (VEC == 2) f = (*reinterpret_cast<const unsigned short*>(mask + v * 2) & 0x4040u) != 0;
 		else f = (*reinterpret_cast<const unsigned int*>(mask + v * 4) & 0x40404040u) != 0;
 	}
@@ -218,10 +254,10 @@ template <typename REAL>
 __global__ void __launch_bounds__(256) k_project_gradient(Sys<REAL> sy, const float* __restrict__ sU, const float* __restrict__ sV,
                                                           const float* __restrict__ sW, const float* __restrict__ phi, float* __restrict__ dU,
                                                           float* __restrict__ dV, float* __restrict__ dW, REAL scale, float gdt, int add_g,
-                                                          REAL max_ratio) {
+                                                          REAL max_ratio, size_t c0, size_t c1) {
 	const int nx = sy.rb.nx, ny = sy.rb.ny, nz = sy.rb.nz;
-	size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (c >= (size_t)nx * ny * nz) return;
+	size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= c1) return;
 	int x = (int)(c % nx), y = (int)((c / nx) % ny), z = (int)(c / ((size_t)nx * ny));
 	int col = (x + y + z) & 1, s = x & 1;
 	size_t q = sy.rb.at(x >> 1, y, z);
@@ -276,12 +312,17 @@ template <typename REAL> static Sys<REAL> make_sys(fs3_sim* s) {
 int fs3i_alloc_pressure(fs3_sim* s) {
 	int prec = s->prm.precision ? 1 : 0;
 	if (s->p[0] && s->alloc_precision == prec) return FS3_OK;
+	if (s->p[0] && s->world > 1) {
+		// a sharded handle allocates the fp64-sized system once (arena offsets must agree on all ranks) and reinterprets it
+		s->alloc_precision = prec; s->system_valid = false; s->sor_list_valid = false;
+		return FS3_OK;
+	}
 	for (int c = 0; c < 2; c++) {
-		if (s->p[c]) cudaFree(s->p[c]); if (s->b[c]) cudaFree(s->b[c]); if (s->dg[c]) cudaFree(s->dg[c]); if (s->mask[c]) cudaFree(s->mask[c]);
-		if (s->sor_list[c]) cudaFree(s->sor_list[c]); if (s->sor_pos[c]) cudaFree(s->sor_pos[c]);
+		fs3i_free(s, s->p[c]); fs3i_free(s, s->b[c]); fs3i_free(s, s->dg[c]); fs3i_free(s, s->mask[c]);
+		fs3i_free(s, s->sor_list[c]); fs3i_free(s, s->sor_pos[c]);
 		s->p[c] = s->b[c] = s->dg[c] = nullptr; s->mask[c] = nullptr; s->sor_list[c] = s->sor_pos[c] = nullptr;
 	}
-	if (s->sor_flags) cudaFree(s->sor_flags);
+	fs3i_free(s, s->sor_flags);
 	s->sor_flags = nullptr;
 	RBLayout& rb = s->rb;
 	rb.nx = s->nx; rb.ny = s->ny; rb.nz = s->nz;
@@ -289,18 +330,19 @@ int fs3i_alloc_pressure(fs3_sim* s) {
 	rb.hp = (rb.hx + 3) / 4 * 4;
 	rb.plane = (size_t)rb.hp * s->ny;
 	rb.total = rb.plane * (size_t)(s->nz + 2);
-	size_t es = prec ? 4 : 8;
+	size_t es = (prec && s->world == 1) ? 4 : 8;
+	int rc;
 	for (int c = 0; c < 2; c++) {
-		FS3_CUDA(cudaMalloc(&s->p[c], rb.total * es)); FS3_CUDA(cudaMalloc(&s->b[c], rb.total * es));
-		FS3_CUDA(cudaMalloc(&s->dg[c], rb.total * es)); FS3_CUDA(cudaMalloc((void**)&s->mask[c], rb.total));
+		if ((rc = fs3i_alloc(s, &s->p[c], rb.total * es)) || (rc = fs3i_alloc(s, &s->b[c], rb.total * es)) ||
+		    (rc = fs3i_alloc(s, &s->dg[c], rb.total * es)) || (rc = fs3i_alloc(s, (void**)&s->mask[c], rb.total))) return rc;
 		FS3_CUDA(cudaMemsetAsync(s->p[c], 0, rb.total * es, s->stream)); FS3_CUDA(cudaMemsetAsync(s->b[c], 0, rb.total * es, s->stream));
 		FS3_CUDA(cudaMemsetAsync(s->dg[c], 0, rb.total * es, s->stream)); FS3_CUDA(cudaMemsetAsync(s->mask[c], 0, rb.total, s->stream));
 	}
-	const size_t nvec = rb.total / (prec ? 4 : 2);
-	FS3_CUDA(cudaMalloc((void**)&s->sor_flags, (nvec + 1) * sizeof(uint32_t)));
+	const size_t nvec = rb.total / ((prec && s->world == 1) ? 4 : 2);
+	if ((rc = fs3i_alloc(s, (void**)&s->sor_flags, (nvec + 1) * sizeof(uint32_t)))) return rc;
 	for (int c = 0; c < 2; c++) {
-		FS3_CUDA(cudaMalloc((void**)&s->sor_list[c], nvec * sizeof(uint32_t)));
-		FS3_CUDA(cudaMalloc((void**)&s->sor_pos[c], (nvec + 1) * sizeof(uint32_t)));
+		if ((rc = fs3i_alloc(s, (void**)&s->sor_list[c], nvec * sizeof(uint32_t)))) return rc;
+		if ((rc = fs3i_alloc(s, (void**)&s->sor_pos[c], (nvec + 1) * sizeof(uint32_t)))) return rc;
 	}
 	if ((nvec + 1) / 4096 + 2 > s->scan_block_cap) { s->err = "scan scratch too small for the SOR lists"; return FS3_ERR_STATE; }
 	s->alloc_precision = prec;
@@ -311,68 +353,128 @@ int fs3i_alloc_pressure(fs3_sim* s) {
 
 static double fs3_omega(const fs3_sim* s) { return s->prm.omega > 0 ? s->prm.omega : 2 - 3.16343 / s->nx; }  // S3D.cpp:944
 
-template <typename REAL, int VEC> static int sor_loop_t(fs3_sim* s, int iters) {
+// active-vector lists of both colours (flags -> exclusive scan -> compaction) over this rank's slab; counts stay on the device
+template <typename REAL, int VEC> static int sor_prepare_t(fs3_sim* s) {
+	if (s->sor_list_valid) return FS3_OK;
+	const size_t nvec = s->rb.total / VEC;
+	const size_t v0 = s->rb.plane * (size_t)(s->z0 + 1) / VEC, v1 = s->rb.plane * (size_t)(s->z1 + 1) / VEC;
+	for (int c = 0; c < 2; c++) {
+		k_sor_flags<VEC><<<cdiv((long long)nvec + 1, 256), 256, 0, s->stream>>>(s->mask[c], nvec, s->sor_flags, v0, v1); FS3_LAUNCH_CHECK();
+		int rc = fs3i_scan_u32(s, s->sor_flags, s->sor_pos[c], nvec + 1);
+		if (rc) return rc;
+		k_sor_compact<VEC><<<cdiv((long long)nvec, 256), 256, 0, s->stream>>>(s->sor_flags, s->sor_pos[c], nvec, s->rb, c, s->sor_list[c]); FS3_LAUNCH_CHECK();
+		s->sor_count[c] = s->sor_pos[c] + nvec;
+	}
+	s->sor_list_valid = true;
+	return FS3_OK;
+}
+int fs3i_sor_prepare(fs3_sim* s) { return s->alloc_precision ? sor_prepare_t<float, 4>(s) : sor_prepare_t<double, 2>(s); }
+
+// half sweep k (colour k & 1) of the current projection
+template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	Sys<REAL> sy = make_sys<REAL>(s);
 	REAL omega = (REAL)fs3_omega(s);
 	if (sizeof(REAL) == 4) omega = (REAL)2 - (REAL)3.16343 / s->nx, omega = s->prm.omega > 0 ? (REAL)s->prm.omega : omega;
 	REAL omo = (REAL)1 - omega;
-	if (!s->sor_list_valid) {
-		// active-vector lists of both colours (flags -> exclusive scan -> compaction); count stays on the device
-		const size_t nvec = s->rb.total / VEC;
-		for (int c = 0; c < 2; c++) {
-			k_sor_flags<VEC><<<cdiv((long long)nvec + 1, 256), 256, 0, s->stream>>>(s->mask[c], nvec, s->sor_flags); FS3_LAUNCH_CHECK();
-			int rc = fs3i_scan_u32(s, s->sor_flags, s->sor_pos[c], nvec + 1);
-			if (rc) return rc;
-			k_sor_compact<VEC><<<cdiv((long long)nvec, 256), 256, 0, s->stream>>>(s->sor_flags, s->sor_pos[c], nvec, s->rb, c, s->sor_list[c]); FS3_LAUNCH_CHECK();
-			s->sor_count[c] = s->sor_pos[c] + nvec;
-		}
-		s->sor_list_valid = true;
-	}
 	// persistent grid-stride launch: enough blocks to fill the machine; the list length is read on the device
-	size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * s->nz;
-	int nb = (int)std::min<long long>(cdiv((long long)threads, 256), (long long)s->sm_count * 8);
+	size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * (s->z1 - s->z0);
+	int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, 256)), (long long)s->sm_count * 8);
+	const int c = k & 1;
+	if (s->world == 1) {
+		k_sor_half<REAL, VEC, false><<<nb, 256, 0, s->stream>>>(sy, c, omega, omo, s->sor_list[c], s->sor_count[c], SorShard{}); FS3_LAUNCH_CHECK();
+		return FS3_OK;
+	}
+	SorShard sh;
+	const bool lo = s->rank > 0, hi = s->rank < s->world - 1;
+	sh.peer_p[0] = lo ? fs3_peer(s, s->rank - 1, (char*)s->p[c]) : nullptr;
+	sh.peer_p[1] = hi ? fs3_peer(s, s->rank + 1, (char*)s->p[c]) : nullptr;
+	// my epoch goes to the lower neighbour's "from above" slot and to the upper neighbour's "from below" slot
+	sh.peer_flag[0] = lo ? fs3_peer(s, s->rank - 1, s->bar) + FS3_MAX_WORLD + 1 : nullptr;
+	sh.peer_flag[1] = hi ? fs3_peer(s, s->rank + 1, s->bar) + FS3_MAX_WORLD + 0 : nullptr;
+	sh.my_flag = s->bar + FS3_MAX_WORLD;
+	sh.wait_epoch = s->sor_e0 + (uint32_t)k;
+	sh.signal_epoch = s->sor_e0 + (uint32_t)k + 1u;
+	sh.lo_begin = s->rb.plane * (size_t)(s->z0 + 1); sh.lo_end = sh.lo_begin + s->rb.plane;
+	sh.hi_begin = s->rb.plane * (size_t)s->z1; sh.hi_end = sh.hi_begin + s->rb.plane;
+	sh.done = s->sor_done; sh.flags = s->dev_flags; sh.nospin = s->lockstep ? 1 : 0;
+	k_sor_half<REAL, VEC, true><<<nb, 256, 0, s->stream>>>(sy, c, omega, omo, s->sor_list[c], s->sor_count[c], sh); FS3_LAUNCH_CHECK();
+	s->sor_epoch = sh.signal_epoch;
+	return FS3_OK;
+}
+int fs3i_sor_half_launch(fs3_sim* s, int k) { return s->alloc_precision ? sor_half_t<float, 4>(s, k) : sor_half_t<double, 2>(s, k); }
+
+int fs3i_sor_loop(fs3_sim* s, int iters) {
+	int rc = fs3i_sor_prepare(s);
+	if (rc) return rc;
 	bool rec = s->prm.record_residuals != 0;
 	if (rec) {
+		if (s->world > 1) { s->err = "residual recording is not available on a sharded handle"; return FS3_ERR_STATE; }
 		if (iters > s->res_cap) { s->err = "residual buffer too small"; return FS3_ERR_STATE; }
 		FS3_CUDA(cudaMemsetAsync(s->res, 0, sizeof(double) * 2 * iters, s->stream));
 	}
 	for (int it = 0; it < iters; it++) {
-		k_sor_half<REAL, VEC><<<nb, 256, 0, s->stream>>>(sy, 0, omega, omo, s->sor_list[0], s->sor_count[0]); FS3_LAUNCH_CHECK();
-		k_sor_half<REAL, VEC><<<nb, 256, 0, s->stream>>>(sy, 1, omega, omo, s->sor_list[1], s->sor_count[1]); FS3_LAUNCH_CHECK();
-		if (rec) { k_sor_residual<REAL><<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(sy, s->res + 2 * it); FS3_LAUNCH_CHECK(); }
+		if ((rc = fs3i_sor_half_launch(s, 2 * it)) || (rc = fs3i_sor_half_launch(s, 2 * it + 1))) return rc;
+		if (rec) {
+			if (s->alloc_precision) k_sor_residual<float><<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(make_sys<float>(s), s->res + 2 * it);
+			else k_sor_residual<double><<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(make_sys<double>(s), s->res + 2 * it);
+			FS3_LAUNCH_CHECK();
+		}
 	}
 	s->res_count = rec ? iters : 0;
 	return FS3_OK;
 }
-int fs3i_sor_loop(fs3_sim* s, int iters) {
-	return s->alloc_precision ? sor_loop_t<float, 4>(s, iters) : sor_loop_t<double, 2>(s, iters);
-}
 
-template <typename REAL> static int project_t(fs3_sim* s, float dt, bool from_old, bool with_gravity) {
+template <typename REAL> static int project_setup_t(fs3_sim* s, float dt, bool from_old, bool with_gravity) {
 	Sys<REAL> sy = make_sys<REAL>(s);
 	const float *sU = from_old ? s->oU : s->U, *sV = from_old ? s->oV : s->V, *sW = from_old ? s->oW : s->W;
 	REAL dx = (REAL)1.0 / s->cpm;                       // S3D.cpp:834
 	REAL scale = -dx * s->prm.rho / dt;                 // S3D.cpp:835
 	float gdt = s->prm.gravity_y * dt;                  // S3D.cpp:784
-	int nb = cdiv((long long)s->nC, 256);
+	const size_t plane = (size_t)s->nx * s->ny, c0 = plane * s->z0, c1 = plane * s->z1;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_PROJECT_SETUP], s->stream);
-	k_project_setup<REAL><<<nb, 256, 0, s->stream>>>(sy, sU, sV, sW, s->phi, scale, gdt, with_gravity ? 1 : 0, (REAL)1000.0);
+	k_project_setup<REAL><<<cdiv((long long)(c1 - c0), 256), 256, 0, s->stream>>>(sy, sU, sV, sW, s->phi, scale, gdt, with_gravity ? 1 : 0, (REAL)1000.0, c0, c1);
 	FS3_LAUNCH_CHECK();
+	if (s->world > 1) {
+		// p = 0 also on the ghost planes the neighbours will store into (they do so only after this rank's "set up" signal)
+		for (int c = 0; c < 2; c++) {
+			FS3_CUDA(cudaMemsetAsync((REAL*)s->p[c] + s->rb.plane * (size_t)s->z0, 0, s->rb.plane * sizeof(REAL), s->stream));
+			FS3_CUDA(cudaMemsetAsync((REAL*)s->p[c] + s->rb.plane * (size_t)(s->z1 + 1), 0, s->rb.plane * sizeof(REAL), s->stream));
+		}
+	}
 	s->system_valid = true;
 	s->sor_list_valid = false;
-	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_PROJECT_SOR], s->stream);
-	int rc = fs3i_sor_loop(s, s->prm.sor_iterations);
+	return FS3_OK;
+}
+int fs3i_project_setup(fs3_sim* s, float dt, bool from_old, bool with_gravity) {
+	int rc = fs3i_alloc_pressure(s);
 	if (rc) return rc;
+	return s->alloc_precision ? project_setup_t<float>(s, dt, from_old, with_gravity) : project_setup_t<double>(s, dt, from_old, with_gravity);
+}
+
+template <typename REAL> static int project_gradient_t(fs3_sim* s, float dt, bool from_old, bool with_gravity) {
+	Sys<REAL> sy = make_sys<REAL>(s);
+	const float *sU = from_old ? s->oU : s->U, *sV = from_old ? s->oV : s->V, *sW = from_old ? s->oW : s->W;
+	REAL dx = (REAL)1.0 / s->cpm;
+	float gdt = s->prm.gravity_y * dt;
+	const size_t plane = (size_t)s->nx * s->ny, c0 = plane * s->z0, c1 = plane * s->z1;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_PROJECT_TOVEL], s->stream);
 	REAL gscale = dt / (s->prm.rho * dx);               // S3D.cpp:1015
-	k_project_gradient<REAL><<<nb, 256, 0, s->stream>>>(sy, sU, sV, sW, s->phi, s->U, s->V, s->W, gscale, gdt, with_gravity ? 1 : 0, (REAL)1000.0);
+	k_project_gradient<REAL><<<cdiv((long long)(c1 - c0), 256), 256, 0, s->stream>>>(sy, sU, sV, sW, s->phi, s->U, s->V, s->W, gscale, gdt,
+	                                                                                 with_gravity ? 1 : 0, (REAL)1000.0, c0, c1);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
+int fs3i_project_gradient(fs3_sim* s, float dt, bool from_old, bool with_gravity) {
+	return s->alloc_precision ? project_gradient_t<float>(s, dt, from_old, with_gravity) : project_gradient_t<double>(s, dt, from_old, with_gravity);
+}
+
+// the whole projection on one GPU
 int fs3i_project(fs3_sim* s, float dt, bool from_old, bool with_gravity) {
-	int rc = fs3i_alloc_pressure(s);
+	int rc = fs3i_project_setup(s, dt, from_old, with_gravity);
 	if (rc) return rc;
-	return s->alloc_precision ? project_t<float>(s, dt, from_old, with_gravity) : project_t<double>(s, dt, from_old, with_gravity);
+	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_PROJECT_SOR], s->stream);
+	if ((rc = fs3i_sor_loop(s, s->prm.sor_iterations))) return rc;
+	return fs3i_project_gradient(s, dt, from_old, with_gravity);
 }
 
 int fs3i_clear_pressure(fs3_sim* s) {

@@ -1,0 +1,304 @@
+// z-slab sharding of FluidSim3::Simulate over the GPUs of one box.
+//
+// One rank per GPU.  Every rank holds full-size grid arrays (global indexing) and owns the cells / face nodes with z in
+// [z0, z1) and the particles whose cell (int)roundf(n*Z) (S3D.cpp:288) lies there.  All device memory of a rank is one
+// arena exported through ONE CUDA-IPC handle, so rank a reaches array X of rank b at  peer_base[b] + (X - arena).
+// Data moves by stores / copies into the peers' arrays over NVLink (no staging, no library collective):
+//   * SOR: the sweep kernel itself stores its boundary planes into the neighbours' ghost planes and raises their epoch
+//     flag from its last block (project.cu, k_sor_half<.., SHARD>);
+//   * particle migration: emigrants are packed per destination and copied to the tail of the destination's live range;
+//   * ghost layers for the P2G gather: one cell layer of sorted particles + its cell_start rows is PULLED from each
+//     neighbour and spliced in directly below / above the own range, so the gather kernel is unchanged;
+//   * slab all-gathers (seed records, P2G result, projected field): each rank copies its slab into every peer.
+// Ordering is by epoch flags in device memory written with st.release.sys by the producer and polled by a one-warp
+// kernel (or the sweep kernel's first warp) of the consumer.  A step is a fixed sequence of PHASES, each "wait, work,
+// signal"; a multi-process handle runs them back to back on its stream, a lockstep group (all ranks in one process on one
+// stream, for single-GPU testing) runs phase k of every rank before phase k+1, which satisfies every wait by stream
+// order -- waits then never spin and a wait that is not already satisfied is reported as an error (flags[2]).
+// The two stages with a sequential dependence along z (the 8 Gauss-Seidel level-set sweeps and the layered
+// extrapolation) run REPLICATED on gathered inputs; everything else runs on the slab.
+#include "fs3_internal.cuh"
+#include <algorithm>
+
+static inline size_t up512(size_t b) { return (b + 511) / 512 * 512; }
+
+// Upper bound of everything fs3_create allocates for one rank (each allocation rounded up to 512 B).
+size_t fs3i_arena_bytes(int n, long long ptot, long long mig_cap, int world) {
+	const size_t N = (size_t)n, nC = N * N * N, nF = (N + 1) * N * N, nH = 8 * nC;
+	size_t t = 0;
+	t += 6 * up512(nF * 4) + up512(nC * 4);                                   // U V W oU oV oW phi
+	t += 2 * up512((nH + 1) * 4) + up512(nH * 4);                             // cell_count, cell_start, cell_fill
+	t += up512(((nH + 1) / 4096 + 2) * 4);                                    // scan_block
+	t += up512(nC * 16) + up512(nC * 4);                                      // ls_rec, closest
+	t += 6 * up512(nF * 4);                                                   // cdv, orderv
+	t += up512(3 * (3 * (3 * N + 8) + 2) * 4) + up512(16 * 2 * 4096) + 512;   // bucket, res, dev_flags
+	t += 4 * up512((size_t)ptot * 16) + 2 * up512((size_t)ptot * 4);          // pos, vel (x2), cellid, tmp_id
+	const size_t hp = ((N + 1) / 2 + 3) / 4 * 4, total = hp * N * (N + 2), nvec = total / 2;
+	t += 2 * (3 * up512(total * 8) + up512(total));                           // p, b, diag, mask per colour
+	t += up512((nvec + 1) * 4) + 2 * (up512(nvec * 4) + up512((nvec + 1) * 4)); // SOR lists
+	const size_t nt = ((N + 7) / 8) * ((N + 7) / 8) * ((N + 3) / 4);
+	t += up512(8 * nt * 4) + up512(nt * 4) + 512;                             // level-set item table, epochs, ticket
+	t += up512((size_t)world * world * 4) + up512((2 * (size_t)world + 1) * 4) + up512((size_t)mig_cap * 4) + 2 * up512((size_t)mig_cap * 16);
+	t += up512((FS3_MAX_WORLD + 2) * 4) + 512;                                // bar, sor_done
+	return t + (1u << 20);
+}
+
+int fs3i_alloc(fs3_sim* s, void** p, size_t bytes) {
+	if (!s->arena) {
+		FS3_CUDA(cudaMalloc(p, bytes ? bytes : 1));
+		return FS3_OK;
+	}
+	size_t b = up512(bytes ? bytes : 1);
+	if (s->arena_used + b > s->arena_bytes) { s->err = "device arena of the sharded handle is too small (fs3i_arena_bytes)"; return FS3_ERR_STATE; }
+	*p = s->arena + s->arena_used;
+	s->arena_used += b;
+	return FS3_OK;
+}
+void fs3i_free(fs3_sim* s, void* p) {
+	if (p && !s->arena) cudaFree(p);
+}
+
+int fs3i_shard_alloc(fs3_sim* s) {
+	int rc;
+	const int w = s->world;
+	if ((rc = fs3i_alloc(s, (void**)&s->mig_matrix, (size_t)w * w * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_ctl, (2 * (size_t)w + 1) * 4)) ||
+	    (rc = fs3i_alloc(s, (void**)&s->leaver_idx, (size_t)s->mig_cap * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_pos, (size_t)s->mig_cap * 16)) ||
+	    (rc = fs3i_alloc(s, (void**)&s->mig_vel, (size_t)s->mig_cap * 16)) || (rc = fs3i_alloc(s, (void**)&s->bar, (FS3_MAX_WORLD + 2) * 4)) ||
+	    (rc = fs3i_alloc(s, (void**)&s->sor_done, 4)))
+		return rc;
+	FS3_CUDA(cudaMallocHost((void**)&s->h_pin, (size_t)std::max(w * w, 64) * 4));
+	return FS3_OK;
+}
+
+// ---- barrier = signal (publish my epoch to every rank) + wait (every rank has published it) -----------------------
+struct PeerPtrs { uint32_t* p[FS3_MAX_WORLD]; };
+
+__global__ void k_bar_signal(PeerPtrs bars, int rank, int world, uint32_t epoch) {
+	const int r = threadIdx.x;
+	if (r < world && r != rank) { __threadfence_system(); fs3_st_release_sys(bars.p[r] + rank, epoch); }
+}
+__global__ void k_bar_wait(const uint32_t* bar, int rank, int world, uint32_t epoch, int* flags, int nospin) {
+	const int r = threadIdx.x;
+	if (r < world && r != rank) fs3_flag_wait(bar + r, epoch, flags, nospin);
+}
+int fs3i_signal(fs3_sim* s) {
+	PeerPtrs pp;
+	for (int r = 0; r < s->world; r++) pp.p[r] = fs3_peer(s, r, s->bar);
+	s->bar_epoch++;
+	k_bar_signal<<<1, 32, 0, s->stream>>>(pp, s->rank, s->world, s->bar_epoch); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+int fs3i_wait(fs3_sim* s) {
+	k_bar_wait<<<1, 32, 0, s->stream>>>(s->bar, s->rank, s->world, s->bar_epoch, s->dev_flags, s->lockstep ? 1 : 0); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes) {
+	if (!bytes) return FS3_OK;
+	for (int k = 1; k < s->world; k++) {
+		const int r = (s->rank + k) % s->world;   // staggered so that the ranks do not all target the same peer at once
+		FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, r, (char*)ptr) + byte_off, (char*)ptr + byte_off, bytes, cudaMemcpyDefault, s->stream));
+	}
+	return FS3_OK;
+}
+
+// ---- SOR neighbour epochs: slot FS3_MAX_WORLD+0 is written by the lower, +1 by the upper neighbour ----------------
+__global__ void k_sor_signal(uint32_t* lo_flag, uint32_t* hi_flag, uint32_t epoch) {
+	__threadfence_system();
+	if (threadIdx.x == 0 && lo_flag) fs3_st_release_sys(lo_flag, epoch);
+	if (threadIdx.x == 1 && hi_flag) fs3_st_release_sys(hi_flag, epoch);
+}
+__global__ void k_sor_wait(const uint32_t* my_flag, int has_lo, int has_hi, uint32_t epoch, int* flags, int nospin) {
+	if (threadIdx.x == 0 && has_lo) fs3_flag_wait(my_flag + 0, epoch, flags, nospin);
+	if (threadIdx.x == 1 && has_hi) fs3_flag_wait(my_flag + 1, epoch, flags, nospin);
+}
+int fs3i_sor_signal(fs3_sim* s) {
+	s->sor_epoch++;
+	s->sor_e0 = s->sor_epoch;
+	uint32_t* lo = s->rank > 0 ? fs3_peer(s, s->rank - 1, s->bar) + FS3_MAX_WORLD + 1 : nullptr;
+	uint32_t* hi = s->rank < s->world - 1 ? fs3_peer(s, s->rank + 1, s->bar) + FS3_MAX_WORLD + 0 : nullptr;
+	k_sor_signal<<<1, 32, 0, s->stream>>>(lo, hi, s->sor_e0); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+int fs3i_sor_wait(fs3_sim* s, uint32_t epoch) {
+	k_sor_wait<<<1, 32, 0, s->stream>>>(s->bar + FS3_MAX_WORLD, s->rank > 0, s->rank < s->world - 1, epoch, s->dev_flags, s->lockstep ? 1 : 0);
+	FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+// ---- particle migration ----------------------------------------------------------------------------------------------
+// row `rank` of the count matrix goes into every rank's copy
+__global__ void k_mig_publish(PeerPtrs mats, const uint32_t* __restrict__ ctl, int rank, int world) {
+	const int d = threadIdx.x;
+	if (d >= world) return;
+	for (int j = 0; j < world; j++) mats.p[d][rank * world + j] = ctl[j];
+}
+int fs3i_mig_publish(fs3_sim* s) {
+	PeerPtrs pp;
+	for (int r = 0; r < s->world; r++) pp.p[r] = fs3_peer(s, r, s->mig_matrix);
+	k_mig_publish<<<1, 32, 0, s->stream>>>(pp, s->mig_ctl, s->rank, s->world); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+// After the barrier every rank holds the whole count matrix: bring it to the host (the one host round trip of the
+// migration), append my emigrants to the tail of each destination's live range, and advance the replicated bookkeeping.
+int fs3i_mig_exchange(fs3_sim* s) {
+	const int w = s->world, me = s->rank;
+	FS3_CUDA(cudaMemcpyAsync(s->h_pin, s->mig_matrix, (size_t)w * w * 4, cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	int rc = fs3i_check_flags(s);
+	if (rc) return rc;
+	const uint32_t* m = s->h_pin;
+	long long out_me = 0;
+	for (int d = 0; d < w; d++) out_me += m[me * w + d];
+	if (out_me > s->mig_cap) { s->err = "more emigrants in one step than the migration buffer holds"; return FS3_ERR_STATE; }
+	long long base = 0;
+	for (int d = 0; d < w; d++) {
+		const long long cnt = m[me * w + d];
+		if (d != me && cnt > 0) {
+			long long off = s->np_all[d];   // the destination's live range is hole-free up to its pre-migration length
+			for (int r = 0; r < me; r++) off += m[r * w + d];
+			FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, d, s->pos[s->cur]) + s->poff + off, s->mig_pos + base, (size_t)cnt * sizeof(float4), cudaMemcpyDefault, s->stream));
+			FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, d, s->vel[s->cur]) + s->poff + off, s->mig_vel + base, (size_t)cnt * sizeof(float4), cudaMemcpyDefault, s->stream));
+		}
+		base += cnt;
+	}
+	long long in_len = 0;
+	for (int d = 0; d < w; d++) {
+		long long arrive = 0, leave = 0;
+		for (int r = 0; r < w; r++) { arrive += m[r * w + d]; leave += m[d * w + r]; }
+		if (s->np_all[d] + arrive > s->cap) { s->err = "particle capacity of a slab exceeded by migration"; return FS3_ERR_STATE; }
+		if (d == me) in_len = s->np_all[d] + arrive;
+		s->np_all[d] += arrive - leave;
+	}
+	s->np_in = in_len;
+	s->np = s->np_all[me];
+	s->sorted = false;
+	return FS3_OK;
+}
+
+// ---- ghost layers: one cell layer (two half-cell layers) of each neighbour's sorted particles ---------------------
+// Keys [ka, kb) of the neighbour's cell_start describe the layer.  Its particles are copied to just below (hi == 0) or just
+// above (hi == 1) my own sorted range and my cell_start rows for those keys are rebased, so that cell_start stays one
+// monotone array over [ka_lo, kb_hi] and every gather kernel works unchanged on slab + ghosts.
+__global__ void __launch_bounds__(256) k_ghost_pull(const uint32_t* __restrict__ nstart, const float4* __restrict__ npos, const float4* __restrict__ nvel,
+                                                    uint32_t* __restrict__ mystart, float4* __restrict__ mypos, float4* __restrict__ myvel, size_t ka,
+                                                    size_t kb, int hi, uint32_t poff, uint32_t np, uint32_t gcap, int* __restrict__ flags) {
+	const uint32_t nb = nstart[ka], ne = nstart[kb], cnt = ne - nb;
+	if (cnt > gcap) { if (blockIdx.x == 0 && threadIdx.x == 0) flags[3] = 1; return; }
+	const uint32_t dst0 = hi ? poff + np : poff - cnt;
+	const size_t nk = kb - ka + (hi ? 1 : 0);
+	const size_t stride = (size_t)gridDim.x * blockDim.x, t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	for (size_t k = t0; k < nk; k += stride) mystart[ka + k] = dst0 + (nstart[ka + k] - nb);
+	for (size_t t = t0; t < cnt; t += stride) { mypos[dst0 + t] = npos[nb + t]; myvel[dst0 + t] = nvel[nb + t]; }
+}
+int fs3i_ghost_pull(fs3_sim* s) {
+	const size_t hplane = (size_t)(2 * s->nx) * (2 * s->ny);
+	const int nb = s->sm_count * 4;
+	for (int hi = 0; hi < 2; hi++) {
+		const int r = hi ? s->rank + 1 : s->rank - 1;
+		if (r < 0 || r >= s->world) continue;
+		const size_t ka = hi ? hplane * (size_t)(2 * s->z1) : hplane * (size_t)(2 * s->z0 - 2), kb = ka + 2 * hplane;
+		k_ghost_pull<<<nb, 256, 0, s->stream>>>(fs3_peer(s, r, s->cell_start), fs3_peer(s, r, s->pos[s->cur]), fs3_peer(s, r, s->vel[s->cur]), s->cell_start,
+		                                         s->pos[s->cur], s->vel[s->cur], ka, kb, hi, (uint32_t)s->poff, (uint32_t)s->np, (uint32_t)s->gcap, s->dev_flags);
+		FS3_LAUNCH_CHECK();
+	}
+	return FS3_OK;
+}
+
+// ---- the step as phases ------------------------------------------------------------------------------------------------
+int fs3i_num_step_phases(const fs3_sim* s) { return 8 + 2 * s->prm.sor_iterations; }
+
+static float flip_alpha(const fs3_sim* s, float dt) {
+	float a = 6 * dt * s->prm.nu * s->cpm * s->cpm;   // S3D.cpp:114
+	return a < 0.0f ? 0.0f : (a > 1.0f ? 1.0f : a);
+}
+
+// slab of a z-slowest array: element range [plane*za, plane*zb)
+static int push_planes(fs3_sim* s, void* arr, size_t plane_elems, size_t elem_bytes, int za, int zb) {
+	return fs3i_push(s, arr, plane_elems * elem_bytes * (size_t)za, plane_elems * elem_bytes * (size_t)(zb - za));
+}
+
+int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
+	const bool T = s->prm.record_stage_times != 0;
+	const int I = s->prm.sor_iterations;
+	const size_t pU = (size_t)(s->nx + 1) * s->ny, pV = (size_t)s->nx * (s->ny + 1), pW = (size_t)s->nx * s->ny, pC = pW;
+	const bool last = s->rank == s->world - 1;
+	int rc;
+	if (ph == 0) {          // Advect (S3D.cpp:190-232); emigrants -> outgoing buffers; publish the count row
+		if (T) cudaEventRecord(s->ev[FS3_T_ADVECT], s->stream);
+		if ((rc = fs3i_advect(s, dt)) || (rc = fs3i_mig_pack(s)) || (rc = fs3i_mig_publish(s))) return rc;
+		return fs3i_signal(s);
+	}
+	if (ph == 1) {          // counts of all ranks are here: send the emigrants
+		if ((rc = fs3i_wait(s)) || (rc = fs3i_mig_exchange(s))) return rc;
+		return fs3i_signal(s);
+	}
+	if (ph == 2) {          // immigrants have landed: counting sort of the slab's particles
+		if ((rc = fs3i_wait(s))) return rc;
+		if (T) cudaEventRecord(s->ev[FS3_T_BIN], s->stream);
+		if ((rc = fs3i_bin(s))) return rc;
+		return fs3i_signal(s);
+	}
+	if (ph == 3) {          // neighbours are sorted: ghost layers; level-set seed of the slab, gathered on every rank
+		if ((rc = fs3i_wait(s)) || (rc = fs3i_ghost_pull(s)) || (rc = fs3i_levelset_seed(s))) return rc;
+		if ((rc = push_planes(s, s->ls_rec, pC, sizeof(float4), s->z0, s->z1))) return rc;
+		return fs3i_signal(s);
+	}
+	if (ph == 4) {          // 8 sweeps (replicated); P2G of the slab's face nodes, gathered on every rank
+		if ((rc = fs3i_wait(s)) || (rc = fs3i_levelset_sweeps(s)) || (rc = fs3i_p2g_gather(s))) return rc;
+		const int zw = s->z1 + (last ? 1 : 0);
+		if ((rc = push_planes(s, s->oU, pU, 4, s->z0, s->z1)) || (rc = push_planes(s, s->oV, pV, 4, s->z0, s->z1)) ||
+		    (rc = push_planes(s, s->oW, pW, 4, s->z0, zw)) || (rc = push_planes(s, s->cdv[0], pU, 4, s->z0, s->z1)) ||
+		    (rc = push_planes(s, s->cdv[1], pV, 4, s->z0, s->z1)) || (rc = push_planes(s, s->cdv[2], pW, 4, s->z0, zw)))
+			return rc;
+		return fs3i_signal(s);
+	}
+	if (ph == 5) {          // extrapolation (replicated); pressure system of the slab; tell the neighbours it is set up
+		if ((rc = fs3i_wait(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_project_setup(s, dt, true, true)) || (rc = fs3i_sor_prepare(s))) return rc;
+		if ((rc = fs3i_sor_signal(s))) return rc;
+		if (T) cudaEventRecord(s->ev[FS3_T_PROJECT_SOR], s->stream);
+		return FS3_OK;
+	}
+	if (ph < 6 + 2 * I) return fs3i_sor_half_launch(s, ph - 6);   // compute + halo exchange in one kernel
+	if (ph == 6 + 2 * I) {  // pressure gradient on the slab; the projected field is gathered on every rank
+		if ((rc = fs3i_sor_wait(s, s->sor_e0 + 2u * (uint32_t)I)) || (rc = fs3i_project_gradient(s, dt, true, true))) return rc;
+		// the gradient kernel of cell plane z writes the W faces z+1 (and z = 0 on rank 0): that is the range it owns here
+		if ((rc = push_planes(s, s->U, pU, 4, s->z0, s->z1)) || (rc = push_planes(s, s->V, pV, 4, s->z0, s->z1)) ||
+		    (rc = push_planes(s, s->W, pW, 4, s->rank == 0 ? 0 : s->z0 + 1, s->z1 + 1)))
+			return rc;
+		return fs3i_signal(s);
+	}
+	if (ph == 7 + 2 * I) {  // PIC/FLIP blend (S3D.cpp:148-180)
+		if ((rc = fs3i_wait(s))) return rc;
+		if (T) cudaEventRecord(s->ev[FS3_T_FLIP_APPLY], s->stream);
+		const float alpha = flip_alpha(s, dt);
+		if ((rc = fs3i_flip_combine(s, alpha)) || (rc = fs3i_g2p(s, alpha))) return rc;
+		if (T) cudaEventRecord(s->ev[FS3_T_TOTAL], s->stream);
+		return FS3_OK;
+	}
+	s->err = "no such step phase";
+	return FS3_ERR_INVALID;
+}
+
+// ResetSimulation (S3D.cpp:41-99) as phases: generate the slab's particles, migrate the ones whose jitter rounded them
+// into a neighbouring slab, sort.
+int fs3i_reset_phase(fs3_sim* s, int ph) {
+	int rc;
+	if (ph == 0) {
+		if ((rc = fs3i_reset_grids(s)) || (rc = fs3i_reset_particles_slab(s)) || (rc = fs3i_mig_mark(s)) || (rc = fs3i_mig_pack(s)) ||
+		    (rc = fs3i_mig_publish(s)))
+			return rc;
+		return fs3i_signal(s);
+	}
+	if (ph == 1) {
+		if ((rc = fs3i_wait(s)) || (rc = fs3i_mig_exchange(s))) return rc;
+		return fs3i_signal(s);
+	}
+	if (ph == 2) {
+		if ((rc = fs3i_wait(s))) return rc;
+		return fs3i_bin(s);
+	}
+	s->err = "no such reset phase";
+	return FS3_ERR_INVALID;
+}

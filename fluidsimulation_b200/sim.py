@@ -25,7 +25,10 @@ ABI_SYMBOLS = [
     "fs3_stage_bodyforces", "fs3_stage_project", "fs3_stage_g2p", "fs3_extrapolate", "fs3_get_cell_indices",
     "fs3_get_cell_counts", "fs3_get_closest", "fs3_get_pressure", "fs3_get_rhs_diag", "fs3_get_sor_residuals",
     "fs3_stage_times", "fs3_sor_bench", "fs3_set_phi_all_fluid", "fs3_stream", "fs3_kernel_launches",
+    "fs3_create_sharded", "fs3_shard_get_handle", "fs3_shard_connect", "fs3_shard_plan", "fs3_shard_info",
+    "fs3_num_local_particles", "fs3_group_create", "fs3_group_reset", "fs3_group_step",
 ]
+SHARD_HANDLE_BYTES = 128
 
 
 class Fs3Params(C.Structure):
@@ -57,6 +60,8 @@ def load_library():
         _lib.fs3_kernel_launches.argtypes = [C.c_void_p]
         _lib.fs3_stream.restype = C.c_void_p
         _lib.fs3_stream.argtypes = [C.c_void_p]
+        _lib.fs3_num_local_particles.restype = C.c_longlong
+        _lib.fs3_num_local_particles.argtypes = [C.c_void_p]
     return _lib
 
 
@@ -64,19 +69,71 @@ def _ptr(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None else None
 
 
+def shard_plan(nz, world, rank):
+    """[z0, z1) of rank's slab (include/fs3.h fs3_shard_plan; pure host arithmetic, no GPU needed)."""
+    lib = load_library()
+    z0, z1 = C.c_int(0), C.c_int(0)
+    rc = lib.fs3_shard_plan(C.c_int(nz), C.c_int(world), C.c_int(rank), C.byref(z0), C.byref(z1))
+    if rc != FS3_OK:
+        raise Fs3Error("z-slab sharding needs 1 <= world <= 16, nz divisible by world and slabs of at least 2 planes")
+    return z0.value, z1.value
+
+
+def merge_particles(parts):
+    """Merges the per-rank results of get_particles() of a sharded simulation (records of other ranks are NaN)."""
+    out = np.array(parts[0], copy=True)
+    for p in parts[1:]:
+        m = ~np.isnan(p[:, 0])
+        out[m] = p[m]
+    return out
+
+
+def torch_allgather(group=None):
+    """`allgather` callable for FluidSim3(world > 1) over torch.distributed (any backend)."""
+    import torch.distributed as dist
+
+    def f(blob):
+        out = [None] * dist.get_world_size(group)
+        dist.all_gather_object(out, blob, group=group)
+        return out
+    return f
+
+
 class FluidSim3:
     """Drop-in for the reference class; grid/particle arrays cross the boundary as numpy arrays."""
 
-    def __init__(self, xSize, ySize, zSize, CellsPerMeter, device=0):
+    def __init__(self, xSize, ySize, zSize, CellsPerMeter, device=0, rank=0, world=1, allgather=None, _handle=None):
+        """world > 1: this process is rank `rank` of a z-slab sharded simulation (one process per GPU).  `allgather` is a
+        callable taking this rank's handle blob (bytes) and returning the blobs of all ranks in rank order, e.g.
+        ``lambda b: torch_allgather_bytes(b)``; construction, Simulate and ResetSimulation are then collective."""
         self._lib = load_library()
         self._h = C.c_void_p()
-        rc = self._lib.fs3_create(C.c_int(xSize), C.c_int(ySize), C.c_int(zSize), C.c_float(CellsPerMeter),
-                                  C.c_int(device), C.byref(self._h))
-        if rc != FS3_OK:
-            raise Fs3Error("fs3_create failed (%d): %s" % (rc, self._lib.fs3_last_error(None).decode()))
+        self.rank, self.world = rank, world
+        self._owned = _handle is None
+        if _handle is not None:
+            self._h = _handle
+        elif world == 1:
+            rc = self._lib.fs3_create(C.c_int(xSize), C.c_int(ySize), C.c_int(zSize), C.c_float(CellsPerMeter),
+                                      C.c_int(device), C.byref(self._h))
+            if rc != FS3_OK:
+                raise Fs3Error("fs3_create failed (%d): %s" % (rc, self._lib.fs3_last_error(None).decode()))
+        else:
+            if allgather is None:
+                raise Fs3Error("a sharded FluidSim3 needs an `allgather` callable to exchange the ranks' handle blobs")
+            rc = self._lib.fs3_create_sharded(C.c_int(xSize), C.c_int(ySize), C.c_int(zSize), C.c_float(CellsPerMeter),
+                                              C.c_int(device), C.c_int(rank), C.c_int(world), C.byref(self._h))
+            if rc != FS3_OK:
+                raise Fs3Error("fs3_create_sharded failed (%d): %s" % (rc, self._lib.fs3_last_error(None).decode()))
+            blob = C.create_string_buffer(SHARD_HANDLE_BYTES)
+            self._ck(self._lib.fs3_shard_get_handle(self._h, blob))
+            blobs = allgather(blob.raw)
+            if len(blobs) != world or any(len(b) != SHARD_HANDLE_BYTES for b in blobs):
+                raise Fs3Error("allgather must return one %d-byte blob per rank" % SHARD_HANDLE_BYTES)
+            self._ck(self._lib.fs3_shard_connect(self._h, b"".join(blobs)))
         self.mX, self.mY, self.mZ = xSize, ySize, zSize
         n = xSize
         self.nU, self.nV, self.nW, self.nC = (n + 1) * n * n, n * (n + 1) * n, n * n * (n + 1), n ** 3
+        self.z0, self.z1 = shard_plan(zSize, world, rank)
 
     # -- plumbing ------------------------------------------------------------------------------
     def _ck(self, rc):
@@ -85,7 +142,8 @@ class FluidSim3:
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:
-            self._lib.fs3_destroy(self._h)
+            if self._owned:
+                self._lib.fs3_destroy(self._h)
             self._h = None
 
     def __del__(self):
@@ -113,6 +171,10 @@ class FluidSim3:
     @property
     def num_particles(self):
         return int(self._lib.fs3_num_particles(self._h))
+
+    @property
+    def num_local_particles(self):
+        return int(self._lib.fs3_num_local_particles(self._h))
 
     @property
     def kernel_launches(self):
@@ -234,3 +296,88 @@ class FluidSim3:
 
     def set_phi_all_fluid(self):
         self._ck(self._lib.fs3_set_phi_all_fluid(self._h))
+
+
+class FluidSim3Group:
+    """All ranks of a z-slab sharded simulation inside this process on ONE device, stepped in lockstep (fs3_group_*):
+    the sharded code path without needing several GPUs.  `ranks[r]` is a FluidSim3 view of rank r."""
+
+    def __init__(self, n, world, device=0):
+        self._lib = load_library()
+        self.world, self.n = world, n
+        self._arr = (C.c_void_p * world)()
+        rc = self._lib.fs3_group_create(C.c_int(n), C.c_int(n), C.c_int(n), C.c_float(float(n)), C.c_int(device), C.c_int(world), self._arr)
+        if rc != FS3_OK:
+            raise Fs3Error("fs3_group_create failed (%d): %s" % (rc, self._lib.fs3_last_error(None).decode()))
+        self.ranks = [FluidSim3(n, n, n, float(n), device, r, world, _handle=C.c_void_p(self._arr[r])) for r in range(world)]
+
+    def _ck(self, rc):
+        if rc != FS3_OK:
+            msgs = [self._lib.fs3_last_error(C.c_void_p(self._arr[r])).decode() for r in range(self.world)]
+            raise Fs3Error("fs3 group error %d: %s" % (rc, " | ".join(m for m in msgs if m)))
+
+    def Simulate(self, dt):
+        self._ck(self._lib.fs3_group_step(self._arr, C.c_int(self.world), C.c_float(dt)))
+
+    def ResetSimulation(self):
+        self._ck(self._lib.fs3_group_reset(self._arr, C.c_int(self.world)))
+
+    def sync(self):
+        for r in self.ranks:
+            r.sync()
+
+    def set_params(self, **kw):
+        for r in self.ranks:
+            r.set_params(**kw)
+
+    def set_particles(self, p):
+        for r in self.ranks:
+            r.set_particles(p)
+
+    def set_velocity(self, u, v, w):
+        for r in self.ranks:
+            r.set_velocity(u, v, w)
+
+    def set_phi(self, phi):
+        for r in self.ranks:
+            r.set_phi(phi)
+
+    def get_particles(self):
+        return merge_particles([r.get_particles() for r in self.ranks])
+
+    def get_cell_indices(self):
+        out = self.ranks[0].get_cell_indices()
+        for r in self.ranks[1:]:
+            c = r.get_cell_indices()
+            out = np.where(c >= 0, c, out)
+        return out
+
+    def get_pressure(self):
+        """Natural-order p stitched from the slabs (each rank holds its own planes)."""
+        n = self.n
+        out = np.empty(n ** 3, np.float64)
+        for r in self.ranks:
+            out.reshape(n, n * n)[r.z0:r.z1] = r.get_pressure().reshape(n, n * n)[r.z0:r.z1]
+        return out
+
+    @property
+    def num_particles(self):
+        return self.ranks[0].num_particles
+
+    @property
+    def kernel_launches(self):
+        return sum(r.kernel_launches for r in self.ranks)
+
+    def close(self):
+        for r in reversed(self.ranks):
+            r._h = None
+        for k in reversed(range(self.world)):
+            if self._arr[k]:
+                self._lib.fs3_destroy(C.c_void_p(self._arr[k]))
+                self._arr[k] = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -74,6 +74,32 @@ int fs3_step(fs3_sim* s, float dt);
 int fs3_sync(fs3_sim* s);
 const char* fs3_last_error(const fs3_sim* s); /* s may be NULL: error of the last failed fs3_create */
 
+/* ---- z-slab sharding over the GPUs of one box (north_star: "large grids are split into z-slabs") --------------
+ * One rank per GPU, one process per rank.  Rank r owns the cell planes z in [r*nz/world, (r+1)*nz/world), the face nodes
+ * on them and the particles whose cell lies there.  The reference has no counterpart (single-threaded CPU class); the
+ * surface stays FluidSim3's: every rank constructs, steps and reads back with the same calls, which become COLLECTIVE
+ * (every rank must make them in the same order).  Ranks talk through CUDA-IPC peer memory over NVLink; the caller only
+ * has to carry FS3_SHARD_HANDLE_BYTES per rank between the processes once (MPI_Allgather, torch.distributed, a file):
+ *     fs3_create_sharded(...); fs3_shard_get_handle(h, mine); <all-gather the blobs in rank order>; fs3_shard_connect(h, all);
+ * fs3_shard_connect ends with the collective ResetSimulation, as the reference constructor does (Simulation3D.cpp:30).
+ * Afterwards fs3_step / fs3_reset / fs3_set_particles (same full array on every rank) / fs3_set_velocity / fs3_set_phi work
+ * as before; fs3_get_velocity and fs3_get_phi return the whole grids on every rank; fs3_get_particles fills the records
+ * of the particles this rank owns and leaves NaN (all bits set) in the others, so the ranks' arrays merge trivially.
+ * Every rank needs its own GPU (ranks wait on each other inside kernels); fs3_shard_connect refuses a shared one. */
+#define FS3_SHARD_HANDLE_BYTES 128
+int fs3_create_sharded(int nx, int ny, int nz, float cells_per_meter, int device, int rank, int world, fs3_sim** out);
+int fs3_shard_get_handle(fs3_sim* s, void* blob);
+int fs3_shard_connect(fs3_sim* s, const void* blobs_in_rank_order);
+int fs3_shard_plan(int nz, int world, int rank, int* z0, int* z1);   /* pure host arithmetic: the slab of a rank */
+int fs3_shard_info(const fs3_sim* s, int* rank, int* world, int* z0, int* z1);
+long long fs3_num_local_particles(const fs3_sim* s);                   /* particles this rank owns right now */
+/* All ranks inside ONE process on ONE device, sharing a stream and stepped phase by phase ("lockstep"): the same slab
+ * kernels, halo stores, migration and ghost-layer code as the multi-process path, but every cross-rank wait is already
+ * satisfied by stream order, so it runs (and is parity-tested) on a single GPU.  out/handles = array of `world` handles. */
+int fs3_group_create(int nx, int ny, int nz, float cells_per_meter, int device, int world, fs3_sim** out);
+int fs3_group_reset(fs3_sim** handles, int world);
+int fs3_group_step(fs3_sim** handles, int world, float dt);
+
 /* ---- state access (reference: public m_particles; private m_MU/m_MV/m_MW/m_Phi) ------------ */
 long long fs3_num_particles(const fs3_sim* s);                      /* m_particles.size() */
 int fs3_get_particles(fs3_sim* s, fs3_particle* host);              /* m_particles, creation order */

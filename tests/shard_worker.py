@@ -1,0 +1,65 @@
+"""Worker of the multi-process sharded tests: `torchrun --nproc-per-node N tests/shard_worker.py --n 24 --steps 3`.
+Every rank builds its slab of the simulation on its own GPU, steps it, and rank 0 compares the merged result bit for
+bit with a single-GPU run of the same library on its device."""
+import argparse
+import os
+import sys
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from fluidsimulation_b200 import FluidSim3, merge_particles, torch_allgather
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n", type=int, default=24)
+    ap.add_argument("--steps", type=int, default=3)
+    a = ap.parse_args()
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
+    dist.init_process_group(backend="gloo")
+    n = a.n
+    sim = FluidSim3(n, n, n, float(n), device=local, rank=rank, world=world, allgather=torch_allgather())
+    for _ in range(a.steps):
+        sim.Simulate(0.01)
+    sim.sync()
+    mine = sim.get_particles()
+    parts = [None] * world
+    dist.all_gather_object(parts, mine)
+    press = [None] * world
+    dist.all_gather_object(press, sim.get_pressure().reshape(n, n * n)[sim.z0:sim.z1])
+    uvw = sim.get_velocity()
+    ok = True
+    if rank == 0:
+        one = FluidSim3(n, n, n, float(n), device=local)
+        for _ in range(a.steps):
+            one.Simulate(0.01)
+        one.sync()
+        merged = merge_particles(parts)
+        same = lambda x, y: np.array_equal(np.ascontiguousarray(x).view(np.uint32), np.ascontiguousarray(y).view(np.uint32))
+        ok = same(merged, one.get_particles())
+        ok = ok and np.array_equal(np.concatenate(press).reshape(-1), one.get_pressure())
+        ok = ok and all(same(x, y) for x, y in zip(uvw, one.get_velocity())) and same(sim.get_phi(), one.get_phi())
+        print("rank 0: merged result %s the single-GPU run (%d particles, %d steps, world %d)" % ("matches" if ok else "DIFFERS FROM", merged.shape[0], a.steps, world))
+    flag = [ok]
+    dist.broadcast_object_list(flag, src=0)
+    # every rank holds the complete grids
+    ref = [None]
+    if rank == 0:
+        ref = [[x.tobytes() for x in uvw]]
+    dist.broadcast_object_list(ref, src=0)
+    grids_equal = all(x.tobytes() == y for x, y in zip(uvw, ref[0]))
+    allok = [None] * world
+    dist.all_gather_object(allok, grids_equal)
+    sim.close()
+    dist.barrier()
+    if rank == 0 and flag[0] and all(allok):
+        print("SHARD_WORKER_OK")
+    dist.destroy_process_group()
+    sys.exit(0 if (flag[0] and all(allok)) else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,149 @@
+"""z-slab sharded step against the single-GPU path and the CPU oracle -- needs a B200 (`-m gpu`).
+
+The lockstep group runs every rank of the sharded simulation inside one process on ONE device (include/fs3.h
+fs3_group_*): the same slab kernels, SOR halo stores, particle migration and ghost-layer splicing as the multi-process
+path, with the cross-rank waits satisfied by stream order.  Every stage of the sharded step does the same arithmetic in
+the same order as the single-GPU step (the P2G gather walks the same sorted runs), so the bar is BIT-EXACT against the
+single-GPU result, which test_gpu_parity.py holds against the oracle.
+"""
+import os
+import subprocess
+import sys
+import numpy as np
+import pytest
+
+from oracle_lib import Oracle
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def same(a, b):
+    return np.array_equal(bits(a), bits(b))
+
+
+def mk(n):
+    from fluidsimulation_b200 import FluidSim3
+    return FluidSim3(n, n, n, float(n))
+
+
+def mkg(n, world):
+    from fluidsimulation_b200 import FluidSim3Group
+    return FluidSim3Group(n, world)
+
+
+@pytest.mark.parametrize("n,world", [(16, 2), (16, 4), (24, 3), (32, 8)])
+def test_group_reset_bitexact(n, world):
+    g, one = mkg(n, world), mk(n)
+    assert g.num_particles == one.num_particles
+    assert sum(r.num_local_particles for r in g.ranks) == one.num_particles
+    assert same(g.get_particles(), one.get_particles())
+    for r in g.ranks:
+        for a, b in zip(r.get_velocity(), one.get_velocity()):
+            assert same(a, b)
+    # ownership: every particle sits on the rank whose slab holds its cell
+    cells = one.get_cell_indices()
+    for r in g.ranks:
+        mine = ~np.isnan(r.get_particles()[:, 0])
+        z = cells[mine] // (n * n)
+        assert mine.sum() == r.num_local_particles and (z >= r.z0).all() and (z < r.z1).all()
+    g.close()
+
+
+@pytest.mark.parametrize("n,world,steps", [(16, 2, 3), (16, 4, 2), (24, 2, 4), (24, 3, 2), (32, 4, 6)])
+def test_group_steps_bitexact_vs_single_gpu(n, world, steps):
+    g, one = mkg(n, world), mk(n)
+    for k in range(steps):
+        g.Simulate(0.01); one.Simulate(0.01)
+        g.sync(); one.sync()
+        assert same(g.get_particles(), one.get_particles()), "particles differ after step %d" % (k + 1)
+        assert np.array_equal(g.get_cell_indices(), one.get_cell_indices())
+        assert np.array_equal(g.get_pressure(), one.get_pressure()), "pressure differs after step %d" % (k + 1)
+        for r in g.ranks:      # the grids are complete on every rank after a step
+            for name, a, b in zip("UVW", r.get_velocity(), one.get_velocity()):
+                assert same(a, b), "%s differs on rank %d after step %d" % (name, r.rank, k + 1)
+            assert same(r.get_phi(), one.get_phi())
+            assert np.array_equal(r.get_closest(), one.get_closest())
+    assert sum(r.num_local_particles for r in g.ranks) == one.num_particles
+    g.close()
+
+
+def test_group_fp32_solve_bitexact_vs_single_gpu():
+    n = 16
+    g, one = mkg(n, 2), mk(n)
+    g.set_params(precision=1); one.set_params(precision=1)
+    for _ in range(2):
+        g.Simulate(0.01); one.Simulate(0.01)
+    g.sync(); one.sync()
+    assert same(g.get_particles(), one.get_particles())
+    g.close()
+
+
+def test_group_against_oracle_and_teacher_forcing():
+    """Sharded step from the oracle's state (set_particles / set_velocity / set_phi are per-rank uploads of the full arrays)."""
+    n = 16
+    g, ora = mkg(n, 2), Oracle(n)
+    for step in range(4):
+        g.set_particles(ora.get_particles()); g.set_velocity(*ora.get_velocity()); g.set_phi(ora.get_phi())
+        g.Simulate(0.01); ora.step(0.01)
+        g.sync()
+        p, q = g.get_particles(), ora.get_particles()
+        assert np.array_equal(g.get_cell_indices(), ora.get_cell_indices()), step
+        assert float(np.abs(p - q).max()) <= 1e-5 * max(1.0, float(np.abs(q).max()))
+        assert same(g.ranks[1].get_phi(), ora.get_phi())
+    g.close()
+
+
+def test_group_migration_moves_particles_between_slabs():
+    """A dam break sloshes mostly in x; force z traffic with a strong +z velocity field and check ownership afterwards."""
+    n = 16
+    g, one = mkg(n, 2), mk(n)
+    u, v, w = one.get_velocity()
+    w = np.full_like(w, 4.0)            # 4 m/s * 0.01 s * 16 cells/m = 0.64 cells per step
+    for s in (g, one):
+        s.set_velocity(u, v, w)
+    before = [r.num_local_particles for r in g.ranks]
+    for _ in range(3):
+        g.Simulate(0.01); one.Simulate(0.01)
+    g.sync(); one.sync()
+    after = [r.num_local_particles for r in g.ranks]
+    assert sum(after) == sum(before) == one.num_particles
+    assert same(g.get_particles(), one.get_particles())
+    cells = one.get_cell_indices()
+    for r in g.ranks:
+        mine = ~np.isnan(r.get_particles()[:, 0])
+        z = cells[mine] // (n * n)
+        assert (z >= r.z0).all() and (z < r.z1).all()
+    assert after != before, "the test is meant to move particles across the slab boundary"
+    g.close()
+
+
+def test_group_reset_after_steps_and_hooks_refused():
+    from fluidsimulation_b200 import Fs3Error
+    n = 16
+    g, one = mkg(n, 2), mk(n)
+    g.Simulate(0.01)
+    g.ResetSimulation()
+    g.sync()
+    assert same(g.get_particles(), one.get_particles())
+    with pytest.raises(Fs3Error):
+        g.ranks[0].advect()             # stage hooks are single-GPU only
+    with pytest.raises(Fs3Error):
+        g.ranks[0].Simulate(0.01)       # a lockstep rank cannot step alone
+    g.close()
+
+
+def test_multiprocess_two_gpus():
+    """One process per GPU over CUDA IPC (needs two B200s: run with `gpurun --gpus 2`; skipped on a single-GPU box)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (ranks spin on each other's flags and must not share a device)")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                          "--master-port", "29533", os.path.join(ROOT, "tests", "shard_worker.py"), "--n", "24", "--steps", "3"],
+                         capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "SHARD_WORKER_OK" in out.stdout
