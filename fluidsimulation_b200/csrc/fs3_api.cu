@@ -402,6 +402,43 @@ int fs3_set_particles(fs3_sim* s, const fs3_particle* host, long long count) {
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	return FS3_OK;
 }
+// The particles this rank owns, compact, with their creation ids (= index into the reference's m_particles).  The cheap
+// per-rank way in and out of a sharded simulation: every rank moves only its own 1/world of the particles.
+int fs3_get_local_particles(fs3_sim* s, fs3_particle* host, int* ids, long long cap, long long* count) {
+	ENTER(s);
+	if (count) *count = s->np;
+	if (s->np <= 0) return FS3_OK;
+	if (!host || !ids || cap < s->np) return FS3_ERR_INVALID;
+	const size_t n = (size_t)s->np;
+	int rc = fs3i_staging(s, n * (sizeof(fs3_particle) + 4));
+	if (rc) return rc;
+	fs3_particle* dp = (fs3_particle*)s->stage_ptr;
+	int* di = (int*)((char*)s->stage_ptr + n * sizeof(fs3_particle));
+	if ((rc = fs3i_pack_local(s, dp, di))) return rc;
+	FS3_CUDA(cudaMemcpyAsync(host, dp, n * sizeof(fs3_particle), cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaMemcpyAsync(ids, di, n * 4, cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	return FS3_OK;
+}
+// Replaces this rank's particles.  They need not lie in the rank's slab: the next step's migration delivers strays.
+int fs3_set_local_particles(fs3_sim* s, const fs3_particle* host, const int* ids, long long count) {
+	ENTER(s);
+	if (count < 0 || (count > 0 && (!host || !ids))) return FS3_ERR_INVALID;
+	if (s->world == 1) return fail(s, FS3_ERR_STATE, "fs3_set_local_particles is for sharded handles (use fs3_set_particles)");
+	if (count > s->cap) return fail(s, FS3_ERR_STATE, "more particles than the slab's capacity");
+	const size_t n = (size_t)(count > 0 ? count : 1);
+	int rc = fs3i_staging(s, n * (sizeof(fs3_particle) + 4));
+	if (rc) return rc;
+	fs3_particle* dp = (fs3_particle*)s->stage_ptr;
+	int* di = (int*)((char*)s->stage_ptr + n * sizeof(fs3_particle));
+	if (count > 0) {
+		FS3_CUDA(cudaMemcpyAsync(dp, host, (size_t)count * sizeof(fs3_particle), cudaMemcpyHostToDevice, s->stream));
+		FS3_CUDA(cudaMemcpyAsync(di, ids, (size_t)count * 4, cudaMemcpyHostToDevice, s->stream));
+	}
+	if ((rc = fs3i_load_local(s, dp, di, count))) return rc;
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	return FS3_OK;
+}
 int fs3_get_velocity(fs3_sim* s, float* U, float* V, float* W) {
 	ENTER(s);
 	if (U) FS3_CUDA(cudaMemcpyAsync(U, s->U, s->nU * 4, cudaMemcpyDeviceToHost, s->stream));

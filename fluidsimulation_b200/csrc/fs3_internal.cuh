@@ -107,7 +107,7 @@ struct fs3_sim {
 	long long gcap;            // capacity of each ghost region (== poff)
 	long long np_in;           // length of the live range including dead slots (id < 0) left by emigrants; == np when sorted
 	long long np_all[FS3_MAX_WORLD];  // live particle count of every rank, tracked identically on all ranks
-	uint32_t* mig_matrix;      // world x world: [r*world+d] = particles rank r sends to rank d (row r written by rank r)
+	uint32_t* mig_matrix;      // world x (world+1): row r (written by rank r into every copy) = particles r sends to each rank, then the length of r's live range
 	uint32_t* mig_ctl;         // [0,world) counts, [world,2world) cursors, [2world] number of emigrants
 	uint32_t* leaver_idx;      // indices (relative to poff) of this step's emigrants
 	float4 *mig_pos, *mig_vel; // emigrants grouped by destination
@@ -269,6 +269,8 @@ int fs3i_reset_particles_slab(fs3_sim* s);
 int fs3i_mig_mark(fs3_sim* s);                                              // emigrants of the live range (not fused with Advect)
 int fs3i_mig_pack(fs3_sim* s);
 int fs3i_load_particles_owned(fs3_sim* s, const fs3_particle* dev_in, long long count);
+int fs3i_pack_local(fs3_sim* s, fs3_particle* dev_out, int* dev_ids);
+int fs3i_load_local(fs3_sim* s, const fs3_particle* dev_in, const int* dev_ids, long long count);
 // project.cu (sharded pieces)
 int fs3i_project_setup(fs3_sim* s, float dt, bool from_old, bool with_gravity);
 int fs3i_sor_prepare(fs3_sim* s);

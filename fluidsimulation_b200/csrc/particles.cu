@@ -444,6 +444,33 @@ int fs3i_load_particles_owned(fs3_sim* s, const fs3_particle* dev_in, long long 
 	s->np = s->np_in = std::min<long long>(s->np_all[s->rank], s->cap);
 	return fs3i_check_flags(s);
 }
+// this rank's particles as compact AoS + creation ids (live range must be hole-free: true at every API boundary)
+__global__ void k_pack_local(const float4* __restrict__ pos, const float4* __restrict__ vel, long long np, fs3_particle* __restrict__ out, int* __restrict__ ids) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	float4 p = pos[i], v = vel[i];
+	out[i] = fs3_particle{p.x, p.y, p.z, v.x, v.y, v.z};
+	ids[i] = __float_as_int(p.w);
+}
+__global__ void k_load_local(const fs3_particle* __restrict__ in, const int* __restrict__ ids, long long np, float4* __restrict__ pos, float4* __restrict__ vel) {
+	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= np) return;
+	fs3_particle q = in[i];
+	pos[i] = make_float4(q.X, q.Y, q.Z, __int_as_float(ids[i]));
+	vel[i] = make_float4(q.uX, q.uY, q.uZ, 0.0f);
+}
+int fs3i_pack_local(fs3_sim* s, fs3_particle* dev_out, int* dev_ids) {
+	if (s->np_in != s->np) { s->err = "live range has holes (mid-step)"; return FS3_ERR_STATE; }
+	if (s->np <= 0) return FS3_OK;
+	k_pack_local<<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->vel[s->cur] + s->poff, s->np, dev_out, dev_ids); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+int fs3i_load_local(fs3_sim* s, const fs3_particle* dev_in, const int* dev_ids, long long count) {
+	s->np = s->np_in = count; s->np_all[s->rank] = count; s->cur = 0; s->sorted = false; s->closest_valid = false;
+	if (count <= 0) return FS3_OK;
+	k_load_local<<<cdiv(count, 256), 256, 0, s->stream>>>(dev_in, dev_ids, count, s->pos[0] + s->poff, s->vel[0] + s->poff); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
 int fs3i_cell_indices(fs3_sim* s, int* dev_out) {
 	if (s->np_in <= 0) return FS3_OK;
 	GridDims d{s->nx, s->ny, s->nz};

@@ -38,7 +38,7 @@ size_t fs3i_arena_bytes(int n, long long ptot, long long mig_cap, int world) {
 	t += up512((nvec + 1) * 4) + 2 * (up512(nvec * 4) + up512((nvec + 1) * 4)); // SOR lists
 	const size_t nt = ((N + 7) / 8) * ((N + 7) / 8) * ((N + 3) / 4);
 	t += up512(8 * nt * 4) + up512(nt * 4) + 512;                             // level-set item table, epochs, ticket
-	t += up512((size_t)world * world * 4) + up512((2 * (size_t)world + 1) * 4) + up512((size_t)mig_cap * 4) + 2 * up512((size_t)mig_cap * 16);
+	t += up512((size_t)world * (world + 1) * 4) + up512((2 * (size_t)world + 1) * 4) + up512((size_t)mig_cap * 4) + 2 * up512((size_t)mig_cap * 16);
 	t += up512((FS3_MAX_WORLD + 2) * 4) + 512;                                // bar, sor_done
 	return t + (1u << 20);
 }
@@ -61,12 +61,12 @@ void fs3i_free(fs3_sim* s, void* p) {
 int fs3i_shard_alloc(fs3_sim* s) {
 	int rc;
 	const int w = s->world;
-	if ((rc = fs3i_alloc(s, (void**)&s->mig_matrix, (size_t)w * w * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_ctl, (2 * (size_t)w + 1) * 4)) ||
+	if ((rc = fs3i_alloc(s, (void**)&s->mig_matrix, (size_t)w * (w + 1) * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_ctl, (2 * (size_t)w + 1) * 4)) ||
 	    (rc = fs3i_alloc(s, (void**)&s->leaver_idx, (size_t)s->mig_cap * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_pos, (size_t)s->mig_cap * 16)) ||
 	    (rc = fs3i_alloc(s, (void**)&s->mig_vel, (size_t)s->mig_cap * 16)) || (rc = fs3i_alloc(s, (void**)&s->bar, (FS3_MAX_WORLD + 2) * 4)) ||
 	    (rc = fs3i_alloc(s, (void**)&s->sor_done, 4)))
 		return rc;
-	FS3_CUDA(cudaMallocHost((void**)&s->h_pin, (size_t)std::max(w * w, 64) * 4));
+	FS3_CUDA(cudaMallocHost((void**)&s->h_pin, (size_t)std::max(w * (w + 1), 64) * 4));
 	return FS3_OK;
 }
 
@@ -127,51 +127,52 @@ int fs3i_sor_wait(fs3_sim* s, uint32_t epoch) {
 }
 
 // ---- particle migration ----------------------------------------------------------------------------------------------
-// row `rank` of the count matrix goes into every rank's copy
-__global__ void k_mig_publish(PeerPtrs mats, const uint32_t* __restrict__ ctl, int rank, int world) {
+// row `rank` of the count matrix -- emigrants per destination, then the length of my live range -- goes into every rank's copy
+__global__ void k_mig_publish(PeerPtrs mats, const uint32_t* __restrict__ ctl, int rank, int world, uint32_t live_len) {
 	const int d = threadIdx.x;
 	if (d >= world) return;
-	for (int j = 0; j < world; j++) mats.p[d][rank * world + j] = ctl[j];
+	uint32_t* row = mats.p[d] + rank * (world + 1);
+	for (int j = 0; j < world; j++) row[j] = ctl[j];
+	row[world] = live_len;
 }
 int fs3i_mig_publish(fs3_sim* s) {
 	PeerPtrs pp;
 	for (int r = 0; r < s->world; r++) pp.p[r] = fs3_peer(s, r, s->mig_matrix);
-	k_mig_publish<<<1, 32, 0, s->stream>>>(pp, s->mig_ctl, s->rank, s->world); FS3_LAUNCH_CHECK();
+	k_mig_publish<<<1, 32, 0, s->stream>>>(pp, s->mig_ctl, s->rank, s->world, (uint32_t)s->np_in); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 
 // After the barrier every rank holds the whole count matrix: bring it to the host (the one host round trip of the
 // migration), append my emigrants to the tail of each destination's live range, and advance the replicated bookkeeping.
 int fs3i_mig_exchange(fs3_sim* s) {
-	const int w = s->world, me = s->rank;
-	FS3_CUDA(cudaMemcpyAsync(s->h_pin, s->mig_matrix, (size_t)w * w * 4, cudaMemcpyDeviceToHost, s->stream));
+	const int w = s->world, me = s->rank, W1 = w + 1;
+	FS3_CUDA(cudaMemcpyAsync(s->h_pin, s->mig_matrix, (size_t)w * W1 * 4, cudaMemcpyDeviceToHost, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	int rc = fs3i_check_flags(s);
 	if (rc) return rc;
-	const uint32_t* m = s->h_pin;
+	const uint32_t* m = s->h_pin;   // m[r*W1 + d] = particles r -> d;  m[r*W1 + w] = length of r's live range (hole-free before this migration)
 	long long out_me = 0;
-	for (int d = 0; d < w; d++) out_me += m[me * w + d];
+	for (int d = 0; d < w; d++) out_me += m[me * W1 + d];
 	if (out_me > s->mig_cap) { s->err = "more emigrants in one step than the migration buffer holds"; return FS3_ERR_STATE; }
 	long long base = 0;
 	for (int d = 0; d < w; d++) {
-		const long long cnt = m[me * w + d];
+		const long long cnt = m[me * W1 + d];
 		if (d != me && cnt > 0) {
-			long long off = s->np_all[d];   // the destination's live range is hole-free up to its pre-migration length
-			for (int r = 0; r < me; r++) off += m[r * w + d];
+			long long off = m[d * W1 + w];
+			for (int r = 0; r < me; r++) off += m[r * W1 + d];
 			FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, d, s->pos[s->cur]) + s->poff + off, s->mig_pos + base, (size_t)cnt * sizeof(float4), cudaMemcpyDefault, s->stream));
 			FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, d, s->vel[s->cur]) + s->poff + off, s->mig_vel + base, (size_t)cnt * sizeof(float4), cudaMemcpyDefault, s->stream));
 		}
 		base += cnt;
 	}
-	long long in_len = 0;
 	for (int d = 0; d < w; d++) {
 		long long arrive = 0, leave = 0;
-		for (int r = 0; r < w; r++) { arrive += m[r * w + d]; leave += m[d * w + r]; }
-		if (s->np_all[d] + arrive > s->cap) { s->err = "particle capacity of a slab exceeded by migration"; return FS3_ERR_STATE; }
-		if (d == me) in_len = s->np_all[d] + arrive;
-		s->np_all[d] += arrive - leave;
+		for (int r = 0; r < w; r++) { arrive += m[r * W1 + d]; leave += m[d * W1 + r]; }
+		const long long len = m[d * W1 + w];
+		if (len + arrive > s->cap) { s->err = "particle capacity of a slab exceeded by migration"; return FS3_ERR_STATE; }
+		if (d == me) s->np_in = len + arrive;
+		s->np_all[d] = len - leave + arrive;
 	}
-	s->np_in = in_len;
 	s->np = s->np_all[me];
 	s->sorted = false;
 	return FS3_OK;

@@ -26,7 +26,7 @@ ABI_SYMBOLS = [
     "fs3_get_cell_counts", "fs3_get_closest", "fs3_get_pressure", "fs3_get_rhs_diag", "fs3_get_sor_residuals",
     "fs3_stage_times", "fs3_sor_bench", "fs3_set_phi_all_fluid", "fs3_stream", "fs3_kernel_launches",
     "fs3_create_sharded", "fs3_shard_get_handle", "fs3_shard_connect", "fs3_shard_plan", "fs3_shard_info",
-    "fs3_num_local_particles", "fs3_group_create", "fs3_group_reset", "fs3_group_step",
+    "fs3_num_local_particles", "fs3_get_local_particles", "fs3_set_local_particles", "fs3_group_create", "fs3_group_reset", "fs3_group_step",
 ]
 SHARD_HANDLE_BYTES = 128
 
@@ -193,6 +193,21 @@ class FluidSim3:
     def set_particles(self, p):
         p = np.ascontiguousarray(p, np.float32)
         self._ck(self._lib.fs3_set_particles(self._h, _ptr(p), C.c_longlong(p.shape[0])))
+
+    def get_local_particles(self, out=None, ids=None):
+        """(records, creation ids) of the particles this rank owns."""
+        n = self.num_local_particles
+        if out is None:
+            out = np.empty((n, 6), np.float32)
+        if ids is None:
+            ids = np.empty(n, np.int32)
+        cnt = C.c_longlong(0)
+        self._ck(self._lib.fs3_get_local_particles(self._h, _ptr(out), _ptr(ids), C.c_longlong(out.shape[0]), C.byref(cnt)))
+        return out[:cnt.value], ids[:cnt.value]
+
+    def set_local_particles(self, p, ids):
+        p, ids = np.ascontiguousarray(p, np.float32), np.ascontiguousarray(ids, np.int32)
+        self._ck(self._lib.fs3_set_local_particles(self._h, _ptr(p), _ptr(ids), C.c_longlong(p.shape[0])))
 
     def get_velocity(self):
         u, v, w = np.empty(self.nU, np.float32), np.empty(self.nV, np.float32), np.empty(self.nW, np.float32)

@@ -93,6 +93,10 @@ int fs3_shard_connect(fs3_sim* s, const void* blobs_in_rank_order);
 int fs3_shard_plan(int nz, int world, int rank, int* z0, int* z1);   /* pure host arithmetic: the slab of a rank */
 int fs3_shard_info(const fs3_sim* s, int* rank, int* world, int* z0, int* z1);
 long long fs3_num_local_particles(const fs3_sim* s);                   /* particles this rank owns right now */
+/* This rank's own particles, compact, with their creation ids (index into the reference's m_particles): the per-rank way in
+ * and out, each rank moving 1/world of the data.  Uploaded particles may lie outside the slab; the next step migrates them. */
+int fs3_get_local_particles(fs3_sim* s, fs3_particle* host, int* ids, long long cap, long long* count);
+int fs3_set_local_particles(fs3_sim* s, const fs3_particle* host, const int* ids, long long count);
 /* All ranks inside ONE process on ONE device, sharing a stream and stepped phase by phase ("lockstep"): the same slab
  * kernels, halo stores, migration and ghost-layer code as the multi-process path, but every cross-rank wait is already
  * satisfied by stream order, so it runs (and is parity-tested) on a single GPU.  out/handles = array of `world` handles. */
