@@ -131,7 +131,13 @@ def run_gpu(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local_rank))
     n = args.grid
-    sim = FluidSim3(n, n, n, float(n), device=local_rank)
+    sharded = world > 1 and not args.replicas
+    if sharded:
+        # z-slab sharding: ONE simulation over all ranks (strong scaling); handle blobs travel over torch.distributed once
+        from fluidsimulation_b200 import torch_allgather
+        sim = FluidSim3(n, n, n, float(n), device=local_rank, rank=rank, world=world, allgather=torch_allgather())
+    else:
+        sim = FluidSim3(n, n, n, float(n), device=local_rank)
     sim.set_params(precision=1 if args.precision == "fp32" else 0, record_stage_times=1)
     P = sim.num_particles
     stream = torch.cuda.ExternalStream(sim.stream, device=local_rank)
@@ -164,51 +170,87 @@ def run_gpu(args, rank, world, local_rank):
     barrier()
     clocks = sampler.stop()
     launches = sim.kernel_launches - launches0
+    if world > 1:
+        t = torch.tensor([float(launches)], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        launches = int(t.item())
     ms = e0.elapsed_time(e1)
     if world > 1:
         t = torch.tensor([ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    value = world * P * args.steps / (ms * 1e-3)
+    jobs = 1 if sharded else world          # sharded: P is the particle count of the whole simulation
+    value = jobs * P * args.steps / (ms * 1e-3)
 
     # ---- end to end through the reference-facing calls with HOST buffers --------------------------------
     # m_particles lives in pinned host memory: upload it, Simulate, read it back (Old3D.cpp:234,263-269).
-    host = torch.empty((P, 6), dtype=torch.float32, pin_memory=True)
-    hnp = host.numpy()
-    sim.get_particles(out=hnp)
     e2e_steps = max(1, min(args.steps, 5))
-    barrier()
-    t0 = time.perf_counter()
-    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    g0.record(stream)
-    for _ in range(e2e_steps):
-        sim.set_particles(hnp)
-        sim.Simulate(0.01)
+    if sharded:
+        # every rank moves the particles it owns (records + creation ids) through its own pinned buffers
+        capl = int(sim.num_local_particles * 1.25) + 65536
+        host = torch.empty((capl, 6), dtype=torch.float32, pin_memory=True)
+        hids = torch.empty((capl,), dtype=torch.int32, pin_memory=True)
+        hnp, inp = host.numpy(), hids.numpy()
+        lp, li = sim.get_local_particles(out=hnp, ids=inp)
+        moved = 0
+        barrier()
+        t0 = time.perf_counter()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record(stream)
+        for _ in range(e2e_steps):
+            sim.set_local_particles(lp, li)
+            moved += lp.shape[0] * 28
+            sim.Simulate(0.01)
+            lp, li = sim.get_local_particles(out=hnp, ids=inp)
+            moved += lp.shape[0] * 28
+        g1.record(stream)
+        sim.sync()
+        barrier()
+        t = torch.tensor([float(moved)], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        bytes_each_way = float(t.item()) / 2 / e2e_steps
+    else:
+        host = torch.empty((P, 6), dtype=torch.float32, pin_memory=True)
+        hnp = host.numpy()
         sim.get_particles(out=hnp)
-    g1.record(stream)
-    sim.sync()
-    barrier()
+        barrier()
+        t0 = time.perf_counter()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record(stream)
+        for _ in range(e2e_steps):
+            sim.set_particles(hnp)
+            sim.Simulate(0.01)
+            sim.get_particles(out=hnp)
+        g1.record(stream)
+        sim.sync()
+        barrier()
+        bytes_each_way = P * 24
     e2e_ms = max(g0.elapsed_time(g1), (time.perf_counter() - t0) * 1e3)
     if world > 1:
         t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
-    e2e_value = world * P * e2e_steps / (e2e_ms * 1e-3)
+    e2e_value = jobs * P * e2e_steps / (e2e_ms * 1e-3)
 
     # ---- roofline of the dominant kernel (one colour sweep of red-black SOR) ----------------------------
     iters = sim.get_params().sor_iterations
     n_launch = 2 * iters * args.steps
     avg_launch_ms = sor_ms / n_launch
-    fluid_cells = int((sim.get_phi() < 0).sum())
+    phi = sim.get_phi().reshape(n, n * n)
+    fluid_cells = int((phi[sim.z0:sim.z1] < 0).sum())      # the cells this rank sweeps
+    if world > 1:   # the slowest rank sets the time: report the largest slab
+        t = torch.tensor([float(fluid_cells)], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        fluid_cells = int(t.item())
     bytes_per_launch = SOR_BYTES_PER_CELL_ITER[args.precision] * fluid_cells / 2.0
     peak, peak_src = measured_peaks()
     achieved = bytes_per_launch / (avg_launch_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": "k_sor_half<%s>" % ("float,4" if args.precision == "fp32" else "double,2"),
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": args.traffic,
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_us": avg_launch_ms * 1e3,
-                "launches_timed": n_launch, "fluid_cells": fluid_cells, "grid_cells": n ** 3,
+                "launches_timed": n_launch, "fluid_cells": fluid_cells, "grid_cells": n ** 3 // (world if sharded else 1),
                 "cell_updates_per_s": fluid_cells * iters * args.steps / (sor_ms * 1e-3),
-                "grid_cells_per_s": n ** 3 * iters * args.steps / (sor_ms * 1e-3),
+                "grid_cells_per_s": n ** 3 // (world if sharded else 1) * iters * args.steps / (sor_ms * 1e-3),
                 "share_of_step": sor_ms / ms}
 
     if rank == 0:
@@ -219,12 +261,12 @@ def run_gpu(args, rank, world, local_rank):
             cpu = {"value": cv, "unit": "particle-steps/s", "cores": 1, "kind": kind,
                    "sample": "%d^3 dam break (%d particles), 2 Simulate(0.01) steps, %.1f s, single thread (the reference has no threads)" % (cn, cP, cdt)}
         line = {"metric": "particle-steps/s", "value": value, "unit": "particle-steps/s", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
                 "dtype": "f32 particles/grids, %s pressure solve" % ("f32" if args.precision == "fp32" else "f64"), "data": "synthetic",
-                "config": {"workload": "FluidSim3 dam-break full step, %d^3 grid, %d particles/GPU, 100 SOR iterations, dt=0.01" % (n, P),
-                           "parallelism": "1 GPU" if world == 1 else "%d independent replicas (z-slab sharding not built yet)" % world,
+                "config": {"workload": "FluidSim3 dam-break full step, %d^3 grid, %d particles%s, 100 SOR iterations, dt=0.01" % (n, P, " in total" if sharded else "/GPU"),
+                           "parallelism": "1 GPU" if world == 1 else ("%d z-slabs, one rank per GPU, CUDA-IPC peer stores over NVLink (SOR halo fused into the sweep, particle migration, ghost layers); level-set sweeps and extrapolation replicated" % world if sharded else "%d independent replicas" % world),
                            "l2": "working set (%.1f GB) larger than L2; no flush" % ((P * 64 + 40.0 * n ** 3) / 1e9)},
-                "e2e": {"value": e2e_value, "unit": "particle-steps/s", "h2d_bytes_per_step": P * 24, "d2h_bytes_per_step": P * 24,
+                "e2e": {"value": e2e_value, "unit": "particle-steps/s", "h2d_bytes_per_step": int(bytes_each_way), "d2h_bytes_per_step": int(bytes_each_way),
                         "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
                 "stage_ms_per_step": {k: v / args.steps for k, v in stage_acc.items()}}
@@ -243,6 +285,7 @@ def main():
     ap.add_argument("--precision", choices=["fp64", "fp32"], default="fp64")
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--replicas", action="store_true", help="N>1: N independent simulations instead of one z-slab sharded simulation")
     ap.add_argument("--traffic", type=float, default=None, help="ncu dram bytes per launch of the dominant kernel (profiles/)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -103,68 +103,88 @@ struct SorShard {
 	uint32_t wait_epoch, signal_epoch;
 	size_t lo_begin, lo_end, hi_begin, hi_end;   // element ranges of the slab's first / last plane in a colour array
 	uint32_t* done;           // block counter
+	const uint32_t *n_lo, *n_hi;   // list positions: entries [0, n_lo) lie in the slab's first plane, [n_hi, n) in its last
 	int* flags;
 	int nospin;
 };
-template <typename REAL, int VEC, bool SHARD>
-__global__ void __launch_bounds__(256) k_sor_half(Sys<REAL> sy, int colour, REAL omega, REAL one_minus_omega,
-                                                  const uint32_t* __restrict__ list, const uint32_t* __restrict__ count, SorShard sh) {
+// one list entry: VEC consecutive cells of one colour.  PUSH: also store the result into the neighbours' ghost planes.
+template <typename REAL, int VEC, bool PUSH>
+__device__ __forceinline__ void sor_vector(const Sys<REAL>& sy, int colour, REAL omega, REAL one_minus_omega, uint32_t ent, const SorShard& sh) {
 	typedef Ops<REAL> O;
 	typedef typename VecT<REAL, VEC>::type V;
 	typedef typename VecT<REAL, VEC>::mtype M;
-	if (SHARD) {
-		if (threadIdx.x < 2 && sh.peer_flag[threadIdx.x]) fs3_flag_wait(sh.my_flag + threadIdx.x, sh.wait_epoch, sh.flags, sh.nospin);
-		__syncthreads();
-	}
-	const uint32_t n = __ldg(count);
 	const REAL* __restrict__ o = sy.p[colour ^ 1];
 	const M nodiag = VEC == 2 ? (M)0x8080 : (M)0x80808080u;
-	for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
-		const uint32_t ent = __ldg(list + t);
-		const int s = (int)(ent >> 31);   // x parity of this colour in this row
-		const size_t base = (size_t)(ent & 0x7fffffffu) * VEC;
-		const M mm = *reinterpret_cast<const M*>(sy.mask[colour] + base);
-		REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
-		*reinterpret_cast<V*>(own) = *reinterpret_cast<const V*>(sy.p[colour] + base);
-		*reinterpret_cast<V*>(bb) = *reinterpret_cast<const V*>(sy.b[colour] + base);
-		*reinterpret_cast<V*>(xc) = *reinterpret_cast<const V*>(o + base);
-		*reinterpret_cast<V*>(ym) = *reinterpret_cast<const V*>(o + base - sy.rb.hp);
-		*reinterpret_cast<V*>(yp) = *reinterpret_cast<const V*>(o + base + sy.rb.hp);
-		*reinterpret_cast<V*>(zm) = *reinterpret_cast<const V*>(o + base - sy.rb.plane);
-		*reinterpret_cast<V*>(zp) = *reinterpret_cast<const V*>(o + base + sy.rb.plane);
-		const REAL edge = s == 0 ? o[base - 1] : o[base + VEC];
-		if ((mm & nodiag) != nodiag) *reinterpret_cast<V*>(dd) = *reinterpret_cast<const V*>(sy.dg[colour] + base);
+	const int s = (int)(ent >> 31);   // x parity of this colour in this row
+	const size_t base = (size_t)(ent & 0x7fffffffu) * VEC;
+	const M mm = *reinterpret_cast<const M*>(sy.mask[colour] + base);
+	REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
+	*reinterpret_cast<V*>(own) = *reinterpret_cast<const V*>(sy.p[colour] + base);
+	*reinterpret_cast<V*>(bb) = *reinterpret_cast<const V*>(sy.b[colour] + base);
+	*reinterpret_cast<V*>(xc) = *reinterpret_cast<const V*>(o + base);
+	*reinterpret_cast<V*>(ym) = *reinterpret_cast<const V*>(o + base - sy.rb.hp);
+	*reinterpret_cast<V*>(yp) = *reinterpret_cast<const V*>(o + base + sy.rb.hp);
+	*reinterpret_cast<V*>(zm) = *reinterpret_cast<const V*>(o + base - sy.rb.plane);
+	*reinterpret_cast<V*>(zp) = *reinterpret_cast<const V*>(o + base + sy.rb.plane);
+	const REAL edge = s == 0 ? o[base - 1] : o[base + VEC];
+	if ((mm & nodiag) != nodiag) *reinterpret_cast<V*>(dd) = *reinterpret_cast<const V*>(sy.dg[colour] + base);
 #pragma unroll
-		for (int e = 0; e < VEC; e++) {
-			const unsigned m = (unsigned)(mm >> (8 * e)) & 0xffu;
-			if (!(m & 64u)) continue;
-			// other-colour x neighbours: left at index e-1+s, right at e+s
-			const REAL L = s ? xc[e] : (e == 0 ? edge : xc[e > 0 ? e - 1 : 0]);
-			const REAL R = s ? (e == VEC - 1 ? edge : xc[e < VEC - 1 ? e + 1 : e]) : xc[e];
-			REAL nms = 0;                                   // neighborMinusSum, order x-,x+,y-,y+,z-,z+ (S3D.cpp:964-993)
-			if (m & 1u) nms = O::sub(nms, L);
-			if (m & 2u) nms = O::sub(nms, R);
-			if (m & 4u) nms = O::sub(nms, ym[e]);
-			if (m & 8u) nms = O::sub(nms, yp[e]);
-			if (m & 16u) nms = O::sub(nms, zm[e]);
-			if (m & 32u) nms = O::sub(nms, zp[e]);
-			const REAL dg = (m & 128u) ? (REAL)__popc(m & 63u) : dd[e];
-			// p = (1-omega) p + omega (b - nms) / diag   (S3D.cpp:996)
-			own[e] = O::add(O::mul(one_minus_omega, own[e]), O::div(O::mul(omega, O::sub(bb[e], nms)), dg));
-		}
-		*reinterpret_cast<V*>(sy.p[colour] + base) = *reinterpret_cast<V*>(own);
-		if (SHARD) {
-			if (sh.peer_p[0] && base >= sh.lo_begin && base < sh.lo_end) *reinterpret_cast<V*>(reinterpret_cast<REAL*>(sh.peer_p[0]) + base) = *reinterpret_cast<V*>(own);
-			if (sh.peer_p[1] && base >= sh.hi_begin && base < sh.hi_end) *reinterpret_cast<V*>(reinterpret_cast<REAL*>(sh.peer_p[1]) + base) = *reinterpret_cast<V*>(own);
-		}
+	for (int e = 0; e < VEC; e++) {
+		const unsigned m = (unsigned)(mm >> (8 * e)) & 0xffu;
+		if (!(m & 64u)) continue;
+		// other-colour x neighbours: left at index e-1+s, right at e+s
+		const REAL L = s ? xc[e] : (e == 0 ? edge : xc[e > 0 ? e - 1 : 0]);
+		const REAL R = s ? (e == VEC - 1 ? edge : xc[e < VEC - 1 ? e + 1 : e]) : xc[e];
+		REAL nms = 0;                                   // neighborMinusSum, order x-,x+,y-,y+,z-,z+ (S3D.cpp:964-993)
+		if (m & 1u) nms = O::sub(nms, L);
+		if (m & 2u) nms = O::sub(nms, R);
+		if (m & 4u) nms = O::sub(nms, ym[e]);
+		if (m & 8u) nms = O::sub(nms, yp[e]);
+		if (m & 16u) nms = O::sub(nms, zm[e]);
+		if (m & 32u) nms = O::sub(nms, zp[e]);
+		const REAL dg = (m & 128u) ? (REAL)__popc(m & 63u) : dd[e];
+		// p = (1-omega) p + omega (b - nms) / diag   (S3D.cpp:996)
+		own[e] = O::add(O::mul(one_minus_omega, own[e]), O::div(O::mul(omega, O::sub(bb[e], nms)), dg));
 	}
-	if (SHARD) {
-		// publish: every thread's peer stores are made visible system-wide, then the last block raises the neighbours' flags
-		__threadfence_system();
+	*reinterpret_cast<V*>(sy.p[colour] + base) = *reinterpret_cast<V*>(own);
+	if (PUSH) {
+		if (sh.peer_p[0] && base >= sh.lo_begin && base < sh.lo_end) *reinterpret_cast<V*>(reinterpret_cast<REAL*>(sh.peer_p[0]) + base) = *reinterpret_cast<V*>(own);
+		if (sh.peer_p[1] && base >= sh.hi_begin && base < sh.hi_end) *reinterpret_cast<V*>(reinterpret_cast<REAL*>(sh.peer_p[1]) + base) = *reinterpret_cast<V*>(own);
+	}
+}
+
+// SHARD: BOUNDARY FIRST.  The list is in memory order, so the active vectors of the slab's first plane are its first n_lo
+// entries and those of its last plane the entries from n_hi on (both read from the scan of the activity flags).  The
+// lowest-numbered blocks sweep these two planes first, storing every result into the neighbour's ghost plane as well,
+// and the last of them to finish raises the neighbours' epoch flags; only then does the grid turn to the interior.  The
+// neighbours therefore get this half sweep's halo while the interior is still being swept, and the halo this rank waits
+// for at the start of the NEXT half sweep was sent a whole interior sweep earlier: the NVLink latency is off the critical
+// path.  (No write-after-read hazard: ghost planes are only read by the boundary vectors, i.e. before the signal that
+// allows the neighbour to overwrite them.)
+template <typename REAL, int VEC, bool SHARD>
+__global__ void __launch_bounds__(256) k_sor_half(Sys<REAL> sy, int colour, REAL omega, REAL one_minus_omega,
+                                                  const uint32_t* __restrict__ list, const uint32_t* __restrict__ count, SorShard sh) {
+	const uint32_t n = __ldg(count);
+	const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, G = gridDim.x * blockDim.x;
+	if (!SHARD) {
+		for (uint32_t t = gtid; t < n; t += G) sor_vector<REAL, VEC, false>(sy, colour, omega, one_minus_omega, __ldg(list + t), sh);
+		return;
+	}
+	if (threadIdx.x < 2 && sh.peer_flag[threadIdx.x]) fs3_flag_wait(sh.my_flag + threadIdx.x, sh.wait_epoch, sh.flags, sh.nospin);
+	__syncthreads();
+	const uint32_t n_lo = __ldg(sh.n_lo), n_hi = __ldg(sh.n_hi), B = n_lo + (n - n_hi);
+	bool pushed = false;
+	for (uint32_t t = gtid; t < B; t += G) {
+		sor_vector<REAL, VEC, true>(sy, colour, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))), sh);
+		pushed = true;
+	}
+	const uint32_t nbb = min(gridDim.x, max(1u, (B + blockDim.x - 1) / blockDim.x));   // blocks that hold boundary work
+	if (blockIdx.x < nbb) {
+		if (pushed) __threadfence_system();   // my peer stores are visible system-wide before the block reports in
 		__syncthreads();
 		if (threadIdx.x == 0) {
-			const uint32_t t = atomicAdd(sh.done, 1u);
-			if (t == gridDim.x - 1) {
+			const uint32_t d = atomicAdd(sh.done, 1u);
+			if (d == nbb - 1) {
 				*sh.done = 0;
 				__threadfence_system();
 				if (sh.peer_flag[0]) fs3_st_release_sys(sh.peer_flag[0], sh.signal_epoch);
@@ -172,6 +192,7 @@ __global__ void __launch_bounds__(256) k_sor_half(Sys<REAL> sy, int colour, REAL
 			}
 		}
 	}
+	for (uint32_t t = gtid; t < n - B; t += G) sor_vector<REAL, VEC, false>(sy, colour, omega, one_minus_omega, __ldg(list + n_lo + t), sh);
 }
 
 // active-vector flags (+1 trailing zero so that the exclusive scan's last entry is the count) and compaction
@@ -397,6 +418,9 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	sh.lo_begin = s->rb.plane * (size_t)(s->z0 + 1); sh.lo_end = sh.lo_begin + s->rb.plane;
 	sh.hi_begin = s->rb.plane * (size_t)s->z1; sh.hi_end = sh.hi_begin + s->rb.plane;
 	sh.done = s->sor_done; sh.flags = s->dev_flags; sh.nospin = s->lockstep ? 1 : 0;
+	// exclusive scan of the activity flags at the end of the first plane / the start of the last plane of the slab
+	sh.n_lo = s->sor_pos[c] + s->rb.plane * (size_t)(s->z0 + 2) / VEC;
+	sh.n_hi = s->sor_pos[c] + s->rb.plane * (size_t)s->z1 / VEC;
 	k_sor_half<REAL, VEC, true><<<nb, 256, 0, s->stream>>>(sy, c, omega, omo, s->sor_list[c], s->sor_count[c], sh); FS3_LAUNCH_CHECK();
 	s->sor_epoch = sh.signal_epoch;
 	return FS3_OK;

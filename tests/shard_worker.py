@@ -1,4 +1,4 @@
-"""Worker of the multi-process sharded tests: `torchrun --nproc-per-node N tests/shard_worker.py --n 24 --steps 3`.
+"""Worker of the multi-process sharded tests: `torchrun --nproc-per-node N tests/shard_worker.py 24 3`.
 Every rank builds its slab of the simulation on its own GPU, steps it, and rank 0 compares the merged result bit for
 bit with a single-GPU run of the same library on its device."""
 import argparse
@@ -15,8 +15,8 @@ def main():
     import torch.distributed as dist
     from fluidsimulation_b200 import FluidSim3, merge_particles, torch_allgather
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=24)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("n", type=int, nargs="?", default=24)
+    ap.add_argument("steps", type=int, nargs="?", default=3)
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
     dist.init_process_group(backend="gloo")

@@ -143,7 +143,7 @@ def test_multiprocess_two_gpus():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (ranks spin on each other's flags and must not share a device)")
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-                          "--master-port", "29533", os.path.join(ROOT, "tests", "shard_worker.py"), "--n", "24", "--steps", "3"],
+                          "--master-port", "29533", os.path.join(ROOT, "tests", "shard_worker.py"), "24", "3"],
                          capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "SHARD_WORKER_OK" in out.stdout
