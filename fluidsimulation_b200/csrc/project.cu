@@ -7,6 +7,7 @@
 // independent; same IEEE operations, no FMA contraction); REAL = float is the fast mode.
 #include "fs3_internal.cuh"
 #include <algorithm>
+#include <cstdlib>
 
 template <typename T> struct Ops;
 template <> struct Ops<double> {
@@ -86,6 +87,11 @@ __global__ void __launch_bounds__(256) k_project_setup(Sys<REAL> sy, const float
 template <typename REAL, int VEC> struct VecT;
 template <> struct VecT<double, 2> { typedef double2 type; typedef unsigned short mtype; };
 template <> struct VecT<float, 4> { typedef float4 type; typedef unsigned int mtype; };
+// 128-bit loads / stores into register arrays (component-wise, so that the arrays never get an address and stay in registers)
+__device__ __forceinline__ void ldv(const double* p, double (&a)[2]) { const double2 t = *reinterpret_cast<const double2*>(p); a[0] = t.x; a[1] = t.y; }
+__device__ __forceinline__ void ldv(const float* p, float (&a)[4]) { const float4 t = *reinterpret_cast<const float4*>(p); a[0] = t.x; a[1] = t.y; a[2] = t.z; a[3] = t.w; }
+__device__ __forceinline__ void stv(double* p, const double (&a)[2]) { *reinterpret_cast<double2*>(p) = make_double2(a[0], a[1]); }
+__device__ __forceinline__ void stv(float* p, const float (&a)[4]) { *reinterpret_cast<float4*>(p) = make_float4(a[0], a[1], a[2], a[3]); }
 
 // The sweep runs over a compacted list of the colour's ACTIVE vectors (VEC consecutive colour cells of which
 // at least one is fluid), built once per projection (200 sweeps reuse it): every resident warp does useful
@@ -108,26 +114,46 @@ struct SorShard {
 	int nospin;
 };
 // one list entry: VEC consecutive cells of one colour.  PUSH: also store the result into the neighbours' ghost planes.
+// The colour-dependent pointers are resolved once per thread with selects: indexing the kernel-parameter structs with a
+// run-time colour would make the compiler copy them to local memory.
+template <typename REAL> struct SorPtrs {
+	REAL* own; const REAL* other; const REAL* b; const REAL* dg; const unsigned char* mask;
+	size_t hp, plane;
+	REAL *peer_lo, *peer_hi;
+	size_t lo_begin, lo_end, hi_begin, hi_end;
+};
+template <typename REAL>
+__device__ __forceinline__ SorPtrs<REAL> sor_ptrs(const Sys<REAL>& sy, int colour, const SorShard& sh) {
+	SorPtrs<REAL> sp;
+	sp.own = colour ? sy.p[1] : sy.p[0]; sp.other = colour ? sy.p[0] : sy.p[1];
+	sp.b = colour ? sy.b[1] : sy.b[0]; sp.dg = colour ? sy.dg[1] : sy.dg[0]; sp.mask = colour ? sy.mask[1] : sy.mask[0];
+	sp.hp = (size_t)sy.rb.hp; sp.plane = sy.rb.plane;
+	sp.peer_lo = reinterpret_cast<REAL*>(sh.peer_p[0]); sp.peer_hi = reinterpret_cast<REAL*>(sh.peer_p[1]);
+	sp.lo_begin = sh.lo_begin; sp.lo_end = sh.lo_end; sp.hi_begin = sh.hi_begin; sp.hi_end = sh.hi_end;
+	return sp;
+}
 template <typename REAL, int VEC, bool PUSH>
-__device__ __forceinline__ void sor_vector(const Sys<REAL>& sy, int colour, REAL omega, REAL one_minus_omega, uint32_t ent, const SorShard& sh) {
+__device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, REAL one_minus_omega, uint32_t ent) {
 	typedef Ops<REAL> O;
 	typedef typename VecT<REAL, VEC>::type V;
 	typedef typename VecT<REAL, VEC>::mtype M;
-	const REAL* __restrict__ o = sy.p[colour ^ 1];
+	const REAL* __restrict__ o = sp.other;
 	const M nodiag = VEC == 2 ? (M)0x8080 : (M)0x80808080u;
 	const int s = (int)(ent >> 31);   // x parity of this colour in this row
 	const size_t base = (size_t)(ent & 0x7fffffffu) * VEC;
-	const M mm = *reinterpret_cast<const M*>(sy.mask[colour] + base);
+	const M mm = *reinterpret_cast<const M*>(sp.mask + base);
 	REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
-	*reinterpret_cast<V*>(own) = *reinterpret_cast<const V*>(sy.p[colour] + base);
-	*reinterpret_cast<V*>(bb) = *reinterpret_cast<const V*>(sy.b[colour] + base);
-	*reinterpret_cast<V*>(xc) = *reinterpret_cast<const V*>(o + base);
-	*reinterpret_cast<V*>(ym) = *reinterpret_cast<const V*>(o + base - sy.rb.hp);
-	*reinterpret_cast<V*>(yp) = *reinterpret_cast<const V*>(o + base + sy.rb.hp);
-	*reinterpret_cast<V*>(zm) = *reinterpret_cast<const V*>(o + base - sy.rb.plane);
-	*reinterpret_cast<V*>(zp) = *reinterpret_cast<const V*>(o + base + sy.rb.plane);
+	ldv(sp.own + base, own);
+	ldv(sp.b + base, bb);
+	ldv(o + base, xc);
+	ldv(o + base - sp.hp, ym);
+	ldv(o + base + sp.hp, yp);
+	ldv(o + base - sp.plane, zm);
+	ldv(o + base + sp.plane, zp);
 	const REAL edge = s == 0 ? o[base - 1] : o[base + VEC];
-	if ((mm & nodiag) != nodiag) *reinterpret_cast<V*>(dd) = *reinterpret_cast<const V*>(sy.dg[colour] + base);
+#pragma unroll
+	for (int e = 0; e < VEC; e++) dd[e] = (REAL)1;
+	if ((mm & nodiag) != nodiag) ldv(sp.dg + base, dd);
 #pragma unroll
 	for (int e = 0; e < VEC; e++) {
 		const unsigned m = (unsigned)(mm >> (8 * e)) & 0xffu;
@@ -146,10 +172,10 @@ __device__ __forceinline__ void sor_vector(const Sys<REAL>& sy, int colour, REAL
 		// p = (1-omega) p + omega (b - nms) / diag   (S3D.cpp:996)
 		own[e] = O::add(O::mul(one_minus_omega, own[e]), O::div(O::mul(omega, O::sub(bb[e], nms)), dg));
 	}
-	*reinterpret_cast<V*>(sy.p[colour] + base) = *reinterpret_cast<V*>(own);
+	stv(sp.own + base, own);
 	if (PUSH) {
-		if (sh.peer_p[0] && base >= sh.lo_begin && base < sh.lo_end) *reinterpret_cast<V*>(reinterpret_cast<REAL*>(sh.peer_p[0]) + base) = *reinterpret_cast<V*>(own);
-		if (sh.peer_p[1] && base >= sh.hi_begin && base < sh.hi_end) *reinterpret_cast<V*>(reinterpret_cast<REAL*>(sh.peer_p[1]) + base) = *reinterpret_cast<V*>(own);
+		if (sp.peer_lo && base >= sp.lo_begin && base < sp.lo_end) stv(sp.peer_lo + base, own);
+		if (sp.peer_hi && base >= sp.hi_begin && base < sp.hi_end) stv(sp.peer_hi + base, own);
 	}
 }
 
@@ -161,21 +187,26 @@ __device__ __forceinline__ void sor_vector(const Sys<REAL>& sy, int colour, REAL
 // for at the start of the NEXT half sweep was sent a whole interior sweep earlier: the NVLink latency is off the critical
 // path.  (No write-after-read hazard: ghost planes are only read by the boundary vectors, i.e. before the signal that
 // allows the neighbour to overwrite them.)
+#ifndef FS3_SOR_MINB
+#define FS3_SOR_MINB 4
+#endif
 template <typename REAL, int VEC, bool SHARD>
-__global__ void __launch_bounds__(256) k_sor_half(Sys<REAL> sy, int colour, REAL omega, REAL one_minus_omega,
+__global__ void __launch_bounds__(256, FS3_SOR_MINB) k_sor_half(Sys<REAL> sy, int colour, REAL omega, REAL one_minus_omega,
                                                   const uint32_t* __restrict__ list, const uint32_t* __restrict__ count, SorShard sh) {
 	const uint32_t n = __ldg(count);
 	const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, G = gridDim.x * blockDim.x;
+	const SorPtrs<REAL> sp = sor_ptrs<REAL>(sy, colour, sh);
 	if (!SHARD) {
-		for (uint32_t t = gtid; t < n; t += G) sor_vector<REAL, VEC, false>(sy, colour, omega, one_minus_omega, __ldg(list + t), sh);
+		for (uint32_t t = gtid; t < n; t += G) sor_vector<REAL, VEC, false>(sp, omega, one_minus_omega, __ldg(list + t));
 		return;
 	}
-	if (threadIdx.x < 2 && sh.peer_flag[threadIdx.x]) fs3_flag_wait(sh.my_flag + threadIdx.x, sh.wait_epoch, sh.flags, sh.nospin);
+	if (threadIdx.x == 0 && sh.peer_flag[0]) fs3_flag_wait(sh.my_flag, sh.wait_epoch, sh.flags, sh.nospin);
+	if (threadIdx.x == 1 && sh.peer_flag[1]) fs3_flag_wait(sh.my_flag + 1, sh.wait_epoch, sh.flags, sh.nospin);
 	__syncthreads();
 	const uint32_t n_lo = __ldg(sh.n_lo), n_hi = __ldg(sh.n_hi), B = n_lo + (n - n_hi);
 	bool pushed = false;
 	for (uint32_t t = gtid; t < B; t += G) {
-		sor_vector<REAL, VEC, true>(sy, colour, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))), sh);
+		sor_vector<REAL, VEC, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
 		pushed = true;
 	}
 	const uint32_t nbb = min(gridDim.x, max(1u, (B + blockDim.x - 1) / blockDim.x));   // blocks that hold boundary work
@@ -192,7 +223,7 @@ __global__ void __launch_bounds__(256) k_sor_half(Sys<REAL> sy, int colour, REAL
 			}
 		}
 	}
-	for (uint32_t t = gtid; t < n - B; t += G) sor_vector<REAL, VEC, false>(sy, colour, omega, one_minus_omega, __ldg(list + n_lo + t), sh);
+	for (uint32_t t = gtid; t < n - B; t += G) sor_vector<REAL, VEC, false>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
 }
 
 // active-vector flags (+1 trailing zero so that the exclusive scan's last entry is the count) and compaction
@@ -399,7 +430,15 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	REAL omo = (REAL)1 - omega;
 	// persistent grid-stride launch: enough blocks to fill the machine; the list length is read on the device
 	size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * (s->z1 - s->z0);
-	int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, 256)), (long long)s->sm_count * 8);
+	static int per_sm = 0;   // resident blocks per SM of the sweep kernel: the grid is exactly one wave
+	if (!per_sm) {
+		int a = 0, b = 0;
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_sor_half<REAL, VEC, false>, 256, 0);
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_sor_half<REAL, VEC, true>, 256, 0);
+		per_sm = std::max(1, std::min(a, b));
+		if (const char* e = getenv("FS3_SOR_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));
+	}
+	int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, 256)), (long long)s->sm_count * per_sm);
 	const int c = k & 1;
 	if (s->world == 1) {
 		k_sor_half<REAL, VEC, false><<<nb, 256, 0, s->stream>>>(sy, c, omega, omo, s->sor_list[c], s->sor_count[c], SorShard{}); FS3_LAUNCH_CHECK();
