@@ -71,7 +71,7 @@ struct fs3_sim {
 	int* orderv[3];          // nodes with cd>0 bucketed by distance
 	uint32_t* bucket;        // per slot: histogram / starts / cursors (3*bucket_cap+2 words)
 	int bucket_cap;
-	uint32_t* h_bucket;      // pinned host copy of the starts, (bucket_cap+1) words per slot
+	uint32_t* ex_arrive;     // arrive counter of the layered fill's grid barrier
 
 	// pressure system
 	RBLayout rb;

@@ -13,47 +13,85 @@
 #include "fs3_internal.cuh"
 
 // AX = staggered axis of this face grid (0:U, 1:V, 2:W).  Grid extents (xs,ys,zs) = cells + 1 on AX.
+// A thread owns a 1 x 2 x 2 block of nodes (i; j0,j0+1; k0,k0+1): their supports share half-rows, so the 4 nodes walk
+// 6 x 6 particle runs instead of 4 x 16, and a CTA of 32 x 2 x 2 threads (32 x 4 x 4 nodes) re-reads each half-row
+// from L1 rather than L2.  Every node still sees its particles in the order (hz, hy, run) of the one-node-per-thread
+// formulation, so the sums are bit-identical to it (and independent of how the grid is cut into slabs).
+#define P2G_KY 2
+#define P2G_KZ 2
 template <int AX>
 __global__ void __launch_bounds__(128) k_p2g_gather(const float4* __restrict__ pos, const float4* __restrict__ vel,
                                                     const uint32_t* __restrict__ start, GridDims d, float cpm, float* __restrict__ grid,
-                                                    int* __restrict__ cd, size_t q0, size_t q1) {
-	const int xs = d.nx + (AX == 0), ys = d.ny + (AX == 1), zs = d.nz + (AX == 2);
-	size_t q = q0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (q >= q1) return;
-	int i = (int)(q % xs), j = (int)((q / xs) % ys), k = (int)(q / ((size_t)xs * ys));
-	// wall planes: forced to zero and valid (S3D.cpp:578-599)
-	int m_ax = AX == 0 ? i : (AX == 1 ? j : k), n_ax = AX == 0 ? d.nx : (AX == 1 ? d.ny : d.nz);
-	if (m_ax == 0 || m_ax == n_ax) { grid[q] = 0.f; cd[q] = 0; return; }
-	// half-cell support: staggered axis [2m-2, 2m+1], other axes [2m-1, 2m+2], clipped to the grid
+                                                    int* __restrict__ cd, int kbeg, int kend) {
+	const int xs = d.nx + (AX == 0), ys = d.ny + (AX == 1);
+	const int i = blockIdx.x * 32 + (threadIdx.x & 31);
+	const int j0 = (blockIdx.y * 2 + ((threadIdx.x >> 5) & 1)) * P2G_KY;
+	const int k0 = kbeg + (blockIdx.z * 2 + (threadIdx.x >> 6)) * P2G_KZ;
+	if (j0 >= ys || k0 >= kend) return;   // warp-uniform
 	const int HX = 2 * d.nx, HY = 2 * d.ny, HZ = 2 * d.nz;
-	int x0 = max(2 * i - (AX == 0 ? 2 : 1), 0), x1 = min(2 * i + (AX == 0 ? 1 : 2), HX - 1);
-	int y0 = max(2 * j - (AX == 1 ? 2 : 1), 0), y1 = min(2 * j + (AX == 1 ? 1 : 2), HY - 1);
-	int z0 = max(2 * k - (AX == 2 ? 2 : 1), 0), z1 = min(2 * k + (AX == 2 ? 1 : 2), HZ - 1);
-	const float fi = (float)i, fj = (float)j, fk = (float)k;
+	// half-cell support: staggered axis [2m-2, 2m+1], other axes [2m-1, 2m+2], clipped to the grid
+	const bool lane_in = i < xs;
+	const int x0 = max(2 * i - (AX == 0 ? 2 : 1), 0), x1 = min(2 * i + (AX == 0 ? 1 : 2), HX - 1);
+	const int ylo = 2 * j0 - (AX == 1 ? 2 : 1), zlo = 2 * k0 - (AX == 2 ? 2 : 1);
+	const float fi = (float)i;
+	const float fj[2] = {(float)j0, (float)(j0 + 1)}, fk[2] = {(float)k0, (float)(k0 + 1)};
 	const float* __restrict__ vcomp = reinterpret_cast<const float*>(vel) + AX;
-	float sum = 0.f, amt = 0.f;
-	for (int hz = z0; hz <= z1; hz++)
-		for (int hy = y0; hy <= y1; hy++) {
-			size_t row = (size_t)HX * ((size_t)hy + (size_t)HY * hz);
-			uint32_t b = __ldg(start + row + x0), e = __ldg(start + row + x1 + 1);
+	float sum[P2G_KZ][P2G_KY], amt[P2G_KZ][P2G_KY];
+#pragma unroll
+	for (int c = 0; c < P2G_KZ; c++)
+#pragma unroll
+		for (int b = 0; b < P2G_KY; b++) sum[c][b] = amt[c][b] = 0.f;
+	// (the two run loops stay rolled: 36 unrolled copies of the particle loop overflow the instruction cache)
+#pragma unroll 1
+	for (int rz = 0; rz < 2 * P2G_KZ + 2; rz++) {
+		const int hz = zlo + rz;
+		if (hz < 0 || hz >= HZ) continue;
+#pragma unroll 1
+		for (int ry = 0; ry < 2 * P2G_KY + 2; ry++) {
+			const int hy = ylo + ry;
+			if (hy < 0 || hy >= HY) continue;
+			const size_t row = (size_t)HX * ((size_t)hy + (size_t)HY * hz);
+			uint32_t b = 0, e = 0;
+			if (lane_in) { b = __ldg(start + row + x0); e = __ldg(start + row + x1 + 1); }
 			for (uint32_t t = b; t < e; t++) {
-				float4 p = __ldg(pos + t);
+				const float4 p = __ldg(pos + t);
 				float qx = __fmul_rn(p.x, cpm), qy = __fmul_rn(p.y, cpm), qz = __fmul_rn(p.z, cpm);   // S3D.cpp:442-444
 				if (AX == 0) qx = __fadd_rn(qx, 0.5f);
 				if (AX == 1) qy = __fadd_rn(qy, 0.5f);
 				if (AX == 2) qz = __fadd_rn(qz, 0.5f);
-				float wx = __fsub_rn(1.f, fabsf(__fsub_rn(qx, fi)));
-				float wy = __fsub_rn(1.f, fabsf(__fsub_rn(qy, fj)));
-				float wz = __fsub_rn(1.f, fabsf(__fsub_rn(qz, fk)));
-				float w = __fmul_rn(__fmul_rn(wx, wy), wz);                                           // S3D.cpp:472-474
-				float u = __ldg(vcomp + 4 * (size_t)t);
-				sum = __fadd_rn(sum, __fmul_rn(w, u));
-				amt = __fadd_rn(amt, w);
+				const float u = __ldg(vcomp + 4 * (size_t)t);
+				const float wx = __fsub_rn(1.f, fabsf(__fsub_rn(qx, fi)));
+#pragma unroll
+				for (int c = 0; c < P2G_KZ; c++) {
+					if (rz < 2 * c || rz > 2 * c + 3) continue;   // half-row outside node k0+c's support (warp-uniform)
+					const float wz = __fsub_rn(1.f, fabsf(__fsub_rn(qz, fk[c])));
+#pragma unroll
+					for (int bb = 0; bb < P2G_KY; bb++) {
+						if (ry < 2 * bb || ry > 2 * bb + 3) continue;
+						const float wy = __fsub_rn(1.f, fabsf(__fsub_rn(qy, fj[bb])));
+						const float w = __fmul_rn(__fmul_rn(wx, wy), wz);                                   // S3D.cpp:472-474
+						sum[c][bb] = __fadd_rn(sum[c][bb], __fmul_rn(w, u));
+						amt[c][bb] = __fadd_rn(amt[c][bb], w);
+					}
+				}
 			}
 		}
+	}
+	if (!lane_in) return;
 	const float tiny = 1.401298464324817e-45f;  // numeric_limits<float>::denorm_min(), S3D.cpp:540
-	grid[q] = __fdiv_rn(sum, __fadd_rn(tiny, amt));
-	cd[q] = amt > 0.01f ? 0 : FS3_INF_CD;  // S3D.cpp:565-575
+#pragma unroll
+	for (int c = 0; c < P2G_KZ; c++)
+#pragma unroll
+		for (int bb = 0; bb < P2G_KY; bb++) {
+			const int j = j0 + bb, k = k0 + c;
+			if (j >= ys || k >= kend) continue;
+			const size_t q = (size_t)i + (size_t)xs * ((size_t)j + (size_t)ys * k);
+			// wall planes: forced to zero and valid (S3D.cpp:578-599)
+			const int m_ax = AX == 0 ? i : (AX == 1 ? j : k), n_ax = AX == 0 ? d.nx : (AX == 1 ? d.ny : d.nz);
+			if (m_ax == 0 || m_ax == n_ax) { grid[q] = 0.f; cd[q] = 0; continue; }
+			grid[q] = __fdiv_rn(sum[c][bb], __fadd_rn(tiny, amt[c][bb]));
+			cd[q] = amt[c][bb] > 0.01f ? 0 : FS3_INF_CD;  // S3D.cpp:565-575
+		}
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -158,23 +196,93 @@ __global__ void __launch_bounds__(256) k_ex_scatter(const int* __restrict__ cd, 
 	}
 }
 
-__global__ void __launch_bounds__(256) k_ex_fill(float* __restrict__ g, const int* __restrict__ cd, const int* __restrict__ order, uint32_t b,
-                                                 uint32_t e, int xs, int ys, int zs) {
-	uint32_t t = b + blockIdx.x * blockDim.x + threadIdx.x;
-	if (t >= e) return;
-	int q = order[t];
-	int my = cd[q];
-	int x = q % xs, y = (q / xs) % ys, z = q / (xs * ys);
-	int sy = xs, sz = xs * ys;
+// All layers of up to three face grids in ONE persistent launch.  Layer d only reads layer d-1 (a node's closer
+// neighbours are exactly one step closer in L1 distance), so the layers are separated by a grid-wide barrier (arrive
+// counter in L2, one CTA per SM, all co-resident) instead of a kernel boundary, and the bucket starts never leave the
+// device.  Values of the previous layer are read with ld.cg (other SMs wrote them); cd[] is constant during the fill.
+struct ExGrid {
+	float* g;
+	const int* cd;
+	const int* order;
+	const uint32_t* start;   // nb+1 bucket starts
+	int xs, ys, zs, nb;
+};
+struct ExGrids { ExGrid a[3]; int n; };
+#define EX_THREADS 1024
+
+// which of the 6 neighbours (+x,-x,+y,-y,+z,-z, S3D.cpp:743) of node q are strictly closer: independent of the fill itself
+__device__ __forceinline__ int ex_closer_mask(const ExGrid& G, int q) {
+	const int* __restrict__ cd = G.cd;
+	const int my = __ldg(cd + q);
+	const int xs = G.xs, ys = G.ys, zs = G.zs;
+	const int x = q % xs, y = (q / xs) % ys, z = q / (xs * ys);
+	const int sy = xs, sz = xs * ys;
+	int m = 0;
+	if (x + 1 < xs && __ldg(cd + q + 1) < my) m |= 1;
+	if (x - 1 >= 0 && __ldg(cd + q - 1) < my) m |= 2;
+	if (y + 1 < ys && __ldg(cd + q + sy) < my) m |= 4;
+	if (y - 1 >= 0 && __ldg(cd + q - sy) < my) m |= 8;
+	if (z + 1 < zs && __ldg(cd + q + sz) < my) m |= 16;
+	if (z - 1 >= 0 && __ldg(cd + q - sz) < my) m |= 32;
+	return m;
+}
+__device__ __forceinline__ void ex_fill_node(const ExGrid& G, int q, int m) {
+	float* __restrict__ g = G.g;
+	const int sy = G.xs, sz = G.xs * G.ys;
+	// all loads first (one L2 round trip), then the reference's sequence of additions
+	const float v0 = (m & 1) ? __ldcg(g + q + 1) : 0.f, v1 = (m & 2) ? __ldcg(g + q - 1) : 0.f;
+	const float v2 = (m & 4) ? __ldcg(g + q + sy) : 0.f, v3 = (m & 8) ? __ldcg(g + q - sy) : 0.f;
+	const float v4 = (m & 16) ? __ldcg(g + q + sz) : 0.f, v5 = (m & 32) ? __ldcg(g + q - sz) : 0.f;
 	float cnt = 0.f, sum = 0.f;
-	// neighbour order +x,-x,+y,-y,+z,-z (S3D.cpp:743)
-	if (x + 1 < xs && cd[q + 1] < my) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, g[q + 1]); }
-	if (x - 1 >= 0 && cd[q - 1] < my) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, g[q - 1]); }
-	if (y + 1 < ys && cd[q + sy] < my) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, g[q + sy]); }
-	if (y - 1 >= 0 && cd[q - sy] < my) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, g[q - sy]); }
-	if (z + 1 < zs && cd[q + sz] < my) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, g[q + sz]); }
-	if (z - 1 >= 0 && cd[q - sz] < my) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, g[q - sz]); }
-	g[q] = __fdiv_rn(sum, cnt);
+	if (m & 1) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, v0); }
+	if (m & 2) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, v1); }
+	if (m & 4) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, v2); }
+	if (m & 8) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, v3); }
+	if (m & 16) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, v4); }
+	if (m & 32) { cnt = __fadd_rn(cnt, 1.f); sum = __fadd_rn(sum, v5); }
+	__stcg(g + q, __fdiv_rn(sum, cnt));
+}
+
+__global__ void __launch_bounds__(EX_THREADS, 1) k_ex_fill_layers(ExGrids P, uint32_t* __restrict__ arrive) {
+	const uint32_t tid = blockIdx.x * EX_THREADS + threadIdx.x, nthr = gridDim.x * EX_THREADS;
+	uint32_t tot[3], b[3], e[3];
+	int pq[3], pm[3];   // this thread's first node of the coming layer and its closer-mask, fetched BEFORE the barrier
+#pragma unroll
+	for (int k = 0; k < 3; k++) {
+		tot[k] = k < P.n ? __ldg(P.a[k].start + P.a[k].nb) : 0u;
+		b[k] = k < P.n ? __ldg(P.a[k].start + 1) : 0u;
+		e[k] = (k < P.n && 1 < P.a[k].nb) ? __ldg(P.a[k].start + 2) : b[k];
+		pq[k] = -1; pm[k] = 0;
+		if (k < P.n && b[k] + tid < e[k]) { pq[k] = __ldg(P.a[k].order + b[k] + tid); pm[k] = ex_closer_mask(P.a[k], pq[k]); }
+	}
+	for (int d = 1;; d++) {
+		bool more = false;
+#pragma unroll
+		for (int k = 0; k < 3; k++) {
+			if (k >= P.n) continue;
+			more |= e[k] < tot[k];
+			if (pq[k] >= 0) ex_fill_node(P.a[k], pq[k], pm[k]);
+			for (uint32_t t = b[k] + tid + nthr; t < e[k]; t += nthr) { const int q = __ldg(P.a[k].order + t); ex_fill_node(P.a[k], q, ex_closer_mask(P.a[k], q)); }
+		}
+		if (!more) break;   // grid-uniform: every CTA reads the same starts
+#pragma unroll
+		for (int k = 0; k < 3; k++) {
+			b[k] = e[k];
+			e[k] = (k < P.n && d + 1 < P.a[k].nb) ? __ldg(P.a[k].start + d + 2) : b[k];
+			pq[k] = -1;
+			if (k < P.n && b[k] + tid < e[k]) { pq[k] = __ldg(P.a[k].order + b[k] + tid); pm[k] = ex_closer_mask(P.a[k], pq[k]); }
+		}
+		// ---- grid barrier d ----
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			__threadfence();
+			atomicAdd(arrive, 1u);
+			const uint32_t need = (uint32_t)d * gridDim.x;
+			uint32_t v;
+			do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(arrive) : "memory"); } while (v < need);
+		}
+		__syncthreads();
+	}
 }
 
 int fs3i_cd_from_valid(fs3_sim* s, const unsigned char* dev_valid, size_t n) {
@@ -200,31 +308,37 @@ int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs) {
 	int hb = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
 	k_ex_hist<<<hb, 256, nb * sizeof(uint32_t), s->stream>>>(cd, n, hist, nb); FS3_LAUNCH_CHECK();
 	k_ex_scan<<<1, 32, 0, s->stream>>>(hist, start, cursor, nb); FS3_LAUNCH_CHECK();
-	FS3_CUDA(cudaMemcpyAsync(s->h_bucket + (size_t)slot * (s->bucket_cap + 1), start, sizeof(uint32_t) * (nb + 1), cudaMemcpyDeviceToHost, s->stream));
 	size_t chunk = 8192;
 	k_ex_scatter<<<cdiv((long long)n, (long long)chunk), 256, 2 * nb * sizeof(uint32_t), s->stream>>>(cd, n, start, cursor, s->orderv[slot], nb, chunk);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 
-// Phase 2: layer-by-layer fill.  Needs the bucket starts on the host (caller synchronised the stream).
-int fs3i_extrap_fill(fs3_sim* s, int slot, float* grid, int xs, int ys, int zs) {
-	int nb = xs + ys + zs + 1;
-	const uint32_t* hb = s->h_bucket + (size_t)slot * (s->bucket_cap + 1);
-	for (int dd = 1; dd < nb; dd++) {
-		uint32_t b = hb[dd], e = hb[dd + 1];
-		if (e > b) {
-			k_ex_fill<<<cdiv((long long)(e - b), 256), 256, 0, s->stream>>>(grid, s->cdv[slot], s->orderv[slot], b, e, xs, ys, zs);
-			FS3_LAUNCH_CHECK();
-		}
+// Phase 2: the layered fill of `count` face grids (slots 0..count-1) in one persistent launch.
+static int extrap_fill_layers(fs3_sim* s, int count, float* const* grids, const int (*dims)[3]) {
+	ExGrids P;
+	P.n = count;
+	for (int k = 0; k < count; k++) {
+		const uint32_t* base = s->bucket + (size_t)k * (3 * (size_t)s->bucket_cap + 2);
+		P.a[k] = ExGrid{grids[k], s->cdv[k], s->orderv[k], base + s->bucket_cap, dims[k][0], dims[k][1], dims[k][2], dims[k][0] + dims[k][1] + dims[k][2] + 1};
 	}
+	for (int k = count; k < 3; k++) P.a[k] = P.a[0];
+	FS3_CUDA(cudaMemsetAsync(s->ex_arrive, 0, sizeof(uint32_t), s->stream));
+	// one CTA per SM: all co-resident (the barrier needs that), 1024 threads each
+	k_ex_fill_layers<<<s->sm_count, EX_THREADS, 0, s->stream>>>(P, s->ex_arrive); FS3_LAUNCH_CHECK();
 	return FS3_OK;
+}
+
+int fs3i_extrap_fill(fs3_sim* s, int slot, float* grid, int xs, int ys, int zs) {
+	if (slot != 0) { s->err = "single-grid fill uses slot 0"; return FS3_ERR_INVALID; }
+	float* g[1] = {grid};
+	const int dims[1][3] = {{xs, ys, zs}};
+	return extrap_fill_layers(s, 1, g, dims);
 }
 
 int fs3i_extrapolate(fs3_sim* s, float* grid, int xs, int ys, int zs) {
 	int rc = fs3i_extrap_prepare(s, 0, xs, ys, zs);
 	if (rc) return rc;
-	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	return fs3i_extrap_fill(s, 0, grid, xs, ys, zs);
 }
 
@@ -235,18 +349,21 @@ void fs3i_p2g_range(const fs3_sim* s, int ax, size_t* q0, size_t* q1) {
 	*q1 = plane * (s->z1 + ((ax == 2 && s->rank == s->world - 1) ? 1 : 0));
 }
 
-int fs3i_p2g_gather(fs3_sim* s) {
+template <int AX> static int p2g_launch(fs3_sim* s, float* grid, int* cd) {
 	GridDims d{s->nx, s->ny, s->nz};
-	const float4 *pos = s->pos[s->cur], *vel = s->vel[s->cur];
+	const int xs = s->nx + (AX == 0), ys = s->ny + (AX == 1);
+	const int kbeg = s->z0, kend = s->z1 + ((AX == 2 && s->rank == s->world - 1) ? 1 : 0);
+	dim3 g(cdiv(xs, 32), cdiv(ys, 2 * P2G_KY), cdiv(kend - kbeg, 2 * P2G_KZ));
+	k_p2g_gather<AX><<<g, 128, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->cell_start, d, s->cpm, grid, cd, kbeg, kend);
+	FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
+int fs3i_p2g_gather(fs3_sim* s) {
 	// P2G writes the "old" set; the projected field is produced from it by fs3i_project (no copy, S3D.cpp:123-134)
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_P2G], s->stream);
-	size_t a, b;
-	fs3i_p2g_range(s, 0, &a, &b);
-	k_p2g_gather<0><<<cdiv((long long)(b - a), 128), 128, 0, s->stream>>>(pos, vel, s->cell_start, d, s->cpm, s->oU, s->cdv[0], a, b); FS3_LAUNCH_CHECK();
-	fs3i_p2g_range(s, 1, &a, &b);
-	k_p2g_gather<1><<<cdiv((long long)(b - a), 128), 128, 0, s->stream>>>(pos, vel, s->cell_start, d, s->cpm, s->oV, s->cdv[1], a, b); FS3_LAUNCH_CHECK();
-	fs3i_p2g_range(s, 2, &a, &b);
-	k_p2g_gather<2><<<cdiv((long long)(b - a), 128), 128, 0, s->stream>>>(pos, vel, s->cell_start, d, s->cpm, s->oW, s->cdv[2], a, b); FS3_LAUNCH_CHECK();
+	int rc;
+	if ((rc = p2g_launch<0>(s, s->oU, s->cdv[0])) || (rc = p2g_launch<1>(s, s->oV, s->cdv[1])) || (rc = p2g_launch<2>(s, s->oW, s->cdv[2]))) return rc;
 	return FS3_OK;
 }
 
@@ -266,10 +383,8 @@ int fs3i_extrapolate_all(fs3_sim* s) {
 		rc = fs3i_extrap_prepare(s, ax, d.nx + (ax == 0), d.ny + (ax == 1), d.nz + (ax == 2));
 		if (rc) return rc;
 	}
-	FS3_CUDA(cudaStreamSynchronize(s->stream));  // one host round trip per step: layer sizes shape the fill launches
-	for (int ax = 0; ax < 3; ax++) {
-		rc = fs3i_extrap_fill(s, ax, ax == 0 ? s->oU : (ax == 1 ? s->oV : s->oW), d.nx + (ax == 0), d.ny + (ax == 1), d.nz + (ax == 2));
-		if (rc) return rc;
-	}
+	float* g[3] = {s->oU, s->oV, s->oW};
+	const int dims[3][3] = {{d.nx + 1, d.ny, d.nz}, {d.nx, d.ny + 1, d.nz}, {d.nx, d.ny, d.nz + 1}};
+	if ((rc = extrap_fill_layers(s, 3, g, dims))) return rc;
 	return FS3_OK;
 }
