@@ -118,6 +118,8 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	if (shared_stream) { s->stream = shared_stream; s->owns_stream = false; }
 	else { CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)); s->owns_stream = true; }
 	for (int k = 0; k < FS3_T_COUNT + 2; k++) CK(cudaEventCreate(&s->ev[k]));
+	CK(cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking));
+	CK(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming)); CK(cudaEventCreate(&s->ev_ls_end));
 	if (world > 1) {
 		s->arena_bytes = fs3i_arena_bytes(nx, ptot, s->mig_cap, world);
 		CK(cudaMalloc((void**)&s->arena, s->arena_bytes));
@@ -264,6 +266,8 @@ int fs3_destroy(fs3_sim* s) {
 	if (!s) return FS3_OK;
 	cudaSetDevice(s->device);
 	if (s->stream) cudaStreamSynchronize(s->stream);
+	if (s->stream2) { cudaStreamSynchronize(s->stream2); cudaStreamDestroy(s->stream2); }
+	if (s->ev_fork) cudaEventDestroy(s->ev_fork); if (s->ev_join) cudaEventDestroy(s->ev_join); if (s->ev_ls_end) cudaEventDestroy(s->ev_ls_end);
 	if (s->arena) {
 		for (int r = 0; r < s->world; r++) if (!s->lockstep && r != s->rank && s->peer_base[r]) cudaIpcCloseMemHandle(s->peer_base[r]);
 		cudaFree(s->arena);
@@ -340,8 +344,14 @@ int fs3_step(fs3_sim* s, float dt) {
 	if ((rc = fs3i_advect(s, dt))) return rc;
 	if (T) cudaEventRecord(s->ev[FS3_T_BIN], s->stream);
 	if ((rc = fs3i_bin(s))) return rc;
-	if ((rc = fs3i_levelset(s))) return rc;            // records LEVELSET_SEED / LEVELSET_SWEEP
-	if ((rc = fs3i_p2g(s))) return rc;                 // records P2G / EXTRAPOLATE
+	if ((rc = fs3i_levelset_seed(s))) return rc;       // records LEVELSET_SEED
+	if ((rc = fs3i_p2g_gather(s))) return rc;          // records P2G
+	// two dependency-bound stages side by side: the 8 sweeps on stream2 (records LEVELSET_SWEEP there) and the layered
+	// extrapolation (records EXTRAPOLATE).  The issue-bound P2G gather is kept out of the overlap: it loses more than the
+	// sweeps gain when they share the SMs.
+	if ((rc = fs3i_levelset_fork(s))) return rc;
+	if ((rc = fs3i_extrapolate_all(s))) return rc;
+	if ((rc = fs3i_levelset_join(s))) return rc;
 	if ((rc = fs3i_project(s, dt, true, true))) return rc;  // records PROJECT_SETUP / SOR / TOVEL; gravity folded in
 	if (T) cudaEventRecord(s->ev[FS3_T_FLIP_APPLY], s->stream);
 	float alpha = flip_alpha(s, dt);
@@ -369,6 +379,13 @@ int fs3_stage_times(fs3_sim* s, float* ms, int cap) {
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	for (int k = 0; k < FS3_T_TOTAL; k++) FS3_CUDA(cudaEventElapsedTime(&ms[k], s->ev[k], s->ev[k + 1]));
 	FS3_CUDA(cudaEventElapsedTime(&ms[FS3_T_TOTAL], s->ev[0], s->ev[FS3_T_TOTAL]));
+	// the sweeps ran on stream2 concurrently with EXTRAPOLATE: their time is their own span (the stage times then add up
+	// to more than TOTAL), and the seed ends where P2G begins
+	if (s->ls_overlapped) {
+		FS3_CUDA(cudaEventElapsedTime(&ms[FS3_T_LEVELSET_SWEEP], s->ev[FS3_T_LEVELSET_SWEEP], s->ev_ls_end));
+		FS3_CUDA(cudaEventElapsedTime(&ms[FS3_T_LEVELSET_SEED], s->ev[FS3_T_LEVELSET_SEED], s->ev[FS3_T_P2G]));
+		FS3_CUDA(cudaEventElapsedTime(&ms[FS3_T_P2G], s->ev[FS3_T_P2G], s->ev[FS3_T_EXTRAPOLATE]));
+	}
 	return FS3_OK;
 }
 

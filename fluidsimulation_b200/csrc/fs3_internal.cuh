@@ -122,6 +122,11 @@ struct fs3_sim {
 	void* stage_ptr;           // device staging for AoS / hook transfers at the boundary
 	size_t stage_bytes;
 	cudaEvent_t ev[FS3_T_COUNT + 2];
+	// the 8 level-set sweeps are latency-bound and independent of P2G + extrapolation: inside a step they run on a second stream
+	cudaStream_t stream2;
+	cudaEvent_t ev_fork, ev_join, ev_ls_end;
+	bool ls_forked;          // sweeps of the current step are in flight on stream2
+	bool ls_overlapped;      // the last step's LEVELSET_SWEEP time is (ev[LEVELSET_SWEEP], ev_ls_end) on stream2
 	float stage_ms[FS3_T_COUNT];
 };
 
@@ -278,7 +283,9 @@ int fs3i_sor_half_launch(fs3_sim* s, int k);                                // h
 int fs3i_project_gradient(fs3_sim* s, float dt, bool from_old, bool with_gravity);
 // levelset.cu / p2g.cu pieces
 int fs3i_levelset_seed(fs3_sim* s);
-int fs3i_levelset_sweeps(fs3_sim* s);
+int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st = nullptr);                // st: stream to run on (default: the handle's)
+int fs3i_levelset_fork(fs3_sim* s);                                          // sweeps on stream2, after everything queued so far
+int fs3i_levelset_join(fs3_sim* s);                                          // main stream waits for them
 int fs3i_p2g_gather(fs3_sim* s);
 void fs3i_p2g_range(const fs3_sim* s, int ax, size_t* q0, size_t* q1);
 int fs3i_extrapolate_all(fs3_sim* s);

@@ -4,8 +4,8 @@
 // In the sweep with direction signs (sx,sy,sz) a cell only reads its three upwind neighbours, after
 // they were finalised in the same sweep, and its three offers stay in x,y,z order inside one thread.
 // Any schedule that respects that partial order gives the reference's result bit for bit, so the grid is
-// cut into 8x8x4 tiles that run as a dataflow (see k_ls_sweep_dataflow) and inside a tile the 18 cell
-// hyperplanes are walked by one warp with the tile + its upwind halo held in shared memory.
+// cut into 16x16x8 tiles that run as a dataflow (see k_ls_sweep_dataflow) and inside a tile the 38 cell
+// hyperplanes are walked by one 128-thread CTA with the tile + its upwind halo held in shared memory.
 // Each cell carries its closest particle as (n*X, n*Y, n*Z, id): the candidate's position travels with
 // the index, so the dependent chain contains no global gather, and phi is recomputed from it
 // (ptDistance is symmetric in its arguments, S3D.cpp:234-236).
@@ -45,34 +45,37 @@ __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos,
 	rec[c] = best;
 }
 
-// All 8 sweeps in ONE persistent launch, scheduled as a dataflow over 8x8x4 tiles, ONE WARP PER TILE.
+// All 8 sweeps in ONE persistent launch, scheduled as a dataflow over 16x16x8 tiles, ONE 128-THREAD CTA PER TILE.
 // Tiles are a fixed partition of physical space.  A work item is (sweep m, tile); the host orders all
 // 8*ntiles items by their earliest possible start level in the dependency DAG (fs3i_levelset_init), and
-// warps draw items through a ticket counter.  A warp that holds an item waits (polling per-tile
+// CTAs draw items through a ticket counter.  A CTA that holds an item waits (polling per-tile
 // completion epochs in L2) until
 //   * the tile itself and its 6 face neighbours have completed sweep m-1 (RAW on its own cells, WAR on
 //     the halo cells its neighbours read in sweep m-1), and
 //   * its 3 upwind neighbours have completed sweep m (RAW on the halo),
-// all of which hold lower tickets, so some running warp can always make progress (no co-residency
+// all of which hold lower tickets, so some running CTA can always make progress (no co-residency
 // assumption, no grid-wide barrier), and consecutive sweeps pipeline behind each other as far as the
-// DAG allows.  The sweep is latency-bound (the DAG is ~600 tiles deep at 256^3), so the tile is shaped
-// for the shortest serial chain: 32 x-lines of 8 cells, one line per lane, 18 cell hyperplanes walked
-// with only __syncwarp() between them; the tile and its three upwind halo faces sit in the warp's
-// private shared memory in SWEEP space (index 0 = most upwind) so that one code path serves all 8
-// directions.  Candidates are first compared by squared distance (sqrt and "- radius" are monotonic,
-// so a candidate that is not closer in d^2 can never win the reference's `dist < phi` test); the full
-// reference expression decides the rest.  Records move with cp.async.cg / st.cg (L2 only: L1 is not
-// coherent across SMs).  The last sweep also writes phi and closestParticles[].
-#define LS_TX 8
-#define LS_TY 8
-#define LS_TZ 4
-#define LS_PX (LS_TX + 2)   // x pitch 10: on a hyperplane a+b+c=s the 8 lanes of a quarter warp hit 8 different 16-byte bank groups (pitch 9 puts all 32 in one)
+// DAG allows.  The sweep is bound by its critical path: 8 n/tx + 4 n/ty + 2 n/tz tile hand-offs (x flips
+// between every pair of sweeps, y every second, z once), each costing a few L2 round trips (poll, halo
+// load, store, release) plus the tile's own tx+ty+tz-2 cell hyperplanes at one shared-memory round trip
+// each.  16x16x8 halves the number of hand-offs of a warp-sized 8x8x4 tile (256 vs 512 at 256^3) while a
+// hyperplane step still costs one barrier.  The tile and its three upwind halo faces sit in shared memory
+// in SWEEP space (index 0 = most upwind) so that one code path serves all 8 directions; 128 threads = the
+// 16x8 x-lines of the tile, thread (b,c) marching along a with hyperplane index s = a+b+c.  Candidates are
+// first compared by squared distance (sqrt and "- radius" are monotonic, so a candidate that is not
+// closer in d^2 can never win the reference's `dist < phi` test); the full reference expression decides
+// the rest.  Records move with cp.async.cg / st.cg (L2 only: L1 is not coherent across SMs).  The last
+// sweep also writes phi and closestParticles[].
+#define LS_TX 16
+#define LS_TY 16
+#define LS_TZ 8
+#define LS_PX (LS_TX + 2)   // x pitch 18 (even): on a hyperplane a+b+c=s the 8 lanes of a quarter warp (consecutive b) hit 8 different 16-byte bank groups
 #define LS_PY (LS_TY + 1)
 #define LS_PZ (LS_TZ + 1)
 #define LS_STEPS (LS_TX + LS_TY + LS_TZ - 2)
-#define LS_WARPS 8
-#define LS_SMEM_BYTES (LS_WARPS * LS_SM_PER_WARP * (sizeof(float4) + sizeof(float)))
-#define LS_SM_PER_WARP (LS_PX * LS_PY * LS_PZ)
+#define LS_THREADS (LS_TY * LS_TZ)
+#define LS_CELLS (LS_PX * LS_PY * LS_PZ)
+#define LS_SMEM_BYTES (LS_CELLS * (sizeof(float4) + sizeof(float)))
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
 	unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
@@ -86,14 +89,13 @@ __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
 }
 __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) { asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory"); }
 
-// false = gave up (another warp aborted, or ~2 s without progress: never hang the GPU)
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
 	uint32_t v;
 	asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
 	return v;
 }
-// Polls with relaxed loads and a capped exponential back-off (waiting warps share the SM with the warps
-// that are computing), then takes the acquire once the epoch is there.
+// Polls with relaxed loads and a capped exponential back-off, then takes the acquire once the epoch is there.
+// false = gave up (another CTA aborted, or ~2 s without progress: never hang the GPU)
 __device__ __forceinline__ bool ls_wait(const uint32_t* f, uint32_t need, int* flags, unsigned sleep_max) {
 	if ((int32_t)(ld_acquire_u32(f) - need) >= 0) return true;
 	long long t0 = clock64();
@@ -118,27 +120,28 @@ __device__ __forceinline__ float ls_d2(float cx, float cy, float cz, float4 q) {
 #ifdef FS3_LS_TRACE
 __device__ unsigned long long* g_ls_trace;   // 8 timestamps per work item (debug builds only, tools/ls_trace.py)
 __device__ __forceinline__ unsigned long long ls_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-#define LS_MARK(k) do { if (lane == 0) g_ls_trace[(size_t)t * 8 + (k)] = ls_now(); } while (0)
+#define LS_MARK(k) do { if (threadIdx.x == 0) g_ls_trace[(size_t)t * 8 + (k)] = ls_now(); } while (0)
 #else
 #define LS_MARK(k) do { } while (0)
 #endif
 
-__global__ void __launch_bounds__(32 * LS_WARPS) k_ls_sweep_dataflow(float4* __restrict__ rec, GridDims d, float radius,
-                                                                     const uint32_t* __restrict__ items, uint32_t* done, uint32_t* ticket,
-                                                                     uint32_t nitems, int ntx, int nty, int ntz, uint32_t epoch0,
-                                                                     int* __restrict__ flags, float* __restrict__ phi, int* __restrict__ closest, unsigned sleep_max) {
+__global__ void __launch_bounds__(LS_THREADS) k_ls_sweep_dataflow(float4* __restrict__ rec, GridDims d, float radius,
+                                                                   const uint32_t* __restrict__ items, uint32_t* done, uint32_t* ticket,
+                                                                   uint32_t nitems, int ntx, int nty, int ntz, uint32_t epoch0,
+                                                                   int* __restrict__ flags, float* __restrict__ phi, int* __restrict__ closest, unsigned sleep_max) {
 	extern __shared__ float4 ls_smem[];
-	const unsigned FULL = 0xffffffffu;
-	const int lane = threadIdx.x & 31;
-	float4* sm = ls_smem + (threadIdx.x >> 5) * LS_SM_PER_WARP;
-	float* m2s = reinterpret_cast<float*>(ls_smem + LS_WARPS * LS_SM_PER_WARP) + (threadIdx.x >> 5) * LS_SM_PER_WARP;
+	__shared__ uint32_t s_ticket;
+	float4* const sm = ls_smem;
+	float* const m2s = reinterpret_cast<float*>(ls_smem + LS_CELLS);
+	const int tid = threadIdx.x;
 #define SMI(a, b, c) (((a) + 1) + LS_PX * (((b) + 1) + LS_PY * ((c) + 1)))
 	const float4 none = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
 	const size_t sY = (size_t)d.nx, sZ = (size_t)d.nx * d.ny;
 	for (;;) {
-		uint32_t t = 0;
-		if (lane == 0) t = atomicAdd(ticket, 1u);
-		t = __shfl_sync(FULL, t, 0);
+		__syncthreads();   // the previous item's shared memory is no longer read
+		if (tid == 0) s_ticket = atomicAdd(ticket, 1u);
+		__syncthreads();
+		const uint32_t t = s_ticket;
 		if (t >= nitems) break;
 		LS_MARK(0);
 		const uint32_t it = __ldg(items + t);
@@ -150,103 +153,99 @@ __global__ void __launch_bounds__(32 * LS_WARPS) k_ls_sweep_dataflow(float4* __r
 		uint32_t* const mydone = done + ((size_t)Tx + (size_t)ntx * ((size_t)Ty + (size_t)nty * Tz));
 		// ---- own cells are final once this tile has completed sweep m-1: start their copy first ----------
 		bool ok = true;
-		if (lane == 0) ok = ls_wait(mydone, E - 1u, flags, sleep_max);
-		if (!__all_sync(FULL, ok)) break;
+		if (tid == 0) ok = ls_wait(mydone, E - 1u, flags, sleep_max);
+		if (!__syncthreads_and(ok)) break;
 		LS_MARK(1);
-		{
-			const int px = lane & 7;
-			const int a = (px < wx && dx < 0) ? wx - 1 - px : px;
 #pragma unroll
-			for (int i = 0; i < LS_TY * LS_TZ / 4; i++) {
-				const int row = (lane >> 3) + 4 * i, py = row & 7, pz = row >> 3;
-				const int b = (py < wy && dy < 0) ? wy - 1 - py : py, c = (pz < wz && dz < 0) ? wz - 1 - pz : pz;
-				if (px < wx && py < wy && pz < wz) cp_async16(sm + SMI(a, b, c), rec + ((size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)(z0 + pz)));
-				else sm[SMI(a, b, c)] = none;
-			}
+		for (int i = 0; i < LS_TX * LS_TY * LS_TZ / LS_THREADS; i++) {
+			const int e = tid + LS_THREADS * i, px = e % LS_TX, py = (e / LS_TX) % LS_TY, pz = e / (LS_TX * LS_TY);
+			const int a = (px < wx && dx < 0) ? wx - 1 - px : px, b = (py < wy && dy < 0) ? wy - 1 - py : py, c = (pz < wz && dz < 0) ? wz - 1 - pz : pz;
+			if (px < wx && py < wy && pz < wz) cp_async16(sm + SMI(a, b, c), rec + ((size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)(z0 + pz)));
+			else sm[SMI(a, b, c)] = none;
 		}
 		// ---- the six neighbours: upwind ones must have finished THIS sweep, the others the previous one ---
-		if (lane >= 1 && lane <= 6) {
-			const int ax = (lane - 1) >> 1, sgn = (lane & 1) ? -1 : 1;   // lanes 1,2: x-,x+   3,4: y-,y+   5,6: z-,z+
+		if (tid >= 1 && tid <= 6) {
+			const int ax = (tid - 1) >> 1, sgn = (tid & 1) ? -1 : 1;   // threads 1,2: x-,x+   3,4: y-,y+   5,6: z-,z+
 			const int qx = Tx + (ax == 0 ? sgn : 0), qy = Ty + (ax == 1 ? sgn : 0), qz = Tz + (ax == 2 ? sgn : 0);
 			const int dir = ax == 0 ? dx : (ax == 1 ? dy : dz);
 			if (qx >= 0 && qx < ntx && qy >= 0 && qy < nty && qz >= 0 && qz < ntz)
 				ok = ls_wait(done + ((size_t)qx + (size_t)ntx * ((size_t)qy + (size_t)nty * qz)), sgn == -dir ? E : E - 1u, flags, sleep_max);
 		}
-		if (!__all_sync(FULL, ok)) break;
+		if (!__syncthreads_and(ok)) break;
 		LS_MARK(2);
 		// ---- three upwind halo faces (sweep coordinate -1 on one axis) ---------------------------------------
 		{
-			// x face: (b, c) = 8 x 4 cells, one per lane
-			const int b = lane & 7, c = lane >> 3;
+			// x face: (b, c) = 16 x 8 cells, one per thread
+			const int b = tid % LS_TY, c = tid / LS_TY;
 			const int qx = dx > 0 ? x0 - 1 : x0 + wx, qy = y0 + (dy > 0 ? b : wy - 1 - b), qz = z0 + (dz > 0 ? c : wz - 1 - c);
 			if (b < wy && c < wz && qx >= 0 && qx < d.nx) cp_async16(sm + SMI(-1, b, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
 			else sm[SMI(-1, b, c)] = none;
 		}
 		{
-			// y face: (a, c) = 8 x 4 cells, one per lane
-			const int a = lane & 7, c = lane >> 3;
+			// y face: (a, c) = 16 x 8 cells, one per thread
+			const int a = tid % LS_TX, c = tid / LS_TX;
 			const int qx = x0 + (dx > 0 ? a : wx - 1 - a), qy = dy > 0 ? y0 - 1 : y0 + wy, qz = z0 + (dz > 0 ? c : wz - 1 - c);
 			if (a < wx && c < wz && qy >= 0 && qy < d.ny) cp_async16(sm + SMI(a, -1, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
 			else sm[SMI(a, -1, c)] = none;
 		}
 #pragma unroll
-		for (int i = 0; i < 2; i++) {
-			// z face: (a, b) = 8 x 8 cells, two per lane
-			const int a = lane & 7, b = (lane >> 3) + 4 * i;
+		for (int i = 0; i < LS_TX * LS_TY / LS_THREADS; i++) {
+			// z face: (a, b) = 16 x 16 cells, two per thread
+			const int e = tid + LS_THREADS * i, a = e % LS_TX, b = e / LS_TX;
 			const int qx = x0 + (dx > 0 ? a : wx - 1 - a), qy = y0 + (dy > 0 ? b : wy - 1 - b), qz = dz > 0 ? z0 - 1 : z0 + wz;
 			if (a < wx && b < wy && qz >= 0 && qz < d.nz) cp_async16(sm + SMI(a, b, -1), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
 			else sm[SMI(a, b, -1)] = none;
 		}
 		cp_async_wait_all();
-		__syncwarp();
+		__syncthreads();
 		LS_MARK(3);
-		// ---- 18 cell hyperplanes; lane = line (b, c), marching along a ---------------------------------------
-		// Branch-free on the hot path: every lane runs every step on addresses that stay inside the warp's own
-		// shared-memory region (inactive lanes compute garbage and store nothing).
+		// ---- the cell hyperplanes; thread = line (b, c), marching along a ------------------------------------
+		// Branch-free on the hot path: every thread runs every step on addresses that stay inside the CTA's
+		// shared memory (inactive threads compute garbage and store nothing).
 		{
-			const int b = lane & 7, c = lane >> 3;
+			const int b = tid % LS_TY, c = tid / LS_TY;
 			const bool line_in = b < wy && c < wz;
 			const int gy = y0 + (dy > 0 ? b : wy - 1 - b), gz = z0 + (dz > 0 ? c : wz - 1 - c);
 			const float cyf = (float)gy, czf = (float)gz;
 			const int li = SMI(0, b, c);
 			const int gx0 = dx > 0 ? x0 : x0 + wx - 1;
 			float4* const grow = rec + (sY * (size_t)gy + sZ * (size_t)gz);
-			// squared distance of every own cell to its current record (off the dependent chain)
-			// Quiet-tile test, fully parallel (no dependent chain): if no cell would accept any of its three
-			// upwind candidates as they stand BEFORE the sweep (q2 < m2 is necessary for acceptance), then by
-			// induction along the sweep order the Gauss-Seidel pass changes nothing and the 18 steps are skipped.
+			// squared distance of every own cell to its current record (off the dependent chain), and the
+			// quiet-tile test, fully parallel: if no cell would accept any of its three upwind candidates as they
+			// stand BEFORE the sweep (q2 < m2 is necessary for acceptance), then by induction along the sweep
+			// order the Gauss-Seidel pass changes nothing and the hyperplane steps are skipped.
 			bool maybe = false;
 			{
-				float4 r8[LS_TX + 1];
-#pragma unroll
-				for (int a = -1; a < LS_TX; a++) r8[a + 1] = sm[li + a];
+				float4 prev = sm[li - 1];
 #pragma unroll
 				for (int a = 0; a < LS_TX; a++) {
 					const float cxf = (float)(gx0 + dx * a);
-					const float4 Y = sm[li + a - LS_PX], Z = sm[li + a - LS_PX * LS_PY];
-					const float m2 = ls_d2(cxf, cyf, czf, r8[a + 1]);
+					const float4 cur = sm[li + a], Y = sm[li + a - LS_PX], Z = sm[li + a - LS_PX * LS_PY];
+					const float m2 = ls_d2(cxf, cyf, czf, cur);
 					m2s[li + a] = m2;
-					const int myid = __float_as_int(r8[a + 1].w), idX = __float_as_int(r8[a].w), idY = __float_as_int(Y.w), idZ = __float_as_int(Z.w);
-					const bool wX = idX > 0 && idX != myid && (myid < 0 || ls_d2(cxf, cyf, czf, r8[a]) < m2);
+					const int myid = __float_as_int(cur.w), idX = __float_as_int(prev.w), idY = __float_as_int(Y.w), idZ = __float_as_int(Z.w);
+					const bool wX = idX > 0 && idX != myid && (myid < 0 || ls_d2(cxf, cyf, czf, prev) < m2);
 					const bool wY = idY > 0 && idY != myid && (myid < 0 || ls_d2(cxf, cyf, czf, Y) < m2);
 					const bool wZ = idZ > 0 && idZ != myid && (myid < 0 || ls_d2(cxf, cyf, czf, Z) < m2);
 					maybe |= (a < wx) && (wX || wY || wZ);
+					prev = cur;
 				}
 			}
-			const bool quiet = !__any_sync(FULL, maybe && line_in);   // (also orders the m2s stores before the loop)
+			const bool quiet = !__syncthreads_or(maybe && line_in);   // (also orders the m2s stores before the loop)
 #ifdef FS3_LS_TRACE
-			if (lane == 0 && quiet) g_ls_trace[(size_t)t * 8 + 6] = 1;
+			if (tid == 0 && quiet) g_ls_trace[(size_t)t * 8 + 6] = 1;
 #endif
 			uint32_t chg = 0;
-			for (int s = 0; s < (quiet ? 0 : LS_STEPS); s++) {
+			const int nsteps = quiet ? 0 : wx + wy + wz - 2;
+			for (int s = 0; s < nsteps; s++) {
 				const int a = s - b - c;
 				const bool act = line_in && (unsigned)a < (unsigned)wx;
-				const float4* q = sm + li + a;
+				const int ac = min(max(a, 0), LS_TX - 1);   // clamped: idle threads read (and discard) a cell of their own line
+				const float4* q = sm + li + ac;
 				float4 mine = q[0];
 				const float4 X = q[-1], Y = q[-LS_PX], Z = q[-LS_PX * LS_PY];
-				float m2 = m2s[li + a];
-				const int gx = gx0 + dx * a;
-				const float cxf = (float)gx;
+				float m2 = m2s[li + ac];
+				const float cxf = (float)(gx0 + dx * ac);
 				int myid = __float_as_int(mine.w);
 				const int idX = __float_as_int(X.w), idY = __float_as_int(Y.w), idZ = __float_as_int(Z.w);
 				const float x2 = ls_d2(cxf, cyf, czf, X), y2 = ls_d2(cxf, cyf, czf, Y), z2 = ls_d2(cxf, cyf, czf, Z);
@@ -269,32 +268,33 @@ __global__ void __launch_bounds__(32 * LS_WARPS) k_ls_sweep_dataflow(float4* __r
 				LS_TRY(Y, idY, y2)
 				LS_TRY(Z, idZ, z2)
 #undef LS_TRY
-				// global write-back is deferred past the loop: __syncwarp() orders memory, so a store in flight
-				// would put an L2 round trip into every step
+				// global write-back is deferred past the loop: a store in flight would put an L2 round trip into every step
 				if (act && changed) { sm[li + a] = mine; m2s[li + a] = m2; chg |= 1u << a; }
-				__syncwarp();
+				__syncthreads();
 			}
 #pragma unroll
 			for (int a = 0; a < LS_TX; a++)
 				if ((chg >> a) & 1u) __stcg(grow + (gx0 + dx * a), sm[li + a]);
-			if (m == 7 && line_in) {
-				// cells never reached keep their previous phi, as in the reference where m_Phi is only written
-				// together with closestParticles (S3D.cpp:248-251,296-299)
-				const size_t g0 = sY * (size_t)gy + sZ * (size_t)gz;
+		}
+		if (m == 7) {
+			// cells never reached keep their previous phi, as in the reference where m_Phi is only written
+			// together with closestParticles (S3D.cpp:248-251,296-299).  x fastest: coalesced stores.
 #pragma unroll
-				for (int a = 0; a < LS_TX; a++) {
-					if (a < wx) {
-						const int id = __float_as_int(sm[li + a].w);
-						const size_t gi = g0 + (size_t)(gx0 + dx * a);
-						closest[gi] = id;
-						if (id >= 0) phi[gi] = __fsub_rn(sqrtf(m2s[li + a]), radius);
-					}
+			for (int i = 0; i < LS_TX * LS_TY * LS_TZ / LS_THREADS; i++) {
+				const int e = tid + LS_THREADS * i, px = e % LS_TX, py = (e / LS_TX) % LS_TY, pz = e / (LS_TX * LS_TY);
+				if (px < wx && py < wy && pz < wz) {
+					const int a = dx < 0 ? wx - 1 - px : px, b = dy < 0 ? wy - 1 - py : py, c = dz < 0 ? wz - 1 - pz : pz;
+					const int id = __float_as_int(sm[SMI(a, b, c)].w);
+					const size_t gi = (size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)(z0 + pz);
+					closest[gi] = id;
+					if (id >= 0) phi[gi] = __fsub_rn(sqrtf(m2s[SMI(a, b, c)]), radius);
 				}
 			}
 		}
-		// ---- publish: the warp's stores, then the epoch (release is cumulative over the barrier) -----------
+		// ---- publish: the CTA's stores, then the epoch (release is cumulative over the barrier) ------------
 		LS_MARK(4);
-		if (lane == 0) st_release_u32(mydone, E);
+		__syncthreads();
+		if (tid == 0) { __threadfence(); st_release_u32(mydone, E); }
 		LS_MARK(5);
 	}
 #undef SMI
@@ -314,23 +314,25 @@ int fs3i_levelset(fs3_sim* s) {
 	int rc = fs3i_bin(s);
 	if (rc) return rc;
 	if ((rc = fs3i_levelset_seed(s))) return rc;
+	s->ls_overlapped = false;
 	return fs3i_levelset_sweeps(s);
 }
 
 // the 8 sweeps over the WHOLE grid (a sharded handle runs them replicated on the gathered seed records)
-int fs3i_levelset_sweeps(fs3_sim* s) {
+int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st) {
 	GridDims d{s->nx, s->ny, s->nz};
 	float radius = s->prm.particle_radius;
-	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SWEEP], s->stream);
+	if (!st) st = s->stream;
+	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SWEEP], st);
 	int ntx = cdiv(d.nx, LS_TX), nty = cdiv(d.ny, LS_TY), ntz = cdiv(d.nz, LS_TZ);
-	FS3_CUDA(cudaMemsetAsync(s->ls_ticket, 0, sizeof(uint32_t), s->stream));
+	FS3_CUDA(cudaMemsetAsync(s->ls_ticket, 0, sizeof(uint32_t), st));
 #ifdef FS3_LS_TRACE
 	static unsigned long long* trace_dev = nullptr;
 	const size_t trace_n = (size_t)8 * s->ls_ntiles * 8;
 	if (!trace_dev) { FS3_CUDA(cudaMalloc((void**)&trace_dev, trace_n * 8)); FS3_CUDA(cudaMemcpyToSymbol(g_ls_trace, &trace_dev, sizeof(trace_dev))); }
-	FS3_CUDA(cudaMemsetAsync(trace_dev, 0, trace_n * 8, s->stream));
+	FS3_CUDA(cudaMemsetAsync(trace_dev, 0, trace_n * 8, st));
 #endif
-	k_ls_sweep_dataflow<<<s->ls_blocks, 32 * LS_WARPS, LS_SMEM_BYTES, s->stream>>>(
+	k_ls_sweep_dataflow<<<s->ls_blocks, LS_THREADS, LS_SMEM_BYTES, st>>>(
 	    s->ls_rec, d, radius, s->ls_order, s->ls_done, s->ls_ticket, 8u * (uint32_t)s->ls_ntiles, ntx, nty, ntz, s->ls_epoch, s->dev_flags, s->phi,
 	    s->closest, (unsigned)s->ls_sleep_ns);
 	FS3_LAUNCH_CHECK();
@@ -340,12 +342,32 @@ int fs3i_levelset_sweeps(fs3_sim* s) {
 	if (const char* path = getenv("FS3_LS_TRACE_FILE")) {
 		std::vector<unsigned long long> h(trace_n);
 		std::vector<uint32_t> ord((size_t)8 * s->ls_ntiles);
-		FS3_CUDA(cudaStreamSynchronize(s->stream));
+		FS3_CUDA(cudaStreamSynchronize(st));
 		FS3_CUDA(cudaMemcpy(h.data(), trace_dev, trace_n * 8, cudaMemcpyDeviceToHost));
 		FS3_CUDA(cudaMemcpy(ord.data(), s->ls_order, ord.size() * 4, cudaMemcpyDeviceToHost));
 		if (FILE* fp = fopen(path, "wb")) { fwrite(h.data(), 8, trace_n, fp); fwrite(ord.data(), 4, ord.size(), fp); fclose(fp); }
 	}
 #endif
+	return FS3_OK;
+}
+
+// The sweeps only touch ls_rec / phi / closest, which nothing else reads before the pressure system is set up: inside a step
+// they overlap the P2G gather and the extrapolation (both bandwidth / issue bound, while the sweeps wait on tile dependencies).
+int fs3i_levelset_fork(fs3_sim* s) {
+	FS3_CUDA(cudaEventRecord(s->ev_fork, s->stream));
+	FS3_CUDA(cudaStreamWaitEvent(s->stream2, s->ev_fork, 0));
+	int rc = fs3i_levelset_sweeps(s, s->stream2);
+	if (rc) return rc;
+	if (s->prm.record_stage_times) cudaEventRecord(s->ev_ls_end, s->stream2);
+	FS3_CUDA(cudaEventRecord(s->ev_join, s->stream2));
+	s->ls_forked = true;
+	s->ls_overlapped = true;
+	return FS3_OK;
+}
+int fs3i_levelset_join(fs3_sim* s) {
+	if (!s->ls_forked) return FS3_OK;
+	FS3_CUDA(cudaStreamWaitEvent(s->stream, s->ev_join, 0));
+	s->ls_forked = false;
 	return FS3_OK;
 }
 
@@ -404,16 +426,15 @@ int fs3i_levelset_init(fs3_sim* s) {
 	int per_sm = 0, sms = 0;
 	const size_t smem = LS_SMEM_BYTES;
 	FS3_CUDA(cudaFuncSetAttribute(k_ls_sweep_dataflow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ls_sweep_dataflow, 32 * LS_WARPS, smem));
+	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ls_sweep_dataflow, LS_THREADS, smem));
 	FS3_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
-	// Two blocks (16 warps) per SM measured best at 256^3: more resident warps only add pollers that compete
-	// with the computing warps for issue slots.  Tunables (debug): FS3_LS_BLOCKS_PER_SM, FS3_LS_SLEEP_NS.
-	const int occ = std::max(1, per_sm);   // never more than can be co-resident: waiting warps must not block ticket holders
-	per_sm = std::min(occ, 2);
+	// Resident CTAs beyond what the DAG can keep busy only add pollers.  Tunables (debug): FS3_LS_BLOCKS_PER_SM, FS3_LS_SLEEP_NS.
+	const int occ = std::max(1, per_sm);
+	per_sm = std::min(occ, 3);
 	if (const char* e = getenv("FS3_LS_BLOCKS_PER_SM")) per_sm = std::min(occ, std::max(1, atoi(e)));
 	s->ls_sleep_ns = 256;
 	if (const char* e = getenv("FS3_LS_SLEEP_NS")) s->ls_sleep_ns = std::max(20, atoi(e));
 	long long blocks = (long long)std::max(1, per_sm) * sms;
-	s->ls_blocks = (int)std::min<long long>(blocks, (8LL * nt + LS_WARPS - 1) / LS_WARPS);
+	s->ls_blocks = (int)std::min<long long>(blocks, 8LL * nt);
 	return FS3_OK;
 }

@@ -208,7 +208,7 @@ struct ExGrid {
 	int xs, ys, zs, nb;
 };
 struct ExGrids { ExGrid a[3]; int n; };
-#define EX_THREADS 1024
+#define EX_THREADS 512
 
 // which of the 6 neighbours (+x,-x,+y,-y,+z,-z, S3D.cpp:743) of node q are strictly closer: independent of the fill itself
 __device__ __forceinline__ int ex_closer_mask(const ExGrid& G, int q) {
@@ -243,7 +243,7 @@ __device__ __forceinline__ void ex_fill_node(const ExGrid& G, int q, int m) {
 	__stcg(g + q, __fdiv_rn(sum, cnt));
 }
 
-__global__ void __launch_bounds__(EX_THREADS, 1) k_ex_fill_layers(ExGrids P, uint32_t* __restrict__ arrive) {
+__global__ void __launch_bounds__(EX_THREADS, 3) k_ex_fill_layers(ExGrids P, uint32_t* __restrict__ arrive) {
 	const uint32_t tid = blockIdx.x * EX_THREADS + threadIdx.x, nthr = gridDim.x * EX_THREADS;
 	uint32_t tot[3], b[3], e[3];
 	int pq[3], pm[3];   // this thread's first node of the coming layer and its closer-mask, fetched BEFORE the barrier
@@ -324,7 +324,8 @@ static int extrap_fill_layers(fs3_sim* s, int count, float* const* grids, const 
 	}
 	for (int k = count; k < 3; k++) P.a[k] = P.a[0];
 	FS3_CUDA(cudaMemsetAsync(s->ex_arrive, 0, sizeof(uint32_t), s->stream));
-	// one CTA per SM: all co-resident (the barrier needs that), 1024 threads each
+	// one CTA per SM, all co-resident (the barrier needs that); 512 threads x <= 40 registers so that a CTA fits beside the two
+	// resident CTAs of the level-set sweep running on stream2
 	k_ex_fill_layers<<<s->sm_count, EX_THREADS, 0, s->stream>>>(P, s->ex_arrive); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }

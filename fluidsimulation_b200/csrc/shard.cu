@@ -246,8 +246,8 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 		if ((rc = push_planes(s, s->ls_rec, pC, sizeof(float4), s->z0, s->z1))) return rc;
 		return fs3i_signal(s);
 	}
-	if (ph == 4) {          // 8 sweeps (replicated); P2G of the slab's face nodes, gathered on every rank
-		if ((rc = fs3i_wait(s)) || (rc = fs3i_levelset_sweeps(s)) || (rc = fs3i_p2g_gather(s))) return rc;
+	if (ph == 4) {          // P2G of the slab's face nodes, gathered on every rank
+		if ((rc = fs3i_p2g_gather(s))) return rc;   // no wait: the gather reads this rank's particles + ghost layers only
 		const int zw = s->z1 + (last ? 1 : 0);
 		if ((rc = push_planes(s, s->oU, pU, 4, s->z0, s->z1)) || (rc = push_planes(s, s->oV, pV, 4, s->z0, s->z1)) ||
 		    (rc = push_planes(s, s->oW, pW, 4, s->z0, zw)) || (rc = push_planes(s, s->cdv[0], pU, 4, s->z0, s->z1)) ||
@@ -255,8 +255,10 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 			return rc;
 		return fs3i_signal(s);
 	}
-	if (ph == 5) {          // extrapolation (replicated); pressure system of the slab; tell the neighbours it is set up
-		if ((rc = fs3i_wait(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_project_setup(s, dt, true, true)) || (rc = fs3i_sor_prepare(s))) return rc;
+	if (ph == 5) {          // 8 sweeps on stream2 beside the extrapolation (both replicated); pressure system of the slab; tell the neighbours it is set up
+		if ((rc = fs3i_wait(s)) || (rc = fs3i_levelset_fork(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_levelset_join(s)) || (rc = fs3i_project_setup(s, dt, true, true)) ||
+		    (rc = fs3i_sor_prepare(s)))
+			return rc;
 		if ((rc = fs3i_sor_signal(s))) return rc;
 		if (T) cudaEventRecord(s->ev[FS3_T_PROJECT_SOR], s->stream);
 		return FS3_OK;

@@ -18,7 +18,7 @@ s.sync()
 os.environ["FS3_LS_TRACE_FILE"] = out
 s.Simulate(0.01)
 s.sync()
-nt = ((n + 7) // 8) ** 2 * ((n + 3) // 4)
+nt = ((n + 15) // 16) ** 2 * ((n + 7) // 8)   # LS_TX x LS_TY x LS_TZ = 16 x 16 x 8 tiles
 raw = np.fromfile(out, np.uint8)
 tr = raw[:8 * nt * 8 * 8].view(np.uint64).reshape(-1, 8).astype(np.int64)
 quiet = tr[:, 6].copy()
@@ -33,7 +33,12 @@ print("items %d, span %.3f ms" % (tr.shape[0], (tr[:, 5].max()) / 1e6))
 for k, nm in enumerate(names):
     print("%-22s mean %8.2f us  median %8.2f  p90 %8.2f  max %8.2f" % (nm, d[:, k].mean(), np.median(d[:, k]), np.percentile(d[:, k], 90), d[:, k].max()))
 busy = (tr[:, 5] - tr[:, 2]) / 1e3
-print("busy (deps ready -> published): mean %.2f us; sum/warps = %.3f ms" % (busy.mean(), busy.sum() / 1e3 / (148 * 24)))
+print("busy (deps ready -> published): mean %.2f us; sum/CTAs = %.3f ms" % (busy.mean(), busy.sum() / 1e3 / (148 * 3)))
 # progress: completion time by ticket decile
 q = np.linspace(0, tr.shape[0] - 1, 11).astype(int)
 print("publish time (ms) at ticket deciles:", np.round(tr[q, 5] / 1e6, 3))
+for nm, sel in (("quiet", quiet == 1), ("active", quiet == 0)):
+    if sel.any():
+        print("%-7s items %7d: load %.2f us, compute %.2f us, fence %.2f us, deps-ready -> published %.2f us" % (
+            nm, int(sel.sum()), d[sel, 2].mean(), d[sel, 3].mean(), d[sel, 4].mean(), busy[sel].mean()))
+print("active fraction by ticket decile:", [round(float(1 - quiet[q[i]:q[i + 1] + 1].mean()), 3) for i in range(10)])
