@@ -73,7 +73,8 @@ __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos,
 #define LS_PY (LS_TY + 1)
 #define LS_PZ (LS_TZ + 1)
 #define LS_STEPS (LS_TX + LS_TY + LS_TZ - 2)
-#define LS_THREADS (LS_TY * LS_TZ)
+#define LS_LINES (LS_TY * LS_TZ)   // threads that march
+#define LS_THREADS 256             // all of them load, run the quiet-tile test and write phi
 #define LS_CELLS (LS_PX * LS_PY * LS_PZ)
 #define LS_SMEM_BYTES (LS_CELLS * (sizeof(float4) + sizeof(float)))
 
@@ -125,14 +126,15 @@ __device__ __forceinline__ unsigned long long ls_now() { unsigned long long t; a
 #define LS_MARK(k) do { } while (0)
 #endif
 
-__global__ void __launch_bounds__(LS_THREADS) k_ls_sweep_dataflow(float4* __restrict__ rec, GridDims d, float radius,
+#define LS_INF __int_as_float(0x7f800000)
+__global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __restrict__ rec, GridDims d, float radius,
                                                                    const uint32_t* __restrict__ items, uint32_t* done, uint32_t* ticket,
                                                                    uint32_t nitems, int ntx, int nty, int ntz, uint32_t epoch0,
                                                                    int* __restrict__ flags, float* __restrict__ phi, int* __restrict__ closest, unsigned sleep_max) {
 	extern __shared__ float4 ls_smem[];
 	__shared__ uint32_t s_ticket;
 	float4* const sm = ls_smem;
-	float* const m2s = reinterpret_cast<float*>(ls_smem + LS_CELLS);
+	float* const m2s = reinterpret_cast<float*>(ls_smem + LS_CELLS);   // squared distance of the cell to its current record
 	const int tid = threadIdx.x;
 #define SMI(a, b, c) (((a) + 1) + LS_PX * (((b) + 1) + LS_PY * ((c) + 1)))
 	const float4 none = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
@@ -175,22 +177,24 @@ __global__ void __launch_bounds__(LS_THREADS) k_ls_sweep_dataflow(float4* __rest
 		LS_MARK(2);
 		// ---- three upwind halo faces (sweep coordinate -1 on one axis) ---------------------------------------
 		{
-			// x face: (b, c) = 16 x 8 cells, one per thread
-			const int b = tid % LS_TY, c = tid / LS_TY;
+			// x face: (b, c) = 16 x 8 cells, threads 0..127
+			const int b = tid % LS_TY, c = (tid / LS_TY) % LS_TZ;
 			const int qx = dx > 0 ? x0 - 1 : x0 + wx, qy = y0 + (dy > 0 ? b : wy - 1 - b), qz = z0 + (dz > 0 ? c : wz - 1 - c);
-			if (b < wy && c < wz && qx >= 0 && qx < d.nx) cp_async16(sm + SMI(-1, b, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
+			if (tid >= LS_LINES) {}
+			else if (b < wy && c < wz && qx >= 0 && qx < d.nx) cp_async16(sm + SMI(-1, b, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
 			else sm[SMI(-1, b, c)] = none;
 		}
 		{
-			// y face: (a, c) = 16 x 8 cells, one per thread
-			const int a = tid % LS_TX, c = tid / LS_TX;
+			// y face: (a, c) = 16 x 8 cells, threads 128..255
+			const int a = tid % LS_TX, c = (tid / LS_TX) % LS_TZ;
 			const int qx = x0 + (dx > 0 ? a : wx - 1 - a), qy = dy > 0 ? y0 - 1 : y0 + wy, qz = z0 + (dz > 0 ? c : wz - 1 - c);
-			if (a < wx && c < wz && qy >= 0 && qy < d.ny) cp_async16(sm + SMI(a, -1, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
+			if (tid < LS_LINES) {}
+			else if (a < wx && c < wz && qy >= 0 && qy < d.ny) cp_async16(sm + SMI(a, -1, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
 			else sm[SMI(a, -1, c)] = none;
 		}
 #pragma unroll
 		for (int i = 0; i < LS_TX * LS_TY / LS_THREADS; i++) {
-			// z face: (a, b) = 16 x 16 cells, two per thread
+			// z face: (a, b) = 16 x 16 cells, one per thread
 			const int e = tid + LS_THREADS * i, a = e % LS_TX, b = e / LS_TX;
 			const int qx = x0 + (dx > 0 ? a : wx - 1 - a), qy = y0 + (dy > 0 ? b : wy - 1 - b), qz = dz > 0 ? z0 - 1 : z0 + wz;
 			if (a < wx && b < wy && qz >= 0 && qz < d.nz) cp_async16(sm + SMI(a, b, -1), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
@@ -199,10 +203,58 @@ __global__ void __launch_bounds__(LS_THREADS) k_ls_sweep_dataflow(float4* __rest
 		cp_async_wait_all();
 		__syncthreads();
 		LS_MARK(3);
-		// ---- the cell hyperplanes; thread = line (b, c), marching along a ------------------------------------
-		// Branch-free on the hot path: every thread runs every step on addresses that stay inside the CTA's
-		// shared memory (inactive threads compute garbage and store nothing).
+		// ---- squared distance of every own cell to its current record, and the quiet-tile test ---------------------------
+		// Fully parallel, x fastest (conflict-free): if no cell would accept any of its three upwind candidates as
+		// they stand BEFORE the sweep (q2 < m2 is necessary for acceptance: sqrt and "- radius" are monotonic),
+		// then by induction along the sweep order the Gauss-Seidel pass changes nothing and the march is skipped.
+		bool maybe = false;
+#ifdef FS3_LS_TRACE
+		unsigned tr_cnt = 0; unsigned long long tr_pl = 0;
+#endif
 		{
+			const int a = tid % LS_TX, b = tid / LS_TX;   // 16 x 16 threads, looping over c
+			const float cxf = (float)(dx > 0 ? x0 + a : x0 + wx - 1 - a), cyf = (float)(dy > 0 ? y0 + b : y0 + wy - 1 - b);
+#pragma unroll
+			for (int c = 0; c < LS_TZ; c++) {
+				const float czf = (float)(dz > 0 ? z0 + c : z0 + wz - 1 - c);
+				const int i = SMI(a, b, c);
+				const float4 cur = sm[i], X = sm[i - 1], Y = sm[i - LS_PX], Z = sm[i - LS_PX * LS_PY];
+				// no record: infinitely far (any valid candidate wins); the same record in a neighbour has the same d^2 and never wins
+				const float m2 = __float_as_int(cur.w) >= 0 ? ls_d2(cxf, cyf, czf, cur) : LS_INF;
+				m2s[i] = m2;
+				const bool wX = __float_as_int(X.w) > 0 && ls_d2(cxf, cyf, czf, X) < m2;
+				const bool wY = __float_as_int(Y.w) > 0 && ls_d2(cxf, cyf, czf, Y) < m2;
+				const bool wZ = __float_as_int(Z.w) > 0 && ls_d2(cxf, cyf, czf, Z) < m2;
+				maybe |= a < wx && b < wy && c < wz && (wX || wY || wZ);
+#ifdef FS3_LS_TRACE
+				if (a < wx && b < wy && c < wz && (wX || wY || wZ)) { tr_cnt++; tr_pl |= 1ull << (a + b + c); }
+#endif
+			}
+		}
+#ifdef FS3_LS_TRACE
+		__shared__ unsigned long long tr_planes;
+		__shared__ unsigned int tr_maybe, tr_chg_cells;
+		__shared__ unsigned long long tr_chg_planes;
+		if (tid == 0) { tr_planes = 0; tr_maybe = 0; tr_chg_cells = 0; tr_chg_planes = 0; }
+		__syncthreads();
+		atomicAdd(&tr_maybe, tr_cnt);
+		atomicOr(&tr_planes, tr_pl);
+#endif
+		const bool quiet = !__syncthreads_or(maybe);   // (also orders the m2s stores before the march)
+#ifdef FS3_LS_TRACE
+		if (tid == 0 && quiet) g_ls_trace[(size_t)t * 8 + 6] = 1;
+#endif
+		// ---- the cell hyperplanes; thread = line (b, c), marching along a ------------------------------------
+		// clsInner on the upwind x-, y-, z-neighbour in that order (S3D.cpp:310-315 and siblings): index <= 0 is never
+		// propagated (:242); a cell without a record takes any candidate and strict `dist < phi` keeps the incumbent
+		// (:248) -- with "no record" and "no candidate" at distance +inf both are one comparison.
+		// Fast path, branch-free, in squared distances: q2 >= m2 can never win (sqrt and "- radius" are monotonic)
+		// and q2 < m2 by more than 2^-21 relative with sqrt(m2) >= 0.5 always wins (the sqrt values differ by >= 1 ulp
+		// and sqrt(m2) - 1 is exact).  A comparison that falls between the two marks the step ambiguous and the
+		// whole warp repeats it with the reference's full expression (warp-uniform branch, rare).
+		// Idle threads compute garbage on a clamped cell of their own line and store nothing; only the 128 line
+		// threads take part (named barrier 1).
+		if (!quiet && tid < LS_LINES) {
 			const int b = tid % LS_TY, c = tid / LS_TY;
 			const bool line_in = b < wy && c < wz;
 			const int gy = y0 + (dy > 0 ? b : wy - 1 - b), gz = z0 + (dz > 0 ? c : wz - 1 - c);
@@ -210,67 +262,53 @@ __global__ void __launch_bounds__(LS_THREADS) k_ls_sweep_dataflow(float4* __rest
 			const int li = SMI(0, b, c);
 			const int gx0 = dx > 0 ? x0 : x0 + wx - 1;
 			float4* const grow = rec + (sY * (size_t)gy + sZ * (size_t)gz);
-			// squared distance of every own cell to its current record (off the dependent chain), and the
-			// quiet-tile test, fully parallel: if no cell would accept any of its three upwind candidates as they
-			// stand BEFORE the sweep (q2 < m2 is necessary for acceptance), then by induction along the sweep
-			// order the Gauss-Seidel pass changes nothing and the hyperplane steps are skipped.
-			bool maybe = false;
-			{
-				float4 prev = sm[li - 1];
-#pragma unroll
-				for (int a = 0; a < LS_TX; a++) {
-					const float cxf = (float)(gx0 + dx * a);
-					const float4 cur = sm[li + a], Y = sm[li + a - LS_PX], Z = sm[li + a - LS_PX * LS_PY];
-					const float m2 = ls_d2(cxf, cyf, czf, cur);
-					m2s[li + a] = m2;
-					const int myid = __float_as_int(cur.w), idX = __float_as_int(prev.w), idY = __float_as_int(Y.w), idZ = __float_as_int(Z.w);
-					const bool wX = idX > 0 && idX != myid && (myid < 0 || ls_d2(cxf, cyf, czf, prev) < m2);
-					const bool wY = idY > 0 && idY != myid && (myid < 0 || ls_d2(cxf, cyf, czf, Y) < m2);
-					const bool wZ = idZ > 0 && idZ != myid && (myid < 0 || ls_d2(cxf, cyf, czf, Z) < m2);
-					maybe |= (a < wx) && (wX || wY || wZ);
-					prev = cur;
-				}
-			}
-			const bool quiet = !__syncthreads_or(maybe && line_in);   // (also orders the m2s stores before the loop)
-#ifdef FS3_LS_TRACE
-			if (tid == 0 && quiet) g_ls_trace[(size_t)t * 8 + 6] = 1;
-#endif
 			uint32_t chg = 0;
-			const int nsteps = quiet ? 0 : wx + wy + wz - 2;
+			const int nsteps = wx + wy + wz - 2;
 			for (int s = 0; s < nsteps; s++) {
 				const int a = s - b - c;
 				const bool act = line_in && (unsigned)a < (unsigned)wx;
-				const int ac = min(max(a, 0), LS_TX - 1);   // clamped: idle threads read (and discard) a cell of their own line
+				const int ac = min(max(a, 0), LS_TX - 1);
 				const float4* q = sm + li + ac;
-				float4 mine = q[0];
-				const float4 X = q[-1], Y = q[-LS_PX], Z = q[-LS_PX * LS_PY];
-				float m2 = m2s[li + ac];
+				const float4 mine0 = q[0], X = q[-1], Y = q[-LS_PX], Z = q[-LS_PX * LS_PY];
+				const float m20 = m2s[li + ac];
 				const float cxf = (float)(gx0 + dx * ac);
-				int myid = __float_as_int(mine.w);
-				const int idX = __float_as_int(X.w), idY = __float_as_int(Y.w), idZ = __float_as_int(Z.w);
-				const float x2 = ls_d2(cxf, cyf, czf, X), y2 = ls_d2(cxf, cyf, czf, Y), z2 = ls_d2(cxf, cyf, czf, Z);
-				bool changed = false;
-				// clsInner on the upwind x-, y-, z-neighbour in that order (S3D.cpp:310-315 and siblings): index <= 0 is
-				// never propagated (:242); strict `<` keeps the incumbent (:248).  Same id = same record = no change.
-				// `sure`: q2 < m2 by more than 2^-21 relative with sqrt(m2) >= 0.5 implies sqrt(q2)-r < sqrt(m2)-r in
-				// fp32 (the sqrt values differ by >= 1 ulp and sqrt(m2)-1 is exact); anything closer takes the
-				// reference's full expression.
-#define LS_TRY(Q, idQ, q2)                                                                                                   \
+				// a candidate with index <= 0 is never propagated (S3D.cpp:242): infinitely far
+				const float x2 = __float_as_int(X.w) > 0 ? ls_d2(cxf, cyf, czf, X) : LS_INF;
+				const float y2 = __float_as_int(Y.w) > 0 ? ls_d2(cxf, cyf, czf, Y) : LS_INF;
+				const float z2 = __float_as_int(Z.w) > 0 ? ls_d2(cxf, cyf, czf, Z) : LS_INF;
+				float4 mine = mine0;
+				float m2 = m20;
+				bool changed = false, amb = false;
+#define LS_FAST(Q, q2)                                                                                                        \
 	{                                                                                                                        \
-		const bool valid = idQ > 0 && idQ != myid;                                                                           \
-		const bool sure = m2 >= 0.25f && q2 < __fmul_rn(m2, 0.99999905f);                                                    \
-		bool take = valid && (myid < 0 || sure);                                                                             \
-		if (valid && myid >= 0 && !sure && q2 < m2) take = __fsub_rn(sqrtf(q2), radius) < __fsub_rn(sqrtf(m2), radius);      \
+		const bool take = m2 >= 0.25f && q2 < __fmul_rn(m2, 0.99999905f);                                                    \
+		amb |= !take && q2 < m2;                                                                                             \
 		mine.x = take ? Q.x : mine.x; mine.y = take ? Q.y : mine.y; mine.z = take ? Q.z : mine.z; mine.w = take ? Q.w : mine.w; \
-		myid = take ? idQ : myid; m2 = take ? q2 : m2; changed |= take;                                                      \
+		m2 = take ? q2 : m2; changed |= take;                                                                                \
 	}
-				LS_TRY(X, idX, x2)
-				LS_TRY(Y, idY, y2)
-				LS_TRY(Z, idZ, z2)
+				LS_FAST(X, x2)
+				LS_FAST(Y, y2)
+				LS_FAST(Z, z2)
+#undef LS_FAST
+				if (__any_sync(0xffffffffu, amb && act)) {
+					mine = mine0; m2 = m20; changed = false;
+#define LS_TRY(Q, q2)                                                                                                         \
+	{                                                                                                                        \
+		const bool take = __fsub_rn(sqrtf(q2), radius) < __fsub_rn(sqrtf(m2), radius);                                       \
+		mine.x = take ? Q.x : mine.x; mine.y = take ? Q.y : mine.y; mine.z = take ? Q.z : mine.z; mine.w = take ? Q.w : mine.w; \
+		m2 = take ? q2 : m2; changed |= take;                                                                                \
+	}
+					LS_TRY(X, x2)
+					LS_TRY(Y, y2)
+					LS_TRY(Z, z2)
 #undef LS_TRY
+				}
 				// global write-back is deferred past the loop: a store in flight would put an L2 round trip into every step
 				if (act && changed) { sm[li + a] = mine; m2s[li + a] = m2; chg |= 1u << a; }
-				__syncthreads();
+#ifdef FS3_LS_TRACE
+				if (act && changed) { atomicAdd(&tr_chg_cells, 1u); atomicOr(&tr_chg_planes, 1ull << s); }
+#endif
+				asm volatile("bar.sync 1, %0;\n" ::"n"(LS_LINES) : "memory");
 			}
 #pragma unroll
 			for (int a = 0; a < LS_TX; a++)
@@ -279,6 +317,7 @@ __global__ void __launch_bounds__(LS_THREADS) k_ls_sweep_dataflow(float4* __rest
 		if (m == 7) {
 			// cells never reached keep their previous phi, as in the reference where m_Phi is only written
 			// together with closestParticles (S3D.cpp:248-251,296-299).  x fastest: coalesced stores.
+			__syncthreads();
 #pragma unroll
 			for (int i = 0; i < LS_TX * LS_TY * LS_TZ / LS_THREADS; i++) {
 				const int e = tid + LS_THREADS * i, px = e % LS_TX, py = (e / LS_TX) % LS_TY, pz = e / (LS_TX * LS_TY);
@@ -294,6 +333,9 @@ __global__ void __launch_bounds__(LS_THREADS) k_ls_sweep_dataflow(float4* __rest
 		// ---- publish: the CTA's stores, then the epoch (release is cumulative over the barrier) ------------
 		LS_MARK(4);
 		__syncthreads();
+#ifdef FS3_LS_TRACE
+		if (tid == 0 && !quiet) g_ls_trace[(size_t)t * 8 + 7] = (unsigned long long)tr_maybe | ((unsigned long long)__popcll(tr_planes) << 16) | ((unsigned long long)tr_chg_cells << 24) | ((unsigned long long)__popcll(tr_chg_planes) << 40) | ((unsigned long long)(tr_chg_planes ? 64 - __clzll(tr_chg_planes) - (__ffsll(tr_chg_planes) - 1) : 0) << 48);
+#endif
 		if (tid == 0) { __threadfence(); st_release_u32(mydone, E); }
 		LS_MARK(5);
 	}
