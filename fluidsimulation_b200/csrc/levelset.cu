@@ -133,6 +133,7 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
                                                                    int* __restrict__ flags, float* __restrict__ phi, int* __restrict__ closest, unsigned sleep_max) {
 	extern __shared__ float4 ls_smem[];
 	__shared__ uint32_t s_ticket;
+	__shared__ unsigned s_planes[2];
 	float4* const sm = ls_smem;
 	float* const m2s = reinterpret_cast<float*>(ls_smem + LS_CELLS);   // squared distance of the cell to its current record
 	const int tid = threadIdx.x;
@@ -207,10 +208,11 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 		// Fully parallel, x fastest (conflict-free): if no cell would accept any of its three upwind candidates as
 		// they stand BEFORE the sweep (q2 < m2 is necessary for acceptance: sqrt and "- radius" are monotonic),
 		// then by induction along the sweep order the Gauss-Seidel pass changes nothing and the march is skipped.
-		bool maybe = false;
-#ifdef FS3_LS_TRACE
-		unsigned tr_cnt = 0; unsigned long long tr_pl = 0;
-#endif
+		// The hyperplanes a+b+c that hold such a cell are collected in a bit mask: the march only runs a hyperplane that
+		// holds one, or that follows a hyperplane in which a record changed.
+		unsigned long long planes = 0;
+		if (tid == 0) { s_planes[0] = 0u; s_planes[1] = 0u; }
+		__syncthreads();
 		{
 			const int a = tid % LS_TX, b = tid / LS_TX;   // 16 x 16 threads, looping over c
 			const float cxf = (float)(dx > 0 ? x0 + a : x0 + wx - 1 - a), cyf = (float)(dy > 0 ? y0 + b : y0 + wy - 1 - b);
@@ -225,22 +227,14 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 				const bool wX = __float_as_int(X.w) > 0 && ls_d2(cxf, cyf, czf, X) < m2;
 				const bool wY = __float_as_int(Y.w) > 0 && ls_d2(cxf, cyf, czf, Y) < m2;
 				const bool wZ = __float_as_int(Z.w) > 0 && ls_d2(cxf, cyf, czf, Z) < m2;
-				maybe |= a < wx && b < wy && c < wz && (wX || wY || wZ);
-#ifdef FS3_LS_TRACE
-				if (a < wx && b < wy && c < wz && (wX || wY || wZ)) { tr_cnt++; tr_pl |= 1ull << (a + b + c); }
-#endif
+				if (a < wx && b < wy && c < wz && (wX || wY || wZ)) planes |= 1ull << (a + b + c);
 			}
+			const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)planes), hi = __reduce_or_sync(0xffffffffu, (unsigned)(planes >> 32));
+			if ((tid & 31) == 0) { if (lo) atomicOr(&s_planes[0], lo); if (hi) atomicOr(&s_planes[1], hi); }
 		}
-#ifdef FS3_LS_TRACE
-		__shared__ unsigned long long tr_planes;
-		__shared__ unsigned int tr_maybe, tr_chg_cells;
-		__shared__ unsigned long long tr_chg_planes;
-		if (tid == 0) { tr_planes = 0; tr_maybe = 0; tr_chg_cells = 0; tr_chg_planes = 0; }
-		__syncthreads();
-		atomicAdd(&tr_maybe, tr_cnt);
-		atomicOr(&tr_planes, tr_pl);
-#endif
-		const bool quiet = !__syncthreads_or(maybe);   // (also orders the m2s stores before the march)
+		__syncthreads();   // (also orders the m2s stores before the march)
+		planes = (unsigned long long)s_planes[0] | ((unsigned long long)s_planes[1] << 32);
+		const bool quiet = planes == 0;
 #ifdef FS3_LS_TRACE
 		if (tid == 0 && quiet) g_ls_trace[(size_t)t * 8 + 6] = 1;
 #endif
@@ -264,7 +258,7 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 			float4* const grow = rec + (sY * (size_t)gy + sZ * (size_t)gz);
 			uint32_t chg = 0;
 			const int nsteps = wx + wy + wz - 2;
-			for (int s = 0; s < nsteps; s++) {
+			for (int s = __ffsll((long long)planes) - 1; s < nsteps; s++) {
 				const int a = s - b - c;
 				const bool act = line_in && (unsigned)a < (unsigned)wx;
 				const int ac = min(max(a, 0), LS_TX - 1);
@@ -305,10 +299,16 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 				}
 				// global write-back is deferred past the loop: a store in flight would put an L2 round trip into every step
 				if (act && changed) { sm[li + a] = mine; m2s[li + a] = m2; chg |= 1u << a; }
-#ifdef FS3_LS_TRACE
-				if (act && changed) { atomicAdd(&tr_chg_cells, 1u); atomicOr(&tr_chg_planes, 1ull << s); }
-#endif
-				asm volatile("bar.sync 1, %0;\n" ::"n"(LS_LINES) : "memory");
+				// barrier among the 128 line threads + "did any record change in this hyperplane"
+				int any;
+				asm volatile("{\n .reg .pred p, q;\n setp.ne.u32 q, %1, 0;\n barrier.red.or.pred p, 1, %2, q;\n selp.u32 %0, 1, 0, p;\n}\n"
+				             : "=r"(any) : "r"((unsigned)(act && changed)), "n"(LS_LINES) : "memory");
+				if (!any) {
+					// nothing changed: the next hyperplane that can is the next one holding a candidate cell
+					const unsigned long long rest = s + 1 < 64 ? planes >> (s + 1) : 0ull;
+					if (!rest) break;
+					s += __ffsll((long long)rest) - 1;
+				}
 			}
 #pragma unroll
 			for (int a = 0; a < LS_TX; a++)
@@ -333,9 +333,6 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 		// ---- publish: the CTA's stores, then the epoch (release is cumulative over the barrier) ------------
 		LS_MARK(4);
 		__syncthreads();
-#ifdef FS3_LS_TRACE
-		if (tid == 0 && !quiet) g_ls_trace[(size_t)t * 8 + 7] = (unsigned long long)tr_maybe | ((unsigned long long)__popcll(tr_planes) << 16) | ((unsigned long long)tr_chg_cells << 24) | ((unsigned long long)__popcll(tr_chg_planes) << 40) | ((unsigned long long)(tr_chg_planes ? 64 - __clzll(tr_chg_planes) - (__ffsll(tr_chg_planes) - 1) : 0) << 48);
-#endif
 		if (tid == 0) { __threadfence(); st_release_u32(mydone, E); }
 		LS_MARK(5);
 	}

@@ -42,13 +42,3 @@ for nm, sel in (("quiet", quiet == 1), ("active", quiet == 0)):
         print("%-7s items %7d: load %.2f us, compute %.2f us, fence %.2f us, deps-ready -> published %.2f us" % (
             nm, int(sel.sum()), d[sel, 2].mean(), d[sel, 3].mean(), d[sel, 4].mean(), busy[sel].mean()))
 print("active fraction by ticket decile:", [round(float(1 - quiet[q[i]:q[i + 1] + 1].mean()), 3) for i in range(10)])
-x = raw[:8 * nt * 8 * 8].view(np.uint64).reshape(-1, 8)[:, 7]
-act = quiet == 0
-mb, mpl, cc, cpl, span = (x & 0xffff).astype(int), ((x >> 16) & 0xff).astype(int), ((x >> 24) & 0xffff).astype(int), ((x >> 40) & 0xff).astype(int), ((x >> 48) & 0xff).astype(int)
-print("active tiles: maybe cells mean %.1f (median %d) of 2048; hyperplanes with a maybe cell mean %.1f of 38; changed cells mean %.1f (median %d); hyperplanes with a change mean %.1f; first..last changed hyperplane span mean %.1f" % (
-    mb[act].mean(), np.median(mb[act]), mpl[act].mean(), cc[act].mean(), np.median(cc[act]), cpl[act].mean(), span[act].mean()))
-print("active tiles with 0 changed cells: %.3f; with <= 8 changed: %.3f" % ((cc[act] == 0).mean(), (cc[act] <= 8).mean()))
-for m in range(8):
-    sel = act & (sweep == m)
-    if sel.any():
-        print("sweep %d: active %6d  maybe %.1f  maybe planes %.1f  changed cells %.1f  changed planes %.1f  span %.1f" % (m, sel.sum(), mb[sel].mean(), mpl[sel].mean(), cc[sel].mean(), cpl[sel].mean(), span[sel].mean()))
