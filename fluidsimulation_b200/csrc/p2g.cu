@@ -13,10 +13,11 @@
 #include "fs3_internal.cuh"
 
 // AX = staggered axis of this face grid (0:U, 1:V, 2:W).  Grid extents (xs,ys,zs) = cells + 1 on AX.
-// A thread owns a 1 x 2 x 2 block of nodes (i; j0,j0+1; k0,k0+1): their supports share half-rows, so the 4 nodes walk
-// 6 x 6 particle runs instead of 4 x 16, and a CTA of 32 x 2 x 2 threads (32 x 4 x 4 nodes) re-reads each half-row
-// from L1 rather than L2.  Every node still sees its particles in the order (hz, hy, run) of the one-node-per-thread
+// A thread owns a 2 x 2 x 2 block of nodes (i0,i0+1; j0,j0+1; k0,k0+1): their supports share half-rows and overlap
+// along x, so the 8 nodes walk 6 x 6 particle runs of 6 half-cells instead of 8 x 16 runs of 4, and a CTA of
+// 32 x 2 x 2 threads (64 x 4 x 4 nodes) re-reads each half-row from L1 rather than L2.  Every node still sees its particles in the order (hz, hy, run) of the one-node-per-thread
 // formulation, so the sums are bit-identical to it (and independent of how the grid is cut into slabs).
+#define P2G_KX 2
 #define P2G_KY 2
 #define P2G_KZ 2
 template <int AX>
@@ -24,23 +25,27 @@ __global__ void __launch_bounds__(128) k_p2g_gather(const float4* __restrict__ p
                                                     const uint32_t* __restrict__ start, GridDims d, float cpm, float* __restrict__ grid,
                                                     int* __restrict__ cd, int kbeg, int kend) {
 	const int xs = d.nx + (AX == 0), ys = d.ny + (AX == 1);
-	const int i = blockIdx.x * 32 + (threadIdx.x & 31);
+	const int i0 = (blockIdx.x * 32 + (threadIdx.x & 31)) * P2G_KX;
 	const int j0 = (blockIdx.y * 2 + ((threadIdx.x >> 5) & 1)) * P2G_KY;
 	const int k0 = kbeg + (blockIdx.z * 2 + (threadIdx.x >> 6)) * P2G_KZ;
 	if (j0 >= ys || k0 >= kend) return;   // warp-uniform
 	const int HX = 2 * d.nx, HY = 2 * d.ny, HZ = 2 * d.nz;
-	// half-cell support: staggered axis [2m-2, 2m+1], other axes [2m-1, 2m+2], clipped to the grid
-	const bool lane_in = i < xs;
-	const int x0 = max(2 * i - (AX == 0 ? 2 : 1), 0), x1 = min(2 * i + (AX == 0 ? 1 : 2), HX - 1);
+	// half-cell support of a node: staggered axis [2m-2, 2m+1], other axes [2m-1, 2m+2], clipped to the grid.  Along x
+	// the thread's two nodes share one run of 6 half-cells; a particle of the run that lies outside a node's own 4
+	// gets the clamped weight max(0, 1-|q-i|) = 0 there, which leaves that node's sums unchanged bit for bit.
+	const bool lane_in = i0 < xs;
+	const int x0 = max(2 * i0 - (AX == 0 ? 2 : 1), 0), x1 = min(2 * (i0 + P2G_KX - 1) + (AX == 0 ? 1 : 2), HX - 1);
 	const int ylo = 2 * j0 - (AX == 1 ? 2 : 1), zlo = 2 * k0 - (AX == 2 ? 2 : 1);
-	const float fi = (float)i;
+	const float fi[2] = {(float)i0, (float)(i0 + 1)};
 	const float fj[2] = {(float)j0, (float)(j0 + 1)}, fk[2] = {(float)k0, (float)(k0 + 1)};
 	const float* __restrict__ vcomp = reinterpret_cast<const float*>(vel) + AX;
-	float sum[P2G_KZ][P2G_KY], amt[P2G_KZ][P2G_KY];
+	float sum[P2G_KZ][P2G_KY][P2G_KX], amt[P2G_KZ][P2G_KY][P2G_KX];
 #pragma unroll
 	for (int c = 0; c < P2G_KZ; c++)
 #pragma unroll
-		for (int b = 0; b < P2G_KY; b++) sum[c][b] = amt[c][b] = 0.f;
+		for (int b = 0; b < P2G_KY; b++)
+#pragma unroll
+			for (int a = 0; a < P2G_KX; a++) sum[c][b][a] = amt[c][b][a] = 0.f;
 	// (the two run loops stay rolled: 36 unrolled copies of the particle loop overflow the instruction cache)
 #pragma unroll 1
 	for (int rz = 0; rz < 2 * P2G_KZ + 2; rz++) {
@@ -60,7 +65,9 @@ __global__ void __launch_bounds__(128) k_p2g_gather(const float4* __restrict__ p
 				if (AX == 1) qy = __fadd_rn(qy, 0.5f);
 				if (AX == 2) qz = __fadd_rn(qz, 0.5f);
 				const float u = __ldg(vcomp + 4 * (size_t)t);
-				const float wx = __fsub_rn(1.f, fabsf(__fsub_rn(qx, fi)));
+				float wx[P2G_KX];
+#pragma unroll
+				for (int a = 0; a < P2G_KX; a++) wx[a] = fmaxf(__fsub_rn(1.f, fabsf(__fsub_rn(qx, fi[a]))), 0.f);
 #pragma unroll
 				for (int c = 0; c < P2G_KZ; c++) {
 					if (rz < 2 * c || rz > 2 * c + 3) continue;   // half-row outside node k0+c's support (warp-uniform)
@@ -69,9 +76,12 @@ __global__ void __launch_bounds__(128) k_p2g_gather(const float4* __restrict__ p
 					for (int bb = 0; bb < P2G_KY; bb++) {
 						if (ry < 2 * bb || ry > 2 * bb + 3) continue;
 						const float wy = __fsub_rn(1.f, fabsf(__fsub_rn(qy, fj[bb])));
-						const float w = __fmul_rn(__fmul_rn(wx, wy), wz);                                   // S3D.cpp:472-474
-						sum[c][bb] = __fadd_rn(sum[c][bb], __fmul_rn(w, u));
-						amt[c][bb] = __fadd_rn(amt[c][bb], w);
+#pragma unroll
+						for (int a = 0; a < P2G_KX; a++) {
+							const float w = __fmul_rn(__fmul_rn(wx[a], wy), wz);                              // S3D.cpp:472-474
+							sum[c][bb][a] = __fadd_rn(sum[c][bb][a], __fmul_rn(w, u));
+							amt[c][bb][a] = __fadd_rn(amt[c][bb][a], w);
+						}
 					}
 				}
 			}
@@ -82,16 +92,18 @@ __global__ void __launch_bounds__(128) k_p2g_gather(const float4* __restrict__ p
 #pragma unroll
 	for (int c = 0; c < P2G_KZ; c++)
 #pragma unroll
-		for (int bb = 0; bb < P2G_KY; bb++) {
-			const int j = j0 + bb, k = k0 + c;
-			if (j >= ys || k >= kend) continue;
-			const size_t q = (size_t)i + (size_t)xs * ((size_t)j + (size_t)ys * k);
-			// wall planes: forced to zero and valid (S3D.cpp:578-599)
-			const int m_ax = AX == 0 ? i : (AX == 1 ? j : k), n_ax = AX == 0 ? d.nx : (AX == 1 ? d.ny : d.nz);
-			if (m_ax == 0 || m_ax == n_ax) { grid[q] = 0.f; cd[q] = 0; continue; }
-			grid[q] = __fdiv_rn(sum[c][bb], __fadd_rn(tiny, amt[c][bb]));
-			cd[q] = amt[c][bb] > 0.01f ? 0 : FS3_INF_CD;  // S3D.cpp:565-575
-		}
+		for (int bb = 0; bb < P2G_KY; bb++)
+#pragma unroll
+			for (int a = 0; a < P2G_KX; a++) {
+				const int i = i0 + a, j = j0 + bb, k = k0 + c;
+				if (i >= xs || j >= ys || k >= kend) continue;
+				const size_t q = (size_t)i + (size_t)xs * ((size_t)j + (size_t)ys * k);
+				// wall planes: forced to zero and valid (S3D.cpp:578-599)
+				const int m_ax = AX == 0 ? i : (AX == 1 ? j : k), n_ax = AX == 0 ? d.nx : (AX == 1 ? d.ny : d.nz);
+				if (m_ax == 0 || m_ax == n_ax) { grid[q] = 0.f; cd[q] = 0; continue; }
+				grid[q] = __fdiv_rn(sum[c][bb][a], __fadd_rn(tiny, amt[c][bb][a]));
+				cd[q] = amt[c][bb][a] > 0.01f ? 0 : FS3_INF_CD;  // S3D.cpp:565-575
+			}
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -354,7 +366,7 @@ template <int AX> static int p2g_launch(fs3_sim* s, float* grid, int* cd) {
 	GridDims d{s->nx, s->ny, s->nz};
 	const int xs = s->nx + (AX == 0), ys = s->ny + (AX == 1);
 	const int kbeg = s->z0, kend = s->z1 + ((AX == 2 && s->rank == s->world - 1) ? 1 : 0);
-	dim3 g(cdiv(xs, 32), cdiv(ys, 2 * P2G_KY), cdiv(kend - kbeg, 2 * P2G_KZ));
+	dim3 g(cdiv(xs, 32 * P2G_KX), cdiv(ys, 2 * P2G_KY), cdiv(kend - kbeg, 2 * P2G_KZ));
 	k_p2g_gather<AX><<<g, 128, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->cell_start, d, s->cpm, grid, cd, kbeg, kend);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;

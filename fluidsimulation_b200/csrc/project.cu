@@ -197,7 +197,18 @@ __global__ void __launch_bounds__(256, FS3_SOR_MINB) k_sor_half(Sys<REAL> sy, in
 	const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, G = gridDim.x * blockDim.x;
 	const SorPtrs<REAL> sp = sor_ptrs<REAL>(sy, colour, sh);
 	if (!SHARD) {
-		for (uint32_t t = gtid; t < n; t += G) sor_vector<REAL, VEC, false>(sp, omega, one_minus_omega, __ldg(list + t));
+		// Programmatic dependent launch: the next half sweep may be scheduled as soon as every CTA of this one has got
+		// here (its CTAs take the SM slots this grid frees while it drains and wait below), and this grid waits until the
+		// previous half sweep has completed and its stores are visible.  The list, the mask and b are constant during
+		// the solve, so the first entry is fetched ahead of the wait.
+		asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+		uint32_t ent = gtid < n ? __ldg(list + gtid) : 0u;
+		asm volatile("griddepcontrol.wait;\n" ::: "memory");
+		for (uint32_t t = gtid; t < n; t += G) {
+			const uint32_t nxt = t + G < n ? __ldg(list + t + G) : 0u;
+			sor_vector<REAL, VEC, false>(sp, omega, one_minus_omega, ent);
+			ent = nxt;
+		}
 		return;
 	}
 	if (threadIdx.x == 0 && sh.peer_flag[0]) fs3_flag_wait(sh.my_flag, sh.wait_epoch, sh.flags, sh.nospin);
@@ -441,7 +452,17 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, 256)), (long long)s->sm_count * per_sm);
 	const int c = k & 1;
 	if (s->world == 1) {
-		k_sor_half<REAL, VEC, false><<<nb, 256, 0, s->stream>>>(sy, c, omega, omo, s->sor_list[c], s->sor_count[c], SorShard{}); FS3_LAUNCH_CHECK();
+		// half sweeps after the first are launched with programmatic stream serialization (see the kernel); the first one
+		// follows the set-up kernels with a normal dependency
+		cudaLaunchConfig_t cfg = {};
+		cfg.gridDim = dim3(nb); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
+		cudaLaunchAttribute at[1];
+		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+		at[0].val.programmaticStreamSerializationAllowed = 1;
+		cfg.attrs = at; cfg.numAttrs = (k > 0 && !s->prm.record_residuals) ? 1 : 0;
+		const uint32_t* lst = s->sor_list[c]; const uint32_t* cnt = s->sor_count[c];
+		FS3_CUDA(cudaLaunchKernelEx(&cfg, k_sor_half<REAL, VEC, false>, sy, c, omega, omo, lst, cnt, SorShard{}));
+		FS3_LAUNCH_CHECK();
 		return FS3_OK;
 	}
 	SorShard sh;
