@@ -139,7 +139,7 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	s->scan_block_cap = (s->nH + 1) / 4096 + 2;
 	CA(s->scan_block, s->scan_block_cap * 4);
 	CA(s->ls_rec, s->nC * sizeof(float4)); CA(s->closest, s->nC * 4);
-	for (int k = 0; k < 3; k++) { CA(s->cdv[k], nmax * 4); CA(s->orderv[k], nmax * 4); }
+	for (int k = 0; k < 3; k++) { CA(s->cdv[k], nmax * 4); CA(s->orderv[k], nmax * 4); CA(s->exmask[k], nmax); }
 	s->bucket_cap = nx + ny + nz + 8;
 	CA(s->bucket, 3 * (3 * (size_t)s->bucket_cap + 2) * 4);
 	CA(s->ex_arrive, 4);
@@ -275,7 +275,7 @@ int fs3_destroy(fs3_sim* s) {
 	} else {
 		void* ptrs[] = {s->U, s->V, s->W, s->oU, s->oV, s->oW, s->phi, s->pos[0], s->pos[1], s->vel[0], s->vel[1], s->cellid, s->cell_count,
 		                s->cell_start, s->cell_fill, s->tmp_id, s->scan_block, s->ls_rec, s->closest, s->cdv[0], s->cdv[1], s->cdv[2], s->orderv[0],
-		                s->orderv[1], s->orderv[2], s->bucket, s->p[0], s->p[1], s->b[0], s->b[1], s->dg[0], s->dg[1], s->mask[0], s->mask[1],
+		                s->orderv[1], s->orderv[2], s->exmask[0], s->exmask[1], s->exmask[2], s->bucket, s->p[0], s->p[1], s->b[0], s->b[1], s->dg[0], s->dg[1], s->mask[0], s->mask[1],
 		                s->res, s->dev_flags, s->ex_arrive, s->ls_order, s->ls_done, s->ls_ticket, s->sor_flags, s->sor_pos[0], s->sor_pos[1], s->sor_list[0], s->sor_list[1]};
 		for (void* p : ptrs) if (p) cudaFree(p);
 	}

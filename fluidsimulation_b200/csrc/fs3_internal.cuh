@@ -69,6 +69,7 @@ struct fs3_sim {
 	// extrapolation scratch (sized for the largest face grid)
 	int* cdv[3];             // L1 distance, one slot per face grid
 	int* orderv[3];          // nodes with cd>0 bucketed by distance
+	unsigned char* exmask[3]; // per list entry: which of the node's 6 neighbours are strictly closer
 	uint32_t* bucket;        // per slot: histogram / starts / cursors (3*bucket_cap+2 words)
 	int bucket_cap;
 	uint32_t* ex_arrive;     // arrive counter of the layered fill's grid barrier

@@ -11,6 +11,8 @@
 // instead of particle-index order).  Normalisation, the validity test and the wall faces are fused in,
 // and the kernel also initialises the L1-distance grid of the extrapolation.
 #include "fs3_internal.cuh"
+#include <algorithm>
+#include <cstdlib>
 
 // AX = staggered axis of this face grid (0:U, 1:V, 2:W).  Grid extents (xs,ys,zs) = cells + 1 on AX.
 // A thread owns a 2 x 2 x 2 block of nodes (i0,i0+1; j0,j0+1; k0,k0+1): their supports share half-rows and overlap
@@ -190,8 +192,12 @@ __global__ void k_ex_scan(const uint32_t* __restrict__ hist, uint32_t* __restric
 		start[nb] = acc;
 	}
 }
+// Node lists bucketed by distance.  The scatter also records, per list entry, which of the node's 6 neighbours
+// (+x,-x,+y,-y,+z,-z, S3D.cpp:743) are strictly closer: it walks the grid in memory order, so the neighbour distances
+// come from cache here, and the fill -- whose layers are one dependent step each -- is left with the value loads only.
 __global__ void __launch_bounds__(256) k_ex_scatter(const int* __restrict__ cd, size_t n, const uint32_t* __restrict__ start,
-                                                    uint32_t* __restrict__ cursor, int* __restrict__ order, int nb, size_t chunk) {
+                                                    uint32_t* __restrict__ cursor, int* __restrict__ order, unsigned char* __restrict__ exmask,
+                                                    int nb, size_t chunk, int xs, int ys, int zs) {
 	extern __shared__ uint32_t sh[];  // [0,nb): block counts then block base; [nb,2nb): local cursor
 	uint32_t* cnt = sh;
 	uint32_t* loc = sh + nb;
@@ -202,9 +208,23 @@ __global__ void __launch_bounds__(256) k_ex_scatter(const int* __restrict__ cd, 
 	__syncthreads();
 	for (int b = threadIdx.x; b < nb; b += blockDim.x) if (cnt[b]) cnt[b] = start[b] + atomicAdd(cursor + b, cnt[b]);
 	__syncthreads();
+	const size_t sy = (size_t)xs, sz = (size_t)xs * ys;
 	for (size_t q = q0 + threadIdx.x; q < q1; q += blockDim.x) {
-		int c = cd[q];
-		if (c > 0) { int b = min(c, nb - 1); order[cnt[b] + atomicAdd(loc + b, 1u)] = (int)q; }
+		const int my = cd[q];
+		if (my > 0) {
+			const int x = (int)(q % xs), y = (int)((q / xs) % ys), z = (int)(q / sz);
+			int m = 0;
+			if (x + 1 < xs && __ldg(cd + q + 1) < my) m |= 1;
+			if (x - 1 >= 0 && __ldg(cd + q - 1) < my) m |= 2;
+			if (y + 1 < ys && __ldg(cd + q + sy) < my) m |= 4;
+			if (y - 1 >= 0 && __ldg(cd + q - sy) < my) m |= 8;
+			if (z + 1 < zs && __ldg(cd + q + sz) < my) m |= 16;
+			if (z - 1 >= 0 && __ldg(cd + q - sz) < my) m |= 32;
+			const int b = min(my, nb - 1);
+			const uint32_t slot = cnt[b] + atomicAdd(loc + b, 1u);
+			order[slot] = (int)q;
+			exmask[slot] = (unsigned char)m;
+		}
 	}
 }
 
@@ -214,30 +234,14 @@ __global__ void __launch_bounds__(256) k_ex_scatter(const int* __restrict__ cd, 
 // device.  Values of the previous layer are read with ld.cg (other SMs wrote them); cd[] is constant during the fill.
 struct ExGrid {
 	float* g;
-	const int* cd;
 	const int* order;
+	const unsigned char* mask;   // closer-neighbour bits of the list entries
 	const uint32_t* start;   // nb+1 bucket starts
 	int xs, ys, zs, nb;
 };
 struct ExGrids { ExGrid a[3]; int n; };
 #define EX_THREADS 512
 
-// which of the 6 neighbours (+x,-x,+y,-y,+z,-z, S3D.cpp:743) of node q are strictly closer: independent of the fill itself
-__device__ __forceinline__ int ex_closer_mask(const ExGrid& G, int q) {
-	const int* __restrict__ cd = G.cd;
-	const int my = __ldg(cd + q);
-	const int xs = G.xs, ys = G.ys, zs = G.zs;
-	const int x = q % xs, y = (q / xs) % ys, z = q / (xs * ys);
-	const int sy = xs, sz = xs * ys;
-	int m = 0;
-	if (x + 1 < xs && __ldg(cd + q + 1) < my) m |= 1;
-	if (x - 1 >= 0 && __ldg(cd + q - 1) < my) m |= 2;
-	if (y + 1 < ys && __ldg(cd + q + sy) < my) m |= 4;
-	if (y - 1 >= 0 && __ldg(cd + q - sy) < my) m |= 8;
-	if (z + 1 < zs && __ldg(cd + q + sz) < my) m |= 16;
-	if (z - 1 >= 0 && __ldg(cd + q - sz) < my) m |= 32;
-	return m;
-}
 __device__ __forceinline__ void ex_fill_node(const ExGrid& G, int q, int m) {
 	float* __restrict__ g = G.g;
 	const int sy = G.xs, sz = G.xs * G.ys;
@@ -265,7 +269,7 @@ __global__ void __launch_bounds__(EX_THREADS, 3) k_ex_fill_layers(ExGrids P, uin
 		b[k] = k < P.n ? __ldg(P.a[k].start + 1) : 0u;
 		e[k] = (k < P.n && 1 < P.a[k].nb) ? __ldg(P.a[k].start + 2) : b[k];
 		pq[k] = -1; pm[k] = 0;
-		if (k < P.n && b[k] + tid < e[k]) { pq[k] = __ldg(P.a[k].order + b[k] + tid); pm[k] = ex_closer_mask(P.a[k], pq[k]); }
+		if (k < P.n && b[k] + tid < e[k]) { pq[k] = __ldg(P.a[k].order + b[k] + tid); pm[k] = __ldg(P.a[k].mask + b[k] + tid); }
 	}
 	for (int d = 1;; d++) {
 		bool more = false;
@@ -273,8 +277,14 @@ __global__ void __launch_bounds__(EX_THREADS, 3) k_ex_fill_layers(ExGrids P, uin
 		for (int k = 0; k < 3; k++) {
 			if (k >= P.n) continue;
 			more |= e[k] < tot[k];
-			if (pq[k] >= 0) ex_fill_node(P.a[k], pq[k], pm[k]);
-			for (uint32_t t = b[k] + tid + nthr; t < e[k]; t += nthr) { const int q = __ldg(P.a[k].order + t); ex_fill_node(P.a[k], q, ex_closer_mask(P.a[k], q)); }
+			// the list entry of the next iteration is fetched while this one's values are in flight
+			int q = pq[k], m = pm[k];
+			for (uint32_t t = b[k] + tid; t < e[k]; t += nthr) {
+				int nq = -1, nm = 0;
+				if (t + nthr < e[k]) { nq = __ldg(P.a[k].order + t + nthr); nm = __ldg(P.a[k].mask + t + nthr); }
+				ex_fill_node(P.a[k], q, m);
+				q = nq; m = nm;
+			}
 		}
 		if (!more) break;   // grid-uniform: every CTA reads the same starts
 #pragma unroll
@@ -282,7 +292,7 @@ __global__ void __launch_bounds__(EX_THREADS, 3) k_ex_fill_layers(ExGrids P, uin
 			b[k] = e[k];
 			e[k] = (k < P.n && d + 1 < P.a[k].nb) ? __ldg(P.a[k].start + d + 2) : b[k];
 			pq[k] = -1;
-			if (k < P.n && b[k] + tid < e[k]) { pq[k] = __ldg(P.a[k].order + b[k] + tid); pm[k] = ex_closer_mask(P.a[k], pq[k]); }
+			if (k < P.n && b[k] + tid < e[k]) { pq[k] = __ldg(P.a[k].order + b[k] + tid); pm[k] = __ldg(P.a[k].mask + b[k] + tid); }
 		}
 		// ---- grid barrier d ----
 		__syncthreads();
@@ -321,7 +331,7 @@ int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs) {
 	k_ex_hist<<<hb, 256, nb * sizeof(uint32_t), s->stream>>>(cd, n, hist, nb); FS3_LAUNCH_CHECK();
 	k_ex_scan<<<1, 32, 0, s->stream>>>(hist, start, cursor, nb); FS3_LAUNCH_CHECK();
 	size_t chunk = 8192;
-	k_ex_scatter<<<cdiv((long long)n, (long long)chunk), 256, 2 * nb * sizeof(uint32_t), s->stream>>>(cd, n, start, cursor, s->orderv[slot], nb, chunk);
+	k_ex_scatter<<<cdiv((long long)n, (long long)chunk), 256, 2 * nb * sizeof(uint32_t), s->stream>>>(cd, n, start, cursor, s->orderv[slot], s->exmask[slot], nb, chunk, xs, ys, zs);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
@@ -332,13 +342,20 @@ static int extrap_fill_layers(fs3_sim* s, int count, float* const* grids, const 
 	P.n = count;
 	for (int k = 0; k < count; k++) {
 		const uint32_t* base = s->bucket + (size_t)k * (3 * (size_t)s->bucket_cap + 2);
-		P.a[k] = ExGrid{grids[k], s->cdv[k], s->orderv[k], base + s->bucket_cap, dims[k][0], dims[k][1], dims[k][2], dims[k][0] + dims[k][1] + dims[k][2] + 1};
+		P.a[k] = ExGrid{grids[k], s->orderv[k], s->exmask[k], base + s->bucket_cap, dims[k][0], dims[k][1], dims[k][2], dims[k][0] + dims[k][1] + dims[k][2] + 1};
 	}
 	for (int k = count; k < 3; k++) P.a[k] = P.a[0];
 	FS3_CUDA(cudaMemsetAsync(s->ex_arrive, 0, sizeof(uint32_t), s->stream));
-	// one CTA per SM, all co-resident (the barrier needs that); 512 threads x <= 40 registers so that a CTA fits beside the two
-	// resident CTAs of the level-set sweep running on stream2
-	k_ex_fill_layers<<<s->sm_count, EX_THREADS, 0, s->stream>>>(P, s->ex_arrive); FS3_LAUNCH_CHECK();
+	// All CTAs co-resident (the barrier needs that).  One CTA per SM, 512 threads x <= 40 registers, fits beside the two
+	// resident CTAs of the level-set sweep running on stream2; FS3_EX_BLOCKS_PER_SM (debug) trades that overlap for threads.
+	static int occ = 0, forced = 0;
+	if (!occ) {
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ex_fill_layers, EX_THREADS, 0);
+		occ = std::max(1, occ);
+		if (const char* e = getenv("FS3_EX_BLOCKS_PER_SM")) forced = std::max(1, std::min(occ, atoi(e)));
+	}
+	const int per_sm = forced ? forced : 1;
+	k_ex_fill_layers<<<s->sm_count * per_sm, EX_THREADS, 0, s->stream>>>(P, s->ex_arrive); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 

@@ -211,6 +211,10 @@ __global__ void __launch_bounds__(256, FS3_SOR_MINB) k_sor_half(Sys<REAL> sy, in
 		}
 		return;
 	}
+	// (programmatic dependent launch as above; the wait comes first because the block counter and, in a lockstep group,
+	// the neighbours' flags are only valid once the previous kernel in the stream has completed)
+	asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+	asm volatile("griddepcontrol.wait;\n" ::: "memory");
 	if (threadIdx.x == 0 && sh.peer_flag[0]) fs3_flag_wait(sh.my_flag, sh.wait_epoch, sh.flags, sh.nospin);
 	if (threadIdx.x == 1 && sh.peer_flag[1]) fs3_flag_wait(sh.my_flag + 1, sh.wait_epoch, sh.flags, sh.nospin);
 	__syncthreads();
@@ -481,7 +485,17 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	// exclusive scan of the activity flags at the end of the first plane / the start of the last plane of the slab
 	sh.n_lo = s->sor_pos[c] + s->rb.plane * (size_t)(s->z0 + 2) / VEC;
 	sh.n_hi = s->sor_pos[c] + s->rb.plane * (size_t)s->z1 / VEC;
-	k_sor_half<REAL, VEC, true><<<nb, 256, 0, s->stream>>>(sy, c, omega, omo, s->sor_list[c], s->sor_count[c], sh); FS3_LAUNCH_CHECK();
+	{
+		cudaLaunchConfig_t cfg = {};
+		cfg.gridDim = dim3(nb); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
+		cudaLaunchAttribute at[1];
+		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+		at[0].val.programmaticStreamSerializationAllowed = 1;
+		cfg.attrs = at; cfg.numAttrs = k > 0 ? 1 : 0;
+		const uint32_t* lst = s->sor_list[c]; const uint32_t* cnt = s->sor_count[c];
+		FS3_CUDA(cudaLaunchKernelEx(&cfg, k_sor_half<REAL, VEC, true>, sy, c, omega, omo, lst, cnt, sh));
+		FS3_LAUNCH_CHECK();
+	}
 	s->sor_epoch = sh.signal_epoch;
 	return FS3_OK;
 }
