@@ -18,6 +18,7 @@ static std::string g_create_error;
 static int fail(fs3_sim* s, int code, const char* msg) { s->err = msg; return code; }
 
 static int ensure_particle_capacity(fs3_sim* s, long long count) {
+	if ((unsigned long long)count > (unsigned long long)s->nH) { s->err = "more particles than half-cells (8 per cell on average): not supported"; return FS3_ERR_INVALID; }
 	if (count <= s->cap) return FS3_OK;
 	if (s->arena) { s->err = "particle capacity of a sharded handle is fixed at creation"; return FS3_ERR_STATE; }
 	for (int k = 0; k < 2; k++) {
@@ -93,7 +94,7 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	s->prm.rho = 1000.0f; s->prm.gravity_y = -9.81f; s->prm.nu = 8.90f * 1e-4f / 1000.0f; s->prm.particle_radius = 1.0f;  // S3D.h:135-145
 	s->prm.record_stage_times = 0;
 	s->nU = (size_t)(nx + 1) * ny * nz; s->nV = (size_t)nx * (ny + 1) * nz; s->nW = (size_t)nx * ny * (nz + 1); s->nC = (size_t)nx * ny * nz;
-	s->launches = 0; s->np = 0; s->np_in = 0; s->cap = 0; s->cur = 0; s->sorted = false; s->closest_valid = false; s->system_valid = false;
+	s->launches = 0; s->np = 0; s->np_in = 0; s->cap = 0; s->cur = 0; s->sorted = false; s->counted = false; s->closest_valid = false; s->system_valid = false;
 	s->sor_list_valid = false; s->sm_count = prop.multiProcessorCount;
 	s->alloc_precision = -1; s->res_cap = 4096; s->res_count = 0; s->stage_ptr = nullptr; s->stage_bytes = 0;
 	s->rank = rank; s->world = world; s->z0 = rank * (nz / world); s->z1 = s->z0 + nz / world; s->lockstep = lockstep;

@@ -45,11 +45,12 @@ struct fs3_sim {
 	float4 *pos[2], *vel[2];
 	int cur;                 // which buffer holds the live particles
 	bool sorted;             // live buffer is half-cell-sorted and cell_start is valid
+	bool counted;            // Advect already produced cellid / arrival / cell_count of the live buffer (single GPU: fused)
 	size_t nH;               // 8*nC half-cells: the sort key is the particle's octant inside its cell, (2n)^3 grid, x fastest
 	uint32_t* cellid;        // per particle (live order), cell index
 	uint32_t* cell_count;    // nH+1
 	uint32_t* cell_start;    // nH+1 exclusive scan
-	uint32_t* cell_fill;     // nH cursor
+	uint32_t* cell_fill;     // per particle (live order): arrival order inside its half-cell (nH words >= any particle count)
 	int* tmp_id;             // per sorted slot: creation id (ranking key)
 	uint32_t* scan_block;    // block sums for the scan
 	size_t scan_block_cap;

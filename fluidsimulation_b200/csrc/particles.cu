@@ -68,7 +68,7 @@ int fs3i_reset_grids(fs3_sim* s) {
 	k_reset_grids<<<cdiv((long long)tot, 256 * 4), 256, 0, s->stream>>>(s->U, s->V, s->W, s->nU, s->nV, s->nW);
 	FS3_LAUNCH_CHECK();
 	s->cur = 0;
-	s->sorted = false;
+	s->sorted = false; s->counted = false;
 	s->closest_valid = false;
 	s->system_valid = false;
 	return FS3_OK;
@@ -126,13 +126,35 @@ __device__ __forceinline__ void mig_note(const MigArgs& m, long long i, float z)
 	}
 }
 
+// Half-cell key of a particle for the counting sort (see "Binning" below) and its count; shared by Advect (single GPU: the
+// sort's counting pass is fused into it) and k_bin_count.
+struct BinArgs {
+	uint32_t* cellid;    // per particle: half-cell key
+	uint32_t* arrival;   // per particle: arrival order inside the half-cell
+	uint32_t* count;     // per half-cell
+	int* flags;
+	int zlo, zhi;
+};
+__device__ __forceinline__ void bin_note(const BinArgs& B, long long i, float4 p, GridDims d) {
+	int cx, cy, cz;
+	int hx = fs3_halfcell_axis(p.x, (float)d.nx, cx), hy = fs3_halfcell_axis(p.y, (float)d.ny, cy), hz = fs3_halfcell_axis(p.z, (float)d.nz, cz);
+	if (cx < 0 || cx >= d.nx || cy < 0 || cy >= d.ny || cz < B.zlo || cz >= B.zhi) {
+		B.flags[0] = 1;  // outside the box (or the slab): the reference skips such particles; Advect's clamp makes this unreachable
+		hx = min(max(hx, 0), 2 * d.nx - 1); hy = min(max(hy, 0), 2 * d.ny - 1); hz = min(max(hz, 2 * B.zlo), 2 * B.zhi - 1);
+	}
+	uint32_t c = (uint32_t)hx + (uint32_t)(2 * d.nx) * ((uint32_t)hy + (uint32_t)(2 * d.ny) * (uint32_t)hz);
+	B.cellid[i] = c;
+	B.arrival[i] = atomicAdd(B.count + c, 1u);   // arrival order inside the half-cell: a unique provisional slot (the rank by creation id follows)
+}
+
 template <bool SHARD>
 __global__ void __launch_bounds__(256) k_advect(float4* __restrict__ pos, long long np, GridDims d, float dt,
-                                                const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W, MigArgs mig) {
+                                                const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W, MigArgs mig,
+                                                BinArgs bin) {
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	float4 p = pos[i];
-	if (__float_as_int(p.w) < 0) return;   // dead slot (emigrated)
+	if (__float_as_int(p.w) < 0) { if (!SHARD) bin.cellid[i] = 0xffffffffu; return; }   // dead slot (emigrated)
 	float fx = (float)d.nx, fy = (float)d.ny, fz = (float)d.nz;
 	float3 k1 = fs3_interp(U, V, W, d, __fmul_rn(fx, p.x), __fmul_rn(fy, p.y), __fmul_rn(fz, p.z));
 	float h = __fmul_rn(0.5f, dt);
@@ -154,6 +176,7 @@ __global__ void __launch_bounds__(256) k_advect(float4* __restrict__ pos, long l
 	p.z = fs3_clamp(p.z, (-0.5f + eps) / fz, __fadd_rn(1.0f, (-0.5f - eps) / fz));
 	pos[i] = p;
 	if (SHARD) mig_note(mig, i, p.z);
+	else bin_note(bin, i, p, d);
 }
 
 static MigArgs mig_args(fs3_sim* s) {
@@ -165,19 +188,23 @@ static MigArgs mig_args(fs3_sim* s) {
 
 int fs3i_advect(fs3_sim* s, float dt) {
 	GridDims d{s->nx, s->ny, s->nz};
-	s->sorted = false;
+	s->sorted = false; s->counted = false;
 	s->closest_valid = false;
 	if (s->world > 1) {
 		FS3_CUDA(cudaMemsetAsync(s->mig_ctl, 0, (2 * s->world + 1) * sizeof(uint32_t), s->stream));
 		if (s->np_in > 0) {
-			k_advect<true><<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->np_in, d, dt, s->U, s->V, s->W, mig_args(s));
+			k_advect<true><<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->np_in, d, dt, s->U, s->V, s->W, mig_args(s), BinArgs{});
 			FS3_LAUNCH_CHECK();
 		}
 		return FS3_OK;
 	}
 	if (s->np <= 0) return FS3_OK;
-	k_advect<false><<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, dt, s->U, s->V, s->W, MigArgs{});
+	// the counting pass of the sort that always follows is fused in (the new position is in registers)
+	FS3_CUDA(cudaMemsetAsync(s->cell_count, 0, (s->nH + 1) * sizeof(uint32_t), s->stream));
+	k_advect<false><<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, dt, s->U, s->V, s->W, MigArgs{},
+	                                                          BinArgs{s->cellid, s->cell_fill, s->cell_count, s->dev_flags, 0, s->nz});
 	FS3_LAUNCH_CHECK();
+	s->counted = true;
 	return FS3_OK;
 }
 
@@ -192,7 +219,7 @@ __global__ void __launch_bounds__(256) k_mig_mark(const float4* __restrict__ pos
 int fs3i_mig_mark(fs3_sim* s) {
 	FS3_CUDA(cudaMemsetAsync(s->mig_ctl, 0, (2 * s->world + 1) * sizeof(uint32_t), s->stream));
 	if (s->np_in > 0) { k_mig_mark<<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->np_in, mig_args(s)); FS3_LAUNCH_CHECK(); }
-	s->sorted = false;
+	s->sorted = false; s->counted = false;
 	return FS3_OK;
 }
 
@@ -228,21 +255,12 @@ int fs3i_mig_pack(fs3_sim* s) {
 // is deterministic (no dependence on atomic arrival order) and "lowest index wins" tie-breaks
 // (S3D.cpp:296) fall out of a forward scan of the cell's segment.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_bin_count(const float4* __restrict__ pos, long long np, GridDims d, int zlo, int zhi,
-                                                   uint32_t* __restrict__ cellid, uint32_t* __restrict__ count, int* __restrict__ flags) {
+__global__ void __launch_bounds__(256) k_bin_count(const float4* __restrict__ pos, long long np, GridDims d, BinArgs bin) {
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	float4 p = pos[i];
-	if (__float_as_int(p.w) < 0) { cellid[i] = 0xffffffffu; return; }   // dead slot of an emigrant
-	int cx, cy, cz;
-	int hx = fs3_halfcell_axis(p.x, (float)d.nx, cx), hy = fs3_halfcell_axis(p.y, (float)d.ny, cy), hz = fs3_halfcell_axis(p.z, (float)d.nz, cz);
-	if (cx < 0 || cx >= d.nx || cy < 0 || cy >= d.ny || cz < zlo || cz >= zhi) {
-		flags[0] = 1;  // outside the box (or the slab): the reference skips such particles; Advect's clamp makes this unreachable
-		hx = min(max(hx, 0), 2 * d.nx - 1); hy = min(max(hy, 0), 2 * d.ny - 1); hz = min(max(hz, 2 * zlo), 2 * zhi - 1);
-	}
-	uint32_t c = (uint32_t)hx + (uint32_t)(2 * d.nx) * ((uint32_t)hy + (uint32_t)(2 * d.ny) * (uint32_t)hz);
-	cellid[i] = c;
-	atomicAdd(count + c, 1u);
+	if (__float_as_int(p.w) < 0) { bin.cellid[i] = 0xffffffffu; return; }   // dead slot of an emigrant
+	bin_note(bin, i, p, d);
 }
 
 // --- exclusive scan of uint32 (reduce / scan block sums / apply), tile = 512 threads x 8 items ----
@@ -322,12 +340,12 @@ int fs3i_scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n, uint3
 }
 
 __global__ void __launch_bounds__(256) k_bin_scatter_ids(const float4* __restrict__ pos, const uint32_t* __restrict__ cellid, long long np,
-                                                         const uint32_t* __restrict__ start, uint32_t* __restrict__ fill, int* __restrict__ tmp_id) {
+                                                         const uint32_t* __restrict__ start, const uint32_t* __restrict__ arrival, int* __restrict__ tmp_id) {
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	uint32_t c = cellid[i];
 	if (c == 0xffffffffu) return;
-	uint32_t slot = start[c] + atomicAdd(fill + c, 1u);
+	uint32_t slot = start[c] + arrival[i];
 	tmp_id[slot] = __float_as_int(pos[i].w);
 }
 
@@ -355,13 +373,15 @@ int fs3i_bin(fs3_sim* s) {
 	if (s->sorted) return FS3_OK;
 	const size_t hplane = (size_t)(2 * s->nx) * (2 * s->ny);
 	const size_t K0 = hplane * (size_t)(2 * s->z0), K1 = hplane * (size_t)(2 * s->z1);
-	FS3_CUDA(cudaMemsetAsync(s->cell_count + K0, 0, (K1 - K0 + 1) * sizeof(uint32_t), s->stream));
-	FS3_CUDA(cudaMemsetAsync(s->cell_fill + K0, 0, (K1 - K0) * sizeof(uint32_t), s->stream));
+	if (!s->counted) FS3_CUDA(cudaMemsetAsync(s->cell_count + K0, 0, (K1 - K0 + 1) * sizeof(uint32_t), s->stream));
 	if (s->np_in > 0) {
 		GridDims d{s->nx, s->ny, s->nz};
 		int nb = cdiv(s->np_in, 256);
 		const float4 *pin = s->pos[s->cur] + s->poff, *vin = s->vel[s->cur] + s->poff;
-		k_bin_count<<<nb, 256, 0, s->stream>>>(pin, s->np_in, d, s->z0, s->z1, s->cellid, s->cell_count, s->dev_flags); FS3_LAUNCH_CHECK();
+		if (!s->counted) {
+			k_bin_count<<<nb, 256, 0, s->stream>>>(pin, s->np_in, d, BinArgs{s->cellid, s->cell_fill, s->cell_count, s->dev_flags, s->z0, s->z1});
+			FS3_LAUNCH_CHECK();
+		}
 		int rc = fs3i_scan_u32(s, s->cell_count + K0, s->cell_start + K0, K1 - K0 + 1, (uint32_t)s->poff);
 		if (rc) return rc;
 		k_bin_scatter_ids<<<nb, 256, 0, s->stream>>>(pin, s->cellid, s->np_in, s->cell_start, s->cell_fill, s->tmp_id); FS3_LAUNCH_CHECK();
@@ -374,6 +394,7 @@ int fs3i_bin(fs3_sim* s) {
 	}
 	s->np_in = s->np;
 	s->sorted = true;
+	s->counted = false;
 	return FS3_OK;
 }
 
@@ -411,7 +432,7 @@ int fs3i_unsort_particles(fs3_sim* s, fs3_particle* dev_out) {
 	return FS3_OK;
 }
 int fs3i_load_particles(fs3_sim* s, const fs3_particle* dev_in, long long count) {
-	s->np = s->np_in = count; s->cur = 0; s->sorted = false; s->closest_valid = false;
+	s->np = s->np_in = count; s->cur = 0; s->sorted = false; s->counted = false; s->closest_valid = false;
 	if (count <= 0) return FS3_OK;
 	k_load<<<cdiv(count, 256), 256, 0, s->stream>>>(dev_in, count, s->pos[0], s->vel[0]); FS3_LAUNCH_CHECK();
 	return FS3_OK;
@@ -431,7 +452,7 @@ __global__ void __launch_bounds__(256) k_load_owned(const fs3_particle* __restri
 	vel[k] = make_float4(q.uX, q.uY, q.uZ, 0.0f);
 }
 int fs3i_load_particles_owned(fs3_sim* s, const fs3_particle* dev_in, long long count) {
-	s->cur = 0; s->sorted = false; s->closest_valid = false;
+	s->cur = 0; s->sorted = false; s->counted = false; s->closest_valid = false;
 	FS3_CUDA(cudaMemsetAsync(s->mig_ctl, 0, (2 * s->world + 1) * sizeof(uint32_t), s->stream));
 	if (count > 0) {
 		k_load_owned<<<cdiv(count, 256), 256, 0, s->stream>>>(dev_in, count, mig_args(s), s->pos[0] + s->poff, s->vel[0] + s->poff, s->mig_ctl,
@@ -466,7 +487,7 @@ int fs3i_pack_local(fs3_sim* s, fs3_particle* dev_out, int* dev_ids) {
 	return FS3_OK;
 }
 int fs3i_load_local(fs3_sim* s, const fs3_particle* dev_in, const int* dev_ids, long long count) {
-	s->np = s->np_in = count; s->np_all[s->rank] = count; s->cur = 0; s->sorted = false; s->closest_valid = false;
+	s->np = s->np_in = count; s->np_all[s->rank] = count; s->cur = 0; s->sorted = false; s->counted = false; s->closest_valid = false;
 	if (count <= 0) return FS3_OK;
 	k_load_local<<<cdiv(count, 256), 256, 0, s->stream>>>(dev_in, dev_ids, count, s->pos[0] + s->poff, s->vel[0] + s->poff); FS3_LAUNCH_CHECK();
 	return FS3_OK;

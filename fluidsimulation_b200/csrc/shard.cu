@@ -174,7 +174,7 @@ int fs3i_mig_exchange(fs3_sim* s) {
 		s->np_all[d] = len - leave + arrive;
 	}
 	s->np = s->np_all[me];
-	s->sorted = false;
+	s->sorted = false; s->counted = false;
 	return FS3_OK;
 }
 
