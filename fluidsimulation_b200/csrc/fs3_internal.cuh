@@ -52,7 +52,7 @@ struct fs3_sim {
 	uint32_t* cell_start;    // nH+1 exclusive scan
 	uint32_t* cell_fill;     // per particle (live order): arrival order inside its half-cell (nH words >= any particle count)
 	int* tmp_id;             // per sorted slot: creation id (ranking key)
-	uint32_t* scan_block;    // block sums for the scan
+	uint32_t* scan_block;    // look-back scan scratch: scan_block_cap 64-bit tile states, then the ticket
 	size_t scan_block_cap;
 
 	// level set

@@ -295,47 +295,75 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total)
 	return base + inc - v;
 }
 
-__global__ void __launch_bounds__(SCAN_T) k_scan_reduce(const uint32_t* __restrict__ in, size_t n, uint32_t* __restrict__ bsum) {
-	size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_I;
-	uint32_t v = 0;
-#pragma unroll
-	for (int k = 0; k < SCAN_I; k++) if (base + k < n) v += in[base + k];
-	uint32_t tot;
-	block_excl_scan(v, &tot);
-	if (threadIdx.x == 0) bsum[blockIdx.x] = tot;
+// Single pass with decoupled look-back: tiles are handed out by a ticket (so a tile's predecessors are always running or
+// done), every tile publishes its aggregate, then its inclusive prefix, as (flag << 32 | value) words, and resolves its
+// own prefix by walking back over the predecessors' words.  The input is read once and the output written once.
+#define SCAN_AGG 1ull
+#define SCAN_INC 2ull
+__device__ __forceinline__ unsigned long long scan_ld(const unsigned long long* p) {
+	unsigned long long v;
+	asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];\n" : "=l"(v) : "l"(p) : "memory");
+	return v;
 }
-__global__ void __launch_bounds__(SCAN_T) k_scan_blocks(uint32_t* __restrict__ bsum, int nb) {
-	__shared__ uint32_t carry;
-	if (threadIdx.x == 0) carry = 0;
+__device__ __forceinline__ void scan_st(unsigned long long* p, unsigned long long v) { asm volatile("st.relaxed.gpu.global.u64 [%0], %1;\n" ::"l"(p), "l"(v) : "memory"); }
+
+__global__ void __launch_bounds__(SCAN_T) k_scan_lookback(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
+                                                          unsigned long long* __restrict__ state, uint32_t* __restrict__ ticket, uint32_t base0) {
+	__shared__ uint32_t s_tile, s_prefix;
+	if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
 	__syncthreads();
-	for (int b0 = 0; b0 < nb; b0 += SCAN_T) {
-		int i = b0 + threadIdx.x;
-		uint32_t v = i < nb ? bsum[i] : 0, tot;
-		uint32_t ex = block_excl_scan(v, &tot);
-		uint32_t c = carry;
-		if (i < nb) bsum[i] = ex + c;
-		__syncthreads();
-		if (threadIdx.x == 0) carry = c + tot;
-		__syncthreads();
-	}
-}
-__global__ void __launch_bounds__(SCAN_T) k_scan_apply(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
-                                                       const uint32_t* __restrict__ bsum, uint32_t base0) {
-	size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_I;
+	const uint32_t tile = s_tile;
+	const size_t base = (size_t)tile * SCAN_TILE + (size_t)threadIdx.x * SCAN_I;
 	uint32_t loc[SCAN_I], v = 0;
+	if (base + SCAN_I <= n && (reinterpret_cast<uintptr_t>(in + base) & 15) == 0) {
+		const uint4 a = *reinterpret_cast<const uint4*>(in + base), b = *reinterpret_cast<const uint4*>(in + base + 4);
+		loc[0] = a.x; loc[1] = a.y; loc[2] = a.z; loc[3] = a.w; loc[4] = b.x; loc[5] = b.y; loc[6] = b.z; loc[7] = b.w;
+	} else {
 #pragma unroll
-	for (int k = 0; k < SCAN_I; k++) { loc[k] = base + k < n ? in[base + k] : 0; v += loc[k]; }
-	uint32_t ex = block_excl_scan(v, nullptr) + bsum[blockIdx.x] + base0;
+		for (int k = 0; k < SCAN_I; k++) loc[k] = base + k < n ? in[base + k] : 0;
+	}
 #pragma unroll
-	for (int k = 0; k < SCAN_I; k++) { if (base + k < n) out[base + k] = ex; ex += loc[k]; }
+	for (int k = 0; k < SCAN_I; k++) v += loc[k];
+	uint32_t tot;
+	const uint32_t ex_in_tile = block_excl_scan(v, &tot);
+	if (threadIdx.x == 0) {
+		uint32_t prefix = 0;
+		if (tile == 0) {
+			scan_st(state, (SCAN_INC << 32) | tot);
+		} else {
+			scan_st(state + tile, (SCAN_AGG << 32) | tot);
+			for (uint32_t j = tile - 1;; j--) {
+				unsigned long long w;
+				do { w = scan_ld(state + j); } while ((w >> 32) == 0);
+				prefix += (uint32_t)w;
+				if ((w >> 32) == SCAN_INC) break;
+			}
+			scan_st(state + tile, (SCAN_INC << 32) | (uint32_t)(prefix + tot));
+		}
+		s_prefix = prefix;
+	}
+	__syncthreads();
+	uint32_t ex = ex_in_tile + s_prefix + base0;
+	if (base + SCAN_I <= n && (reinterpret_cast<uintptr_t>(out + base) & 15) == 0) {
+		uint4 a, b;
+		a.x = ex; ex += loc[0]; a.y = ex; ex += loc[1]; a.z = ex; ex += loc[2]; a.w = ex; ex += loc[3];
+		b.x = ex; ex += loc[4]; b.y = ex; ex += loc[5]; b.z = ex; ex += loc[6]; b.w = ex;
+		*reinterpret_cast<uint4*>(out + base) = a; *reinterpret_cast<uint4*>(out + base + 4) = b;
+	} else {
+#pragma unroll
+		for (int k = 0; k < SCAN_I; k++) { if (base + k < n) out[base + k] = ex; ex += loc[k]; }
+	}
 }
 
 int fs3i_scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n, uint32_t base0) {
 	int nb = cdiv((long long)n, SCAN_TILE);
 	if ((size_t)nb > s->scan_block_cap) { s->err = "scan scratch too small"; return FS3_ERR_STATE; }
-	k_scan_reduce<<<nb, SCAN_T, 0, s->stream>>>(in, n, s->scan_block); FS3_LAUNCH_CHECK();
-	k_scan_blocks<<<1, SCAN_T, 0, s->stream>>>(s->scan_block, nb); FS3_LAUNCH_CHECK();
-	k_scan_apply<<<nb, SCAN_T, 0, s->stream>>>(in, out, n, s->scan_block, base0); FS3_LAUNCH_CHECK();
+	// scratch: one 64-bit word per tile, then the ticket
+	unsigned long long* state = reinterpret_cast<unsigned long long*>(s->scan_block);
+	uint32_t* ticket = reinterpret_cast<uint32_t*>(state + s->scan_block_cap);
+	FS3_CUDA(cudaMemsetAsync(s->scan_block, 0, ((size_t)nb + 0) * 8, s->stream));
+	FS3_CUDA(cudaMemsetAsync(ticket, 0, 4, s->stream));
+	k_scan_lookback<<<nb, SCAN_T, 0, s->stream>>>(in, out, n, state, ticket, base0); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 

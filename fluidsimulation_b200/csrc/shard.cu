@@ -28,7 +28,7 @@ size_t fs3i_arena_bytes(int n, long long ptot, long long mig_cap, int world) {
 	size_t t = 0;
 	t += 6 * up512(nF * 4) + up512(nC * 4);                                   // U V W oU oV oW phi
 	t += 2 * up512((nH + 1) * 4) + up512(nH * 4);                             // cell_count, cell_start, cell_fill
-	t += up512(((nH + 1) / 4096 + 2) * 4);                                    // scan_block
+	t += up512(((nH + 1) / 4096 + 2) * 8 + 16);                               // scan_block
 	t += up512(nC * 16) + up512(nC * 4);                                      // ls_rec, closest
 	t += 6 * up512(nF * 4) + 3 * up512(nF);                                   // cdv, orderv, exmask
 	t += up512(3 * (3 * (3 * N + 8) + 2) * 4) + up512(16 * 2 * 4096) + 512;   // bucket, res, dev_flags
