@@ -211,21 +211,20 @@ __global__ void __launch_bounds__(256, FS3_SOR_MINB) k_sor_half(Sys<REAL> sy, in
 		}
 		return;
 	}
-	// (programmatic dependent launch as above; the wait comes first because the block counter and, in a lockstep group,
-	// the neighbours' flags are only valid once the previous kernel in the stream has completed)
-	asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
-	asm volatile("griddepcontrol.wait;\n" ::: "memory");
-	if (threadIdx.x == 0 && sh.peer_flag[0]) fs3_flag_wait(sh.my_flag, sh.wait_epoch, sh.flags, sh.nospin);
-	if (threadIdx.x == 1 && sh.peer_flag[1]) fs3_flag_wait(sh.my_flag + 1, sh.wait_epoch, sh.flags, sh.nospin);
-	__syncthreads();
+	// Boundary blocks and interior blocks are disjoint: only the vectors of the slab's first and last plane read the
+	// neighbours' ghost planes, so only the blocks that sweep them wait for the neighbours' epoch, and the system-scope
+	// fence + signal that follow their stores stay off the interior blocks' path.
 	const uint32_t n_lo = __ldg(sh.n_lo), n_hi = __ldg(sh.n_hi), B = n_lo + (n - n_hi);
-	bool pushed = false;
-	for (uint32_t t = gtid; t < B; t += G) {
-		sor_vector<REAL, VEC, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
-		pushed = true;
-	}
-	const uint32_t nbb = min(gridDim.x, max(1u, (B + blockDim.x - 1) / blockDim.x));   // blocks that hold boundary work
-	if (blockIdx.x < nbb) {
+	const uint32_t nbb = min(max(gridDim.x / 4u, 1u), max(1u, (B + blockDim.x - 1) / blockDim.x));   // blocks that hold the boundary work
+	if (blockIdx.x < nbb || gridDim.x == 1) {
+		if (threadIdx.x == 0 && sh.peer_flag[0]) fs3_flag_wait(sh.my_flag, sh.wait_epoch, sh.flags, sh.nospin);
+		if (threadIdx.x == 1 && sh.peer_flag[1]) fs3_flag_wait(sh.my_flag + 1, sh.wait_epoch, sh.flags, sh.nospin);
+		__syncthreads();
+		bool pushed = false;
+		for (uint32_t t = gtid; t < B; t += nbb * blockDim.x) {
+			sor_vector<REAL, VEC, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
+			pushed = true;
+		}
 		if (pushed) __threadfence_system();   // my peer stores are visible system-wide before the block reports in
 		__syncthreads();
 		if (threadIdx.x == 0) {
@@ -237,8 +236,11 @@ __global__ void __launch_bounds__(256, FS3_SOR_MINB) k_sor_half(Sys<REAL> sy, in
 				if (sh.peer_flag[1]) fs3_st_release_sys(sh.peer_flag[1], sh.signal_epoch);
 			}
 		}
+		if (gridDim.x > 1) return;
 	}
-	for (uint32_t t = gtid; t < n - B; t += G) sor_vector<REAL, VEC, false>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
+	// interior: the remaining blocks (all of a one-block grid)
+	const uint32_t ib = gridDim.x == 1 ? 0u : blockIdx.x - nbb, IG = gridDim.x == 1 ? blockDim.x : (gridDim.x - nbb) * blockDim.x;
+	for (uint32_t t = ib * blockDim.x + threadIdx.x; t < n - B; t += IG) sor_vector<REAL, VEC, false>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
 }
 
 // active-vector flags (+1 trailing zero so that the exclusive scan's last entry is the count) and compaction
@@ -485,17 +487,7 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	// exclusive scan of the activity flags at the end of the first plane / the start of the last plane of the slab
 	sh.n_lo = s->sor_pos[c] + s->rb.plane * (size_t)(s->z0 + 2) / VEC;
 	sh.n_hi = s->sor_pos[c] + s->rb.plane * (size_t)s->z1 / VEC;
-	{
-		cudaLaunchConfig_t cfg = {};
-		cfg.gridDim = dim3(nb); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
-		cudaLaunchAttribute at[1];
-		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-		at[0].val.programmaticStreamSerializationAllowed = 1;
-		cfg.attrs = at; cfg.numAttrs = k > 0 ? 1 : 0;
-		const uint32_t* lst = s->sor_list[c]; const uint32_t* cnt = s->sor_count[c];
-		FS3_CUDA(cudaLaunchKernelEx(&cfg, k_sor_half<REAL, VEC, true>, sy, c, omega, omo, lst, cnt, sh));
-		FS3_LAUNCH_CHECK();
-	}
+	k_sor_half<REAL, VEC, true><<<nb, 256, 0, s->stream>>>(sy, c, omega, omo, s->sor_list[c], s->sor_count[c], sh); FS3_LAUNCH_CHECK();
 	s->sor_epoch = sh.signal_epoch;
 	return FS3_OK;
 }

@@ -81,11 +81,12 @@ __global__ void k_bar_wait(const uint32_t* bar, int rank, int world, uint32_t ep
 	const int r = threadIdx.x;
 	if (r < world && r != rank) fs3_flag_wait(bar + r, epoch, flags, nospin);
 }
-int fs3i_signal(fs3_sim* s) {
+// st: the stream the publication is ordered on (default: the handle's main stream)
+int fs3i_signal(fs3_sim* s, cudaStream_t st) {
 	PeerPtrs pp;
 	for (int r = 0; r < s->world; r++) pp.p[r] = fs3_peer(s, r, s->bar);
 	s->bar_epoch++;
-	k_bar_signal<<<1, 32, 0, s->stream>>>(pp, s->rank, s->world, s->bar_epoch); FS3_LAUNCH_CHECK();
+	k_bar_signal<<<1, 32, 0, st ? st : s->stream>>>(pp, s->rank, s->world, s->bar_epoch); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 int fs3i_wait(fs3_sim* s) {
@@ -93,12 +94,30 @@ int fs3i_wait(fs3_sim* s) {
 	return FS3_OK;
 }
 
-int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes) {
+int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes, cudaStream_t st) {
 	if (!bytes) return FS3_OK;
 	for (int k = 1; k < s->world; k++) {
 		const int r = (s->rank + k) % s->world;   // staggered so that the ranks do not all target the same peer at once
-		FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, r, (char*)ptr) + byte_off, (char*)ptr + byte_off, bytes, cudaMemcpyDefault, s->stream));
+		FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, r, (char*)ptr) + byte_off, (char*)ptr + byte_off, bytes, cudaMemcpyDefault, st ? st : s->stream));
 	}
+	return FS3_OK;
+}
+
+// Slab all-gathers that the next kernels of this rank do not depend on go to stream2, behind everything queued on the main
+// stream so far: the copies (and the barrier signal that follows them) overlap this rank's next kernels.  A lockstep group
+// keeps them on the shared stream, where stream order is what satisfies the other ranks' waits.
+static int xfer_begin(fs3_sim* s, cudaStream_t* st) {
+	if (s->lockstep) { *st = s->stream; return FS3_OK; }
+	FS3_CUDA(cudaEventRecord(s->ev_fork, s->stream));
+	FS3_CUDA(cudaStreamWaitEvent(s->stream2, s->ev_fork, 0));
+	*st = s->stream2;
+	return FS3_OK;
+}
+// main stream waits until everything queued on stream2 so far has completed (before it overwrites what was being sent)
+static int xfer_join(fs3_sim* s) {
+	if (s->lockstep) return FS3_OK;
+	FS3_CUDA(cudaEventRecord(s->ev_xfer, s->stream2));
+	FS3_CUDA(cudaStreamWaitEvent(s->stream, s->ev_xfer, 0));
 	return FS3_OK;
 }
 
@@ -216,8 +235,8 @@ static float flip_alpha(const fs3_sim* s, float dt) {
 }
 
 // slab of a z-slowest array: element range [plane*za, plane*zb)
-static int push_planes(fs3_sim* s, void* arr, size_t plane_elems, size_t elem_bytes, int za, int zb) {
-	return fs3i_push(s, arr, plane_elems * elem_bytes * (size_t)za, plane_elems * elem_bytes * (size_t)(zb - za));
+static int push_planes(fs3_sim* s, void* arr, size_t plane_elems, size_t elem_bytes, int za, int zb, cudaStream_t st = nullptr) {
+	return fs3i_push(s, arr, plane_elems * elem_bytes * (size_t)za, plane_elems * elem_bytes * (size_t)(zb - za), st);
 }
 
 int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
@@ -241,23 +260,27 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 		if ((rc = fs3i_bin(s))) return rc;
 		return fs3i_signal(s);
 	}
-	if (ph == 3) {          // neighbours are sorted: ghost layers; level-set seed of the slab, gathered on every rank
+	if (ph == 3) {          // neighbours are sorted: ghost layers; level-set seed of the slab, gathered on every rank (stream2)
 		if ((rc = fs3i_wait(s)) || (rc = fs3i_ghost_pull(s)) || (rc = fs3i_levelset_seed(s))) return rc;
-		if ((rc = push_planes(s, s->ls_rec, pC, sizeof(float4), s->z0, s->z1))) return rc;
-		return fs3i_signal(s);
+		cudaStream_t xs;
+		if ((rc = xfer_begin(s, &xs)) || (rc = push_planes(s, s->ls_rec, pC, sizeof(float4), s->z0, s->z1, xs))) return rc;
+		return fs3i_signal(s, xs);
 	}
-	if (ph == 4) {          // P2G of the slab's face nodes, gathered on every rank
+	if (ph == 4) {          // P2G of the slab's face nodes (overlaps the seed gather), gathered on every rank (stream2)
 		if ((rc = fs3i_p2g_gather(s))) return rc;   // no wait: the gather reads this rank's particles + ghost layers only
 		const int zw = s->z1 + (last ? 1 : 0);
-		if ((rc = push_planes(s, s->oU, pU, 4, s->z0, s->z1)) || (rc = push_planes(s, s->oV, pV, 4, s->z0, s->z1)) ||
-		    (rc = push_planes(s, s->oW, pW, 4, s->z0, zw)) || (rc = push_planes(s, s->cdv[0], pU, 4, s->z0, s->z1)) ||
-		    (rc = push_planes(s, s->cdv[1], pV, 4, s->z0, s->z1)) || (rc = push_planes(s, s->cdv[2], pW, 4, s->z0, zw)))
+		cudaStream_t xs;
+		if ((rc = xfer_begin(s, &xs))) return rc;
+		if ((rc = push_planes(s, s->oU, pU, 4, s->z0, s->z1, xs)) || (rc = push_planes(s, s->oV, pV, 4, s->z0, s->z1, xs)) ||
+		    (rc = push_planes(s, s->oW, pW, 4, s->z0, zw, xs)) || (rc = push_planes(s, s->cdv[0], pU, 4, s->z0, s->z1, xs)) ||
+		    (rc = push_planes(s, s->cdv[1], pV, 4, s->z0, s->z1, xs)) || (rc = push_planes(s, s->cdv[2], pW, 4, s->z0, zw, xs)))
 			return rc;
-		return fs3i_signal(s);
+		return fs3i_signal(s, xs);
 	}
 	if (ph == 5) {          // 8 sweeps on stream2 beside the extrapolation (both replicated); pressure system of the slab; tell the neighbours it is set up
-		if ((rc = fs3i_wait(s)) || (rc = fs3i_levelset_fork(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_levelset_join(s)) || (rc = fs3i_project_setup(s, dt, true, true)) ||
-		    (rc = fs3i_sor_prepare(s)))
+		// own outgoing copies are complete before the replicated stages overwrite the arrays they read (the sweeps run on stream2, behind them)
+		if ((rc = xfer_join(s)) || (rc = fs3i_wait(s)) || (rc = fs3i_levelset_fork(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_levelset_join(s)) ||
+		    (rc = fs3i_project_setup(s, dt, true, true)) || (rc = fs3i_sor_prepare(s)))
 			return rc;
 		if ((rc = fs3i_sor_signal(s))) return rc;
 		if (T) cudaEventRecord(s->ev[FS3_T_PROJECT_SOR], s->stream);
