@@ -147,7 +147,7 @@ def test_extrapolate_bitexact(dims):
         assert same(sim.extrapolate(src, valid, *dims), ora.extrapolate(src, valid, *dims))
 
 
-@pytest.mark.parametrize("n,steps,tol", [(16, 1, 1e-5), (16, 5, 1e-5), (32, 2, 1e-5), (32, 10, 1e-4)])
+@pytest.mark.parametrize("n,steps,tol", [(16, 1, 1e-5), (16, 5, 1e-5), (32, 2, 1e-5), (32, 10, 1e-4), (64, 1, 1e-5)])   # 64^3 = BASELINE.json configs[1]
 def test_free_running_steps(n, steps, tol):
     sim, ora = mk(n), Oracle(n)
     for _ in range(steps):
@@ -220,7 +220,7 @@ def test_errors():
         sim.get_closest()            # no level set yet
 
 
-@pytest.mark.parametrize("n", [64, 128])
+@pytest.mark.parametrize("n", [64, 128, 256])   # 256^3 = the bench configuration (BASELINE.json configs[3])
 def test_full_size_properties(n):
     """Size-independent properties at sizes the oracle is too slow for."""
     sim = mk(n)

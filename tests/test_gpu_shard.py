@@ -54,7 +54,7 @@ def test_group_reset_bitexact(n, world):
     g.close()
 
 
-@pytest.mark.parametrize("n,world,steps", [(16, 2, 3), (16, 4, 2), (24, 2, 4), (24, 3, 2), (32, 4, 6)])
+@pytest.mark.parametrize("n,world,steps", [(16, 2, 3), (16, 4, 2), (24, 2, 4), (24, 3, 2), (32, 4, 6), (96, 4, 2)])
 def test_group_steps_bitexact_vs_single_gpu(n, world, steps):
     g, one = mkg(n, world), mk(n)
     for k in range(steps):
