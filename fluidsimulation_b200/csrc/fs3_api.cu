@@ -120,6 +120,7 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	else { CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)); s->owns_stream = true; }
 	for (int k = 0; k < FS3_T_COUNT + 2; k++) CK(cudaEventCreate(&s->ev[k]));
 	CK(cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking));
+	CK(cudaStreamCreateWithFlags(&s->stream3, cudaStreamNonBlocking));
 	CK(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming)); CK(cudaEventCreate(&s->ev_ls_end)); CK(cudaEventCreateWithFlags(&s->ev_xfer, cudaEventDisableTiming));
 	if (world > 1) {
 		s->arena_bytes = fs3i_arena_bytes(nx, ptot, s->mig_cap, world);
@@ -268,6 +269,7 @@ int fs3_destroy(fs3_sim* s) {
 	cudaSetDevice(s->device);
 	if (s->stream) cudaStreamSynchronize(s->stream);
 	if (s->stream2) { cudaStreamSynchronize(s->stream2); cudaStreamDestroy(s->stream2); }
+	if (s->stream3) { cudaStreamSynchronize(s->stream3); cudaStreamDestroy(s->stream3); }
 	if (s->ev_fork) cudaEventDestroy(s->ev_fork); if (s->ev_join) cudaEventDestroy(s->ev_join); if (s->ev_ls_end) cudaEventDestroy(s->ev_ls_end); if (s->ev_xfer) cudaEventDestroy(s->ev_xfer);
 	if (s->arena) {
 		for (int r = 0; r < s->world; r++) if (!s->lockstep && r != s->rank && s->peer_base[r]) cudaIpcCloseMemHandle(s->peer_base[r]);

@@ -125,7 +125,8 @@ struct fs3_sim {
 	size_t stage_bytes;
 	cudaEvent_t ev[FS3_T_COUNT + 2];
 	// the 8 level-set sweeps are latency-bound and independent of P2G + extrapolation: inside a step they run on a second stream
-	cudaStream_t stream2;
+	cudaStream_t stream2;    // level-set sweeps
+	cudaStream_t stream3;    // sharded handles: slab all-gathers (copies + the barrier signal that follows them)
 	cudaEvent_t ev_fork, ev_join, ev_ls_end, ev_xfer;
 	bool ls_forked;          // sweeps of the current step are in flight on stream2
 	bool ls_overlapped;      // the last step's LEVELSET_SWEEP time is (ev[LEVELSET_SWEEP], ev_ls_end) on stream2
@@ -286,7 +287,7 @@ int fs3i_project_gradient(fs3_sim* s, float dt, bool from_old, bool with_gravity
 // levelset.cu / p2g.cu pieces
 int fs3i_levelset_seed(fs3_sim* s);
 int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st = nullptr);                // st: stream to run on (default: the handle's)
-int fs3i_levelset_fork(fs3_sim* s);                                          // sweeps on stream2, after everything queued so far
+int fs3i_levelset_fork(fs3_sim* s, bool after_barrier = false);              // sweeps on stream2, after everything queued so far (and, sharded, after the current barrier epoch)
 int fs3i_levelset_join(fs3_sim* s);                                          // main stream waits for them
 int fs3i_p2g_gather(fs3_sim* s);
 void fs3i_p2g_range(const fs3_sim* s, int ax, size_t* q0, size_t* q1);
@@ -294,7 +295,7 @@ int fs3i_extrapolate_all(fs3_sim* s);
 // shard.cu
 int fs3i_shard_alloc(fs3_sim* s);
 int fs3i_signal(fs3_sim* s, cudaStream_t st = nullptr);                      // barrier, first half: publish my epoch to all ranks
-int fs3i_wait(fs3_sim* s);                                                  // barrier, second half: all ranks reached my epoch
+int fs3i_wait(fs3_sim* s, cudaStream_t st = nullptr);                        // barrier, second half: all ranks reached my epoch
 int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes, cudaStream_t st = nullptr);   // copy a range of one of my arrays into the same range of every peer
 int fs3i_sor_signal(fs3_sim* s);                                            // "system set up": first SOR epoch of this projection to both neighbours
 int fs3i_sor_wait(fs3_sim* s, uint32_t epoch);

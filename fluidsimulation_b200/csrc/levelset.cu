@@ -392,11 +392,14 @@ int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st) {
 
 // The sweeps only touch ls_rec / phi / closest, which nothing else reads before the pressure system is set up: inside a step
 // they overlap the P2G gather and the extrapolation (both bandwidth / issue bound, while the sweeps wait on tile dependencies).
-int fs3i_levelset_fork(fs3_sim* s) {
+int fs3i_levelset_fork(fs3_sim* s, bool after_barrier) {
 	FS3_CUDA(cudaEventRecord(s->ev_fork, s->stream));
 	FS3_CUDA(cudaStreamWaitEvent(s->stream2, s->ev_fork, 0));
-	int rc = fs3i_levelset_sweeps(s, s->stream2);
-	if (rc) return rc;
+	int rc;
+	// sharded: the gathered seed records are complete once every rank has published the current barrier epoch; that wait
+	// sits on stream2 too, so the main stream goes on with the P2G gather meanwhile
+	if (after_barrier && (rc = fs3i_wait(s, s->stream2))) return rc;
+	if ((rc = fs3i_levelset_sweeps(s, s->stream2))) return rc;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev_ls_end, s->stream2);
 	FS3_CUDA(cudaEventRecord(s->ev_join, s->stream2));
 	s->ls_forked = true;

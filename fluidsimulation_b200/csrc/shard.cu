@@ -89,8 +89,8 @@ int fs3i_signal(fs3_sim* s, cudaStream_t st) {
 	k_bar_signal<<<1, 32, 0, st ? st : s->stream>>>(pp, s->rank, s->world, s->bar_epoch); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
-int fs3i_wait(fs3_sim* s) {
-	k_bar_wait<<<1, 32, 0, s->stream>>>(s->bar, s->rank, s->world, s->bar_epoch, s->dev_flags, s->lockstep ? 1 : 0); FS3_LAUNCH_CHECK();
+int fs3i_wait(fs3_sim* s, cudaStream_t st) {
+	k_bar_wait<<<1, 32, 0, st ? st : s->stream>>>(s->bar, s->rank, s->world, s->bar_epoch, s->dev_flags, s->lockstep ? 1 : 0); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 
@@ -103,20 +103,20 @@ int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes, cudaStream_t
 	return FS3_OK;
 }
 
-// Slab all-gathers that the next kernels of this rank do not depend on go to stream2, behind everything queued on the main
+// Slab all-gathers that the next kernels of this rank do not depend on go to stream3, behind everything queued on the main
 // stream so far: the copies (and the barrier signal that follows them) overlap this rank's next kernels.  A lockstep group
 // keeps them on the shared stream, where stream order is what satisfies the other ranks' waits.
 static int xfer_begin(fs3_sim* s, cudaStream_t* st) {
 	if (s->lockstep) { *st = s->stream; return FS3_OK; }
 	FS3_CUDA(cudaEventRecord(s->ev_fork, s->stream));
-	FS3_CUDA(cudaStreamWaitEvent(s->stream2, s->ev_fork, 0));
-	*st = s->stream2;
+	FS3_CUDA(cudaStreamWaitEvent(s->stream3, s->ev_fork, 0));
+	*st = s->stream3;
 	return FS3_OK;
 }
-// main stream waits until everything queued on stream2 so far has completed (before it overwrites what was being sent)
+// main stream waits until everything queued on stream3 so far has completed (before it overwrites what was being sent)
 static int xfer_join(fs3_sim* s) {
 	if (s->lockstep) return FS3_OK;
-	FS3_CUDA(cudaEventRecord(s->ev_xfer, s->stream2));
+	FS3_CUDA(cudaEventRecord(s->ev_xfer, s->stream3));
 	FS3_CUDA(cudaStreamWaitEvent(s->stream, s->ev_xfer, 0));
 	return FS3_OK;
 }
@@ -260,14 +260,19 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 		if ((rc = fs3i_bin(s))) return rc;
 		return fs3i_signal(s);
 	}
-	if (ph == 3) {          // neighbours are sorted: ghost layers; level-set seed of the slab, gathered on every rank (stream2)
+	if (ph == 3) {          // neighbours are sorted: ghost layers; level-set seed of the slab, gathered on every rank (stream3)
 		if ((rc = fs3i_wait(s)) || (rc = fs3i_ghost_pull(s)) || (rc = fs3i_levelset_seed(s))) return rc;
 		cudaStream_t xs;
 		if ((rc = xfer_begin(s, &xs)) || (rc = push_planes(s, s->ls_rec, pC, sizeof(float4), s->z0, s->z1, xs))) return rc;
-		return fs3i_signal(s, xs);
+		if ((rc = fs3i_signal(s, xs))) return rc;
+		// this rank's seed records have left before the sweeps (which update ls_rec in place) may start
+		if (!s->lockstep) { FS3_CUDA(cudaEventRecord(s->ev_xfer, s->stream3)); FS3_CUDA(cudaStreamWaitEvent(s->stream2, s->ev_xfer, 0)); }
+		return FS3_OK;
 	}
-	if (ph == 4) {          // P2G of the slab's face nodes (overlaps the seed gather), gathered on every rank (stream2)
-		if ((rc = fs3i_p2g_gather(s))) return rc;   // no wait: the gather reads this rank's particles + ghost layers only
+	if (ph == 4) {          // the 8 sweeps start on stream2 as soon as every rank's seeds are here (replicated); meanwhile P2G of
+		                    // the slab's face nodes on the main stream, gathered on every rank (stream3)
+		if ((rc = fs3i_levelset_fork(s, true))) return rc;
+		if ((rc = fs3i_p2g_gather(s))) return rc;   // no wait on the main stream: the gather reads this rank's particles + ghost layers only
 		const int zw = s->z1 + (last ? 1 : 0);
 		cudaStream_t xs;
 		if ((rc = xfer_begin(s, &xs))) return rc;
@@ -277,9 +282,9 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 			return rc;
 		return fs3i_signal(s, xs);
 	}
-	if (ph == 5) {          // 8 sweeps on stream2 beside the extrapolation (both replicated); pressure system of the slab; tell the neighbours it is set up
-		// own outgoing copies are complete before the replicated stages overwrite the arrays they read (the sweeps run on stream2, behind them)
-		if ((rc = xfer_join(s)) || (rc = fs3i_wait(s)) || (rc = fs3i_levelset_fork(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_levelset_join(s)) ||
+	if (ph == 5) {          // extrapolation (replicated) beside the sweeps; pressure system of the slab; tell the neighbours it is set up
+		// own outgoing copies are complete before the extrapolation overwrites the arrays they read
+		if ((rc = xfer_join(s)) || (rc = fs3i_wait(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_levelset_join(s)) ||
 		    (rc = fs3i_project_setup(s, dt, true, true)) || (rc = fs3i_sor_prepare(s)))
 			return rc;
 		if ((rc = fs3i_sor_signal(s))) return rc;
