@@ -290,6 +290,8 @@ int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st = nullptr);                
 int fs3i_levelset_fork(fs3_sim* s, bool after_barrier = false);              // sweeps on stream2, after everything queued so far (and, sharded, after the current barrier epoch)
 int fs3i_levelset_join(fs3_sim* s);                                          // main stream waits for them
 int fs3i_p2g_gather(fs3_sim* s);
+int fs3i_p2g_gather_axis(fs3_sim* s, int ax);                                // one face grid of the slab
+int fs3i_cd_from_tags(fs3_sim* s);                                           // sharded: validity of the other slabs' nodes from the gathered grids
 void fs3i_p2g_range(const fs3_sim* s, int ax, size_t* q0, size_t* q1);
 int fs3i_extrapolate_all(fs3_sim* s);
 // shard.cu

@@ -19,13 +19,14 @@
 // along x, so the 8 nodes walk 6 x 6 particle runs of 6 half-cells instead of 8 x 16 runs of 4, and a CTA of
 // 32 x 2 x 2 threads (64 x 4 x 4 nodes) re-reads each half-row from L1 rather than L2.  Every node still sees its particles in the order (hz, hy, run) of the one-node-per-thread
 // formulation, so the sums are bit-identical to it (and independent of how the grid is cut into slabs).
+#define FS3_INVALID_TAG 0x7fc0f53a   // a quiet NaN no arithmetic produces
 #define P2G_KX 2
 #define P2G_KY 2
 #define P2G_KZ 2
 template <int AX>
 __global__ void __launch_bounds__(128) k_p2g_gather(const float4* __restrict__ pos, const float4* __restrict__ vel,
                                                     const uint32_t* __restrict__ start, GridDims d, float cpm, float* __restrict__ grid,
-                                                    int* __restrict__ cd, int kbeg, int kend) {
+                                                    int* __restrict__ cd, int kbeg, int kend, int tag_invalid) {
 	const int xs = d.nx + (AX == 0), ys = d.ny + (AX == 1);
 	const int i0 = (blockIdx.x * 32 + (threadIdx.x & 31)) * P2G_KX;
 	const int j0 = (blockIdx.y * 2 + ((threadIdx.x >> 5) & 1)) * P2G_KY;
@@ -103,8 +104,11 @@ __global__ void __launch_bounds__(128) k_p2g_gather(const float4* __restrict__ p
 				// wall planes: forced to zero and valid (S3D.cpp:578-599)
 				const int m_ax = AX == 0 ? i : (AX == 1 ? j : k), n_ax = AX == 0 ? d.nx : (AX == 1 ? d.ny : d.nz);
 				if (m_ax == 0 || m_ax == n_ax) { grid[q] = 0.f; cd[q] = 0; continue; }
-				grid[q] = __fdiv_rn(sum[c][bb][a], __fadd_rn(tiny, amt[c][bb][a]));
-				cd[q] = amt[c][bb][a] > 0.01f ? 0 : FS3_INF_CD;  // S3D.cpp:565-575
+				const bool valid = amt[c][bb][a] > 0.01f;  // S3D.cpp:565-575
+				// The value of an invalid node is dead (the extrapolation overwrites every such node).  A sharded handle stores
+				// a tagged NaN there instead, so that the slab all-gather carries the validity with the grid (fs3i_cd_from_tags).
+				grid[q] = (!valid && tag_invalid) ? __int_as_float(FS3_INVALID_TAG) : __fdiv_rn(sum[c][bb][a], __fadd_rn(tiny, amt[c][bb][a]));
+				cd[q] = valid ? 0 : FS3_INF_CD;
 			}
 }
 
@@ -384,16 +388,40 @@ template <int AX> static int p2g_launch(fs3_sim* s, float* grid, int* cd) {
 	const int xs = s->nx + (AX == 0), ys = s->ny + (AX == 1);
 	const int kbeg = s->z0, kend = s->z1 + ((AX == 2 && s->rank == s->world - 1) ? 1 : 0);
 	dim3 g(cdiv(xs, 32 * P2G_KX), cdiv(ys, 2 * P2G_KY), cdiv(kend - kbeg, 2 * P2G_KZ));
-	k_p2g_gather<AX><<<g, 128, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->cell_start, d, s->cpm, grid, cd, kbeg, kend);
+	k_p2g_gather<AX><<<g, 128, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->cell_start, d, s->cpm, grid, cd, kbeg, kend, s->world > 1 ? 1 : 0);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 
-int fs3i_p2g_gather(fs3_sim* s) {
+// one face grid (0: U, 1: V, 2: W) of this rank's slab
+int fs3i_p2g_gather_axis(fs3_sim* s, int ax) {
 	// P2G writes the "old" set; the projected field is produced from it by fs3i_project (no copy, S3D.cpp:123-134)
-	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_P2G], s->stream);
+	if (ax == 0 && s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_P2G], s->stream);
+	return ax == 0 ? p2g_launch<0>(s, s->oU, s->cdv[0]) : ax == 1 ? p2g_launch<1>(s, s->oV, s->cdv[1]) : p2g_launch<2>(s, s->oW, s->cdv[2]);
+}
+int fs3i_p2g_gather(fs3_sim* s) {
 	int rc;
-	if ((rc = p2g_launch<0>(s, s->oU, s->cdv[0])) || (rc = p2g_launch<1>(s, s->oV, s->cdv[1])) || (rc = p2g_launch<2>(s, s->oW, s->cdv[2]))) return rc;
+	if ((rc = fs3i_p2g_gather_axis(s, 0)) || (rc = fs3i_p2g_gather_axis(s, 1)) || (rc = fs3i_p2g_gather_axis(s, 2))) return rc;
+	return FS3_OK;
+}
+
+// Sharded: validity (cd = 0 / inf) of the face nodes OUTSIDE this rank's slab from the tags in the gathered grids.
+__global__ void __launch_bounds__(256) k_cd_from_tags(const float* __restrict__ grid, int* __restrict__ cd, size_t n, size_t own0, size_t own1) {
+	size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (q >= n - (own1 - own0)) return;
+	if (q >= own0) q += own1 - own0;
+	cd[q] = __float_as_int(grid[q]) == FS3_INVALID_TAG ? FS3_INF_CD : 0;
+}
+int fs3i_cd_from_tags(fs3_sim* s) {
+	float* g[3] = {s->oU, s->oV, s->oW};
+	const size_t nn[3] = {s->nU, s->nV, s->nW};
+	for (int ax = 0; ax < 3; ax++) {
+		size_t a, b;
+		fs3i_p2g_range(s, ax, &a, &b);
+		const size_t rest = nn[ax] - (b - a);
+		if (!rest) continue;
+		k_cd_from_tags<<<cdiv((long long)rest, 256), 256, 0, s->stream>>>(g[ax], s->cdv[ax], nn[ax], a, b); FS3_LAUNCH_CHECK();
+	}
 	return FS3_OK;
 }
 

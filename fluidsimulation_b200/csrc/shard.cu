@@ -272,19 +272,22 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 	if (ph == 4) {          // the 8 sweeps start on stream2 as soon as every rank's seeds are here (replicated); meanwhile P2G of
 		                    // the slab's face nodes on the main stream, gathered on every rank (stream3)
 		if ((rc = fs3i_levelset_fork(s, true))) return rc;
-		if ((rc = fs3i_p2g_gather(s))) return rc;   // no wait on the main stream: the gather reads this rank's particles + ghost layers only
+		// no wait on the main stream: the gather reads this rank's particles + ghost layers only.  Each face grid leaves as soon as
+		// it is done (while the next one is gathered); invalid nodes travel as tagged NaNs, so the validity needs no copy of its own.
 		const int zw = s->z1 + (last ? 1 : 0);
-		cudaStream_t xs;
-		if ((rc = xfer_begin(s, &xs))) return rc;
-		if ((rc = push_planes(s, s->oU, pU, 4, s->z0, s->z1, xs)) || (rc = push_planes(s, s->oV, pV, 4, s->z0, s->z1, xs)) ||
-		    (rc = push_planes(s, s->oW, pW, 4, s->z0, zw, xs)) || (rc = push_planes(s, s->cdv[0], pU, 4, s->z0, s->z1, xs)) ||
-		    (rc = push_planes(s, s->cdv[1], pV, 4, s->z0, s->z1, xs)) || (rc = push_planes(s, s->cdv[2], pW, 4, s->z0, zw, xs)))
-			return rc;
+		cudaStream_t xs = nullptr;
+		for (int ax = 0; ax < 3; ax++) {
+			if ((rc = fs3i_p2g_gather_axis(s, ax)) || (rc = xfer_begin(s, &xs))) return rc;
+			if (ax == 0) rc = push_planes(s, s->oU, pU, 4, s->z0, s->z1, xs);
+			else if (ax == 1) rc = push_planes(s, s->oV, pV, 4, s->z0, s->z1, xs);
+			else rc = push_planes(s, s->oW, pW, 4, s->z0, zw, xs);
+			if (rc) return rc;
+		}
 		return fs3i_signal(s, xs);
 	}
 	if (ph == 5) {          // extrapolation (replicated) beside the sweeps; pressure system of the slab; tell the neighbours it is set up
 		// own outgoing copies are complete before the extrapolation overwrites the arrays they read
-		if ((rc = xfer_join(s)) || (rc = fs3i_wait(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_levelset_join(s)) ||
+		if ((rc = xfer_join(s)) || (rc = fs3i_wait(s)) || (rc = fs3i_cd_from_tags(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_levelset_join(s)) ||
 		    (rc = fs3i_project_setup(s, dt, true, true)) || (rc = fs3i_sor_prepare(s)))
 			return rc;
 		if ((rc = fs3i_sor_signal(s))) return rc;
