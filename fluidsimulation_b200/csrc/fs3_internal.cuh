@@ -225,6 +225,7 @@ __device__ __forceinline__ uint32_t fs3_ld_relaxed_sys(const uint32_t* p) {
 	asm volatile("ld.relaxed.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
 	return v;
 }
+__device__ __forceinline__ void fs3_st_relaxed_sys(uint32_t* p, uint32_t v) { asm volatile("st.relaxed.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory"); }
 __device__ __forceinline__ void fs3_st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory"); }
 // Waits until *f has reached `need` (epochs wrap: signed difference).  Never hangs: gives up after ~4 s (or at once in
 // lockstep mode, where stream order must already have satisfied the wait) and raises flags[2].

@@ -214,6 +214,9 @@ __global__ void __launch_bounds__(256, FS3_SOR_MINB) k_sor_half(Sys<REAL> sy, in
 	// Boundary blocks and interior blocks are disjoint: only the vectors of the slab's first and last plane read the
 	// neighbours' ghost planes, so only the blocks that sweep them wait for the neighbours' epoch, and the system-scope
 	// fence + signal that follow their stores stay off the interior blocks' path.
+	// (with programmatic dependent launch: nothing below may run before the previous half sweep has completed)
+	asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+	asm volatile("griddepcontrol.wait;\n" ::: "memory");
 	const uint32_t n_lo = __ldg(sh.n_lo), n_hi = __ldg(sh.n_hi), B = n_lo + (n - n_hi);
 	const uint32_t nbb = min(max(gridDim.x / 4u, 1u), max(1u, (B + blockDim.x - 1) / blockDim.x));   // blocks that hold the boundary work
 	if (blockIdx.x < nbb || gridDim.x == 1) {
@@ -231,9 +234,9 @@ __global__ void __launch_bounds__(256, FS3_SOR_MINB) k_sor_half(Sys<REAL> sy, in
 			const uint32_t d = atomicAdd(sh.done, 1u);
 			if (d == nbb - 1) {
 				*sh.done = 0;
-				__threadfence_system();
-				if (sh.peer_flag[0]) fs3_st_release_sys(sh.peer_flag[0], sh.signal_epoch);
-				if (sh.peer_flag[1]) fs3_st_release_sys(sh.peer_flag[1], sh.signal_epoch);
+				__threadfence_system();   // ONE system-scope fence orders every block's (already fenced) stores before both flags
+				if (sh.peer_flag[0]) fs3_st_relaxed_sys(sh.peer_flag[0], sh.signal_epoch);
+				if (sh.peer_flag[1]) fs3_st_relaxed_sys(sh.peer_flag[1], sh.signal_epoch);
 			}
 		}
 		if (gridDim.x > 1) return;
@@ -487,7 +490,19 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	// exclusive scan of the activity flags at the end of the first plane / the start of the last plane of the slab
 	sh.n_lo = s->sor_pos[c] + s->rb.plane * (size_t)(s->z0 + 2) / VEC;
 	sh.n_hi = s->sor_pos[c] + s->rb.plane * (size_t)s->z1 / VEC;
-	k_sor_half<REAL, VEC, true><<<nb, 256, 0, s->stream>>>(sy, c, omega, omo, s->sor_list[c], s->sor_count[c], sh); FS3_LAUNCH_CHECK();
+	{
+		static int pdl = -1;   // debug switch: chain the sharded half sweeps with programmatic dependent launch too
+		if (pdl < 0) { const char* e = getenv("FS3_SOR_SHARD_PDL"); pdl = e ? atoi(e) : 0; }
+		cudaLaunchConfig_t cfg = {};
+		cfg.gridDim = dim3(nb); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
+		cudaLaunchAttribute at[1];
+		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+		at[0].val.programmaticStreamSerializationAllowed = 1;
+		cfg.attrs = at; cfg.numAttrs = (pdl && k > 0) ? 1 : 0;
+		const uint32_t* lst = s->sor_list[c]; const uint32_t* cnt = s->sor_count[c];
+		FS3_CUDA(cudaLaunchKernelEx(&cfg, k_sor_half<REAL, VEC, true>, sy, c, omega, omo, lst, cnt, sh));
+		FS3_LAUNCH_CHECK();
+	}
 	s->sor_epoch = sh.signal_epoch;
 	return FS3_OK;
 }
