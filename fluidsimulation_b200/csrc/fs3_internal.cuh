@@ -118,6 +118,8 @@ struct fs3_sim {
 	uint32_t* bar;             // [r] barrier epoch written by rank r; [FS3_MAX_WORLD+0/1] SOR epoch of the lower/upper neighbour
 	uint32_t bar_epoch, sor_epoch;
 	uint32_t* sor_done;        // block counter of the fused end-of-sweep signal
+	int sor_halves;            // half sweeps of the current fs3i_sor_loop call
+	float sor_persist_ratio;   // > 0 while the persisting L2 carve-out is up: hit ratio of the half sweeps' access window
 	uint32_t sor_e0;           // SOR epoch of "system set up" of the current projection
 
 	int* dev_flags;            // [0] particle outside, [1] level-set wait timeout, [2] cross-rank wait failed, [3] shard capacity

@@ -24,7 +24,7 @@
 #define P2G_KY 2
 #define P2G_KZ 2
 template <int AX>
-__global__ void __launch_bounds__(128) k_p2g_gather(const float4* __restrict__ pos, const float4* __restrict__ vel,
+__global__ void __launch_bounds__(128, 8) k_p2g_gather(const float4* __restrict__ pos, const float4* __restrict__ vel,
                                                     const uint32_t* __restrict__ start, GridDims d, float cpm, float* __restrict__ grid,
                                                     int* __restrict__ cd, int kbeg, int kend, int tag_invalid) {
 	const int xs = d.nx + (AX == 0), ys = d.ny + (AX == 1);

@@ -90,6 +90,10 @@ template <> struct VecT<float, 4> { typedef float4 type; typedef unsigned int mt
 // 128-bit loads / stores into register arrays (component-wise, so that the arrays never get an address and stay in registers)
 __device__ __forceinline__ void ldv(const double* p, double (&a)[2]) { const double2 t = *reinterpret_cast<const double2*>(p); a[0] = t.x; a[1] = t.y; }
 __device__ __forceinline__ void ldv(const float* p, float (&a)[4]) { const float4 t = *reinterpret_cast<const float4*>(p); a[0] = t.x; a[1] = t.y; a[2] = t.z; a[3] = t.w; }
+// streaming (evict-first) loads for the operands that are read once per half sweep -- b, diag, mask, list -- so that they do
+// not push the two colours of p, which every half sweep reads again, out of the 126 MB L2
+__device__ __forceinline__ void ldv_stream(const double* p, double (&a)[2]) { const double2 t = __ldcs(reinterpret_cast<const double2*>(p)); a[0] = t.x; a[1] = t.y; }
+__device__ __forceinline__ void ldv_stream(const float* p, float (&a)[4]) { const float4 t = __ldcs(reinterpret_cast<const float4*>(p)); a[0] = t.x; a[1] = t.y; a[2] = t.z; a[3] = t.w; }
 __device__ __forceinline__ void stv(double* p, const double (&a)[2]) { *reinterpret_cast<double2*>(p) = make_double2(a[0], a[1]); }
 __device__ __forceinline__ void stv(float* p, const float (&a)[4]) { *reinterpret_cast<float4*>(p) = make_float4(a[0], a[1], a[2], a[3]); }
 
@@ -141,10 +145,10 @@ __device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, 
 	const M nodiag = VEC == 2 ? (M)0x8080 : (M)0x80808080u;
 	const int s = (int)(ent >> 31);   // x parity of this colour in this row
 	const size_t base = (size_t)(ent & 0x7fffffffu) * VEC;
-	const M mm = *reinterpret_cast<const M*>(sp.mask + base);
+	const M mm = __ldcs(reinterpret_cast<const M*>(sp.mask + base));
 	REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
 	ldv(sp.own + base, own);
-	ldv(sp.b + base, bb);
+	ldv_stream(sp.b + base, bb);
 	ldv(o + base, xc);
 	ldv(o + base - sp.hp, ym);
 	ldv(o + base + sp.hp, yp);
@@ -153,7 +157,7 @@ __device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, 
 	const REAL edge = s == 0 ? o[base - 1] : o[base + VEC];
 #pragma unroll
 	for (int e = 0; e < VEC; e++) dd[e] = (REAL)1;
-	if ((mm & nodiag) != nodiag) ldv(sp.dg + base, dd);
+	if ((mm & nodiag) != nodiag) ldv_stream(sp.dg + base, dd);
 #pragma unroll
 	for (int e = 0; e < VEC; e++) {
 		const unsigned m = (unsigned)(mm >> (8 * e)) & 0xffu;
@@ -442,6 +446,25 @@ template <typename REAL, int VEC> static int sor_prepare_t(fs3_sim* s) {
 }
 int fs3i_sor_prepare(fs3_sim* s) { return s->alloc_precision ? sor_prepare_t<float, 4>(s) : sor_prepare_t<double, 2>(s); }
 
+// L2 residency of p during the solve.  The two colours of p are the only operands one half sweep shares with the next; b,
+// the mask and the list stream through once per sweep and, left alone, keep pushing p out of the 126 MB L2.  For the length
+// of fs3i_sor_loop a persisting L2 carve-out is raised (it is a real partition: while it exists every other kernel has
+// that much less L2, hence the stream synchronisation + cudaDeviceSetLimit on both sides of the solve) and every half
+// sweep is launched with an access-policy window over the colour it writes.  The fraction of the window that persists
+// is carve-out / bytes of p the active vectors touch, so that the persisting lines never thrash among themselves; below
+// 0.5 (large grids) or for grids that fit in L2 anyway the feature stays off and the solve runs without the two syncs.
+// FS3_SOR_L2_PERSIST_MB caps the carve-out (0 = never).
+static size_t sor_persist_cap(fs3_sim* s) {
+	static long long bytes = -1;
+	if (bytes < 0) {
+		const char* e = getenv("FS3_SOR_L2_PERSIST_MB");
+		cudaDeviceProp pr; cudaGetDeviceProperties(&pr, s->device);
+		bytes = (long long)pr.persistingL2CacheMaxSize;
+		if (e) bytes = std::min<long long>(bytes, atoll(e) << 20);
+		if ((size_t)pr.accessPolicyMaxWindowSize < ((size_t)64 << 20)) bytes = 0;
+	}
+	return (size_t)bytes;
+}
 // half sweep k (colour k & 1) of the current projection
 template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	Sys<REAL> sy = make_sys<REAL>(s);
@@ -465,10 +488,23 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 		// follows the set-up kernels with a normal dependency
 		cudaLaunchConfig_t cfg = {};
 		cfg.gridDim = dim3(nb); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
-		cudaLaunchAttribute at[1];
-		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-		at[0].val.programmaticStreamSerializationAllowed = 1;
-		cfg.attrs = at; cfg.numAttrs = (k > 0 && !s->prm.record_residuals) ? 1 : 0;
+		cudaLaunchAttribute at[2];
+		int na = 0;
+		if (s->sor_persist_ratio > 0) {
+			at[na].id = cudaLaunchAttributeAccessPolicyWindow;
+			at[na].val.accessPolicyWindow.base_ptr = s->p[c];
+			at[na].val.accessPolicyWindow.num_bytes = s->rb.total * sizeof(REAL);
+			at[na].val.accessPolicyWindow.hitRatio = s->sor_persist_ratio;
+			at[na].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+			at[na].val.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+			na++;
+		}
+		if (k > 0 && !s->prm.record_residuals) {
+			at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+			at[na].val.programmaticStreamSerializationAllowed = 1;
+			na++;
+		}
+		cfg.attrs = at; cfg.numAttrs = na;
 		const uint32_t* lst = s->sor_list[c]; const uint32_t* cnt = s->sor_count[c];
 		FS3_CUDA(cudaLaunchKernelEx(&cfg, k_sor_half<REAL, VEC, false>, sy, c, omega, omo, lst, cnt, SorShard{}));
 		FS3_LAUNCH_CHECK();
@@ -517,6 +553,21 @@ int fs3i_sor_loop(fs3_sim* s, int iters) {
 		if (iters > s->res_cap) { s->err = "residual buffer too small"; return FS3_ERR_STATE; }
 		FS3_CUDA(cudaMemsetAsync(s->res, 0, sizeof(double) * 2 * iters, s->stream));
 	}
+	s->sor_halves = 2 * iters;
+	s->sor_persist_ratio = 0;
+	const size_t es = s->alloc_precision ? 4 : 8, cap = s->world == 1 && !rec ? sor_persist_cap(s) : 0;
+	if (cap && 2 * s->rb.total * es > ((size_t)48 << 20) && s->rb.total * es <= ((size_t)128 << 20)) {
+		uint32_t cnt[2];
+		FS3_CUDA(cudaMemcpyAsync(&cnt[0], s->sor_count[0], 4, cudaMemcpyDeviceToHost, s->stream));
+		FS3_CUDA(cudaMemcpyAsync(&cnt[1], s->sor_count[1], 4, cudaMemcpyDeviceToHost, s->stream));
+		FS3_CUDA(cudaStreamSynchronize(s->stream));
+		const double touched = ((double)cnt[0] + cnt[1]) * 16.0;   // one 128-bit vector per list entry
+		const double ratio = touched > 0 ? std::min(1.0, 0.95 * (double)cap / touched) : 0.0;
+		if (ratio >= 0.5 && touched > (double)((size_t)32 << 20)) {
+			FS3_CUDA(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, cap));
+			s->sor_persist_ratio = (float)ratio;
+		}
+	}
 	for (int it = 0; it < iters; it++) {
 		if ((rc = fs3i_sor_half_launch(s, 2 * it)) || (rc = fs3i_sor_half_launch(s, 2 * it + 1))) return rc;
 		if (rec) {
@@ -524,6 +575,11 @@ int fs3i_sor_loop(fs3_sim* s, int iters) {
 			else k_sor_residual<double><<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(make_sys<double>(s), s->res + 2 * it);
 			FS3_LAUNCH_CHECK();
 		}
+	}
+	if (s->sor_persist_ratio > 0) {
+		FS3_CUDA(cudaStreamSynchronize(s->stream));
+		FS3_CUDA(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0));
+		s->sor_persist_ratio = 0;
 	}
 	s->res_count = rec ? iters : 0;
 	return FS3_OK;

@@ -294,7 +294,7 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 		if (T) cudaEventRecord(s->ev[FS3_T_PROJECT_SOR], s->stream);
 		return FS3_OK;
 	}
-	if (ph < 6 + 2 * I) return fs3i_sor_half_launch(s, ph - 6);   // compute + halo exchange in one kernel
+	if (ph < 6 + 2 * I) { s->sor_halves = 2 * I; return fs3i_sor_half_launch(s, ph - 6); }   // compute + halo exchange in one kernel
 	if (ph == 6 + 2 * I) {  // pressure gradient on the slab; the projected field is gathered on every rank
 		if ((rc = fs3i_sor_wait(s, s->sor_e0 + 2u * (uint32_t)I)) || (rc = fs3i_project_gradient(s, dt, true, true))) return rc;
 		// the gradient kernel of cell plane z writes the W faces z+1 (and z = 0 on rank 0): that is the range it owns here
