@@ -278,7 +278,7 @@ def run_gpu(args, rank, world, local_rank):
                         "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
                 "stage_ms_per_step": {k: v / args.steps for k, v in stage_acc.items()},
-                "stage_note": "LEVELSET_SWEEP runs on a second stream beside EXTRAPOLATE: the two overlap, stage times add up to more than TOTAL"}
+                "stage_note": "LEVELSET_SWEEP runs on a second stream beside P2G and EXTRAPOLATE: they overlap, stage times add up to more than TOTAL"}
         print(json.dumps(line), flush=True)
     sim.close()
     if world > 1:

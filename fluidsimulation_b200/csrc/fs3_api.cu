@@ -348,11 +348,16 @@ int fs3_step(fs3_sim* s, float dt) {
 	if (T) cudaEventRecord(s->ev[FS3_T_BIN], s->stream);
 	if ((rc = fs3i_bin(s))) return rc;
 	if ((rc = fs3i_levelset_seed(s))) return rc;       // records LEVELSET_SEED
+	// The 8 sweeps are bound by their dependency chain, not by throughput: they run on stream2 (LEVELSET_SWEEP is recorded
+	// there) with ONE CTA per SM beside the P2G gather and the extrapolation, and are joined before the projection, which
+	// is the first stage that reads phi.  At one CTA per SM the issue-bound gather loses 1.2 ms at 256^3 and the sweeps
+	// take 6.6 instead of 3.7 ms, but all of that is hidden (19.55 -> 18.9 ms per step; 128^3: 4.24 -> 3.78; 512^3: even).
+	// FS3_LS_EARLY=0 starts them after the gather instead (the earlier arrangement; then FS3_LS_BLOCKS_PER_SM=2 is best).
+	static int ls_early = -1;
+	if (ls_early < 0) { const char* e = getenv("FS3_LS_EARLY"); ls_early = e ? atoi(e) : 1; }
+	if (ls_early && (rc = fs3i_levelset_fork(s))) return rc;
 	if ((rc = fs3i_p2g_gather(s))) return rc;          // records P2G
-	// two dependency-bound stages side by side: the 8 sweeps on stream2 (records LEVELSET_SWEEP there) and the layered
-	// extrapolation (records EXTRAPOLATE).  The issue-bound P2G gather is kept out of the overlap: it loses more than the
-	// sweeps gain when they share the SMs.
-	if ((rc = fs3i_levelset_fork(s))) return rc;
+	if (!ls_early && (rc = fs3i_levelset_fork(s))) return rc;
 	if ((rc = fs3i_extrapolate_all(s))) return rc;
 	if ((rc = fs3i_levelset_join(s))) return rc;
 	if ((rc = fs3i_project(s, dt, true, true))) return rc;  // records PROJECT_SETUP / SOR / TOVEL; gravity folded in

@@ -472,9 +472,10 @@ int fs3i_levelset_init(fs3_sim* s) {
 	FS3_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
 	// Resident CTAs beyond what the DAG can keep busy only add pollers.  Tunables (debug): FS3_LS_BLOCKS_PER_SM, FS3_LS_SLEEP_NS.
 	const int occ = std::max(1, per_sm);
-	// Two CTAs (40 K registers) per SM: the sweep is bound by its critical path, not by throughput, and that leaves room for
-	// a CTA of the extrapolation fill running beside it (measured best at 256^3 and at 512^3).
-	per_sm = std::min(occ, 2);
+	// The sweep is bound by its critical path, not by throughput.  Single GPU: one CTA per SM, because the sweeps run beside
+	// the P2G gather and the extrapolation (fs3_step) and should take as little from them as possible.  Sharded: two, the
+	// replicated sweeps are the longest chain of the step there.
+	per_sm = std::min(occ, s->world == 1 ? 1 : 2);
 	if (const char* e = getenv("FS3_LS_BLOCKS_PER_SM")) per_sm = std::min(occ, std::max(1, atoi(e)));
 	s->ls_sleep_ns = 256;
 	if (const char* e = getenv("FS3_LS_SLEEP_NS")) s->ls_sleep_ns = std::max(20, atoi(e));
