@@ -347,15 +347,18 @@ int fs3_step(fs3_sim* s, float dt) {
 	if ((rc = fs3i_advect(s, dt))) return rc;
 	if (T) cudaEventRecord(s->ev[FS3_T_BIN], s->stream);
 	if ((rc = fs3i_bin(s))) return rc;
-	if ((rc = fs3i_levelset_seed(s))) return rc;       // records LEVELSET_SEED
+	static int ls_early = -1;
+	if (ls_early < 0) { const char* e = getenv("FS3_LS_EARLY"); ls_early = e ? atoi(e) : 1; }
+	static int seed_fork = -1;
+	if (seed_fork < 0) { const char* e = getenv("FS3_LS_SEED_FORK"); seed_fork = e ? atoi(e) : 0; }
+	s->ls_seed_forked = false;
+	if (!(ls_early && seed_fork) && (rc = fs3i_levelset_seed(s))) return rc;       // records LEVELSET_SEED
 	// The 8 sweeps are bound by their dependency chain, not by throughput: they run on stream2 (LEVELSET_SWEEP is recorded
 	// there) with ONE CTA per SM beside the P2G gather and the extrapolation, and are joined before the projection, which
 	// is the first stage that reads phi.  At one CTA per SM the issue-bound gather loses 1.2 ms at 256^3 and the sweeps
 	// take 6.6 instead of 3.7 ms, but all of that is hidden (19.55 -> 18.9 ms per step; 128^3: 4.24 -> 3.78; 512^3: even).
 	// FS3_LS_EARLY=0 starts them after the gather instead (the earlier arrangement; then FS3_LS_BLOCKS_PER_SM=2 is best).
-	static int ls_early = -1;
-	if (ls_early < 0) { const char* e = getenv("FS3_LS_EARLY"); ls_early = e ? atoi(e) : 1; }
-	if (ls_early && (rc = fs3i_levelset_fork(s))) return rc;
+	if (ls_early && (rc = fs3i_levelset_fork(s, false, seed_fork != 0))) return rc;
 	if ((rc = fs3i_p2g_gather(s))) return rc;          // records P2G
 	if (!ls_early && (rc = fs3i_levelset_fork(s))) return rc;
 	if ((rc = fs3i_extrapolate_all(s))) return rc;
@@ -391,7 +394,8 @@ int fs3_stage_times(fs3_sim* s, float* ms, int cap) {
 	// to more than TOTAL), and the seed ends where P2G begins
 	if (s->ls_overlapped) {
 		FS3_CUDA(cudaEventElapsedTime(&ms[FS3_T_LEVELSET_SWEEP], s->ev[FS3_T_LEVELSET_SWEEP], s->ev_ls_end));
-		FS3_CUDA(cudaEventElapsedTime(&ms[FS3_T_LEVELSET_SEED], s->ev[FS3_T_LEVELSET_SEED], s->ev[FS3_T_P2G]));
+		if (!s->ls_seed_forked) FS3_CUDA(cudaEventElapsedTime(&ms[FS3_T_LEVELSET_SEED], s->ev[FS3_T_LEVELSET_SEED], s->ev[FS3_T_P2G]));
+		else FS3_CUDA(cudaEventElapsedTime(&ms[FS3_T_BIN], s->ev[FS3_T_BIN], s->ev[FS3_T_P2G]));
 		FS3_CUDA(cudaEventElapsedTime(&ms[FS3_T_P2G], s->ev[FS3_T_P2G], s->ev[FS3_T_EXTRAPOLATE]));
 	}
 	return FS3_OK;

@@ -119,6 +119,7 @@ struct fs3_sim {
 	uint32_t bar_epoch, sor_epoch;
 	uint32_t* sor_done;        // block counter of the fused end-of-sweep signal
 	int sor_halves;            // half sweeps of the current fs3i_sor_loop call
+	bool ls_seed_forked;       // the seed of the current step ran on stream2 in front of the sweeps
 	float sor_persist_ratio;   // > 0 while the persisting L2 carve-out is up: hit ratio of the half sweeps' access window
 	uint32_t sor_e0;           // SOR epoch of "system set up" of the current projection
 
@@ -288,9 +289,9 @@ int fs3i_sor_prepare(fs3_sim* s);
 int fs3i_sor_half_launch(fs3_sim* s, int k);                                // half sweep k of the current projection
 int fs3i_project_gradient(fs3_sim* s, float dt, bool from_old, bool with_gravity);
 // levelset.cu / p2g.cu pieces
-int fs3i_levelset_seed(fs3_sim* s);
+int fs3i_levelset_seed(fs3_sim* s, cudaStream_t st = nullptr);
 int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st = nullptr);                // st: stream to run on (default: the handle's)
-int fs3i_levelset_fork(fs3_sim* s, bool after_barrier = false);              // sweeps on stream2, after everything queued so far (and, sharded, after the current barrier epoch)
+int fs3i_levelset_fork(fs3_sim* s, bool after_barrier = false, bool with_seed = false);              // sweeps on stream2, after everything queued so far (and, sharded, after the current barrier epoch)
 int fs3i_levelset_join(fs3_sim* s);                                          // main stream waits for them
 int fs3i_p2g_gather(fs3_sim* s);
 int fs3i_p2g_gather_axis(fs3_sim* s, int ax);                                // one face grid of the slab

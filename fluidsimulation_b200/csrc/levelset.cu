@@ -340,11 +340,12 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 }
 
 // seed of the cells of this rank's slab (world == 1: all cells)
-int fs3i_levelset_seed(fs3_sim* s) {
+int fs3i_levelset_seed(fs3_sim* s, cudaStream_t st) {
 	GridDims d{s->nx, s->ny, s->nz};
-	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SEED], s->stream);
+	if (!st) st = s->stream;
+	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SEED], st);
 	const size_t plane = (size_t)s->nx * s->ny, c0 = plane * s->z0, c1 = plane * s->z1;
-	k_ls_seed<<<cdiv((long long)(c1 - c0), 256), 256, 0, s->stream>>>(s->pos[s->cur], s->cell_start, d, s->prm.particle_radius, s->ls_rec, c0, c1);
+	k_ls_seed<<<cdiv((long long)(c1 - c0), 256), 256, 0, st>>>(s->pos[s->cur], s->cell_start, d, s->prm.particle_radius, s->ls_rec, c0, c1);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
@@ -392,10 +393,12 @@ int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st) {
 
 // The sweeps only touch ls_rec / phi / closest, which nothing else reads before the pressure system is set up: inside a step
 // they overlap the P2G gather and the extrapolation (both bandwidth / issue bound, while the sweeps wait on tile dependencies).
-int fs3i_levelset_fork(fs3_sim* s, bool after_barrier) {
+int fs3i_levelset_fork(fs3_sim* s, bool after_barrier, bool with_seed) {
 	FS3_CUDA(cudaEventRecord(s->ev_fork, s->stream));
 	FS3_CUDA(cudaStreamWaitEvent(s->stream2, s->ev_fork, 0));
 	int rc;
+	s->ls_seed_forked = with_seed;
+	if (with_seed && (rc = fs3i_levelset_seed(s, s->stream2))) return rc;   // single GPU: the seed needs the sorted particles only
 	// sharded: the gathered seed records are complete once every rank has published the current barrier epoch; that wait
 	// sits on stream2 too, so the main stream goes on with the P2G gather meanwhile
 	if (after_barrier && (rc = fs3i_wait(s, s->stream2))) return rc;

@@ -148,12 +148,13 @@ __device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, 
 	const M mm = __ldcs(reinterpret_cast<const M*>(sp.mask + base));
 	REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
 	ldv(sp.own + base, own);
-	ldv_stream(sp.b + base, bb);
+#ifndef FS3_SOR_EXP
+#define FS3_SOR_EXP 0   // timing experiments only (wrong results): 1 = no z-neighbour loads, 2 = no b load, 3 = no y-neighbour loads
+#endif
 	ldv(o + base, xc);
-	ldv(o + base - sp.hp, ym);
-	ldv(o + base + sp.hp, yp);
-	ldv(o + base - sp.plane, zm);
-	ldv(o + base + sp.plane, zp);
+	if (FS3_SOR_EXP == 2) ldv(o + base, bb); else ldv_stream(sp.b + base, bb);
+	if (FS3_SOR_EXP == 3) { ldv(o + base, ym); ldv(o + base, yp); } else { ldv(o + base - sp.hp, ym); ldv(o + base + sp.hp, yp); }
+	if (FS3_SOR_EXP == 1) { ldv(o + base, zm); ldv(o + base, zp); } else { ldv(o + base - sp.plane, zm); ldv(o + base + sp.plane, zp); }
 	const REAL edge = s == 0 ? o[base - 1] : o[base + VEC];
 #pragma unroll
 	for (int e = 0; e < VEC; e++) dd[e] = (REAL)1;
