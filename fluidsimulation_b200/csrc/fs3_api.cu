@@ -70,6 +70,10 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 		g_create_error = "only cubic grids with cells_per_meter == nx (>= 4) are supported, as the reference's own results are only defined there";
 		return FS3_ERR_INVALID;
 	}
+	if (nx > 812) {
+		g_create_error = "grids above 812^3 are not supported: half-cell sort keys ((2n)^3) and grid element indices are 32 bits";
+		return FS3_ERR_INVALID;
+	}
 	if (world < 1 || world > FS3_MAX_WORLD || rank < 0 || rank >= world || nz % world != 0 || (world > 1 && nz / world < 2)) {
 		g_create_error = "z-slab sharding needs 1 <= world <= 16, nz divisible by world and slabs of at least 2 cell planes";
 		return FS3_ERR_INVALID;

@@ -174,12 +174,21 @@ __device__ __forceinline__ void fs3_split(float c, float hi, int last, int& i0, 
 	f = __fsub_rn(cc, (float)i);
 }
 
-__device__ __forceinline__ float fs3_tri(const float* __restrict__ g, size_t base, int sy, size_t sz, float fx, float fy, float fz) {
-	// x lerps first, then y, then z (S3D.h:87-97)
-	float a00 = fs3_lerp(__ldg(g + base), __ldg(g + base + 1), fx);
-	float a10 = fs3_lerp(__ldg(g + base + sy), __ldg(g + base + sy + 1), fx);
-	float a01 = fs3_lerp(__ldg(g + base + sz), __ldg(g + base + sz + 1), fx);
-	float a11 = fs3_lerp(__ldg(g + base + sz + sy), __ldg(g + base + sz + sy + 1), fx);
+// Four row pointers (x run of 2 at y, y+1 on planes z, z+1) and eight loads at immediate offsets 0 / 4: the address
+// arithmetic is 4 pointer adds per component instead of one per tap (the particle kernels are issue-bound).  Element indices
+// fit in 32 bits for every grid the library accepts (the half-cell keys already require (2n)^3 < 2^32).
+__device__ __forceinline__ float fs3_tri(const float* __restrict__ g, uint32_t base, uint32_t sy, uint32_t sz, float fx, float fy, float fz) {
+	// x lerps first, then y, then z (S3D.h:87-97).  Row starts as 32-bit element indices (one add each), one widening
+	// multiply-add per row pointer.
+	const uint32_t b10 = base + sy, b01 = base + sz, b11 = b01 + sy;
+	const float* __restrict__ r00 = g + base;
+	const float* __restrict__ r10 = g + b10;
+	const float* __restrict__ r01 = g + b01;
+	const float* __restrict__ r11 = g + b11;
+	float a00 = fs3_lerp(__ldg(r00), __ldg(r00 + 1), fx);
+	float a10 = fs3_lerp(__ldg(r10), __ldg(r10 + 1), fx);
+	float a01 = fs3_lerp(__ldg(r01), __ldg(r01 + 1), fx);
+	float a11 = fs3_lerp(__ldg(r11), __ldg(r11 + 1), fx);
 	return fs3_lerp(fs3_lerp(a00, a10, fy), fs3_lerp(a01, a11, fy), fz);
 }
 
@@ -194,10 +203,11 @@ __device__ __forceinline__ float3 fs3_interp(const float* __restrict__ U, const 
 	fs3_split(__fadd_rn(i, 0.5f), (float)d.nx, d.nx, eI, gI);
 	fs3_split(__fadd_rn(j, 0.5f), (float)d.ny, d.ny, eJ, gJ);
 	fs3_split(__fadd_rn(k, 0.5f), (float)d.nz, d.nz, eK, gK);
+	const uint32_t nx = (uint32_t)d.nx, ny = (uint32_t)d.ny;
 	float3 r;
-	r.x = fs3_tri(U, (size_t)eI + (size_t)(d.nx + 1) * ((size_t)iJ + (size_t)d.ny * iK), d.nx + 1, (size_t)(d.nx + 1) * d.ny, gI, fJ, fK);
-	r.y = fs3_tri(V, (size_t)iI + (size_t)d.nx * ((size_t)eJ + (size_t)(d.ny + 1) * iK), d.nx, (size_t)d.nx * (d.ny + 1), fI, gJ, fK);
-	r.z = fs3_tri(W, (size_t)iI + (size_t)d.nx * ((size_t)iJ + (size_t)d.ny * eK), d.nx, (size_t)d.nx * d.ny, fI, fJ, gK);
+	r.x = fs3_tri(U, (uint32_t)eI + (nx + 1u) * ((uint32_t)iJ + ny * (uint32_t)iK), nx + 1u, (nx + 1u) * ny, gI, fJ, fK);
+	r.y = fs3_tri(V, (uint32_t)iI + nx * ((uint32_t)eJ + (ny + 1u) * (uint32_t)iK), nx, nx * (ny + 1u), fI, gJ, fK);
+	r.z = fs3_tri(W, (uint32_t)iI + nx * ((uint32_t)iJ + ny * (uint32_t)eK), nx, nx * ny, fI, fJ, gK);
 	return r;
 }
 

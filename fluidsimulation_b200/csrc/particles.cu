@@ -147,10 +147,26 @@ __device__ __forceinline__ void bin_note(const BinArgs& B, long long i, float4 p
 	B.arrival[i] = atomicAdd(B.count + c, 1u);   // arrival order inside the half-cell: a unique provisional slot (the rank by creation id follows)
 }
 
+// Clamp box of Advect, [(-0.5+0.1)/n, 1+(-0.5-0.1)/n] per axis (S3D.cpp:226-230): six IEEE float divisions that depend on the
+// grid only, so the host does them once per launch instead of every thread (same single-precision operations, same results).
+struct AdvectBox {
+	float lo[3], hi[3];
+};
+static AdvectBox advect_box(const fs3_sim* s) {
+	AdvectBox b;
+	const float eps = 0.1f, n[3] = {(float)s->nx, (float)s->ny, (float)s->nz};
+	for (int a = 0; a < 3; a++) {
+		volatile float lo = (-0.5f + eps) / n[a], q = (-0.5f - eps) / n[a];   // volatile: keep every intermediate a rounded float
+		volatile float hi = 1.0f + q;
+		b.lo[a] = lo; b.hi[a] = hi;
+	}
+	return b;
+}
+
 template <bool SHARD>
 __global__ void __launch_bounds__(256) k_advect(float4* __restrict__ pos, long long np, GridDims d, float dt,
                                                 const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W, MigArgs mig,
-                                                BinArgs bin) {
+                                                BinArgs bin, AdvectBox box) {
 	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= np) return;
 	float4 p = pos[i];
@@ -170,10 +186,9 @@ __global__ void __launch_bounds__(256) k_advect(float4* __restrict__ pos, long l
 	p.x = __fadd_rn(p.x, __fmul_rn(dt, vx));
 	p.y = __fadd_rn(p.y, __fmul_rn(dt, vy));
 	p.z = __fadd_rn(p.z, __fmul_rn(dt, vz));
-	const float eps = 0.1f;
-	p.x = fs3_clamp(p.x, (-0.5f + eps) / fx, __fadd_rn(1.0f, (-0.5f - eps) / fx));
-	p.y = fs3_clamp(p.y, (-0.5f + eps) / fy, __fadd_rn(1.0f, (-0.5f - eps) / fy));
-	p.z = fs3_clamp(p.z, (-0.5f + eps) / fz, __fadd_rn(1.0f, (-0.5f - eps) / fz));
+	p.x = fs3_clamp(p.x, box.lo[0], box.hi[0]);
+	p.y = fs3_clamp(p.y, box.lo[1], box.hi[1]);
+	p.z = fs3_clamp(p.z, box.lo[2], box.hi[2]);
 	pos[i] = p;
 	if (SHARD) mig_note(mig, i, p.z);
 	else bin_note(bin, i, p, d);
@@ -193,7 +208,7 @@ int fs3i_advect(fs3_sim* s, float dt) {
 	if (s->world > 1) {
 		FS3_CUDA(cudaMemsetAsync(s->mig_ctl, 0, (2 * s->world + 1) * sizeof(uint32_t), s->stream));
 		if (s->np_in > 0) {
-			k_advect<true><<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->np_in, d, dt, s->U, s->V, s->W, mig_args(s), BinArgs{});
+			k_advect<true><<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->np_in, d, dt, s->U, s->V, s->W, mig_args(s), BinArgs{}, advect_box(s));
 			FS3_LAUNCH_CHECK();
 		}
 		return FS3_OK;
@@ -202,7 +217,7 @@ int fs3i_advect(fs3_sim* s, float dt) {
 	// the counting pass of the sort that always follows is fused in (the new position is in registers)
 	FS3_CUDA(cudaMemsetAsync(s->cell_count, 0, (s->nH + 1) * sizeof(uint32_t), s->stream));
 	k_advect<false><<<cdiv(s->np, 256), 256, 0, s->stream>>>(s->pos[s->cur], s->np, d, dt, s->U, s->V, s->W, MigArgs{},
-	                                                          BinArgs{s->cellid, s->cell_fill, s->cell_count, s->dev_flags, 0, s->nz});
+	                                                          BinArgs{s->cellid, s->cell_fill, s->cell_count, s->dev_flags, 0, s->nz}, advect_box(s));
 	FS3_LAUNCH_CHECK();
 	s->counted = true;
 	return FS3_OK;

@@ -195,8 +195,11 @@ __device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, 
 #ifndef FS3_SOR_MINB
 #define FS3_SOR_MINB 4
 #endif
+#ifndef FS3_SOR_THREADS
+#define FS3_SOR_THREADS 256
+#endif
 template <typename REAL, int VEC, bool SHARD>
-__global__ void __launch_bounds__(256, FS3_SOR_MINB) k_sor_half(Sys<REAL> sy, int colour, REAL omega, REAL one_minus_omega,
+__global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_half(Sys<REAL> sy, int colour, REAL omega, REAL one_minus_omega,
                                                   const uint32_t* __restrict__ list, const uint32_t* __restrict__ count, SorShard sh) {
 	const uint32_t n = __ldg(count);
 	const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, G = gridDim.x * blockDim.x;
@@ -477,18 +480,18 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	static int per_sm = 0;   // resident blocks per SM of the sweep kernel: the grid is exactly one wave
 	if (!per_sm) {
 		int a = 0, b = 0;
-		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_sor_half<REAL, VEC, false>, 256, 0);
-		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_sor_half<REAL, VEC, true>, 256, 0);
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_sor_half<REAL, VEC, false>, FS3_SOR_THREADS, 0);
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_sor_half<REAL, VEC, true>, FS3_SOR_THREADS, 0);
 		per_sm = std::max(1, std::min(a, b));
 		if (const char* e = getenv("FS3_SOR_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));
 	}
-	int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, 256)), (long long)s->sm_count * per_sm);
+	int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, FS3_SOR_THREADS)), (long long)s->sm_count * per_sm);
 	const int c = k & 1;
 	if (s->world == 1) {
 		// half sweeps after the first are launched with programmatic stream serialization (see the kernel); the first one
 		// follows the set-up kernels with a normal dependency
 		cudaLaunchConfig_t cfg = {};
-		cfg.gridDim = dim3(nb); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
+		cfg.gridDim = dim3(nb); cfg.blockDim = dim3(FS3_SOR_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
 		cudaLaunchAttribute at[2];
 		int na = 0;
 		if (s->sor_persist_ratio > 0) {
@@ -531,7 +534,7 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 		static int pdl = -1;   // debug switch: chain the sharded half sweeps with programmatic dependent launch too
 		if (pdl < 0) { const char* e = getenv("FS3_SOR_SHARD_PDL"); pdl = e ? atoi(e) : 0; }
 		cudaLaunchConfig_t cfg = {};
-		cfg.gridDim = dim3(nb); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
+		cfg.gridDim = dim3(nb); cfg.blockDim = dim3(FS3_SOR_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
 		cudaLaunchAttribute at[1];
 		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
 		at[0].val.programmaticStreamSerializationAllowed = 1;
