@@ -341,21 +341,30 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_lookback(const uint32_t* __rest
 	for (int k = 0; k < SCAN_I; k++) v += loc[k];
 	uint32_t tot;
 	const uint32_t ex_in_tile = block_excl_scan(v, &tot);
-	if (threadIdx.x == 0) {
+	// look-back by the first warp, 32 predecessors per step: every lane waits for its predecessor's word, the nearest one
+	// that already holds an inclusive prefix ends the walk
+	if (threadIdx.x < 32) {
+		const int lane = threadIdx.x;
 		uint32_t prefix = 0;
 		if (tile == 0) {
-			scan_st(state, (SCAN_INC << 32) | tot);
+			if (lane == 0) scan_st(state, (SCAN_INC << 32) | tot);
 		} else {
-			scan_st(state + tile, (SCAN_AGG << 32) | tot);
-			for (uint32_t j = tile - 1;; j--) {
-				unsigned long long w;
-				do { w = scan_ld(state + j); } while ((w >> 32) == 0);
-				prefix += (uint32_t)w;
-				if ((w >> 32) == SCAN_INC) break;
+			if (lane == 0) scan_st(state + tile, (SCAN_AGG << 32) | tot);
+			for (long long j = (long long)tile - 1;; j -= 32) {
+				const long long idx = j - lane;
+				unsigned long long w = SCAN_INC << 32;   // before the first tile: an inclusive prefix of 0
+				if (idx >= 0) do { w = scan_ld(state + idx); } while ((w >> 32) == 0);
+				const unsigned inc = __ballot_sync(0xffffffffu, (w >> 32) == SCAN_INC);
+				const int first = inc ? __ffs(inc) - 1 : 31;
+				uint32_t val = lane <= first ? (uint32_t)w : 0u;
+#pragma unroll
+				for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+				prefix += val;
+				if (inc) break;
 			}
-			scan_st(state + tile, (SCAN_INC << 32) | (uint32_t)(prefix + tot));
+			if (lane == 0) scan_st(state + tile, (SCAN_INC << 32) | (uint32_t)(prefix + tot));
 		}
-		s_prefix = prefix;
+		if (lane == 0) s_prefix = prefix;
 	}
 	__syncthreads();
 	uint32_t ex = ex_in_tile + s_prefix + base0;
