@@ -388,6 +388,9 @@ template <int AX> static int p2g_launch(fs3_sim* s, float* grid, int* cd) {
 	const int xs = s->nx + (AX == 0), ys = s->ny + (AX == 1);
 	const int kbeg = s->z0, kend = s->z1 + ((AX == 2 && s->rank == s->world - 1) ? 1 : 0);
 	dim3 g(cdiv(xs, 32 * P2G_KX), cdiv(ys, 2 * P2G_KY), cdiv(kend - kbeg, 2 * P2G_KZ));
+	static int carve = -2;   // debug: FS3_P2G_CARVEOUT = preferred shared-memory carve-out in percent (L1 sensitivity experiments)
+	if (carve == -2) { const char* e = getenv("FS3_P2G_CARVEOUT"); carve = e ? atoi(e) : -1; }
+	if (carve >= 0) cudaFuncSetAttribute(k_p2g_gather<AX>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
 	k_p2g_gather<AX><<<g, 128, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->cell_start, d, s->cpm, grid, cd, kbeg, kend, s->world > 1 ? 1 : 0);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
