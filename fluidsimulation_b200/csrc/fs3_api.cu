@@ -7,6 +7,7 @@
 #include <algorithm>
 
 static std::string g_create_error;
+void fs3i_set_global_error(const std::string& msg) { g_create_error = msg; }   // host-only entry points have no handle to put it in
 
 #define ENTER(s)                                                       \
 	if (!(s)) return FS3_ERR_INVALID;                                  \
@@ -98,7 +99,7 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	s->prm.rho = 1000.0f; s->prm.gravity_y = -9.81f; s->prm.nu = 8.90f * 1e-4f / 1000.0f; s->prm.particle_radius = 1.0f;  // S3D.h:135-145
 	s->prm.record_stage_times = 0;
 	s->nU = (size_t)(nx + 1) * ny * nz; s->nV = (size_t)nx * (ny + 1) * nz; s->nW = (size_t)nx * ny * (nz + 1); s->nC = (size_t)nx * ny * nz;
-	s->launches = 0; s->np = 0; s->np_in = 0; s->cap = 0; s->cur = 0; s->sorted = false; s->counted = false; s->closest_valid = false; s->system_valid = false;
+	s->launches = 0; s->steps = 0; s->np = 0; s->np_in = 0; s->cap = 0; s->cur = 0; s->sorted = false; s->counted = false; s->closest_valid = false; s->system_valid = false;
 	s->sor_list_valid = false; s->sm_count = prop.multiProcessorCount;
 	s->alloc_precision = -1; s->res_cap = 4096; s->res_count = 0; s->stage_ptr = nullptr; s->stage_bytes = 0;
 	s->rank = rank; s->world = world; s->z0 = rank * (nz / world); s->z1 = s->z0 + nz / world; s->lockstep = lockstep;
@@ -265,6 +266,7 @@ int fs3_group_reset(fs3_sim** h, int world) {
 	cudaSetDevice(h[0]->device);
 	for (int ph = 0; ph < 3; ph++)
 		for (int r = 0; r < world; r++) { int rc = fs3i_reset_phase(h[r], ph); if (rc) return rc; }
+	for (int r = 0; r < world; r++) h[r]->steps = 0;
 	return FS3_OK;
 }
 
@@ -287,6 +289,7 @@ int fs3_destroy(fs3_sim* s) {
 		for (void* p : ptrs) if (p) cudaFree(p);
 	}
 	if (s->stage_ptr) cudaFree(s->stage_ptr);
+	fs3i_consumer_free(s);
 	for (int k = 0; k < FS3_T_COUNT + 2; k++) if (s->ev[k]) cudaEventDestroy(s->ev[k]);
 	if (s->stream && s->owns_stream) cudaStreamDestroy(s->stream);
 	delete s;
@@ -298,11 +301,13 @@ int fs3_reset(fs3_sim* s) {
 	if (s->world > 1) {
 		if (s->lockstep) return fail(s, FS3_ERR_STATE, "a lockstep group is reset with fs3_group_reset");
 		if (!s->n_ipc_opened) return fail(s, FS3_ERR_STATE, "sharded handle is not connected (fs3_shard_connect)");
+		s->steps = 0;
 		return run_reset_phases(s);   // collective: every rank calls fs3_reset
 	}
 	long long np = 8LL * (s->nz - 2) * (s->ny - 2) * (s->nx - 1 - s->nx / 2);
 	int rc = ensure_particle_capacity(s, np > 0 ? np : 1);
 	if (rc) return rc;
+	s->steps = 0;
 	return fs3i_reset(s);
 }
 
@@ -345,6 +350,7 @@ int fs3_step(fs3_sim* s, float dt) {
 		if (!s->n_ipc_opened) return fail(s, FS3_ERR_STATE, "sharded handle is not connected (fs3_shard_connect)");
 		const int nph = fs3i_num_step_phases(s);
 		for (int ph = 0; ph < nph; ph++) if ((rc = fs3i_step_phase(s, ph, dt))) return rc;
+		s->steps++;
 		return FS3_OK;
 	}
 	if (T) cudaEventRecord(s->ev[FS3_T_ADVECT], s->stream);
@@ -373,6 +379,7 @@ int fs3_step(fs3_sim* s, float dt) {
 	if ((rc = fs3i_flip_combine(s, alpha))) return rc;
 	if ((rc = fs3i_g2p(s, alpha))) return rc;
 	if (T) cudaEventRecord(s->ev[FS3_T_TOTAL], s->stream);
+	s->steps++;
 	return FS3_OK;
 }
 
@@ -384,6 +391,7 @@ int fs3_group_step(fs3_sim** h, int world, float dt) {
 	const int nph = fs3i_num_step_phases(h[0]);
 	for (int ph = 0; ph < nph; ph++)
 		for (int r = 0; r < world; r++) { int rc = fs3i_step_phase(h[r], ph, dt); if (rc) return rc; }
+	for (int r = 0; r < world; r++) h[r]->steps++;
 	return FS3_OK;
 }
 

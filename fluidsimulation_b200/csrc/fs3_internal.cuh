@@ -31,6 +31,7 @@ struct fs3_sim {
 	cudaStream_t stream;
 	std::string err;
 	long long launches;
+	long long steps;         // Simulate() calls since the last ResetSimulation (saved in state files)
 
 	// MAC grids.  cur = field seen by Advect / returned by get_velocity (the projected field);
 	// old = target of P2G, kept as "old grid" for FLIP (S3D.cpp:123-156).
@@ -122,6 +123,13 @@ struct fs3_sim {
 	bool ls_seed_forked;       // the seed of the current step ran on stream2 in front of the sweeps
 	float sor_persist_ratio;   // > 0 while the persisting L2 carve-out is up: hit ratio of the half sweeps' access window
 	uint32_t sor_e0;           // SOR epoch of "system set up" of the current projection
+
+	// consumer interface (consumer.cu): allocated on first use, never touched by Simulate
+	float* phi_blur;           // 7-point mean of phi (gpBlur.hlsl) as of the last fs3_blur_phi
+	bool phi_blur_valid;
+	uint32_t* bin_offsets;     // nC+1: cell-major exclusive offsets into `binned`
+	fs3_particle* binned;      // particles as 24-byte records, cell by cell
+	size_t phi_blur_bytes, bin_offsets_bytes, binned_bytes;
 
 	int* dev_flags;            // [0] particle outside, [1] level-set wait timeout, [2] cross-rank wait failed, [3] shard capacity
 	void* stage_ptr;           // device staging for AoS / hook transfers at the boundary
@@ -322,6 +330,8 @@ int fs3i_step_phase(fs3_sim* s, int phase, float dt);
 int fs3i_reset_phase(fs3_sim* s, int phase);
 int fs3i_num_step_phases(const fs3_sim* s);
 size_t fs3i_arena_bytes(int n, long long ptot, long long mig_cap, int world);
+// consumer.cu
+void fs3i_consumer_free(fs3_sim* s);
 
 template <typename T> static inline T* fs3_peer(const fs3_sim* s, int r, T* p) {
 	return reinterpret_cast<T*>(s->peer_base[r] + (reinterpret_cast<char*>(p) - s->arena));

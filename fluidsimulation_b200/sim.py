@@ -27,6 +27,10 @@ ABI_SYMBOLS = [
     "fs3_stage_times", "fs3_sor_bench", "fs3_set_phi_all_fluid", "fs3_stream", "fs3_kernel_launches",
     "fs3_create_sharded", "fs3_shard_get_handle", "fs3_shard_connect", "fs3_shard_plan", "fs3_shard_info",
     "fs3_num_local_particles", "fs3_get_local_particles", "fs3_set_local_particles", "fs3_group_create", "fs3_group_reset", "fs3_group_step",
+    "fs3_phi_device", "fs3_blur_phi", "fs3_phi_blurred_device", "fs3_get_phi_blurred", "fs3_export_binned", "fs3_get_binned",
+    "fs3_sample_phi", "fs3_sample_phi_device",
+    "fs3_save_state", "fs3_load_state", "fs3_step_count", "fs3_state_file_info", "fs3_state_file_write", "fs3_state_file_read",
+    "fs3_state_checksum",
 ]
 SHARD_HANDLE_BYTES = 128
 
@@ -35,6 +39,14 @@ class Fs3Params(C.Structure):
     _fields_ = [("sor_iterations", C.c_int), ("omega", C.c_double), ("precision", C.c_int), ("force_dt_0_01", C.c_int),
                 ("record_residuals", C.c_int), ("rho", C.c_float), ("gravity_y", C.c_float), ("nu", C.c_float),
                 ("particle_radius", C.c_float), ("record_stage_times", C.c_int)]
+
+
+class Fs3StateInfo(C.Structure):
+    """include/fs3.h fs3_state_info: the header of an on-disk state file."""
+    _fields_ = [("version", C.c_int), ("nx", C.c_int), ("ny", C.c_int), ("nz", C.c_int), ("cells_per_meter", C.c_float),
+                ("num_particles", C.c_longlong), ("total_particles", C.c_longlong), ("steps", C.c_longlong),
+                ("rank", C.c_int), ("world", C.c_int), ("has_ids", C.c_int), ("params", Fs3Params),
+                ("rank_particles", C.c_longlong * 16), ("payload_bytes", C.c_ulonglong), ("checksum", C.c_ulonglong)]
 
 
 class Fs3Error(RuntimeError):
@@ -62,7 +74,65 @@ def load_library():
         _lib.fs3_stream.argtypes = [C.c_void_p]
         _lib.fs3_num_local_particles.restype = C.c_longlong
         _lib.fs3_num_local_particles.argtypes = [C.c_void_p]
+        _lib.fs3_step_count.restype = C.c_longlong
+        _lib.fs3_step_count.argtypes = [C.c_void_p]
+        _lib.fs3_state_checksum.restype = C.c_ulonglong
+        _lib.fs3_state_checksum.argtypes = [C.c_void_p, C.c_size_t, C.c_ulonglong]
+        for name in ("fs3_save_state", "fs3_load_state"):
+            getattr(_lib, name).argtypes = [C.c_void_p, C.c_char_p]
+        _lib.fs3_state_file_info.argtypes = [C.c_char_p, C.POINTER(Fs3StateInfo)]
+        _lib.fs3_state_file_write.argtypes = [C.c_char_p, C.POINTER(Fs3StateInfo)] + [C.c_void_p] * 6
+        _lib.fs3_state_file_read.argtypes = [C.c_char_p, C.POINTER(Fs3StateInfo)] + [C.c_void_p] * 6
+        _lib.fs3_sample_phi.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]
+        _lib.fs3_sample_phi_device.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]
     return _lib
+
+
+def _host_ck(rc):
+    if rc != FS3_OK:
+        raise Fs3Error("fs3 error %d: %s" % (rc, load_library().fs3_last_error(None).decode()))
+
+
+def state_checksum(data, seed=0):
+    """64-bit checksum of a state file's payload sections (include/fs3.h fs3_state_checksum); seed chains sections."""
+    a = np.ascontiguousarray(data)
+    return int(load_library().fs3_state_checksum(_ptr(a), a.nbytes, seed))
+
+
+def state_file_info(path):
+    """Header of a state file (host only, no GPU needed)."""
+    info = Fs3StateInfo()
+    _host_ck(load_library().fs3_state_file_info(os.fsencode(path), C.byref(info)))
+    return info
+
+
+def state_file_write(path, n, particles, U, V, W, phi, ids=None, steps=0, rank=0, world=1, total_particles=None, params=None,
+                     rank_particles=None):
+    """Writes a state file from host arrays (host only): the same bytes fs3_save_state produces for that state."""
+    p = np.ascontiguousarray(particles, np.float32).reshape(-1, 6)
+    info = Fs3StateInfo()
+    info.version, info.nx, info.ny, info.nz, info.cells_per_meter = 1, n, n, n, float(n)
+    info.num_particles, info.steps, info.rank, info.world = p.shape[0], steps, rank, world
+    info.total_particles = p.shape[0] if total_particles is None else total_particles
+    info.has_ids = 0 if ids is None else 1
+    if params is not None:
+        info.params = params
+    for r, c in enumerate(rank_particles if rank_particles is not None else [p.shape[0]]):
+        info.rank_particles[r] = c
+    ids = None if ids is None else np.ascontiguousarray(ids, np.int32)
+    arrs = [np.ascontiguousarray(a, np.float32) for a in (U, V, W, phi)]
+    _host_ck(load_library().fs3_state_file_write(os.fsencode(path), C.byref(info), _ptr(p), _ptr(ids), *[_ptr(a) for a in arrs]))
+
+
+def state_file_read(path):
+    """(info, particles, ids or None, U, V, W, phi) of a state file, checksum verified (host only)."""
+    info = state_file_info(path)
+    n = info.nx
+    p = np.empty((info.num_particles, 6), np.float32)
+    ids = np.empty(info.num_particles, np.int32) if info.has_ids else None
+    U, V, W, phi = (np.empty(k, np.float32) for k in ((n + 1) * n * n, n * (n + 1) * n, n * n * (n + 1), n ** 3))
+    _host_ck(load_library().fs3_state_file_read(os.fsencode(path), C.byref(info), _ptr(p), _ptr(ids), _ptr(U), _ptr(V), _ptr(W), _ptr(phi)))
+    return info, p, ids, U, V, W, phi
 
 
 def _ptr(a):
@@ -311,6 +381,51 @@ class FluidSim3:
 
     def set_phi_all_fluid(self):
         self._ck(self._lib.fs3_set_phi_all_fluid(self._h))
+
+    # -- consumer interface (GPFluidSim's public m_gpPhiSRV / m_gpCountsSRV / m_gpBinnedParticles, Simulation.h:118-140) ----
+    def blur_phi(self):
+        """FX/gpBlur.hlsl into a second device buffer; returns the blurred phi as a host array."""
+        self._ck(self._lib.fs3_blur_phi(self._h))
+        out = np.empty(self.nC, np.float32)
+        self._ck(self._lib.fs3_get_phi_blurred(self._h, _ptr(out)))
+        return out
+
+    def phi_device(self, blurred=False):
+        """Raw device address of phi (or of the blurred copy) for a CUDA consumer."""
+        p = C.c_void_p()
+        f = self._lib.fs3_phi_blurred_device if blurred else self._lib.fs3_phi_device
+        self._ck(f(self._h, C.byref(p)))
+        return p.value
+
+    def get_binned(self):
+        """(records grouped by cell (P,6), offsets[n^3+1])."""
+        out, off = np.empty((self.num_particles, 6), np.float32), np.empty(self.nC + 1, np.uint32)
+        self._ck(self._lib.fs3_get_binned(self._h, _ptr(out), _ptr(off)))
+        return out, off
+
+    def binned_device(self):
+        """Device addresses (records, offsets) of the cell-major export."""
+        a, b = C.c_void_p(), C.c_void_p()
+        self._ck(self._lib.fs3_export_binned(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def sample_phi(self, xyz, blurred=False):
+        """FX/Render.fx map(p) at (K,3) points of the unit box: distance to the surface in metres."""
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.empty(xyz.shape[0], np.float32)
+        self._ck(self._lib.fs3_sample_phi(self._h, _ptr(xyz), C.c_longlong(xyz.shape[0]), C.c_int(int(blurred)), _ptr(out)))
+        return out
+
+    # -- on-disk state ---------------------------------------------------------------------------------
+    def save_state(self, path):
+        self._ck(self._lib.fs3_save_state(self._h, os.fsencode(path)))
+
+    def load_state(self, path):
+        self._ck(self._lib.fs3_load_state(self._h, os.fsencode(path)))
+
+    @property
+    def step_count(self):
+        return int(self._lib.fs3_step_count(self._h))
 
 
 class FluidSim3Group:

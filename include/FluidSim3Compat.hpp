@@ -73,6 +73,21 @@ public:
 		phi.resize((size_t)mX * mY * mZ);
 		Check(fs3_get_phi(m_h, phi.data()), "fs3_get_phi");
 	}
+	// on-disk state (fs3.h: lossless replacement of the reference's debugroutines.h text dumps)
+	void SaveState(const std::string& path) { Check(fs3_save_state(m_h, path.c_str()), "fs3_save_state"); }
+	void LoadState(const std::string& path) {
+		Check(fs3_load_state(m_h, path.c_str()), "fs3_load_state");
+		m_dirty = false;
+		if (m_readback) FetchParticles();
+	}
+	// what GPFluidSim hands to its renderer (Simulation.h:118-140): phi and its blurred copy as device buffers
+	const float* PhiDevice() { const float* p = nullptr; Check(fs3_phi_device(m_h, &p), "fs3_phi_device"); return p; }
+	const float* BlurredPhiDevice() {
+		const float* p = nullptr;
+		Check(fs3_blur_phi(m_h), "fs3_blur_phi");
+		Check(fs3_phi_blurred_device(m_h, &p), "fs3_phi_blurred_device");
+		return p;
+	}
 	fs3_sim* Handle() { return m_h; }
 
 	std::vector<Particle3> m_particles;   // creation order, as in the reference (never reordered)

@@ -31,6 +31,7 @@ extern "C" {
 #define FS3_ERR_CUDA (-2)       /* CUDA runtime error (message in last_error)  */
 #define FS3_ERR_STATE (-3)      /* call order / missing prerequisite stage     */
 #define FS3_ERR_PARTICLE (-4)   /* particle outside the simulation box         */
+#define FS3_ERR_IO (-5)         /* state file missing, truncated or corrupt    */
 
 /* Wire layout of one particle == reference `struct Particle3` (ParticleDefs.h:39-47): 24 bytes. */
 typedef struct fs3_particle {
@@ -144,6 +145,64 @@ int fs3_sor_bench(fs3_sim* s, int iters, float* ms_out);
 int fs3_set_phi_all_fluid(fs3_sim* s);
 void* fs3_stream(fs3_sim* s);              /* the cudaStream_t all work is queued on */
 long long fs3_kernel_launches(const fs3_sim* s); /* number of kernels launched so far by this handle */
+
+/* ---- phi / binned-particle consumer interface ------------------------------------------
+ * What the reference's GPU class hands to its renderer: the public members m_gpPhiSRV, m_gpCountsSRV and
+ * m_gpBinnedParticles (Simulation.h:118-140), the phi blur it runs after every step (FX/gpBlur.hlsl:6-17, dispatched
+ * at Simulation.cpp:561-565) and the renderer's distance lookup map() (FX/Render.fx:77-115) -- as DEVICE buffers and
+ * kernels a downstream CUDA ray-marcher can consume without a graphics API.  Device pointers stay valid until
+ * fs3_destroy (the binned buffers: until the next fs3_export_binned); their contents are ordered on fs3_stream().
+ * None of these calls changes the solver's state: the blur writes a second buffer, never phi itself. */
+int fs3_phi_device(fs3_sim* s, const float** dev_phi);              /* m_gpPhiSRV: phi[nx*ny*nz], cell units */
+/* gpBlur: 7-point mean (c + x+ + x- + y+ + y- + z+ + z-) / 7, out-of-range taps read 0 (D3D11 texture semantics).
+ * The shader updates phi in place while neighbours read it (racy); this is the deterministic reading: every tap
+ * sees the un-blurred phi.  Asynchronous. */
+int fs3_blur_phi(fs3_sim* s);
+int fs3_phi_blurred_device(fs3_sim* s, const float** dev_phi);     /* result of the last fs3_blur_phi */
+int fs3_get_phi_blurred(fs3_sim* s, float* host);
+/* m_gpBinnedParticles + prefix-summed m_gpCounts (gpBinParticles.hlsl:13-31, Simulation.cpp:660-686): the particles
+ * as 24-byte records grouped by cell (cell = x + nx*(y + ny*z), cell of a particle = roundf(n*X), Simulation3D.cpp:286-288)
+ * and offsets[nx*ny*nz + 1] with the records of cell c at [offsets[c], offsets[c+1]).  Order inside a cell: by octant,
+ * then creation id (the shader's InterlockedAdd order is unspecified).  Single-GPU handles only. */
+int fs3_export_binned(fs3_sim* s, const fs3_particle** dev_binned, const unsigned** dev_offsets);
+int fs3_get_binned(fs3_sim* s, fs3_particle* host_binned, unsigned* host_offsets);   /* host copies; either may be NULL */
+/* Render.fx map(p): distance to the surface in metres at `count` points (x,y,z triples, unit box) -- quintic-smoothed
+ * fractions on x and z, explicit fp32 trilinear filter with clamp addressing in place of the hardware sampler, result
+ * scaled by 1/nx.  blurred != 0 samples the fs3_blur_phi buffer.  The _device form takes device pointers and is
+ * asynchronous on fs3_stream(). */
+int fs3_sample_phi(fs3_sim* s, const float* xyz, long long count, int blurred, float* out);
+int fs3_sample_phi_device(fs3_sim* s, const float* dev_xyz, long long count, int blurred, float* dev_out);
+
+/* ---- on-disk state --------------------------------------------------------------------
+ * One binary file with everything Simulate() reads at the start of a step (particles in creation order, U, V, W) plus
+ * phi, the parameters and the step counter: save, destroy, create, load, and the next fs3_step continues
+ * bit-identically.  Replaces the reference's lossy tab-separated text dumps (debugroutines.h:24-178).  Layout:
+ * 256-byte header | particles (24 B each) | [creation ids, 4 B each] | U | V | W | phi, little-endian; the header
+ * carries a 64-bit checksum of the payload.  Sharded handles: every rank saves / loads its OWN file (the rank's particles
+ * with their creation ids + the whole grids) and must be restored with the same rank / world. */
+typedef struct fs3_state_info {
+	int version;                 /* 1 */
+	int nx, ny, nz;
+	float cells_per_meter;
+	long long num_particles;     /* particle records in this file */
+	long long total_particles;   /* particles of the whole simulation (== num_particles unless sharded) */
+	long long steps;             /* Simulate() calls since the last ResetSimulation */
+	int rank, world;             /* 0, 1 unless the file is one rank of a sharded run */
+	int has_ids;                 /* 1 = an id section follows the particles */
+	fs3_params params;           /* record_* switches are not stored */
+	long long rank_particles[16]; /* live particle count of every rank at save time */
+	unsigned long long payload_bytes, checksum;
+} fs3_state_info;
+int fs3_save_state(fs3_sim* s, const char* path);
+int fs3_load_state(fs3_sim* s, const char* path);
+long long fs3_step_count(const fs3_sim* s);
+/* Host-only file access (no GPU, no handle; errors through fs3_last_error(NULL)): header, whole-file write, whole-file
+ * read into caller-owned buffers sized from the header (a NULL buffer skips its section and the checksum test). */
+int fs3_state_file_info(const char* path, fs3_state_info* info);
+int fs3_state_file_write(const char* path, const fs3_state_info* info, const fs3_particle* particles, const int* ids,
+                         const float* U, const float* V, const float* W, const float* phi);
+int fs3_state_file_read(const char* path, fs3_state_info* info, fs3_particle* particles, int* ids, float* U, float* V, float* W, float* phi);
+unsigned long long fs3_state_checksum(const void* data, size_t bytes, unsigned long long seed);   /* seed 0 starts a chain */
 
 #ifdef __cplusplus
 }

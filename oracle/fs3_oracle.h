@@ -56,6 +56,11 @@ void fs3o_stage_project_f32(fs3o* s, float dt);
 /* max and L2 of divergence over phi<0 cells, as PrintDivergence (Simulation3D.cpp:1095-1138) */
 void fs3o_divergence(const fs3o* s, double* maxdiv, double* l2);
 
+/* ---- consumer interface (fs3_consumer_oracle.c; PARITY UNPINNED: restates D3D11 shaders that cannot run here) ---- */
+void fs3o_blur_phi(const float* phi, float* out, int nx, int ny, int nz);                    /* FX/gpBlur.hlsl:6-17 */
+void fs3o_sample_phi(const float* phi, int nx, int ny, int nz, const float* xyz, long count, float* out); /* FX/Render.fx:77-115 */
+void fs3o_bin_particles(const float* part6, long np, int nx, int ny, int nz, float cpm, float* binned6, unsigned* offsets); /* FX/gpBinParticles.hlsl:13-31 */
+
 #ifdef __cplusplus
 }
 #endif

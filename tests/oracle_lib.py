@@ -21,8 +21,8 @@ _u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
 
 def build_oracle():
     """(Re)build the checkers when sources are newer than the libraries."""
-    src = os.path.join(ROOT, "oracle", "fs3_oracle.c")
-    if (not os.path.exists(ORACLE_SO)) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(src) \
+    srcs = [os.path.join(ROOT, "oracle", f) for f in ("fs3_oracle.c", "fs3_consumer_oracle.c", "fs3_oracle.h")]
+    if (not os.path.exists(ORACLE_SO)) or os.path.getmtime(ORACLE_SO) < max(os.path.getmtime(s) for s in srcs) \
             or (os.path.isdir("/root/reference") and not os.path.exists(REF_SO)):
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
 
@@ -197,6 +197,45 @@ class Oracle(_Base):
         self._fn("divergence", None, C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double))(
             self.h, C.byref(a), C.byref(b))
         return a.value, b.value
+
+
+def _olib():
+    if Oracle.lib is None:
+        build_oracle()
+        Oracle.lib = C.CDLL(ORACLE_SO)
+    return Oracle.lib
+
+
+_u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
+
+
+def blur_phi(phi, n):
+    """FX/gpBlur.hlsl:6-17, deterministic (Jacobi) reading -- oracle/fs3_consumer_oracle.c."""
+    f = _olib().fs3o_blur_phi
+    f.restype, f.argtypes = None, [_f32p, _f32p, C.c_int, C.c_int, C.c_int]
+    out = np.empty(n ** 3, np.float32)
+    f(np.ascontiguousarray(phi, np.float32), out, n, n, n)
+    return out
+
+
+def sample_phi(phi, n, xyz):
+    """FX/Render.fx:77-115 map() -- oracle/fs3_consumer_oracle.c."""
+    f = _olib().fs3o_sample_phi
+    f.restype, f.argtypes = None, [_f32p, C.c_int, C.c_int, C.c_int, _f32p, C.c_long, _f32p]
+    xyz = np.ascontiguousarray(xyz, np.float32)
+    out = np.empty(xyz.shape[0], np.float32)
+    f(np.ascontiguousarray(phi, np.float32), n, n, n, xyz, xyz.shape[0], out)
+    return out
+
+
+def bin_particles(particles, n):
+    """Cell-major particle records + offsets[n^3+1] -- oracle/fs3_consumer_oracle.c."""
+    f = _olib().fs3o_bin_particles
+    f.restype, f.argtypes = None, [_f32p, C.c_long, C.c_int, C.c_int, C.c_int, C.c_float, _f32p, _u32p]
+    p = np.ascontiguousarray(particles, np.float32)
+    out, off = np.zeros_like(p), np.empty(n ** 3 + 1, np.uint32)
+    f(p, p.shape[0], n, n, n, float(n), out, off)
+    return out, off
 
 
 def cellhash(particles, n):
