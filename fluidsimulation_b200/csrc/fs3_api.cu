@@ -62,6 +62,16 @@ extern "C" {
 
 const char* fs3_last_error(const fs3_sim* s) { return s ? s->err.c_str() : g_create_error.c_str(); }
 
+// The reference's hard-coded constants (S3D.h:135-145, S3D.cpp:104,944-946).
+int fs3_default_params(fs3_params* p) {
+	if (!p) return FS3_ERR_INVALID;
+	memset((void*)p, 0, sizeof(*p));
+	p->sor_iterations = 100; p->omega = 0; p->precision = 0; p->force_dt_0_01 = 1; p->record_residuals = 0;
+	p->rho = 1000.0f; p->gravity_y = -9.81f; p->nu = 8.90f * 1e-4f / 1000.0f; p->particle_radius = 1.0f;
+	p->record_stage_times = 0;
+	return FS3_OK;
+}
+
 // Shared by fs3_create (world 1), fs3_create_sharded (one rank of a multi-process job) and fs3_group_create (all ranks in
 // this process).  A sharded handle is NOT reset here: ResetSimulation needs the peers (fs3_shard_connect / group create).
 static int create_common(int nx, int ny, int nz, float cpm, int device, int rank, int world, bool lockstep, cudaStream_t shared_stream, fs3_sim** out) {
@@ -93,11 +103,8 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	}
 	fs3_sim* s = new (std::nothrow) fs3_sim();
 	if (!s) return FS3_ERR_INVALID;
-	memset((void*)&s->prm, 0, sizeof(s->prm));
+	fs3_default_params(&s->prm);
 	s->device = device; s->nx = nx; s->ny = ny; s->nz = nz; s->cpm = cpm;
-	s->prm.sor_iterations = 100; s->prm.omega = 0; s->prm.precision = 0; s->prm.force_dt_0_01 = 1; s->prm.record_residuals = 0;
-	s->prm.rho = 1000.0f; s->prm.gravity_y = -9.81f; s->prm.nu = 8.90f * 1e-4f / 1000.0f; s->prm.particle_radius = 1.0f;  // S3D.h:135-145
-	s->prm.record_stage_times = 0;
 	s->nU = (size_t)(nx + 1) * ny * nz; s->nV = (size_t)nx * (ny + 1) * nz; s->nW = (size_t)nx * ny * (nz + 1); s->nC = (size_t)nx * ny * nz;
 	s->launches = 0; s->steps = 0; s->np = 0; s->np_in = 0; s->cap = 0; s->cur = 0; s->sorted = false; s->counted = false; s->closest_valid = false; s->system_valid = false;
 	s->sor_list_valid = false; s->sm_count = prop.multiProcessorCount;

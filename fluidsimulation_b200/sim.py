@@ -30,7 +30,7 @@ ABI_SYMBOLS = [
     "fs3_phi_device", "fs3_blur_phi", "fs3_phi_blurred_device", "fs3_get_phi_blurred", "fs3_export_binned", "fs3_get_binned",
     "fs3_sample_phi", "fs3_sample_phi_device",
     "fs3_save_state", "fs3_load_state", "fs3_step_count", "fs3_state_file_info", "fs3_state_file_write", "fs3_state_file_read",
-    "fs3_state_checksum",
+    "fs3_state_checksum", "fs3_default_params",
 ]
 SHARD_HANDLE_BYTES = 128
 
@@ -117,6 +117,8 @@ def state_file_write(path, n, particles, U, V, W, phi, ids=None, steps=0, rank=0
     info.has_ids = 0 if ids is None else 1
     if params is not None:
         info.params = params
+    else:
+        _host_ck(load_library().fs3_default_params(C.byref(info.params)))
     for r, c in enumerate(rank_particles if rank_particles is not None else [p.shape[0]]):
         info.rank_particles[r] = c
     ids = None if ids is None else np.ascontiguousarray(ids, np.int32)

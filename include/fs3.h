@@ -113,6 +113,7 @@ int fs3_get_velocity(fs3_sim* s, float* U, float* V, float* W);     /* any may b
 int fs3_set_velocity(fs3_sim* s, const float* U, const float* V, const float* W);
 int fs3_get_phi(fs3_sim* s, float* phi);
 int fs3_set_phi(fs3_sim* s, const float* phi);
+int fs3_default_params(fs3_params* p);              /* the reference's hard-coded values; host only */
 int fs3_get_params(const fs3_sim* s, fs3_params* p);
 int fs3_set_params(fs3_sim* s, const fs3_params* p);
 

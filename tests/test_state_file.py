@@ -47,6 +47,7 @@ def test_round_trip_and_layout(tmp_path):
     info = state_file_info(path)
     assert (info.version, info.nx, info.ny, info.nz, info.cells_per_meter) == (1, n, n, n, float(n))
     assert (info.num_particles, info.total_particles, info.steps, info.rank, info.world, info.has_ids) == (p.shape[0], p.shape[0], 2, 0, 1, 0)
+    assert info.params.sor_iterations == 100 and info.params.rho == 1000.0 and info.params.force_dt_0_01 == 1   # fs3_default_params
     info2, p2, ids2, u2, v2, w2, phi2 = state_file_read(path)
     assert ids2 is None and info2.checksum == info.checksum
     for a, b in ((p, p2), (u, u2), (v, v2), (w, w2), (phi, phi2)):
