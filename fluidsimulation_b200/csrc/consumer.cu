@@ -24,7 +24,9 @@ static int fail(fs3_sim* s, int code, const char* msg) { s->err = msg; return co
 // ------------------------------------------------------------------------------------------------
 // K26: out = (c + x+ + x- + y+ + y- + z+ + z-) / 7, summed left to right (gpBlur.hlsl:9-16).
 // HBM-bound: 4 B read + 4 B written per cell; the six neighbour taps hit L1/L2.  A thread owns four
-// consecutive x cells: five 128-bit loads (centre row, y and z neighbours) and two scalar x taps.
+// consecutive x cells and marches BLUR_ZC planes up: per plane three 128-bit loads (next plane's centre row,
+// the two y neighbours), two scalar x taps, one streaming 128-bit store; 3-D launch, no index divisions
+// (the first version, one thread per 4 cells with a linear index, was issue-bound: 226 instructions per thread).
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float blur7(float c, float xp, float xm, float yp, float ym, float zp, float zm) {
 	float a = __fadd_rn(c, xp);
@@ -32,27 +34,31 @@ __device__ __forceinline__ float blur7(float c, float xp, float xm, float yp, fl
 	return __fdiv_rn(a, 7.0f);
 }
 
+#define BLUR_ZC 8   // planes a thread marches through: the z taps of plane k are the centre rows of planes k-1 / k+1, kept in registers
 __global__ void __launch_bounds__(256) k_blur_phi_v4(const float* __restrict__ phi, float* __restrict__ out, int nx, int ny, int nz) {
-	const int qx = nx >> 2;
-	const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (q >= (size_t)qx * ny * nz) return;
-	const int x4 = (int)(q % qx), y = (int)((q / qx) % ny), z = (int)(q / ((size_t)qx * ny));
-	const size_t row = (size_t)nx * ((size_t)y + (size_t)ny * z), plane = (size_t)nx * ny;
-	const size_t base = row + 4 * (size_t)x4;
+	const int x4 = blockIdx.x * 32 + threadIdx.x, y = blockIdx.y * 8 + threadIdx.y, z0 = blockIdx.z * BLUR_ZC;
+	if (x4 >= (nx >> 2) || y >= ny) return;
+	const size_t plane = (size_t)nx * ny;
+	size_t base = 4 * (size_t)x4 + (size_t)nx * ((size_t)y + (size_t)ny * z0);
 	const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-	const float4 c = __ldg(reinterpret_cast<const float4*>(phi + base));
-	const float4 yp = y + 1 < ny ? __ldg(reinterpret_cast<const float4*>(phi + base + nx)) : zero;
-	const float4 ym = y > 0 ? __ldg(reinterpret_cast<const float4*>(phi + base - nx)) : zero;
-	const float4 zp = z + 1 < nz ? __ldg(reinterpret_cast<const float4*>(phi + base + plane)) : zero;
-	const float4 zm = z > 0 ? __ldg(reinterpret_cast<const float4*>(phi + base - plane)) : zero;
-	const float xl = x4 > 0 ? __ldg(phi + base - 1) : 0.f;
-	const float xr = x4 + 1 < qx ? __ldg(phi + base + 4) : 0.f;
-	float4 r;
-	r.x = blur7(c.x, c.y, xl, yp.x, ym.x, zp.x, zm.x);
-	r.y = blur7(c.y, c.z, c.x, yp.y, ym.y, zp.y, zm.y);
-	r.z = blur7(c.z, c.w, c.y, yp.z, ym.z, zp.z, zm.z);
-	r.w = blur7(c.w, xr, c.z, yp.w, ym.w, zp.w, zm.w);
-	reinterpret_cast<float4*>(out + base)[0] = r;
+	const bool has_l = x4 > 0, has_r = 4 * x4 + 4 < nx, has_yp = y + 1 < ny, has_ym = y > 0;
+	float4 zm = z0 > 0 ? __ldg(reinterpret_cast<const float4*>(phi + base - plane)) : zero;
+	float4 c = __ldg(reinterpret_cast<const float4*>(phi + base));
+	const int z1 = min(z0 + BLUR_ZC, nz);
+	for (int z = z0; z < z1; z++, base += plane) {
+		const float4 zp = z + 1 < nz ? __ldg(reinterpret_cast<const float4*>(phi + base + plane)) : zero;
+		const float4 yp = has_yp ? __ldg(reinterpret_cast<const float4*>(phi + base + nx)) : zero;
+		const float4 ym = has_ym ? __ldg(reinterpret_cast<const float4*>(phi + base - nx)) : zero;
+		const float xl = has_l ? __ldg(phi + base - 1) : 0.f;
+		const float xr = has_r ? __ldg(phi + base + 4) : 0.f;
+		float4 r;
+		r.x = blur7(c.x, c.y, xl, yp.x, ym.x, zp.x, zm.x);
+		r.y = blur7(c.y, c.z, c.x, yp.y, ym.y, zp.y, zm.y);
+		r.z = blur7(c.z, c.w, c.y, yp.z, ym.z, zp.z, zm.z);
+		r.w = blur7(c.w, xr, c.z, yp.w, ym.w, zp.w, zm.w);
+		__stcs(reinterpret_cast<float4*>(out + base), r);   // written once, read by another kernel: do not displace phi in L2
+		zm = c; c = zp;
+	}
 }
 
 __global__ void __launch_bounds__(256) k_blur_phi_scalar(const float* __restrict__ phi, float* __restrict__ out, int nx, int ny, int nz) {
@@ -155,7 +161,10 @@ static int ensure(fs3_sim* s, void** p, size_t* have, size_t bytes) {
 static int blur(fs3_sim* s) {
 	int rc = ensure(s, (void**)&s->phi_blur, &s->phi_blur_bytes, s->nC * 4);
 	if (rc) return rc;
-	if ((s->nx & 3) == 0) { k_blur_phi_v4<<<cdiv((long long)(s->nC >> 2), 256), 256, 0, s->stream>>>(s->phi, s->phi_blur, s->nx, s->ny, s->nz); FS3_LAUNCH_CHECK(); }
+	if ((s->nx & 3) == 0) {
+		dim3 grid(cdiv(s->nx >> 2, 32), cdiv(s->ny, 8), cdiv(s->nz, BLUR_ZC));
+		k_blur_phi_v4<<<grid, dim3(32, 8, 1), 0, s->stream>>>(s->phi, s->phi_blur, s->nx, s->ny, s->nz); FS3_LAUNCH_CHECK();
+	}
 	else { k_blur_phi_scalar<<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(s->phi, s->phi_blur, s->nx, s->ny, s->nz); FS3_LAUNCH_CHECK(); }
 	s->phi_blur_valid = true;
 	return FS3_OK;
