@@ -24,6 +24,9 @@ __device__ __forceinline__ float ls_dist(float cx, float cy, float cz, float4 q,
 
 // Seed (S3D.cpp:281-300): minimum kernel distance over the particles of the cell (its 8 half-cells); the
 // reference's strict `phi > k` in index order keeps the lowest index on ties.
+// A cell's particles are four runs (FS3_FOR_CELL_RANGES) of about two particles each.  The eight run bounds and then the first
+// two particles of every run are fetched before anything is compared (8 independent loads in flight per thread instead of
+// one dependent load per loop iteration); longer runs finish in a tail loop.  min by (k, id) does not depend on the order.
 __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos, const uint32_t* __restrict__ start, GridDims d, float radius,
                                                  float4* __restrict__ rec, size_t c0, size_t c1) {
 	size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -32,16 +35,33 @@ __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos,
 	float4 best = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
 	float bk = 0.f;
 	int bid = -1;
-	FS3_FOR_CELL_RANGES(start, d, x, y, z, b, e) {
-		for (uint32_t t = b; t < e; t++) {
-			float4 p = __ldg(pos + t);
-			float4 q = make_float4(__fmul_rn(p.x, (float)d.nx), __fmul_rn(p.y, (float)d.ny), __fmul_rn(p.z, (float)d.nz), p.w);
-			float k = ls_dist((float)x, (float)y, (float)z, q, radius);
-			int id = __float_as_int(p.w);
-			// reference: particles in index order, replace on strictly smaller distance (S3D.cpp:296) == min by (k, id)
-			if (bid < 0 || k < bk || (k == bk && id < bid)) { bk = k; bid = id; best = q; }
-		}
+	auto consider = [&](const float4 p) {
+		float4 q = make_float4(__fmul_rn(p.x, (float)d.nx), __fmul_rn(p.y, (float)d.ny), __fmul_rn(p.z, (float)d.nz), p.w);
+		float k = ls_dist((float)x, (float)y, (float)z, q, radius);
+		int id = __float_as_int(p.w);
+		// reference: particles in index order, replace on strictly smaller distance (S3D.cpp:296) == min by (k, id)
+		if (bid < 0 || k < bk || (k == bk && id < bid)) { bk = k; bid = id; best = q; }
+	};
+	uint32_t B[4], E[4];
+#pragma unroll
+	for (int hr = 0; hr < 4; hr++) {
+		const size_t row = (size_t)(2 * x) + (size_t)(2 * d.nx) * ((size_t)(2 * y + (hr & 1)) + (size_t)(2 * d.ny) * (2 * z + (hr >> 1)));
+		B[hr] = __ldg(start + row); E[hr] = __ldg(start + row + 2);
 	}
+	float4 P[8];
+#pragma unroll
+	for (int hr = 0; hr < 4; hr++) {
+		if (B[hr] < E[hr]) P[2 * hr] = __ldg(pos + B[hr]);
+		if (B[hr] + 1 < E[hr]) P[2 * hr + 1] = __ldg(pos + B[hr] + 1);
+	}
+#pragma unroll
+	for (int hr = 0; hr < 4; hr++) {
+		if (B[hr] < E[hr]) consider(P[2 * hr]);
+		if (B[hr] + 1 < E[hr]) consider(P[2 * hr + 1]);
+	}
+#pragma unroll
+	for (int hr = 0; hr < 4; hr++)
+		for (uint32_t t = B[hr] + 2; t < E[hr]; t++) consider(__ldg(pos + t));
 	rec[c] = best;
 }
 
