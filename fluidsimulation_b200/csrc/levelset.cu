@@ -503,6 +503,8 @@ int fs3i_levelset_init(fs3_sim* s) {
 	s->ls_sleep_ns = 256;
 	if (const char* e = getenv("FS3_LS_SLEEP_NS")) s->ls_sleep_ns = std::max(20, atoi(e));
 	long long blocks = (long long)std::max(1, per_sm) * sms;
+	// FS3_LS_BLOCKS (debug): absolute grid size, e.g. 1.5 CTAs per SM; the ticket scheme needs no co-residency, any count is valid
+	if (const char* e = getenv("FS3_LS_BLOCKS")) blocks = std::min<long long>((long long)occ * sms, std::max(1, atoi(e)));
 	s->ls_blocks = (int)std::min<long long>(blocks, 8LL * nt);
 	return FS3_OK;
 }

@@ -1,9 +1,7 @@
 #!/bin/bash
-# One bounded GPU session (edit per shot): parity tests of what changed, A/B of a tunable through bench.py.  Logs -> gpurun_out/.
+# One bounded GPU session: the whole GPU suite, smoke(), the default bench and the reference arm.  Logs -> gpurun_out/.
 mkdir -p gpurun_out
 cd "$(dirname "$0")/.."
-timeout 200 python -m pytest tests/test_gpu_parity.py tests/test_gpu_shard.py -m gpu -q -x > gpurun_out/t_parity.log 2>&1; echo "parity rc=$?"
-tail -3 gpurun_out/t_parity.log
-for it in 16 8 32; do
-  FS3_SCAN_ITEMS=$it timeout 100 python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/bench_scan$it.json 2> gpurun_out/bench_scan$it.err; echo "bench scan=$it rc=$?"
-done
+timeout 300 python -m pytest tests -m gpu -q -x > gpurun_out/t_all.log 2>&1; echo "suite rc=$?"; tail -2 gpurun_out/t_all.log
+timeout 100 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -1 gpurun_out/smoke.log
+timeout 150 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
