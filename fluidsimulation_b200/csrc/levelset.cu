@@ -496,14 +496,17 @@ int fs3i_levelset_init(fs3_sim* s) {
 	// Resident CTAs beyond what the DAG can keep busy only add pollers.  Tunables (debug): FS3_LS_BLOCKS_PER_SM, FS3_LS_SLEEP_NS.
 	const int occ = std::max(1, per_sm);
 	// The sweep is bound by its critical path, not by throughput.  Single GPU: one CTA per SM, because the sweeps run beside
-	// the P2G gather and the extrapolation (fs3_step) and should take as little from them as possible.  Sharded: two, the
-	// replicated sweeps are the longest chain of the step there.
+	// the P2G gather and the extrapolation (fs3_step) and should take as little from them as possible.  Sharded: the replicated
+	// sweeps run beside the slab's gather and the replicated extrapolation and must end with them; measured at 256^3 on 2 GPUs
+	// with 2 / 1.5 / 1.25 / 1 CTAs per SM: sweeps 3.85 / 4.14 / 4.58 / 5.34 ms, step 13.56 / 12.88 / 12.69 / 13.18 ms.  The
+	// sweeps' slack shrinks with the world size (the gather gets shorter, the sweeps do not): 1.25 per SM up to 4 ranks, 1.5 above.
 	per_sm = std::min(occ, s->world == 1 ? 1 : 2);
 	if (const char* e = getenv("FS3_LS_BLOCKS_PER_SM")) per_sm = std::min(occ, std::max(1, atoi(e)));
 	s->ls_sleep_ns = 256;
 	if (const char* e = getenv("FS3_LS_SLEEP_NS")) s->ls_sleep_ns = std::max(20, atoi(e));
 	long long blocks = (long long)std::max(1, per_sm) * sms;
-	// FS3_LS_BLOCKS (debug): absolute grid size, e.g. 1.5 CTAs per SM; the ticket scheme needs no co-residency, any count is valid
+	if (s->world > 1 && occ >= 2 && !getenv("FS3_LS_BLOCKS_PER_SM")) blocks = s->world <= 4 ? (5LL * sms) / 4 : (3LL * sms) / 2;
+	// FS3_LS_BLOCKS (debug): absolute grid size; the ticket scheme needs no co-residency, any count is valid
 	if (const char* e = getenv("FS3_LS_BLOCKS")) blocks = std::min<long long>((long long)occ * sms, std::max(1, atoi(e)));
 	s->ls_blocks = (int)std::min<long long>(blocks, 8LL * nt);
 	return FS3_OK;
