@@ -1,5 +1,5 @@
 #!/bin/bash
-# One bounded GPU session: sharded (lockstep) parity tests after the sweep grid-size change.  Logs -> gpurun_out/.
+# One bounded GPU session: edge-scene parity tests.  Logs -> gpurun_out/.
 mkdir -p gpurun_out
 cd "$(dirname "$0")/.."
-timeout 60 python -m pytest tests/test_gpu_shard.py tests/test_state_file.py -m gpu -q -x > gpurun_out/t_shard.log 2>&1; echo "shard tests rc=$?"; tail -2 gpurun_out/t_shard.log
+timeout 24 python -m pytest tests/test_edge_scenes.py -m gpu -q > gpurun_out/t_edge.log 2>&1; echo "edge tests rc=$?"; tail -15 gpurun_out/t_edge.log
