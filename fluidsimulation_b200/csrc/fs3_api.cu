@@ -369,17 +369,22 @@ int fs3_step(fs3_sim* s, float dt) {
 	static int seed_fork = -1;
 	if (seed_fork < 0) { const char* e = getenv("FS3_LS_SEED_FORK"); seed_fork = e ? atoi(e) : 0; }
 	s->ls_seed_forked = false;
-	if (!(ls_early && seed_fork) && (rc = fs3i_levelset_seed(s))) return rc;       // records LEVELSET_SEED
-	// The 8 sweeps are bound by their dependency chain, not by throughput: they run on stream2 (LEVELSET_SWEEP is recorded
-	// there) with ONE CTA per SM beside the P2G gather and the extrapolation, and are joined before the projection, which
-	// is the first stage that reads phi.  At one CTA per SM the issue-bound gather loses 1.2 ms at 256^3 and the sweeps
-	// take 6.6 instead of 3.7 ms, but all of that is hidden (19.55 -> 18.9 ms per step; 128^3: 4.24 -> 3.78; 512^3: even).
-	// FS3_LS_EARLY=0 starts them after the gather instead (the earlier arrangement; then FS3_LS_BLOCKS_PER_SM=2 is best).
-	if (ls_early && (rc = fs3i_levelset_fork(s, false, seed_fork != 0))) return rc;
-	if ((rc = fs3i_p2g_gather(s))) return rc;          // records P2G
-	if (!ls_early && (rc = fs3i_levelset_fork(s))) return rc;
-	if ((rc = fs3i_extrapolate_all(s))) return rc;
-	if ((rc = fs3i_levelset_join(s))) return rc;
+	if (s->prm.levelset_mode == 1) {
+		// line-sweep level set (opt-in, levelset_lines.cu): 26 short launches on the main stream, nothing to fork or join
+		if ((rc = fs3i_levelset_lines(s)) || (rc = fs3i_p2g_gather(s)) || (rc = fs3i_extrapolate_all(s))) return rc;
+	} else {
+		if (!(ls_early && seed_fork) && (rc = fs3i_levelset_seed(s))) return rc;       // records LEVELSET_SEED
+		// The 8 sweeps are bound by their dependency chain, not by throughput: they run on stream2 (LEVELSET_SWEEP is recorded
+		// there) with ONE CTA per SM beside the P2G gather and the extrapolation, and are joined before the projection, which
+		// is the first stage that reads phi.  At one CTA per SM the issue-bound gather loses 1.2 ms at 256^3 and the sweeps
+		// take 6.6 instead of 3.7 ms, but all of that is hidden (19.55 -> 18.9 ms per step; 128^3: 4.24 -> 3.78; 512^3: even).
+		// FS3_LS_EARLY=0 starts them after the gather instead (the earlier arrangement; then FS3_LS_BLOCKS_PER_SM=2 is best).
+		if (ls_early && (rc = fs3i_levelset_fork(s, false, seed_fork != 0))) return rc;
+		if ((rc = fs3i_p2g_gather(s))) return rc;          // records P2G
+		if (!ls_early && (rc = fs3i_levelset_fork(s))) return rc;
+		if ((rc = fs3i_extrapolate_all(s))) return rc;
+		if ((rc = fs3i_levelset_join(s))) return rc;
+	}
 	if ((rc = fs3i_project(s, dt, true, true))) return rc;  // records PROJECT_SETUP / SOR / TOVEL; gravity folded in
 	if (T) cudaEventRecord(s->ev[FS3_T_FLIP_APPLY], s->stream);
 	float alpha = flip_alpha(s, dt);
@@ -527,6 +532,8 @@ int fs3_set_params(fs3_sim* s, const fs3_params* p) {
 	if (p->sor_iterations < 0 || p->sor_iterations > s->res_cap) return fail(s, FS3_ERR_INVALID, "sor_iterations out of range [0,4096]");
 	if (p->omega >= 2.0) return fail(s, FS3_ERR_INVALID, "omega must be < 2");
 	if (!(p->rho > 0.0f)) return fail(s, FS3_ERR_INVALID, "rho must be positive");
+	if (p->levelset_mode != 0 && p->levelset_mode != 1) return fail(s, FS3_ERR_INVALID, "levelset_mode must be 0 or 1");
+	if (p->levelset_mode == 1 && s->world > 1) return fail(s, FS3_ERR_STATE, "the line-sweep level set (levelset_mode 1) is not available on a sharded handle");
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	s->prm = *p;
 	return fs3i_alloc_pressure(s);

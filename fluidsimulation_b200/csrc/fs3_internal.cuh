@@ -332,6 +332,8 @@ int fs3i_num_step_phases(const fs3_sim* s);
 size_t fs3i_arena_bytes(int n, long long ptot, long long mig_cap, int world);
 // consumer.cu
 void fs3i_consumer_free(fs3_sim* s);
+// levelset_lines.cu
+int fs3i_levelset_lines(fs3_sim* s);                                         // fs3_params.levelset_mode == 1
 
 template <typename T> static inline T* fs3_peer(const fs3_sim* s, int r, T* p) {
 	return reinterpret_cast<T*>(s->peer_base[r] + (reinterpret_cast<char*>(p) - s->arena));

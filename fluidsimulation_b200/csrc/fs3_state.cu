@@ -44,7 +44,8 @@ struct fs3_state_disk_header {
 	float rho, gravity_y, nu, particle_radius;
 	int64_t np_all[FS3_MAX_WORLD];
 	uint64_t payload_bytes, checksum;
-	uint64_t reserved;
+	int32_t levelset_mode;   // 0 in files written before the field existed (the reserved word was zero)
+	int32_t reserved;
 };
 static_assert(sizeof(fs3_state_disk_header) == 256, "state file header must be 256 bytes");
 
@@ -72,7 +73,7 @@ void to_disk(const fs3_state_info* in, fs3_state_disk_header* h) {
 	h->rank = in->rank; h->world = in->world; h->has_ids = in->has_ids ? 1 : 0;
 	h->precision = in->params.precision; h->sor_iterations = in->params.sor_iterations; h->force_dt_0_01 = in->params.force_dt_0_01;
 	h->omega = in->params.omega; h->rho = in->params.rho; h->gravity_y = in->params.gravity_y; h->nu = in->params.nu;
-	h->particle_radius = in->params.particle_radius;
+	h->particle_radius = in->params.particle_radius; h->levelset_mode = in->params.levelset_mode;
 	for (int r = 0; r < FS3_MAX_WORLD; r++) h->np_all[r] = in->rank_particles[r];
 }
 void from_disk(const fs3_state_disk_header* h, fs3_state_info* out) {
@@ -83,7 +84,7 @@ void from_disk(const fs3_state_disk_header* h, fs3_state_info* out) {
 	out->rank = h->rank; out->world = h->world; out->has_ids = h->has_ids;
 	out->params.precision = h->precision; out->params.sor_iterations = h->sor_iterations; out->params.force_dt_0_01 = h->force_dt_0_01;
 	out->params.omega = h->omega; out->params.rho = h->rho; out->params.gravity_y = h->gravity_y; out->params.nu = h->nu;
-	out->params.particle_radius = h->particle_radius;
+	out->params.particle_radius = h->particle_radius; out->params.levelset_mode = h->levelset_mode;
 	for (int r = 0; r < FS3_MAX_WORLD; r++) out->rank_particles[r] = h->np_all[r];
 	out->payload_bytes = h->payload_bytes; out->checksum = h->checksum;
 }

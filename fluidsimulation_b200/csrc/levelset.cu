@@ -371,6 +371,7 @@ int fs3i_levelset_seed(fs3_sim* s, cudaStream_t st) {
 }
 
 int fs3i_levelset(fs3_sim* s) {
+	if (s->prm.levelset_mode == 1) return fs3i_levelset_lines(s);
 	int rc = fs3i_bin(s);
 	if (rc) return rc;
 	if ((rc = fs3i_levelset_seed(s))) return rc;

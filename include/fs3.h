@@ -50,6 +50,10 @@ typedef struct fs3_params {
 	int record_residuals;   /* 1 = record ||b - A p|| after every SOR iteration (instrumentation, slower) */
 	float rho, gravity_y, nu, particle_radius; /* 1000, -9.81, 8.9e-7, 1.0 (Simulation3D.h:135-145) */
 	int record_stage_times; /* 1 = bracket every stage with CUDA events (fs3_stage_times) */
+	int levelset_mode;      /* 0 = ComputeLevelSet of the CPU class: seed + 8 Gauss-Seidel sweeps (default, the parity path);
+	                           1 = the reference's GPU formulation: closest particle among 27 cells + 24 line sweeps
+	                           (FX/gpComputeClosestParticleNeighbors.hlsl, FX/gpClosestParticlesSweep*.hlsl, Simulation.cpp:718-794).
+	                           A different level set (no grid-long dependency chain); single-GPU handles only */
 } fs3_params;
 
 /* Stage taxonomy for fs3_stage_times, named after the reference profiler marks (GPUProfiler.h:16-44). */

@@ -61,6 +61,9 @@ void fs3o_blur_phi(const float* phi, float* out, int nx, int ny, int nz);       
 void fs3o_sample_phi(const float* phi, int nx, int ny, int nz, const float* xyz, long count, float* out); /* FX/Render.fx:77-115 */
 void fs3o_bin_particles(const float* part6, long np, int nx, int ny, int nz, float cpm, float* binned6, unsigned* offsets); /* FX/gpBinParticles.hlsl:13-31 */
 
+/* ---- line-sweep level set (fs3_gpu_semantics_oracle.c; PARITY UNPINNED: restates D3D11 shaders that cannot run here) ---- */
+int fs3o_gls_levelset(const float* part6, long np, int nx, int ny, int nz, float cpm, float radius, float* phi, int* closest);
+
 #ifdef __cplusplus
 }
 #endif

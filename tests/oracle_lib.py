@@ -21,7 +21,7 @@ _u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
 
 def build_oracle():
     """(Re)build the checkers when sources are newer than the libraries."""
-    srcs = [os.path.join(ROOT, "oracle", f) for f in ("fs3_oracle.c", "fs3_consumer_oracle.c", "fs3_oracle.h")]
+    srcs = [os.path.join(ROOT, "oracle", f) for f in ("fs3_oracle.c", "fs3_consumer_oracle.c", "fs3_gpu_semantics_oracle.c", "fs3_oracle.h")]
     if (not os.path.exists(ORACLE_SO)) or os.path.getmtime(ORACLE_SO) < max(os.path.getmtime(s) for s in srcs) \
             or (os.path.isdir("/root/reference") and not os.path.exists(REF_SO)):
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
@@ -236,6 +236,17 @@ def bin_particles(particles, n):
     out, off = np.zeros_like(p), np.empty(n ** 3 + 1, np.uint32)
     f(p, p.shape[0], n, n, n, float(n), out, off)
     return out, off
+
+
+def gls_levelset(particles, n, radius=1.0):
+    """Line-sweep level set (27-cell seed + 24 line sweeps) -- oracle/fs3_gpu_semantics_oracle.c.  Returns (phi, closest)."""
+    f = _olib().fs3o_gls_levelset
+    f.restype, f.argtypes = C.c_int, [_f32p, C.c_long, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, _f32p, _i32p]
+    p = np.ascontiguousarray(particles, np.float32)
+    phi, closest = np.empty(n ** 3, np.float32), np.empty(n ** 3, np.int32)
+    rc = f(p, p.shape[0], n, n, n, float(n), float(radius), phi, closest)
+    assert rc == 0, "no particle inside the grid"
+    return phi, closest
 
 
 def cellhash(particles, n):
