@@ -80,6 +80,9 @@ def load_library():
         _lib.fs3_state_checksum.argtypes = [C.c_void_p, C.c_size_t, C.c_ulonglong]
         for name in ("fs3_save_state", "fs3_load_state"):
             getattr(_lib, name).argtypes = [C.c_void_p, C.c_char_p]
+        _lib.fs3_default_params.argtypes = [C.POINTER(Fs3Params)]
+        _lib.fs3_get_params.argtypes = [C.c_void_p, C.POINTER(Fs3Params)]
+        _lib.fs3_set_params.argtypes = [C.c_void_p, C.POINTER(Fs3Params)]
         _lib.fs3_state_file_info.argtypes = [C.c_char_p, C.POINTER(Fs3StateInfo)]
         _lib.fs3_state_file_write.argtypes = [C.c_char_p, C.POINTER(Fs3StateInfo)] + [C.c_void_p] * 6
         _lib.fs3_state_file_read.argtypes = [C.c_char_p, C.POINTER(Fs3StateInfo)] + [C.c_void_p] * 6

@@ -5,6 +5,7 @@ box); oracle/fs3_gpu_semantics_oracle.c restates a deterministic reading.  CPU p
 (phi is the distance to the particle it names, never below the true distance and close to it, independent of how the
 particle array is ordered up to ties).  GPU part (`-m gpu`): the CUDA kernels bit-exact to the restatement, run in a
 worker process."""
+import ctypes as C
 import os
 import subprocess
 import sys
@@ -73,7 +74,7 @@ def test_mode_field_is_in_the_abi_and_the_state_file(tmp_path):
     ora = Oracle(n)
     prm = Fs3Params()
     from fluidsimulation_b200 import load_library
-    load_library().fs3_default_params(prm)
+    assert load_library().fs3_default_params(C.byref(prm)) == 0
     assert prm.levelset_mode == 0
     prm.levelset_mode = 1
     path = str(tmp_path / "m.fs3")
