@@ -209,3 +209,51 @@ def test_sharded_group_save_load_resume_bitexact(tmp_path):
         h.Simulate(0.01)
     h.sync()
     assert np.array_equal(bits(h.get_particles()), bits(want)), "resumed sharded run diverged"
+
+
+# ---- C++ host tool over the same ABI (examples/state_info.cpp) and the per-rank files of a sharded run (gloo, world 2) ----
+def build_tool():
+    import subprocess
+    from fluidsimulation_b200 import build
+    build.build()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe, src = os.path.join(root, "examples", "state_info"), os.path.join(root, "examples", "state_info.cpp")
+    deps = [src, os.path.join(root, "include", "fs3.h")]
+    if (not os.path.exists(exe)) or any(os.path.getmtime(d) > os.path.getmtime(exe) for d in deps):
+        lib = os.path.join(root, "fluidsimulation_b200")
+        subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-I" + os.path.join(root, "include"), src, "-L" + lib, "-lfluidsim3_b200",
+                               "-Wl,-rpath," + lib, "-Wl,-rpath,$ORIGIN/../fluidsimulation_b200", "-o", exe])
+    return exe
+
+
+def test_cpp_state_tool(tmp_path):
+    import subprocess
+    from fluidsimulation_b200 import state_file_write
+    exe = build_tool()
+    n = 16
+    _, p, (u, v, w), phi = oracle_state(n, 1)
+    path, tsv = str(tmp_path / "t.fs3"), str(tmp_path / "slice.tsv")
+    state_file_write(path, n, p, u, v, w, phi, steps=1)
+    r = subprocess.run([exe, path, "phi", "5", tsv], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "grid 16x16x16" in r.stdout and "steps 1" in r.stdout and "OK" in r.stdout
+    l2_phi = float(r.stdout.split("phi ")[-1].split()[0])
+    assert abs(l2_phi - float(np.sqrt((phi.astype(np.float64) ** 2).sum()))) <= 1e-6 * l2_phi
+    # the text slice round-trips fp32 exactly (%.9g), unlike the reference's 6-digit dumps
+    sl = np.loadtxt(tsv, dtype=np.float64).astype(np.float32)
+    assert np.array_equal(bits(sl), bits(phi.reshape(n, n, n)[:, 5, :]))
+    raw = bytearray(open(path, "rb").read()); raw[300] ^= 1
+    bad = str(tmp_path / "bad.fs3"); open(bad, "wb").write(bytes(raw))
+    r = subprocess.run([exe, bad], capture_output=True, text=True)
+    assert r.returncode == 1 and "checksum" in r.stderr
+
+
+def test_per_rank_files_two_rank_gloo(tmp_path):
+    import subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29537", os.path.join(root, "tests", "state_shard_worker.py"), str(tmp_path)],
+                       capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "state shard worker ok" in r.stdout
