@@ -45,7 +45,7 @@ struct fs3_state_disk_header {
 	int64_t np_all[FS3_MAX_WORLD];
 	uint64_t payload_bytes, checksum;
 	int32_t levelset_mode;   // 0 in files written before the field existed (the reserved word was zero)
-	int32_t reserved;
+	int32_t extrapolation_mode;
 };
 static_assert(sizeof(fs3_state_disk_header) == 256, "state file header must be 256 bytes");
 
@@ -74,6 +74,7 @@ void to_disk(const fs3_state_info* in, fs3_state_disk_header* h) {
 	h->precision = in->params.precision; h->sor_iterations = in->params.sor_iterations; h->force_dt_0_01 = in->params.force_dt_0_01;
 	h->omega = in->params.omega; h->rho = in->params.rho; h->gravity_y = in->params.gravity_y; h->nu = in->params.nu;
 	h->particle_radius = in->params.particle_radius; h->levelset_mode = in->params.levelset_mode;
+	h->extrapolation_mode = in->params.extrapolation_mode;
 	for (int r = 0; r < FS3_MAX_WORLD; r++) h->np_all[r] = in->rank_particles[r];
 }
 void from_disk(const fs3_state_disk_header* h, fs3_state_info* out) {
@@ -85,6 +86,7 @@ void from_disk(const fs3_state_disk_header* h, fs3_state_info* out) {
 	out->params.precision = h->precision; out->params.sor_iterations = h->sor_iterations; out->params.force_dt_0_01 = h->force_dt_0_01;
 	out->params.omega = h->omega; out->params.rho = h->rho; out->params.gravity_y = h->gravity_y; out->params.nu = h->nu;
 	out->params.particle_radius = h->particle_radius; out->params.levelset_mode = h->levelset_mode;
+	out->params.extrapolation_mode = h->extrapolation_mode;
 	for (int r = 0; r < FS3_MAX_WORLD; r++) out->rank_particles[r] = h->np_all[r];
 	out->payload_bytes = h->payload_bytes; out->checksum = h->checksum;
 }

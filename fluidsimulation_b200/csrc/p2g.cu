@@ -370,7 +370,40 @@ int fs3i_extrap_fill(fs3_sim* s, int slot, float* grid, int xs, int ys, int zs) 
 	return extrap_fill_layers(s, 1, g, dims);
 }
 
+// ------------------------------------------------------------------------------------------------
+// fs3_params.extrapolation_mode = 1: the reference's GPU formulation of the extrapolation,
+// FX/gpExtrapolateParticleVelocities.hlsl:16-42 -- an invalid node becomes the mean of its valid 6-neighbours
+// (sum in the order +x -x +y -y +z -z, divided by their number), or 0 when it has none; ONE layer, no distance
+// transform, no buckets, no barrier per layer.  Out-of-range neighbours are texture reads that return 0 in D3D11,
+// which is finite, so they count as valid zeros (kept).  The shader updates the grid in place while neighbours read
+// it; reading taken here: only nodes valid BEFORE the pass are neighbours (they are never written, so the in-place
+// update below is race-free).  cd = 0 marks a valid node, as everywhere in this file.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_ex_one_layer(float* __restrict__ grid, const int* __restrict__ cd, int xs, int ys, int zs) {
+	const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (q >= (size_t)xs * ys * zs || cd[q] == 0) return;
+	const int x = (int)(q % xs), y = (int)((q / xs) % ys), z = (int)(q / ((size_t)xs * ys));
+	const size_t plane = (size_t)xs * ys;
+	float sum = 0.0f, num = 0.0f;
+#define FS3_TAP(inside, off)                                                              \
+	if (!(inside)) num = __fadd_rn(num, 1.0f);                                            \
+	else if (cd[off] == 0) { sum = __fadd_rn(sum, grid[off]); num = __fadd_rn(num, 1.0f); }
+	FS3_TAP(x + 1 < xs, q + 1)
+	FS3_TAP(x > 0, q - 1)
+	FS3_TAP(y + 1 < ys, q + xs)
+	FS3_TAP(y > 0, q - xs)
+	FS3_TAP(z + 1 < zs, q + plane)
+	FS3_TAP(z > 0, q - plane)
+#undef FS3_TAP
+	grid[q] = num != 0.0f ? __fdiv_rn(sum, num) : 0.0f;
+}
+static int extrap_one_layer(fs3_sim* s, float* grid, const int* cd, int xs, int ys, int zs) {
+	k_ex_one_layer<<<cdiv((long long)xs * ys * zs, 256), 256, 0, s->stream>>>(grid, cd, xs, ys, zs); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+
 int fs3i_extrapolate(fs3_sim* s, float* grid, int xs, int ys, int zs) {
+	if (s->prm.extrapolation_mode == 1) return extrap_one_layer(s, grid, s->cdv[0], xs, ys, zs);
 	int rc = fs3i_extrap_prepare(s, 0, xs, ys, zs);
 	if (rc) return rc;
 	return fs3i_extrap_fill(s, 0, grid, xs, ys, zs);
@@ -440,6 +473,12 @@ int fs3i_extrapolate_all(fs3_sim* s) {
 	GridDims d{s->nx, s->ny, s->nz};
 	int rc;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_EXTRAPOLATE], s->stream);
+	if (s->prm.extrapolation_mode == 1) {
+		float* gg[3] = {s->oU, s->oV, s->oW};
+		for (int ax = 0; ax < 3; ax++)
+			if ((rc = extrap_one_layer(s, gg[ax], s->cdv[ax], d.nx + (ax == 0), d.ny + (ax == 1), d.nz + (ax == 2)))) return rc;
+		return FS3_OK;
+	}
 	for (int ax = 0; ax < 3; ax++) {
 		rc = fs3i_extrap_prepare(s, ax, d.nx + (ax == 0), d.ny + (ax == 1), d.nz + (ax == 2));
 		if (rc) return rc;

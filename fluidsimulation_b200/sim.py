@@ -38,7 +38,8 @@ SHARD_HANDLE_BYTES = 128
 class Fs3Params(C.Structure):
     _fields_ = [("sor_iterations", C.c_int), ("omega", C.c_double), ("precision", C.c_int), ("force_dt_0_01", C.c_int),
                 ("record_residuals", C.c_int), ("rho", C.c_float), ("gravity_y", C.c_float), ("nu", C.c_float),
-                ("particle_radius", C.c_float), ("record_stage_times", C.c_int), ("levelset_mode", C.c_int)]
+                ("particle_radius", C.c_float), ("record_stage_times", C.c_int), ("levelset_mode", C.c_int),
+                ("extrapolation_mode", C.c_int)]
 
 
 class Fs3StateInfo(C.Structure):

@@ -54,6 +54,9 @@ typedef struct fs3_params {
 	                           1 = the reference's GPU formulation: closest particle among 27 cells + 24 line sweeps
 	                           (FX/gpComputeClosestParticleNeighbors.hlsl, FX/gpClosestParticlesSweep*.hlsl, Simulation.cpp:718-794).
 	                           A different level set (no grid-long dependency chain); single-GPU handles only */
+	int extrapolation_mode; /* 0 = ExtrapolateValues of the CPU class: every layer, by L1 distance (default, the parity path);
+	                           1 = the reference's GPU formulation: ONE layer, the rest of the air 0
+	                           (FX/gpExtrapolateParticleVelocities.hlsl:16-42); single-GPU handles only */
 } fs3_params;
 
 /* Stage taxonomy for fs3_stage_times, named after the reference profiler marks (GPUProfiler.h:16-44). */

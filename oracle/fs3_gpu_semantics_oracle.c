@@ -101,3 +101,29 @@ int fs3o_gls_levelset(const float* part6, long np, int nx, int ny, int nz, float
 	free(q); free(order); free(offsets); free(key); free(cursor);
 	return 0;
 }
+
+/* FX/gpExtrapolateParticleVelocities.hlsl:16-42 -- one layer: an invalid node (the shader's +INF marker; here valid[q] == 0)
+ * becomes the mean of its valid 6-neighbours, summed in the order +x -x +y -y +z -z and divided by their number, or 0 when
+ * it has none.  Out-of-range neighbours are texture reads that return 0 (finite), so they count as valid zeros.  The shader
+ * updates the grid in place while neighbours read it (racy); reading: only nodes valid before the pass are neighbours. */
+void fs3o_gls_extrapolate(float* grid, const unsigned char* valid, int xs, int ys, int zs) {
+	size_t plane = (size_t)xs * ys, n = plane * zs;
+	float* out = (float*)malloc(sizeof(float) * n);
+	memcpy(out, grid, sizeof(float) * n);
+	for (int z = 0; z < zs; z++)
+		for (int y = 0; y < ys; y++)
+			for (int x = 0; x < xs; x++) {
+				size_t q = (size_t)x + (size_t)xs * y + plane * z;
+				if (valid[q]) continue;
+				float sum = 0.0f, num = 0.0f;
+				const int inside[6] = {x + 1 < xs, x > 0, y + 1 < ys, y > 0, z + 1 < zs, z > 0};
+				const size_t off[6] = {q + 1, q - 1, q + xs, q - xs, q + plane, q - plane};
+				for (int k = 0; k < 6; k++) {
+					if (!inside[k]) num = num + 1.0f;
+					else if (valid[off[k]]) { sum = sum + grid[off[k]]; num = num + 1.0f; }
+				}
+				out[q] = num != 0.0f ? sum / num : 0.0f;
+			}
+	memcpy(grid, out, sizeof(float) * n);
+	free(out);
+}

@@ -62,6 +62,7 @@ void fs3o_sample_phi(const float* phi, int nx, int ny, int nz, const float* xyz,
 void fs3o_bin_particles(const float* part6, long np, int nx, int ny, int nz, float cpm, float* binned6, unsigned* offsets); /* FX/gpBinParticles.hlsl:13-31 */
 
 /* ---- line-sweep level set (fs3_gpu_semantics_oracle.c; PARITY UNPINNED: restates D3D11 shaders that cannot run here) ---- */
+void fs3o_gls_extrapolate(float* grid, const unsigned char* valid, int xs, int ys, int zs);   /* FX/gpExtrapolateParticleVelocities.hlsl:16-42 */
 int fs3o_gls_levelset(const float* part6, long np, int nx, int ny, int nz, float cpm, float radius, float* phi, int* closest);
 
 #ifdef __cplusplus

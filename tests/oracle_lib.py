@@ -249,6 +249,15 @@ def gls_levelset(particles, n, radius=1.0):
     return phi, closest
 
 
+def gls_extrapolate(src, valid, xs, ys, zs):
+    """One-layer extrapolation (FX/gpExtrapolateParticleVelocities.hlsl) -- oracle/fs3_gpu_semantics_oracle.c."""
+    f = _olib().fs3o_gls_extrapolate
+    f.restype, f.argtypes = None, [_f32p, _u8p, C.c_int, C.c_int, C.c_int]
+    g = np.ascontiguousarray(src, np.float32).copy()
+    f(g, np.ascontiguousarray(valid, np.uint8), xs, ys, zs)
+    return g
+
+
 def cellhash(particles, n):
     """word-wise FNV-1a over per-particle cell indices (roundf semantics)."""
     p = particles[:, :3].astype(np.float32) * np.float32(n)
