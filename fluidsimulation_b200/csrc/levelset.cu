@@ -500,13 +500,16 @@ int fs3i_levelset_init(fs3_sim* s) {
 	// the P2G gather and the extrapolation (fs3_step) and should take as little from them as possible.  Sharded: the replicated
 	// sweeps run beside the slab's gather and the replicated extrapolation and must end with them; measured at 256^3 on 2 GPUs
 	// with 2 / 1.5 / 1.25 / 1 CTAs per SM: sweeps 3.85 / 4.14 / 4.58 / 5.34 ms, step 13.56 / 12.88 / 12.69 / 13.18 ms.  The
-	// sweeps' slack shrinks with the world size (the gather gets shorter, the sweeps do not): 1.25 per SM up to 4 ranks, 1.5 above.
+	// sweeps' slack shrinks with the world size (the gather gets shorter, the sweeps do not) and is gone at 8 ranks -- there the
+	// extrapolation stage already ends with the join (sweeps 3.87 ms + the seed barrier = gather 1.57 + extrapolation 2.99) --
+	// so 1.25 per SM on 2 ranks (measured), 1.5 on 3-4 (by the same timeline: sweeps + barrier 4.4 ms against gather +
+	// extrapolation 5.2 ms at N = 4) and the measured 2 per SM above.
 	per_sm = std::min(occ, s->world == 1 ? 1 : 2);
 	if (const char* e = getenv("FS3_LS_BLOCKS_PER_SM")) per_sm = std::min(occ, std::max(1, atoi(e)));
 	s->ls_sleep_ns = 256;
 	if (const char* e = getenv("FS3_LS_SLEEP_NS")) s->ls_sleep_ns = std::max(20, atoi(e));
 	long long blocks = (long long)std::max(1, per_sm) * sms;
-	if (s->world > 1 && occ >= 2 && !getenv("FS3_LS_BLOCKS_PER_SM")) blocks = s->world <= 4 ? (5LL * sms) / 4 : (3LL * sms) / 2;
+	if (s->world > 1 && s->world <= 4 && occ >= 2 && !getenv("FS3_LS_BLOCKS_PER_SM")) blocks = s->world == 2 ? (5LL * sms) / 4 : (3LL * sms) / 2;
 	// FS3_LS_BLOCKS (debug): absolute grid size; the ticket scheme needs no co-residency, any count is valid
 	if (const char* e = getenv("FS3_LS_BLOCKS")) blocks = std::min<long long>((long long)occ * sms, std::max(1, atoi(e)));
 	s->ls_blocks = (int)std::min<long long>(blocks, 8LL * nt);
