@@ -153,3 +153,19 @@ def test_gpu_consumer_at_256_properties():
     # and the export is a permutation of the particles: column sums agree exactly in integer arithmetic
     p = sim.get_particles()
     assert np.array_equal(bits(out).sum(0, dtype=np.uint64), bits(p).sum(0, dtype=np.uint64))
+
+
+def test_restatements_match_committed_fixture():
+    """tests/golden/gpuform16.npz freezes the deterministic reading of the 8(f) restatements (see make_golden_8f.py)."""
+    import os
+    import sys
+    g = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    sys.path.insert(0, g)
+    import make_golden_8f
+    want = np.load(os.path.join(g, "gpuform16.npz"))
+    got = make_golden_8f.compute()
+    assert sorted(want.files) == sorted(got)
+    for k in want.files:
+        a, b = np.ascontiguousarray(got[k]), want[k]
+        assert a.dtype == b.dtype and a.shape == b.shape, k
+        assert a.tobytes() == b.tobytes(), k
