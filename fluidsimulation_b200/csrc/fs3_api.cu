@@ -534,7 +534,6 @@ int fs3_set_params(fs3_sim* s, const fs3_params* p) {
 	if (!(p->rho > 0.0f)) return fail(s, FS3_ERR_INVALID, "rho must be positive");
 	if (p->levelset_mode != 0 && p->levelset_mode != 1) return fail(s, FS3_ERR_INVALID, "levelset_mode must be 0 or 1");
 	if (p->extrapolation_mode != 0 && p->extrapolation_mode != 1) return fail(s, FS3_ERR_INVALID, "extrapolation_mode must be 0 or 1");
-	if (p->extrapolation_mode == 1 && s->world > 1) return fail(s, FS3_ERR_STATE, "the one-layer extrapolation (extrapolation_mode 1) is not available on a sharded handle");
 	if (p->levelset_mode == 1 && s->world > 1) return fail(s, FS3_ERR_STATE, "the line-sweep level set (levelset_mode 1) is not available on a sharded handle");
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	s->prm = *p;

@@ -56,7 +56,8 @@ typedef struct fs3_params {
 	                           A different level set (no grid-long dependency chain); single-GPU handles only */
 	int extrapolation_mode; /* 0 = ExtrapolateValues of the CPU class: every layer, by L1 distance (default, the parity path);
 	                           1 = the reference's GPU formulation: ONE layer, the rest of the air 0
-	                           (FX/gpExtrapolateParticleVelocities.hlsl:16-42); single-GPU handles only */
+	                           (FX/gpExtrapolateParticleVelocities.hlsl:16-42); on a sharded handle it runs replicated on the
+	                           gathered P2G grids, like the default */
 } fs3_params;
 
 /* Stage taxonomy for fs3_stage_times, named after the reference profiler marks (GPUProfiler.h:16-44). */

@@ -42,6 +42,19 @@ def main():
         assert np.array_equal(bits(s2.get_phi()), bits(want_phi))
         s2.close()
     sim.close()
+    # z-slab sharded (2 ranks in lockstep on this GPU): the one-layer pass runs replicated on the gathered grids, bit-identical
+    from fluidsimulation_b200 import FluidSim3Group
+    one, grp = FluidSim3(16, 16, 16, 16.0), FluidSim3Group(16, 2)
+    one.set_params(extrapolation_mode=1)
+    grp.set_params(extrapolation_mode=1)
+    for _ in range(3):
+        one.Simulate(0.01)
+        grp.Simulate(0.01)
+    one.sync()
+    grp.sync()
+    assert np.array_equal(bits(grp.get_particles()), bits(one.get_particles())), "sharded one-layer extrapolation differs from single GPU"
+    grp.close()
+    one.close()
     print("GEX_WORKER_OK")
 
 
