@@ -53,7 +53,7 @@ int fs3i_check_flags(fs3_sim* s) {
 	if (h[0] || h[1] || h[2] || h[3]) FS3_CUDA(cudaMemsetAsync(s->dev_flags, 0, 4 * sizeof(int), s->stream));
 	if (h[2]) return fail(s, FS3_ERR_STATE, "a cross-rank wait was not satisfied (peer rank missing, out of step, or timed out); results invalid");
 	if (h[3]) return fail(s, FS3_ERR_STATE, "a slab's particle, ghost-layer or migration capacity was exceeded; results invalid");
-	if (h[1]) return fail(s, FS3_ERR_STATE, "level-set dataflow sweep timed out waiting for a tile dependency (results invalid)");
+	if (h[1]) return fail(s, FS3_ERR_STATE, "a device-side dependency wait timed out (level-set tile hand-off or extrapolation layer barrier); results invalid");
 	if (h[0]) return fail(s, FS3_ERR_PARTICLE, "a particle lay outside the grid (or its rank's slab) when binned (positions must be inside the Advect clamp box)");
 	return FS3_OK;
 }
@@ -107,7 +107,7 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	s->device = device; s->nx = nx; s->ny = ny; s->nz = nz; s->cpm = cpm;
 	s->nU = (size_t)(nx + 1) * ny * nz; s->nV = (size_t)nx * (ny + 1) * nz; s->nW = (size_t)nx * ny * (nz + 1); s->nC = (size_t)nx * ny * nz;
 	s->launches = 0; s->steps = 0; s->np = 0; s->np_in = 0; s->cap = 0; s->cur = 0; s->sorted = false; s->counted = false; s->closest_valid = false; s->system_valid = false;
-	s->sor_list_valid = false; s->sm_count = prop.multiProcessorCount;
+	s->sor_list_valid = false; s->sm_count = prop.multiProcessorCount; s->sor_per_sm = 0; s->persist_cap = -1;
 	s->alloc_precision = -1; s->res_cap = 4096; s->res_count = 0; s->stage_ptr = nullptr; s->stage_bytes = 0;
 	s->rank = rank; s->world = world; s->z0 = rank * (nz / world); s->z1 = s->z0 + nz / world; s->lockstep = lockstep;
 	s->bar_epoch = 0; s->sor_epoch = 0; s->sor_e0 = 0; s->n_ipc_opened = 0; s->poff = 0; s->gcap = 0; s->mig_cap = 0;
@@ -364,24 +364,18 @@ int fs3_step(fs3_sim* s, float dt) {
 	if ((rc = fs3i_advect(s, dt))) return rc;
 	if (T) cudaEventRecord(s->ev[FS3_T_BIN], s->stream);
 	if ((rc = fs3i_bin(s))) return rc;
-	static int ls_early = -1;
-	if (ls_early < 0) { const char* e = getenv("FS3_LS_EARLY"); ls_early = e ? atoi(e) : 1; }
-	static int seed_fork = -1;
-	if (seed_fork < 0) { const char* e = getenv("FS3_LS_SEED_FORK"); seed_fork = e ? atoi(e) : 0; }
 	s->ls_seed_forked = false;
 	if (s->prm.levelset_mode == 1) {
 		// line-sweep level set (opt-in, levelset_lines.cu): 26 short launches on the main stream, nothing to fork or join
 		if ((rc = fs3i_levelset_lines(s)) || (rc = fs3i_p2g_gather(s)) || (rc = fs3i_extrapolate_all(s))) return rc;
 	} else {
-		if (!(ls_early && seed_fork) && (rc = fs3i_levelset_seed(s))) return rc;       // records LEVELSET_SEED
+		if ((rc = fs3i_levelset_seed(s))) return rc;       // records LEVELSET_SEED
 		// The 8 sweeps are bound by their dependency chain, not by throughput: they run on stream2 (LEVELSET_SWEEP is recorded
 		// there) with ONE CTA per SM beside the P2G gather and the extrapolation, and are joined before the projection, which
 		// is the first stage that reads phi.  At one CTA per SM the issue-bound gather loses 1.2 ms at 256^3 and the sweeps
 		// take 6.6 instead of 3.7 ms, but all of that is hidden (19.55 -> 18.9 ms per step; 128^3: 4.24 -> 3.78; 512^3: even).
-		// FS3_LS_EARLY=0 starts them after the gather instead (the earlier arrangement; then FS3_LS_BLOCKS_PER_SM=2 is best).
-		if (ls_early && (rc = fs3i_levelset_fork(s, false, seed_fork != 0))) return rc;
+		if ((rc = fs3i_levelset_fork(s, false, false))) return rc;
 		if ((rc = fs3i_p2g_gather(s))) return rc;          // records P2G
-		if (!ls_early && (rc = fs3i_levelset_fork(s))) return rc;
 		if ((rc = fs3i_extrapolate_all(s))) return rc;
 		if ((rc = fs3i_levelset_join(s))) return rc;
 	}

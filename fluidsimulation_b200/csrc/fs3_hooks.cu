@@ -32,7 +32,146 @@ __global__ void k_cell_counts(const uint32_t* __restrict__ start, GridDims d, in
 	out[q] = n;
 }
 
+// ---- PrintDivergence (S3D.cpp:1095-1138) and the state fingerprints ------------------------------------------------
+// Block partials in a fixed tree order, then one block adds the partials in index order: the result does not depend on
+// scheduling (no floating-point atomics).
+__global__ void __launch_bounds__(256) k_divergence(const float* __restrict__ U, const float* __restrict__ V, const float* __restrict__ W,
+                                                    const float* __restrict__ phi, GridDims d, size_t c0, size_t c1, double* __restrict__ part) {
+	const size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	double sq = 0.0, mx = 0.0;
+	if (c < c1 && phi[c] < 0.0f) {
+		const int x = (int)(c % d.nx), y = (int)((c / d.nx) % d.ny), z = (int)(c / ((size_t)d.nx * d.ny));
+		const size_t iu = (size_t)x + (size_t)(d.nx + 1) * ((size_t)y + (size_t)d.ny * z);
+		const size_t iv = (size_t)x + (size_t)d.nx * ((size_t)y + (size_t)(d.ny + 1) * z);
+		// velUp - velDown + velRight - velLeft + velFwds - velBkwds, left to right in fp32 (S3D.cpp:1118)
+		float dv = __fsub_rn(V[iv + d.nx], V[iv]);
+		dv = __fadd_rn(dv, U[iu + 1]); dv = __fsub_rn(dv, U[iu]);
+		dv = __fadd_rn(dv, W[c + (size_t)d.nx * d.ny]); dv = __fsub_rn(dv, W[c]);
+		mx = dv > 0.0f ? (double)dv : 0.0;
+		sq = (double)__fmul_rn(dv, dv);
+	}
+	__shared__ double s_sq[256], s_mx[256];
+	s_sq[threadIdx.x] = sq; s_mx[threadIdx.x] = mx;
+	__syncthreads();
+	for (int o = 128; o > 0; o >>= 1) {
+		if (threadIdx.x < o) { s_sq[threadIdx.x] += s_sq[threadIdx.x + o]; s_mx[threadIdx.x] = fmax(s_mx[threadIdx.x], s_mx[threadIdx.x + o]); }
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) { part[2 * (size_t)blockIdx.x] = s_sq[0]; part[2 * (size_t)blockIdx.x + 1] = s_mx[0]; }
+}
+// out[0] = max of the partial maxima, out[1] = sum of the partial sums, both in a fixed order
+__global__ void __launch_bounds__(256) k_partials_final(const double* __restrict__ part, size_t nblocks, double* __restrict__ out) {
+	__shared__ double s_sq[256], s_mx[256];
+	double sq = 0.0, mx = 0.0;
+	for (size_t b = threadIdx.x; b < nblocks; b += 256) { sq += part[2 * b]; mx = fmax(mx, part[2 * b + 1]); }
+	s_sq[threadIdx.x] = sq; s_mx[threadIdx.x] = mx;
+	__syncthreads();
+	for (int o = 128; o > 0; o >>= 1) {
+		if (threadIdx.x < o) { s_sq[threadIdx.x] += s_sq[threadIdx.x + o]; s_mx[threadIdx.x] = fmax(s_mx[threadIdx.x], s_mx[threadIdx.x + o]); }
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) { out[0] = s_mx[0]; out[1] = s_sq[0]; }
+}
+
+__device__ __forceinline__ unsigned long long fs3_mix64(unsigned long long x) {   // splitmix64 finaliser
+	x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull; x ^= x >> 27; x *= 0x94d049bb133111ebull; x ^= x >> 31;
+	return x;
+}
+__device__ __forceinline__ void fs3_warp_add_u64(unsigned long long v, unsigned long long* dst) {
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+	if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst, v);   // integer addition modulo 2^64: order-independent
+}
+__global__ void __launch_bounds__(256) k_check_particles(const float4* __restrict__ pos, const float4* __restrict__ vel, long long np, GridDims d,
+                                                         unsigned long long* __restrict__ out) {
+	const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned long long hp = 0, hc = 0, cnt = 0;
+	if (i < np) {
+		const float4 p = pos[i], v = vel[i];
+		const int id = __float_as_int(p.w);
+		if (id >= 0) {
+			const int cx = fs3_cell_axis(p.x, (float)d.nx), cy = fs3_cell_axis(p.y, (float)d.ny), cz = fs3_cell_axis(p.z, (float)d.nz);
+			const unsigned cell = (unsigned)(cx + d.nx * (cy + d.ny * cz));
+			hc = fs3_mix64(((unsigned long long)(unsigned)id << 32) | cell);
+			unsigned long long h = hc;
+			h = fs3_mix64(h ^ (((unsigned long long)__float_as_uint(p.x) << 32) | __float_as_uint(p.y)));
+			h = fs3_mix64(h ^ (((unsigned long long)__float_as_uint(p.z) << 32) | __float_as_uint(v.x)));
+			h = fs3_mix64(h ^ (((unsigned long long)__float_as_uint(v.y) << 32) | __float_as_uint(v.z)));
+			hp = h; cnt = 1;
+		}
+	}
+	fs3_warp_add_u64(hp, out + 0); fs3_warp_add_u64(hc, out + 1); fs3_warp_add_u64(cnt, out + 2);
+}
+__global__ void __launch_bounds__(256) k_check_grid(const float* __restrict__ g, size_t q0, size_t q1, unsigned long long* __restrict__ hash, double* __restrict__ part) {
+	const size_t q = q0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned long long h = 0;
+	double v = 0.0;
+	if (q < q1) { const float f = g[q]; h = fs3_mix64(((unsigned long long)q << 32) ^ (unsigned long long)__float_as_uint(f) ^ 0x5851f42d4c957f2dull); v = (double)f; }
+	fs3_warp_add_u64(h, hash);
+	__shared__ double s_v[256];
+	s_v[threadIdx.x] = v;
+	__syncthreads();
+	for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) s_v[threadIdx.x] += s_v[threadIdx.x + o]; __syncthreads(); }
+	if (threadIdx.x == 0) { part[2 * (size_t)blockIdx.x] = s_v[0]; part[2 * (size_t)blockIdx.x + 1] = 0.0; }
+}
+
 extern "C" {
+
+int fs3_get_divergence(fs3_sim* s, double* maxdiv, double* l2) {
+	ENTER(s);
+	if (!maxdiv || !l2) return FS3_ERR_INVALID;
+	const size_t plane = (size_t)s->nx * s->ny, c0 = plane * s->z0, c1 = plane * s->z1;
+	const size_t nb = (c1 - c0 + 255) / 256;
+	int rc = fs3i_staging(s, (2 * nb + 2) * sizeof(double));
+	if (rc) return rc;
+	double* part = (double*)s->stage_ptr;
+	k_divergence<<<(unsigned)nb, 256, 0, s->stream>>>(s->U, s->V, s->W, s->phi, GridDims{s->nx, s->ny, s->nz}, c0, c1, part + 2); FS3_LAUNCH_CHECK();
+	k_partials_final<<<1, 256, 0, s->stream>>>(part + 2, nb, part); FS3_LAUNCH_CHECK();
+	double h[2];
+	FS3_CUDA(cudaMemcpyAsync(h, part, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	*maxdiv = h[0];
+	*l2 = std::sqrt(h[1]);
+	return FS3_OK;
+}
+
+int fs3_checksum(fs3_sim* s, fs3_check* out) {
+	ENTER(s);
+	if (!out) return FS3_ERR_INVALID;
+	size_t nmax = s->nW > s->nU ? s->nW : s->nU;
+	if (s->nV > nmax) nmax = s->nV;
+	const size_t nbmax = (nmax + 255) / 256;
+	int rc = fs3i_staging(s, 64 + (2 * nbmax + 2) * sizeof(double));
+	if (rc) return rc;
+	unsigned long long* acc = (unsigned long long*)s->stage_ptr;            // [0..2] particles, [3..6] grid hashes
+	double* part = (double*)((char*)s->stage_ptr + 64);
+	FS3_CUDA(cudaMemsetAsync(acc, 0, 64, s->stream));
+	const GridDims d{s->nx, s->ny, s->nz};
+	if (s->np_in > 0) {
+		k_check_particles<<<cdiv(s->np_in, 256), 256, 0, s->stream>>>(s->pos[s->cur] + s->poff, s->vel[s->cur] + s->poff, s->np_in, d, acc);
+		FS3_LAUNCH_CHECK();
+	}
+	const float* g[4] = {s->U, s->V, s->W, s->phi};
+	double sums[4] = {0, 0, 0, 0};
+	for (int k = 0; k < 4; k++) {
+		size_t q0, q1;
+		if (k < 3) fs3i_p2g_range(s, k, &q0, &q1);
+		else { q0 = (size_t)s->nx * s->ny * s->z0; q1 = (size_t)s->nx * s->ny * s->z1; }
+		const size_t nb = (q1 - q0 + 255) / 256;
+		k_check_grid<<<(unsigned)nb, 256, 0, s->stream>>>(g[k], q0, q1, acc + 3 + k, part + 2); FS3_LAUNCH_CHECK();
+		k_partials_final<<<1, 256, 0, s->stream>>>(part + 2, nb, part); FS3_LAUNCH_CHECK();
+		double h[2];
+		FS3_CUDA(cudaMemcpyAsync(h, part, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
+		FS3_CUDA(cudaStreamSynchronize(s->stream));
+		sums[k] = h[1];
+	}
+	unsigned long long h[7];
+	FS3_CUDA(cudaMemcpyAsync(h, acc, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
+	FS3_CUDA(cudaStreamSynchronize(s->stream));
+	out->particle_hash = h[0]; out->cell_hash = h[1]; out->particles = (long long)h[2];
+	for (int k = 0; k < 4; k++) { out->grid_hash[k] = h[3 + k]; out->grid_sum[k] = sums[k]; }
+	return FS3_OK;
+}
 
 int fs3_stage_advect(fs3_sim* s, float dt) { ENTER(s); SINGLE(s); return fs3i_advect(s, dt); }
 int fs3_stage_bin(fs3_sim* s) { ENTER(s); SINGLE(s); return fs3i_bin(s); }

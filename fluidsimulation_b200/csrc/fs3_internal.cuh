@@ -89,6 +89,8 @@ struct fs3_sim {
 	uint32_t* sor_count[2];     // = sor_pos[c] + nvec (device pointer to the list length)
 	bool sor_list_valid;
 	int sm_count;
+	int sor_per_sm;            // resident CTAs per SM of the sweep kernel (0 = not queried yet)
+	long long persist_cap;     // largest persisting-L2 carve-out of the device (-1 = not queried yet)
 	double* res;               // device: [2*i] sum r^2, [2*i+1] max |r| (as double bits)
 	int res_cap, res_count;
 

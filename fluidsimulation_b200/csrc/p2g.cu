@@ -263,8 +263,10 @@ __device__ __forceinline__ void ex_fill_node(const ExGrid& G, int q, int m) {
 	__stcg(g + q, __fdiv_rn(sum, cnt));
 }
 
-__global__ void __launch_bounds__(EX_THREADS, 3) k_ex_fill_layers(ExGrids P, uint32_t* __restrict__ arrive) {
+__global__ void __launch_bounds__(EX_THREADS, 3) k_ex_fill_layers(ExGrids P, uint32_t* __restrict__ arrive, int* __restrict__ flags) {
 	const uint32_t tid = blockIdx.x * EX_THREADS + threadIdx.x, nthr = gridDim.x * EX_THREADS;
+	__shared__ int s_abort;
+	if (threadIdx.x == 0) s_abort = 0;
 	uint32_t tot[3], b[3], e[3];
 	int pq[3], pm[3];   // this thread's first node of the coming layer and its closer-mask, fetched BEFORE the barrier
 #pragma unroll
@@ -305,9 +307,17 @@ __global__ void __launch_bounds__(EX_THREADS, 3) k_ex_fill_layers(ExGrids P, uin
 			atomicAdd(arrive, 1u);
 			const uint32_t need = (uint32_t)d * gridDim.x;
 			uint32_t v;
-			do { asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(arrive) : "memory"); } while (v < need);
+			// The launch is cooperative, so every CTA is resident and the spin ends; the clock bound only turns a broken
+			// assumption (or a CTA that gave up) into an error report instead of a hang.
+			const long long t0 = clock64();
+			for (unsigned it = 1;; it++) {
+				asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(arrive) : "memory");
+				if (v >= need) break;
+				if ((it & 4095u) == 0 && (*reinterpret_cast<volatile int*>(flags + 1) || clock64() - t0 > 8000000000LL)) { flags[1] = 1; s_abort = 1; break; }
+			}
 		}
 		__syncthreads();
+		if (s_abort) return;
 	}
 }
 
@@ -350,16 +360,12 @@ static int extrap_fill_layers(fs3_sim* s, int count, float* const* grids, const 
 	}
 	for (int k = count; k < 3; k++) P.a[k] = P.a[0];
 	FS3_CUDA(cudaMemsetAsync(s->ex_arrive, 0, sizeof(uint32_t), s->stream));
-	// All CTAs co-resident (the barrier needs that).  One CTA per SM, 512 threads x <= 40 registers, fits beside the two
-	// resident CTAs of the level-set sweep running on stream2; FS3_EX_BLOCKS_PER_SM (debug) trades that overlap for threads.
-	static int occ = 0, forced = 0;
-	if (!occ) {
-		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ex_fill_layers, EX_THREADS, 0);
-		occ = std::max(1, occ);
-		if (const char* e = getenv("FS3_EX_BLOCKS_PER_SM")) forced = std::max(1, std::min(occ, atoi(e)));
-	}
-	const int per_sm = forced ? forced : 1;
-	k_ex_fill_layers<<<s->sm_count * per_sm, EX_THREADS, 0, s->stream>>>(P, s->ex_arrive); FS3_LAUNCH_CHECK();
+	// The grid barrier needs every CTA resident: a COOPERATIVE launch makes that all-or-nothing (the driver only starts the grid
+	// when all of it fits, also beside other handles or contexts on the device).  One CTA per SM, 512 threads x <= 40 registers:
+	// fits beside the resident CTAs of the level-set sweep running on stream2.
+	void* args[] = {(void*)&P, (void*)&s->ex_arrive, (void*)&s->dev_flags};
+	FS3_CUDA(cudaLaunchCooperativeKernel((const void*)k_ex_fill_layers, dim3(s->sm_count), dim3(EX_THREADS), args, 0, s->stream));
+	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 
@@ -421,9 +427,6 @@ template <int AX> static int p2g_launch(fs3_sim* s, float* grid, int* cd) {
 	const int xs = s->nx + (AX == 0), ys = s->ny + (AX == 1);
 	const int kbeg = s->z0, kend = s->z1 + ((AX == 2 && s->rank == s->world - 1) ? 1 : 0);
 	dim3 g(cdiv(xs, 32 * P2G_KX), cdiv(ys, 2 * P2G_KY), cdiv(kend - kbeg, 2 * P2G_KZ));
-	static int carve = -2;   // debug: FS3_P2G_CARVEOUT = preferred shared-memory carve-out in percent (L1 sensitivity experiments)
-	if (carve == -2) { const char* e = getenv("FS3_P2G_CARVEOUT"); carve = e ? atoi(e) : -1; }
-	if (carve >= 0) cudaFuncSetAttribute(k_p2g_gather<AX>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
 	k_p2g_gather<AX><<<g, 128, 0, s->stream>>>(s->pos[s->cur], s->vel[s->cur], s->cell_start, d, s->cpm, grid, cd, kbeg, kend, s->world > 1 ? 1 : 0);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;

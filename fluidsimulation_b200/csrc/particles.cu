@@ -386,9 +386,8 @@ __global__ void __launch_bounds__(SCAN_T) k_scan_lookback(const uint32_t* __rest
 
 int fs3i_scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n, uint32_t base0) {
 	// items per thread: a tile's cost is a chain of latencies (ticket, load, block scan, look-back, store), so larger tiles
-	// amortise it better -- BIN at 256^3 with 8 / 16 / 32 items: 1.80 / 1.67 / 1.65 ms.  FS3_SCAN_ITEMS overrides for measurements.
-	static int items = -1;
-	if (items < 0) { const char* e = getenv("FS3_SCAN_ITEMS"); items = e ? atoi(e) : 32; if (items != 8 && items != 16) items = 32; }
+	// amortise it better -- BIN at 256^3 with 8 / 16 / 32 items: 1.80 / 1.67 / 1.65 ms.
+	const int items = 32;
 	int nb = cdiv((long long)n, SCAN_T * items);
 	if ((size_t)nb > s->scan_block_cap) { s->err = "scan scratch too small"; return FS3_ERR_STATE; }
 	// scratch: one 64-bit word per tile, then the ticket
@@ -396,9 +395,7 @@ int fs3i_scan_u32(fs3_sim* s, const uint32_t* in, uint32_t* out, size_t n, uint3
 	uint32_t* ticket = reinterpret_cast<uint32_t*>(state + s->scan_block_cap);
 	FS3_CUDA(cudaMemsetAsync(s->scan_block, 0, ((size_t)nb + 0) * 8, s->stream));
 	FS3_CUDA(cudaMemsetAsync(ticket, 0, 4, s->stream));
-	if (items == 8) k_scan_lookback<8><<<nb, SCAN_T, 0, s->stream>>>(in, out, n, state, ticket, base0);
-	else if (items == 32) k_scan_lookback<32><<<nb, SCAN_T, 0, s->stream>>>(in, out, n, state, ticket, base0);
-	else k_scan_lookback<16><<<nb, SCAN_T, 0, s->stream>>>(in, out, n, state, ticket, base0);
+	k_scan_lookback<32><<<nb, SCAN_T, 0, s->stream>>>(in, out, n, state, ticket, base0);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
@@ -455,6 +452,10 @@ int fs3i_bin(fs3_sim* s) {
 	} else {
 		int rc = fs3i_scan_u32(s, s->cell_count + K0, s->cell_start + K0, K1 - K0 + 1, (uint32_t)s->poff);
 		if (rc) return rc;
+		// A sharded rank whose slab is empty flips its buffer like every other rank: the neighbours address this rank's live
+		// buffer with THEIR OWN `cur` (immigrants in fs3i_mig_exchange, ghost layers in fs3i_ghost_pull), so `cur` must stay
+		// identical on all ranks whatever each slab holds.
+		if (s->world > 1) s->cur ^= 1;
 	}
 	s->np_in = s->np;
 	s->sorted = true;
@@ -551,9 +552,10 @@ int fs3i_pack_local(fs3_sim* s, fs3_particle* dev_out, int* dev_ids) {
 	return FS3_OK;
 }
 int fs3i_load_local(fs3_sim* s, const fs3_particle* dev_in, const int* dev_ids, long long count) {
-	s->np = s->np_in = count; s->np_all[s->rank] = count; s->cur = 0; s->sorted = false; s->counted = false; s->closest_valid = false;
+	// per-rank call (not collective): the live buffer index `cur` is shared state of the whole group and is left alone
+	s->np = s->np_in = count; s->np_all[s->rank] = count; s->sorted = false; s->counted = false; s->closest_valid = false;
 	if (count <= 0) return FS3_OK;
-	k_load_local<<<cdiv(count, 256), 256, 0, s->stream>>>(dev_in, dev_ids, count, s->pos[0] + s->poff, s->vel[0] + s->poff); FS3_LAUNCH_CHECK();
+	k_load_local<<<cdiv(count, 256), 256, 0, s->stream>>>(dev_in, dev_ids, count, s->pos[s->cur] + s->poff, s->vel[s->cur] + s->poff); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
 int fs3i_cell_indices(fs3_sim* s, int* dev_out) {

@@ -148,13 +148,10 @@ __device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, 
 	const M mm = __ldcs(reinterpret_cast<const M*>(sp.mask + base));
 	REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
 	ldv(sp.own + base, own);
-#ifndef FS3_SOR_EXP
-#define FS3_SOR_EXP 0   // timing experiments only (wrong results): 1 = no z-neighbour loads, 2 = no b load, 3 = no y-neighbour loads
-#endif
 	ldv(o + base, xc);
-	if (FS3_SOR_EXP == 2) ldv(o + base, bb); else ldv_stream(sp.b + base, bb);
-	if (FS3_SOR_EXP == 3) { ldv(o + base, ym); ldv(o + base, yp); } else { ldv(o + base - sp.hp, ym); ldv(o + base + sp.hp, yp); }
-	if (FS3_SOR_EXP == 1) { ldv(o + base, zm); ldv(o + base, zp); } else { ldv(o + base - sp.plane, zm); ldv(o + base + sp.plane, zp); }
+	ldv_stream(sp.b + base, bb);
+	ldv(o + base - sp.hp, ym); ldv(o + base + sp.hp, yp);
+	ldv(o + base - sp.plane, zm); ldv(o + base + sp.plane, zp);
 	const REAL edge = s == 0 ? o[base - 1] : o[base + VEC];
 #pragma unroll
 	for (int e = 0; e < VEC; e++) dd[e] = (REAL)1;
@@ -457,17 +454,14 @@ int fs3i_sor_prepare(fs3_sim* s) { return s->alloc_precision ? sor_prepare_t<flo
 // sweep is launched with an access-policy window over the colour it writes.  The fraction of the window that persists
 // is carve-out / bytes of p the active vectors touch, so that the persisting lines never thrash among themselves; below
 // 0.5 (large grids) or for grids that fit in L2 anyway the feature stays off and the solve runs without the two syncs.
-// FS3_SOR_L2_PERSIST_MB caps the carve-out (0 = never).
 static size_t sor_persist_cap(fs3_sim* s) {
-	static long long bytes = -1;
-	if (bytes < 0) {
-		const char* e = getenv("FS3_SOR_L2_PERSIST_MB");
-		cudaDeviceProp pr; cudaGetDeviceProperties(&pr, s->device);
-		bytes = (long long)pr.persistingL2CacheMaxSize;
-		if (e) bytes = std::min<long long>(bytes, atoll(e) << 20);
-		if ((size_t)pr.accessPolicyMaxWindowSize < ((size_t)64 << 20)) bytes = 0;
+	if (s->persist_cap < 0) {   // per handle (= per device): the largest carve-out the device offers
+		cudaDeviceProp pr;
+		s->persist_cap = 0;
+		if (cudaGetDeviceProperties(&pr, s->device) == cudaSuccess && (size_t)pr.accessPolicyMaxWindowSize >= ((size_t)64 << 20))
+			s->persist_cap = (long long)pr.persistingL2CacheMaxSize;
 	}
-	return (size_t)bytes;
+	return (size_t)s->persist_cap;
 }
 // half sweep k (colour k & 1) of the current projection
 template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
@@ -477,14 +471,13 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	REAL omo = (REAL)1 - omega;
 	// persistent grid-stride launch: enough blocks to fill the machine; the list length is read on the device
 	size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * (s->z1 - s->z0);
-	static int per_sm = 0;   // resident blocks per SM of the sweep kernel: the grid is exactly one wave
-	if (!per_sm) {
+	if (!s->sor_per_sm) {    // resident blocks per SM of the sweep kernel: the grid is exactly one wave
 		int a = 0, b = 0;
 		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_sor_half<REAL, VEC, false>, FS3_SOR_THREADS, 0);
 		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_sor_half<REAL, VEC, true>, FS3_SOR_THREADS, 0);
-		per_sm = std::max(1, std::min(a, b));
-		if (const char* e = getenv("FS3_SOR_BLOCKS_PER_SM")) per_sm = std::max(1, atoi(e));
+		s->sor_per_sm = std::max(1, std::min(a, b));
 	}
+	const int per_sm = s->sor_per_sm;
 	int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, FS3_SOR_THREADS)), (long long)s->sm_count * per_sm);
 	const int c = k & 1;
 	if (s->world == 1) {
@@ -531,14 +524,11 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	sh.n_lo = s->sor_pos[c] + s->rb.plane * (size_t)(s->z0 + 2) / VEC;
 	sh.n_hi = s->sor_pos[c] + s->rb.plane * (size_t)s->z1 / VEC;
 	{
-		static int pdl = -1;   // debug switch: chain the sharded half sweeps with programmatic dependent launch too
-		if (pdl < 0) { const char* e = getenv("FS3_SOR_SHARD_PDL"); pdl = e ? atoi(e) : 0; }
+		// (programmatic dependent launch stays off here: measured 12.7 -> 14.9 us per half sweep on 8 GPUs, the boundary
+		// blocks' flag wait then holds SM slots the previous sweep's interior blocks need)
 		cudaLaunchConfig_t cfg = {};
 		cfg.gridDim = dim3(nb); cfg.blockDim = dim3(FS3_SOR_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = s->stream;
-		cudaLaunchAttribute at[1];
-		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-		at[0].val.programmaticStreamSerializationAllowed = 1;
-		cfg.attrs = at; cfg.numAttrs = (pdl && k > 0) ? 1 : 0;
+		cfg.attrs = nullptr; cfg.numAttrs = 0;
 		const uint32_t* lst = s->sor_list[c]; const uint32_t* cnt = s->sor_count[c];
 		FS3_CUDA(cudaLaunchKernelEx(&cfg, k_sor_half<REAL, VEC, true>, sy, c, omega, omo, lst, cnt, sh));
 		FS3_LAUNCH_CHECK();
@@ -548,9 +538,30 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 }
 int fs3i_sor_half_launch(fs3_sim* s, int k) { return s->alloc_precision ? sor_half_t<float, 4>(s, k) : sor_half_t<double, 2>(s, k); }
 
+// The persisting-L2 size is a DEVICE-wide limit: whatever the host application (or another handle) had configured is put
+// back when the solve ends, on every path out of fs3i_sor_loop.
+struct PersistLimitGuard {
+	size_t prev = 0;
+	bool raised = false;
+	bool raise(size_t bytes) {
+		if (cudaDeviceGetLimit(&prev, cudaLimitPersistingL2CacheSize) != cudaSuccess) return false;
+		if (prev >= bytes) return true;   // the application already keeps a carve-out at least this large: use it, leave it
+		if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, bytes) != cudaSuccess) { cudaGetLastError(); return false; }
+		raised = true;
+		return true;
+	}
+	void restore(cudaStream_t st) {
+		if (!raised) return;
+		cudaStreamSynchronize(st);
+		cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, prev);
+		raised = false;
+	}
+};
+
 int fs3i_sor_loop(fs3_sim* s, int iters) {
 	int rc = fs3i_sor_prepare(s);
 	if (rc) return rc;
+	PersistLimitGuard guard;
 	bool rec = s->prm.record_residuals != 0;
 	if (rec) {
 		if (s->world > 1) { s->err = "residual recording is not available on a sharded handle"; return FS3_ERR_STATE; }
@@ -567,24 +578,20 @@ int fs3i_sor_loop(fs3_sim* s, int iters) {
 		FS3_CUDA(cudaStreamSynchronize(s->stream));
 		const double touched = ((double)cnt[0] + cnt[1]) * 16.0;   // one 128-bit vector per list entry
 		const double ratio = touched > 0 ? std::min(1.0, 0.95 * (double)cap / touched) : 0.0;
-		if (ratio >= 0.5 && touched > (double)((size_t)32 << 20)) {
-			FS3_CUDA(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, cap));
-			s->sor_persist_ratio = (float)ratio;
-		}
+		if (ratio >= 0.5 && touched > (double)((size_t)32 << 20) && guard.raise(cap)) s->sor_persist_ratio = (float)ratio;
 	}
-	for (int it = 0; it < iters; it++) {
-		if ((rc = fs3i_sor_half_launch(s, 2 * it)) || (rc = fs3i_sor_half_launch(s, 2 * it + 1))) return rc;
+	for (int it = 0; it < iters && !rc; it++) {
+		if ((rc = fs3i_sor_half_launch(s, 2 * it)) || (rc = fs3i_sor_half_launch(s, 2 * it + 1))) break;
 		if (rec) {
 			if (s->alloc_precision) k_sor_residual<float><<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(make_sys<float>(s), s->res + 2 * it);
 			else k_sor_residual<double><<<cdiv((long long)s->nC, 256), 256, 0, s->stream>>>(make_sys<double>(s), s->res + 2 * it);
-			FS3_LAUNCH_CHECK();
+			s->launches++;
+			if (cudaGetLastError() != cudaSuccess) { s->err = "residual kernel launch failed"; rc = FS3_ERR_CUDA; }
 		}
 	}
-	if (s->sor_persist_ratio > 0) {
-		FS3_CUDA(cudaStreamSynchronize(s->stream));
-		FS3_CUDA(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0));
-		s->sor_persist_ratio = 0;
-	}
+	guard.restore(s->stream);   // also on the error paths above
+	s->sor_persist_ratio = 0;
+	if (rc) return rc;
 	s->res_count = rec ? iters : 0;
 	return FS3_OK;
 }

@@ -30,7 +30,7 @@ ABI_SYMBOLS = [
     "fs3_phi_device", "fs3_blur_phi", "fs3_phi_blurred_device", "fs3_get_phi_blurred", "fs3_export_binned", "fs3_get_binned",
     "fs3_sample_phi", "fs3_sample_phi_device",
     "fs3_save_state", "fs3_load_state", "fs3_step_count", "fs3_state_file_info", "fs3_state_file_write", "fs3_state_file_read",
-    "fs3_state_checksum", "fs3_default_params",
+    "fs3_state_checksum", "fs3_default_params", "fs3_get_divergence", "fs3_checksum",
 ]
 SHARD_HANDLE_BYTES = 128
 
@@ -48,6 +48,12 @@ class Fs3StateInfo(C.Structure):
                 ("num_particles", C.c_longlong), ("total_particles", C.c_longlong), ("steps", C.c_longlong),
                 ("rank", C.c_int), ("world", C.c_int), ("has_ids", C.c_int), ("params", Fs3Params),
                 ("rank_particles", C.c_longlong * 16), ("payload_bytes", C.c_ulonglong), ("checksum", C.c_ulonglong)]
+
+
+class Fs3Check(C.Structure):
+    """include/fs3.h fs3_check: order-independent fingerprints of the state (sums modulo 2^64)."""
+    _fields_ = [("particle_hash", C.c_ulonglong), ("cell_hash", C.c_ulonglong), ("particles", C.c_longlong),
+                ("grid_hash", C.c_ulonglong * 4), ("grid_sum", C.c_double * 4)]
 
 
 class Fs3Error(RuntimeError):
@@ -87,6 +93,8 @@ def load_library():
         _lib.fs3_state_file_info.argtypes = [C.c_char_p, C.POINTER(Fs3StateInfo)]
         _lib.fs3_state_file_write.argtypes = [C.c_char_p, C.POINTER(Fs3StateInfo)] + [C.c_void_p] * 6
         _lib.fs3_state_file_read.argtypes = [C.c_char_p, C.POINTER(Fs3StateInfo)] + [C.c_void_p] * 6
+        _lib.fs3_get_divergence.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        _lib.fs3_checksum.argtypes = [C.c_void_p, C.POINTER(Fs3Check)]
         _lib.fs3_sample_phi.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]
         _lib.fs3_sample_phi_device.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]
     return _lib
@@ -379,6 +387,19 @@ class FluidSim3:
         ms = np.zeros(len(STAGE_NAMES), np.float32)
         self._ck(self._lib.fs3_stage_times(self._h, _ptr(ms), len(STAGE_NAMES)))
         return dict(zip(STAGE_NAMES, ms.tolist()))
+
+    def divergence(self):
+        """(max, l2) of the divergence over phi < 0 cells (PrintDivergence, Simulation3D.cpp:1095-1138); sharded: this rank's planes."""
+        a, b = C.c_double(0), C.c_double(0)
+        self._ck(self._lib.fs3_get_divergence(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def checksum(self):
+        """dict of the fs3_check fingerprints (sharded: this rank's share; shares add up modulo 2^64)."""
+        c = Fs3Check()
+        self._ck(self._lib.fs3_checksum(self._h, C.byref(c)))
+        return {"particle_hash": int(c.particle_hash), "cell_hash": int(c.cell_hash), "particles": int(c.particles),
+                "grid_hash": [int(x) for x in c.grid_hash], "grid_sum": [float(x) for x in c.grid_sum]}
 
     def sor_bench(self, iters):
         ms = C.c_float(0)

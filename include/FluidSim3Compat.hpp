@@ -45,6 +45,7 @@ public:
 
 	void ResetSimulation() {
 		Check(fs3_reset(m_h), "fs3_reset");
+		m_dirty = false;   // host edits made before the reset are gone, like the vector the reference rebuilds (Simulation3D.cpp:73-98)
 		if (m_readback) FetchParticles();
 	}
 	// The reference clamps dt to [0, 1/15] and then overrides it with 0.01 (Simulation3D.cpp:103-104);
@@ -52,7 +53,9 @@ public:
 	void Simulate(float dt) {
 		if (m_dirty) PushParticles();
 		Check(fs3_step(m_h, dt), "fs3_step");
-		if (m_readback) FetchParticles();
+		// fs3_sync also reports deferred device errors (a particle outside the box, a dependency wait that timed out, a slab
+		// over capacity) that the asynchronous step could not return
+		if (m_readback) { Check(fs3_sync(m_h), "fs3_sync"); FetchParticles(); }
 	}
 
 	// ---- beyond the reference surface -------------------------------------------------------------

@@ -145,6 +145,24 @@ int fs3_get_pressure(fs3_sim* s, double* p);       /* p[] of the last Project, n
 int fs3_get_rhs_diag(fs3_sim* s, double* b, double* diag);
 int fs3_get_sor_residuals(fs3_sim* s, double* l2, double* linf, int cap, int* count);
 int fs3_stage_times(fs3_sim* s, float* ms, int cap); /* FS3_T_* order, last step, milliseconds */
+/* FluidSim3::PrintDivergence (Simulation3D.cpp:1095-1138) as a validation metric: over the cells with phi < 0, the largest
+ * (signed) value of (V(y+1)-V(y)) + (U(x+1)-U(x)) + (W(z+1)-W(z)) evaluated in fp32 in that order, and the square root of
+ * the sum of its squares accumulated in double.  Sharded handle: the rank's own cell planes only (combine: max of the
+ * maxima, square root of the sum of the squared l2 values). */
+int fs3_get_divergence(fs3_sim* s, double* max_divergence, double* l2);
+/* Order-independent 64-bit fingerprints of the state, computed on the device (measurement hook: bench.py prints them as
+ * `check`, and a sharded run must reproduce the single-GPU values exactly).  Every value is a sum modulo 2^64 of a mixed
+ * per-element word, so the ranks' values of a sharded simulation ADD UP to the single-GPU value:
+ *   particle_hash: over the rank's particles, mix(creation id, cell index (int)roundf(n*X) (Simulation3D.cpp:286-288),
+ *                  bit patterns of X,Y,Z,uX,uY,uZ);  cell_hash: mix(creation id, cell index) only
+ *   grid_hash[0..3]: U, V, W, phi over the rank's own planes, mix(element index, bit pattern);  grid_sum: plain sums in double */
+typedef struct fs3_check {
+	unsigned long long particle_hash, cell_hash;
+	long long particles;
+	unsigned long long grid_hash[4];
+	double grid_sum[4];
+} fs3_check;
+int fs3_checksum(fs3_sim* s, fs3_check* out);
 
 /* ---- measurement: projection microbench (BASELINE config 3) ------------------------------- */
 /* Runs `iters` red-black SOR iterations on the current b/diag/mask (from the last project setup)

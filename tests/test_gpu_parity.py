@@ -52,12 +52,8 @@ def test_reset_bitexact(n):
     assert same(sim.get_particles(), ora.get_particles())
 
 
-@pytest.mark.parametrize("n,warm", [(16, 0), (24, 2), (32, 5)])
-def test_stages_from_identical_state(n, warm):
-    sim, ora = mk(n), Oracle(n)
-    for _ in range(warm):
-        ora.step()
-    sync_state(sim, ora)
+def stage_ladder(sim, ora):
+    """One Simulate() taken apart: every stage starts from identical inputs on both sides (Simulation3D.cpp:101-188)."""
     # Advect
     sim.advect(); ora.advect()
     assert same(sim.get_particles(), ora.get_particles()), "advect not bit-exact"
@@ -81,15 +77,55 @@ def test_stages_from_identical_state(n, warm):
     assert same(sim.get_velocity()[1], ora.get_velocity()[1])
     sim.project(); ora.project()
     pg, po = sim.get_pressure(), ora.get_pressure()
-    assert np.abs(pg - po).max() <= 1e-12 * max(1.0, np.abs(po).max()), "pressure: %g" % np.abs(pg - po).max()
+    assert np.array_equal(pg, po), "pressure: %g" % np.abs(pg - po).max()
+    del pg, po
     b_g, d_g = sim.get_rhs_diag(); b_o, d_o = ora.get_rhs_diag()
     assert np.array_equal(b_g, b_o) and np.array_equal(d_g, d_o)
+    del b_g, d_g, b_o, d_o
     for name, a, b in zip("UVW", sim.get_velocity(), ora.get_velocity()):
-        assert close(a, b, 1e-7), "projected %s: %g" % (name, np.abs(a - b).max())
+        assert same(a, b), "projected %s: %g" % (name, np.abs(a - b).max())
+    # PrintDivergence of the projected field (Simulation3D.cpp:1095-1138): identical grids, so the same maximum; the l2 sum is
+    # accumulated in another order
+    dg, do = sim.divergence(), ora.divergence()
+    assert dg[0] == do[0] and abs(dg[1] - do[1]) <= 1e-12 * max(1.0, do[1]), (dg, do)
     # G2P from identical inputs
-    sim.set_velocity(*ora.get_velocity())
     sim.g2p(*old); ora.g2p(*old)
     assert same(sim.get_particles(), ora.get_particles()), "G2P not bit-exact"
+
+
+@pytest.mark.parametrize("n,warm", [(16, 0), (24, 2), (32, 5)])
+def test_stages_from_identical_state(n, warm):
+    sim, ora = mk(n), Oracle(n)
+    for _ in range(warm):
+        ora.step()
+    sync_state(sim, ora)
+    stage_ladder(sim, ora)
+
+
+@pytest.mark.parametrize("n", [128, 256])   # 256^3 = the bench configuration (BASELINE.json configs[3]); ~10 s / ~80 s of oracle time
+def test_bench_sizes_against_oracle(n):
+    """The sizes bench.py times, against the oracle: reset, one free-running Simulate, then one Simulate taken apart stage by
+    stage from the oracle's state.  Code paths that only exist at these sizes (the persisting-L2 window of the SOR, the
+    look-back scan over thousands of chained tiles, level-set tile tables of 10^4..10^5 items, extrapolation layers that
+    spill L2) are on this path."""
+    sim, ora = mk(n), Oracle(n)
+    assert sim.num_particles == ora.num_particles == 8 * (n - 2) ** 2 * (n - 1 - n // 2)
+    assert same(sim.get_particles(), ora.get_particles()), "reset differs"
+    for a, b in zip(sim.get_velocity(), ora.get_velocity()):
+        assert same(a, b)
+    sim.Simulate(0.01); ora.step(0.01)
+    sim.sync()
+    assert np.array_equal(sim.get_cell_indices(), ora.get_cell_indices()), "particle->cell indices differ after one step"
+    assert np.array_equal(sim.get_cell_counts(), ora.get_cell_counts())
+    assert same(sim.get_phi(), ora.get_phi()), "phi not bit-exact after one step"
+    assert np.array_equal(sim.get_closest(), ora.get_closest())
+    assert close(sim.get_particles(), ora.get_particles())
+    for name, a, b in zip("UVW", sim.get_velocity(), ora.get_velocity()):
+        assert close(a, b), "%s after one step: %g" % (name, np.abs(a - b).max())
+    dg, do = sim.divergence(), ora.divergence()
+    assert abs(dg[1] - do[1]) <= 1e-3 * max(1.0, do[1]), (dg, do)
+    sync_state(sim, ora)
+    stage_ladder(sim, ora)
 
 
 def test_pressure_bitexact_fp64():
@@ -116,8 +152,6 @@ def test_projection_fp32_fast_mode():
     sim.bodyforces(); ora.bodyforces(); sim.project(); ora.project()
     for a, b in zip(sim.get_velocity(), ora.get_velocity()):
         assert close(a, b), np.abs(a - b).max()     # fp32 solve vs the fp64 oracle: inside 1e-5 (Simulation.cpp:899-900)
-    ora2 = Oracle(n)
-    ora2.set_particles(ora.get_particles())
 
 
 def test_residual_history_matches():
@@ -153,8 +187,25 @@ def test_free_running_steps(n, steps, tol):
     for _ in range(steps):
         sim.Simulate(0.01); ora.step(0.01)
     sim.sync()
-    assert np.array_equal(sim.get_cell_indices(), ora.get_cell_indices()) or steps > 2
-    assert close(sim.get_particles(), ora.get_particles(), tol)
+    p, q = sim.get_particles(), ora.get_particles()
+    ci, co = sim.get_cell_indices(), ora.get_cell_indices()
+    bad = np.nonzero(ci != co)[0]
+    # Bit-exact indices (BASELINE.json north_star).  Free-running positions differ by a few ulp after the first P2G (its sums
+    # run in another order), so from the second Advect on a particle that sits on a cell boundary to within that difference
+    # may round to the other side: every mismatch must be such a particle (n*X within 1e-3 cells of a half-integer on the
+    # axis where the cells differ), and there are none at all within the first two steps.
+    if steps <= 2:
+        assert bad.size == 0
+    else:
+        assert bad.size <= max(1, p.shape[0] // 20000)
+        for i in bad:
+            d = np.abs(np.array(np.unravel_index(ci[i], (n, n, n))) - np.array(np.unravel_index(co[i], (n, n, n))))[::-1]
+            assert d.max() == 1
+            for ax in range(3):
+                if d[ax]:
+                    f = float(q[i, ax]) * n
+                    assert abs(f - np.floor(f) - 0.5) < 1e-3, (i, ax, f)
+    assert close(p, q, tol)
     for a, b in zip(sim.get_velocity(), ora.get_velocity()):
         assert close(a, b, tol)
     assert close(sim.get_phi(), ora.get_phi(), tol)

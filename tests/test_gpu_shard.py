@@ -122,6 +122,58 @@ def test_group_migration_moves_particles_between_slabs():
     g.close()
 
 
+def test_group_empty_slab_receives_immigrants():
+    """A slab that holds no particle at first and is filled by migration later: every rank must keep the same live-buffer
+    parity whatever its slab holds (the neighbours address its buffers with their own), else the immigrants land in the
+    buffer the rank does not read."""
+    n, world = 16, 4
+    g, one = mkg(n, world), mk(n)
+    rng = np.random.default_rng(11)
+    P = 3000
+    pos = rng.uniform(0.15, 0.85, (P, 3)).astype(np.float32)
+    pos[:, 2] = rng.uniform(0.30, 0.47, P).astype(np.float32)      # cells z = 5..7: all in slab 1 (planes 4..7); slabs 0, 2, 3 are empty
+    part = np.ascontiguousarray(np.concatenate([pos, np.zeros((P, 3), np.float32)], axis=1))
+    u, v, w = one.get_velocity()
+    u, v, w = np.zeros_like(u), np.zeros_like(v), np.full_like(w, 6.0)   # 6 m/s * 0.01 s * 16 cells/m: about one cell per step, upwards
+    for s in (g, one):
+        s.set_particles(part)
+        s.set_velocity(u, v, w)
+        s.set_params(gravity_y=0.0)
+    assert [r.num_local_particles for r in g.ranks] == [0, P, 0, 0]
+    seen = set()
+    for k in range(6):
+        g.Simulate(0.01); one.Simulate(0.01)
+        g.sync(); one.sync()
+        assert same(g.get_particles(), one.get_particles()), "particles differ after step %d" % (k + 1)
+        assert np.array_equal(g.get_cell_indices(), one.get_cell_indices())
+        seen.add(tuple(r.num_local_particles for r in g.ranks))
+        for s in (g, one):
+            s.set_velocity(u, v, w)          # keep the upward flow going (the projection takes most of it out)
+    assert any(c[2] > 0 for c in seen), "the test is meant to move particles into an empty slab: %r" % (seen,)
+    g.close()
+
+
+def test_group_checksum_adds_up_to_single_gpu():
+    """fs3_checksum: the ranks' fingerprints add up (mod 2^64) to the single-GPU values -- what bench.py --gpus N verifies."""
+    n, world = 24, 3
+    g, one = mkg(n, world), mk(n)
+    for _ in range(2):
+        g.Simulate(0.01); one.Simulate(0.01)
+    g.sync(); one.sync()
+    c1 = one.checksum()
+    cs = [r.checksum() for r in g.ranks]
+    M = 1 << 64
+    assert sum(c["particles"] for c in cs) == c1["particles"] == one.num_particles
+    assert sum(c["particle_hash"] for c in cs) % M == c1["particle_hash"]
+    assert sum(c["cell_hash"] for c in cs) % M == c1["cell_hash"]
+    for k in range(4):
+        assert sum(c["grid_hash"][k] for c in cs) % M == c1["grid_hash"][k], k
+        assert abs(sum(c["grid_sum"][k] for c in cs) - c1["grid_sum"][k]) <= 1e-9 * max(1.0, abs(c1["grid_sum"][k]))
+    one.Simulate(0.01); one.sync()
+    assert one.checksum()["particle_hash"] != c1["particle_hash"]
+    g.close()
+
+
 def test_group_reset_after_steps_and_hooks_refused():
     from fluidsimulation_b200 import Fs3Error
     n = 16

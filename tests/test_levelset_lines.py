@@ -118,7 +118,6 @@ def test_gpu_line_sweep_level_set_bitexact():
 
 
 @pytest.mark.gpu
-@pytest.mark.xfail(strict=False, reason="extrapolation_mode = 1 was written after the round's GPU budget was spent: this test is its first run on a GPU")
 def test_gpu_one_layer_extrapolation_bitexact():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "gex_worker.py")], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "GEX_WORKER_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-3000:]
