@@ -96,27 +96,82 @@ def cpu_reference_run(n, steps, warmup):
     return P * steps / dt, dt, kind, P
 
 
-def pick_cpu_grid(total_steps, budget_s):
-    for n in (128, 96, 64, 48, 32):
-        if n_particles(n) / 1.0e6 * total_steps <= budget_s:
-            return n
-    return 32
+CPU_STEP_RATE = 1.8e6    # particle-steps/s of the reference on one host core, conservative (measured 2.2e6 - 2.6e6 on the GPU boxes)
+
+
+def workload_name(n, P, total=False, extra=""):
+    return "FluidSim3 dam-break full step, %d^3 grid, %d particles%s, 100 SOR iterations, dt=0.01%s" % (n, P, " in total" if total else "", extra)
 
 
 def run_reference(args, rank, world):
+    """The reference's own CPU FluidSim3 on the bench grid itself.  One 256^3 step takes ~30 s on one host core (the reference
+    has no threads), so the run is a BOUNDED sample of the workload: as many of the K steps as fit ~2 minutes, at least one,
+    from the same ResetSimulation state, no warm-up steps (nothing to warm on the CPU)."""
     if rank != 0:
         return
-    n = pick_cpu_grid(args.steps + args.warmup, 150.0)
-    value, dt, kind, P = cpu_reference_run(n, args.steps, args.warmup)
-    sample = "%d^3 dam break (%d particles), %d Simulate(0.01) steps, 1 thread" % (n, P, args.steps)
+    n = args.grid
+    est = n_particles(n) / CPU_STEP_RATE
+    steps_run = int(max(1, min(args.steps, 130.0 // est)))
+    value, dt, kind, P = cpu_reference_run(n, steps_run, 0)
+    sample = "%d^3 dam break (%d particles), %d of the %d Simulate(0.01) steps timed (%.1f s), no warm-up, 1 thread (the reference has no threads)" % (
+        n, P, steps_run, args.steps, dt)
     line = {"impl": "reference", "metric": "particle-steps/s", "value": value, "unit": "particle-steps/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32 particles/grids, f64 pressure solve", "data": "synthetic",
-            "config": {"workload": "FluidSim3 dam-break step at %d^3 (target config: 256^3, 65.5M particles); CPU sample at %d^3, "
-                                   "throughput is linear in particle count (BASELINE.md section 2)" % (args.grid, n)},
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / steps_run, "higher_is_better": True,
+            "scaling": "strong" if args.gpus > 1 else "none (1 GPU)", "vs_baseline": None, "dtype": "f32 particles/grids, f64 pressure solve", "data": "synthetic",
+            "config": {"workload": workload_name(n, P, args.gpus > 1), "parallelism": "reference CPU code, 1 host thread", "steps_timed": steps_run},
             "cpu_baseline": {"value": value, "unit": "particle-steps/s", "cores": 1, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "particle-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+CHECK_STEPS = 2
+M64 = 1 << 64
+
+
+def state_check(sim, world, dist, torch):
+    """fs3_checksum of this rank's share, summed over the ranks modulo 2^64 (int64 tensors wrap) -> the whole simulation's fingerprint."""
+    c = sim.checksum()
+    ints = [c["particle_hash"], c["cell_hash"], c["particles"]] + c["grid_hash"]
+    sums = list(c["grid_sum"])
+    if world > 1:
+        t = torch.tensor([v - M64 if v >= (1 << 63) else v for v in ints], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        ints = [int(v) % M64 for v in t.tolist()]
+        f = torch.tensor(sums, device="cuda", dtype=torch.float64)
+        dist.all_reduce(f, op=dist.ReduceOp.SUM)
+        sums = f.tolist()
+    return {"particle_hash": "%016x" % ints[0], "cell_hash": "%016x" % ints[1], "particles": ints[2],
+            "grid_hash": ["%016x" % v for v in ints[3:7]], "sumU": sums[0], "sumV": sums[1], "sumW": sums[2], "sumPhi": sums[3]}
+
+
+def verify_sharded(sim, n, world, rank, local_rank, dist, torch, FluidSim3):
+    """bench.py --gpus N verifies what it times: CHECK_STEPS steps of the sharded simulation from ResetSimulation, fingerprinted
+    on the device, must equal the same steps of a single-GPU simulation (run by rank 0 on its own GPU beside its slab): the
+    sharded step is bit-identical to the single-GPU step by design, so equality of the 64-bit fingerprints is the bar.
+    Afterwards the sharded simulation is reset, so the timed steps start from the same state as at N = 1."""
+    for _ in range(CHECK_STEPS):
+        sim.Simulate(0.01)
+    sim.sync()
+    got = state_check(sim, world, dist, torch)
+    verdict = [None]
+    if rank == 0:
+        if n > 384:
+            verdict = [{"status": "skipped", "why": "a %d^3 single-GPU twin does not fit beside rank 0's slab" % n, "steps": CHECK_STEPS, "sharded": got}]
+        else:
+            one = FluidSim3(n, n, n, float(n), device=local_rank)
+            for _ in range(CHECK_STEPS):
+                one.Simulate(0.01)
+            one.sync()
+            ref = state_check(one, 1, dist, torch)
+            one.close()
+            keys = ("particle_hash", "cell_hash", "particles", "grid_hash")
+            ok = all(got[k] == ref[k] for k in keys)
+            verdict = [{"status": "pass" if ok else "FAIL", "against": "single-GPU run of the same %d steps in the same process (rank 0)" % CHECK_STEPS,
+                        "steps": CHECK_STEPS, "sharded": got, "single_gpu": ref}]
+    dist.broadcast_object_list(verdict, src=0)
+    sim.ResetSimulation()
+    sim.sync()
+    return verdict[0]
 
 
 def run_gpu(args, rank, world, local_rank):
@@ -144,6 +199,15 @@ def run_gpu(args, rank, world, local_rank):
         sim.set_params(levelset_mode=1, extrapolation_mode=1)
     P = sim.num_particles
     stream = torch.cuda.ExternalStream(sim.stream, device=local_rank)
+    check = None
+    if sharded and not args.gpu_formulation:
+        check = verify_sharded(sim, n, world, rank, local_rank, dist, torch, FluidSim3)
+        if check["status"] == "FAIL":
+            if rank == 0:
+                print(json.dumps({"error": "sharded result differs from the single-GPU result", "check": check}), flush=True)
+            sim.close()
+            dist.destroy_process_group()
+            raise SystemExit(3)
 
     def barrier():
         torch.cuda.synchronize()
@@ -178,6 +242,7 @@ def run_gpu(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         launches = int(t.item())
     ms = e0.elapsed_time(e1)
+    final_state = state_check(sim, world if sharded else 1, dist, torch)     # outside the timed region
     if world > 1:
         t = torch.tensor([ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -256,7 +321,13 @@ def run_gpu(args, rank, world, local_rank):
             traffic, traffic_src = float(t["dram_bytes_per_launch"]), t["source"]
         except Exception:
             traffic, traffic_src = None, None
-    roofline = {"bound": "hbm", "kernel": "k_sor_half<%s>" % ("float,4" if args.precision == "fp32" else "double,2"),
+    sys_mb = 2 * (n // 2 + 3) // 4 * 4 * n * (n + 2) * (4 if args.precision == "fp32" else 8) / 2 ** 20     # both colours of p
+    l2_assisted = world == 1 and 48 < sys_mb <= 256
+    roofline = {"bound": "hbm", "l2_assisted": l2_assisted,
+                "note": ("`achieved` counts ALGORITHMIC bytes (SURVEY.md 8(d): p 24 + b 8 + diag 8 + phi/mask 8 per fluid-cell update); at this size the two "
+                         "colours of p are held in the persisting L2 carve-out across the 200 launches, so DRAM sees less than that and frac can exceed 1; "
+                         "`traffic` is the DRAM side") if l2_assisted else "`achieved` counts algorithmic bytes per fluid-cell update (SURVEY.md 8(d))",
+                "kernel": "k_sor_half<%s>" % ("float,4" if args.precision == "fp32" else "double,2"),
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_per_launch, "avg_launch_us": avg_launch_ms * 1e3,
                 "launches_timed": n_launch, "fluid_cells": fluid_cells, "grid_cells": n ** 3 // (world if sharded else 1),
@@ -267,21 +338,25 @@ def run_gpu(args, rank, world, local_rank):
     if rank == 0:
         cpu = None
         if not args.no_cpu_baseline:
-            cn = 128 if n >= 128 else n
-            cv, cdt, kind, cP = cpu_reference_run(cn, 2, 0)
+            # ONE step of the bench workload itself where that is <= ~40 s of CPU (256^3: ~30 s), else the largest grid that is
+            cn = n if n_particles(n) / CPU_STEP_RATE <= 40.0 else 256
+            cv, cdt, kind, cP = cpu_reference_run(cn, 1, 0)
             cpu = {"value": cv, "unit": "particle-steps/s", "cores": 1, "kind": kind,
-                   "sample": "%d^3 dam break (%d particles), 2 Simulate(0.01) steps, %.1f s, single thread (the reference has no threads)" % (cn, cP, cdt)}
+                   "sample": "%d^3 dam break (%d particles), 1 Simulate(0.01) step from ResetSimulation, %.1f s, single thread (the reference has no threads)" % (cn, cP, cdt)}
+        if check is None:
+            check = {"status": "recorded", "against": "nothing to compare at 1 GPU: these are the single-GPU fingerprints a sharded run must reproduce",
+                     "steps": args.warmup + args.steps}
         line = {"metric": "particle-steps/s", "value": value, "unit": "particle-steps/s", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if sharded else "weak", "vs_baseline": None,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "strong" if sharded else ("weak" if world > 1 else "none (1 GPU; N > 1 shards this same simulation: strong)"), "vs_baseline": None,
                 "dtype": "f32 particles/grids, %s pressure solve" % ("f32" if args.precision == "fp32" else "f64"), "data": "synthetic",
-                "config": {"workload": "FluidSim3 dam-break full step, %d^3 grid, %d particles%s, 100 SOR iterations, dt=0.01%s" % (
-                               n, P, " in total" if sharded else "/GPU",
-                               "; NON-DEFAULT level set + extrapolation in the reference's GPU formulation (levelset_mode=1, extrapolation_mode=1): not the headline configuration" if args.gpu_formulation else ""),
+                "config": {"workload": workload_name(n, P, sharded, "; NON-DEFAULT level set + extrapolation in the reference's GPU formulation (levelset_mode=1, extrapolation_mode=1): not the headline configuration" if args.gpu_formulation else ""),
                            "parallelism": "1 GPU" if world == 1 else ("%d z-slabs, one rank per GPU, CUDA-IPC peer stores over NVLink (SOR halo fused into the sweep, particle migration, ghost layers, slab all-gathers on a copy stream); level-set sweeps and extrapolation replicated" % world if sharded else "%d independent replicas" % world),
                            "l2": "working set (%.1f GB) larger than L2; no flush" % ((P * 64 + 40.0 * n ** 3) / 1e9)},
                 "e2e": {"value": e2e_value, "unit": "particle-steps/s", "h2d_bytes_per_step": int(bytes_each_way), "d2h_bytes_per_step": int(bytes_each_way),
                         "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+                "check": check, "state_after_timed_steps": final_state,
                 "stage_ms_per_step": {k: v / args.steps for k, v in stage_acc.items()},
                 "stage_note": "LEVELSET_SWEEP runs on a second stream beside P2G and EXTRAPOLATE: they overlap, stage times add up to more than TOTAL"}
         print(json.dumps(line), flush=True)

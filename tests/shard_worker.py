@@ -17,14 +17,25 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("n", type=int, nargs="?", default=24)
     ap.add_argument("steps", type=int, nargs="?", default=3)
+    ap.add_argument("--zflow", type=float, default=0.0, help="m/s: W is overwritten with this value before every step, so that particles "
+                    "cross slab boundaries (migration) and both SOR neighbours of every interior rank carry fluid")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
     dist.init_process_group(backend="gloo")
     n = a.n
     sim = FluidSim3(n, n, n, float(n), device=local, rank=rank, world=world, allgather=torch_allgather())
-    for _ in range(a.steps):
-        sim.Simulate(0.01)
-    sim.sync()
+    owned0 = sim.num_local_particles
+
+    def run(s):
+        for _ in range(a.steps):
+            if a.zflow:
+                u, v, w = s.get_velocity()
+                s.set_velocity(u, v, np.full_like(w, a.zflow))
+            s.Simulate(0.01)
+        s.sync()
+    run(sim)
+    moved = [None] * world
+    dist.all_gather_object(moved, sim.num_local_particles - owned0)
     mine = sim.get_particles()
     parts = [None] * world
     dist.all_gather_object(parts, mine)
@@ -34,15 +45,17 @@ def main():
     ok = True
     if rank == 0:
         one = FluidSim3(n, n, n, float(n), device=local)
-        for _ in range(a.steps):
-            one.Simulate(0.01)
-        one.sync()
+        run(one)
         merged = merge_particles(parts)
         same = lambda x, y: np.array_equal(np.ascontiguousarray(x).view(np.uint32), np.ascontiguousarray(y).view(np.uint32))
         ok = same(merged, one.get_particles())
         ok = ok and np.array_equal(np.concatenate(press).reshape(-1), one.get_pressure())
         ok = ok and all(same(x, y) for x, y in zip(uvw, one.get_velocity())) and same(sim.get_phi(), one.get_phi())
-        print("rank 0: merged result %s the single-GPU run (%d particles, %d steps, world %d)" % ("matches" if ok else "DIFFERS FROM", merged.shape[0], a.steps, world))
+        print("rank 0: merged result %s the single-GPU run (%d^3, %d particles, %d steps, world %d, zflow %g, change of the ranks' particle counts %r)" % (
+            "matches" if ok else "DIFFERS FROM", n, merged.shape[0], a.steps, world, a.zflow, moved))
+        if a.zflow and not any(moved):
+            ok = False
+            print("rank 0: --zflow was meant to move particles between slabs and did not")
     flag = [ok]
     dist.broadcast_object_list(flag, src=0)
     # every rank holds the complete grids

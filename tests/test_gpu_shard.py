@@ -189,13 +189,17 @@ def test_group_reset_after_steps_and_hooks_refused():
     g.close()
 
 
-def test_multiprocess_two_gpus():
-    """One process per GPU over CUDA IPC (needs two B200s: run with `gpurun --gpus 2`; skipped on a single-GPU box)."""
+@pytest.mark.parametrize("world,n,steps,zflow", [(2, 24, 3, 0.0), (2, 32, 4, 4.0), (4, 64, 4, 4.0), (8, 96, 4, 4.0)])
+def test_multiprocess_sharded_step(world, n, steps, zflow):
+    """One process per GPU over CUDA IPC: the merged result must equal the single-GPU run bit for bit.  With zflow the grid
+    velocity W is forced before every step, so particles migrate between slabs and every rank's SOR halo carries fluid.
+    Needs `world` B200s (`gpurun --gpus N`); skipped on a box with fewer (ranks spin on each other's flags inside kernels and
+    must not share a device)."""
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs (ranks spin on each other's flags and must not share a device)")
-    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-                          "--master-port", "29533", os.path.join(ROOT, "tests", "shard_worker.py"), "24", "3"],
-                         capture_output=True, text=True, timeout=600)
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
+                          "--master-port", str(29533 + world), os.path.join(ROOT, "tests", "shard_worker.py"), str(n), str(steps), "--zflow", str(zflow)],
+                         capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "SHARD_WORKER_OK" in out.stdout
