@@ -65,72 +65,69 @@ __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos,
 	rec[c] = best;
 }
 
-// All 8 sweeps in ONE persistent launch, scheduled as a dataflow over 16x16x8 tiles, ONE 128-THREAD CTA PER TILE.
-// Tiles are a fixed partition of physical space.  A work item is (sweep m, tile); the host orders all
-// 8*ntiles items by their earliest possible start level in the dependency DAG (fs3i_levelset_init), and
-// CTAs draw items through a ticket counter.  A CTA that holds an item waits (polling per-tile
-// completion epochs in L2) until
-//   * the tile itself and its 6 face neighbours have completed sweep m-1 (RAW on its own cells, WAR on
-//     the halo cells its neighbours read in sweep m-1), and
-//   * its 3 upwind neighbours have completed sweep m (RAW on the halo),
-// all of which hold lower tickets, so some running CTA can always make progress (no co-residency
-// assumption, no grid-wide barrier), and consecutive sweeps pipeline behind each other as far as the
-// DAG allows.  The sweep is bound by its critical path: 8 n/tx + 4 n/ty + 2 n/tz tile hand-offs (x flips
-// between every pair of sweeps, y every second, z once), each costing a few L2 round trips (poll, halo
-// load, store, release) plus the tile's own tx+ty+tz-2 cell hyperplanes at one shared-memory round trip
-// each.  16x16x8 halves the number of hand-offs of a warp-sized 8x8x4 tile (256 vs 512 at 256^3) while a
-// hyperplane step still costs one barrier.  The tile and its three upwind halo faces sit in shared memory
-// in SWEEP space (index 0 = most upwind) so that one code path serves all 8 directions; 128 threads = the
-// 16x8 x-lines of the tile, thread (b,c) marching along a with hyperplane index s = a+b+c.  Candidates are
-// first compared by squared distance (sqrt and "- radius" are monotonic, so a candidate that is not
-// closer in d^2 can never win the reference's `dist < phi` test); the full reference expression decides
-// the rest.  Records move with cp.async.cg / st.cg (L2 only: L1 is not coherent across SMs).  The last
-// sweep also writes phi and closestParticles[].
-#define LS_TX 16
-#define LS_TY 16
-#define LS_TZ 8
-#define LS_PX (LS_TX + 2)   // x pitch 18 (even): on a hyperplane a+b+c=s the 8 lanes of a quarter warp (consecutive b) hit 8 different 16-byte bank groups
-#define LS_PY (LS_TY + 1)
-#define LS_PZ (LS_TZ + 1)
-#define LS_STEPS (LS_TX + LS_TY + LS_TZ - 2)
-#define LS_LINES (LS_TY * LS_TZ)   // threads that march
-#define LS_THREADS 256             // all of them load, run the quiet-tile test and write phi
-#define LS_CELLS (LS_PX * LS_PY * LS_PZ)
-#define LS_SMEM_BYTES (LS_CELLS * (sizeof(float4) + sizeof(float)))
+// ------------------------------------------------------------------------------------------------------------------------
+// The 8 Gauss-Seidel sweeps (S3D.cpp:306-416), EXACTLY, as a pipeline of skewed warp strips.
+//
+// In the sweep with direction signs (dx,dy,dz) cell (a,b,c) -- sweep coordinates, 0 = most upwind -- reads the final values of
+// (a-1,b,c), (a,b-1,c), (a,b,c-1) in that order; any schedule that respects this partial order reproduces the reference bit for
+// bit.  The schedule here: a TILE is all of x times 32 rows (y) times BZ planes (z); one CTA of BZ warps works on it in lock
+// step, lane l of warp w handling cell  a = t - l - w  of row l, plane w  at step t.  Then
+//   * the x candidate is the lane's own result of the previous step (a register),
+//   * the y candidate is lane l-1's result of the previous step (one warp shuffle),
+//   * the z candidate is warp w-1's result of the previous step (double-buffered shared memory, one CTA barrier per step),
+// so a step is ~100 instructions per lane with no global memory on the dependent chain.  The cell's own record and the halo
+// records a tile edge needs (row -1 for lane 0, plane -1 for warp 0) are prefetched LS_D steps ahead with cp.async.cg into
+// shared-memory rings that every lane reads back itself.  Tiles hand off to their downwind y / z neighbours at step
+// granularity: a tile publishes the number of steps it has completed every LS_CH steps (release store after a fence), and the
+// consumer, which runs the same skew, only has to stay 32 (y) or BZ (z) steps + the prefetch distance behind.  A whole sweep
+// therefore costs about  nx + (ny + nz) cells  of dependent steps plus one L2 round trip per tile hop, instead of one
+// complete-tile latency per hop.  (sweep, tile) items are drawn by ticket in the order of their depth in the dependency DAG, as
+// before: every dependency of an item holds a lower ticket, so some running CTA can always proceed -- no co-residency assumption.
+// Progress words: prog[tile] = (E0 + m) * 2048 + steps completed in sweep m, 2047 = sweep complete (wrap-safe comparisons).
+// Conditions for (m, T): T and its four y/z neighbours have completed sweep m-1 (own cells final; nobody still reads what T is
+// about to overwrite); the upwind y / z tiles are far enough into sweep m (checked before every prefetch).
+// The last sweep also writes phi and closestParticles[].
+#define LS_D 7         // prefetch distance in steps
+#define LS_R 8         // ring slots (> LS_D)
+#define LS_CH 8        // steps between progress publications
+#define LS_PROG_SHIFT 11
+#define LS_PROG_DONE 2047u
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
 	unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
 	uint32_t v;
 	asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
 	return v;
 }
 __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) { asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory"); }
-
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
 	uint32_t v;
 	asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
 	return v;
 }
-// Polls with relaxed loads and a capped exponential back-off, then takes the acquire once the epoch is there.
-// false = gave up (another CTA aborted, or ~2 s without progress: never hang the GPU)
-__device__ __forceinline__ bool ls_wait(const uint32_t* f, uint32_t need, int* flags, unsigned sleep_max) {
-	if ((int32_t)(ld_acquire_u32(f) - need) >= 0) return true;
+// Waits until *f has reached `need` (wrap-safe) and returns the value seen; polls with relaxed loads and a capped back-off, then
+// takes the acquire.  ok = false: gave up (another CTA aborted, or ~2 s without progress: never hang the GPU).
+__device__ __forceinline__ uint32_t ls_wait(const uint32_t* f, uint32_t need, int* flags, unsigned sleep_max, bool& ok) {
+	uint32_t v = ld_acquire_u32(f);
+	if ((int32_t)(v - need) >= 0) return v;
 	long long t0 = clock64();
 	unsigned ns = 32;
 	for (unsigned it = 1;; it++) {
-		if ((int32_t)(ld_relaxed_u32(f) - need) >= 0) break;
+		v = ld_relaxed_u32(f);
+		if ((int32_t)(v - need) >= 0) break;
 		__nanosleep(ns);
 		ns = min(ns * 2, sleep_max);
 		if ((it & 255u) == 0) {
-			if (*reinterpret_cast<volatile int*>(flags + 1)) return false;
-			if (clock64() - t0 > 4000000000LL) { flags[1] = 1; return false; }
+			if (*reinterpret_cast<volatile int*>(flags + 1)) { ok = false; return v; }
+			if (clock64() - t0 > 4000000000LL) { flags[1] = 1; ok = false; return v; }
 		}
 	}
-	return (int32_t)(ld_acquire_u32(f) - need) >= 0;
+	return ld_acquire_u32(f);
 }
 
 __device__ __forceinline__ float ls_d2(float cx, float cy, float cz, float4 q) {
@@ -138,161 +135,156 @@ __device__ __forceinline__ float ls_d2(float cx, float cy, float cz, float4 q) {
 	return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));   // ptDistance's radicand, S3D.cpp:234-236
 }
 
-#ifdef FS3_LS_TRACE
-__device__ unsigned long long* g_ls_trace;   // 8 timestamps per work item (debug builds only, tools/ls_trace.py)
-__device__ __forceinline__ unsigned long long ls_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-#define LS_MARK(k) do { if (threadIdx.x == 0) g_ls_trace[(size_t)t * 8 + (k)] = ls_now(); } while (0)
-#else
-#define LS_MARK(k) do { } while (0)
-#endif
-
 #define LS_INF __int_as_float(0x7f800000)
-__global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __restrict__ rec, GridDims d, float radius,
-                                                                   const uint32_t* __restrict__ items, uint32_t* done, uint32_t* ticket,
-                                                                   uint32_t nitems, int ntx, int nty, int ntz, uint32_t epoch0,
+template <int BZ> struct LsSmem {
+	float4 own[LS_R][BZ][32];   // the cell's record before the sweep, slot = step % LS_R, written and read by the same lane
+	float4 zh[LS_R][32];        // plane -1 of the tile (warp 0's z candidates)
+	float4 yh[LS_R][BZ];        // row -1 of the tile (lane 0's y candidates)
+	float4 zb[2][BZ][32];       // results of the previous step, for the warp of the next plane
+};
+__device__ __forceinline__ int ld_volatile_s32(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
+__device__ __forceinline__ void st_volatile_s32(int* p, int v) { *reinterpret_cast<volatile int*>(p) = v; }
+
+// BZ compute warps + ONE HELPER WARP.  The helper keeps every global-memory round trip of the hand-off protocol off the
+// compute warps' dependent chain: it polls the upwind tiles' progress words and posts what it saw in shared memory (s_ky,
+// s_kz), and it publishes this tile's own progress (fence + release store) whenever the step counter the compute warps leave
+// in shared memory (s_steps) has advanced by LS_CH.  The compute warps synchronise among themselves with a named barrier.
+template <int BZ>
+__global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __restrict__ rec, GridDims d, float radius, const uint32_t* __restrict__ items,
+                                                                   uint32_t* prog, uint32_t* ticket, uint32_t nitems, int nty, int ntz, uint32_t E0,
                                                                    int* __restrict__ flags, float* __restrict__ phi, int* __restrict__ closest, unsigned sleep_max) {
-	extern __shared__ float4 ls_smem[];
+	extern __shared__ float4 ls_smem_raw[];
+	LsSmem<BZ>& sm = *reinterpret_cast<LsSmem<BZ>*>(ls_smem_raw);
 	__shared__ uint32_t s_ticket;
-	__shared__ unsigned s_planes[2];
-	float4* const sm = ls_smem;
-	float* const m2s = reinterpret_cast<float*>(ls_smem + LS_CELLS);   // squared distance of the cell to its current record
-	const int tid = threadIdx.x;
-#define SMI(a, b, c) (((a) + 1) + LS_PX * (((b) + 1) + LS_PY * ((c) + 1)))
+	__shared__ int s_ky, s_kz, s_steps, s_abort, s_stop[2], s_dead;
+	const int tid = threadIdx.x, l = tid & 31, w = tid >> 5;
+	if (tid == 0) s_dead = 0;
 	const float4 none = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
 	const size_t sY = (size_t)d.nx, sZ = (size_t)d.nx * d.ny;
+	const int Ttot = d.nx + 31 + BZ - 1;      // steps of a tile: the last lane of the last warp handles a = nx-1 at step Ttot-1
 	for (;;) {
 		__syncthreads();   // the previous item's shared memory is no longer read
-		if (tid == 0) s_ticket = atomicAdd(ticket, 1u);
+		if (tid == 0) { s_ticket = s_dead ? nitems : atomicAdd(ticket, 1u); s_steps = 0; s_abort = 0; s_stop[0] = s_stop[1] = 0; }
 		__syncthreads();
-		const uint32_t t = s_ticket;
-		if (t >= nitems) break;
-		LS_MARK(0);
-		const uint32_t it = __ldg(items + t);
-		const int m = (int)(it >> 27), Tx = (int)(it & 511u), Ty = (int)((it >> 9) & 511u), Tz = (int)((it >> 18) & 511u);
+		const uint32_t tk = s_ticket;
+		if (tk >= nitems) break;
+		const uint32_t it = __ldg(items + tk);
+		const int m = (int)(it >> 27), Ty = (int)((it >> 9) & 511u), Tz = (int)((it >> 18) & 511u);
 		const int dx = (m & 1) ? -1 : 1, dy = (m & 2) ? -1 : 1, dz = (m & 4) ? -1 : 1;   // sweep order of S3D.cpp:306-416
-		const uint32_t E = epoch0 + (uint32_t)m + 1u;
-		const int x0 = Tx * LS_TX, y0 = Ty * LS_TY, z0 = Tz * LS_TZ;
-		const int wx = min(LS_TX, d.nx - x0), wy = min(LS_TY, d.ny - y0), wz = min(LS_TZ, d.nz - z0);
-		uint32_t* const mydone = done + ((size_t)Tx + (size_t)ntx * ((size_t)Ty + (size_t)nty * Tz));
-		// ---- own cells are final once this tile has completed sweep m-1: start their copy first ----------
+		const uint32_t base = (E0 + (uint32_t)m) << LS_PROG_SHIFT;
+		const int y0 = Ty * 32, z0 = Tz * BZ;
+		const int h = min(32, d.ny - y0), dep = min(BZ, d.nz - z0);
+		uint32_t* const myprog = prog + ((size_t)Ty + (size_t)nty * Tz);
+		const int uyT = Ty - dy, uzT = Tz - dz;                       // upwind tiles of this sweep
+		const bool has_uy = uyT >= 0 && uyT < nty, has_uz = uzT >= 0 && uzT < ntz;
+		const uint32_t* const prog_uy = prog + ((size_t)(has_uy ? uyT : Ty) + (size_t)nty * Tz);
+		const uint32_t* const prog_uz = prog + ((size_t)Ty + (size_t)nty * (has_uz ? uzT : Tz));
+		// ---- this tile and its four neighbours have completed the previous sweep -------------------------------------------
 		bool ok = true;
-		if (tid == 0) ok = ls_wait(mydone, E - 1u, flags, sleep_max);
+		if (tid < 5) {
+			const int qy = Ty + (tid == 1 ? -1 : tid == 2 ? 1 : 0), qz = Tz + (tid == 3 ? -1 : tid == 4 ? 1 : 0);
+			if (qy >= 0 && qy < nty && qz >= 0 && qz < ntz) (void)ls_wait(prog + ((size_t)qy + (size_t)nty * qz), base - 1u, flags, sleep_max, ok);
+		}
+		if (tid == 0) { s_ky = has_uy ? 0 : 0x7fffffff; s_kz = has_uz ? 0 : 0x7fffffff; }
 		if (!__syncthreads_and(ok)) break;
-		LS_MARK(1);
-#pragma unroll
-		for (int i = 0; i < LS_TX * LS_TY * LS_TZ / LS_THREADS; i++) {
-			const int e = tid + LS_THREADS * i, px = e % LS_TX, py = (e / LS_TX) % LS_TY, pz = e / (LS_TX * LS_TY);
-			const int a = (px < wx && dx < 0) ? wx - 1 - px : px, b = (py < wy && dy < 0) ? wy - 1 - py : py, c = (pz < wz && dz < 0) ? wz - 1 - pz : pz;
-			if (px < wx && py < wy && pz < wz) cp_async16(sm + SMI(a, b, c), rec + ((size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)(z0 + pz)));
-			else sm[SMI(a, b, c)] = none;
-		}
-		// ---- the six neighbours: upwind ones must have finished THIS sweep, the others the previous one ---
-		if (tid >= 1 && tid <= 6) {
-			const int ax = (tid - 1) >> 1, sgn = (tid & 1) ? -1 : 1;   // threads 1,2: x-,x+   3,4: y-,y+   5,6: z-,z+
-			const int qx = Tx + (ax == 0 ? sgn : 0), qy = Ty + (ax == 1 ? sgn : 0), qz = Tz + (ax == 2 ? sgn : 0);
-			const int dir = ax == 0 ? dx : (ax == 1 ? dy : dz);
-			if (qx >= 0 && qx < ntx && qy >= 0 && qy < nty && qz >= 0 && qz < ntz)
-				ok = ls_wait(done + ((size_t)qx + (size_t)ntx * ((size_t)qy + (size_t)nty * qz)), sgn == -dir ? E : E - 1u, flags, sleep_max);
-		}
-		if (!__syncthreads_and(ok)) break;
-		LS_MARK(2);
-		// ---- three upwind halo faces (sweep coordinate -1 on one axis) ---------------------------------------
-		{
-			// x face: (b, c) = 16 x 8 cells, threads 0..127
-			const int b = tid % LS_TY, c = (tid / LS_TY) % LS_TZ;
-			const int qx = dx > 0 ? x0 - 1 : x0 + wx, qy = y0 + (dy > 0 ? b : wy - 1 - b), qz = z0 + (dz > 0 ? c : wz - 1 - c);
-			if (tid >= LS_LINES) {}
-			else if (b < wy && c < wz && qx >= 0 && qx < d.nx) cp_async16(sm + SMI(-1, b, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
-			else sm[SMI(-1, b, c)] = none;
-		}
-		{
-			// y face: (a, c) = 16 x 8 cells, threads 128..255
-			const int a = tid % LS_TX, c = (tid / LS_TX) % LS_TZ;
-			const int qx = x0 + (dx > 0 ? a : wx - 1 - a), qy = dy > 0 ? y0 - 1 : y0 + wy, qz = z0 + (dz > 0 ? c : wz - 1 - c);
-			if (tid < LS_LINES) {}
-			else if (a < wx && c < wz && qy >= 0 && qy < d.ny) cp_async16(sm + SMI(a, -1, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
-			else sm[SMI(a, -1, c)] = none;
-		}
-#pragma unroll
-		for (int i = 0; i < LS_TX * LS_TY / LS_THREADS; i++) {
-			// z face: (a, b) = 16 x 16 cells, one per thread
-			const int e = tid + LS_THREADS * i, a = e % LS_TX, b = e / LS_TX;
-			const int qx = x0 + (dx > 0 ? a : wx - 1 - a), qy = y0 + (dy > 0 ? b : wy - 1 - b), qz = dz > 0 ? z0 - 1 : z0 + wz;
-			if (a < wx && b < wy && qz >= 0 && qz < d.nz) cp_async16(sm + SMI(a, b, -1), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
-			else sm[SMI(a, b, -1)] = none;
-		}
-		cp_async_wait_all();
-		__syncthreads();
-		LS_MARK(3);
-		// ---- squared distance of every own cell to its current record, and the quiet-tile test ---------------------------
-		// Fully parallel, x fastest (conflict-free): if no cell would accept any of its three upwind candidates as
-		// they stand BEFORE the sweep (q2 < m2 is necessary for acceptance: sqrt and "- radius" are monotonic),
-		// then by induction along the sweep order the Gauss-Seidel pass changes nothing and the march is skipped.
-		// The hyperplanes a+b+c that hold such a cell are collected in a bit mask: the march only runs a hyperplane that
-		// holds one, or that follows a hyperplane in which a record changed.
-		unsigned long long planes = 0;
-		if (tid == 0) { s_planes[0] = 0u; s_planes[1] = 0u; }
-		__syncthreads();
-		{
-			const int a = tid % LS_TX, b = tid / LS_TX;   // 16 x 16 threads, looping over c
-			const float cxf = (float)(dx > 0 ? x0 + a : x0 + wx - 1 - a), cyf = (float)(dy > 0 ? y0 + b : y0 + wy - 1 - b);
-#pragma unroll
-			for (int c = 0; c < LS_TZ; c++) {
-				const float czf = (float)(dz > 0 ? z0 + c : z0 + wz - 1 - c);
-				const int i = SMI(a, b, c);
-				const float4 cur = sm[i], X = sm[i - 1], Y = sm[i - LS_PX], Z = sm[i - LS_PX * LS_PY];
-				// no record: infinitely far (any valid candidate wins); the same record in a neighbour has the same d^2 and never wins
-				const float m2 = __float_as_int(cur.w) >= 0 ? ls_d2(cxf, cyf, czf, cur) : LS_INF;
-				m2s[i] = m2;
-				const bool wX = __float_as_int(X.w) > 0 && ls_d2(cxf, cyf, czf, X) < m2;
-				const bool wY = __float_as_int(Y.w) > 0 && ls_d2(cxf, cyf, czf, Y) < m2;
-				const bool wZ = __float_as_int(Z.w) > 0 && ls_d2(cxf, cyf, czf, Z) < m2;
-				if (a < wx && b < wy && c < wz && (wX || wY || wZ)) planes |= 1ull << (a + b + c);
+		if (w == BZ) {
+			// ================================ helper warp =================================================================
+			if (l == 0) {
+				int pub = 0, ky = has_uy ? 0 : Ttot, kz = has_uz ? 0 : Ttot;
+				long long t_last = clock64();
+				for (;;) {
+					bool moved = false;
+					const int st = ld_volatile_s32(&s_steps);
+					if (st >= Ttot) break;
+					if (st >= pub + LS_CH) { __threadfence(); st_release_u32(myprog, base + (uint32_t)st); pub = st; moved = true; }
+					if (ky < Ttot) {
+						const int k = min((int)(ld_acquire_u32(prog_uy) - base), Ttot);
+						if (k > ky) { ky = k; __threadfence_block(); st_volatile_s32(&s_ky, k); moved = true; }
+					}
+					if (kz < Ttot) {
+						const int k = min((int)(ld_acquire_u32(prog_uz) - base), Ttot);
+						if (k > kz) { kz = k; __threadfence_block(); st_volatile_s32(&s_kz, k); moved = true; }
+					}
+					if (moved) t_last = clock64();
+					else {
+						__nanosleep(100);
+						if (clock64() - t_last > 4000000000LL || *reinterpret_cast<volatile int*>(flags + 1)) { flags[1] = 1; st_volatile_s32(&s_dead, 1); st_volatile_s32(&s_abort, 1); break; }
+					}
+				}
+				if (!ld_volatile_s32(&s_abort)) { __threadfence(); st_release_u32(myprog, base + LS_PROG_DONE); }   // sweep m of this tile is complete
 			}
-			const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)planes), hi = __reduce_or_sync(0xffffffffu, (unsigned)(planes >> 32));
-			if ((tid & 31) == 0) { if (lo) atomicOr(&s_planes[0], lo); if (hi) atomicOr(&s_planes[1], hi); }
+			continue;   // meets the compute warps at the barrier on top of the item loop
 		}
-		__syncthreads();   // (also orders the m2s stores before the march)
-		planes = (unsigned long long)s_planes[0] | ((unsigned long long)s_planes[1] << 32);
-		const bool quiet = planes == 0;
-#ifdef FS3_LS_TRACE
-		if (tid == 0 && quiet) g_ls_trace[(size_t)t * 8 + 6] = 1;
-#endif
-		// ---- the cell hyperplanes; thread = line (b, c), marching along a ------------------------------------
-		// clsInner on the upwind x-, y-, z-neighbour in that order (S3D.cpp:310-315 and siblings): index <= 0 is never
-		// propagated (:242); a cell without a record takes any candidate and strict `dist < phi` keeps the incumbent
-		// (:248) -- with "no record" and "no candidate" at distance +inf both are one comparison.
-		// Fast path, branch-free, in squared distances: q2 >= m2 can never win (sqrt and "- radius" are monotonic)
-		// and q2 < m2 by more than 2^-21 relative with sqrt(m2) >= 0.5 always wins (the sqrt values differ by >= 1 ulp
-		// and sqrt(m2) - 1 is exact).  A comparison that falls between the two marks the step ambiguous and the
-		// whole warp repeats it with the reference's full expression (warp-uniform branch, rare).
-		// Idle threads compute garbage on a clamped cell of their own line and store nothing; only the 128 line
-		// threads take part (named barrier 1).
-		if (!quiet && tid < LS_LINES) {
-			const int b = tid % LS_TY, c = tid / LS_TY;
-			const bool line_in = b < wy && c < wz;
-			const int gy = y0 + (dy > 0 ? b : wy - 1 - b), gz = z0 + (dz > 0 ? c : wz - 1 - c);
-			const float cyf = (float)gy, czf = (float)gz;
-			const int li = SMI(0, b, c);
-			const int gx0 = dx > 0 ? x0 : x0 + wx - 1;
-			float4* const grow = rec + (sY * (size_t)gy + sZ * (size_t)gz);
-			uint32_t chg = 0;
-			const int nsteps = wx + wy + wz - 2;
-			for (int s = __ffsll((long long)planes) - 1; s < nsteps; s++) {
-				const int a = s - b - c;
-				const bool act = line_in && (unsigned)a < (unsigned)wx;
-				const int ac = min(max(a, 0), LS_TX - 1);
-				const float4* q = sm + li + ac;
-				const float4 mine0 = q[0], X = q[-1], Y = q[-LS_PX], Z = q[-LS_PX * LS_PY];
-				const float m20 = m2s[li + ac];
-				const float cxf = (float)(gx0 + dx * ac);
-				// a candidate with index <= 0 is never propagated (S3D.cpp:242): infinitely far
+		// ================================ compute warps ===================================================================
+		const bool lane_in = l < h && w < dep;
+		const int gy = y0 + (dy > 0 ? l : h - 1 - l), gz = z0 + (dz > 0 ? w : dep - 1 - w);
+		const float cyf = (float)gy, czf = (float)gz;
+		const int gx0 = dx > 0 ? 0 : d.nx - 1;                       // physical x of a = 0
+		float4* const row = rec + (sY * (size_t)(lane_in ? gy : y0) + sZ * (size_t)(lane_in ? gz : z0));
+		// halo rows: row -1 (lane 0 of every warp) and plane -1 (every lane of warp 0), in the upwind tiles
+		const int gyh = dy > 0 ? y0 - 1 : y0 + h, gzh = dz > 0 ? z0 - 1 : z0 + dep;
+		const float4* const rowY = rec + (sY * (size_t)(has_uy ? gyh : y0) + sZ * (size_t)(lane_in ? gz : z0));
+		const float4* const rowZ = rec + (sY * (size_t)(lane_in ? gy : y0) + sZ * (size_t)(has_uz ? gzh : z0));
+		const bool doY = l == 0 && w < dep, doZ = w == 0 && l < h;
+		// prefetch of the records step tp needs; the caller has made sure the upwind tiles are far enough
+		auto prefetch = [&](int tp) {
+			const int slot = tp & (LS_R - 1);
+			const int a = tp - l - w;
+			if ((unsigned)a < (unsigned)d.nx && lane_in) cp_async16(&sm.own[slot][w][l], row + (gx0 + dx * a)); else sm.own[slot][w][l] = none;
+			if (doY) { const int ay = tp - w; if (has_uy && (unsigned)ay < (unsigned)d.nx) cp_async16(&sm.yh[slot][w], rowY + (gx0 + dx * ay)); else sm.yh[slot][w] = none; }
+			if (doZ) { const int az = tp - l; if (has_uz && (unsigned)az < (unsigned)d.nx) cp_async16(&sm.zh[slot][l], rowZ + (gx0 + dx * az)); else sm.zh[slot][l] = none; }
+			cp_async_commit();
+		};
+		// thread 0: the upwind tiles have completed the steps that produce what step tp reads (row 31 / plane BZ-1 of the same
+		// column: 32 / BZ steps later in the producer's own skew); spins on what the helper posts
+		auto ensure = [&](int tp) -> bool {
+			const int needy = min(tp + 32, Ttot), needz = min(tp + BZ, Ttot);
+			while (ld_volatile_s32(&s_ky) < needy || ld_volatile_s32(&s_kz) < needz)
+				if (ld_volatile_s32(&s_abort)) return false;
+			__threadfence_block();
+			return true;
+		};
+		int stop = 0;
+		if (tid == 0 && !ensure(LS_D)) s_stop[1] = 1;
+		asm volatile("bar.sync 1, %0;\n" ::"n"(BZ * 32) : "memory");
+		stop = ld_volatile_s32(&s_stop[1]);
+		if (!stop) {
+#pragma unroll 1
+			for (int tp = 0; tp < LS_D; tp++) prefetch(tp);
+			if (w < BZ - 1) sm.zb[1][w][l] = none;   // "previous step" of step 0
+			asm volatile("bar.sync 1, %0;\n" ::"n"(BZ * 32) : "memory");
+			float4 prev = none;
+#pragma unroll 1
+			for (int t = 0; t < Ttot; t++) {
+				if (t + LS_D < Ttot) prefetch(t + LS_D); else cp_async_commit();
+				cp_async_wait<LS_D>();
+				const int slot = t & (LS_R - 1);
+				const int a = t - l - w;
+				const bool act = lane_in && (unsigned)a < (unsigned)d.nx;
+				const int gx = gx0 + dx * a;
+				const float cxf = (float)gx;
+				const float4 mine0 = sm.own[slot][w][l];
+				float4 Z;
+				if (w > 0) Z = sm.zb[(t + 1) & 1][w - 1][l]; else Z = sm.zh[slot][l];
+				float4 Y;
+				Y.x = __shfl_up_sync(0xffffffffu, prev.x, 1); Y.y = __shfl_up_sync(0xffffffffu, prev.y, 1);
+				Y.z = __shfl_up_sync(0xffffffffu, prev.z, 1); Y.w = __shfl_up_sync(0xffffffffu, prev.w, 1);
+				if (l == 0) Y = sm.yh[slot][w];
+				const float4 X = prev;
+				// clsInner on the upwind x-, y-, z-neighbour in that order (S3D.cpp:310-315 and siblings): a candidate with index <= 0
+				// is never propagated (:242); a cell without a record takes any candidate and strict `dist < phi` keeps the
+				// incumbent (:248) -- with "no record" and "no candidate" at distance +inf both are one comparison.
+				const float m20 = __float_as_int(mine0.w) >= 0 ? ls_d2(cxf, cyf, czf, mine0) : LS_INF;
 				const float x2 = __float_as_int(X.w) > 0 ? ls_d2(cxf, cyf, czf, X) : LS_INF;
 				const float y2 = __float_as_int(Y.w) > 0 ? ls_d2(cxf, cyf, czf, Y) : LS_INF;
 				const float z2 = __float_as_int(Z.w) > 0 ? ls_d2(cxf, cyf, czf, Z) : LS_INF;
 				float4 mine = mine0;
 				float m2 = m20;
 				bool changed = false, amb = false;
+				// Fast path, branch-free, in squared distances: q2 >= m2 can never win (sqrt and "- radius" are monotonic) and
+				// q2 < m2 by more than 2^-21 relative with sqrt(m2) >= 0.5 always wins (the sqrt values differ by >= 1 ulp and
+				// sqrt(m2) - 1 is exact).  A comparison that falls between the two marks the step ambiguous and the whole warp
+				// repeats it with the reference's full expression (warp-uniform branch, rare).
 #define LS_FAST(Q, q2)                                                                                                        \
 	{                                                                                                                        \
 		const bool take = m2 >= 0.25f && q2 < __fmul_rn(m2, 0.99999905f);                                                    \
@@ -317,46 +309,34 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 					LS_TRY(Z, z2)
 #undef LS_TRY
 				}
-				// global write-back is deferred past the loop: a store in flight would put an L2 round trip into every step
-				if (act && changed) { sm[li + a] = mine; m2s[li + a] = m2; chg |= 1u << a; }
-				// barrier among the 128 line threads + "did any record change in this hyperplane"
-				int any;
-				asm volatile("{\n .reg .pred p, q;\n setp.ne.u32 q, %1, 0;\n barrier.red.or.pred p, 1, %2, q;\n selp.u32 %0, 1, 0, p;\n}\n"
-				             : "=r"(any) : "r"((unsigned)(act && changed)), "n"(LS_LINES) : "memory");
-				if (!any) {
-					// nothing changed: the next hyperplane that can is the next one holding a candidate cell
-					const unsigned long long rest = s + 1 < 64 ? planes >> (s + 1) : 0ull;
-					if (!rest) break;
-					s += __ffsll((long long)rest) - 1;
-				}
-			}
-#pragma unroll
-			for (int a = 0; a < LS_TX; a++)
-				if ((chg >> a) & 1u) __stcg(grow + (gx0 + dx * a), sm[li + a]);
-		}
-		if (m == 7) {
-			// cells never reached keep their previous phi, as in the reference where m_Phi is only written
-			// together with closestParticles (S3D.cpp:248-251,296-299).  x fastest: coalesced stores.
-			__syncthreads();
-#pragma unroll
-			for (int i = 0; i < LS_TX * LS_TY * LS_TZ / LS_THREADS; i++) {
-				const int e = tid + LS_THREADS * i, px = e % LS_TX, py = (e / LS_TX) % LS_TY, pz = e / (LS_TX * LS_TY);
-				if (px < wx && py < wy && pz < wz) {
-					const int a = dx < 0 ? wx - 1 - px : px, b = dy < 0 ? wy - 1 - py : py, c = dz < 0 ? wz - 1 - pz : pz;
-					const int id = __float_as_int(sm[SMI(a, b, c)].w);
-					const size_t gi = (size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)(z0 + pz);
+				if (!act) mine = none;
+				if (w < BZ - 1) sm.zb[t & 1][w][l] = mine;
+				if (act && changed) __stcg(row + gx, mine);
+				if (m == 7 && act) {
+					// cells never reached keep their previous phi, as in the reference where m_Phi is only written together with
+					// closestParticles (S3D.cpp:248-251,296-299)
+					const int id = __float_as_int(mine.w);
+					const size_t gi = (size_t)gx + sY * (size_t)gy + sZ * (size_t)gz;
 					closest[gi] = id;
-					if (id >= 0) phi[gi] = __fsub_rn(sqrtf(m2s[SMI(a, b, c)]), radius);
+					if (id >= 0) phi[gi] = __fsub_rn(sqrtf(m2), radius);
 				}
+				prev = mine;
+				if (tid == 0) {
+					// steps < t are complete: every compute thread issued their stores before the last barrier
+					__threadfence_block();
+					st_volatile_s32(&s_steps, t);
+					if (t + 1 + LS_D < Ttot && !ensure(t + 1 + LS_D)) s_stop[t & 1] = 1;
+				}
+				asm volatile("bar.sync 1, %0;\n" ::"n"(BZ * 32) : "memory");
+				if (ld_volatile_s32(&s_stop[t & 1])) { stop = 1; break; }
 			}
 		}
-		// ---- publish: the CTA's stores, then the epoch (release is cumulative over the barrier) ------------
-		LS_MARK(4);
-		__syncthreads();
-		if (tid == 0) { __threadfence(); st_release_u32(mydone, E); }
-		LS_MARK(5);
+		if (tid == 0) {
+			if (stop) { st_volatile_s32(&s_dead, 1); st_volatile_s32(&s_abort, 1); }
+			__threadfence_block();
+			st_volatile_s32(&s_steps, stop ? 0x7fffffff : Ttot);
+		}
 	}
-#undef SMI
 }
 
 // seed of the cells of this rank's slab (world == 1: all cells)
@@ -380,35 +360,22 @@ int fs3i_levelset(fs3_sim* s) {
 }
 
 // the 8 sweeps over the WHOLE grid (a sharded handle runs them replicated on the gathered seed records)
+#ifndef LS_BZ
+#define LS_BZ 8     // planes per tile = compute warps per CTA
+#endif
 int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st) {
 	GridDims d{s->nx, s->ny, s->nz};
 	float radius = s->prm.particle_radius;
 	if (!st) st = s->stream;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SWEEP], st);
-	int ntx = cdiv(d.nx, LS_TX), nty = cdiv(d.ny, LS_TY), ntz = cdiv(d.nz, LS_TZ);
+	const int nty = cdiv(d.ny, 32), ntz = cdiv(d.nz, LS_BZ);
 	FS3_CUDA(cudaMemsetAsync(s->ls_ticket, 0, sizeof(uint32_t), st));
-#ifdef FS3_LS_TRACE
-	static unsigned long long* trace_dev = nullptr;
-	const size_t trace_n = (size_t)8 * s->ls_ntiles * 8;
-	if (!trace_dev) { FS3_CUDA(cudaMalloc((void**)&trace_dev, trace_n * 8)); FS3_CUDA(cudaMemcpyToSymbol(g_ls_trace, &trace_dev, sizeof(trace_dev))); }
-	FS3_CUDA(cudaMemsetAsync(trace_dev, 0, trace_n * 8, st));
-#endif
-	k_ls_sweep_dataflow<<<s->ls_blocks, LS_THREADS, LS_SMEM_BYTES, st>>>(
-	    s->ls_rec, d, radius, s->ls_order, s->ls_done, s->ls_ticket, 8u * (uint32_t)s->ls_ntiles, ntx, nty, ntz, s->ls_epoch, s->dev_flags, s->phi,
+	k_ls_sweep_strips<LS_BZ><<<s->ls_blocks, (LS_BZ + 1) * 32, sizeof(LsSmem<LS_BZ>), st>>>(
+	    s->ls_rec, d, radius, s->ls_order, s->ls_done, s->ls_ticket, 8u * (uint32_t)s->ls_ntiles, nty, ntz, s->ls_epoch, s->dev_flags, s->phi,
 	    s->closest, (unsigned)s->ls_sleep_ns);
 	FS3_LAUNCH_CHECK();
 	s->ls_epoch += 8;
 	s->closest_valid = true;
-#ifdef FS3_LS_TRACE
-	if (const char* path = getenv("FS3_LS_TRACE_FILE")) {
-		std::vector<unsigned long long> h(trace_n);
-		std::vector<uint32_t> ord((size_t)8 * s->ls_ntiles);
-		FS3_CUDA(cudaStreamSynchronize(st));
-		FS3_CUDA(cudaMemcpy(h.data(), trace_dev, trace_n * 8, cudaMemcpyDeviceToHost));
-		FS3_CUDA(cudaMemcpy(ord.data(), s->ls_order, ord.size() * 4, cudaMemcpyDeviceToHost));
-		if (FILE* fp = fopen(path, "wb")) { fwrite(h.data(), 8, trace_n, fp); fwrite(ord.data(), 4, ord.size(), fp); fclose(fp); }
-	}
-#endif
 	return FS3_OK;
 }
 
@@ -437,43 +404,42 @@ int fs3i_levelset_join(fs3_sim* s) {
 	return FS3_OK;
 }
 
-// Work-item table, completion epochs and the persistent grid size (called once from fs3_create).
-// Items (sweep m, tile) are sorted by their level in the dependency DAG -- the earliest "time" at which the
-// item could run if every item took one unit -- which is a topological order (every dependency has a
-// strictly smaller level), so ticket order is deadlock-free, and it lets sweep m+1 start behind sweep m as
-// soon as the DAG allows instead of after it.
+// Work-item table, progress words and the persistent grid size (called once from fs3_create).
+// Items (sweep m, tile) are sorted by their level in the dependency DAG -- the earliest "time" at which the item could start
+// if every hand-off took one unit -- which is a topological order (every dependency has a strictly smaller level), so ticket
+// order is deadlock-free, and tiles of one wavefront hold neighbouring tickets, i.e. run at the same time.
+__global__ void k_fill_u32(uint32_t* p, size_t n, uint32_t v) {
+	size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (q < n) p[q] = v;
+}
 int fs3i_levelset_init(fs3_sim* s) {
-	const int ntx = cdiv(s->nx, LS_TX), nty = cdiv(s->ny, LS_TY), ntz = cdiv(s->nz, LS_TZ);
-	if (ntx > 511 || nty > 511 || ntz > 511) { s->err = "grid too large for the level-set tile table"; return FS3_ERR_INVALID; }
-	const int nt = ntx * nty * ntz;
-	auto tid = [&](int x, int y, int z) { return x + ntx * (y + nty * z); };
+	const int nty = cdiv(s->ny, 32), ntz = cdiv(s->nz, LS_BZ);
+	if (nty > 511 || ntz > 511 || s->nx + 31 + LS_BZ >= (int)LS_PROG_DONE) { s->err = "grid too large for the level-set tile table"; return FS3_ERR_INVALID; }
+	const int nt = nty * ntz;
+	auto tid = [&](int y, int z) { return y + nty * z; };
 	std::vector<int> prev(nt, -1), cur(nt, 0);
 	std::vector<std::pair<int, uint32_t>> items;
 	items.reserve((size_t)8 * nt);
 	int maxlevel = 0;
 	for (int m = 0; m < 8; m++) {
-		const int dx = (m & 1) ? -1 : 1, dy = (m & 2) ? -1 : 1, dz = (m & 4) ? -1 : 1;
+		const int dy = (m & 2) ? -1 : 1, dz = (m & 4) ? -1 : 1;
 		for (int kz = 0; kz < ntz; kz++)
-			for (int ky = 0; ky < nty; ky++)
-				for (int kx = 0; kx < ntx; kx++) {   // sweep-space order: upwind neighbours are visited first
-					const int x = dx > 0 ? kx : ntx - 1 - kx, y = dy > 0 ? ky : nty - 1 - ky, z = dz > 0 ? kz : ntz - 1 - kz;
-					int L = 0;
-					if (kx > 0) L = std::max(L, cur[tid(x - dx, y, z)] + 1);
-					if (ky > 0) L = std::max(L, cur[tid(x, y - dy, z)] + 1);
-					if (kz > 0) L = std::max(L, cur[tid(x, y, z - dz)] + 1);
-					if (m > 0) {
-						L = std::max(L, prev[tid(x, y, z)] + 1);
-						if (x > 0) L = std::max(L, prev[tid(x - 1, y, z)] + 1);
-						if (x < ntx - 1) L = std::max(L, prev[tid(x + 1, y, z)] + 1);
-						if (y > 0) L = std::max(L, prev[tid(x, y - 1, z)] + 1);
-						if (y < nty - 1) L = std::max(L, prev[tid(x, y + 1, z)] + 1);
-						if (z > 0) L = std::max(L, prev[tid(x, y, z - 1)] + 1);
-						if (z < ntz - 1) L = std::max(L, prev[tid(x, y, z + 1)] + 1);
-					}
-					cur[tid(x, y, z)] = L;
-					maxlevel = std::max(maxlevel, L);
-					items.emplace_back(L, (uint32_t)x | ((uint32_t)y << 9) | ((uint32_t)z << 18) | ((uint32_t)m << 27));
+			for (int ky = 0; ky < nty; ky++) {   // sweep-space order: upwind neighbours are visited first
+				const int y = dy > 0 ? ky : nty - 1 - ky, z = dz > 0 ? kz : ntz - 1 - kz;
+				int L = 0;
+				if (ky > 0) L = std::max(L, cur[tid(y - dy, z)] + 1);
+				if (kz > 0) L = std::max(L, cur[tid(y, z - dz)] + 1);
+				if (m > 0) {
+					L = std::max(L, prev[tid(y, z)] + 1);
+					if (y > 0) L = std::max(L, prev[tid(y - 1, z)] + 1);
+					if (y < nty - 1) L = std::max(L, prev[tid(y + 1, z)] + 1);
+					if (z > 0) L = std::max(L, prev[tid(y, z - 1)] + 1);
+					if (z < ntz - 1) L = std::max(L, prev[tid(y, z + 1)] + 1);
 				}
+				cur[tid(y, z)] = L;
+				maxlevel = std::max(maxlevel, L);
+				items.emplace_back(L, ((uint32_t)y << 9) | ((uint32_t)z << 18) | ((uint32_t)m << 27));
+			}
 		prev = cur;
 	}
 	std::stable_sort(items.begin(), items.end(), [](const std::pair<int, uint32_t>& a, const std::pair<int, uint32_t>& b) { return a.first < b.first; });
@@ -484,34 +450,21 @@ int fs3i_levelset_init(fs3_sim* s) {
 	if ((rc = fs3i_alloc(s, (void**)&s->ls_done, sizeof(uint32_t) * nt))) return rc;
 	if ((rc = fs3i_alloc(s, (void**)&s->ls_ticket, sizeof(uint32_t)))) return rc;
 	FS3_CUDA(cudaMemcpyAsync(s->ls_order, ord.data(), sizeof(uint32_t) * ord.size(), cudaMemcpyHostToDevice, s->stream));
-	FS3_CUDA(cudaMemsetAsync(s->ls_done, 0, sizeof(uint32_t) * nt, s->stream));
+	// the first call's sweeps have global indices 8..15: every tile starts as "sweep 7 complete"
+	s->ls_epoch = 8;
+	k_fill_u32<<<cdiv(nt, 256), 256, 0, s->stream>>>(s->ls_done, (size_t)nt, (7u << LS_PROG_SHIFT) + LS_PROG_DONE); FS3_LAUNCH_CHECK();
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	s->ls_ntiles = nt;
 	s->ls_levels = maxlevel + 1;
-	s->ls_epoch = 0;
 	int per_sm = 0, sms = 0;
-	const size_t smem = LS_SMEM_BYTES;
-	FS3_CUDA(cudaFuncSetAttribute(k_ls_sweep_dataflow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ls_sweep_dataflow, LS_THREADS, smem));
+	const size_t smem = sizeof(LsSmem<LS_BZ>);
+	FS3_CUDA(cudaFuncSetAttribute(k_ls_sweep_strips<LS_BZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ls_sweep_strips<LS_BZ>, (LS_BZ + 1) * 32, smem));
 	FS3_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
-	// Resident CTAs beyond what the DAG can keep busy only add pollers.  Tunables (debug): FS3_LS_BLOCKS_PER_SM, FS3_LS_SLEEP_NS.
-	const int occ = std::max(1, per_sm);
-	// The sweep is bound by its critical path, not by throughput.  Single GPU: one CTA per SM, because the sweeps run beside
-	// the P2G gather and the extrapolation (fs3_step) and should take as little from them as possible.  Sharded: the replicated
-	// sweeps run beside the slab's gather and the replicated extrapolation and must end with them; measured at 256^3 on 2 GPUs
-	// with 2 / 1.5 / 1.25 / 1 CTAs per SM: sweeps 3.85 / 4.14 / 4.58 / 5.34 ms, step 13.56 / 12.88 / 12.69 / 13.18 ms.  The
-	// sweeps' slack shrinks with the world size (the gather gets shorter, the sweeps do not) and is gone at 8 ranks -- there the
-	// extrapolation stage already ends with the join (sweeps 3.87 ms + the seed barrier = gather 1.57 + extrapolation 2.99) --
-	// so 1.25 per SM on 2 ranks (measured), 1.5 on 3-4 (by the same timeline: sweeps + barrier 4.4 ms against gather +
-	// extrapolation 5.2 ms at N = 4) and the measured 2 per SM above.
-	per_sm = std::min(occ, s->world == 1 ? 1 : 2);
-	if (const char* e = getenv("FS3_LS_BLOCKS_PER_SM")) per_sm = std::min(occ, std::max(1, atoi(e)));
+	// Every tile of a sweep can be in flight at once (they follow each other at hand-off distance), so the grid holds up to one
+	// CTA per tile; the ticket scheme needs no co-residency, any count is valid.
 	s->ls_sleep_ns = 256;
-	if (const char* e = getenv("FS3_LS_SLEEP_NS")) s->ls_sleep_ns = std::max(20, atoi(e));
-	long long blocks = (long long)std::max(1, per_sm) * sms;
-	if (s->world > 1 && s->world <= 4 && occ >= 2 && !getenv("FS3_LS_BLOCKS_PER_SM")) blocks = s->world == 2 ? (5LL * sms) / 4 : (3LL * sms) / 2;
-	// FS3_LS_BLOCKS (debug): absolute grid size; the ticket scheme needs no co-residency, any count is valid
-	if (const char* e = getenv("FS3_LS_BLOCKS")) blocks = std::min<long long>((long long)occ * sms, std::max(1, atoi(e)));
-	s->ls_blocks = (int)std::min<long long>(blocks, 8LL * nt);
+	const long long resident = (long long)std::max(1, std::min(per_sm, 2)) * sms;
+	s->ls_blocks = (int)std::max<long long>(1, std::min<long long>(resident, nt));
 	return FS3_OK;
 }
