@@ -22,13 +22,42 @@ __device__ __forceinline__ float ls_dist(float cx, float cy, float cz, float4 q,
 	return __fsub_rn(sqrtf(s), radius);
 }
 
+// ---- DIAMOND layout of the per-cell records -----------------------------------------------------------------------------
+// A sweep step of one warp touches 32 cells on a diagonal of an (x, 32 rows) strip: x + r = const when the sweep runs the same
+// way in x and y, x - r = const when it does not.  In natural order those are 32 different cache lines per load or store, and
+// the load/store unit serialises them (measured: the whole sweep was bound by that).  A layout that makes one family of
+// diagonals contiguous scatters the other, so the strip is cut into DIAMONDS instead: with u = x + r, v = x - r + 31, a 512-byte
+// block holds the 32 cells of one 8 x 8 square in (u, v) (u + v is always odd, so half the square's points are cells).  Either
+// kind of diagonal then crosses 8 blocks and uses 4 consecutive-in-time cells of each: 8 lines per warp instruction for every
+// sweep direction, and every fetched sector is used.  u >> 3 and v >> 3 differ by at most 4, so a strip is (S + 7) / 8 block
+// columns of 9 blocks, S = nx + 31 (1.27x the natural size at nx = 256).  Strips are ordered (z, y / 32): z planes stay contiguous.
+struct LsLayout {
+	int nty, ub;        // strips per plane, block columns per strip
+	uint32_t strip;     // records per strip
+};
+static inline LsLayout ls_layout(int nx, int ny) {
+	LsLayout L;
+	L.nty = (ny + 31) / 32; L.ub = (nx + 31 + 7) / 8; L.strip = (uint32_t)L.ub * 9u * 32u;
+	return L;
+}
+size_t fs3i_levelset_plane_elems(int nx, int ny) { const LsLayout L = ls_layout(nx, ny); return (size_t)L.nty * L.strip; }
+size_t fs3i_levelset_rec_elems(int nx, int ny, int nz) {
+	const size_t diamond = fs3i_levelset_plane_elems(nx, ny) * (size_t)nz, natural = (size_t)nx * ny * nz;
+	return diamond > natural ? diamond : natural;
+}
+__device__ __forceinline__ uint32_t ls_off(int x, int r) {   // offset of cell (x, row r) inside its strip
+	const int u = x + r, v = x - r + 31, U = u >> 3, V = v >> 3;
+	return (uint32_t)(((U * 9 + (V - U + 4)) << 5) + ((((u & 7) << 3) + (v & 7)) >> 1));
+}
+__device__ __forceinline__ size_t ls_strip_base(const LsLayout& L, int ty, int z) { return ((size_t)z * L.nty + ty) * (size_t)L.strip; }
+
 // Seed (S3D.cpp:281-300): minimum kernel distance over the particles of the cell (its 8 half-cells); the
 // reference's strict `phi > k` in index order keeps the lowest index on ties.
 // A cell's particles are four runs (FS3_FOR_CELL_RANGES) of about two particles each.  The eight run bounds and then the first
 // two particles of every run are fetched before anything is compared (8 independent loads in flight per thread instead of
 // one dependent load per loop iteration); longer runs finish in a tail loop.  min by (k, id) does not depend on the order.
 __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos, const uint32_t* __restrict__ start, GridDims d, float radius,
-                                                 float4* __restrict__ rec, size_t c0, size_t c1) {
+                                                 float4* __restrict__ rec, LsLayout L, size_t c0, size_t c1) {
 	size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (c >= c1) return;
 	int x = (int)(c % d.nx), y = (int)((c / d.nx) % d.ny), z = (int)(c / ((size_t)d.nx * d.ny));
@@ -62,7 +91,20 @@ __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos,
 #pragma unroll
 	for (int hr = 0; hr < 4; hr++)
 		for (uint32_t t = B[hr] + 2; t < E[hr]; t++) consider(__ldg(pos + t));
-	rec[c] = best;
+	rec[ls_strip_base(L, y >> 5, z) + ls_off(x, y & 31)] = best;
+}
+
+// phi and closestParticles[] from the records the last sweep left.  Cells never reached keep their previous phi, as in the
+// reference where m_Phi is only written together with closestParticles (S3D.cpp:248-251,296-299).
+__global__ void __launch_bounds__(256) k_ls_finish(const float4* __restrict__ rec, LsLayout L, GridDims d, float radius, float* __restrict__ phi,
+                                                   int* __restrict__ closest, size_t c0, size_t c1) {
+	size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= c1) return;
+	int x = (int)(c % d.nx), y = (int)((c / d.nx) % d.ny), z = (int)(c / ((size_t)d.nx * d.ny));
+	const float4 q = __ldcg(rec + ls_strip_base(L, y >> 5, z) + ls_off(x, y & 31));
+	const int id = __float_as_int(q.w);
+	closest[c] = id;
+	if (id >= 0) phi[c] = ls_dist((float)x, (float)y, (float)z, q, radius);
 }
 
 // ------------------------------------------------------------------------------------------------------------------------
@@ -136,6 +178,13 @@ __device__ __forceinline__ float ls_d2(float cx, float cy, float cz, float4 q) {
 }
 
 #define LS_INF __int_as_float(0x7f800000)
+#ifdef FS3_LS_TRACE
+__device__ unsigned long long* g_ls_trace;   // 4 timestamps per work item (debug side build only, tools/ls_trace.py)
+__device__ __forceinline__ unsigned long long ls_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define LS_MARK(k) do { if (tid == 0) g_ls_trace[(size_t)tk * 4 + (k)] = ls_now(); } while (0)
+#else
+#define LS_MARK(k) do { } while (0)
+#endif
 template <int BZ> struct LsSmem {
 	float4 own[LS_R][BZ][32];   // the cell's record before the sweep, slot = step % LS_R, written and read by the same lane
 	float4 zh[LS_R][32];        // plane -1 of the tile (warp 0's z candidates)
@@ -150,9 +199,9 @@ __device__ __forceinline__ void st_volatile_s32(int* p, int v) { *reinterpret_ca
 // s_kz), and it publishes this tile's own progress (fence + release store) whenever the step counter the compute warps leave
 // in shared memory (s_steps) has advanced by LS_CH.  The compute warps synchronise among themselves with a named barrier.
 template <int BZ>
-__global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __restrict__ rec, GridDims d, float radius, const uint32_t* __restrict__ items,
+__global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __restrict__ rec, LsLayout L, GridDims d, float radius, const uint32_t* __restrict__ items,
                                                                    uint32_t* prog, uint32_t* ticket, uint32_t nitems, int nty, int ntz, uint32_t E0,
-                                                                   int* __restrict__ flags, float* __restrict__ phi, int* __restrict__ closest, unsigned sleep_max) {
+                                                                   int* __restrict__ flags, unsigned sleep_max) {
 	extern __shared__ float4 ls_smem_raw[];
 	LsSmem<BZ>& sm = *reinterpret_cast<LsSmem<BZ>*>(ls_smem_raw);
 	__shared__ uint32_t s_ticket;
@@ -160,7 +209,7 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 	const int tid = threadIdx.x, l = tid & 31, w = tid >> 5;
 	if (tid == 0) s_dead = 0;
 	const float4 none = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-	const size_t sY = (size_t)d.nx, sZ = (size_t)d.nx * d.ny;
+	const bool fast_ok = radius == 1.0f;
 	const int Ttot = d.nx + 31 + BZ - 1;      // steps of a tile: the last lane of the last warp handles a = nx-1 at step Ttot-1
 	for (;;) {
 		__syncthreads();   // the previous item's shared memory is no longer read
@@ -168,6 +217,7 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 		__syncthreads();
 		const uint32_t tk = s_ticket;
 		if (tk >= nitems) break;
+		LS_MARK(0);
 		const uint32_t it = __ldg(items + tk);
 		const int m = (int)(it >> 27), Ty = (int)((it >> 9) & 511u), Tz = (int)((it >> 18) & 511u);
 		const int dx = (m & 1) ? -1 : 1, dy = (m & 2) ? -1 : 1, dz = (m & 4) ? -1 : 1;   // sweep order of S3D.cpp:306-416
@@ -187,6 +237,7 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 		}
 		if (tid == 0) { s_ky = has_uy ? 0 : 0x7fffffff; s_kz = has_uz ? 0 : 0x7fffffff; }
 		if (!__syncthreads_and(ok)) break;
+		LS_MARK(1);
 		if (w == BZ) {
 			// ================================ helper warp =================================================================
 			if (l == 0) {
@@ -197,17 +248,21 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 					const int st = ld_volatile_s32(&s_steps);
 					if (st >= Ttot) break;
 					if (st >= pub + LS_CH) { __threadfence(); st_release_u32(myprog, base + (uint32_t)st); pub = st; moved = true; }
+					// RELAXED polls: an acquire load is LDG + CCTL.IVALL on this architecture, and an L1 invalidation every few
+					// hundred nanoseconds stalls the load/store unit the compute warps' shared-memory traffic goes through.  No
+					// invalidation is needed: the records this flag guards are fetched with cp.async.cg, which bypasses L1, after
+					// the compute warps' next barrier.
 					if (ky < Ttot) {
-						const int k = min((int)(ld_acquire_u32(prog_uy) - base), Ttot);
-						if (k > ky) { ky = k; __threadfence_block(); st_volatile_s32(&s_ky, k); moved = true; }
+						const int k = min((int)(ld_relaxed_u32(prog_uy) - base), Ttot);
+						if (k > ky) { ky = k; st_volatile_s32(&s_ky, k); moved = true; }
 					}
 					if (kz < Ttot) {
-						const int k = min((int)(ld_acquire_u32(prog_uz) - base), Ttot);
-						if (k > kz) { kz = k; __threadfence_block(); st_volatile_s32(&s_kz, k); moved = true; }
+						const int k = min((int)(ld_relaxed_u32(prog_uz) - base), Ttot);
+						if (k > kz) { kz = k; st_volatile_s32(&s_kz, k); moved = true; }
 					}
 					if (moved) t_last = clock64();
 					else {
-						__nanosleep(100);
+						__nanosleep(200);
 						if (clock64() - t_last > 4000000000LL || *reinterpret_cast<volatile int*>(flags + 1)) { flags[1] = 1; st_volatile_s32(&s_dead, 1); st_volatile_s32(&s_abort, 1); break; }
 					}
 				}
@@ -220,19 +275,21 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 		const int gy = y0 + (dy > 0 ? l : h - 1 - l), gz = z0 + (dz > 0 ? w : dep - 1 - w);
 		const float cyf = (float)gy, czf = (float)gz;
 		const int gx0 = dx > 0 ? 0 : d.nx - 1;                       // physical x of a = 0
-		float4* const row = rec + (sY * (size_t)(lane_in ? gy : y0) + sZ * (size_t)(lane_in ? gz : z0));
-		// halo rows: row -1 (lane 0 of every warp) and plane -1 (every lane of warp 0), in the upwind tiles
-		const int gyh = dy > 0 ? y0 - 1 : y0 + h, gzh = dz > 0 ? z0 - 1 : z0 + dep;
-		const float4* const rowY = rec + (sY * (size_t)(has_uy ? gyh : y0) + sZ * (size_t)(lane_in ? gz : z0));
-		const float4* const rowZ = rec + (sY * (size_t)(lane_in ? gy : y0) + sZ * (size_t)(has_uz ? gzh : z0));
+		// strips (diamond layout): own row r of strip (Ty, gz); halo row -1 = the last row in sweep order of the upwind y tile
+		// (lane 0 of every warp); halo plane -1 = the same row of the upwind z tile's last plane (every lane of warp 0)
+		const int r = gy & 31;
+		float4* const row = rec + ls_strip_base(L, Ty, lane_in ? gz : z0);
+		const int gzh = dz > 0 ? z0 - 1 : z0 + dep, rY = dy > 0 ? 31 : 0;
+		const float4* const rowY = rec + ls_strip_base(L, has_uy ? uyT : Ty, lane_in ? gz : z0);
+		const float4* const rowZ = rec + ls_strip_base(L, Ty, has_uz ? gzh : z0);
 		const bool doY = l == 0 && w < dep, doZ = w == 0 && l < h;
 		// prefetch of the records step tp needs; the caller has made sure the upwind tiles are far enough
 		auto prefetch = [&](int tp) {
 			const int slot = tp & (LS_R - 1);
 			const int a = tp - l - w;
-			if ((unsigned)a < (unsigned)d.nx && lane_in) cp_async16(&sm.own[slot][w][l], row + (gx0 + dx * a)); else sm.own[slot][w][l] = none;
-			if (doY) { const int ay = tp - w; if (has_uy && (unsigned)ay < (unsigned)d.nx) cp_async16(&sm.yh[slot][w], rowY + (gx0 + dx * ay)); else sm.yh[slot][w] = none; }
-			if (doZ) { const int az = tp - l; if (has_uz && (unsigned)az < (unsigned)d.nx) cp_async16(&sm.zh[slot][l], rowZ + (gx0 + dx * az)); else sm.zh[slot][l] = none; }
+			if ((unsigned)a < (unsigned)d.nx && lane_in) cp_async16(&sm.own[slot][w][l], row + ls_off(gx0 + dx * a, r)); else sm.own[slot][w][l] = none;
+			if (doY) { const int ay = tp - w; if (has_uy && (unsigned)ay < (unsigned)d.nx) cp_async16(&sm.yh[slot][w], rowY + ls_off(gx0 + dx * ay, rY)); else sm.yh[slot][w] = none; }
+			if (doZ) { const int az = tp - l; if (has_uz && (unsigned)az < (unsigned)d.nx) cp_async16(&sm.zh[slot][l], rowZ + ls_off(gx0 + dx * az, r)); else sm.zh[slot][l] = none; }
 			cp_async_commit();
 		};
 		// thread 0: the upwind tiles have completed the steps that produce what step tp reads (row 31 / plane BZ-1 of the same
@@ -241,13 +298,16 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 			const int needy = min(tp + 32, Ttot), needz = min(tp + BZ, Ttot);
 			while (ld_volatile_s32(&s_ky) < needy || ld_volatile_s32(&s_kz) < needz)
 				if (ld_volatile_s32(&s_abort)) return false;
-			__threadfence_block();
+			// (no fence: the helper took the acquire; the records are fetched after the next barrier with cp.async.cg, i.e. from
+			// L2, where the producer's fence has made them visible before its progress word.  A CTA-scope fence here is a
+			// MEMBAR.SC that waits for the thread's own outstanding stores -- an L2 round trip in every step.)
 			return true;
 		};
 		int stop = 0;
 		if (tid == 0 && !ensure(LS_D)) s_stop[1] = 1;
 		asm volatile("bar.sync 1, %0;\n" ::"n"(BZ * 32) : "memory");
 		stop = ld_volatile_s32(&s_stop[1]);
+		LS_MARK(2);
 		if (!stop) {
 #pragma unroll 1
 			for (int tp = 0; tp < LS_D; tp++) prefetch(tp);
@@ -281,13 +341,15 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 				float4 mine = mine0;
 				float m2 = m20;
 				bool changed = false, amb = false;
-				// Fast path, branch-free, in squared distances: q2 >= m2 can never win (sqrt and "- radius" are monotonic) and
-				// q2 < m2 by more than 2^-21 relative with sqrt(m2) >= 0.5 always wins (the sqrt values differ by >= 1 ulp and
-				// sqrt(m2) - 1 is exact).  A comparison that falls between the two marks the step ambiguous and the whole warp
-				// repeats it with the reference's full expression (warp-uniform branch, rare).
+				// Fast path, branch-free, in squared distances (radius == 1 only): q2 >= m2 can never win (sqrt and "- radius" are
+				// monotonic); q2 < m2 by more than 2^-21 relative with sqrt(m2) >= 0.5 always wins (the sqrt values differ by
+				// >= 1 ulp and sqrt(m2) - 1 is exact); and below that -- both roots < 0.5, the common case inside the fluid --
+				// q2 < m2 - 2^-22 always wins (the roots then differ by > 2^-22 - 2^-25, and rounding root - 1 to the 2^-24 grid of
+				// (-1, -0.5] moves each side by at most 2^-25).  A comparison that falls between "never" and "always" marks the
+				// step ambiguous and the whole warp repeats it with the reference's full expression (warp-uniform branch, rare).
 #define LS_FAST(Q, q2)                                                                                                        \
 	{                                                                                                                        \
-		const bool take = m2 >= 0.25f && q2 < __fmul_rn(m2, 0.99999905f);                                                    \
+		const bool take = q2 < (m2 >= 0.25f ? __fmul_rn(m2, 0.99999905f) : __fsub_rn(m2, 2.5e-7f)) && fast_ok;                \
 		amb |= !take && q2 < m2;                                                                                             \
 		mine.x = take ? Q.x : mine.x; mine.y = take ? Q.y : mine.y; mine.z = take ? Q.z : mine.z; mine.w = take ? Q.w : mine.w; \
 		m2 = take ? q2 : m2; changed |= take;                                                                                \
@@ -311,19 +373,11 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 				}
 				if (!act) mine = none;
 				if (w < BZ - 1) sm.zb[t & 1][w][l] = mine;
-				if (act && changed) __stcg(row + gx, mine);
-				if (m == 7 && act) {
-					// cells never reached keep their previous phi, as in the reference where m_Phi is only written together with
-					// closestParticles (S3D.cpp:248-251,296-299)
-					const int id = __float_as_int(mine.w);
-					const size_t gi = (size_t)gx + sY * (size_t)gy + sZ * (size_t)gz;
-					closest[gi] = id;
-					if (id >= 0) phi[gi] = __fsub_rn(sqrtf(m2), radius);
-				}
+				if (act && changed) __stcg(row + ls_off(gx, r), mine);
 				prev = mine;
 				if (tid == 0) {
-					// steps < t are complete: every compute thread issued their stores before the last barrier
-					__threadfence_block();
+					// steps < t are complete: every compute thread issued their stores before the last barrier (the helper's
+					// gpu-scope fence in front of its release store orders them, as in the usual barrier + fence + flag pattern)
 					st_volatile_s32(&s_steps, t);
 					if (t + 1 + LS_D < Ttot && !ensure(t + 1 + LS_D)) s_stop[t & 1] = 1;
 				}
@@ -331,9 +385,9 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 				if (ld_volatile_s32(&s_stop[t & 1])) { stop = 1; break; }
 			}
 		}
+		LS_MARK(3);
 		if (tid == 0) {
 			if (stop) { st_volatile_s32(&s_dead, 1); st_volatile_s32(&s_abort, 1); }
-			__threadfence_block();
 			st_volatile_s32(&s_steps, stop ? 0x7fffffff : Ttot);
 		}
 	}
@@ -345,7 +399,7 @@ int fs3i_levelset_seed(fs3_sim* s, cudaStream_t st) {
 	if (!st) st = s->stream;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SEED], st);
 	const size_t plane = (size_t)s->nx * s->ny, c0 = plane * s->z0, c1 = plane * s->z1;
-	k_ls_seed<<<cdiv((long long)(c1 - c0), 256), 256, 0, st>>>(s->pos[s->cur], s->cell_start, d, s->prm.particle_radius, s->ls_rec, c0, c1);
+	k_ls_seed<<<cdiv((long long)(c1 - c0), 256), 256, 0, st>>>(s->pos[s->cur], s->cell_start, d, s->prm.particle_radius, s->ls_rec, ls_layout(s->nx, s->ny), c0, c1);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
@@ -370,10 +424,29 @@ int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st) {
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SWEEP], st);
 	const int nty = cdiv(d.ny, 32), ntz = cdiv(d.nz, LS_BZ);
 	FS3_CUDA(cudaMemsetAsync(s->ls_ticket, 0, sizeof(uint32_t), st));
+	const LsLayout L = ls_layout(s->nx, s->ny);
+#ifdef FS3_LS_TRACE
+	static unsigned long long* trace_dev = nullptr;
+	const size_t trace_n = (size_t)8 * s->ls_ntiles * 4;
+	if (!trace_dev) { FS3_CUDA(cudaMalloc((void**)&trace_dev, trace_n * 8)); FS3_CUDA(cudaMemcpyToSymbol(g_ls_trace, &trace_dev, sizeof(trace_dev))); }
+	FS3_CUDA(cudaMemsetAsync(trace_dev, 0, trace_n * 8, st));
+#endif
 	k_ls_sweep_strips<LS_BZ><<<s->ls_blocks, (LS_BZ + 1) * 32, sizeof(LsSmem<LS_BZ>), st>>>(
-	    s->ls_rec, d, radius, s->ls_order, s->ls_done, s->ls_ticket, 8u * (uint32_t)s->ls_ntiles, nty, ntz, s->ls_epoch, s->dev_flags, s->phi,
-	    s->closest, (unsigned)s->ls_sleep_ns);
+	    s->ls_rec, L, d, radius, s->ls_order, s->ls_done, s->ls_ticket, 8u * (uint32_t)s->ls_ntiles, nty, ntz, s->ls_epoch, s->dev_flags,
+	    (unsigned)s->ls_sleep_ns);
 	FS3_LAUNCH_CHECK();
+	k_ls_finish<<<cdiv((long long)s->nC, 256), 256, 0, st>>>(s->ls_rec, L, d, radius, s->phi, s->closest, 0, s->nC);
+	FS3_LAUNCH_CHECK();
+#ifdef FS3_LS_TRACE
+	{
+		std::vector<unsigned long long> h(trace_n);
+		std::vector<uint32_t> ord((size_t)8 * s->ls_ntiles);
+		FS3_CUDA(cudaStreamSynchronize(st));
+		FS3_CUDA(cudaMemcpy(h.data(), trace_dev, trace_n * 8, cudaMemcpyDeviceToHost));
+		FS3_CUDA(cudaMemcpy(ord.data(), s->ls_order, ord.size() * 4, cudaMemcpyDeviceToHost));
+		if (FILE* fp = fopen("/tmp/ls_trace.bin", "wb")) { fwrite(h.data(), 8, trace_n, fp); fwrite(ord.data(), 4, ord.size(), fp); fclose(fp); }
+	}
+#endif
 	s->ls_epoch += 8;
 	s->closest_valid = true;
 	return FS3_OK;

@@ -131,7 +131,7 @@ def test_group_empty_slab_receives_immigrants():
     rng = np.random.default_rng(11)
     P = 3000
     pos = rng.uniform(0.15, 0.85, (P, 3)).astype(np.float32)
-    pos[:, 2] = rng.uniform(0.30, 0.47, P).astype(np.float32)      # cells z = 5..7: all in slab 1 (planes 4..7); slabs 0, 2, 3 are empty
+    pos[:, 2] = rng.uniform(0.30, 0.45, P).astype(np.float32)      # n*Z in 4.8..7.2, cells z = 5..7: all in slab 1 (planes 4..7); slabs 0, 2, 3 are empty
     part = np.ascontiguousarray(np.concatenate([pos, np.zeros((P, 3), np.float32)], axis=1))
     u, v, w = one.get_velocity()
     u, v, w = np.zeros_like(u), np.zeros_like(v), np.full_like(w, 6.0)   # 6 m/s * 0.01 s * 16 cells/m: about one cell per step, upwards
