@@ -45,10 +45,10 @@ size_t fs3i_levelset_rec_elems(int nx, int ny, int nz) {
 	const size_t diamond = fs3i_levelset_plane_elems(nx, ny) * (size_t)nz, natural = (size_t)nx * ny * nz;
 	return diamond > natural ? diamond : natural;
 }
-__device__ __forceinline__ uint32_t ls_off(int x, int r) {   // offset of cell (x, row r) inside its strip
-	const int u = x + r, v = x - r + 31, U = u >> 3, V = v >> 3;
-	return (uint32_t)(((U * 9 + (V - U + 4)) << 5) + ((((u & 7) << 3) + (v & 7)) >> 1));
+__device__ __forceinline__ uint32_t ls_off_uv(int u, int v) {   // block (U, V) at U * 9 + (V - U + 4) = 8 U + V + 4
+	return (uint32_t)((((u & ~7) + (v >> 3) + 4) << 5) + ((((u & 7) << 3) + (v & 7)) >> 1));
 }
+__device__ __forceinline__ uint32_t ls_off(int x, int r) { return ls_off_uv(x + r, x - r + 31); }   // offset of cell (x, row r) inside its strip
 __device__ __forceinline__ size_t ls_strip_base(const LsLayout& L, int ty, int z) { return ((size_t)z * L.nty + ty) * (size_t)L.strip; }
 
 // Seed (S3D.cpp:281-300): minimum kernel distance over the particles of the cell (its 8 half-cells); the
@@ -112,25 +112,35 @@ __global__ void __launch_bounds__(256) k_ls_finish(const float4* __restrict__ re
 //
 // In the sweep with direction signs (dx,dy,dz) cell (a,b,c) -- sweep coordinates, 0 = most upwind -- reads the final values of
 // (a-1,b,c), (a,b-1,c), (a,b,c-1) in that order; any schedule that respects this partial order reproduces the reference bit for
-// bit.  The schedule here: a TILE is all of x times 32 rows (y) times BZ planes (z); one CTA of BZ warps works on it in lock
-// step, lane l of warp w handling cell  a = t - l - w  of row l, plane w  at step t.  Then
+// bit.  The schedule here: a TILE is all of x times 32 rows (y) times BZ planes (z); BZ COMPUTE WARPS work on it in lock step,
+// lane l of warp w handling cell  a = t - l - w  of row l, plane w  at step t.  Then
 //   * the x candidate is the lane's own result of the previous step (a register),
 //   * the y candidate is lane l-1's result of the previous step (one warp shuffle),
-//   * the z candidate is warp w-1's result of the previous step (double-buffered shared memory, one CTA barrier per step),
-// so a step is ~100 instructions per lane with no global memory on the dependent chain.  The cell's own record and the halo
-// records a tile edge needs (row -1 for lane 0, plane -1 for warp 0) are prefetched LS_D steps ahead with cp.async.cg into
-// shared-memory rings that every lane reads back itself.  Tiles hand off to their downwind y / z neighbours at step
-// granularity: a tile publishes the number of steps it has completed every LS_CH steps (release store after a fence), and the
-// consumer, which runs the same skew, only has to stay 32 (y) or BZ (z) steps + the prefetch distance behind.  A whole sweep
-// therefore costs about  nx + (ny + nz) cells  of dependent steps plus one L2 round trip per tile hop, instead of one
-// complete-tile latency per hop.  (sweep, tile) items are drawn by ticket in the order of their depth in the dependency DAG, as
-// before: every dependency of an item holds a lower ticket, so some running CTA can always proceed -- no co-residency assumption.
-// Progress words: prog[tile] = (E0 + m) * 2048 + steps completed in sweep m, 2047 = sweep complete (wrap-safe comparisons).
+//   * the z candidate is warp w-1's result of the previous step (the shared-memory ring the results leave through),
+// and a step's dependent chain holds no global memory access and no address arithmetic: the CTA is WARP-SPECIALISED.
+//   * LW loader warps run ahead of the compute warps: they fetch the cells' records and the halo records a tile edge needs (row
+//     -1 for lane 0, plane -1 for warp 0) with cp.async.cg into an LS_NS-stage shared-memory ring and hand every stage over
+//     through a named barrier (loaders bar.arrive, compute warps bar.sync -- the same barrier that orders the compute warps' own
+//     step-to-step hand-off, so a step costs ONE barrier);
+//   * a storer warp drains the result ring to global memory (only records that changed), and publishes the tile's progress --
+//     fence + release store of "steps stored" every LS_CH steps: the thread that fences is the thread that stored;
+//   * a poller warp follows the progress words of the upwind tiles and posts them in shared memory for the loaders.
+// (The first version did all of this in the compute warps: 770 ns per step, the serial latency of ~220 instructions of one
+// warp; the same tiles and hand-offs, so the comparison is clean.)
+// Tiles hand off to their downwind y / z neighbours at STEP granularity: the consumer runs the same skew and only has to stay
+// 32 (y) or BZ (z) steps + the loaders' lead behind the producer's stored steps.  A whole sweep therefore costs about
+// nx + (ny + nz) cells of dependent steps plus one L2 round trip per tile hop, instead of one complete-tile latency per hop.
+// (sweep, tile) items are drawn by ticket in the order of their depth in the dependency DAG: every dependency of an item holds a
+// lower ticket, so some running CTA can always proceed -- no co-residency assumption.
+// Progress words: prog[tile] = (E0 + m) * 2048 + steps stored in sweep m, 2047 = sweep complete (wrap-safe comparisons).
 // Conditions for (m, T): T and its four y/z neighbours have completed sweep m-1 (own cells final; nobody still reads what T is
-// about to overwrite); the upwind y / z tiles are far enough into sweep m (checked before every prefetch).
-// The last sweep also writes phi and closestParticles[].
-#define LS_D 7         // prefetch distance in steps
-#define LS_R 8         // ring slots (> LS_D)
+// about to overwrite); the upwind y / z tiles are far enough into sweep m (checked by the loader of the halos).
+// phi and closestParticles[] are written from the final records by k_ls_finish.
+#define LS_CHK 4       // steps per loader chunk (one cp.async group, one hand-over barrier)
+#define LS_NSLOT 4     // chunk slots of the input ring
+#define LS_NS (LS_CHK * LS_NSLOT)   // stages of the input ring
+#define LS_NO 8        // slots of the result ring
+#define LS_LW 4        // loader warps
 #define LS_CH 8        // steps between progress publications
 #define LS_PROG_SHIFT 11
 #define LS_PROG_DONE 2047u
@@ -178,42 +188,57 @@ __device__ __forceinline__ float ls_d2(float cx, float cy, float cz, float4 q) {
 }
 
 #define LS_INF __int_as_float(0x7f800000)
+#ifndef LS_EXP
+#define LS_EXP 0    // timing experiments of the debug trace build only (wrong results): 1 = no exact fallback, 2 = helpers sleep while they wait, 4 = no arithmetic
+#endif
+#define LS_SPIN_PAUSE() do { if (LS_EXP & 2) __nanosleep(40); } while (0)
 #ifdef FS3_LS_TRACE
 __device__ unsigned long long* g_ls_trace;   // 4 timestamps per work item (debug side build only, tools/ls_trace.py)
 __device__ __forceinline__ unsigned long long ls_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-#define LS_MARK(k) do { if (tid == 0) g_ls_trace[(size_t)tk * 4 + (k)] = ls_now(); } while (0)
+#define LS_MARK(k) do { if (tid == 0) g_ls_trace[(size_t)tk * 8 + (k)] = ls_now(); } while (0)
 #else
 #define LS_MARK(k) do { } while (0)
 #endif
+#define LS_YH 32       // stages of the row -1 ring (16 bytes per compute warp and step: cheap to make deep)
+// keeps the compiler from moving shared-memory accesses across a counter hand-over (the counters themselves are volatile)
+#define LS_CFENCE() asm volatile("" ::: "memory")
 template <int BZ> struct LsSmem {
-	float4 own[LS_R][BZ][32];   // the cell's record before the sweep, slot = step % LS_R, written and read by the same lane
-	float4 zh[LS_R][32];        // plane -1 of the tile (warp 0's z candidates)
-	float4 yh[LS_R][BZ];        // row -1 of the tile (lane 0's y candidates)
-	float4 zb[2][BZ][32];       // results of the previous step, for the warp of the next plane
+	float4 own[LS_NS][BZ][32];   // the cells' records before the sweep, stage = step % LS_NS
+	float4 zh[LS_NS][32];        // plane -1 of the tile (warp 0's z candidates)
+	float4 yh[LS_YH][BZ];        // row -1 of the tile (lane 0's y candidates)
+	float4 out[LS_NO][BZ][32];   // results, slot = step % LS_NO: read by the warp of the next plane one step later and by the storer
+	uint32_t omask[LS_NO][BZ];   // lanes whose record changed (the storer writes only those)
+	// hand-over counters (volatile accesses): steps completed per compute warp, chunks loaded per loader, steps written out by the
+	// storer, steps the upwind tiles have stored in this sweep (posted by the poller), "a wait gave up: stop honouring waits"
+	int cnt[BZ], loaded[LS_LW], stored, ky, kz, abort;
 };
 __device__ __forceinline__ int ld_volatile_s32(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
 __device__ __forceinline__ void st_volatile_s32(int* p, int v) { *reinterpret_cast<volatile int*>(p) = v; }
 
-// BZ compute warps + ONE HELPER WARP.  The helper keeps every global-memory round trip of the hand-off protocol off the
-// compute warps' dependent chain: it polls the upwind tiles' progress words and posts what it saw in shared memory (s_ky,
-// s_kz), and it publishes this tile's own progress (fence + release store) whenever the step counter the compute warps leave
-// in shared memory (s_steps) has advanced by LS_CH.  The compute warps synchronise among themselves with a named barrier.
 template <int BZ>
-__global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __restrict__ rec, LsLayout L, GridDims d, float radius, const uint32_t* __restrict__ items,
+__global__ void __launch_bounds__((BZ + LS_LW + 2) * 32) k_ls_sweep_strips(float4* __restrict__ rec, LsLayout L, GridDims d, float radius, const uint32_t* __restrict__ items,
                                                                    uint32_t* prog, uint32_t* ticket, uint32_t nitems, int nty, int ntz, uint32_t E0,
                                                                    int* __restrict__ flags, unsigned sleep_max) {
 	extern __shared__ float4 ls_smem_raw[];
 	LsSmem<BZ>& sm = *reinterpret_cast<LsSmem<BZ>*>(ls_smem_raw);
 	__shared__ uint32_t s_ticket;
-	__shared__ int s_ky, s_kz, s_steps, s_abort, s_stop[2], s_dead;
-	const int tid = threadIdx.x, l = tid & 31, w = tid >> 5;
-	if (tid == 0) s_dead = 0;
+	__shared__ int s_dead;
+	int tid;
+	asm volatile("mov.u32 %0, %%tid.x;" : "=r"(tid));   // (volatile: keeps the compiler from re-reading the special register in the loops)
+	const int l = tid & 31, w = tid >> 5;
 	const float4 none = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
 	const bool fast_ok = radius == 1.0f;
 	const int Ttot = d.nx + 31 + BZ - 1;      // steps of a tile: the last lane of the last warp handles a = nx-1 at step Ttot-1
+	constexpr int NC = BZ * 32;
+	static_assert(BZ <= 32 && LS_LW <= 32, "counters are gathered by one warp");
+	// steps every compute warp has completed (one counter per lane, warp-wide minimum)
+	auto steps_done = [&]() -> int { return __reduce_min_sync(0xffffffffu, l < BZ ? ld_volatile_s32(&sm.cnt[l]) : 0x7fffffff); };
+	if (tid == 0) s_dead = 0;
 	for (;;) {
 		__syncthreads();   // the previous item's shared memory is no longer read
-		if (tid == 0) { s_ticket = s_dead ? nitems : atomicAdd(ticket, 1u); s_steps = 0; s_abort = 0; s_stop[0] = s_stop[1] = 0; }
+		if (tid == 0) { s_ticket = s_dead ? nitems : atomicAdd(ticket, 1u); sm.stored = 0; sm.abort = 0; }
+		if (tid < BZ) sm.cnt[tid] = 0;
+		if (tid < LS_LW) sm.loaded[tid] = 0;
 		__syncthreads();
 		const uint32_t tk = s_ticket;
 		if (tk >= nitems) break;
@@ -227,109 +252,48 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 		uint32_t* const myprog = prog + ((size_t)Ty + (size_t)nty * Tz);
 		const int uyT = Ty - dy, uzT = Tz - dz;                       // upwind tiles of this sweep
 		const bool has_uy = uyT >= 0 && uyT < nty, has_uz = uzT >= 0 && uzT < ntz;
-		const uint32_t* const prog_uy = prog + ((size_t)(has_uy ? uyT : Ty) + (size_t)nty * Tz);
-		const uint32_t* const prog_uz = prog + ((size_t)Ty + (size_t)nty * (has_uz ? uzT : Tz));
+		const int gx0 = dx > 0 ? 0 : d.nx - 1;                       // physical x of a = 0
 		// ---- this tile and its four neighbours have completed the previous sweep -------------------------------------------
 		bool ok = true;
 		if (tid < 5) {
 			const int qy = Ty + (tid == 1 ? -1 : tid == 2 ? 1 : 0), qz = Tz + (tid == 3 ? -1 : tid == 4 ? 1 : 0);
 			if (qy >= 0 && qy < nty && qz >= 0 && qz < ntz) (void)ls_wait(prog + ((size_t)qy + (size_t)nty * qz), base - 1u, flags, sleep_max, ok);
 		}
-		if (tid == 0) { s_ky = has_uy ? 0 : 0x7fffffff; s_kz = has_uz ? 0 : 0x7fffffff; }
+		if (tid == 0) { sm.ky = has_uy ? 0 : 0x7fffffff; sm.kz = has_uz ? 0 : 0x7fffffff; }
+		if (tid < NC && w < BZ - 1) sm.out[LS_NO - 1][w][l] = none;   // "results of step -1": what warp w+1 reads at step 0
 		if (!__syncthreads_and(ok)) break;
 		LS_MARK(1);
-		if (w == BZ) {
-			// ================================ helper warp =================================================================
-			if (l == 0) {
-				int pub = 0, ky = has_uy ? 0 : Ttot, kz = has_uz ? 0 : Ttot;
-				long long t_last = clock64();
-				for (;;) {
-					bool moved = false;
-					const int st = ld_volatile_s32(&s_steps);
-					if (st >= Ttot) break;
-					if (st >= pub + LS_CH) { __threadfence(); st_release_u32(myprog, base + (uint32_t)st); pub = st; moved = true; }
-					// RELAXED polls: an acquire load is LDG + CCTL.IVALL on this architecture, and an L1 invalidation every few
-					// hundred nanoseconds stalls the load/store unit the compute warps' shared-memory traffic goes through.  No
-					// invalidation is needed: the records this flag guards are fetched with cp.async.cg, which bypasses L1, after
-					// the compute warps' next barrier.
-					if (ky < Ttot) {
-						const int k = min((int)(ld_relaxed_u32(prog_uy) - base), Ttot);
-						if (k > ky) { ky = k; st_volatile_s32(&s_ky, k); moved = true; }
-					}
-					if (kz < Ttot) {
-						const int k = min((int)(ld_relaxed_u32(prog_uz) - base), Ttot);
-						if (k > kz) { kz = k; st_volatile_s32(&s_kz, k); moved = true; }
-					}
-					if (moved) t_last = clock64();
-					else {
-						__nanosleep(200);
-						if (clock64() - t_last > 4000000000LL || *reinterpret_cast<volatile int*>(flags + 1)) { flags[1] = 1; st_volatile_s32(&s_dead, 1); st_volatile_s32(&s_abort, 1); break; }
-					}
-				}
-				if (!ld_volatile_s32(&s_abort)) { __threadfence(); st_release_u32(myprog, base + LS_PROG_DONE); }   // sweep m of this tile is complete
-			}
-			continue;   // meets the compute warps at the barrier on top of the item loop
-		}
-		// ================================ compute warps ===================================================================
-		const bool lane_in = l < h && w < dep;
-		const int gy = y0 + (dy > 0 ? l : h - 1 - l), gz = z0 + (dz > 0 ? w : dep - 1 - w);
-		const float cyf = (float)gy, czf = (float)gz;
-		const int gx0 = dx > 0 ? 0 : d.nx - 1;                       // physical x of a = 0
-		// strips (diamond layout): own row r of strip (Ty, gz); halo row -1 = the last row in sweep order of the upwind y tile
-		// (lane 0 of every warp); halo plane -1 = the same row of the upwind z tile's last plane (every lane of warp 0)
-		const int r = gy & 31;
-		float4* const row = rec + ls_strip_base(L, Ty, lane_in ? gz : z0);
-		const int gzh = dz > 0 ? z0 - 1 : z0 + dep, rY = dy > 0 ? 31 : 0;
-		const float4* const rowY = rec + ls_strip_base(L, has_uy ? uyT : Ty, lane_in ? gz : z0);
-		const float4* const rowZ = rec + ls_strip_base(L, Ty, has_uz ? gzh : z0);
-		const bool doY = l == 0 && w < dep, doZ = w == 0 && l < h;
-		// prefetch of the records step tp needs; the caller has made sure the upwind tiles are far enough
-		auto prefetch = [&](int tp) {
-			const int slot = tp & (LS_R - 1);
-			const int a = tp - l - w;
-			if ((unsigned)a < (unsigned)d.nx && lane_in) cp_async16(&sm.own[slot][w][l], row + ls_off(gx0 + dx * a, r)); else sm.own[slot][w][l] = none;
-			if (doY) { const int ay = tp - w; if (has_uy && (unsigned)ay < (unsigned)d.nx) cp_async16(&sm.yh[slot][w], rowY + ls_off(gx0 + dx * ay, rY)); else sm.yh[slot][w] = none; }
-			if (doZ) { const int az = tp - l; if (has_uz && (unsigned)az < (unsigned)d.nx) cp_async16(&sm.zh[slot][l], rowZ + ls_off(gx0 + dx * az, r)); else sm.zh[slot][l] = none; }
-			cp_async_commit();
-		};
-		// thread 0: the upwind tiles have completed the steps that produce what step tp reads (row 31 / plane BZ-1 of the same
-		// column: 32 / BZ steps later in the producer's own skew); spins on what the helper posts
-		auto ensure = [&](int tp) -> bool {
-			const int needy = min(tp + 32, Ttot), needz = min(tp + BZ, Ttot);
-			while (ld_volatile_s32(&s_ky) < needy || ld_volatile_s32(&s_kz) < needz)
-				if (ld_volatile_s32(&s_abort)) return false;
-			// (no fence: the helper took the acquire; the records are fetched after the next barrier with cp.async.cg, i.e. from
-			// L2, where the producer's fence has made them visible before its progress word.  A CTA-scope fence here is a
-			// MEMBAR.SC that waits for the thread's own outstanding stores -- an L2 round trip in every step.)
-			return true;
-		};
-		int stop = 0;
-		if (tid == 0 && !ensure(LS_D)) s_stop[1] = 1;
-		asm volatile("bar.sync 1, %0;\n" ::"n"(BZ * 32) : "memory");
-		stop = ld_volatile_s32(&s_stop[1]);
-		LS_MARK(2);
-		if (!stop) {
-#pragma unroll 1
-			for (int tp = 0; tp < LS_D; tp++) prefetch(tp);
-			if (w < BZ - 1) sm.zb[1][w][l] = none;   // "previous step" of step 0
-			asm volatile("bar.sync 1, %0;\n" ::"n"(BZ * 32) : "memory");
+		if (w < BZ) {
+			// ================================ compute warps ===============================================================
+			// No CTA barrier in the step loop: warp w only needs warp w-1's result of the previous step, the loader of its rows and the
+			// loader of the halos, and a free result slot -- four counters in shared memory, and the ring slack absorbs jitter.
+			const bool lane_in = l < h && w < dep;
+			const int gy = y0 + (dy > 0 ? l : h - 1 - l), gz = z0 + (dz > 0 ? w : dep - 1 - w);
+			const float cyf = (float)gy, czf = (float)gz;
+			const int* const cnt_up = &sm.cnt[w > 0 ? w - 1 : 0];
+			const int* const cnt_down = &sm.cnt[w < BZ - 1 ? w + 1 : w];
 			float4 prev = none;
+			LS_MARK(2);
 #pragma unroll 1
 			for (int t = 0; t < Ttot; t++) {
-				if (t + LS_D < Ttot) prefetch(t + LS_D); else cp_async_commit();
-				cp_async_wait<LS_D>();
-				const int slot = t & (LS_R - 1);
+				if ((t & (LS_CHK - 1)) == 0) {
+					const int c = t / LS_CHK;   // the chunk's records and halos are in shared memory
+					while (ld_volatile_s32(&sm.loaded[w & (LS_LW - 1)]) <= c || ld_volatile_s32(&sm.loaded[0]) <= c) { }
+					LS_CFENCE();
+				}
+				// (read early, checked before the result is written: the latency hides behind the step)
+				int stored = ld_volatile_s32(&sm.stored);
+				int up = w > 0 ? ld_volatile_s32(cnt_up) : 0x7fffffff;
+				int down = w < BZ - 1 ? ld_volatile_s32(cnt_down) : 0x7fffffff;
+				const int slot = t & (LS_NS - 1);
 				const int a = t - l - w;
 				const bool act = lane_in && (unsigned)a < (unsigned)d.nx;
-				const int gx = gx0 + dx * a;
-				const float cxf = (float)gx;
+				const float cxf = (float)(gx0 + dx * a);
 				const float4 mine0 = sm.own[slot][w][l];
-				float4 Z;
-				if (w > 0) Z = sm.zb[(t + 1) & 1][w - 1][l]; else Z = sm.zh[slot][l];
 				float4 Y;
 				Y.x = __shfl_up_sync(0xffffffffu, prev.x, 1); Y.y = __shfl_up_sync(0xffffffffu, prev.y, 1);
 				Y.z = __shfl_up_sync(0xffffffffu, prev.z, 1); Y.w = __shfl_up_sync(0xffffffffu, prev.w, 1);
-				if (l == 0) Y = sm.yh[slot][w];
+				if (l == 0) Y = sm.yh[t & (LS_YH - 1)][w];
 				const float4 X = prev;
 				// clsInner on the upwind x-, y-, z-neighbour in that order (S3D.cpp:310-315 and siblings): a candidate with index <= 0
 				// is never propagated (:242); a cell without a record takes any candidate and strict `dist < phi` keeps the
@@ -337,6 +301,11 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 				const float m20 = __float_as_int(mine0.w) >= 0 ? ls_d2(cxf, cyf, czf, mine0) : LS_INF;
 				const float x2 = __float_as_int(X.w) > 0 ? ls_d2(cxf, cyf, czf, X) : LS_INF;
 				const float y2 = __float_as_int(Y.w) > 0 ? ls_d2(cxf, cyf, czf, Y) : LS_INF;
+				// warp w-1 has finished step t-1: its result is this warp's z candidate
+				while (up < t) up = ld_volatile_s32(cnt_up);
+				LS_CFENCE();
+				float4 Z;
+				if (w > 0) Z = sm.out[(t + LS_NO - 1) & (LS_NO - 1)][w - 1][l]; else Z = sm.zh[slot][l];
 				const float z2 = __float_as_int(Z.w) > 0 ? ls_d2(cxf, cyf, czf, Z) : LS_INF;
 				float4 mine = mine0;
 				float m2 = m20;
@@ -354,11 +323,13 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 		mine.x = take ? Q.x : mine.x; mine.y = take ? Q.y : mine.y; mine.z = take ? Q.z : mine.z; mine.w = take ? Q.w : mine.w; \
 		m2 = take ? q2 : m2; changed |= take;                                                                                \
 	}
+				if (!(LS_EXP & 4)) {
 				LS_FAST(X, x2)
 				LS_FAST(Y, y2)
 				LS_FAST(Z, z2)
+				}
 #undef LS_FAST
-				if (__any_sync(0xffffffffu, amb && act)) {
+				if (!(LS_EXP & 1) && __any_sync(0xffffffffu, amb && act)) {
 					mine = mine0; m2 = m20; changed = false;
 #define LS_TRY(Q, q2)                                                                                                         \
 	{                                                                                                                        \
@@ -372,23 +343,158 @@ __global__ void __launch_bounds__((BZ + 1) * 32) k_ls_sweep_strips(float4* __res
 #undef LS_TRY
 				}
 				if (!act) mine = none;
-				if (w < BZ - 1) sm.zb[t & 1][w][l] = mine;
-				if (act && changed) __stcg(row + ls_off(gx, r), mine);
-				prev = mine;
-				if (tid == 0) {
-					// steps < t are complete: every compute thread issued their stores before the last barrier (the helper's
-					// gpu-scope fence in front of its release store orders them, as in the usual barrier + fence + flag pattern)
-					st_volatile_s32(&s_steps, t);
-					if (t + 1 + LS_D < Ttot && !ensure(t + 1 + LS_D)) s_stop[t & 1] = 1;
+				const int oslot = t & (LS_NO - 1);
+				// the result slot is free: the storer (which walks the warps' skew, iteration i = step + warp) has written out this
+				// warp's step t - LS_NO, and warp w+1 has read it (in its step t - LS_NO + 1)
+				while ((stored < t - LS_NO + 1 + w || down < t - LS_NO + 2) && !ld_volatile_s32(&sm.abort)) {
+					stored = ld_volatile_s32(&sm.stored);
+					if (w < BZ - 1) down = ld_volatile_s32(cnt_down);
 				}
-				asm volatile("bar.sync 1, %0;\n" ::"n"(BZ * 32) : "memory");
-				if (ld_volatile_s32(&s_stop[t & 1])) { stop = 1; break; }
+				LS_CFENCE();
+				sm.out[oslot][w][l] = mine;
+				const unsigned cm = __ballot_sync(0xffffffffu, act && changed);
+				if (l == 0) sm.omask[oslot][w] = cm;
+				prev = mine;
+				LS_CFENCE();
+				__syncwarp();
+				if (l == 0) st_volatile_s32(&sm.cnt[w], t + 1);
 			}
-		}
-		LS_MARK(3);
-		if (tid == 0) {
-			if (stop) { st_volatile_s32(&s_dead, 1); st_volatile_s32(&s_abort, 1); }
-			st_volatile_s32(&s_steps, stop ? 0x7fffffff : Ttot);
+			LS_MARK(3);
+		} else if (w < BZ + LS_LW) {
+			// ================================ loader warps =================================================================
+			// loader j fetches the records of compute warps j, j + LS_LW, ...; loader 0 also row -1 (lanes 0..BZ-1, one per compute
+			// warp) and plane -1 (all lanes), which depend on the upwind tiles' progress
+			const int j = w - BZ;
+			const bool row_in = l < h;
+			const int r = (y0 + (dy > 0 ? l : h - 1 - l)) & 31;
+			const int gzh = dz > 0 ? z0 - 1 : z0 + dep, rY = dy > 0 ? 31 : 0;
+			const float4* const stripZ = rec + ls_strip_base(L, Ty, has_uz ? gzh : z0);
+			// lane k < BZ of loader 0: row -1 of plane k
+			const int gzk = z0 + (dz > 0 ? l : dep - 1 - l);
+			const float4* const stripY = rec + ls_strip_base(L, has_uy ? uyT : Ty, (l < dep) ? gzk : z0);
+			int seen = 0;   // steps every compute warp has completed, as last read
+			const int nch = (Ttot + LS_CHK - 1) / LS_CHK;
+			// u, v of the diamond layout for column a = 0 of this lane's row; a column step moves both by dx
+			const int u0 = gx0 + r, v0 = gx0 - r + 31;
+#pragma unroll 1
+			for (int c = 0; c < nch + 2; c++) {
+				if (c < nch) {
+					// the chunk slot was last used by chunk c - LS_NSLOT: the warps this loader serves have completed its steps (loader 0:
+					// that includes warp 0, the reader of plane -1; the deep row -1 ring only needs EVERY warp within LS_YH steps)
+					while (seen < LS_CHK * (c - LS_NSLOT + 1)) {
+						LS_SPIN_PAUSE();
+						seen = 0x7fffffff;
+#pragma unroll
+						for (int cw = j; cw < BZ; cw += LS_LW) seen = min(seen, ld_volatile_s32(&sm.cnt[cw]));
+					}
+					if (j == 0) { int all = steps_done(); while (all < LS_CHK * (c + 1) - LS_YH) all = steps_done(); }
+					LS_CFENCE();
+					const int tp0 = c * LS_CHK;
+					if (j == 0) {
+						// the upwind tiles have STORED the steps that produce what the chunk's last step reads: row 31 / plane BZ-1 of
+						// the same column, 32 / BZ steps later in the producer's own skew
+						const int needy = min(tp0 + LS_CHK - 1 + 32, Ttot), needz = min(tp0 + LS_CHK - 1 + BZ, Ttot);
+						while ((ld_volatile_s32(&sm.ky) < needy || ld_volatile_s32(&sm.kz) < needz) && !ld_volatile_s32(&sm.abort)) { LS_SPIN_PAUSE(); }
+#pragma unroll
+						for (int k = 0; k < LS_CHK; k++) {
+							const int tp = tp0 + k, slot = tp & (LS_NS - 1);
+							const int az = tp - l;
+							if (has_uz && row_in && (unsigned)az < (unsigned)d.nx) cp_async16(&sm.zh[slot][l], stripZ + ls_off_uv(u0 + dx * az, v0 + dx * az)); else sm.zh[slot][l] = none;
+							if (l < BZ) {
+								const int ay = tp - l;   // compute warp l handles column tp - l in its lane 0
+								if (has_uy && l < dep && (unsigned)ay < (unsigned)d.nx) cp_async16(&sm.yh[tp & (LS_YH - 1)][l], stripY + ls_off(gx0 + dx * ay, rY)); else sm.yh[tp & (LS_YH - 1)][l] = none;
+							}
+						}
+					}
+#pragma unroll
+					for (int cw = j; cw < BZ; cw += LS_LW) {
+						const int gz = z0 + (dz > 0 ? cw : dep - 1 - cw);
+						const float4* const strip = rec + ls_strip_base(L, Ty, cw < dep ? gz : z0);
+						const bool pl_in = row_in && cw < dep;
+#pragma unroll
+						for (int k = 0; k < LS_CHK; k++) {
+							const int tp = tp0 + k, slot = tp & (LS_NS - 1);
+							const int a = tp - l - cw;
+							if (pl_in && (unsigned)a < (unsigned)d.nx) cp_async16(&sm.own[slot][cw][l], strip + ls_off_uv(u0 + dx * a, v0 + dx * a));
+							else sm.own[slot][cw][l] = none;
+						}
+					}
+				}
+				cp_async_commit();
+				cp_async_wait<2>();
+				// chunk c - 2 (records and none fills of every lane) is in shared memory
+				LS_CFENCE();
+				__syncwarp();
+				if (l == 0 && c >= 2) st_volatile_s32(&sm.loaded[j], c - 1);
+			}
+		} else if (w == BZ + LS_LW) {
+			// ================================ storer warp ==================================================================
+			// lane l writes the changed records of row l for every plane, and the warp publishes "steps stored"
+			const int r = (y0 + (dy > 0 ? l : h - 1 - l)) & 31;
+			const int u0 = gx0 + r, v0 = gx0 - r + 31;
+			// The storer walks the compute warps' skew: iteration i writes step i - cw of warp cw, which that warp completes about
+			// when warp 0 completes step i -- so no warp is held back by the ring for the sake of a slower one.
+			int pub = 0;
+#pragma unroll 1
+			for (int i = 0; i < Ttot + BZ - 1; i++) {
+				// warp cw has finished step i - cw (lanes 0..BZ-1 look at one counter each)
+				for (;;) {
+					const int c = l < BZ ? ld_volatile_s32(&sm.cnt[l]) : 0x7fffffff;
+					if (__all_sync(0xffffffffu, l >= BZ || c > min(i - l, Ttot - 1))) break;
+					LS_SPIN_PAUSE();
+				}
+				LS_CFENCE();
+#pragma unroll
+				for (int cw = 0; cw < BZ; cw++) {
+					const int ts = i - cw;
+					if ((unsigned)ts < (unsigned)Ttot) {
+						const unsigned cm = sm.omask[ts & (LS_NO - 1)][cw];
+						if ((cm >> l) & 1u) {
+							const int a = ts - l - cw;
+							const int gz = z0 + (dz > 0 ? cw : dep - 1 - cw);
+							__stcg(rec + ls_strip_base(L, Ty, gz) + ls_off_uv(u0 + dx * a, v0 + dx * a), sm.out[ts & (LS_NO - 1)][cw][l]);
+						}
+					}
+				}
+				LS_CFENCE();
+				__syncwarp();
+				if (l == 0) {
+					st_volatile_s32(&sm.stored, i + 1);
+					const int done = i + 1 - (BZ - 1);   // steps of which EVERY warp's records are written out
+					if (done >= pub + LS_CH && done < Ttot) { __threadfence(); st_release_u32(myprog, base + (uint32_t)done); pub = done; }
+				}
+			}
+			__syncwarp();
+			if (l == 0) { __threadfence(); st_release_u32(myprog, base + LS_PROG_DONE); }   // sweep m of this tile is complete
+		} else {
+			// ================================ poller warp ==================================================================
+			if (l == 0) {
+				const uint32_t* const prog_uy = prog + ((size_t)(has_uy ? uyT : Ty) + (size_t)nty * Tz);
+				const uint32_t* const prog_uz = prog + ((size_t)Ty + (size_t)nty * (has_uz ? uzT : Tz));
+				int ky = has_uy ? 0 : Ttot, kz = has_uz ? 0 : Ttot;
+				long long t_last = clock64();
+				// RELAXED polls: an acquire load is LDG + CCTL.IVALL on this architecture (an L1 invalidation per poll), and none
+				// is needed -- the records these words guard are fetched with cp.async.cg, which bypasses L1, after they were posted
+				while (ky < Ttot || kz < Ttot) {
+					bool moved = false;
+					if (ky < Ttot) {
+						const int k = min((int)(ld_relaxed_u32(prog_uy) - base), Ttot);
+						if (k > ky) { ky = k; st_volatile_s32(&sm.ky, k); moved = true; }
+					}
+					if (kz < Ttot) {
+						const int k = min((int)(ld_relaxed_u32(prog_uz) - base), Ttot);
+						if (k > kz) { kz = k; st_volatile_s32(&sm.kz, k); moved = true; }
+					}
+					if (moved) t_last = clock64();
+					else {
+						__nanosleep(200);
+						if (clock64() - t_last > 4000000000LL || *reinterpret_cast<volatile int*>(flags + 1)) {
+							flags[1] = 1; st_volatile_s32(&s_dead, 1); st_volatile_s32(&sm.abort, 1);   // waits are no longer honoured: the item runs out
+							break;
+						}
+					}
+				}
+			}
 		}
 	}
 }
@@ -427,11 +533,11 @@ int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st) {
 	const LsLayout L = ls_layout(s->nx, s->ny);
 #ifdef FS3_LS_TRACE
 	static unsigned long long* trace_dev = nullptr;
-	const size_t trace_n = (size_t)8 * s->ls_ntiles * 4;
+	const size_t trace_n = (size_t)8 * s->ls_ntiles * 8;
 	if (!trace_dev) { FS3_CUDA(cudaMalloc((void**)&trace_dev, trace_n * 8)); FS3_CUDA(cudaMemcpyToSymbol(g_ls_trace, &trace_dev, sizeof(trace_dev))); }
 	FS3_CUDA(cudaMemsetAsync(trace_dev, 0, trace_n * 8, st));
 #endif
-	k_ls_sweep_strips<LS_BZ><<<s->ls_blocks, (LS_BZ + 1) * 32, sizeof(LsSmem<LS_BZ>), st>>>(
+	k_ls_sweep_strips<LS_BZ><<<s->ls_blocks, (LS_BZ + LS_LW + 2) * 32, sizeof(LsSmem<LS_BZ>), st>>>(
 	    s->ls_rec, L, d, radius, s->ls_order, s->ls_done, s->ls_ticket, 8u * (uint32_t)s->ls_ntiles, nty, ntz, s->ls_epoch, s->dev_flags,
 	    (unsigned)s->ls_sleep_ns);
 	FS3_LAUNCH_CHECK();
@@ -532,7 +638,7 @@ int fs3i_levelset_init(fs3_sim* s) {
 	int per_sm = 0, sms = 0;
 	const size_t smem = sizeof(LsSmem<LS_BZ>);
 	FS3_CUDA(cudaFuncSetAttribute(k_ls_sweep_strips<LS_BZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ls_sweep_strips<LS_BZ>, (LS_BZ + 1) * 32, smem));
+	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ls_sweep_strips<LS_BZ>, (LS_BZ + LS_LW + 2) * 32, smem));
 	FS3_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
 	// Every tile of a sweep can be in flight at once (they follow each other at hand-off distance), so the grid holds up to one
 	// CTA per tile; the ticket scheme needs no co-residency, any count is valid.

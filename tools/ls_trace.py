@@ -8,7 +8,8 @@ from fluidsimulation_b200 import build, sim as simmod  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 BZ = int(sys.argv[2]) if len(sys.argv) > 2 else 8
-lib = build.build(extra_flags=["-DFS3_LS_TRACE", "-DLS_BZ=%d" % BZ], suffix="_trace%d" % BZ)
+EXP = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+lib = build.build(extra_flags=["-DFS3_LS_TRACE", "-DLS_BZ=%d" % BZ, "-DLS_EXP=%d" % EXP], suffix="_trace%d_%d" % (BZ, EXP))
 simmod.LIB_PATH = lib
 s = simmod.FluidSim3(n, n, n, float(n))
 s.Simulate(0.01)
@@ -17,13 +18,15 @@ s.advect(); s.bin(); s.levelset(); s.sync()
 nty, ntz = (n + 31) // 32, (n + BZ - 1) // BZ
 nt = nty * ntz
 raw = np.fromfile("/tmp/ls_trace.bin", np.uint8)
-tr = raw[:8 * nt * 4 * 8].view(np.uint64).reshape(-1, 4).astype(np.int64)
-ordr = raw[8 * nt * 4 * 8:].view(np.uint32)
+tr = raw[:8 * nt * 8 * 8].view(np.uint64).reshape(-1, 8).astype(np.int64)
+acc = tr[:, 4:8].copy()
+tr = tr[:, :4]
+ordr = raw[8 * nt * 8 * 8:].view(np.uint32)
 m = (ordr >> 27).astype(int); ty = ((ordr >> 9) & 511).astype(int); tz = ((ordr >> 18) & 511).astype(int)
 t0 = tr[:, 0].min()
 tr = (tr - t0) / 1e3     # us
 Ttot = n + 31 + BZ - 1
-print("BZ", BZ)
+print("BZ", BZ, "EXP", EXP)
 print("items %d, span %.1f us; steps per item %d" % (tr.shape[0], tr[:, 3].max(), Ttot))
 run = tr[:, 3] - tr[:, 2]
 print("step loop: mean %.2f us per item = %.1f ns per step (min %.1f, max %.1f ns)" % (run.mean(), 1e3 * run.mean() / Ttot, 1e3 * run.min() / Ttot, 1e3 * run.max() / Ttot))
