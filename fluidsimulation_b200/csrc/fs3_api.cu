@@ -152,8 +152,7 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	CA(s->cell_fill, s->nH * 4);
 	s->scan_block_cap = (s->nH + 1) / 4096 + 2;
 	CA(s->scan_block, s->scan_block_cap * 8 + 16);   // 64-bit tile states of the look-back scan + its ticket
-	s->ls_rec_elems = fs3i_levelset_rec_elems(nx, ny, nz);
-	CA(s->ls_rec, s->ls_rec_elems * sizeof(float4)); CA(s->closest, s->nC * 4);
+	CA(s->ls_rec, s->nC * sizeof(float4)); CA(s->closest, s->nC * 4);
 	for (int k = 0; k < 3; k++) { CA(s->cdv[k], nmax * 4); CA(s->orderv[k], nmax * 4); CA(s->exmask[k], nmax); }
 	s->bucket_cap = nx + ny + nz + 8;
 	CA(s->bucket, 3 * (3 * (size_t)s->bucket_cap + 2) * 4);

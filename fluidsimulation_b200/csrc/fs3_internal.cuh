@@ -57,9 +57,7 @@ struct fs3_sim {
 	size_t scan_block_cap;
 
 	// level set
-	float4* ls_rec;          // per cell: closest particle (n*X, n*Y, n*Z, bits(id)); id<0 = none.  Default level set: DIAMOND layout
-	                         // (levelset.cu, LsLayout); levelset_mode 1: natural cell order in the same buffer
-	size_t ls_rec_elems;     // records allocated (the diamond layout is padded)
+	float4* ls_rec;          // per cell: closest particle (n*X, n*Y, n*Z, bits(id)); id<0 = none
 	int* closest;            // per cell creation id (exported)
 	bool closest_valid;
 	// persistent dataflow sweep: tiles in wavefront order, per-tile completion epochs, ticket counter
@@ -291,8 +289,6 @@ int fs3i_flip_combine(fs3_sim* s, float alpha);                             // o
 int fs3i_g2p(fs3_sim* s, float alpha);
 int fs3i_alloc_pressure(fs3_sim* s);
 int fs3i_levelset_init(fs3_sim* s);
-size_t fs3i_levelset_rec_elems(int nx, int ny, int nz);                      // records of the (padded) diamond layout
-size_t fs3i_levelset_plane_elems(int nx, int ny);                            // ... per z plane
 int fs3i_staging(fs3_sim* s, size_t bytes);
 int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs);
 int fs3i_extrap_fill(fs3_sim* s, int slot, float* grid, int xs, int ys, int zs);

@@ -22,42 +22,13 @@ __device__ __forceinline__ float ls_dist(float cx, float cy, float cz, float4 q,
 	return __fsub_rn(sqrtf(s), radius);
 }
 
-// ---- DIAMOND layout of the per-cell records -----------------------------------------------------------------------------
-// A sweep step of one warp touches 32 cells on a diagonal of an (x, 32 rows) strip: x + r = const when the sweep runs the same
-// way in x and y, x - r = const when it does not.  In natural order those are 32 different cache lines per load or store, and
-// the load/store unit serialises them (measured: the whole sweep was bound by that).  A layout that makes one family of
-// diagonals contiguous scatters the other, so the strip is cut into DIAMONDS instead: with u = x + r, v = x - r + 31, a 512-byte
-// block holds the 32 cells of one 8 x 8 square in (u, v) (u + v is always odd, so half the square's points are cells).  Either
-// kind of diagonal then crosses 8 blocks and uses 4 consecutive-in-time cells of each: 8 lines per warp instruction for every
-// sweep direction, and every fetched sector is used.  u >> 3 and v >> 3 differ by at most 4, so a strip is (S + 7) / 8 block
-// columns of 9 blocks, S = nx + 31 (1.27x the natural size at nx = 256).  Strips are ordered (z, y / 32): z planes stay contiguous.
-struct LsLayout {
-	int nty, ub;        // strips per plane, block columns per strip
-	uint32_t strip;     // records per strip
-};
-static inline LsLayout ls_layout(int nx, int ny) {
-	LsLayout L;
-	L.nty = (ny + 31) / 32; L.ub = (nx + 31 + 7) / 8; L.strip = (uint32_t)L.ub * 9u * 32u;
-	return L;
-}
-size_t fs3i_levelset_plane_elems(int nx, int ny) { const LsLayout L = ls_layout(nx, ny); return (size_t)L.nty * L.strip; }
-size_t fs3i_levelset_rec_elems(int nx, int ny, int nz) {
-	const size_t diamond = fs3i_levelset_plane_elems(nx, ny) * (size_t)nz, natural = (size_t)nx * ny * nz;
-	return diamond > natural ? diamond : natural;
-}
-__device__ __forceinline__ uint32_t ls_off_uv(int u, int v) {   // block (U, V) at U * 9 + (V - U + 4) = 8 U + V + 4
-	return (uint32_t)((((u & ~7) + (v >> 3) + 4) << 5) + ((((u & 7) << 3) + (v & 7)) >> 1));
-}
-__device__ __forceinline__ uint32_t ls_off(int x, int r) { return ls_off_uv(x + r, x - r + 31); }   // offset of cell (x, row r) inside its strip
-__device__ __forceinline__ size_t ls_strip_base(const LsLayout& L, int ty, int z) { return ((size_t)z * L.nty + ty) * (size_t)L.strip; }
-
 // Seed (S3D.cpp:281-300): minimum kernel distance over the particles of the cell (its 8 half-cells); the
 // reference's strict `phi > k` in index order keeps the lowest index on ties.
 // A cell's particles are four runs (FS3_FOR_CELL_RANGES) of about two particles each.  The eight run bounds and then the first
 // two particles of every run are fetched before anything is compared (8 independent loads in flight per thread instead of
 // one dependent load per loop iteration); longer runs finish in a tail loop.  min by (k, id) does not depend on the order.
 __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos, const uint32_t* __restrict__ start, GridDims d, float radius,
-                                                 float4* __restrict__ rec, LsLayout L, size_t c0, size_t c1) {
+                                                 float4* __restrict__ rec, size_t c0, size_t c1) {
 	size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (c >= c1) return;
 	int x = (int)(c % d.nx), y = (int)((c / d.nx) % d.ny), z = (int)(c / ((size_t)d.nx * d.ny));
@@ -91,95 +62,75 @@ __global__ void __launch_bounds__(256) k_ls_seed(const float4* __restrict__ pos,
 #pragma unroll
 	for (int hr = 0; hr < 4; hr++)
 		for (uint32_t t = B[hr] + 2; t < E[hr]; t++) consider(__ldg(pos + t));
-	rec[ls_strip_base(L, y >> 5, z) + ls_off(x, y & 31)] = best;
+	rec[c] = best;
 }
 
-// phi and closestParticles[] from the records the last sweep left.  Cells never reached keep their previous phi, as in the
-// reference where m_Phi is only written together with closestParticles (S3D.cpp:248-251,296-299).
-__global__ void __launch_bounds__(256) k_ls_finish(const float4* __restrict__ rec, LsLayout L, GridDims d, float radius, float* __restrict__ phi,
-                                                   int* __restrict__ closest, size_t c0, size_t c1) {
-	size_t c = c0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (c >= c1) return;
-	int x = (int)(c % d.nx), y = (int)((c / d.nx) % d.ny), z = (int)(c / ((size_t)d.nx * d.ny));
-	const float4 q = __ldcg(rec + ls_strip_base(L, y >> 5, z) + ls_off(x, y & 31));
-	const int id = __float_as_int(q.w);
-	closest[c] = id;
-	if (id >= 0) phi[c] = ls_dist((float)x, (float)y, (float)z, q, radius);
-}
-
-// ------------------------------------------------------------------------------------------------------------------------
-// The 8 Gauss-Seidel sweeps (S3D.cpp:306-416), EXACTLY, as a pipeline of skewed warp strips.
-//
-// In the sweep with direction signs (dx,dy,dz) cell (a,b,c) -- sweep coordinates, 0 = most upwind -- reads the final values of
-// (a-1,b,c), (a,b-1,c), (a,b,c-1) in that order; any schedule that respects this partial order reproduces the reference bit for
-// bit.  The schedule here: a TILE is all of x times 32 rows (y) times BZ planes (z); BZ COMPUTE WARPS work on it in lock step,
-// lane l of warp w handling cell  a = t - l - w  of row l, plane w  at step t.  Then
-//   * the x candidate is the lane's own result of the previous step (a register),
-//   * the y candidate is lane l-1's result of the previous step (one warp shuffle),
-//   * the z candidate is warp w-1's result of the previous step (the shared-memory ring the results leave through),
-// and a step's dependent chain holds no global memory access and no address arithmetic: the CTA is WARP-SPECIALISED.
-//   * LW loader warps run ahead of the compute warps: they fetch the cells' records and the halo records a tile edge needs (row
-//     -1 for lane 0, plane -1 for warp 0) with cp.async.cg into an LS_NS-stage shared-memory ring and hand every stage over
-//     through a named barrier (loaders bar.arrive, compute warps bar.sync -- the same barrier that orders the compute warps' own
-//     step-to-step hand-off, so a step costs ONE barrier);
-//   * a storer warp drains the result ring to global memory (only records that changed), and publishes the tile's progress --
-//     fence + release store of "steps stored" every LS_CH steps: the thread that fences is the thread that stored;
-//   * a poller warp follows the progress words of the upwind tiles and posts them in shared memory for the loaders.
-// (The first version did all of this in the compute warps: 770 ns per step, the serial latency of ~220 instructions of one
-// warp; the same tiles and hand-offs, so the comparison is clean.)
-// Tiles hand off to their downwind y / z neighbours at STEP granularity: the consumer runs the same skew and only has to stay
-// 32 (y) or BZ (z) steps + the loaders' lead behind the producer's stored steps.  A whole sweep therefore costs about
-// nx + (ny + nz) cells of dependent steps plus one L2 round trip per tile hop, instead of one complete-tile latency per hop.
-// (sweep, tile) items are drawn by ticket in the order of their depth in the dependency DAG: every dependency of an item holds a
-// lower ticket, so some running CTA can always proceed -- no co-residency assumption.
-// Progress words: prog[tile] = (E0 + m) * 2048 + steps stored in sweep m, 2047 = sweep complete (wrap-safe comparisons).
-// Conditions for (m, T): T and its four y/z neighbours have completed sweep m-1 (own cells final; nobody still reads what T is
-// about to overwrite); the upwind y / z tiles are far enough into sweep m (checked by the loader of the halos).
-// phi and closestParticles[] are written from the final records by k_ls_finish.
-#define LS_CHK 4       // steps per loader chunk (one cp.async group, one hand-over barrier)
-#define LS_NSLOT 4     // chunk slots of the input ring
-#define LS_NS (LS_CHK * LS_NSLOT)   // stages of the input ring
-#define LS_NO 8        // slots of the result ring
-#define LS_LW 4        // loader warps
-#define LS_CH 8        // steps between progress publications
-#define LS_PROG_SHIFT 11
-#define LS_PROG_DONE 2047u
+// All 8 sweeps in ONE persistent launch, scheduled as a dataflow over 16x16x8 tiles, ONE 128-THREAD CTA PER TILE.
+// Tiles are a fixed partition of physical space.  A work item is (sweep m, tile); the host orders all
+// 8*ntiles items by their earliest possible start level in the dependency DAG (fs3i_levelset_init), and
+// CTAs draw items through a ticket counter.  A CTA that holds an item waits (polling per-tile
+// completion epochs in L2) until
+//   * the tile itself and its 6 face neighbours have completed sweep m-1 (RAW on its own cells, WAR on
+//     the halo cells its neighbours read in sweep m-1), and
+//   * its 3 upwind neighbours have completed sweep m (RAW on the halo),
+// all of which hold lower tickets, so some running CTA can always make progress (no co-residency
+// assumption, no grid-wide barrier), and consecutive sweeps pipeline behind each other as far as the
+// DAG allows.  The sweep is bound by its critical path: 8 n/tx + 4 n/ty + 2 n/tz tile hand-offs (x flips
+// between every pair of sweeps, y every second, z once), each costing a few L2 round trips (poll, halo
+// load, store, release) plus the tile's own tx+ty+tz-2 cell hyperplanes at one shared-memory round trip
+// each.  16x16x8 halves the number of hand-offs of a warp-sized 8x8x4 tile (256 vs 512 at 256^3) while a
+// hyperplane step still costs one barrier.  The tile and its three upwind halo faces sit in shared memory
+// in SWEEP space (index 0 = most upwind) so that one code path serves all 8 directions; 128 threads = the
+// 16x8 x-lines of the tile, thread (b,c) marching along a with hyperplane index s = a+b+c.  Candidates are
+// first compared by squared distance (sqrt and "- radius" are monotonic, so a candidate that is not
+// closer in d^2 can never win the reference's `dist < phi` test); the full reference expression decides
+// the rest.  Records move with cp.async.cg / st.cg (L2 only: L1 is not coherent across SMs).  The last
+// sweep also writes phi and closestParticles[].
+#define LS_TX 16
+#define LS_TY 16
+#define LS_TZ 8
+#define LS_PX (LS_TX + 2)   // x pitch 18 (even): on a hyperplane a+b+c=s the 8 lanes of a quarter warp (consecutive b) hit 8 different 16-byte bank groups
+#define LS_PY (LS_TY + 1)
+#define LS_PZ (LS_TZ + 1)
+#define LS_STEPS (LS_TX + LS_TY + LS_TZ - 2)
+#define LS_LINES (LS_TY * LS_TZ)   // threads that march
+#define LS_THREADS 256             // all of them load, run the quiet-tile test and write phi
+#define LS_CELLS (LS_PX * LS_PY * LS_PZ)
+#define LS_SMEM_BYTES (LS_CELLS * (sizeof(float4) + sizeof(float)))
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
 	unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
 	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
 	uint32_t v;
 	asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
 	return v;
 }
 __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) { asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory"); }
+
 __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
 	uint32_t v;
 	asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
 	return v;
 }
-// Waits until *f has reached `need` (wrap-safe) and returns the value seen; polls with relaxed loads and a capped back-off, then
-// takes the acquire.  ok = false: gave up (another CTA aborted, or ~2 s without progress: never hang the GPU).
-__device__ __forceinline__ uint32_t ls_wait(const uint32_t* f, uint32_t need, int* flags, unsigned sleep_max, bool& ok) {
-	uint32_t v = ld_acquire_u32(f);
-	if ((int32_t)(v - need) >= 0) return v;
+// Polls with relaxed loads and a capped exponential back-off, then takes the acquire once the epoch is there.
+// false = gave up (another CTA aborted, or ~2 s without progress: never hang the GPU)
+__device__ __forceinline__ bool ls_wait(const uint32_t* f, uint32_t need, int* flags, unsigned sleep_max) {
+	if ((int32_t)(ld_acquire_u32(f) - need) >= 0) return true;
 	long long t0 = clock64();
 	unsigned ns = 32;
 	for (unsigned it = 1;; it++) {
-		v = ld_relaxed_u32(f);
-		if ((int32_t)(v - need) >= 0) break;
+		if ((int32_t)(ld_relaxed_u32(f) - need) >= 0) break;
 		__nanosleep(ns);
 		ns = min(ns * 2, sleep_max);
 		if ((it & 255u) == 0) {
-			if (*reinterpret_cast<volatile int*>(flags + 1)) { ok = false; return v; }
-			if (clock64() - t0 > 4000000000LL) { flags[1] = 1; ok = false; return v; }
+			if (*reinterpret_cast<volatile int*>(flags + 1)) return false;
+			if (clock64() - t0 > 4000000000LL) { flags[1] = 1; return false; }
 		}
 	}
-	return ld_acquire_u32(f);
+	return (int32_t)(ld_acquire_u32(f) - need) >= 0;
 }
 
 __device__ __forceinline__ float ls_d2(float cx, float cy, float cz, float4 q) {
@@ -187,149 +138,173 @@ __device__ __forceinline__ float ls_d2(float cx, float cy, float cz, float4 q) {
 	return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));   // ptDistance's radicand, S3D.cpp:234-236
 }
 
-#define LS_INF __int_as_float(0x7f800000)
-#ifndef LS_EXP
-#define LS_EXP 0    // timing experiments of the debug trace build only (wrong results): 1 = no exact fallback, 2 = helpers sleep while they wait, 4 = no arithmetic
-#endif
-#define LS_SPIN_PAUSE() do { if (LS_EXP & 2) __nanosleep(40); } while (0)
 #ifdef FS3_LS_TRACE
-__device__ unsigned long long* g_ls_trace;   // 4 timestamps per work item (debug side build only, tools/ls_trace.py)
+__device__ unsigned long long* g_ls_trace;   // 8 timestamps per work item (debug builds only, tools/ls_trace.py)
 __device__ __forceinline__ unsigned long long ls_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
-#define LS_MARK(k) do { if (tid == 0) g_ls_trace[(size_t)tk * 8 + (k)] = ls_now(); } while (0)
+#define LS_MARK(k) do { if (threadIdx.x == 0) g_ls_trace[(size_t)t * 8 + (k)] = ls_now(); } while (0)
 #else
 #define LS_MARK(k) do { } while (0)
 #endif
-#define LS_YH 32       // stages of the row -1 ring (16 bytes per compute warp and step: cheap to make deep)
-// keeps the compiler from moving shared-memory accesses across a counter hand-over (the counters themselves are volatile)
-#define LS_CFENCE() asm volatile("" ::: "memory")
-template <int BZ> struct LsSmem {
-	float4 own[LS_NS][BZ][32];   // the cells' records before the sweep, stage = step % LS_NS
-	float4 zh[LS_NS][32];        // plane -1 of the tile (warp 0's z candidates)
-	float4 yh[LS_YH][BZ];        // row -1 of the tile (lane 0's y candidates)
-	float4 out[LS_NO][BZ][32];   // results, slot = step % LS_NO: read by the warp of the next plane one step later and by the storer
-	uint32_t omask[LS_NO][BZ];   // lanes whose record changed (the storer writes only those)
-	// hand-over counters (volatile accesses): steps completed per compute warp, chunks loaded per loader, steps written out by the
-	// storer, steps the upwind tiles have stored in this sweep (posted by the poller), "a wait gave up: stop honouring waits"
-	int cnt[BZ], loaded[LS_LW], stored, ky, kz, abort;
-};
-__device__ __forceinline__ int ld_volatile_s32(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
-__device__ __forceinline__ void st_volatile_s32(int* p, int v) { *reinterpret_cast<volatile int*>(p) = v; }
 
-template <int BZ>
-__global__ void __launch_bounds__((BZ + LS_LW + 2) * 32) k_ls_sweep_strips(float4* __restrict__ rec, LsLayout L, GridDims d, float radius, const uint32_t* __restrict__ items,
-                                                                   uint32_t* prog, uint32_t* ticket, uint32_t nitems, int nty, int ntz, uint32_t E0,
-                                                                   int* __restrict__ flags, unsigned sleep_max) {
-	extern __shared__ float4 ls_smem_raw[];
-	LsSmem<BZ>& sm = *reinterpret_cast<LsSmem<BZ>*>(ls_smem_raw);
+#define LS_INF __int_as_float(0x7f800000)
+__global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __restrict__ rec, GridDims d, float radius,
+                                                                   const uint32_t* __restrict__ items, uint32_t* done, uint32_t* ticket,
+                                                                   uint32_t nitems, int ntx, int nty, int ntz, uint32_t epoch0,
+                                                                   int* __restrict__ flags, float* __restrict__ phi, int* __restrict__ closest, unsigned sleep_max) {
+	extern __shared__ float4 ls_smem[];
 	__shared__ uint32_t s_ticket;
-	__shared__ int s_dead;
-	int tid;
-	asm volatile("mov.u32 %0, %%tid.x;" : "=r"(tid));   // (volatile: keeps the compiler from re-reading the special register in the loops)
-	const int l = tid & 31, w = tid >> 5;
+	__shared__ unsigned s_planes[2];
+	float4* const sm = ls_smem;
+	float* const m2s = reinterpret_cast<float*>(ls_smem + LS_CELLS);   // squared distance of the cell to its current record
+	const int tid = threadIdx.x;
+#define SMI(a, b, c) (((a) + 1) + LS_PX * (((b) + 1) + LS_PY * ((c) + 1)))
 	const float4 none = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-	const bool fast_ok = radius == 1.0f;
-	const int Ttot = d.nx + 31 + BZ - 1;      // steps of a tile: the last lane of the last warp handles a = nx-1 at step Ttot-1
-	constexpr int NC = BZ * 32;
-	static_assert(BZ <= 32 && LS_LW <= 32, "counters are gathered by one warp");
-	// steps every compute warp has completed (one counter per lane, warp-wide minimum)
-	auto steps_done = [&]() -> int { return __reduce_min_sync(0xffffffffu, l < BZ ? ld_volatile_s32(&sm.cnt[l]) : 0x7fffffff); };
-	if (tid == 0) s_dead = 0;
+	const size_t sY = (size_t)d.nx, sZ = (size_t)d.nx * d.ny;
 	for (;;) {
 		__syncthreads();   // the previous item's shared memory is no longer read
-		if (tid == 0) { s_ticket = s_dead ? nitems : atomicAdd(ticket, 1u); sm.stored = 0; sm.abort = 0; }
-		if (tid < BZ) sm.cnt[tid] = 0;
-		if (tid < LS_LW) sm.loaded[tid] = 0;
+		if (tid == 0) s_ticket = atomicAdd(ticket, 1u);
 		__syncthreads();
-		const uint32_t tk = s_ticket;
-		if (tk >= nitems) break;
+		const uint32_t t = s_ticket;
+		if (t >= nitems) break;
 		LS_MARK(0);
-		const uint32_t it = __ldg(items + tk);
-		const int m = (int)(it >> 27), Ty = (int)((it >> 9) & 511u), Tz = (int)((it >> 18) & 511u);
+		const uint32_t it = __ldg(items + t);
+		const int m = (int)(it >> 27), Tx = (int)(it & 511u), Ty = (int)((it >> 9) & 511u), Tz = (int)((it >> 18) & 511u);
 		const int dx = (m & 1) ? -1 : 1, dy = (m & 2) ? -1 : 1, dz = (m & 4) ? -1 : 1;   // sweep order of S3D.cpp:306-416
-		const uint32_t base = (E0 + (uint32_t)m) << LS_PROG_SHIFT;
-		const int y0 = Ty * 32, z0 = Tz * BZ;
-		const int h = min(32, d.ny - y0), dep = min(BZ, d.nz - z0);
-		uint32_t* const myprog = prog + ((size_t)Ty + (size_t)nty * Tz);
-		const int uyT = Ty - dy, uzT = Tz - dz;                       // upwind tiles of this sweep
-		const bool has_uy = uyT >= 0 && uyT < nty, has_uz = uzT >= 0 && uzT < ntz;
-		const int gx0 = dx > 0 ? 0 : d.nx - 1;                       // physical x of a = 0
-		// ---- this tile and its four neighbours have completed the previous sweep -------------------------------------------
+		const uint32_t E = epoch0 + (uint32_t)m + 1u;
+		const int x0 = Tx * LS_TX, y0 = Ty * LS_TY, z0 = Tz * LS_TZ;
+		const int wx = min(LS_TX, d.nx - x0), wy = min(LS_TY, d.ny - y0), wz = min(LS_TZ, d.nz - z0);
+		uint32_t* const mydone = done + ((size_t)Tx + (size_t)ntx * ((size_t)Ty + (size_t)nty * Tz));
+		// ---- own cells are final once this tile has completed sweep m-1: start their copy first ----------
 		bool ok = true;
-		if (tid < 5) {
-			const int qy = Ty + (tid == 1 ? -1 : tid == 2 ? 1 : 0), qz = Tz + (tid == 3 ? -1 : tid == 4 ? 1 : 0);
-			if (qy >= 0 && qy < nty && qz >= 0 && qz < ntz) (void)ls_wait(prog + ((size_t)qy + (size_t)nty * qz), base - 1u, flags, sleep_max, ok);
-		}
-		if (tid == 0) { sm.ky = has_uy ? 0 : 0x7fffffff; sm.kz = has_uz ? 0 : 0x7fffffff; }
-		if (tid < NC && w < BZ - 1) sm.out[LS_NO - 1][w][l] = none;   // "results of step -1": what warp w+1 reads at step 0
+		if (tid == 0) ok = ls_wait(mydone, E - 1u, flags, sleep_max);
 		if (!__syncthreads_and(ok)) break;
 		LS_MARK(1);
-		if (w < BZ) {
-			// ================================ compute warps ===============================================================
-			// No CTA barrier in the step loop: warp w only needs warp w-1's result of the previous step, the loader of its rows and the
-			// loader of the halos, and a free result slot -- four counters in shared memory, and the ring slack absorbs jitter.
-			const bool lane_in = l < h && w < dep;
-			const int gy = y0 + (dy > 0 ? l : h - 1 - l), gz = z0 + (dz > 0 ? w : dep - 1 - w);
+#pragma unroll
+		for (int i = 0; i < LS_TX * LS_TY * LS_TZ / LS_THREADS; i++) {
+			const int e = tid + LS_THREADS * i, px = e % LS_TX, py = (e / LS_TX) % LS_TY, pz = e / (LS_TX * LS_TY);
+			const int a = (px < wx && dx < 0) ? wx - 1 - px : px, b = (py < wy && dy < 0) ? wy - 1 - py : py, c = (pz < wz && dz < 0) ? wz - 1 - pz : pz;
+			if (px < wx && py < wy && pz < wz) cp_async16(sm + SMI(a, b, c), rec + ((size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)(z0 + pz)));
+			else sm[SMI(a, b, c)] = none;
+		}
+		// ---- the six neighbours: upwind ones must have finished THIS sweep, the others the previous one ---
+		if (tid >= 1 && tid <= 6) {
+			const int ax = (tid - 1) >> 1, sgn = (tid & 1) ? -1 : 1;   // threads 1,2: x-,x+   3,4: y-,y+   5,6: z-,z+
+			const int qx = Tx + (ax == 0 ? sgn : 0), qy = Ty + (ax == 1 ? sgn : 0), qz = Tz + (ax == 2 ? sgn : 0);
+			const int dir = ax == 0 ? dx : (ax == 1 ? dy : dz);
+			if (qx >= 0 && qx < ntx && qy >= 0 && qy < nty && qz >= 0 && qz < ntz)
+				ok = ls_wait(done + ((size_t)qx + (size_t)ntx * ((size_t)qy + (size_t)nty * qz)), sgn == -dir ? E : E - 1u, flags, sleep_max);
+		}
+		if (!__syncthreads_and(ok)) break;
+		LS_MARK(2);
+		// ---- three upwind halo faces (sweep coordinate -1 on one axis) ---------------------------------------
+		{
+			// x face: (b, c) = 16 x 8 cells, threads 0..127
+			const int b = tid % LS_TY, c = (tid / LS_TY) % LS_TZ;
+			const int qx = dx > 0 ? x0 - 1 : x0 + wx, qy = y0 + (dy > 0 ? b : wy - 1 - b), qz = z0 + (dz > 0 ? c : wz - 1 - c);
+			if (tid >= LS_LINES) {}
+			else if (b < wy && c < wz && qx >= 0 && qx < d.nx) cp_async16(sm + SMI(-1, b, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
+			else sm[SMI(-1, b, c)] = none;
+		}
+		{
+			// y face: (a, c) = 16 x 8 cells, threads 128..255
+			const int a = tid % LS_TX, c = (tid / LS_TX) % LS_TZ;
+			const int qx = x0 + (dx > 0 ? a : wx - 1 - a), qy = dy > 0 ? y0 - 1 : y0 + wy, qz = z0 + (dz > 0 ? c : wz - 1 - c);
+			if (tid < LS_LINES) {}
+			else if (a < wx && c < wz && qy >= 0 && qy < d.ny) cp_async16(sm + SMI(a, -1, c), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
+			else sm[SMI(a, -1, c)] = none;
+		}
+#pragma unroll
+		for (int i = 0; i < LS_TX * LS_TY / LS_THREADS; i++) {
+			// z face: (a, b) = 16 x 16 cells, one per thread
+			const int e = tid + LS_THREADS * i, a = e % LS_TX, b = e / LS_TX;
+			const int qx = x0 + (dx > 0 ? a : wx - 1 - a), qy = y0 + (dy > 0 ? b : wy - 1 - b), qz = dz > 0 ? z0 - 1 : z0 + wz;
+			if (a < wx && b < wy && qz >= 0 && qz < d.nz) cp_async16(sm + SMI(a, b, -1), rec + ((size_t)qx + sY * (size_t)qy + sZ * (size_t)qz));
+			else sm[SMI(a, b, -1)] = none;
+		}
+		cp_async_wait_all();
+		__syncthreads();
+		LS_MARK(3);
+		// ---- squared distance of every own cell to its current record, and the quiet-tile test ---------------------------
+		// Fully parallel, x fastest (conflict-free): if no cell would accept any of its three upwind candidates as
+		// they stand BEFORE the sweep (q2 < m2 is necessary for acceptance: sqrt and "- radius" are monotonic),
+		// then by induction along the sweep order the Gauss-Seidel pass changes nothing and the march is skipped.
+		// The hyperplanes a+b+c that hold such a cell are collected in a bit mask: the march only runs a hyperplane that
+		// holds one, or that follows a hyperplane in which a record changed.
+		unsigned long long planes = 0;
+		if (tid == 0) { s_planes[0] = 0u; s_planes[1] = 0u; }
+		__syncthreads();
+		{
+			const int a = tid % LS_TX, b = tid / LS_TX;   // 16 x 16 threads, looping over c
+			const float cxf = (float)(dx > 0 ? x0 + a : x0 + wx - 1 - a), cyf = (float)(dy > 0 ? y0 + b : y0 + wy - 1 - b);
+#pragma unroll
+			for (int c = 0; c < LS_TZ; c++) {
+				const float czf = (float)(dz > 0 ? z0 + c : z0 + wz - 1 - c);
+				const int i = SMI(a, b, c);
+				const float4 cur = sm[i], X = sm[i - 1], Y = sm[i - LS_PX], Z = sm[i - LS_PX * LS_PY];
+				// no record: infinitely far (any valid candidate wins); the same record in a neighbour has the same d^2 and never wins
+				const float m2 = __float_as_int(cur.w) >= 0 ? ls_d2(cxf, cyf, czf, cur) : LS_INF;
+				m2s[i] = m2;
+				const bool wX = __float_as_int(X.w) > 0 && ls_d2(cxf, cyf, czf, X) < m2;
+				const bool wY = __float_as_int(Y.w) > 0 && ls_d2(cxf, cyf, czf, Y) < m2;
+				const bool wZ = __float_as_int(Z.w) > 0 && ls_d2(cxf, cyf, czf, Z) < m2;
+				if (a < wx && b < wy && c < wz && (wX || wY || wZ)) planes |= 1ull << (a + b + c);
+			}
+			const unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)planes), hi = __reduce_or_sync(0xffffffffu, (unsigned)(planes >> 32));
+			if ((tid & 31) == 0) { if (lo) atomicOr(&s_planes[0], lo); if (hi) atomicOr(&s_planes[1], hi); }
+		}
+		__syncthreads();   // (also orders the m2s stores before the march)
+		planes = (unsigned long long)s_planes[0] | ((unsigned long long)s_planes[1] << 32);
+		const bool quiet = planes == 0;
+#ifdef FS3_LS_TRACE
+		if (tid == 0 && quiet) g_ls_trace[(size_t)t * 8 + 6] = 1;
+#endif
+		// ---- the cell hyperplanes; thread = line (b, c), marching along a ------------------------------------
+		// clsInner on the upwind x-, y-, z-neighbour in that order (S3D.cpp:310-315 and siblings): index <= 0 is never
+		// propagated (:242); a cell without a record takes any candidate and strict `dist < phi` keeps the incumbent
+		// (:248) -- with "no record" and "no candidate" at distance +inf both are one comparison.
+		// Fast path, branch-free, in squared distances: q2 >= m2 can never win (sqrt and "- radius" are monotonic)
+		// and q2 < m2 by more than 2^-21 relative with sqrt(m2) >= 0.5 always wins (the sqrt values differ by >= 1 ulp
+		// and sqrt(m2) - 1 is exact).  A comparison that falls between the two marks the step ambiguous and the
+		// whole warp repeats it with the reference's full expression (warp-uniform branch, rare).
+		// Idle threads compute garbage on a clamped cell of their own line and store nothing; only the 128 line
+		// threads take part (named barrier 1).
+		if (!quiet && tid < LS_LINES) {
+			const int b = tid % LS_TY, c = tid / LS_TY;
+			const bool line_in = b < wy && c < wz;
+			const int gy = y0 + (dy > 0 ? b : wy - 1 - b), gz = z0 + (dz > 0 ? c : wz - 1 - c);
 			const float cyf = (float)gy, czf = (float)gz;
-			const int* const cnt_up = &sm.cnt[w > 0 ? w - 1 : 0];
-			const int* const cnt_down = &sm.cnt[w < BZ - 1 ? w + 1 : w];
-			float4 prev = none;
-			LS_MARK(2);
-#pragma unroll 1
-			for (int t = 0; t < Ttot; t++) {
-				if ((t & (LS_CHK - 1)) == 0) {
-					const int c = t / LS_CHK;   // the chunk's records and halos are in shared memory
-					while (ld_volatile_s32(&sm.loaded[w & (LS_LW - 1)]) <= c || ld_volatile_s32(&sm.loaded[0]) <= c) { }
-					LS_CFENCE();
-				}
-				// (read early, checked before the result is written: the latency hides behind the step)
-				int stored = ld_volatile_s32(&sm.stored);
-				int up = w > 0 ? ld_volatile_s32(cnt_up) : 0x7fffffff;
-				int down = w < BZ - 1 ? ld_volatile_s32(cnt_down) : 0x7fffffff;
-				const int slot = t & (LS_NS - 1);
-				const int a = t - l - w;
-				const bool act = lane_in && (unsigned)a < (unsigned)d.nx;
-				const float cxf = (float)(gx0 + dx * a);
-				const float4 mine0 = sm.own[slot][w][l];
-				float4 Y;
-				Y.x = __shfl_up_sync(0xffffffffu, prev.x, 1); Y.y = __shfl_up_sync(0xffffffffu, prev.y, 1);
-				Y.z = __shfl_up_sync(0xffffffffu, prev.z, 1); Y.w = __shfl_up_sync(0xffffffffu, prev.w, 1);
-				if (l == 0) Y = sm.yh[t & (LS_YH - 1)][w];
-				const float4 X = prev;
-				// clsInner on the upwind x-, y-, z-neighbour in that order (S3D.cpp:310-315 and siblings): a candidate with index <= 0
-				// is never propagated (:242); a cell without a record takes any candidate and strict `dist < phi` keeps the
-				// incumbent (:248) -- with "no record" and "no candidate" at distance +inf both are one comparison.
-				const float m20 = __float_as_int(mine0.w) >= 0 ? ls_d2(cxf, cyf, czf, mine0) : LS_INF;
+			const int li = SMI(0, b, c);
+			const int gx0 = dx > 0 ? x0 : x0 + wx - 1;
+			float4* const grow = rec + (sY * (size_t)gy + sZ * (size_t)gz);
+			uint32_t chg = 0;
+			const int nsteps = wx + wy + wz - 2;
+			for (int s = __ffsll((long long)planes) - 1; s < nsteps; s++) {
+				const int a = s - b - c;
+				const bool act = line_in && (unsigned)a < (unsigned)wx;
+				const int ac = min(max(a, 0), LS_TX - 1);
+				const float4* q = sm + li + ac;
+				const float4 mine0 = q[0], X = q[-1], Y = q[-LS_PX], Z = q[-LS_PX * LS_PY];
+				const float m20 = m2s[li + ac];
+				const float cxf = (float)(gx0 + dx * ac);
+				// a candidate with index <= 0 is never propagated (S3D.cpp:242): infinitely far
 				const float x2 = __float_as_int(X.w) > 0 ? ls_d2(cxf, cyf, czf, X) : LS_INF;
 				const float y2 = __float_as_int(Y.w) > 0 ? ls_d2(cxf, cyf, czf, Y) : LS_INF;
-				// warp w-1 has finished step t-1: its result is this warp's z candidate
-				while (up < t) up = ld_volatile_s32(cnt_up);
-				LS_CFENCE();
-				float4 Z;
-				if (w > 0) Z = sm.out[(t + LS_NO - 1) & (LS_NO - 1)][w - 1][l]; else Z = sm.zh[slot][l];
 				const float z2 = __float_as_int(Z.w) > 0 ? ls_d2(cxf, cyf, czf, Z) : LS_INF;
 				float4 mine = mine0;
 				float m2 = m20;
 				bool changed = false, amb = false;
-				// Fast path, branch-free, in squared distances (radius == 1 only): q2 >= m2 can never win (sqrt and "- radius" are
-				// monotonic); q2 < m2 by more than 2^-21 relative with sqrt(m2) >= 0.5 always wins (the sqrt values differ by
-				// >= 1 ulp and sqrt(m2) - 1 is exact); and below that -- both roots < 0.5, the common case inside the fluid --
-				// q2 < m2 - 2^-22 always wins (the roots then differ by > 2^-22 - 2^-25, and rounding root - 1 to the 2^-24 grid of
-				// (-1, -0.5] moves each side by at most 2^-25).  A comparison that falls between "never" and "always" marks the
-				// step ambiguous and the whole warp repeats it with the reference's full expression (warp-uniform branch, rare).
 #define LS_FAST(Q, q2)                                                                                                        \
 	{                                                                                                                        \
-		const bool take = q2 < (m2 >= 0.25f ? __fmul_rn(m2, 0.99999905f) : __fsub_rn(m2, 2.5e-7f)) && fast_ok;                \
+		const bool take = m2 >= 0.25f && q2 < __fmul_rn(m2, 0.99999905f);                                                    \
 		amb |= !take && q2 < m2;                                                                                             \
 		mine.x = take ? Q.x : mine.x; mine.y = take ? Q.y : mine.y; mine.z = take ? Q.z : mine.z; mine.w = take ? Q.w : mine.w; \
 		m2 = take ? q2 : m2; changed |= take;                                                                                \
 	}
-				if (!(LS_EXP & 4)) {
 				LS_FAST(X, x2)
 				LS_FAST(Y, y2)
 				LS_FAST(Z, z2)
-				}
 #undef LS_FAST
-				if (!(LS_EXP & 1) && __any_sync(0xffffffffu, amb && act)) {
+				if (__any_sync(0xffffffffu, amb && act)) {
 					mine = mine0; m2 = m20; changed = false;
 #define LS_TRY(Q, q2)                                                                                                         \
 	{                                                                                                                        \
@@ -342,161 +317,46 @@ __global__ void __launch_bounds__((BZ + LS_LW + 2) * 32) k_ls_sweep_strips(float
 					LS_TRY(Z, z2)
 #undef LS_TRY
 				}
-				if (!act) mine = none;
-				const int oslot = t & (LS_NO - 1);
-				// the result slot is free: the storer (which walks the warps' skew, iteration i = step + warp) has written out this
-				// warp's step t - LS_NO, and warp w+1 has read it (in its step t - LS_NO + 1)
-				while ((stored < t - LS_NO + 1 + w || down < t - LS_NO + 2) && !ld_volatile_s32(&sm.abort)) {
-					stored = ld_volatile_s32(&sm.stored);
-					if (w < BZ - 1) down = ld_volatile_s32(cnt_down);
-				}
-				LS_CFENCE();
-				sm.out[oslot][w][l] = mine;
-				const unsigned cm = __ballot_sync(0xffffffffu, act && changed);
-				if (l == 0) sm.omask[oslot][w] = cm;
-				prev = mine;
-				LS_CFENCE();
-				__syncwarp();
-				if (l == 0) st_volatile_s32(&sm.cnt[w], t + 1);
-			}
-			LS_MARK(3);
-		} else if (w < BZ + LS_LW) {
-			// ================================ loader warps =================================================================
-			// loader j fetches the records of compute warps j, j + LS_LW, ...; loader 0 also row -1 (lanes 0..BZ-1, one per compute
-			// warp) and plane -1 (all lanes), which depend on the upwind tiles' progress
-			const int j = w - BZ;
-			const bool row_in = l < h;
-			const int r = (y0 + (dy > 0 ? l : h - 1 - l)) & 31;
-			const int gzh = dz > 0 ? z0 - 1 : z0 + dep, rY = dy > 0 ? 31 : 0;
-			const float4* const stripZ = rec + ls_strip_base(L, Ty, has_uz ? gzh : z0);
-			// lane k < BZ of loader 0: row -1 of plane k
-			const int gzk = z0 + (dz > 0 ? l : dep - 1 - l);
-			const float4* const stripY = rec + ls_strip_base(L, has_uy ? uyT : Ty, (l < dep) ? gzk : z0);
-			int seen = 0;   // steps every compute warp has completed, as last read
-			const int nch = (Ttot + LS_CHK - 1) / LS_CHK;
-			// u, v of the diamond layout for column a = 0 of this lane's row; a column step moves both by dx
-			const int u0 = gx0 + r, v0 = gx0 - r + 31;
-#pragma unroll 1
-			for (int c = 0; c < nch + 2; c++) {
-				if (c < nch) {
-					// the chunk slot was last used by chunk c - LS_NSLOT: the warps this loader serves have completed its steps (loader 0:
-					// that includes warp 0, the reader of plane -1; the deep row -1 ring only needs EVERY warp within LS_YH steps)
-					while (seen < LS_CHK * (c - LS_NSLOT + 1)) {
-						LS_SPIN_PAUSE();
-						seen = 0x7fffffff;
-#pragma unroll
-						for (int cw = j; cw < BZ; cw += LS_LW) seen = min(seen, ld_volatile_s32(&sm.cnt[cw]));
-					}
-					if (j == 0) { int all = steps_done(); while (all < LS_CHK * (c + 1) - LS_YH) all = steps_done(); }
-					LS_CFENCE();
-					const int tp0 = c * LS_CHK;
-					if (j == 0) {
-						// the upwind tiles have STORED the steps that produce what the chunk's last step reads: row 31 / plane BZ-1 of
-						// the same column, 32 / BZ steps later in the producer's own skew
-						const int needy = min(tp0 + LS_CHK - 1 + 32, Ttot), needz = min(tp0 + LS_CHK - 1 + BZ, Ttot);
-						while ((ld_volatile_s32(&sm.ky) < needy || ld_volatile_s32(&sm.kz) < needz) && !ld_volatile_s32(&sm.abort)) { LS_SPIN_PAUSE(); }
-#pragma unroll
-						for (int k = 0; k < LS_CHK; k++) {
-							const int tp = tp0 + k, slot = tp & (LS_NS - 1);
-							const int az = tp - l;
-							if (has_uz && row_in && (unsigned)az < (unsigned)d.nx) cp_async16(&sm.zh[slot][l], stripZ + ls_off_uv(u0 + dx * az, v0 + dx * az)); else sm.zh[slot][l] = none;
-							if (l < BZ) {
-								const int ay = tp - l;   // compute warp l handles column tp - l in its lane 0
-								if (has_uy && l < dep && (unsigned)ay < (unsigned)d.nx) cp_async16(&sm.yh[tp & (LS_YH - 1)][l], stripY + ls_off(gx0 + dx * ay, rY)); else sm.yh[tp & (LS_YH - 1)][l] = none;
-							}
-						}
-					}
-#pragma unroll
-					for (int cw = j; cw < BZ; cw += LS_LW) {
-						const int gz = z0 + (dz > 0 ? cw : dep - 1 - cw);
-						const float4* const strip = rec + ls_strip_base(L, Ty, cw < dep ? gz : z0);
-						const bool pl_in = row_in && cw < dep;
-#pragma unroll
-						for (int k = 0; k < LS_CHK; k++) {
-							const int tp = tp0 + k, slot = tp & (LS_NS - 1);
-							const int a = tp - l - cw;
-							if (pl_in && (unsigned)a < (unsigned)d.nx) cp_async16(&sm.own[slot][cw][l], strip + ls_off_uv(u0 + dx * a, v0 + dx * a));
-							else sm.own[slot][cw][l] = none;
-						}
-					}
-				}
-				cp_async_commit();
-				cp_async_wait<2>();
-				// chunk c - 2 (records and none fills of every lane) is in shared memory
-				LS_CFENCE();
-				__syncwarp();
-				if (l == 0 && c >= 2) st_volatile_s32(&sm.loaded[j], c - 1);
-			}
-		} else if (w == BZ + LS_LW) {
-			// ================================ storer warp ==================================================================
-			// lane l writes the changed records of row l for every plane, and the warp publishes "steps stored"
-			const int r = (y0 + (dy > 0 ? l : h - 1 - l)) & 31;
-			const int u0 = gx0 + r, v0 = gx0 - r + 31;
-			// The storer walks the compute warps' skew: iteration i writes step i - cw of warp cw, which that warp completes about
-			// when warp 0 completes step i -- so no warp is held back by the ring for the sake of a slower one.
-			int pub = 0;
-#pragma unroll 1
-			for (int i = 0; i < Ttot + BZ - 1; i++) {
-				// warp cw has finished step i - cw (lanes 0..BZ-1 look at one counter each)
-				for (;;) {
-					const int c = l < BZ ? ld_volatile_s32(&sm.cnt[l]) : 0x7fffffff;
-					if (__all_sync(0xffffffffu, l >= BZ || c > min(i - l, Ttot - 1))) break;
-					LS_SPIN_PAUSE();
-				}
-				LS_CFENCE();
-#pragma unroll
-				for (int cw = 0; cw < BZ; cw++) {
-					const int ts = i - cw;
-					if ((unsigned)ts < (unsigned)Ttot) {
-						const unsigned cm = sm.omask[ts & (LS_NO - 1)][cw];
-						if ((cm >> l) & 1u) {
-							const int a = ts - l - cw;
-							const int gz = z0 + (dz > 0 ? cw : dep - 1 - cw);
-							__stcg(rec + ls_strip_base(L, Ty, gz) + ls_off_uv(u0 + dx * a, v0 + dx * a), sm.out[ts & (LS_NO - 1)][cw][l]);
-						}
-					}
-				}
-				LS_CFENCE();
-				__syncwarp();
-				if (l == 0) {
-					st_volatile_s32(&sm.stored, i + 1);
-					const int done = i + 1 - (BZ - 1);   // steps of which EVERY warp's records are written out
-					if (done >= pub + LS_CH && done < Ttot) { __threadfence(); st_release_u32(myprog, base + (uint32_t)done); pub = done; }
+				// global write-back is deferred past the loop: a store in flight would put an L2 round trip into every step
+				if (act && changed) { sm[li + a] = mine; m2s[li + a] = m2; chg |= 1u << a; }
+				// barrier among the 128 line threads + "did any record change in this hyperplane"
+				int any;
+				asm volatile("{\n .reg .pred p, q;\n setp.ne.u32 q, %1, 0;\n barrier.red.or.pred p, 1, %2, q;\n selp.u32 %0, 1, 0, p;\n}\n"
+				             : "=r"(any) : "r"((unsigned)(act && changed)), "n"(LS_LINES) : "memory");
+				if (!any) {
+					// nothing changed: the next hyperplane that can is the next one holding a candidate cell
+					const unsigned long long rest = s + 1 < 64 ? planes >> (s + 1) : 0ull;
+					if (!rest) break;
+					s += __ffsll((long long)rest) - 1;
 				}
 			}
-			__syncwarp();
-			if (l == 0) { __threadfence(); st_release_u32(myprog, base + LS_PROG_DONE); }   // sweep m of this tile is complete
-		} else {
-			// ================================ poller warp ==================================================================
-			if (l == 0) {
-				const uint32_t* const prog_uy = prog + ((size_t)(has_uy ? uyT : Ty) + (size_t)nty * Tz);
-				const uint32_t* const prog_uz = prog + ((size_t)Ty + (size_t)nty * (has_uz ? uzT : Tz));
-				int ky = has_uy ? 0 : Ttot, kz = has_uz ? 0 : Ttot;
-				long long t_last = clock64();
-				// RELAXED polls: an acquire load is LDG + CCTL.IVALL on this architecture (an L1 invalidation per poll), and none
-				// is needed -- the records these words guard are fetched with cp.async.cg, which bypasses L1, after they were posted
-				while (ky < Ttot || kz < Ttot) {
-					bool moved = false;
-					if (ky < Ttot) {
-						const int k = min((int)(ld_relaxed_u32(prog_uy) - base), Ttot);
-						if (k > ky) { ky = k; st_volatile_s32(&sm.ky, k); moved = true; }
-					}
-					if (kz < Ttot) {
-						const int k = min((int)(ld_relaxed_u32(prog_uz) - base), Ttot);
-						if (k > kz) { kz = k; st_volatile_s32(&sm.kz, k); moved = true; }
-					}
-					if (moved) t_last = clock64();
-					else {
-						__nanosleep(200);
-						if (clock64() - t_last > 4000000000LL || *reinterpret_cast<volatile int*>(flags + 1)) {
-							flags[1] = 1; st_volatile_s32(&s_dead, 1); st_volatile_s32(&sm.abort, 1);   // waits are no longer honoured: the item runs out
-							break;
-						}
-					}
+#pragma unroll
+			for (int a = 0; a < LS_TX; a++)
+				if ((chg >> a) & 1u) __stcg(grow + (gx0 + dx * a), sm[li + a]);
+		}
+		if (m == 7) {
+			// cells never reached keep their previous phi, as in the reference where m_Phi is only written
+			// together with closestParticles (S3D.cpp:248-251,296-299).  x fastest: coalesced stores.
+			__syncthreads();
+#pragma unroll
+			for (int i = 0; i < LS_TX * LS_TY * LS_TZ / LS_THREADS; i++) {
+				const int e = tid + LS_THREADS * i, px = e % LS_TX, py = (e / LS_TX) % LS_TY, pz = e / (LS_TX * LS_TY);
+				if (px < wx && py < wy && pz < wz) {
+					const int a = dx < 0 ? wx - 1 - px : px, b = dy < 0 ? wy - 1 - py : py, c = dz < 0 ? wz - 1 - pz : pz;
+					const int id = __float_as_int(sm[SMI(a, b, c)].w);
+					const size_t gi = (size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)(z0 + pz);
+					closest[gi] = id;
+					if (id >= 0) phi[gi] = __fsub_rn(sqrtf(m2s[SMI(a, b, c)]), radius);
 				}
 			}
 		}
+		// ---- publish: the CTA's stores, then the epoch (release is cumulative over the barrier) ------------
+		LS_MARK(4);
+		__syncthreads();
+		if (tid == 0) { __threadfence(); st_release_u32(mydone, E); }
+		LS_MARK(5);
 	}
+#undef SMI
 }
 
 // seed of the cells of this rank's slab (world == 1: all cells)
@@ -505,7 +365,7 @@ int fs3i_levelset_seed(fs3_sim* s, cudaStream_t st) {
 	if (!st) st = s->stream;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SEED], st);
 	const size_t plane = (size_t)s->nx * s->ny, c0 = plane * s->z0, c1 = plane * s->z1;
-	k_ls_seed<<<cdiv((long long)(c1 - c0), 256), 256, 0, st>>>(s->pos[s->cur], s->cell_start, d, s->prm.particle_radius, s->ls_rec, ls_layout(s->nx, s->ny), c0, c1);
+	k_ls_seed<<<cdiv((long long)(c1 - c0), 256), 256, 0, st>>>(s->pos[s->cur], s->cell_start, d, s->prm.particle_radius, s->ls_rec, c0, c1);
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
@@ -520,41 +380,35 @@ int fs3i_levelset(fs3_sim* s) {
 }
 
 // the 8 sweeps over the WHOLE grid (a sharded handle runs them replicated on the gathered seed records)
-#ifndef LS_BZ
-#define LS_BZ 8     // planes per tile = compute warps per CTA
-#endif
 int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st) {
 	GridDims d{s->nx, s->ny, s->nz};
 	float radius = s->prm.particle_radius;
 	if (!st) st = s->stream;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SWEEP], st);
-	const int nty = cdiv(d.ny, 32), ntz = cdiv(d.nz, LS_BZ);
+	int ntx = cdiv(d.nx, LS_TX), nty = cdiv(d.ny, LS_TY), ntz = cdiv(d.nz, LS_TZ);
 	FS3_CUDA(cudaMemsetAsync(s->ls_ticket, 0, sizeof(uint32_t), st));
-	const LsLayout L = ls_layout(s->nx, s->ny);
 #ifdef FS3_LS_TRACE
 	static unsigned long long* trace_dev = nullptr;
 	const size_t trace_n = (size_t)8 * s->ls_ntiles * 8;
 	if (!trace_dev) { FS3_CUDA(cudaMalloc((void**)&trace_dev, trace_n * 8)); FS3_CUDA(cudaMemcpyToSymbol(g_ls_trace, &trace_dev, sizeof(trace_dev))); }
 	FS3_CUDA(cudaMemsetAsync(trace_dev, 0, trace_n * 8, st));
 #endif
-	k_ls_sweep_strips<LS_BZ><<<s->ls_blocks, (LS_BZ + LS_LW + 2) * 32, sizeof(LsSmem<LS_BZ>), st>>>(
-	    s->ls_rec, L, d, radius, s->ls_order, s->ls_done, s->ls_ticket, 8u * (uint32_t)s->ls_ntiles, nty, ntz, s->ls_epoch, s->dev_flags,
-	    (unsigned)s->ls_sleep_ns);
+	k_ls_sweep_dataflow<<<s->ls_blocks, LS_THREADS, LS_SMEM_BYTES, st>>>(
+	    s->ls_rec, d, radius, s->ls_order, s->ls_done, s->ls_ticket, 8u * (uint32_t)s->ls_ntiles, ntx, nty, ntz, s->ls_epoch, s->dev_flags, s->phi,
+	    s->closest, (unsigned)s->ls_sleep_ns);
 	FS3_LAUNCH_CHECK();
-	k_ls_finish<<<cdiv((long long)s->nC, 256), 256, 0, st>>>(s->ls_rec, L, d, radius, s->phi, s->closest, 0, s->nC);
-	FS3_LAUNCH_CHECK();
+	s->ls_epoch += 8;
+	s->closest_valid = true;
 #ifdef FS3_LS_TRACE
-	{
+	if (const char* path = getenv("FS3_LS_TRACE_FILE")) {
 		std::vector<unsigned long long> h(trace_n);
 		std::vector<uint32_t> ord((size_t)8 * s->ls_ntiles);
 		FS3_CUDA(cudaStreamSynchronize(st));
 		FS3_CUDA(cudaMemcpy(h.data(), trace_dev, trace_n * 8, cudaMemcpyDeviceToHost));
 		FS3_CUDA(cudaMemcpy(ord.data(), s->ls_order, ord.size() * 4, cudaMemcpyDeviceToHost));
-		if (FILE* fp = fopen("/tmp/ls_trace.bin", "wb")) { fwrite(h.data(), 8, trace_n, fp); fwrite(ord.data(), 4, ord.size(), fp); fclose(fp); }
+		if (FILE* fp = fopen(path, "wb")) { fwrite(h.data(), 8, trace_n, fp); fwrite(ord.data(), 4, ord.size(), fp); fclose(fp); }
 	}
 #endif
-	s->ls_epoch += 8;
-	s->closest_valid = true;
 	return FS3_OK;
 }
 
@@ -583,42 +437,43 @@ int fs3i_levelset_join(fs3_sim* s) {
 	return FS3_OK;
 }
 
-// Work-item table, progress words and the persistent grid size (called once from fs3_create).
-// Items (sweep m, tile) are sorted by their level in the dependency DAG -- the earliest "time" at which the item could start
-// if every hand-off took one unit -- which is a topological order (every dependency has a strictly smaller level), so ticket
-// order is deadlock-free, and tiles of one wavefront hold neighbouring tickets, i.e. run at the same time.
-__global__ void k_fill_u32(uint32_t* p, size_t n, uint32_t v) {
-	size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (q < n) p[q] = v;
-}
+// Work-item table, completion epochs and the persistent grid size (called once from fs3_create).
+// Items (sweep m, tile) are sorted by their level in the dependency DAG -- the earliest "time" at which the
+// item could run if every item took one unit -- which is a topological order (every dependency has a
+// strictly smaller level), so ticket order is deadlock-free, and it lets sweep m+1 start behind sweep m as
+// soon as the DAG allows instead of after it.
 int fs3i_levelset_init(fs3_sim* s) {
-	const int nty = cdiv(s->ny, 32), ntz = cdiv(s->nz, LS_BZ);
-	if (nty > 511 || ntz > 511 || s->nx + 31 + LS_BZ >= (int)LS_PROG_DONE) { s->err = "grid too large for the level-set tile table"; return FS3_ERR_INVALID; }
-	const int nt = nty * ntz;
-	auto tid = [&](int y, int z) { return y + nty * z; };
+	const int ntx = cdiv(s->nx, LS_TX), nty = cdiv(s->ny, LS_TY), ntz = cdiv(s->nz, LS_TZ);
+	if (ntx > 511 || nty > 511 || ntz > 511) { s->err = "grid too large for the level-set tile table"; return FS3_ERR_INVALID; }
+	const int nt = ntx * nty * ntz;
+	auto tid = [&](int x, int y, int z) { return x + ntx * (y + nty * z); };
 	std::vector<int> prev(nt, -1), cur(nt, 0);
 	std::vector<std::pair<int, uint32_t>> items;
 	items.reserve((size_t)8 * nt);
 	int maxlevel = 0;
 	for (int m = 0; m < 8; m++) {
-		const int dy = (m & 2) ? -1 : 1, dz = (m & 4) ? -1 : 1;
+		const int dx = (m & 1) ? -1 : 1, dy = (m & 2) ? -1 : 1, dz = (m & 4) ? -1 : 1;
 		for (int kz = 0; kz < ntz; kz++)
-			for (int ky = 0; ky < nty; ky++) {   // sweep-space order: upwind neighbours are visited first
-				const int y = dy > 0 ? ky : nty - 1 - ky, z = dz > 0 ? kz : ntz - 1 - kz;
-				int L = 0;
-				if (ky > 0) L = std::max(L, cur[tid(y - dy, z)] + 1);
-				if (kz > 0) L = std::max(L, cur[tid(y, z - dz)] + 1);
-				if (m > 0) {
-					L = std::max(L, prev[tid(y, z)] + 1);
-					if (y > 0) L = std::max(L, prev[tid(y - 1, z)] + 1);
-					if (y < nty - 1) L = std::max(L, prev[tid(y + 1, z)] + 1);
-					if (z > 0) L = std::max(L, prev[tid(y, z - 1)] + 1);
-					if (z < ntz - 1) L = std::max(L, prev[tid(y, z + 1)] + 1);
+			for (int ky = 0; ky < nty; ky++)
+				for (int kx = 0; kx < ntx; kx++) {   // sweep-space order: upwind neighbours are visited first
+					const int x = dx > 0 ? kx : ntx - 1 - kx, y = dy > 0 ? ky : nty - 1 - ky, z = dz > 0 ? kz : ntz - 1 - kz;
+					int L = 0;
+					if (kx > 0) L = std::max(L, cur[tid(x - dx, y, z)] + 1);
+					if (ky > 0) L = std::max(L, cur[tid(x, y - dy, z)] + 1);
+					if (kz > 0) L = std::max(L, cur[tid(x, y, z - dz)] + 1);
+					if (m > 0) {
+						L = std::max(L, prev[tid(x, y, z)] + 1);
+						if (x > 0) L = std::max(L, prev[tid(x - 1, y, z)] + 1);
+						if (x < ntx - 1) L = std::max(L, prev[tid(x + 1, y, z)] + 1);
+						if (y > 0) L = std::max(L, prev[tid(x, y - 1, z)] + 1);
+						if (y < nty - 1) L = std::max(L, prev[tid(x, y + 1, z)] + 1);
+						if (z > 0) L = std::max(L, prev[tid(x, y, z - 1)] + 1);
+						if (z < ntz - 1) L = std::max(L, prev[tid(x, y, z + 1)] + 1);
+					}
+					cur[tid(x, y, z)] = L;
+					maxlevel = std::max(maxlevel, L);
+					items.emplace_back(L, (uint32_t)x | ((uint32_t)y << 9) | ((uint32_t)z << 18) | ((uint32_t)m << 27));
 				}
-				cur[tid(y, z)] = L;
-				maxlevel = std::max(maxlevel, L);
-				items.emplace_back(L, ((uint32_t)y << 9) | ((uint32_t)z << 18) | ((uint32_t)m << 27));
-			}
 		prev = cur;
 	}
 	std::stable_sort(items.begin(), items.end(), [](const std::pair<int, uint32_t>& a, const std::pair<int, uint32_t>& b) { return a.first < b.first; });
@@ -629,21 +484,31 @@ int fs3i_levelset_init(fs3_sim* s) {
 	if ((rc = fs3i_alloc(s, (void**)&s->ls_done, sizeof(uint32_t) * nt))) return rc;
 	if ((rc = fs3i_alloc(s, (void**)&s->ls_ticket, sizeof(uint32_t)))) return rc;
 	FS3_CUDA(cudaMemcpyAsync(s->ls_order, ord.data(), sizeof(uint32_t) * ord.size(), cudaMemcpyHostToDevice, s->stream));
-	// the first call's sweeps have global indices 8..15: every tile starts as "sweep 7 complete"
-	s->ls_epoch = 8;
-	k_fill_u32<<<cdiv(nt, 256), 256, 0, s->stream>>>(s->ls_done, (size_t)nt, (7u << LS_PROG_SHIFT) + LS_PROG_DONE); FS3_LAUNCH_CHECK();
+	FS3_CUDA(cudaMemsetAsync(s->ls_done, 0, sizeof(uint32_t) * nt, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	s->ls_ntiles = nt;
 	s->ls_levels = maxlevel + 1;
+	s->ls_epoch = 0;
 	int per_sm = 0, sms = 0;
-	const size_t smem = sizeof(LsSmem<LS_BZ>);
-	FS3_CUDA(cudaFuncSetAttribute(k_ls_sweep_strips<LS_BZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ls_sweep_strips<LS_BZ>, (LS_BZ + LS_LW + 2) * 32, smem));
+	const size_t smem = LS_SMEM_BYTES;
+	FS3_CUDA(cudaFuncSetAttribute(k_ls_sweep_dataflow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ls_sweep_dataflow, LS_THREADS, smem));
 	FS3_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
-	// Every tile of a sweep can be in flight at once (they follow each other at hand-off distance), so the grid holds up to one
-	// CTA per tile; the ticket scheme needs no co-residency, any count is valid.
+	// Resident CTAs beyond what the DAG can keep busy only add pollers.
+	const int occ = std::max(1, per_sm);
+	// The sweep is bound by its critical path, not by throughput.  Single GPU: one CTA per SM, because the sweeps run beside
+	// the P2G gather and the extrapolation (fs3_step) and should take as little from them as possible.  Sharded: the replicated
+	// sweeps run beside the slab's gather and the replicated extrapolation and must end with them; measured at 256^3 on 2 GPUs
+	// with 2 / 1.5 / 1.25 / 1 CTAs per SM: sweeps 3.85 / 4.14 / 4.58 / 5.34 ms, step 13.56 / 12.88 / 12.69 / 13.18 ms.  The
+	// sweeps' slack shrinks with the world size (the gather gets shorter, the sweeps do not) and is gone at 8 ranks -- there the
+	// extrapolation stage already ends with the join (sweeps 3.87 ms + the seed barrier = gather 1.57 + extrapolation 2.99) --
+	// so 1.25 per SM on 2 ranks (measured), 1.5 on 3-4 (by the same timeline: sweeps + barrier 4.4 ms against gather +
+	// extrapolation 5.2 ms at N = 4) and the measured 2 per SM above.
+	per_sm = std::min(occ, s->world == 1 ? 1 : 2);
 	s->ls_sleep_ns = 256;
-	const long long resident = (long long)std::max(1, std::min(per_sm, 2)) * sms;
-	s->ls_blocks = (int)std::max<long long>(1, std::min<long long>(resident, nt));
+	long long blocks = (long long)std::max(1, per_sm) * sms;
+	if (s->world > 1 && s->world <= 4 && occ >= 2) blocks = s->world == 2 ? (5LL * sms) / 4 : (3LL * sms) / 2;
+	// (the ticket scheme needs no co-residency: any grid size is valid)
+	s->ls_blocks = (int)std::min<long long>(blocks, 8LL * nt);
 	return FS3_OK;
 }

@@ -29,7 +29,7 @@ size_t fs3i_arena_bytes(int n, long long ptot, long long mig_cap, int world) {
 	t += 6 * up512(nF * 4) + up512(nC * 4);                                   // U V W oU oV oW phi
 	t += 2 * up512((nH + 1) * 4) + up512(nH * 4);                             // cell_count, cell_start, cell_fill
 	t += up512(((nH + 1) / 4096 + 2) * 8 + 16);                               // scan_block
-	t += up512(fs3i_levelset_rec_elems(n, n, n) * 16) + up512(nC * 4);        // ls_rec, closest
+	t += up512(nC * 16) + up512(nC * 4);                                      // ls_rec, closest
 	t += 6 * up512(nF * 4) + 3 * up512(nF);                                   // cdv, orderv, exmask
 	t += up512(3 * (3 * (3 * N + 8) + 2) * 4) + up512(16 * 2 * 4096) + 512;   // bucket, res, dev_flags
 	t += 4 * up512((size_t)ptot * 16) + 2 * up512((size_t)ptot * 4);          // pos, vel (x2), cellid, tmp_id
@@ -263,7 +263,7 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 	if (ph == 3) {          // neighbours are sorted: ghost layers; level-set seed of the slab, gathered on every rank (stream3)
 		if ((rc = fs3i_wait(s)) || (rc = fs3i_ghost_pull(s)) || (rc = fs3i_levelset_seed(s))) return rc;
 		cudaStream_t xs;
-		if ((rc = xfer_begin(s, &xs)) || (rc = push_planes(s, s->ls_rec, fs3i_levelset_plane_elems(s->nx, s->ny), sizeof(float4), s->z0, s->z1, xs))) return rc;
+		if ((rc = xfer_begin(s, &xs)) || (rc = push_planes(s, s->ls_rec, pC, sizeof(float4), s->z0, s->z1, xs))) return rc;
 		if ((rc = fs3i_signal(s, xs))) return rc;
 		// this rank's seed records have left before the sweeps (which update ls_rec in place) may start
 		if (!s->lockstep) { FS3_CUDA(cudaEventRecord(s->ev_xfer, s->stream3)); FS3_CUDA(cudaStreamWaitEvent(s->stream2, s->ev_xfer, 0)); }
