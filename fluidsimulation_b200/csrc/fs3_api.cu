@@ -47,10 +47,11 @@ int fs3i_staging(fs3_sim* s, size_t bytes) {
 }
 
 int fs3i_check_flags(fs3_sim* s) {
-	int h[4] = {0, 0, 0, 0};
-	FS3_CUDA(cudaMemcpyAsync(h, s->dev_flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+	int h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+	FS3_CUDA(cudaMemcpyAsync(h, s->dev_flags, 8 * sizeof(int), cudaMemcpyDeviceToHost, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
-	if (h[0] || h[1] || h[2] || h[3]) FS3_CUDA(cudaMemsetAsync(s->dev_flags, 0, 4 * sizeof(int), s->stream));
+	if (h[0] || h[1] || h[2] || h[3] || h[4]) FS3_CUDA(cudaMemsetAsync(s->dev_flags, 0, 8 * sizeof(int), s->stream));
+	if (h[4]) return fail(s, FS3_ERR_STATE, "a particle's Runge-Kutta stage left the velocity halo of its slab (flow faster than one slab per step); results invalid");
 	if (h[2]) return fail(s, FS3_ERR_STATE, "a cross-rank wait was not satisfied (peer rank missing, out of step, or timed out); results invalid");
 	if (h[3]) return fail(s, FS3_ERR_STATE, "a slab's particle, ghost-layer or migration capacity was exceeded; results invalid");
 	if (h[1]) return fail(s, FS3_ERR_STATE, "a device-side dependency wait timed out (level-set tile hand-off or extrapolation layer barrier); results invalid");
@@ -110,7 +111,7 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	s->sor_list_valid = false; s->sm_count = prop.multiProcessorCount; s->sor_per_sm = 0; s->persist_cap = -1;
 	s->alloc_precision = -1; s->res_cap = 4096; s->res_count = 0; s->stage_ptr = nullptr; s->stage_bytes = 0;
 	s->rank = rank; s->world = world; s->z0 = rank * (nz / world); s->z1 = s->z0 + nz / world; s->lockstep = lockstep;
-	s->bar_epoch = 0; s->sor_epoch = 0; s->sor_e0 = 0; s->n_ipc_opened = 0; s->poff = 0; s->gcap = 0; s->mig_cap = 0;
+	s->bar_epoch = 0; s->sor_epoch = 0; s->xfer_epoch = 0; s->sor_e0 = 0; s->n_ipc_opened = 0; s->poff = 0; s->gcap = 0; s->mig_cap = 0;
 	for (int k = 0; k < FS3_T_COUNT; k++) s->stage_ms[k] = 0.f;
 	const long long P = std::max(1LL, 8LL * (nz - 2) * (ny - 2) * (nx - 1 - nx / 2));
 	long long cap = P;
@@ -158,8 +159,8 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	CA(s->bucket, 3 * (3 * (size_t)s->bucket_cap + 2) * 4);
 	CA(s->ex_arrive, 4);
 	CA(s->res, sizeof(double) * 2 * s->res_cap);
-	CA(s->dev_flags, 4 * sizeof(int));
-	CK(cudaMemsetAsync(s->dev_flags, 0, 4 * sizeof(int), s->stream));
+	CA(s->dev_flags, 8 * sizeof(int));
+	CK(cudaMemsetAsync(s->dev_flags, 0, 8 * sizeof(int), s->stream));
 	if (world > 1) {
 		for (int k = 0; k < 2; k++) { CA(s->pos[k], (size_t)ptot * sizeof(float4)); CA(s->vel[k], (size_t)ptot * sizeof(float4)); }
 		CA(s->cellid, (size_t)ptot * 4); CA(s->tmp_id, (size_t)ptot * 4);
@@ -487,6 +488,7 @@ int fs3_set_local_particles(fs3_sim* s, const fs3_particle* host, const int* ids
 }
 int fs3_get_velocity(fs3_sim* s, float* U, float* V, float* W) {
 	ENTER(s);
+	{ int rc = fs3i_field_wait(s); if (rc) return rc; }
 	if (U) FS3_CUDA(cudaMemcpyAsync(U, s->U, s->nU * 4, cudaMemcpyDeviceToHost, s->stream));
 	if (V) FS3_CUDA(cudaMemcpyAsync(V, s->V, s->nV * 4, cudaMemcpyDeviceToHost, s->stream));
 	if (W) FS3_CUDA(cudaMemcpyAsync(W, s->W, s->nW * 4, cudaMemcpyDeviceToHost, s->stream));

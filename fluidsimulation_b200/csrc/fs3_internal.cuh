@@ -8,6 +8,11 @@
 
 #define FS3_INF_CD 1000000000  // ExtrapolateValues' "inf" (S3D.cpp:632)
 #define FS3_MAX_WORLD 16
+// words of a rank's flag block `bar`: [0,16) barrier epochs by rank; [16,18) SOR epochs of the lower / upper neighbour;
+// [32,48) "velocity halo pushed" epochs by rank; [48,64) "whole slab pushed" epochs by rank
+#define FS3_BAR_WORDS (4 * FS3_MAX_WORLD)
+#define FS3_BAR_XNEAR (2 * FS3_MAX_WORLD)
+#define FS3_BAR_XALL (3 * FS3_MAX_WORLD)
 
 // ---- red-black ("colour-split") storage of the pressure system ---------------------------------
 // Cells with (x+y+z)&1 == c live in colour array c at  xh + hp*(y + ny*(z+1)),  xh = x>>1.
@@ -120,6 +125,7 @@ struct fs3_sim {
 	uint32_t* h_pin;           // pinned host scratch (count matrix)
 	uint32_t* bar;             // [r] barrier epoch written by rank r; [FS3_MAX_WORLD+0/1] SOR epoch of the lower/upper neighbour
 	uint32_t bar_epoch, sor_epoch;
+	uint32_t xfer_epoch;       // steps whose projected field this rank has pushed (identical on all ranks)
 	uint32_t* sor_done;        // block counter of the fused end-of-sweep signal
 	int sor_halves;            // half sweeps of the current fs3i_sor_loop call
 	bool ls_seed_forked;       // the seed of the current step ran on stream2 in front of the sweeps
@@ -133,7 +139,8 @@ struct fs3_sim {
 	fs3_particle* binned;      // particles as 24-byte records, cell by cell
 	size_t phi_blur_bytes, bin_offsets_bytes, binned_bytes;
 
-	int* dev_flags;            // [0] particle outside, [1] level-set wait timeout, [2] cross-rank wait failed, [3] shard capacity
+	int* dev_flags;            // [0] particle outside, [1] level-set wait timeout, [2] cross-rank wait failed, [3] shard capacity,
+	                           // [4] Advect left the velocity halo of a sharded handle (8 words)
 	void* stage_ptr;           // device staging for AoS / hook transfers at the boundary
 	size_t stage_bytes;
 	cudaEvent_t ev[FS3_T_COUNT + 2];
@@ -290,7 +297,9 @@ int fs3i_g2p(fs3_sim* s, float alpha);
 int fs3i_alloc_pressure(fs3_sim* s);
 int fs3i_levelset_init(fs3_sim* s);
 int fs3i_staging(fs3_sim* s, size_t bytes);
-int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs);
+int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs, size_t off = 0);
+#define FS3_EX_DEPTH 8                                                        // sharded handles: planes of P2G halo and layers of extrapolation (p2g.cu)
+void fs3i_ex_window(const fs3_sim* s, int ax, int depth, int* w0, int* w1);  // planes [w0, w1) of face grid ax this rank extrapolates
 int fs3i_extrap_fill(fs3_sim* s, int slot, float* grid, int xs, int ys, int zs);
 int fs3i_alloc(fs3_sim* s, void** p, size_t bytes);                         // arena (sharded) or cudaMalloc
 void fs3i_free(fs3_sim* s, void* p);
@@ -322,7 +331,11 @@ int fs3i_extrapolate_all(fs3_sim* s);
 int fs3i_shard_alloc(fs3_sim* s);
 int fs3i_signal(fs3_sim* s, cudaStream_t st = nullptr);                      // barrier, first half: publish my epoch to all ranks
 int fs3i_wait(fs3_sim* s, cudaStream_t st = nullptr);                        // barrier, second half: all ranks reached my epoch
-int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes, cudaStream_t st = nullptr);   // copy a range of one of my arrays into the same range of every peer
+int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes, cudaStream_t st = nullptr);
+int fs3i_flag_signal(fs3_sim* s, unsigned mask, int slot0, uint32_t epoch, cudaStream_t st = nullptr);
+int fs3i_flag_wait(fs3_sim* s, unsigned mask, int slot0, uint32_t epoch, cudaStream_t st = nullptr);
+int fs3i_field_wait(fs3_sim* s);                                            // whole-grid getters: every rank's slab of the projected field has landed
+int fs3i_velocity_halo(const fs3_sim* s);   // copy a range of one of my arrays into the same range of every peer
 int fs3i_sor_signal(fs3_sim* s);                                            // "system set up": first SOR epoch of this projection to both neighbours
 int fs3i_sor_wait(fs3_sim* s, uint32_t epoch);
 int fs3i_ghost_pull(fs3_sim* s);

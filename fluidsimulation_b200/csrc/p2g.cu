@@ -263,7 +263,7 @@ __device__ __forceinline__ void ex_fill_node(const ExGrid& G, int q, int m) {
 	__stcg(g + q, __fdiv_rn(sum, cnt));
 }
 
-__global__ void __launch_bounds__(EX_THREADS, 3) k_ex_fill_layers(ExGrids P, uint32_t* __restrict__ arrive, int* __restrict__ flags) {
+__global__ void __launch_bounds__(EX_THREADS, 3) k_ex_fill_layers(ExGrids P, uint32_t* __restrict__ arrive, int* __restrict__ flags, int max_layers) {
 	const uint32_t tid = blockIdx.x * EX_THREADS + threadIdx.x, nthr = gridDim.x * EX_THREADS;
 	__shared__ int s_abort;
 	if (threadIdx.x == 0) s_abort = 0;
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(EX_THREADS, 3) k_ex_fill_layers(ExGrids P, uin
 #pragma unroll
 		for (int k = 0; k < 3; k++) {
 			if (k >= P.n) continue;
-			more |= e[k] < tot[k];
+			more |= e[k] < tot[k] && d < max_layers;
 			// the list entry of the next iteration is fetched while this one's values are in flight
 			int q = pq[k], m = pm[k];
 			for (uint32_t t = b[k] + tid; t < e[k]; t += nthr) {
@@ -328,10 +328,10 @@ int fs3i_cd_from_valid(fs3_sim* s, const unsigned char* dev_valid, size_t n) {
 
 // Phase 1 for scratch slot `slot` (cdv[slot] initialised to 0 / FS3_INF_CD): distance transform, bucket
 // histogram + starts (copied to pinned host memory), node lists.  Asynchronous.
-int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs) {
+int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs, size_t off) {
 	size_t n = (size_t)xs * ys * zs;
 	if (n > 0x7fffffffull) { s->err = "face grid too large for 32-bit node indices"; return FS3_ERR_INVALID; }
-	int* cd = s->cdv[slot];
+	int* cd = s->cdv[slot] + off;   // off: first node of a z window of the grid (sharded handles), node indices are relative to it
 	size_t rows = (size_t)ys * zs;
 	k_dt_x<<<cdiv((long long)rows * 32, 256), 256, 0, s->stream>>>(cd, xs, rows); FS3_LAUNCH_CHECK();
 	k_dt_line<<<cdiv((long long)xs * zs, 128), 128, 0, s->stream>>>(cd, xs, (size_t)xs * ys, (size_t)xs * zs, ys, (size_t)xs); FS3_LAUNCH_CHECK();
@@ -351,7 +351,7 @@ int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs) {
 }
 
 // Phase 2: the layered fill of `count` face grids (slots 0..count-1) in one persistent launch.
-static int extrap_fill_layers(fs3_sim* s, int count, float* const* grids, const int (*dims)[3]) {
+static int extrap_fill_layers(fs3_sim* s, int count, float* const* grids, const int (*dims)[3], int max_layers = 0x7fffffff) {
 	ExGrids P;
 	P.n = count;
 	for (int k = 0; k < count; k++) {
@@ -363,7 +363,7 @@ static int extrap_fill_layers(fs3_sim* s, int count, float* const* grids, const 
 	// The grid barrier needs every CTA resident: a COOPERATIVE launch makes that all-or-nothing (the driver only starts the grid
 	// when all of it fits, also beside other handles or contexts on the device).  One CTA per SM, 512 threads x <= 40 registers:
 	// fits beside the resident CTAs of the level-set sweep running on stream2.
-	void* args[] = {(void*)&P, (void*)&s->ex_arrive, (void*)&s->dev_flags};
+	void* args[] = {(void*)&P, (void*)&s->ex_arrive, (void*)&s->dev_flags, (void*)&max_layers};
 	FS3_CUDA(cudaLaunchCooperativeKernel((const void*)k_ex_fill_layers, dim3(s->sm_count), dim3(EX_THREADS), args, 0, s->stream));
 	FS3_LAUNCH_CHECK();
 	return FS3_OK;
@@ -453,13 +453,16 @@ __global__ void __launch_bounds__(256) k_cd_from_tags(const float* __restrict__ 
 }
 int fs3i_cd_from_tags(fs3_sim* s) {
 	float* g[3] = {s->oU, s->oV, s->oW};
-	const size_t nn[3] = {s->nU, s->nV, s->nW};
 	for (int ax = 0; ax < 3; ax++) {
 		size_t a, b;
 		fs3i_p2g_range(s, ax, &a, &b);
-		const size_t rest = nn[ax] - (b - a);
+		// only the planes of the extrapolation window that the neighbours pushed
+		int w0, w1;
+		fs3i_ex_window(s, ax, FS3_EX_DEPTH, &w0, &w1);
+		const size_t plane = (size_t)(s->nx + (ax == 0)) * (s->ny + (ax == 1)), base = plane * w0, n = plane * (w1 - w0);
+		const size_t rest = n - (b - a);
 		if (!rest) continue;
-		k_cd_from_tags<<<cdiv((long long)rest, 256), 256, 0, s->stream>>>(g[ax], s->cdv[ax], nn[ax], a, b); FS3_LAUNCH_CHECK();
+		k_cd_from_tags<<<cdiv((long long)rest, 256), 256, 0, s->stream>>>(g[ax] + base, s->cdv[ax] + base, n, a - base, b - base); FS3_LAUNCH_CHECK();
 	}
 	return FS3_OK;
 }
@@ -471,11 +474,62 @@ int fs3i_p2g(fs3_sim* s) {
 	return fs3i_extrapolate_all(s);
 }
 
-// the three face grids over the WHOLE grid (a sharded handle runs this replicated on the gathered P2G result)
+// ---- sharded handles: extrapolation on a z WINDOW of the slab, FS3_EX_DEPTH layers deep -------------------------------
+// A node of layer d (L1 distance d to the nearest valid node) only reads nodes of layer d-1, and every layer-d node of the slab
+// lies within d planes of a valid node: with FS3_EX_DEPTH planes of the neighbours' P2G result on either side (values and
+// validity, pushed by the owners) the distance transform and the first FS3_EX_DEPTH layers come out bit-identical to the
+// whole-grid computation for every node of the slab -- and for the nodes k planes outside it up to layer FS3_EX_DEPTH - k.
+// Deeper layers are never consumed: the divergence and the pressure gradient read faces of fluid cells (phi < 0: a particle
+// within one cell of the centre, hence a valid node within L1 distance 4 of the face), air-air faces come out of the gradient as
+// 0 whatever was extrapolated (S3D.cpp:1024-1037), and G2P interpolates old' = new - (1-alpha) old within one cell of a
+// particle (L1 distance <= 4 again; the combine runs two planes into the halo, where layers up to FS3_EX_DEPTH - 2 are exact).
+// So the slabs need no per-layer exchange and no dependency along z; nodes deeper than FS3_EX_DEPTH are set to 0.
+void fs3i_ex_window(const fs3_sim* s, int ax, int depth, int* w0, int* w1) {
+	const int top = s->nz + (ax == 2 ? 1 : 0);
+	const int own1 = s->z1 + ((ax == 2 && s->rank == s->world - 1) ? 1 : 0);
+	*w0 = std::max(0, s->z0 - depth);
+	*w1 = std::min(top, own1 + depth);
+}
+__global__ void __launch_bounds__(256) k_ex_clear_deep(float* __restrict__ grid, const int* __restrict__ cd, size_t q0, size_t q1, int depth) {
+	const size_t q = q0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (q < q1 && cd[q] > depth) grid[q] = 0.0f;
+}
+static int extrapolate_window(fs3_sim* s) {
+	int rc;
+	float* g[3] = {s->oU, s->oV, s->oW};
+	float* gw[3];
+	int dims[3][3];
+	size_t off[3];
+	for (int ax = 0; ax < 3; ax++) {
+		const int xs = s->nx + (ax == 0), ys = s->ny + (ax == 1);
+		int w0, w1;
+		fs3i_ex_window(s, ax, FS3_EX_DEPTH, &w0, &w1);
+		off[ax] = (size_t)xs * ys * w0;
+		gw[ax] = g[ax] + off[ax];
+		dims[ax][0] = xs; dims[ax][1] = ys; dims[ax][2] = w1 - w0;
+		if (s->prm.extrapolation_mode == 1) {
+			if ((rc = extrap_one_layer(s, gw[ax], s->cdv[ax] + off[ax], xs, ys, w1 - w0))) return rc;
+		} else if ((rc = fs3i_extrap_prepare(s, ax, xs, ys, w1 - w0, off[ax]))) return rc;
+	}
+	if (s->prm.extrapolation_mode == 1) return FS3_OK;
+	if ((rc = extrap_fill_layers(s, 3, gw, dims, FS3_EX_DEPTH))) return rc;
+	for (int ax = 0; ax < 3; ax++) {
+		size_t q0, q1;
+		fs3i_p2g_range(s, ax, &q0, &q1);
+		// (the halo planes keep whatever the fill left: exact up to their own depth, never read beyond it)
+		const size_t plane = (size_t)dims[ax][0] * dims[ax][1];
+		q0 = off[ax]; q1 = off[ax] + plane * dims[ax][2];
+		k_ex_clear_deep<<<cdiv((long long)(q1 - q0), 256), 256, 0, s->stream>>>(g[ax], s->cdv[ax], q0, q1, FS3_EX_DEPTH); FS3_LAUNCH_CHECK();
+	}
+	return FS3_OK;
+}
+
+// the three face grids over the WHOLE grid (single GPU), or over the slab's window (sharded)
 int fs3i_extrapolate_all(fs3_sim* s) {
 	GridDims d{s->nx, s->ny, s->nz};
 	int rc;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_EXTRAPOLATE], s->stream);
+	if (s->world > 1) return extrapolate_window(s);
 	if (s->prm.extrapolation_mode == 1) {
 		float* gg[3] = {s->oU, s->oV, s->oW};
 		for (int ax = 0; ax < 3; ax++)

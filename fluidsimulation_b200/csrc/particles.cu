@@ -112,6 +112,10 @@ struct MigArgs {
 	uint32_t* leaver;    // their indices in the live range
 	uint32_t cap;
 	int rank, world, slab, nz;
+	// index-space z range inside which every tap of InterpolateMACCell falls into planes of the projected field this rank holds
+	// (its slab + the halo its neighbours push, fs3i_velocity_halo); flags[4] reports a Runge-Kutta stage outside it
+	float zmin_ok, zmax_ok;
+	int* flags;
 };
 __device__ __forceinline__ int mig_owner(const MigArgs& m, float z) {
 	int cz = min(max(fs3_cell_axis(z, (float)m.nz), 0), m.nz - 1);
@@ -172,13 +176,15 @@ __global__ void __launch_bounds__(256) k_advect(float4* __restrict__ pos, long l
 	float4 p = pos[i];
 	if (__float_as_int(p.w) < 0) { if (!SHARD) bin.cellid[i] = 0xffffffffu; return; }   // dead slot (emigrated)
 	float fx = (float)d.nx, fy = (float)d.ny, fz = (float)d.nz;
-	float3 k1 = fs3_interp(U, V, W, d, __fmul_rn(fx, p.x), __fmul_rn(fy, p.y), __fmul_rn(fz, p.z));
+	const float z1c = __fmul_rn(fz, p.z);
+	float3 k1 = fs3_interp(U, V, W, d, __fmul_rn(fx, p.x), __fmul_rn(fy, p.y), z1c);
 	float h = __fmul_rn(0.5f, dt);
-	float3 k2 = fs3_interp(U, V, W, d, __fmul_rn(fx, __fadd_rn(p.x, __fmul_rn(h, k1.x))), __fmul_rn(fy, __fadd_rn(p.y, __fmul_rn(h, k1.y))),
-	                       __fmul_rn(fz, __fadd_rn(p.z, __fmul_rn(h, k1.z))));
+	const float z2c = __fmul_rn(fz, __fadd_rn(p.z, __fmul_rn(h, k1.z)));
+	float3 k2 = fs3_interp(U, V, W, d, __fmul_rn(fx, __fadd_rn(p.x, __fmul_rn(h, k1.x))), __fmul_rn(fy, __fadd_rn(p.y, __fmul_rn(h, k1.y))), z2c);
 	float t = __fmul_rn(0.75f, dt);
-	float3 k3 = fs3_interp(U, V, W, d, __fmul_rn(fx, __fadd_rn(p.x, __fmul_rn(t, k2.x))), __fmul_rn(fy, __fadd_rn(p.y, __fmul_rn(t, k2.y))),
-	                       __fmul_rn(fz, __fadd_rn(p.z, __fmul_rn(t, k2.z))));
+	const float z3c = __fmul_rn(fz, __fadd_rn(p.z, __fmul_rn(t, k2.z)));
+	float3 k3 = fs3_interp(U, V, W, d, __fmul_rn(fx, __fadd_rn(p.x, __fmul_rn(t, k2.x))), __fmul_rn(fy, __fadd_rn(p.y, __fmul_rn(t, k2.y))), z3c);
+	if (SHARD && (fminf(z1c, fminf(z2c, z3c)) < mig.zmin_ok || fmaxf(z1c, fmaxf(z2c, z3c)) > mig.zmax_ok)) mig.flags[4] = 1;
 	const float c1 = 2.0f / 9.0f, c2 = 3.0f / 9.0f, c3 = 4.0f / 9.0f;
 	float vx = __fadd_rn(__fadd_rn(__fmul_rn(c1, k1.x), __fmul_rn(c2, k2.x)), __fmul_rn(c3, k3.x));
 	float vy = __fadd_rn(__fadd_rn(__fmul_rn(c1, k1.y), __fmul_rn(c2, k2.y)), __fmul_rn(c3, k3.y));
@@ -198,6 +204,10 @@ static MigArgs mig_args(fs3_sim* s) {
 	MigArgs m;
 	m.ctl = s->mig_ctl; m.leaver = s->leaver_idx; m.cap = (uint32_t)s->mig_cap;
 	m.rank = s->rank; m.world = s->world; m.slab = s->nz / s->world; m.nz = s->nz;
+	const int hv = fs3i_velocity_halo(s), wlo = std::max(0, s->z0 - hv), whi = std::min(s->nz, s->z1 + hv);
+	m.zmin_ok = wlo == 0 ? -1e30f : (float)wlo + 1.0f;
+	m.zmax_ok = whi == s->nz ? 1e30f : (float)whi - 1.5f;
+	m.flags = s->dev_flags;
 	return m;
 }
 
@@ -584,6 +594,21 @@ __global__ void __launch_bounds__(256) k_flip_combine(const float* __restrict__ 
 }
 int fs3i_flip_combine(fs3_sim* s, float alpha) {
 	float om = 1.0f - alpha;
+	if (s->world > 1) {
+		// sharded: G2P only interpolates within one cell of this slab's particles: the slab's planes and two on either side
+		// (k_flip_combine handles a range that is not 16-byte aligned with its scalar tail: the range starts on a float4 boundary
+		// because the first plane is rounded down to one)
+		float *cur[3] = {s->U, s->V, s->W}, *old[3] = {s->oU, s->oV, s->oW};
+		for (int ax = 0; ax < 3; ax++) {
+			const size_t plane = (size_t)(s->nx + (ax == 0)) * (s->ny + (ax == 1));
+			const int top = s->nz + (ax == 2 ? 1 : 0);
+			const int a = std::max(0, s->z0 - 2), b = std::min(top, s->z1 + 2 + (ax == 2 ? 1 : 0));
+			size_t q0 = plane * a, q1 = plane * b;
+			q0 &= ~(size_t)3;
+			k_flip_combine<<<cdiv((long long)((q1 - q0) >> 2) + 1, 256), 256, 0, s->stream>>>(cur[ax] + q0, old[ax] + q0, q1 - q0, om); FS3_LAUNCH_CHECK();
+		}
+		return FS3_OK;
+	}
 	k_flip_combine<<<cdiv((long long)(s->nU >> 2) + 1, 256), 256, 0, s->stream>>>(s->U, s->oU, s->nU, om); FS3_LAUNCH_CHECK();
 	k_flip_combine<<<cdiv((long long)(s->nV >> 2) + 1, 256), 256, 0, s->stream>>>(s->V, s->oV, s->nV, om); FS3_LAUNCH_CHECK();
 	k_flip_combine<<<cdiv((long long)(s->nW >> 2) + 1, 256), 256, 0, s->stream>>>(s->W, s->oW, s->nW, om); FS3_LAUNCH_CHECK();

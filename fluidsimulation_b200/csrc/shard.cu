@@ -63,7 +63,7 @@ int fs3i_shard_alloc(fs3_sim* s) {
 	const int w = s->world;
 	if ((rc = fs3i_alloc(s, (void**)&s->mig_matrix, (size_t)w * (w + 1) * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_ctl, (2 * (size_t)w + 1) * 4)) ||
 	    (rc = fs3i_alloc(s, (void**)&s->leaver_idx, (size_t)s->mig_cap * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_pos, (size_t)s->mig_cap * 16)) ||
-	    (rc = fs3i_alloc(s, (void**)&s->mig_vel, (size_t)s->mig_cap * 16)) || (rc = fs3i_alloc(s, (void**)&s->bar, (FS3_MAX_WORLD + 2) * 4)) ||
+	    (rc = fs3i_alloc(s, (void**)&s->mig_vel, (size_t)s->mig_cap * 16)) || (rc = fs3i_alloc(s, (void**)&s->bar, FS3_BAR_WORDS * 4)) ||
 	    (rc = fs3i_alloc(s, (void**)&s->sor_done, 4)))
 		return rc;
 	FS3_CUDA(cudaMallocHost((void**)&s->h_pin, (size_t)std::max(w * (w + 1), 64) * 4));
@@ -93,6 +93,61 @@ int fs3i_wait(fs3_sim* s, cudaStream_t st) {
 	k_bar_wait<<<1, 32, 0, st ? st : s->stream>>>(s->bar, s->rank, s->world, s->bar_epoch, s->dev_flags, s->lockstep ? 1 : 0); FS3_LAUNCH_CHECK();
 	return FS3_OK;
 }
+
+// ---- selective epoch flags: rank r's word of flag set `slot0` on the ranks in `mask` ---------------------------------------
+__global__ void k_flag_signal(PeerPtrs bars, int rank, unsigned mask, int slot0, uint32_t epoch) {
+	const int r = threadIdx.x;
+	if (r < FS3_MAX_WORLD && ((mask >> r) & 1u) && r != rank) { __threadfence_system(); fs3_st_release_sys(bars.p[r] + slot0 + rank, epoch); }
+}
+__global__ void k_flag_wait(const uint32_t* bar, int rank, unsigned mask, int slot0, uint32_t epoch, int* flags, int nospin) {
+	const int r = threadIdx.x;
+	if (r < FS3_MAX_WORLD && ((mask >> r) & 1u) && r != rank) fs3_flag_wait(bar + slot0 + r, epoch, flags, nospin);
+}
+int fs3i_flag_signal(fs3_sim* s, unsigned mask, int slot0, uint32_t epoch, cudaStream_t st) {
+	PeerPtrs pp;
+	for (int r = 0; r < FS3_MAX_WORLD; r++) pp.p[r] = r < s->world ? fs3_peer(s, r, s->bar) : nullptr;
+	k_flag_signal<<<1, 32, 0, st ? st : s->stream>>>(pp, s->rank, mask, slot0, epoch); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+int fs3i_flag_wait(fs3_sim* s, unsigned mask, int slot0, uint32_t epoch, cudaStream_t st) {
+	k_flag_wait<<<1, 32, 0, st ? st : s->stream>>>(s->bar, s->rank, mask, slot0, epoch, s->dev_flags, s->lockstep ? 1 : 0); FS3_LAUNCH_CHECK();
+	return FS3_OK;
+}
+// The projected field of the last step is complete on this rank once every other rank's copy of its slab has landed (the
+// copies run on the senders' copy streams behind the step): what the whole-grid getters wait for.
+int fs3i_field_wait(fs3_sim* s) {
+	if (s->world < 2 || !s->xfer_epoch) return FS3_OK;
+	return fs3i_flag_wait(s, (1u << s->world) - 1u, FS3_BAR_XALL, s->xfer_epoch, nullptr);
+}
+
+// My planes [a, b) of a z-slowest array go to every rank in `mask` whose range of needed planes [lo(r), hi(r)) overlaps them.
+template <typename F> static int push_overlap(fs3_sim* s, void* arr, size_t plane_bytes, int a, int b, unsigned mask, F need, cudaStream_t st) {
+	for (int k = 1; k < s->world; k++) {
+		const int r = (s->rank + k) % s->world;   // staggered so that the ranks do not all target the same peer at once
+		if (!((mask >> r) & 1u)) continue;
+		int lo, hi;
+		need(r, &lo, &hi);
+		lo = std::max(lo, a); hi = std::min(hi, b);
+		if (lo >= hi) continue;
+		FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, r, (char*)arr) + plane_bytes * (size_t)lo, (char*)arr + plane_bytes * (size_t)lo, plane_bytes * (size_t)(hi - lo), cudaMemcpyDefault,
+		                         st ? st : s->stream));
+	}
+	return FS3_OK;
+}
+// ranks (other than this one) whose slab lies within `halo` planes of this rank's slab
+static unsigned near_mask(const fs3_sim* s, int halo) {
+	const int slab = s->nz / s->world;
+	unsigned m = 0;
+	for (int r = 0; r < s->world; r++) {
+		if (r == s->rank) continue;
+		const int a = r * slab, b = a + slab;
+		if (a < s->z1 + halo + 1 && b > s->z0 - halo - 1) m |= 1u << r;
+	}
+	return m;
+}
+// planes of the velocity halo: a rank reads the projected field up to one neighbouring slab (at least 8 planes) away from its
+// own -- Advect checks that no Runge-Kutta stage leaves that range (fs3i_advect)
+int fs3i_velocity_halo(const fs3_sim* s) { return std::max(s->nz / s->world, 8); }
 
 int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes, cudaStream_t st) {
 	if (!bytes) return FS3_OK;
@@ -274,13 +329,20 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 		if ((rc = fs3i_levelset_fork(s, true))) return rc;
 		// no wait on the main stream: the gather reads this rank's particles + ghost layers only.  Each face grid leaves as soon as
 		// it is done (while the next one is gathered); invalid nodes travel as tagged NaNs, so the validity needs no copy of its own.
+		// Only the ranks whose extrapolation window (FS3_EX_DEPTH planes around their slab) reaches into this slab get planes.
 		const int zw = s->z1 + (last ? 1 : 0);
+		const int slab = s->nz / s->world, world = s->world, nz = s->nz;
+		const unsigned near = near_mask(s, FS3_EX_DEPTH);
 		cudaStream_t xs = nullptr;
 		for (int ax = 0; ax < 3; ax++) {
 			if ((rc = fs3i_p2g_gather_axis(s, ax)) || (rc = xfer_begin(s, &xs))) return rc;
-			if (ax == 0) rc = push_planes(s, s->oU, pU, 4, s->z0, s->z1, xs);
-			else if (ax == 1) rc = push_planes(s, s->oV, pV, 4, s->z0, s->z1, xs);
-			else rc = push_planes(s, s->oW, pW, 4, s->z0, zw, xs);
+			auto need = [=](int r, int* lo, int* hi) {
+				const int top = nz + (ax == 2 ? 1 : 0), own1 = (r + 1) * slab + ((ax == 2 && r == world - 1) ? 1 : 0);
+				*lo = std::max(0, r * slab - FS3_EX_DEPTH); *hi = std::min(top, own1 + FS3_EX_DEPTH);
+			};
+			if (ax == 0) rc = push_overlap(s, s->oU, pU * 4, s->z0, s->z1, near, need, xs);
+			else if (ax == 1) rc = push_overlap(s, s->oV, pV * 4, s->z0, s->z1, near, need, xs);
+			else rc = push_overlap(s, s->oW, pW * 4, s->z0, zw, near, need, xs);
 			if (rc) return rc;
 		}
 		return fs3i_signal(s, xs);
@@ -296,15 +358,31 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 	}
 	if (ph < 6 + 2 * I) { s->sor_halves = 2 * I; return fs3i_sor_half_launch(s, ph - 6); }   // compute + halo exchange in one kernel
 	if (ph == 6 + 2 * I) {  // pressure gradient on the slab; the projected field is gathered on every rank
-		if ((rc = fs3i_sor_wait(s, s->sor_e0 + 2u * (uint32_t)I)) || (rc = fs3i_project_gradient(s, dt, true, true))) return rc;
-		// the gradient kernel of cell plane z writes the W faces z+1 (and z = 0 on rank 0): that is the range it owns here
-		if ((rc = push_planes(s, s->U, pU, 4, s->z0, s->z1)) || (rc = push_planes(s, s->V, pV, 4, s->z0, s->z1)) ||
-		    (rc = push_planes(s, s->W, pW, 4, s->rank == 0 ? 0 : s->z0 + 1, s->z1 + 1)))
+		// the copies of the previous step's field (stream3) have left before the gradient overwrites their source
+		if ((rc = xfer_join(s)) || (rc = fs3i_sor_wait(s, s->sor_e0 + 2u * (uint32_t)I)) || (rc = fs3i_project_gradient(s, dt, true, true))) return rc;
+		// The gradient kernel of cell plane z writes the W faces z+1 (and z = 0 on rank 0): that is the range it owns here.
+		// On the copy stream: (1) the planes inside the neighbours' velocity halo + their flag -- all the next kernels of any
+		// rank read (FLIP blend, G2P, the next Advect); (2) the slab to everybody + a second flag, for the whole-grid getters.
+		const int hv = fs3i_velocity_halo(s), slab = s->nz / s->world, nz = s->nz;
+		const unsigned near = near_mask(s, hv), all = (1u << s->world) - 1u;
+		const int w_a = s->rank == 0 ? 0 : s->z0 + 1, w_b = s->z1 + 1;
+		auto need_c = [=](int r, int* lo, int* hi) { *lo = std::max(0, r * slab - hv); *hi = std::min(nz, (r + 1) * slab + hv); };
+		auto need_w = [=](int r, int* lo, int* hi) { *lo = std::max(0, r * slab - hv); *hi = std::min(nz + 1, (r + 1) * slab + hv + 1); };
+		auto need_all_c = [=](int, int* lo, int* hi) { *lo = 0; *hi = nz; };
+		auto need_all_w = [=](int, int* lo, int* hi) { *lo = 0; *hi = nz + 1; };
+		cudaStream_t xs;
+		if ((rc = xfer_begin(s, &xs))) return rc;
+		s->xfer_epoch++;
+		if ((rc = push_overlap(s, s->U, pU * 4, s->z0, s->z1, near, need_c, xs)) || (rc = push_overlap(s, s->V, pV * 4, s->z0, s->z1, near, need_c, xs)) ||
+		    (rc = push_overlap(s, s->W, pW * 4, w_a, w_b, near, need_w, xs)) || (rc = fs3i_flag_signal(s, near, FS3_BAR_XNEAR, s->xfer_epoch, xs)))
 			return rc;
-		return fs3i_signal(s);
+		if ((rc = push_overlap(s, s->U, pU * 4, s->z0, s->z1, all, need_all_c, xs)) || (rc = push_overlap(s, s->V, pV * 4, s->z0, s->z1, all, need_all_c, xs)) ||
+		    (rc = push_overlap(s, s->W, pW * 4, w_a, w_b, all, need_all_w, xs)) || (rc = fs3i_flag_signal(s, all, FS3_BAR_XALL, s->xfer_epoch, xs)))
+			return rc;
+		return FS3_OK;
 	}
-	if (ph == 7 + 2 * I) {  // PIC/FLIP blend (S3D.cpp:148-180)
-		if ((rc = fs3i_wait(s))) return rc;
+	if (ph == 7 + 2 * I) {  // PIC/FLIP blend (S3D.cpp:148-180), once the neighbours' halo planes of the projected field are here
+		if ((rc = fs3i_flag_wait(s, near_mask(s, fs3i_velocity_halo(s)), FS3_BAR_XNEAR, s->xfer_epoch))) return rc;
 		if (T) cudaEventRecord(s->ev[FS3_T_FLIP_APPLY], s->stream);
 		const float alpha = flip_alpha(s, dt);
 		if ((rc = fs3i_flip_combine(s, alpha)) || (rc = fs3i_g2p(s, alpha))) return rc;
