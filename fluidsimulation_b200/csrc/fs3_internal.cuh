@@ -316,6 +316,7 @@ int fs3i_load_local(fs3_sim* s, const fs3_particle* dev_in, const int* dev_ids, 
 int fs3i_project_setup(fs3_sim* s, float dt, bool from_old, bool with_gravity);
 int fs3i_sor_prepare(fs3_sim* s);
 int fs3i_sor_half_launch(fs3_sim* s, int k);                                // half sweep k of the current projection
+int fs3i_sor_persistent(fs3_sim* s, int halves);                            // multi-process sharded handle: the whole solve in one cooperative launch
 int fs3i_project_gradient(fs3_sim* s, float dt, bool from_old, bool with_gravity);
 // levelset.cu / p2g.cu pieces
 int fs3i_levelset_seed(fs3_sim* s, cudaStream_t st = nullptr);

@@ -94,6 +94,10 @@ __device__ __forceinline__ void ldv(const float* p, float (&a)[4]) { const float
 // not push the two colours of p, which every half sweep reads again, out of the 126 MB L2
 __device__ __forceinline__ void ldv_stream(const double* p, double (&a)[2]) { const double2 t = __ldcs(reinterpret_cast<const double2*>(p)); a[0] = t.x; a[1] = t.y; }
 __device__ __forceinline__ void ldv_stream(const float* p, float (&a)[4]) { const float4 t = __ldcs(reinterpret_cast<const float4*>(p)); a[0] = t.x; a[1] = t.y; a[2] = t.z; a[3] = t.w; }
+// L2 loads: inside ONE launch that runs many half sweeps, p written by other SMs (or by the neighbouring GPU) in the previous half
+// sweep must not be served from this SM's L1
+__device__ __forceinline__ void ldv_cg(const double* p, double (&a)[2]) { const double2 t = __ldcg(reinterpret_cast<const double2*>(p)); a[0] = t.x; a[1] = t.y; }
+__device__ __forceinline__ void ldv_cg(const float* p, float (&a)[4]) { const float4 t = __ldcg(reinterpret_cast<const float4*>(p)); a[0] = t.x; a[1] = t.y; a[2] = t.z; a[3] = t.w; }
 __device__ __forceinline__ void stv(double* p, const double (&a)[2]) { *reinterpret_cast<double2*>(p) = make_double2(a[0], a[1]); }
 __device__ __forceinline__ void stv(float* p, const float (&a)[4]) { *reinterpret_cast<float4*>(p) = make_float4(a[0], a[1], a[2], a[3]); }
 
@@ -136,7 +140,7 @@ __device__ __forceinline__ SorPtrs<REAL> sor_ptrs(const Sys<REAL>& sy, int colou
 	sp.lo_begin = sh.lo_begin; sp.lo_end = sh.lo_end; sp.hi_begin = sh.hi_begin; sp.hi_end = sh.hi_end;
 	return sp;
 }
-template <typename REAL, int VEC, bool PUSH>
+template <typename REAL, int VEC, bool PUSH, bool CG = false>
 __device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, REAL one_minus_omega, uint32_t ent) {
 	typedef Ops<REAL> O;
 	typedef typename VecT<REAL, VEC>::type V;
@@ -147,12 +151,21 @@ __device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, 
 	const size_t base = (size_t)(ent & 0x7fffffffu) * VEC;
 	const M mm = __ldcs(reinterpret_cast<const M*>(sp.mask + base));
 	REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
-	ldv(sp.own + base, own);
-	ldv(o + base, xc);
+	REAL edge;
+	if (CG) {
+		ldv_cg(sp.own + base, own);
+		ldv_cg(o + base, xc);
+		ldv_cg(o + base - sp.hp, ym); ldv_cg(o + base + sp.hp, yp);
+		ldv_cg(o + base - sp.plane, zm); ldv_cg(o + base + sp.plane, zp);
+		edge = __ldcg(s == 0 ? o + base - 1 : o + base + VEC);
+	} else {
+		ldv(sp.own + base, own);
+		ldv(o + base, xc);
+		ldv(o + base - sp.hp, ym); ldv(o + base + sp.hp, yp);
+		ldv(o + base - sp.plane, zm); ldv(o + base + sp.plane, zp);
+		edge = s == 0 ? o[base - 1] : o[base + VEC];
+	}
 	ldv_stream(sp.b + base, bb);
-	ldv(o + base - sp.hp, ym); ldv(o + base + sp.hp, yp);
-	ldv(o + base - sp.plane, zm); ldv(o + base + sp.plane, zp);
-	const REAL edge = s == 0 ? o[base - 1] : o[base + VEC];
 #pragma unroll
 	for (int e = 0; e < VEC; e++) dd[e] = (REAL)1;
 	if ((mm & nodiag) != nodiag) ldv_stream(sp.dg + base, dd);
@@ -249,6 +262,79 @@ __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_half(Sys<
 	// interior: the remaining blocks (all of a one-block grid)
 	const uint32_t ib = gridDim.x == 1 ? 0u : blockIdx.x - nbb, IG = gridDim.x == 1 ? blockDim.x : (gridDim.x - nbb) * blockDim.x;
 	for (uint32_t t = ib * blockDim.x + threadIdx.x; t < n - B; t += IG) sor_vector<REAL, VEC, false>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
+}
+
+// ---- sharded solve in ONE launch (multi-process handles) ---------------------------------------------------------------
+// With a slab per GPU a half sweep needs ~4.5 us of memory traffic but cost 13 us as a launch of its own: the launch, and one
+// NVLink flag round trip that could only start once the kernel was running.  Here all 2 * iterations half sweeps are one
+// cooperative launch: a half sweep is the boundary-first schedule of k_sor_half<.., SHARD> followed by a grid barrier (arrive
+// counter in L2), and the neighbours' epoch flags are polled by CTAs that are already resident.  p travels through L2 only
+// (ld.cg / write-through stores): L1 is not coherent across SMs inside a launch.
+struct SorPersist {
+	void* peer_p[2][2];       // [colour][lower / upper neighbour]
+	uint32_t* peer_flag[2];
+	const uint32_t* my_flag;
+	uint32_t e0;              // epoch of "system set up"; half sweep k waits for e0 + k and signals e0 + k + 1
+	int halves;
+	size_t lo_begin, lo_end, hi_begin, hi_end;
+	const uint32_t *n_lo[2], *n_hi[2], *list[2], *count[2];
+	uint32_t *done, *gbar;
+	int* flags;
+};
+template <typename REAL, int VEC>
+__global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_persistent(Sys<REAL> sy, REAL omega, REAL one_minus_omega, SorPersist P) {
+	const uint32_t G = gridDim.x;
+	for (int k = 0; k < P.halves; k++) {
+		const int c = k & 1;
+		SorShard sh;
+		sh.peer_p[0] = P.peer_p[c][0]; sh.peer_p[1] = P.peer_p[c][1];
+		sh.lo_begin = P.lo_begin; sh.lo_end = P.lo_end; sh.hi_begin = P.hi_begin; sh.hi_end = P.hi_end;
+		const SorPtrs<REAL> sp = sor_ptrs<REAL>(sy, c, sh);
+		const uint32_t* __restrict__ list = c ? P.list[1] : P.list[0];
+		const uint32_t n = __ldg(c ? P.count[1] : P.count[0]), n_lo = __ldg(c ? P.n_lo[1] : P.n_lo[0]), n_hi = __ldg(c ? P.n_hi[1] : P.n_hi[0]);
+		const uint32_t B = n_lo + (n - n_hi);
+		const uint32_t nbb = min(max(G / 4u, 1u), max(1u, (B + blockDim.x - 1) / blockDim.x));   // blocks that hold the boundary work
+		if (blockIdx.x < nbb || G == 1) {
+			if (threadIdx.x == 0 && P.peer_flag[0]) fs3_flag_wait(P.my_flag, P.e0 + (uint32_t)k, P.flags, 0);
+			if (threadIdx.x == 1 && P.peer_flag[1]) fs3_flag_wait(P.my_flag + 1, P.e0 + (uint32_t)k, P.flags, 0);
+			__syncthreads();
+			bool pushed = false;
+			for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < B; t += nbb * blockDim.x) {
+				sor_vector<REAL, VEC, true, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
+				pushed = true;
+			}
+			if (pushed) __threadfence_system();   // my peer stores are visible system-wide before the block reports in
+			__syncthreads();
+			if (threadIdx.x == 0) {
+				const uint32_t dn = atomicAdd(P.done, 1u);
+				if (dn == nbb - 1) {
+					*P.done = 0;
+					__threadfence_system();
+					if (P.peer_flag[0]) fs3_st_relaxed_sys(P.peer_flag[0], P.e0 + (uint32_t)k + 1u);
+					if (P.peer_flag[1]) fs3_st_relaxed_sys(P.peer_flag[1], P.e0 + (uint32_t)k + 1u);
+				}
+			}
+		}
+		if (blockIdx.x >= nbb || G == 1) {
+			const uint32_t ib = G == 1 ? 0u : blockIdx.x - nbb, IG = G == 1 ? blockDim.x : (G - nbb) * blockDim.x;
+			for (uint32_t t = ib * blockDim.x + threadIdx.x; t < n - B; t += IG) sor_vector<REAL, VEC, false, true>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
+		}
+		// ---- grid barrier: the next half sweep reads this colour everywhere -------------------------------------------------
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			__threadfence();
+			atomicAdd(P.gbar, 1u);
+			const uint32_t need = (uint32_t)(k + 1) * G;
+			const long long t0 = clock64();
+			for (unsigned it = 1;; it++) {
+				uint32_t v;
+				asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(P.gbar) : "memory");
+				if (v >= need) break;
+				if ((it & 1023u) == 0 && (*reinterpret_cast<volatile int*>(P.flags + 2) || clock64() - t0 > 8000000000LL)) { P.flags[2] = 1; break; }
+			}
+		}
+		__syncthreads();
+	}
 }
 
 // active-vector flags (+1 trailing zero so that the exclusive scan's last entry is the count) and compaction
@@ -537,6 +623,42 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 	return FS3_OK;
 }
 int fs3i_sor_half_launch(fs3_sim* s, int k) { return s->alloc_precision ? sor_half_t<float, 4>(s, k) : sor_half_t<double, 2>(s, k); }
+
+// all `halves` half sweeps of a multi-process sharded handle in one cooperative launch
+template <typename REAL, int VEC> static int sor_persistent_t(fs3_sim* s, int halves) {
+	Sys<REAL> sy = make_sys<REAL>(s);
+	REAL omega = (REAL)fs3_omega(s);
+	if (sizeof(REAL) == 4) omega = (REAL)2 - (REAL)3.16343 / s->nx, omega = s->prm.omega > 0 ? (REAL)s->prm.omega : omega;
+	REAL omo = (REAL)1 - omega;
+	int per_sm = 0;
+	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sor_persistent<REAL, VEC>, FS3_SOR_THREADS, 0));
+	per_sm = std::max(1, per_sm);
+	const size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * (s->z1 - s->z0);
+	const int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, FS3_SOR_THREADS)), (long long)s->sm_count * per_sm);
+	SorPersist P;
+	const bool lo = s->rank > 0, hi = s->rank < s->world - 1;
+	for (int c = 0; c < 2; c++) {
+		P.peer_p[c][0] = lo ? fs3_peer(s, s->rank - 1, (char*)s->p[c]) : nullptr;
+		P.peer_p[c][1] = hi ? fs3_peer(s, s->rank + 1, (char*)s->p[c]) : nullptr;
+		P.n_lo[c] = s->sor_pos[c] + s->rb.plane * (size_t)(s->z0 + 2) / VEC;
+		P.n_hi[c] = s->sor_pos[c] + s->rb.plane * (size_t)s->z1 / VEC;
+		P.list[c] = s->sor_list[c]; P.count[c] = s->sor_count[c];
+	}
+	P.peer_flag[0] = lo ? fs3_peer(s, s->rank - 1, s->bar) + FS3_MAX_WORLD + 1 : nullptr;
+	P.peer_flag[1] = hi ? fs3_peer(s, s->rank + 1, s->bar) + FS3_MAX_WORLD + 0 : nullptr;
+	P.my_flag = s->bar + FS3_MAX_WORLD;
+	P.e0 = s->sor_e0; P.halves = halves;
+	P.lo_begin = s->rb.plane * (size_t)(s->z0 + 1); P.lo_end = P.lo_begin + s->rb.plane;
+	P.hi_begin = s->rb.plane * (size_t)s->z1; P.hi_end = P.hi_begin + s->rb.plane;
+	P.done = s->sor_done; P.gbar = s->sor_done + 1; P.flags = s->dev_flags;
+	FS3_CUDA(cudaMemsetAsync(s->sor_done, 0, 2 * sizeof(uint32_t), s->stream));
+	void* args[] = {(void*)&sy, (void*)&omega, (void*)&omo, (void*)&P};
+	FS3_CUDA(cudaLaunchCooperativeKernel((const void*)k_sor_persistent<REAL, VEC>, dim3(nb), dim3(FS3_SOR_THREADS), args, 0, s->stream));
+	FS3_LAUNCH_CHECK();
+	s->sor_epoch = s->sor_e0 + (uint32_t)halves;
+	return FS3_OK;
+}
+int fs3i_sor_persistent(fs3_sim* s, int halves) { return s->alloc_precision ? sor_persistent_t<float, 4>(s, halves) : sor_persistent_t<double, 2>(s, halves); }
 
 // The persisting-L2 size is a DEVICE-wide limit: whatever the host application (or another handle) had configured is put
 // back when the solve ends, on every path out of fs3i_sor_loop.

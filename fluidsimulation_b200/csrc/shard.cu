@@ -64,7 +64,7 @@ int fs3i_shard_alloc(fs3_sim* s) {
 	if ((rc = fs3i_alloc(s, (void**)&s->mig_matrix, (size_t)w * (w + 1) * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_ctl, (2 * (size_t)w + 1) * 4)) ||
 	    (rc = fs3i_alloc(s, (void**)&s->leaver_idx, (size_t)s->mig_cap * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_pos, (size_t)s->mig_cap * 16)) ||
 	    (rc = fs3i_alloc(s, (void**)&s->mig_vel, (size_t)s->mig_cap * 16)) || (rc = fs3i_alloc(s, (void**)&s->bar, FS3_BAR_WORDS * 4)) ||
-	    (rc = fs3i_alloc(s, (void**)&s->sor_done, 4)))
+	    (rc = fs3i_alloc(s, (void**)&s->sor_done, 16)))   // [0] block counter of the end-of-sweep signal, [1] grid barrier of the one-launch solve
 		return rc;
 	FS3_CUDA(cudaMallocHost((void**)&s->h_pin, (size_t)std::max(w * (w + 1), 64) * 4));
 	return FS3_OK;
@@ -356,7 +356,13 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 		if (T) cudaEventRecord(s->ev[FS3_T_PROJECT_SOR], s->stream);
 		return FS3_OK;
 	}
-	if (ph < 6 + 2 * I) { s->sor_halves = 2 * I; return fs3i_sor_half_launch(s, ph - 6); }   // compute + halo exchange in one kernel
+	if (ph < 6 + 2 * I) {   // compute + halo exchange in one kernel
+		s->sor_halves = 2 * I;
+		// one launch per half sweep for a lockstep group (the ranks' kernels take turns on one stream); a multi-process handle runs
+		// the whole solve as ONE cooperative launch whose CTAs exchange halos and epoch flags with the neighbours while resident
+		if (s->lockstep) return fs3i_sor_half_launch(s, ph - 6);
+		return ph == 6 ? fs3i_sor_persistent(s, 2 * I) : FS3_OK;
+	}
 	if (ph == 6 + 2 * I) {  // pressure gradient on the slab; the projected field is gathered on every rank
 		// the copies of the previous step's field (stream3) have left before the gradient overwrites their source
 		if ((rc = xfer_join(s)) || (rc = fs3i_sor_wait(s, s->sor_e0 + 2u * (uint32_t)I)) || (rc = fs3i_project_gradient(s, dt, true, true))) return rc;
