@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfluidsim3_b200.so")
-SOURCES = ["particles.cu", "levelset.cu", "p2g.cu", "project.cu", "shard.cu", "fs3_api.cu", "fs3_hooks.cu", "fs3_state.cu", "consumer.cu", "levelset_lines.cu"]
+SOURCES = ["particles.cu", "levelset.cu", "p2g.cu", "project.cu", "shard.cu", "fs3_api.cu", "fs3_hooks.cu", "fs3_state.cu", "consumer.cu", "levelset_lines.cu", "no_alloc.cu"]
 # -fmad=false: the reference is an MSVC /fp:precise build without FMA contraction; parity needs the same.
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-fmad=false",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-O2"]

@@ -30,7 +30,7 @@ ABI_SYMBOLS = [
     "fs3_phi_device", "fs3_blur_phi", "fs3_phi_blurred_device", "fs3_get_phi_blurred", "fs3_export_binned", "fs3_get_binned",
     "fs3_sample_phi", "fs3_sample_phi_device",
     "fs3_save_state", "fs3_load_state", "fs3_step_count", "fs3_state_file_info", "fs3_state_file_write", "fs3_state_file_read",
-    "fs3_state_checksum", "fs3_default_params", "fs3_get_divergence", "fs3_checksum",
+    "fs3_state_checksum", "fs3_default_params", "fs3_get_divergence", "fs3_checksum", "fs3_divergence_no_alloc",
 ]
 SHARD_HANDLE_BYTES = 128
 
@@ -95,6 +95,7 @@ def load_library():
         _lib.fs3_state_file_read.argtypes = [C.c_char_p, C.POINTER(Fs3StateInfo)] + [C.c_void_p] * 6
         _lib.fs3_get_divergence.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         _lib.fs3_checksum.argtypes = [C.c_void_p, C.POINTER(Fs3Check)]
+        _lib.fs3_divergence_no_alloc.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5
         _lib.fs3_sample_phi.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]
         _lib.fs3_sample_phi_device.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]
     return _lib

@@ -150,6 +150,19 @@ int fs3_stage_times(fs3_sim* s, float* ms, int cap); /* FS3_T_* order, last step
  * the sum of its squares accumulated in double.  Sharded handle: the rank's own cell planes only (combine: max of the
  * maxima, square root of the sum of the squared l2 values). */
 int fs3_get_divergence(fs3_sim* s, double* max_divergence, double* l2);
+/* The same metric WITHOUT any allocation and without a handle.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Inputs are DEVICE pointers to U, V, W, phi in the layouts above (on `device`), the output is a DEVICE pointer to
+ * two doubles: out[0] = maximum divergence, out[1] = L2 norm.  Two kernels are queued on `stream` (a cudaStream_t, NULL = the
+ * default stream) and the call returns without synchronising; it calls no cudaMalloc / cudaFree or any allocating routine.
+ * The block partial sums live in a fixed 1 MiB __device__ array inside the library (held by every GPU that loads the library
+ * until the process exits), which limits the grid to FS3_NO_ALLOC_MAX_CELLS cells: larger grids are rejected with
+ * FS3_ERR_INVALID (message through fs3_last_error(NULL)).  All calls share that array: calls that overlap on the GPU (different
+ * streams or host threads) race -- serialise them on one stream.  The first call on a device looks the array's device address
+ * up (cudaGetSymbolAddress); make that call once before starting a graph capture. */
+#define FS3_NO_ALLOC_MAX_CELLS (256 * 256 * 256)
+int fs3_divergence_no_alloc(int device, void* stream, int nx, int ny, int nz, const float* dev_U, const float* dev_V, const float* dev_W,
+                            const float* dev_phi, double* dev_out);
 /* Order-independent 64-bit fingerprints of the state, computed on the device (measurement hook: bench.py prints them as
  * `check`, and a sharded run must reproduce the single-GPU values exactly).  Every value is a sum modulo 2^64 of a mixed
  * per-element word, so the ranks' values of a sharded simulation ADD UP to the single-GPU value:
