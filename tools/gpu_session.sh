@@ -1,11 +1,13 @@
 #!/bin/bash
-# One bounded single-GPU session: GPU test suite, bench, live SOR traffic.  Usage: gpurun --timeout 1500 -- bash tools/gpu_session.sh <tag>
+# One bounded single-GPU session: the no-alloc test alone, the whole GPU suite, bench.  Usage: gpurun --timeout 1500 -- bash tools/gpu_session.sh <tag>
 tag=${1:-r02}
 mkdir -p gpurun_out
-nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv > gpurun_out/${tag}_gpu.txt 2>&1
-timeout 1200 python -m pytest tests -m gpu -x -q --durations=12 > gpurun_out/${tag}_tests.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${tag}_tests.log
-tail -25 gpurun_out/${tag}_tests.log
+timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q > gpurun_out/${tag}_noalloc_alone.log 2>&1; echo "alone rc=$?" >> gpurun_out/${tag}_noalloc_alone.log; tail -4 gpurun_out/${tag}_noalloc_alone.log
+timeout 1200 python -m pytest tests -m gpu -x -q --durations=8 > gpurun_out/${tag}_tests.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${tag}_tests.log
+tail -16 gpurun_out/${tag}_tests.log
 timeout 300 python bench.py --steps 10 --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"
-tail -c 3000 gpurun_out/${tag}_bench.json
-timeout 200 python tools/sor_traffic_gpm.py --out gpurun_out/${tag}_sor_traffic.json > gpurun_out/${tag}_gpm.log 2>&1; echo "gpm rc=$?"; tail -c 1500 gpurun_out/${tag}_gpm.log
-timeout 100 python bench.py --impl reference --grid 96 --steps 2 --warmup 0 > gpurun_out/${tag}_ref.json 2>&1; tail -c 800 gpurun_out/${tag}_ref.json
+python - <<PY
+import json
+d=json.loads(open("gpurun_out/${tag}_bench.json").read().strip().splitlines()[-1])
+print({k:d.get(k) for k in ("ms_per_step","value")}, "e2e", d["e2e"]["ms_per_step"], {k:round(v,3) for k,v in d["stage_ms_per_step"].items()}, "sor_us", round(d["roofline"]["avg_launch_us"],2), "cpu", d["cpu_baseline"])
+PY
