@@ -506,6 +506,7 @@ int fs3_set_velocity(fs3_sim* s, const float* U, const float* V, const float* W)
 int fs3_get_phi(fs3_sim* s, float* phi) {
 	ENTER(s);
 	if (!phi) return FS3_ERR_INVALID;
+	{ int rc = fs3i_field_wait(s); if (rc) return rc; }
 	FS3_CUDA(cudaMemcpyAsync(phi, s->phi, s->nC * 4, cudaMemcpyDeviceToHost, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	return FS3_OK;

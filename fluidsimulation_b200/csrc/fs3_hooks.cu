@@ -257,6 +257,7 @@ int fs3_get_closest(fs3_sim* s, int* closest) {
 	ENTER(s);
 	if (!closest) return FS3_ERR_INVALID;
 	if (!s->closest_valid) return fail(s, FS3_ERR_STATE, "no level set has been computed since the particles last moved");
+	{ int rc = fs3i_field_wait(s); if (rc) return rc; }
 	FS3_CUDA(cudaMemcpyAsync(closest, s->closest, s->nC * 4, cudaMemcpyDeviceToHost, s->stream));
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	return FS3_OK;

@@ -72,6 +72,7 @@ struct fs3_sim {
 	uint32_t ls_epoch;       // host counter: epoch of sweep m of the current call = ls_epoch + m + 1
 	int ls_sleep_ns;         // cap of the poll back-off
 	int ls_ntiles, ls_blocks, ls_levels;   // ls_levels = depth of the dependency DAG (critical path in tiles)
+	long long ls_nitems;     // (sweep, tile) items this handle's sweep kernel runs
 
 	// extrapolation scratch (sized for the largest face grid)
 	int* cdv[3];             // L1 distance, one slot per face grid

@@ -117,12 +117,13 @@ __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
 }
 // Polls with relaxed loads and a capped exponential back-off, then takes the acquire once the epoch is there.
 // false = gave up (another CTA aborted, or ~2 s without progress: never hang the GPU)
-__device__ __forceinline__ bool ls_wait(const uint32_t* f, uint32_t need, int* flags, unsigned sleep_max) {
-	if ((int32_t)(ld_acquire_u32(f) - need) >= 0) return true;
+// sys: the word is written by another GPU (a neighbouring rank's boundary tile)
+__device__ __forceinline__ bool ls_wait(const uint32_t* f, uint32_t need, int* flags, unsigned sleep_max, bool sys = false) {
+	if ((int32_t)((sys ? fs3_ld_acquire_sys(f) : ld_acquire_u32(f)) - need) >= 0) return true;
 	long long t0 = clock64();
 	unsigned ns = 32;
 	for (unsigned it = 1;; it++) {
-		if ((int32_t)(ld_relaxed_u32(f) - need) >= 0) break;
+		if ((int32_t)((sys ? fs3_ld_relaxed_sys(f) : ld_relaxed_u32(f)) - need) >= 0) break;
 		__nanosleep(ns);
 		ns = min(ns * 2, sleep_max);
 		if ((it & 255u) == 0) {
@@ -130,8 +131,22 @@ __device__ __forceinline__ bool ls_wait(const uint32_t* f, uint32_t need, int* f
 			if (clock64() - t0 > 4000000000LL) { flags[1] = 1; return false; }
 		}
 	}
-	return (int32_t)(ld_acquire_u32(f) - need) >= 0;
+	return (int32_t)((sys ? fs3_ld_acquire_sys(f) : ld_acquire_u32(f)) - need) >= 0;
 }
+
+// Where the sweeps' arrays live.  A z-slab sharded simulation sweeps the SAME global dataflow: tile layers are aligned to the
+// slabs (layer Tz belongs to rank Tz / lps), every rank runs the items of its own tiles on its own copy of the arrays (global
+// indexing), and a tile on a slab boundary hands its boundary plane of records and its completion epoch to the neighbouring
+// rank by storing them into that rank's arrays (NVLink peer stores, fence, release) -- the consumer only ever polls and reads
+// its own memory.  base[q] + off_x is array x of rank q (one arena layout for all ranks); a single-GPU handle has world = 1,
+// base[0] = nullptr and absolute addresses as offsets.  A lockstep group (all ranks in one process on one device) runs the
+// items of ALL ranks in one launch with the same code.
+struct LsCtx {
+	char* base[FS3_MAX_WORLD];
+	size_t off_rec, off_done, off_phi, off_closest;
+	int world, slab, lps;   // planes per slab, tile layers per slab
+	int sys;                // 1: neighbouring ranks are other GPUs (system-scope flag accesses)
+};
 
 __device__ __forceinline__ float ls_d2(float cx, float cy, float cz, float4 q) {
 	float dx = __fsub_rn(cx, q.x), dy = __fsub_rn(cy, q.y), dz = __fsub_rn(cz, q.z);
@@ -147,10 +162,10 @@ __device__ __forceinline__ unsigned long long ls_now() { unsigned long long t; a
 #endif
 
 #define LS_INF __int_as_float(0x7f800000)
-__global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __restrict__ rec, GridDims d, float radius,
-                                                                   const uint32_t* __restrict__ items, uint32_t* done, uint32_t* ticket,
+__global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(LsCtx C, GridDims d, float radius,
+                                                                   const uint32_t* __restrict__ items, uint32_t* ticket,
                                                                    uint32_t nitems, int ntx, int nty, int ntz, uint32_t epoch0,
-                                                                   int* __restrict__ flags, float* __restrict__ phi, int* __restrict__ closest, unsigned sleep_max) {
+                                                                   int* __restrict__ flags, unsigned sleep_max) {
 	extern __shared__ float4 ls_smem[];
 	__shared__ uint32_t s_ticket;
 	__shared__ unsigned s_planes[2];
@@ -171,9 +186,15 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 		const int m = (int)(it >> 27), Tx = (int)(it & 511u), Ty = (int)((it >> 9) & 511u), Tz = (int)((it >> 18) & 511u);
 		const int dx = (m & 1) ? -1 : 1, dy = (m & 2) ? -1 : 1, dz = (m & 4) ? -1 : 1;   // sweep order of S3D.cpp:306-416
 		const uint32_t E = epoch0 + (uint32_t)m + 1u;
-		const int x0 = Tx * LS_TX, y0 = Ty * LS_TY, z0 = Tz * LS_TZ;
-		const int wx = min(LS_TX, d.nx - x0), wy = min(LS_TY, d.ny - y0), wz = min(LS_TZ, d.nz - z0);
-		uint32_t* const mydone = done + ((size_t)Tx + (size_t)ntx * ((size_t)Ty + (size_t)nty * Tz));
+		// tile layer Tz = layer `lay` of rank q's slab; the arrays are rank q's copies
+		const int q = Tz / C.lps, lay = Tz - q * C.lps;
+		float4* const rec = reinterpret_cast<float4*>(C.base[q] + C.off_rec);
+		uint32_t* const done = reinterpret_cast<uint32_t*>(C.base[q] + C.off_done);
+		const int x0 = Tx * LS_TX, y0 = Ty * LS_TY, z0 = q * C.slab + lay * LS_TZ;
+		const int wx = min(LS_TX, d.nx - x0), wy = min(LS_TY, d.ny - y0), wz = min(LS_TZ, (q + 1) * C.slab - z0);
+		const size_t tile_idx = (size_t)Tx + (size_t)ntx * ((size_t)Ty + (size_t)nty * Tz);
+		uint32_t* const mydone = done + tile_idx;
+		const bool peer_dn = lay == 0 && q > 0, peer_up = lay == C.lps - 1 && q < C.world - 1;   // neighbouring ranks below / above this tile
 		// ---- own cells are final once this tile has completed sweep m-1: start their copy first ----------
 		bool ok = true;
 		if (tid == 0) ok = ls_wait(mydone, E - 1u, flags, sleep_max);
@@ -192,7 +213,8 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 			const int qx = Tx + (ax == 0 ? sgn : 0), qy = Ty + (ax == 1 ? sgn : 0), qz = Tz + (ax == 2 ? sgn : 0);
 			const int dir = ax == 0 ? dx : (ax == 1 ? dy : dz);
 			if (qx >= 0 && qx < ntx && qy >= 0 && qy < nty && qz >= 0 && qz < ntz)
-				ok = ls_wait(done + ((size_t)qx + (size_t)ntx * ((size_t)qy + (size_t)nty * qz)), sgn == -dir ? E : E - 1u, flags, sleep_max);
+				ok = ls_wait(done + ((size_t)qx + (size_t)ntx * ((size_t)qy + (size_t)nty * qz)), sgn == -dir ? E : E - 1u, flags, sleep_max,
+				             C.sys && ax == 2 && (sgn < 0 ? peer_dn : peer_up));
 		}
 		if (!__syncthreads_and(ok)) break;
 		LS_MARK(2);
@@ -337,6 +359,11 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 		if (m == 7) {
 			// cells never reached keep their previous phi, as in the reference where m_Phi is only written
 			// together with closestParticles (S3D.cpp:248-251,296-299).  x fastest: coalesced stores.
+			float* const phi = reinterpret_cast<float*>(C.base[q] + C.off_phi);
+			int* const closest = reinterpret_cast<int*>(C.base[q] + C.off_closest);
+			// the projection of a neighbouring rank reads phi one plane into this slab: boundary tiles store that plane there too
+			float* const phi_dn = peer_dn ? reinterpret_cast<float*>(C.base[q - 1] + C.off_phi) : nullptr;
+			float* const phi_up = peer_up ? reinterpret_cast<float*>(C.base[q + 1] + C.off_phi) : nullptr;
 			__syncthreads();
 #pragma unroll
 			for (int i = 0; i < LS_TX * LS_TY * LS_TZ / LS_THREADS; i++) {
@@ -346,7 +373,12 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 					const int id = __float_as_int(sm[SMI(a, b, c)].w);
 					const size_t gi = (size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)(z0 + pz);
 					closest[gi] = id;
-					if (id >= 0) phi[gi] = __fsub_rn(sqrtf(m2s[SMI(a, b, c)]), radius);
+					if (id >= 0) {
+						const float ph = __fsub_rn(sqrtf(m2s[SMI(a, b, c)]), radius);
+						phi[gi] = ph;
+						if (phi_dn && pz == 0) phi_dn[gi] = ph;
+						if (phi_up && pz == wz - 1) phi_up[gi] = ph;
+					}
 				}
 			}
 		}
@@ -354,6 +386,26 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(float4* __r
 		LS_MARK(4);
 		__syncthreads();
 		if (tid == 0) { __threadfence(); st_release_u32(mydone, E); }
+		// ---- slab boundary: the plane the neighbouring rank reads as its upwind halo in this sweep direction goes into that
+		// rank's copy of the records, then this tile's epoch into its copy of the epochs (every sweep: its tiles also wait for
+		// "all six neighbours have finished the previous sweep") ---------------------------------------------------------------
+		if (peer_dn || peer_up) {
+			const int px = tid % LS_TX, py = tid / LS_TX;   // 16 x 16 cells of a plane, one per thread
+			if (px < wx && py < wy) {
+				const int a = dx < 0 ? wx - 1 - px : px, b = dy < 0 ? wy - 1 - py : py;
+				// (the physical top plane is the last one of an upward sweep, the physical bottom plane the last one of a downward sweep)
+				if (peer_up && dz > 0)     // read by the rank above in upward sweeps
+					reinterpret_cast<float4*>(C.base[q + 1] + C.off_rec)[(size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)(z0 + wz - 1)] = sm[SMI(a, b, wz - 1)];
+				if (peer_dn && dz < 0)     // read by the rank below in downward sweeps
+					reinterpret_cast<float4*>(C.base[q - 1] + C.off_rec)[(size_t)(x0 + px) + sY * (size_t)(y0 + py) + sZ * (size_t)z0] = sm[SMI(a, b, wz - 1)];
+			}
+			__threadfence_system();
+			__syncthreads();
+			if (tid == 0) {
+				if (peer_up) fs3_st_release_sys(reinterpret_cast<uint32_t*>(C.base[q + 1] + C.off_done) + tile_idx, E);
+				if (peer_dn) fs3_st_release_sys(reinterpret_cast<uint32_t*>(C.base[q - 1] + C.off_done) + tile_idx, E);
+			}
+		}
 		LS_MARK(5);
 	}
 #undef SMI
@@ -379,36 +431,63 @@ int fs3i_levelset(fs3_sim* s) {
 	return fs3i_levelset_sweeps(s);
 }
 
-// the 8 sweeps over the WHOLE grid (a sharded handle runs them replicated on the gathered seed records)
+// Sharded: the boundary tiles of the neighbouring ranks have finished the last sweep, i.e. their phi planes have landed here.
+__global__ void k_ls_wait_layers(const uint32_t* done, int ntiles_layer, size_t lo_first, size_t hi_first, int has_lo, int has_hi, uint32_t need, int* flags, int nospin) {
+	const int t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= ntiles_layer) return;
+	if (has_lo) fs3_flag_wait(done + lo_first + t, need, flags, nospin);
+	if (has_hi) fs3_flag_wait(done + hi_first + t, need, flags, nospin);
+}
+
+// The 8 sweeps.  world == 1: the whole grid.  Multi-process sharded handle: the items of this rank's tiles; the ranks' kernels
+// run at the same time on their GPUs and hand boundary planes and epochs to each other (see LsCtx).  Lockstep group: rank 0
+// launches ONE kernel over the items of all ranks (kernels of different ranks on one device could not wait for each other),
+// the other ranks only advance their epoch counters.
 int fs3i_levelset_sweeps(fs3_sim* s, cudaStream_t st) {
 	GridDims d{s->nx, s->ny, s->nz};
 	float radius = s->prm.particle_radius;
 	if (!st) st = s->stream;
 	if (s->prm.record_stage_times) cudaEventRecord(s->ev[FS3_T_LEVELSET_SWEEP], st);
-	int ntx = cdiv(d.nx, LS_TX), nty = cdiv(d.ny, LS_TY), ntz = cdiv(d.nz, LS_TZ);
-	FS3_CUDA(cudaMemsetAsync(s->ls_ticket, 0, sizeof(uint32_t), st));
+	const int slab = s->nz / s->world, lps = cdiv(slab, LS_TZ);
+	int ntx = cdiv(d.nx, LS_TX), nty = cdiv(d.ny, LS_TY), ntz = s->world * lps;
+	if (s->ls_nitems > 0) {
+		LsCtx C;
+		for (int r = 0; r < FS3_MAX_WORLD; r++) C.base[r] = s->world > 1 && r < s->world ? s->peer_base[r] : nullptr;
+		const char* origin = s->world > 1 ? s->arena : nullptr;
+		C.off_rec = (size_t)((char*)s->ls_rec - origin); C.off_done = (size_t)((char*)s->ls_done - origin);
+		C.off_phi = (size_t)((char*)s->phi - origin); C.off_closest = (size_t)((char*)s->closest - origin);
+		C.world = s->world; C.slab = slab; C.lps = lps; C.sys = (s->world > 1 && !s->lockstep) ? 1 : 0;
+		FS3_CUDA(cudaMemsetAsync(s->ls_ticket, 0, sizeof(uint32_t), st));
 #ifdef FS3_LS_TRACE
-	static unsigned long long* trace_dev = nullptr;
-	const size_t trace_n = (size_t)8 * s->ls_ntiles * 8;
-	if (!trace_dev) { FS3_CUDA(cudaMalloc((void**)&trace_dev, trace_n * 8)); FS3_CUDA(cudaMemcpyToSymbol(g_ls_trace, &trace_dev, sizeof(trace_dev))); }
-	FS3_CUDA(cudaMemsetAsync(trace_dev, 0, trace_n * 8, st));
+		static unsigned long long* trace_dev = nullptr;
+		const size_t trace_n = (size_t)s->ls_nitems * 8;
+		if (!trace_dev) { FS3_CUDA(cudaMalloc((void**)&trace_dev, trace_n * 8)); FS3_CUDA(cudaMemcpyToSymbol(g_ls_trace, &trace_dev, sizeof(trace_dev))); }
+		FS3_CUDA(cudaMemsetAsync(trace_dev, 0, trace_n * 8, st));
 #endif
-	k_ls_sweep_dataflow<<<s->ls_blocks, LS_THREADS, LS_SMEM_BYTES, st>>>(
-	    s->ls_rec, d, radius, s->ls_order, s->ls_done, s->ls_ticket, 8u * (uint32_t)s->ls_ntiles, ntx, nty, ntz, s->ls_epoch, s->dev_flags, s->phi,
-	    s->closest, (unsigned)s->ls_sleep_ns);
-	FS3_LAUNCH_CHECK();
-	s->ls_epoch += 8;
-	s->closest_valid = true;
+		k_ls_sweep_dataflow<<<s->ls_blocks, LS_THREADS, LS_SMEM_BYTES, st>>>(C, d, radius, s->ls_order, s->ls_ticket, (uint32_t)s->ls_nitems, ntx, nty, ntz, s->ls_epoch,
+		                                                                      s->dev_flags, (unsigned)s->ls_sleep_ns);
+		FS3_LAUNCH_CHECK();
 #ifdef FS3_LS_TRACE
-	if (const char* path = getenv("FS3_LS_TRACE_FILE")) {
-		std::vector<unsigned long long> h(trace_n);
-		std::vector<uint32_t> ord((size_t)8 * s->ls_ntiles);
-		FS3_CUDA(cudaStreamSynchronize(st));
-		FS3_CUDA(cudaMemcpy(h.data(), trace_dev, trace_n * 8, cudaMemcpyDeviceToHost));
-		FS3_CUDA(cudaMemcpy(ord.data(), s->ls_order, ord.size() * 4, cudaMemcpyDeviceToHost));
-		if (FILE* fp = fopen(path, "wb")) { fwrite(h.data(), 8, trace_n, fp); fwrite(ord.data(), 4, ord.size(), fp); fclose(fp); }
+		if (const char* path = getenv("FS3_LS_TRACE_FILE")) {
+			std::vector<unsigned long long> h(trace_n);
+			std::vector<uint32_t> ord((size_t)s->ls_nitems);
+			FS3_CUDA(cudaStreamSynchronize(st));
+			FS3_CUDA(cudaMemcpy(h.data(), trace_dev, trace_n * 8, cudaMemcpyDeviceToHost));
+			FS3_CUDA(cudaMemcpy(ord.data(), s->ls_order, ord.size() * 4, cudaMemcpyDeviceToHost));
+			if (FILE* fp = fopen(path, "wb")) { fwrite(h.data(), 8, trace_n, fp); fwrite(ord.data(), 4, ord.size(), fp); fclose(fp); }
+		}
+#endif
 	}
-#endif
+	s->ls_epoch += 8;
+	if (s->world > 1 && !s->lockstep) {
+		// phi one plane beyond the slab (read by the projection) is stored by the neighbours' boundary tiles in their last sweep
+		const int per_layer = ntx * nty;
+		const bool lo = s->rank > 0, hi = s->rank < s->world - 1;
+		k_ls_wait_layers<<<cdiv(per_layer, 128), 128, 0, st>>>(s->ls_done, per_layer, (size_t)per_layer * (size_t)(lo ? s->rank * lps - 1 : 0),
+		                                                       (size_t)per_layer * (size_t)(hi ? (s->rank + 1) * lps : 0), lo ? 1 : 0, hi ? 1 : 0, s->ls_epoch, s->dev_flags, 0);
+		FS3_LAUNCH_CHECK();
+	}
+	s->closest_valid = true;
 	return FS3_OK;
 }
 
@@ -443,7 +522,9 @@ int fs3i_levelset_join(fs3_sim* s) {
 // strictly smaller level), so ticket order is deadlock-free, and it lets sweep m+1 start behind sweep m as
 // soon as the DAG allows instead of after it.
 int fs3i_levelset_init(fs3_sim* s) {
-	const int ntx = cdiv(s->nx, LS_TX), nty = cdiv(s->ny, LS_TY), ntz = cdiv(s->nz, LS_TZ);
+	// tile layers are aligned to the z-slabs (world == 1: one slab), so that every tile belongs to exactly one rank
+	const int slab = s->nz / s->world, lps = cdiv(slab, LS_TZ);
+	const int ntx = cdiv(s->nx, LS_TX), nty = cdiv(s->ny, LS_TY), ntz = s->world * lps;
 	if (ntx > 511 || nty > 511 || ntz > 511) { s->err = "grid too large for the level-set tile table"; return FS3_ERR_INVALID; }
 	const int nt = ntx * nty * ntz;
 	auto tid = [&](int x, int y, int z) { return x + ntx * (y + nty * z); };
@@ -477,10 +558,19 @@ int fs3i_levelset_init(fs3_sim* s) {
 		prev = cur;
 	}
 	std::stable_sort(items.begin(), items.end(), [](const std::pair<int, uint32_t>& a, const std::pair<int, uint32_t>& b) { return a.first < b.first; });
-	std::vector<uint32_t> ord(items.size());
-	for (size_t i = 0; i < items.size(); i++) ord[i] = items[i].second;
+	// The items this handle launches, in the order of the GLOBAL dependency DAG: all of them on one GPU and on rank 0 of a
+	// lockstep group, the tiles of the own slab on a multi-process rank (every rank then draws its items in an order in which
+	// each dependency, local or on another rank, precedes its dependants: no deadlock), none on the other lockstep ranks.
+	std::vector<uint32_t> ord;
+	ord.reserve(items.size());
+	for (size_t i = 0; i < items.size(); i++) {
+		const int owner = (int)((items[i].second >> 18) & 511u) / lps;
+		if (s->world == 1 || (s->lockstep ? s->rank == 0 : owner == s->rank)) ord.push_back(items[i].second);
+	}
+	s->ls_nitems = (long long)ord.size();
+	if (ord.empty()) ord.push_back(0u);
 	int rc;
-	if ((rc = fs3i_alloc(s, (void**)&s->ls_order, sizeof(uint32_t) * ord.size()))) return rc;
+	if ((rc = fs3i_alloc(s, (void**)&s->ls_order, sizeof(uint32_t) * 8 * (size_t)nt))) return rc;   // (same size on every rank: one arena layout)
 	if ((rc = fs3i_alloc(s, (void**)&s->ls_done, sizeof(uint32_t) * nt))) return rc;
 	if ((rc = fs3i_alloc(s, (void**)&s->ls_ticket, sizeof(uint32_t)))) return rc;
 	FS3_CUDA(cudaMemcpyAsync(s->ls_order, ord.data(), sizeof(uint32_t) * ord.size(), cudaMemcpyHostToDevice, s->stream));
@@ -504,11 +594,12 @@ int fs3i_levelset_init(fs3_sim* s) {
 	// extrapolation stage already ends with the join (sweeps 3.87 ms + the seed barrier = gather 1.57 + extrapolation 2.99) --
 	// so 1.25 per SM on 2 ranks (measured), 1.5 on 3-4 (by the same timeline: sweeps + barrier 4.4 ms against gather +
 	// extrapolation 5.2 ms at N = 4) and the measured 2 per SM above.
-	per_sm = std::min(occ, s->world == 1 ? 1 : 2);
+	// One CTA per SM: the sweeps run beside the P2G gather and the extrapolation and should take as little from them as
+	// possible (a multi-process rank only runs its own slab's tiles, 1 / world of the work per dependency level); rank 0 of a
+	// lockstep group runs every rank's items and gets two.
+	per_sm = std::min(occ, (s->world > 1 && s->lockstep) ? 2 : 1);
 	s->ls_sleep_ns = 256;
 	long long blocks = (long long)std::max(1, per_sm) * sms;
-	if (s->world > 1 && s->world <= 4 && occ >= 2) blocks = s->world == 2 ? (5LL * sms) / 4 : (3LL * sms) / 2;
-	// (the ticket scheme needs no co-residency: any grid size is valid)
-	s->ls_blocks = (int)std::min<long long>(blocks, 8LL * nt);
+	s->ls_blocks = (int)std::max<long long>(1, std::min<long long>(blocks, s->ls_nitems));
 	return FS3_OK;
 }

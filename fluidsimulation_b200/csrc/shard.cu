@@ -9,14 +9,17 @@
 //   * particle migration: emigrants are packed per destination and copied to the tail of the destination's live range;
 //   * ghost layers for the P2G gather: one cell layer of sorted particles + its cell_start rows is PULLED from each
 //     neighbour and spliced in directly below / above the own range, so the gather kernel is unchanged;
-//   * slab all-gathers (seed records, P2G result, projected field): each rank copies its slab into every peer.
+//   * level-set sweeps: ONE dataflow over all ranks' tiles; a tile on a slab boundary stores its boundary plane of records, its
+//     phi plane and its completion epoch into the neighbouring rank's arrays (levelset.cu, LsCtx);
+//   * P2G result and projected field: the planes inside the neighbours' extrapolation window / velocity halo go to those
+//     neighbours; whole slabs (projected field, phi, closest) follow on a copy stream behind a second flag, for the getters.
 // Ordering is by epoch flags in device memory written with st.release.sys by the producer and polled by a one-warp
 // kernel (or the sweep kernel's first warp) of the consumer.  A step is a fixed sequence of PHASES, each "wait, work,
 // signal"; a multi-process handle runs them back to back on its stream, a lockstep group (all ranks in one process on one
 // stream, for single-GPU testing) runs phase k of every rank before phase k+1, which satisfies every wait by stream
 // order -- waits then never spin and a wait that is not already satisfied is reported as an error (flags[2]).
-// The two stages with a sequential dependence along z (the 8 Gauss-Seidel level-set sweeps and the layered
-// extrapolation) run REPLICATED on gathered inputs; everything else runs on the slab.
+// Nothing runs replicated: the 8 Gauss-Seidel level-set sweeps are pipelined across the slabs tile by tile, and the layered
+// extrapolation runs on a window of FS3_EX_DEPTH planes around the slab, which is exact for every node the step consumes (p2g.cu).
 #include "fs3_internal.cuh"
 #include <algorithm>
 
@@ -315,18 +318,15 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 		if ((rc = fs3i_bin(s))) return rc;
 		return fs3i_signal(s);
 	}
-	if (ph == 3) {          // neighbours are sorted: ghost layers; level-set seed of the slab, gathered on every rank (stream3)
+	if (ph == 3) {          // neighbours are sorted: ghost layers; level-set seed of the slab
 		if ((rc = fs3i_wait(s)) || (rc = fs3i_ghost_pull(s)) || (rc = fs3i_levelset_seed(s))) return rc;
-		cudaStream_t xs;
-		if ((rc = xfer_begin(s, &xs)) || (rc = push_planes(s, s->ls_rec, pC, sizeof(float4), s->z0, s->z1, xs))) return rc;
-		if ((rc = fs3i_signal(s, xs))) return rc;
-		// this rank's seed records have left before the sweeps (which update ls_rec in place) may start
+		// the copies of the previous step's phi / closest slabs (stream3) have left before the sweeps rewrite them
 		if (!s->lockstep) { FS3_CUDA(cudaEventRecord(s->ev_xfer, s->stream3)); FS3_CUDA(cudaStreamWaitEvent(s->stream2, s->ev_xfer, 0)); }
 		return FS3_OK;
 	}
-	if (ph == 4) {          // the 8 sweeps start on stream2 as soon as every rank's seeds are here (replicated); meanwhile P2G of
-		                    // the slab's face nodes on the main stream, gathered on every rank (stream3)
-		if ((rc = fs3i_levelset_fork(s, true))) return rc;
+	if (ph == 4) {          // the 8 sweeps of the slab's tiles start on stream2 (they exchange boundary planes with the neighbours' sweep
+		                    // kernels while they run); meanwhile P2G of the slab's face nodes on the main stream
+		if ((rc = fs3i_levelset_fork(s, false))) return rc;
 		// no wait on the main stream: the gather reads this rank's particles + ghost layers only.  Each face grid leaves as soon as
 		// it is done (while the next one is gathered); invalid nodes travel as tagged NaNs, so the validity needs no copy of its own.
 		// Only the ranks whose extrapolation window (FS3_EX_DEPTH planes around their slab) reaches into this slab get planes.
@@ -347,7 +347,7 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 		}
 		return fs3i_signal(s, xs);
 	}
-	if (ph == 5) {          // extrapolation (replicated) beside the sweeps; pressure system of the slab; tell the neighbours it is set up
+	if (ph == 5) {          // extrapolation of the slab window beside the sweeps; pressure system of the slab; tell the neighbours it is set up
 		// own outgoing copies are complete before the extrapolation overwrites the arrays they read
 		if ((rc = xfer_join(s)) || (rc = fs3i_wait(s)) || (rc = fs3i_cd_from_tags(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_levelset_join(s)) ||
 		    (rc = fs3i_project_setup(s, dt, true, true)) || (rc = fs3i_sor_prepare(s)))
@@ -383,7 +383,8 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 		    (rc = push_overlap(s, s->W, pW * 4, w_a, w_b, near, need_w, xs)) || (rc = fs3i_flag_signal(s, near, FS3_BAR_XNEAR, s->xfer_epoch, xs)))
 			return rc;
 		if ((rc = push_overlap(s, s->U, pU * 4, s->z0, s->z1, all, need_all_c, xs)) || (rc = push_overlap(s, s->V, pV * 4, s->z0, s->z1, all, need_all_c, xs)) ||
-		    (rc = push_overlap(s, s->W, pW * 4, w_a, w_b, all, need_all_w, xs)) || (rc = fs3i_flag_signal(s, all, FS3_BAR_XALL, s->xfer_epoch, xs)))
+		    (rc = push_overlap(s, s->W, pW * 4, w_a, w_b, all, need_all_w, xs)) || (rc = push_overlap(s, s->phi, pC * 4, s->z0, s->z1, all, need_all_c, xs)) ||
+		    (rc = push_overlap(s, s->closest, pC * 4, s->z0, s->z1, all, need_all_c, xs)) || (rc = fs3i_flag_signal(s, all, FS3_BAR_XALL, s->xfer_epoch, xs)))
 			return rc;
 		return FS3_OK;
 	}
