@@ -532,6 +532,9 @@ int fs3_set_params(fs3_sim* s, const fs3_params* p) {
 	if (p->levelset_mode != 0 && p->levelset_mode != 1) return fail(s, FS3_ERR_INVALID, "levelset_mode must be 0 or 1");
 	if (p->extrapolation_mode != 0 && p->extrapolation_mode != 1) return fail(s, FS3_ERR_INVALID, "extrapolation_mode must be 0 or 1");
 	if (p->levelset_mode == 1 && s->world > 1) return fail(s, FS3_ERR_STATE, "the line-sweep level set (levelset_mode 1) is not available on a sharded handle");
+	// the slab-window extrapolation of a sharded handle is exact for the nodes the step consumes as long as fluid cells lie within
+	// one cell of a particle (p2g.cu, FS3_EX_DEPTH)
+	if (s->world > 1 && !(p->particle_radius <= 1.0f)) return fail(s, FS3_ERR_STATE, "particle_radius > 1 is not available on a sharded handle (extrapolation window)");
 	FS3_CUDA(cudaStreamSynchronize(s->stream));
 	s->prm = *p;
 	return fs3i_alloc_pressure(s);

@@ -77,10 +77,19 @@ __device__ __forceinline__ unsigned long long fs3_mix64(unsigned long long x) { 
 	x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull; x ^= x >> 27; x *= 0x94d049bb133111ebull; x ^= x >> 31;
 	return x;
 }
+// sum over the block (256 threads), then one atomic per block: integer addition modulo 2^64 is order-independent
 __device__ __forceinline__ void fs3_warp_add_u64(unsigned long long v, unsigned long long* dst) {
+	__shared__ unsigned long long s_w[8];
 #pragma unroll
 	for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-	if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst, v);   // integer addition modulo 2^64: order-independent
+	__syncthreads();   // (s_w may still be read from the previous call)
+	if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		unsigned long long t = 0;
+		for (int k = 0; k < 8; k++) t += s_w[k];
+		if (t) atomicAdd(dst, t);
+	}
 }
 __global__ void __launch_bounds__(256) k_check_particles(const float4* __restrict__ pos, const float4* __restrict__ vel, long long np, GridDims d,
                                                          unsigned long long* __restrict__ out) {
