@@ -286,9 +286,7 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(LsCtx C, Gr
 		// (:248) -- with "no record" and "no candidate" at distance +inf both are one comparison.
 		// Fast path, branch-free, in squared distances: q2 >= m2 can never win (sqrt and "- radius" are monotonic)
 		// and q2 < m2 by more than 2^-21 relative with sqrt(m2) >= 0.5 always wins (the sqrt values differ by >= 1 ulp
-		// and sqrt(m2) - 1 is exact); below that (both roots < 0.5, the common case inside the fluid; radius == 1 only)
-		// q2 < m2 - 2^-22 always wins: the roots differ by > 2^-22 - 2^-25 and rounding root - 1 to the 2^-24 grid of
-		// (-1, -0.5] moves each side by at most 2^-25.  A comparison that falls between the two marks the step ambiguous and the
+		// and sqrt(m2) - 1 is exact).  A comparison that falls between the two marks the step ambiguous and the
 		// whole warp repeats it with the reference's full expression (warp-uniform branch, rare).
 		// Idle threads compute garbage on a clamped cell of their own line and store nothing; only the 128 line
 		// threads take part (named barrier 1).
@@ -302,23 +300,13 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(LsCtx C, Gr
 			float4* const grow = rec + (sY * (size_t)gy + sZ * (size_t)gz);
 			uint32_t chg = 0;
 			const int nsteps = wx + wy + wz - 2;
-			// Only the y and z candidates come from other threads: the x candidate is this thread's own result of the previous
-			// hyperplane (kept in a register) and the cell's own record is fetched one hyperplane ahead (the cells of a line are
-			// written by its thread only), so that after the barrier a step starts with two shared-memory loads, not five.
-			float4 prevrec = none, pre_mine = none;
-			float pre_m2 = 0.f;
-			int prev_a = -1000, pre_a = -1000;
-			const bool fast_small = radius == 1.0f;
 			for (int s = __ffsll((long long)planes) - 1; s < nsteps; s++) {
 				const int a = s - b - c;
 				const bool act = line_in && (unsigned)a < (unsigned)wx;
 				const int ac = min(max(a, 0), LS_TX - 1);
 				const float4* q = sm + li + ac;
-				const float4 Y = q[-LS_PX], Z = q[-LS_PX * LS_PY];
-				float4 mine0 = pre_mine, X = prevrec;
-				float m20 = pre_m2;
-				if (pre_a != ac) { mine0 = q[0]; m20 = m2s[li + ac]; }
-				if (prev_a != ac - 1) X = q[-1];
+				const float4 mine0 = q[0], X = q[-1], Y = q[-LS_PX], Z = q[-LS_PX * LS_PY];
+				const float m20 = m2s[li + ac];
 				const float cxf = (float)(gx0 + dx * ac);
 				// a candidate with index <= 0 is never propagated (S3D.cpp:242): infinitely far
 				const float x2 = __float_as_int(X.w) > 0 ? ls_d2(cxf, cyf, czf, X) : LS_INF;
@@ -329,7 +317,7 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(LsCtx C, Gr
 				bool changed = false, amb = false;
 #define LS_FAST(Q, q2)                                                                                                        \
 	{                                                                                                                        \
-		const bool take = m2 >= 0.25f ? q2 < __fmul_rn(m2, 0.99999905f) : (fast_small && q2 < __fsub_rn(m2, 2.5e-7f));       \
+		const bool take = m2 >= 0.25f && q2 < __fmul_rn(m2, 0.99999905f);                                                    \
 		amb |= !take && q2 < m2;                                                                                             \
 		mine.x = take ? Q.x : mine.x; mine.y = take ? Q.y : mine.y; mine.z = take ? Q.z : mine.z; mine.w = take ? Q.w : mine.w; \
 		m2 = take ? q2 : m2; changed |= take;                                                                                \
@@ -353,10 +341,6 @@ __global__ void __launch_bounds__(LS_THREADS, 3) k_ls_sweep_dataflow(LsCtx C, Gr
 				}
 				// global write-back is deferred past the loop: a store in flight would put an L2 round trip into every step
 				if (act && changed) { sm[li + a] = mine; m2s[li + a] = m2; chg |= 1u << a; }
-				// carried into the next hyperplane: this cell's final record (its x candidate), and that cell's own record
-				prevrec = mine; prev_a = a == ac ? a : -1000;
-				pre_a = min(max(a + 1, 0), LS_TX - 1);
-				pre_mine = sm[li + pre_a]; pre_m2 = m2s[li + pre_a];
 				// barrier among the 128 line threads + "did any record change in this hyperplane"
 				int any;
 				asm volatile("{\n .reg .pred p, q;\n setp.ne.u32 q, %1, 0;\n barrier.red.or.pred p, 1, %2, q;\n selp.u32 %0, 1, 0, p;\n}\n"
