@@ -586,18 +586,13 @@ int fs3i_levelset_init(fs3_sim* s) {
 	FS3_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
 	// Resident CTAs beyond what the DAG can keep busy only add pollers.
 	const int occ = std::max(1, per_sm);
-	// The sweep is bound by its critical path, not by throughput.  Single GPU: one CTA per SM, because the sweeps run beside
-	// the P2G gather and the extrapolation (fs3_step) and should take as little from them as possible.  Sharded: the replicated
-	// sweeps run beside the slab's gather and the replicated extrapolation and must end with them; measured at 256^3 on 2 GPUs
-	// with 2 / 1.5 / 1.25 / 1 CTAs per SM: sweeps 3.85 / 4.14 / 4.58 / 5.34 ms, step 13.56 / 12.88 / 12.69 / 13.18 ms.  The
-	// sweeps' slack shrinks with the world size (the gather gets shorter, the sweeps do not) and is gone at 8 ranks -- there the
-	// extrapolation stage already ends with the join (sweeps 3.87 ms + the seed barrier = gather 1.57 + extrapolation 2.99) --
-	// so 1.25 per SM on 2 ranks (measured), 1.5 on 3-4 (by the same timeline: sweeps + barrier 4.4 ms against gather +
-	// extrapolation 5.2 ms at N = 4) and the measured 2 per SM above.
-	// One CTA per SM: the sweeps run beside the P2G gather and the extrapolation and should take as little from them as
-	// possible (a multi-process rank only runs its own slab's tiles, 1 / world of the work per dependency level); rank 0 of a
-	// lockstep group runs every rank's items and gets two.
-	per_sm = std::min(occ, (s->world > 1 && s->lockstep) ? 2 : 1);
+	// The sweep is bound by its critical path, not by throughput, and it runs beside the P2G gather and the extrapolation
+	// (fs3_step), which are issue-bound: resident sweep CTAs beyond what the DAG keeps busy only add pollers and take issue slots
+	// from that chain (measured round 1, one GPU: 19.55 -> 18.9 ms per step with one CTA per SM instead of two).  There is also
+	// a hard reason for ONE CTA per SM: a sweep CTA holds 256 x 80 registers until the last item is done, and a P2G CTA needs
+	// 512 x 64 -- beside two resident sweep CTAs no P2G CTA fits on the SM at all, and the gather would run after the sweeps
+	// instead of beside them.  A sharded rank runs 1 / world of the tiles per dependency level, so one CTA per SM is plenty.
+	per_sm = std::min(occ, 1);
 	s->ls_sleep_ns = 256;
 	long long blocks = (long long)std::max(1, per_sm) * sms;
 	s->ls_blocks = (int)std::max<long long>(1, std::min<long long>(blocks, s->ls_nitems));
