@@ -111,7 +111,7 @@ static int create_common(int nx, int ny, int nz, float cpm, int device, int rank
 	s->sor_list_valid = false; s->sm_count = prop.multiProcessorCount; s->sor_per_sm = 0; s->persist_cap = -1;
 	s->alloc_precision = -1; s->res_cap = 4096; s->res_count = 0; s->stage_ptr = nullptr; s->stage_bytes = 0;
 	s->rank = rank; s->world = world; s->z0 = rank * (nz / world); s->z1 = s->z0 + nz / world; s->lockstep = lockstep;
-	s->bar_epoch = 0; s->sor_epoch = 0; s->xfer_epoch = 0; s->sor_e0 = 0; s->n_ipc_opened = 0; s->poff = 0; s->gcap = 0; s->mig_cap = 0;
+	s->bar_epoch = 0; s->sor_epoch = 0; s->xfer_epoch = 0; s->gather_epoch = 0; s->field_dirty = false; s->sor_e0 = 0; s->n_ipc_opened = 0; s->poff = 0; s->gcap = 0; s->mig_cap = 0;
 	for (int k = 0; k < FS3_T_COUNT; k++) s->stage_ms[k] = 0.f;
 	const long long P = std::max(1LL, 8LL * (nz - 2) * (ny - 2) * (nx - 1 - nx / 2));
 	long long cap = P;

@@ -126,7 +126,9 @@ struct fs3_sim {
 	uint32_t* h_pin;           // pinned host scratch (count matrix)
 	uint32_t* bar;             // [r] barrier epoch written by rank r; [FS3_MAX_WORLD+0/1] SOR epoch of the lower/upper neighbour
 	uint32_t bar_epoch, sor_epoch;
-	uint32_t xfer_epoch;       // steps whose projected field this rank has pushed (identical on all ranks)
+	uint32_t xfer_epoch;       // steps whose velocity halo this rank has pushed (identical on all ranks)
+	uint32_t gather_epoch;     // whole-slab gathers made for the whole-grid getters (identical on all ranks: the getters are collective)
+	bool field_dirty;          // a step has run since the last gather
 	uint32_t* sor_done;        // block counter of the fused end-of-sweep signal
 	int sor_halves;            // half sweeps of the current fs3i_sor_loop call
 	bool ls_seed_forked;       // the seed of the current step ran on stream2 in front of the sweeps
@@ -336,6 +338,7 @@ int fs3i_wait(fs3_sim* s, cudaStream_t st = nullptr);                        // 
 int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes, cudaStream_t st = nullptr);
 int fs3i_flag_signal(fs3_sim* s, unsigned mask, int slot0, uint32_t epoch, cudaStream_t st = nullptr);
 int fs3i_flag_wait(fs3_sim* s, unsigned mask, int slot0, uint32_t epoch, cudaStream_t st = nullptr);
+int fs3i_field_push(fs3_sim* s, cudaStream_t st);
 int fs3i_field_wait(fs3_sim* s);                                            // whole-grid getters: every rank's slab of the projected field has landed
 int fs3i_velocity_halo(const fs3_sim* s);   // copy a range of one of my arrays into the same range of every peer
 int fs3i_sor_signal(fs3_sim* s);                                            // "system set up": first SOR epoch of this projection to both neighbours

@@ -118,11 +118,6 @@ int fs3i_flag_wait(fs3_sim* s, unsigned mask, int slot0, uint32_t epoch, cudaStr
 }
 // The projected field of the last step is complete on this rank once every other rank's copy of its slab has landed (the
 // copies run on the senders' copy streams behind the step): what the whole-grid getters wait for.
-int fs3i_field_wait(fs3_sim* s) {
-	if (s->world < 2 || !s->xfer_epoch) return FS3_OK;
-	return fs3i_flag_wait(s, (1u << s->world) - 1u, FS3_BAR_XALL, s->xfer_epoch, nullptr);
-}
-
 // My planes [a, b) of a z-slowest array go to every rank in `mask` whose range of needed planes [lo(r), hi(r)) overlaps them.
 template <typename F> static int push_overlap(fs3_sim* s, void* arr, size_t plane_bytes, int a, int b, unsigned mask, F need, cudaStream_t st) {
 	for (int k = 1; k < s->world; k++) {
@@ -137,6 +132,32 @@ template <typename F> static int push_overlap(fs3_sim* s, void* arr, size_t plan
 	}
 	return FS3_OK;
 }
+// this rank's slab of the projected field, phi and closest into every rank's arrays, then the "whole slab pushed" flag
+int fs3i_field_push(fs3_sim* s, cudaStream_t st) {
+	const size_t pU = (size_t)(s->nx + 1) * s->ny, pV = (size_t)s->nx * (s->ny + 1), pW = (size_t)s->nx * s->ny, pC = pW;
+	const unsigned all = (1u << s->world) - 1u;
+	const int nz = s->nz, w_a = s->rank == 0 ? 0 : s->z0 + 1, w_b = s->z1 + 1;
+	auto need_all_c = [=](int, int* lo, int* hi) { *lo = 0; *hi = nz; };
+	auto need_all_w = [=](int, int* lo, int* hi) { *lo = 0; *hi = nz + 1; };
+	int rc;
+	s->gather_epoch++;
+	if ((rc = push_overlap(s, s->U, pU * 4, s->z0, s->z1, all, need_all_c, st)) || (rc = push_overlap(s, s->V, pV * 4, s->z0, s->z1, all, need_all_c, st)) ||
+	    (rc = push_overlap(s, s->W, pW * 4, w_a, w_b, all, need_all_w, st)) || (rc = push_overlap(s, s->phi, pC * 4, s->z0, s->z1, all, need_all_c, st)) ||
+	    (rc = push_overlap(s, s->closest, pC * 4, s->z0, s->z1, all, need_all_c, st)) || (rc = fs3i_flag_signal(s, all, FS3_BAR_XALL, s->gather_epoch, st)))
+		return rc;
+	s->field_dirty = false;
+	return FS3_OK;
+}
+// Whole-grid getters of a sharded handle (COLLECTIVE: every rank calls them in the same order): each rank pushes its slab to
+// all the others if a step has run since the last gather, then waits until every other rank's slab has landed.
+int fs3i_field_wait(fs3_sim* s) {
+	if (s->world < 2) return FS3_OK;
+	int rc;
+	if (s->field_dirty && (rc = fs3i_field_push(s, s->stream))) return rc;
+	if (!s->gather_epoch) return FS3_OK;
+	return fs3i_flag_wait(s, (1u << s->world) - 1u, FS3_BAR_XALL, s->gather_epoch, nullptr);
+}
+
 // ranks (other than this one) whose slab lies within `halo` planes of this rank's slab
 static unsigned near_mask(const fs3_sim* s, int halo) {
 	const int slab = s->nz / s->world;
@@ -148,9 +169,9 @@ static unsigned near_mask(const fs3_sim* s, int halo) {
 	}
 	return m;
 }
-// planes of the velocity halo: a rank reads the projected field up to one neighbouring slab (at least 8 planes) away from its
-// own -- Advect checks that no Runge-Kutta stage leaves that range (fs3i_advect)
-int fs3i_velocity_halo(const fs3_sim* s) { return std::max(s->nz / s->world, 8); }
+// planes of the velocity halo: a rank reads the projected field up to n / 8 planes (at most one neighbouring slab, at least 8
+// planes) away from its own: 16.7 m/s at dt = 0.01 whatever the grid.  Advect checks that no Runge-Kutta stage leaves that range.
+int fs3i_velocity_halo(const fs3_sim* s) { return std::max(8, std::min(s->nz / s->world, s->nz / 8)); }
 
 int fs3i_push(fs3_sim* s, void* ptr, size_t byte_off, size_t bytes, cudaStream_t st) {
 	if (!bytes) return FS3_OK;
@@ -367,25 +388,23 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 		// the copies of the previous step's field (stream3) have left before the gradient overwrites their source
 		if ((rc = xfer_join(s)) || (rc = fs3i_sor_wait(s, s->sor_e0 + 2u * (uint32_t)I)) || (rc = fs3i_project_gradient(s, dt, true, true))) return rc;
 		// The gradient kernel of cell plane z writes the W faces z+1 (and z = 0 on rank 0): that is the range it owns here.
-		// On the copy stream: (1) the planes inside the neighbours' velocity halo + their flag -- all the next kernels of any
-		// rank read (FLIP blend, G2P, the next Advect); (2) the slab to everybody + a second flag, for the whole-grid getters.
+		// On the copy stream: the planes inside the neighbours' velocity halo + their flag -- all the next kernels of any rank
+		// read (FLIP blend, G2P, the next Advect).  Whole slabs only travel when a whole-grid getter asks (fs3i_field_wait).
 		const int hv = fs3i_velocity_halo(s), slab = s->nz / s->world, nz = s->nz;
-		const unsigned near = near_mask(s, hv), all = (1u << s->world) - 1u;
+		const unsigned near = near_mask(s, hv);
 		const int w_a = s->rank == 0 ? 0 : s->z0 + 1, w_b = s->z1 + 1;
 		auto need_c = [=](int r, int* lo, int* hi) { *lo = std::max(0, r * slab - hv); *hi = std::min(nz, (r + 1) * slab + hv); };
 		auto need_w = [=](int r, int* lo, int* hi) { *lo = std::max(0, r * slab - hv); *hi = std::min(nz + 1, (r + 1) * slab + hv + 1); };
-		auto need_all_c = [=](int, int* lo, int* hi) { *lo = 0; *hi = nz; };
-		auto need_all_w = [=](int, int* lo, int* hi) { *lo = 0; *hi = nz + 1; };
 		cudaStream_t xs;
 		if ((rc = xfer_begin(s, &xs))) return rc;
 		s->xfer_epoch++;
 		if ((rc = push_overlap(s, s->U, pU * 4, s->z0, s->z1, near, need_c, xs)) || (rc = push_overlap(s, s->V, pV * 4, s->z0, s->z1, near, need_c, xs)) ||
 		    (rc = push_overlap(s, s->W, pW * 4, w_a, w_b, near, need_w, xs)) || (rc = fs3i_flag_signal(s, near, FS3_BAR_XNEAR, s->xfer_epoch, xs)))
 			return rc;
-		if ((rc = push_overlap(s, s->U, pU * 4, s->z0, s->z1, all, need_all_c, xs)) || (rc = push_overlap(s, s->V, pV * 4, s->z0, s->z1, all, need_all_c, xs)) ||
-		    (rc = push_overlap(s, s->W, pW * 4, w_a, w_b, all, need_all_w, xs)) || (rc = push_overlap(s, s->phi, pC * 4, s->z0, s->z1, all, need_all_c, xs)) ||
-		    (rc = push_overlap(s, s->closest, pC * 4, s->z0, s->z1, all, need_all_c, xs)) || (rc = fs3i_flag_signal(s, all, FS3_BAR_XALL, s->xfer_epoch, xs)))
-			return rc;
+		s->field_dirty = true;
+		// a lockstep group gathers right away (its getters are called rank by rank, so they cannot wait for each other); a
+		// multi-process rank gathers when a whole-grid getter is called (fs3i_field_wait): nothing in a step reads those planes
+		if (s->lockstep) return fs3i_field_push(s, xs);
 		return FS3_OK;
 	}
 	if (ph == 7 + 2 * I) {  // PIC/FLIP blend (S3D.cpp:148-180), once the neighbours' halo planes of the projected field are here
