@@ -48,9 +48,13 @@ def main():
         run(one)
         merged = merge_particles(parts)
         same = lambda x, y: np.array_equal(np.ascontiguousarray(x).view(np.uint32), np.ascontiguousarray(y).view(np.uint32))
-        ok = same(merged, one.get_particles())
-        ok = ok and np.array_equal(np.concatenate(press).reshape(-1), one.get_pressure())
-        ok = ok and all(same(x, y) for x, y in zip(uvw, one.get_velocity())) and same(sim.get_phi(), one.get_phi())
+        checks = {"particles": same(merged, one.get_particles()), "pressure": np.array_equal(np.concatenate(press).reshape(-1), one.get_pressure())}
+        for nm, x, y in zip("UVW", uvw, one.get_velocity()):
+            checks[nm] = same(x, y)
+        checks["phi"] = same(sim.get_phi(), one.get_phi())
+        ok = all(checks.values())
+        if not ok:
+            print("rank 0: fields that differ from the single-GPU run:", [k for k, v in checks.items() if not v])
         print("rank 0: merged result %s the single-GPU run (%d^3, %d particles, %d steps, world %d, zflow %g, change of the ranks' particle counts %r)" % (
             "matches" if ok else "DIFFERS FROM", n, merged.shape[0], a.steps, world, a.zflow, moved))
         if a.zflow and not any(moved):

@@ -189,10 +189,12 @@ def test_group_reset_after_steps_and_hooks_refused():
     g.close()
 
 
-@pytest.mark.parametrize("world,n,steps,zflow", [(2, 24, 3, 0.0), (2, 32, 4, 4.0), (4, 64, 4, 4.0), (8, 96, 4, 4.0)])
+@pytest.mark.parametrize("world,n,steps,zflow", [(2, 24, 3, 0.0), (2, 24, 4, 4.0), (2, 32, 4, 4.0), (4, 64, 4, 4.0), (8, 96, 3, 2.0)])
 def test_multiprocess_sharded_step(world, n, steps, zflow):
     """One process per GPU over CUDA IPC: the merged result must equal the single-GPU run bit for bit.  With zflow the grid
     velocity W is forced before every step, so particles migrate between slabs and every rank's SOR halo carries fluid.
+    (The flow must not carry more than a slab's share of particles into the top slab: a slab's particle capacity is twice its even
+    share, so 8 ranks get a gentler flow -- 4 m/s for 4 steps at 96^3 pushes 15 planes of particles into the 12-plane top slab.)
     Needs `world` B200s (`gpurun --gpus N`); skipped on a box with fewer (ranks spin on each other's flags inside kernels and
     must not share a device)."""
     import torch
@@ -201,5 +203,5 @@ def test_multiprocess_sharded_step(world, n, steps, zflow):
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
                           "--master-port", str(29533 + world), os.path.join(ROOT, "tests", "shard_worker.py"), str(n), str(steps), "--zflow", str(zflow)],
                          capture_output=True, text=True, timeout=900)
-    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert out.returncode == 0, "\n".join(l for l in out.stdout.splitlines() if l.startswith("rank 0")) + out.stdout[-1500:] + out.stderr[-1500:]
     assert "SHARD_WORKER_OK" in out.stdout
