@@ -301,7 +301,8 @@ int fs3i_alloc_pressure(fs3_sim* s);
 int fs3i_levelset_init(fs3_sim* s);
 int fs3i_staging(fs3_sim* s, size_t bytes);
 int fs3i_extrap_prepare(fs3_sim* s, int slot, int xs, int ys, int zs, size_t off = 0);
-#define FS3_EX_DEPTH 8                                                        // sharded handles: planes of P2G halo and layers of extrapolation (p2g.cu)
+#define FS3_EX_DEPTH 8
+#define FS3_SOR_DONE_BYTES 8192   // sor_done: block counter, then (128 bytes apart) arrivals + generation copies of the solve's grid barrier                                                        // sharded handles: planes of P2G halo and layers of extrapolation (p2g.cu)
 void fs3i_ex_window(const fs3_sim* s, int ax, int depth, int* w0, int* w1);  // planes [w0, w1) of face grid ax this rank extrapolates
 int fs3i_extrap_fill(fs3_sim* s, int slot, float* grid, int xs, int ys, int zs);
 int fs3i_alloc(fs3_sim* s, void** p, size_t bytes);                         // arena (sharded) or cudaMalloc
@@ -319,6 +320,8 @@ int fs3i_load_local(fs3_sim* s, const fs3_particle* dev_in, const int* dev_ids, 
 int fs3i_project_setup(fs3_sim* s, float dt, bool from_old, bool with_gravity);
 int fs3i_sor_prepare(fs3_sim* s);
 int fs3i_sor_half_launch(fs3_sim* s, int k);                                // half sweep k of the current projection
+bool fs3i_sor_two_plane(const fs3_sim* s);                                  // sharded solve with two-plane halos (one exchange per iteration)?
+int fs3i_sor_push_system(fs3_sim* s);                                       // two-plane halos: b, diag, mask of my boundary reds to the neighbours
 int fs3i_sor_persistent(fs3_sim* s, int halves);                            // multi-process sharded handle: the whole solve in one cooperative launch
 int fs3i_project_gradient(fs3_sim* s, float dt, bool from_old, bool with_gravity);
 // levelset.cu / p2g.cu pieces

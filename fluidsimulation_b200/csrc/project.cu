@@ -6,6 +6,7 @@
 // REAL = double reproduces the reference's fp64 solve bit for bit (each half sweep is order
 // independent; same IEEE operations, no FMA contraction); REAL = float is the fast mode.
 #include "fs3_internal.cuh"
+#include <string>
 #include <algorithm>
 #include <cstdlib>
 
@@ -273,6 +274,36 @@ __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_half(Sys<
 // Measured on 2 GPUs at 256^3 (us per half sweep): this arrangement 17.1; boundary CTAs that also take a share of the interior
 // after their two planes 21.0 (they start it late and the grid barrier waits for them); one 1024-thread CTA per SM with
 // shared interior work 22.1.  The disjoint split stays.
+// Grid barrier of the one-launch solves (all CTAs are co-resident: cooperative launch).  Arrivals are atomics on one word; the last
+// arriver publishes the generation in ANOTHER 128-byte line, which is what everybody else polls with relaxed loads: measured with
+// the arrival word polled by acquire loads of all 592 CTAs, a CTA left the barrier 4 us after the last arrival (tools/sor_trace.py).
+// The generation is replicated over FS3_SOR_GEN_LINES lines (block b polls copy b % LINES): one polled line takes a large share of
+// its L2 slice's request rate while other CTAs are still sweeping.  bar[0] = arrivals, bar[32 r], r = 1.., = generation copies;
+// all zero at launch; k counts the barriers of this launch from 0.
+#define FS3_SOR_GEN_LINES 16
+__device__ __forceinline__ void sor_grid_barrier(uint32_t* bar, uint32_t k, uint32_t G, int* flags) {
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		asm volatile("fence.acq_rel.gpu;\n" ::: "memory");   // (__threadfence() is the sequentially consistent fence: not needed here)
+		const uint32_t old = atomicAdd(bar, 1u);
+		if (old == (k + 1u) * G - 1u) {
+			asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
+			for (int r = 1; r <= FS3_SOR_GEN_LINES; r++) asm volatile("st.relaxed.gpu.global.u32 [%0], %1;\n" ::"l"(bar + 32 * r), "r"(k + 1u) : "memory");
+		} else {
+			const uint32_t* const gen = bar + 32 * (1 + (blockIdx.x % FS3_SOR_GEN_LINES));
+			const long long t0 = clock64();
+			for (unsigned it = 1;; it++) {
+				uint32_t v;
+				asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(gen) : "memory");
+				if (v >= k + 1u) break;
+				__nanosleep(100);
+				if ((it & 1023u) == 0 && (*reinterpret_cast<volatile int*>(flags + 2) || clock64() - t0 > 8000000000LL)) { flags[2] = 1; break; }
+			}
+			asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
+		}
+	}
+	__syncthreads();
+}
 struct SorPersist {
 	void* peer_p[2][2];       // [colour][lower / upper neighbour]
 	uint32_t* peer_flag[2];
@@ -323,20 +354,153 @@ __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_persisten
 			for (uint32_t t = ib * blockDim.x + threadIdx.x; t < n - B; t += IG) sor_vector<REAL, VEC, false, true>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
 		}
 		// ---- grid barrier: the next half sweep reads this colour everywhere -------------------------------------------------
+		sor_grid_barrier(P.gbar, (uint32_t)k, G, P.flags);
+	}
+}
+
+// ---- the same solve with TWO-plane halos: one exchange per ITERATION, both flags off the critical path ----------------------
+// With one-plane halos every half sweep contains a cross-GPU dependency (wait for the neighbour's plane, compute the own boundary,
+// store it over NVLink, system fence, flag, flight: ~7 us), which no schedule inside one rank can hide: at 8 ranks a half sweep
+// took 13.8 us where the memory traffic needs 3.5.  Here a rank also keeps the neighbours' nearest TWO planes: it sweeps the RED
+// cells of the nearest ghost plane itself (same inputs, same arithmetic as the owner: bit-identical), so only BLACK values travel,
+// two planes each way, once per iteration:
+//   red   half sweep: the EDGE entries first (ghost plane + own first plane, the ones that read the neighbour's blacks): wait for
+//                     "blacks of the previous iteration are here" (flag B), sweep them, raise "I have read them" (flag R);
+//                     then the rest;
+//   black half sweep: the BOUNDARY entries first (own first / last two planes): wait for the neighbour's R (it no longer reads
+//                     the ghost blacks I am about to overwrite), sweep them, storing every result into the neighbour's ghost
+//                     planes too, system fence, raise B; then the rest.
+// Both flags are sent at the START of a half sweep and needed at the start of the NEXT one, so the NVLink latency overlaps the
+// interior work; a grid barrier still separates the half sweeps.  The system (b, diag, mask) of the ghost plane is the owner's,
+// copied once per projection (fs3i_sor_push_system).  Lists: red = slab + one ghost plane per neighbour, black = slab.
+#define FS3_SOR_MAX_NBB 256
+struct SorPersist2 {
+	void* peer_black[2];      // colour-1 array of the lower / upper neighbour (nullptr: no neighbour)
+	uint32_t *peer_B[2], *peer_R[2];   // FS3_SOR_MAX_NBB words each in the neighbour's arena: boundary block i writes word i
+	const uint32_t *my_B[2], *my_R[2]; // [0] written by the lower, [1] by the upper neighbour
+	uint32_t e0, nbb;
+	int iters;
+	size_t lo_begin, lo_end, hi_begin, hi_end;   // element ranges of the slab's first / last TWO planes in a colour array
+	const uint32_t *n_lo[2], *n_hi[2], *list[2], *count[2];   // per colour: list entries [0, n_lo) and [n_hi, n) are the edge / boundary entries
+	uint32_t* gbar;
+	int* flags;
+#ifdef FS3_SOR_TRACE
+	unsigned long long* trace;   // [half sweep 64..95][block 0 / last block][8 time stamps] (tools/sor_trace.py)
+#endif
+};
+#ifdef FS3_SOR_TRACE
+__device__ __forceinline__ unsigned long long fs3_gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define SOR_TR(i) do { if (tr && threadIdx.x == 0) tr[i] = fs3_gtime(); } while (0)
+#else
+#define SOR_TR(i) do { } while (0)
+#endif
+template <typename REAL, int VEC>
+__global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_persistent2(Sys<REAL> sy, REAL omega, REAL one_minus_omega, SorPersist2 P) {
+	const uint32_t G = gridDim.x;
+	const uint32_t nbb = P.nbb;   // blocks that sweep the edge / boundary entries: the SAME number on every rank
+	const bool bnd = blockIdx.x < nbb;
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+	for (int k = 0; k < 2 * P.iters; k++) {
+		const int c = k & 1, it = k >> 1;
+#ifdef FS3_SOR_TRACE
+		// half sweeps 64..95: first and last block; 96, 97: every block (rows of 8 after the first 32 * 2)
+		unsigned long long* const tr = (k >= 64 && k < 96 && (blockIdx.x == 0 || blockIdx.x == G - 1)) ? P.trace + ((size_t)(k - 64) * 2 + (blockIdx.x == 0 ? 0 : 1)) * 8
+		                               : (k == 96 || k == 97) ? P.trace + (64 + (size_t)(k - 96) * 1024 + blockIdx.x) * 8 : nullptr;
+#endif
+		SOR_TR(0);
+		SorShard sh;
+		sh.peer_p[0] = P.peer_black[0]; sh.peer_p[1] = P.peer_black[1];
+		sh.lo_begin = P.lo_begin; sh.lo_end = P.lo_end; sh.hi_begin = P.hi_begin; sh.hi_end = P.hi_end;
+		const SorPtrs<REAL> sp = sor_ptrs<REAL>(sy, c, sh);
+		const uint32_t* __restrict__ list = c ? P.list[1] : P.list[0];
+		const uint32_t n = __ldg(c ? P.count[1] : P.count[0]), n_lo = __ldg(c ? P.n_lo[1] : P.n_lo[0]), n_hi = __ldg(c ? P.n_hi[1] : P.n_hi[0]);
+		const uint32_t B = n_lo + (n - n_hi);
+		if (bnd) {
+			// red waits for the blacks of iteration it - 1 (flag B; none at it = 0: the host waited for "system set up"), black for "the
+			// neighbour has read them" (flag R): EVERY boundary block of the neighbour has written the epoch into its word
+			if (k > 0 && warp < 2) {
+				const uint32_t* const w = c ? (warp ? P.my_R[1] : P.my_R[0]) : (warp ? P.my_B[1] : P.my_B[0]);
+				if (w) for (uint32_t i = lane; i < nbb; i += 32) fs3_flag_wait(w + i, P.e0 + (uint32_t)(it + c), P.flags, 0);
+			}
+			__syncthreads();
+			SOR_TR(1);
+			for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < B; t += nbb * blockDim.x)
+				sor_vector<REAL, VEC, false, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
+			SOR_TR(2);
+		}
+		if (!bnd || G == 1) {
+			const uint32_t ib = G == 1 ? 0u : blockIdx.x - nbb, IG = G == 1 ? blockDim.x : (G - nbb) * blockDim.x;
+			for (uint32_t t = ib * blockDim.x + threadIdx.x; t < n - B; t += IG) sor_vector<REAL, VEC, false, true>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
+		}
+		// ---- grid barrier; the boundary blocks serve the neighbours AFTER they have arrived ----------------------------------------
+		// Any fence of a thread that has stores (or atomics) to a peer in flight waits for their NVLink acknowledgements (4 - 6 us
+		// measured, gpu scope as well as system scope), so such a thread cannot arrive quickly.  Hence: the boundary blocks sweep
+		// their entries into local memory only; thread 0 (which never touches peer memory) arrives; THEN warps 1.. copy the block's
+		// entries from L2 into the neighbours' ghost planes and lane 0 of warp 1 fences at system scope and stores the epoch into
+		// this block's word of the neighbours' flag arrays -- while the other blocks are already in the next half sweep.  (One word
+		// per block: 148 remote atomics on ONE word serialise at the target, 9 us measured.)  Red (flag R) publishes no data, only
+		// "my reads of the ghost blacks are done": they are (their values went into stores that precede the block barrier).
+		__shared__ int s_last;
 		__syncthreads();
+		SOR_TR(4);
 		if (threadIdx.x == 0) {
-			__threadfence();
-			atomicAdd(P.gbar, 1u);
-			const uint32_t need = (uint32_t)(k + 1) * G;
-			const long long t0 = clock64();
-			for (unsigned it = 1;; it++) {
-				uint32_t v;
-				asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(P.gbar) : "memory");
-				if (v >= need) break;
-				if ((it & 1023u) == 0 && (*reinterpret_cast<volatile int*>(P.flags + 2) || clock64() - t0 > 8000000000LL)) { P.flags[2] = 1; break; }
+			// (acq_rel fences: __threadfence() is the sequentially consistent one, which this protocol does not need)
+			asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
+			const uint32_t old = atomicAdd(P.gbar, 1u);
+			s_last = old == (uint32_t)(k + 1) * G - 1u;
+			if (s_last) {
+				asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
+				for (int r = 1; r <= FS3_SOR_GEN_LINES; r++) asm volatile("st.relaxed.gpu.global.u32 [%0], %1;\n" ::"l"(P.gbar + 32 * r), "r"((uint32_t)k + 1u) : "memory");
+			}
+			SOR_TR(5);
+		}
+		if (bnd && c) __syncthreads();   // (the copy's peer stores would hold up thread 0's fence)
+		if (bnd && warp >= 1) {
+			if (c) {
+				// this block's entries are t0 + j, j < blockDim.x, for t0 = blockIdx.x * blockDim.x + m * nbb * blockDim.x
+				for (uint32_t t0 = blockIdx.x * blockDim.x; t0 < B; t0 += nbb * blockDim.x)
+					for (uint32_t j = threadIdx.x - 32; j < blockDim.x && t0 + j < B; j += blockDim.x - 32) {
+						const uint32_t t = t0 + j;
+						const size_t base = (size_t)(__ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))) & 0x7fffffffu) * VEC;
+						REAL v[VEC];
+						ldv_cg(sp.own + base, v);
+						if (sp.peer_lo && base >= sp.lo_begin && base < sp.lo_end) stv(sp.peer_lo + base, v);
+						if (sp.peer_hi && base >= sp.hi_begin && base < sp.hi_end) stv(sp.peer_hi + base, v);
+					}
+				asm volatile("bar.sync 1, %0;\n" ::"r"(blockDim.x - 32) : "memory");
+			}
+			if (threadIdx.x == 32) {
+				if (c) asm volatile("fence.acq_rel.sys;\n" ::: "memory");
+				uint32_t* const f0 = c ? P.peer_B[0] : P.peer_R[0];
+				uint32_t* const f1 = c ? P.peer_B[1] : P.peer_R[1];
+				if (f0) fs3_st_relaxed_sys(f0 + blockIdx.x, P.e0 + (uint32_t)it + 1u);
+				if (f1) fs3_st_relaxed_sys(f1 + blockIdx.x, P.e0 + (uint32_t)it + 1u);
+#ifdef FS3_SOR_TRACE
+				if (tr) tr[3] = fs3_gtime();
+#endif
 			}
 		}
+		if (threadIdx.x == 0 && !s_last) {
+			// the generation is replicated over FS3_SOR_GEN_LINES lines (= L2 slices): hundreds of CTAs polling ONE line while the
+			// others are still sweeping take a large share of that slice's request rate, and the sweep is as slow as its slowest slice
+			const uint32_t* const gen = P.gbar + 32 * (1 + (blockIdx.x % FS3_SOR_GEN_LINES));
+			const long long t0 = clock64();
+			for (unsigned itn = 1;; itn++) {
+				uint32_t v;
+				asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(gen) : "memory");
+				if (v >= (uint32_t)k + 1u) break;
+				__nanosleep(100);
+				if ((itn & 1023u) == 0 && (*reinterpret_cast<volatile int*>(P.flags + 2) || clock64() - t0 > 8000000000LL)) { P.flags[2] = 1; break; }
+			}
+			asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
+		}
 		__syncthreads();
+		SOR_TR(6);
+	}
+	// the neighbours' last blacks have landed in the ghost planes when the kernel ends (the gradient reads them)
+	if (blockIdx.x == 0 && warp < 2) {
+		const uint32_t* const w = warp ? P.my_B[1] : P.my_B[0];
+		if (w) for (uint32_t i = lane; i < nbb; i += 32) fs3_flag_wait(w + i, P.e0 + (uint32_t)P.iters, P.flags, 0);
 	}
 }
 
@@ -523,8 +687,11 @@ static double fs3_omega(const fs3_sim* s) { return s->prm.omega > 0 ? s->prm.ome
 template <typename REAL, int VEC> static int sor_prepare_t(fs3_sim* s) {
 	if (s->sor_list_valid) return FS3_OK;
 	const size_t nvec = s->rb.total / VEC;
-	const size_t v0 = s->rb.plane * (size_t)(s->z0 + 1) / VEC, v1 = s->rb.plane * (size_t)(s->z1 + 1) / VEC;
 	for (int c = 0; c < 2; c++) {
+		// two-plane halos (fs3i_sor_two_plane): the red list also holds the neighbours' nearest plane
+		const int g = (c == 0 && fs3i_sor_two_plane(s)) ? 1 : 0;
+		const int za = s->z0 - ((g && s->rank > 0) ? 1 : 0), zb = s->z1 + ((g && s->rank < s->world - 1) ? 1 : 0);
+		const size_t v0 = s->rb.plane * (size_t)(za + 1) / VEC, v1 = s->rb.plane * (size_t)(zb + 1) / VEC;
 		k_sor_flags<VEC><<<cdiv((long long)nvec + 1, 256), 256, 0, s->stream>>>(s->mask[c], nvec, s->sor_flags, v0, v1); FS3_LAUNCH_CHECK();
 		int rc = fs3i_scan_u32(s, s->sor_flags, s->sor_pos[c], nvec + 1);
 		if (rc) return rc;
@@ -653,15 +820,114 @@ template <typename REAL, int VEC> static int sor_persistent_t(fs3_sim* s, int ha
 	P.e0 = s->sor_e0; P.halves = halves;
 	P.lo_begin = s->rb.plane * (size_t)(s->z0 + 1); P.lo_end = P.lo_begin + s->rb.plane;
 	P.hi_begin = s->rb.plane * (size_t)s->z1; P.hi_end = P.hi_begin + s->rb.plane;
-	P.done = s->sor_done; P.gbar = s->sor_done + 1; P.flags = s->dev_flags;
-	FS3_CUDA(cudaMemsetAsync(s->sor_done, 0, 2 * sizeof(uint32_t), s->stream));
+	P.done = s->sor_done; P.gbar = s->sor_done + 32; P.flags = s->dev_flags;
+	FS3_CUDA(cudaMemsetAsync(s->sor_done, 0, 4096, s->stream));
 	void* args[] = {(void*)&sy, (void*)&omega, (void*)&omo, (void*)&P};
 	FS3_CUDA(cudaLaunchCooperativeKernel((const void*)k_sor_persistent<REAL, VEC>, dim3(nb), dim3(FS3_SOR_THREADS), args, 0, s->stream));
 	FS3_LAUNCH_CHECK();
 	s->sor_epoch = s->sor_e0 + (uint32_t)halves;
 	return FS3_OK;
 }
-int fs3i_sor_persistent(fs3_sim* s, int halves) { return s->alloc_precision ? sor_persistent_t<float, 4>(s, halves) : sor_persistent_t<double, 2>(s, halves); }
+
+// two-plane halos: multi-process handles whose slab has room for two distinct boundary planes on either side
+bool fs3i_sor_two_plane(const fs3_sim* s) { return s->world > 1 && !s->lockstep && s->nz / s->world >= 4; }
+
+template <typename REAL, int VEC> static int sor_persistent2_t(fs3_sim* s, int iters) {
+	Sys<REAL> sy = make_sys<REAL>(s);
+	REAL omega = (REAL)fs3_omega(s);
+	if (sizeof(REAL) == 4) omega = (REAL)2 - (REAL)3.16343 / s->nx, omega = s->prm.omega > 0 ? (REAL)s->prm.omega : omega;
+	REAL omo = (REAL)1 - omega;
+	int per_sm = 0;
+	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sor_persistent2<REAL, VEC>, FS3_SOR_THREADS, 0));
+	per_sm = std::max(1, per_sm);
+	const size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * (s->z1 - s->z0 + 2);
+	const int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, FS3_SOR_THREADS)), (long long)s->sm_count * per_sm);
+	SorPersist2 P;
+	const bool lo = s->rank > 0, hi = s->rank < s->world - 1;
+	const size_t pl = s->rb.plane;
+	// flag arrays in sor_done (words): B from below 1024, B from above 1280, R from below 1536, R from above 1792; 256 each
+	uint32_t* const fl_lo = lo ? fs3_peer(s, s->rank - 1, s->sor_done) : nullptr;
+	uint32_t* const fl_hi = hi ? fs3_peer(s, s->rank + 1, s->sor_done) : nullptr;
+	P.peer_black[0] = lo ? fs3_peer(s, s->rank - 1, (char*)s->p[1]) : nullptr;
+	P.peer_black[1] = hi ? fs3_peer(s, s->rank + 1, (char*)s->p[1]) : nullptr;
+	P.peer_B[0] = lo ? fl_lo + 1280 : nullptr; P.peer_B[1] = hi ? fl_hi + 1024 : nullptr;
+	P.peer_R[0] = lo ? fl_lo + 1792 : nullptr; P.peer_R[1] = hi ? fl_hi + 1536 : nullptr;
+	P.my_B[0] = lo ? s->sor_done + 1024 : nullptr; P.my_B[1] = hi ? s->sor_done + 1280 : nullptr;
+	P.my_R[0] = lo ? s->sor_done + 1536 : nullptr; P.my_R[1] = hi ? s->sor_done + 1792 : nullptr;
+	P.e0 = s->sor_e0; P.iters = iters;
+	// Boundary blocks do nothing else (they wait on the neighbours), and the sweep's throughput is proportional to the blocks that
+	// work on it, so their number follows their share of the planes (x 2 for their waits), a function of the grid and the world
+	// size only: every rank must arrive at the same number.  256^3: 139 of 592 blocks at 8 ranks, 36 at 2 ranks.
+	P.nbb = (uint32_t)std::min(std::min(std::max(nb / 4, 1), FS3_SOR_MAX_NBB), std::max(8, (int)(2LL * nb * 4 / (s->z1 - s->z0 + 2))));
+	// array plane index of cell plane z is z + 1.  Pushed: the slab's first / last two planes of black
+	P.lo_begin = pl * (size_t)(s->z0 + 1); P.lo_end = pl * (size_t)(s->z0 + 3);
+	P.hi_begin = pl * (size_t)(s->z1 - 1); P.hi_end = pl * (size_t)(s->z1 + 1);
+	// red: planes z0-1, z0 and z1-1, z1 read the neighbours' blacks; black: planes z0, z0+1 and z1-2, z1-1 are pushed.
+	// Without a neighbour the range is empty (the scan is 0 up to the list's first plane and n from its last one on).
+	P.n_lo[0] = s->sor_pos[0] + pl * (size_t)(lo ? s->z0 + 2 : s->z0 + 1) / VEC;
+	P.n_hi[0] = s->sor_pos[0] + pl * (size_t)(hi ? s->z1 : s->z1 + 1) / VEC;
+	P.n_lo[1] = s->sor_pos[1] + pl * (size_t)(lo ? s->z0 + 3 : s->z0 + 1) / VEC;
+	P.n_hi[1] = s->sor_pos[1] + pl * (size_t)(hi ? s->z1 - 1 : s->z1 + 1) / VEC;
+	for (int c = 0; c < 2; c++) { P.list[c] = s->sor_list[c]; P.count[c] = s->sor_count[c]; }
+	P.gbar = s->sor_done + 32; P.flags = s->dev_flags;
+	FS3_CUDA(cudaMemsetAsync(s->sor_done, 0, 4096, s->stream));   // the barrier words; NOT the flag arrays the neighbours write
+#ifdef FS3_SOR_TRACE
+	static unsigned long long* trace_buf = nullptr;
+	static int trace_calls = 0;
+	if (!trace_buf) FS3_CUDA(cudaMallocManaged((void**)&trace_buf, (64 + 2048) * 8 * sizeof(unsigned long long)));
+	P.trace = trace_buf;
+#endif
+	void* args[] = {(void*)&sy, (void*)&omega, (void*)&omo, (void*)&P};
+	FS3_CUDA(cudaLaunchCooperativeKernel((const void*)k_sor_persistent2<REAL, VEC>, dim3(nb), dim3(FS3_SOR_THREADS), args, 0, s->stream));
+	FS3_LAUNCH_CHECK();
+#ifdef FS3_SOR_TRACE
+	if (++trace_calls == 4) {
+		FS3_CUDA(cudaStreamSynchronize(s->stream));
+		std::string out;
+		char buf[256];
+		for (int k = 0; k < 32; k++)
+			for (int b = 0; b < 2; b++) {
+				const unsigned long long* t = trace_buf + ((size_t)k * 2 + b) * 8;
+				snprintf(buf, sizeof buf, "sortrace rank %d half %d %s", s->rank, k + 64, b ? "interior" : "boundary"); out += buf;
+				for (int i = 1; i < 7; i++) { snprintf(buf, sizeof buf, " %6lld", t[i] >= t[0] && t[i] ? (long long)(t[i] - t[0]) : -1LL); out += buf; }
+				snprintf(buf, sizeof buf, "  start +%lld\n", k ? (long long)(t[0] - trace_buf[((size_t)(k - 1) * 2 + b) * 8]) : 0LL); out += buf;
+			}
+		for (int h = 0; h < 2; h++) {
+			const unsigned long long* base = trace_buf + (64 + (size_t)h * 1024) * 8;
+			unsigned long long tmin = ~0ULL;
+			for (int b = 0; b < nb; b++) tmin = std::min(tmin, base[(size_t)b * 8]);
+			for (int b = 0; b < nb; b++) {
+				const unsigned long long* t = base + (size_t)b * 8;
+				snprintf(buf, sizeof buf, "sorblocks rank %d half %d block %d%s", s->rank, 96 + h, b, b < (int)P.nbb ? " B" : ""); out += buf;
+				for (int i = 0; i < 7; i++) { snprintf(buf, sizeof buf, " %6lld", t[i] ? (long long)(t[i] - tmin) : -1LL); out += buf; }
+				out += "\n";
+			}
+		}
+		snprintf(buf, sizeof buf, "gpurun_out/sortrace_rank%d.txt", s->rank);
+		if (FILE* f = fopen(buf, "w")) { fwrite(out.data(), 1, out.size(), f); fclose(f); }
+	}
+#endif
+	s->sor_epoch = s->sor_e0 + 2u * (uint32_t)iters;   // (the flags end at e0 + iters; the next projection's e0 lies above either scheme's range)
+	return FS3_OK;
+}
+int fs3i_sor_persistent(fs3_sim* s, int halves) {
+	if (fs3i_sor_two_plane(s)) return s->alloc_precision ? sor_persistent2_t<float, 4>(s, halves / 2) : sor_persistent2_t<double, 2>(s, halves / 2);
+	return s->alloc_precision ? sor_persistent_t<float, 4>(s, halves) : sor_persistent_t<double, 2>(s, halves);
+}
+// two-plane halos: the system (b, diag, mask) of the RED cells of my first / last plane goes to the neighbour that sweeps them too
+int fs3i_sor_push_system(fs3_sim* s) {
+	if (!fs3i_sor_two_plane(s)) return FS3_OK;
+	const size_t es = s->alloc_precision ? 4 : 8, pl = s->rb.plane;
+	for (int side = 0; side < 2; side++) {
+		const int r = side ? s->rank + 1 : s->rank - 1;
+		if (r < 0 || r >= s->world) continue;
+		const size_t off = pl * (size_t)(side ? s->z1 : s->z0 + 1);   // array plane of cell plane z1 - 1 / z0
+		FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, r, (char*)s->b[0]) + off * es, (char*)s->b[0] + off * es, pl * es, cudaMemcpyDefault, s->stream));
+		FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, r, (char*)s->dg[0]) + off * es, (char*)s->dg[0] + off * es, pl * es, cudaMemcpyDefault, s->stream));
+		FS3_CUDA(cudaMemcpyAsync(fs3_peer(s, r, (char*)s->mask[0]) + off, (char*)s->mask[0] + off, pl, cudaMemcpyDefault, s->stream));
+	}
+	return FS3_OK;
+}
 
 // The persisting-L2 size is a DEVICE-wide limit: whatever the host application (or another handle) had configured is put
 // back when the solve ends, on every path out of fs3i_sor_loop.
@@ -736,6 +1002,10 @@ template <typename REAL> static int project_setup_t(fs3_sim* s, float dt, bool f
 		for (int c = 0; c < 2; c++) {
 			FS3_CUDA(cudaMemsetAsync((REAL*)s->p[c] + s->rb.plane * (size_t)s->z0, 0, s->rb.plane * sizeof(REAL), s->stream));
 			FS3_CUDA(cudaMemsetAsync((REAL*)s->p[c] + s->rb.plane * (size_t)(s->z1 + 1), 0, s->rb.plane * sizeof(REAL), s->stream));
+		}
+		if (fs3i_sor_two_plane(s)) {   // ... and the second ghost plane of black
+			if (s->rank > 0) FS3_CUDA(cudaMemsetAsync((REAL*)s->p[1] + s->rb.plane * (size_t)(s->z0 - 1), 0, s->rb.plane * sizeof(REAL), s->stream));
+			if (s->rank < s->world - 1) FS3_CUDA(cudaMemsetAsync((REAL*)s->p[1] + s->rb.plane * (size_t)(s->z1 + 2), 0, s->rb.plane * sizeof(REAL), s->stream));
 		}
 	}
 	s->system_valid = true;

@@ -42,7 +42,7 @@ size_t fs3i_arena_bytes(int n, long long ptot, long long mig_cap, int world) {
 	const size_t nt = ((N + 7) / 8) * ((N + 7) / 8) * ((N + 3) / 4);
 	t += up512(8 * nt * 4) + up512(nt * 4) + 512;                             // level-set item table, epochs, ticket
 	t += up512((size_t)world * (world + 1) * 4) + up512((2 * (size_t)world + 1) * 4) + up512((size_t)mig_cap * 4) + 2 * up512((size_t)mig_cap * 16);
-	t += up512((FS3_MAX_WORLD + 2) * 4) + 512;                                // bar, sor_done
+	t += up512(FS3_BAR_WORDS * 4) + FS3_SOR_DONE_BYTES;                       // bar, sor_done
 	return t + (1u << 20);
 }
 
@@ -67,7 +67,7 @@ int fs3i_shard_alloc(fs3_sim* s) {
 	if ((rc = fs3i_alloc(s, (void**)&s->mig_matrix, (size_t)w * (w + 1) * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_ctl, (2 * (size_t)w + 1) * 4)) ||
 	    (rc = fs3i_alloc(s, (void**)&s->leaver_idx, (size_t)s->mig_cap * 4)) || (rc = fs3i_alloc(s, (void**)&s->mig_pos, (size_t)s->mig_cap * 16)) ||
 	    (rc = fs3i_alloc(s, (void**)&s->mig_vel, (size_t)s->mig_cap * 16)) || (rc = fs3i_alloc(s, (void**)&s->bar, FS3_BAR_WORDS * 4)) ||
-	    (rc = fs3i_alloc(s, (void**)&s->sor_done, 16)))   // [0] block counter of the end-of-sweep signal, [1] grid barrier of the one-launch solve
+	    (rc = fs3i_alloc(s, (void**)&s->sor_done, FS3_SOR_DONE_BYTES)))   // [0] block counter of the end-of-sweep signal; from [32] on the one-launch solve's grid barrier
 		return rc;
 	FS3_CUDA(cudaMallocHost((void**)&s->h_pin, (size_t)std::max(w * (w + 1), 64) * 4));
 	return FS3_OK;
@@ -371,9 +371,12 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 	if (ph == 5) {          // extrapolation of the slab window beside the sweeps; pressure system of the slab; tell the neighbours it is set up
 		// own outgoing copies are complete before the extrapolation overwrites the arrays they read
 		if ((rc = xfer_join(s)) || (rc = fs3i_wait(s)) || (rc = fs3i_cd_from_tags(s)) || (rc = fs3i_extrapolate_all(s)) || (rc = fs3i_levelset_join(s)) ||
-		    (rc = fs3i_project_setup(s, dt, true, true)) || (rc = fs3i_sor_prepare(s)))
+		    (rc = fs3i_project_setup(s, dt, true, true)))
 			return rc;
-		if ((rc = fs3i_sor_signal(s))) return rc;
+		if (fs3i_sor_two_plane(s)) {
+			// the red list also covers the neighbours' nearest plane: their masks must be here before it is built
+			if ((rc = fs3i_sor_push_system(s)) || (rc = fs3i_sor_signal(s)) || (rc = fs3i_sor_wait(s, s->sor_e0)) || (rc = fs3i_sor_prepare(s))) return rc;
+		} else if ((rc = fs3i_sor_prepare(s)) || (rc = fs3i_sor_signal(s))) return rc;
 		if (T) cudaEventRecord(s->ev[FS3_T_PROJECT_SOR], s->stream);
 		return FS3_OK;
 	}
@@ -386,7 +389,7 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 	}
 	if (ph == 6 + 2 * I) {  // pressure gradient on the slab; the projected field is gathered on every rank
 		// the copies of the previous step's field (stream3) have left before the gradient overwrites their source
-		if ((rc = xfer_join(s)) || (rc = fs3i_sor_wait(s, s->sor_e0 + 2u * (uint32_t)I)) || (rc = fs3i_project_gradient(s, dt, true, true))) return rc;
+		if ((rc = xfer_join(s)) || (!fs3i_sor_two_plane(s) && (rc = fs3i_sor_wait(s, s->sor_epoch))) || (rc = fs3i_project_gradient(s, dt, true, true))) return rc;
 		// The gradient kernel of cell plane z writes the W faces z+1 (and z = 0 on rank 0): that is the range it owns here.
 		// On the copy stream: the planes inside the neighbours' velocity halo + their flag -- all the next kernels of any rank
 		// read (FLIP blend, G2P, the next Advect).  Whole slabs only travel when a whole-grid getter asks (fs3i_field_wait).
