@@ -99,6 +99,13 @@ __device__ __forceinline__ void ldv_stream(const float* p, float (&a)[4]) { cons
 // sweep must not be served from this SM's L1
 __device__ __forceinline__ void ldv_cg(const double* p, double (&a)[2]) { const double2 t = __ldcg(reinterpret_cast<const double2*>(p)); a[0] = t.x; a[1] = t.y; }
 __device__ __forceinline__ void ldv_cg(const float* p, float (&a)[4]) { const float4 t = __ldcg(reinterpret_cast<const float4*>(p)); a[0] = t.x; a[1] = t.y; a[2] = t.z; a[3] = t.w; }
+// system-scope loads: operands that live in (or were just written by) a neighbouring GPU
+__device__ __forceinline__ void ldv_sys(const double* p, double (&a)[2]) { asm volatile("ld.relaxed.sys.global.v2.f64 {%0, %1}, [%2];\n" : "=d"(a[0]), "=d"(a[1]) : "l"(p) : "memory"); }
+__device__ __forceinline__ void ldv_sys(const float* p, float (&a)[4]) {
+	asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];\n" : "=f"(a[0]), "=f"(a[1]), "=f"(a[2]), "=f"(a[3]) : "l"(p) : "memory");
+}
+__device__ __forceinline__ double ld_sys(const double* p) { double v; asm volatile("ld.relaxed.sys.global.f64 %0, [%1];\n" : "=d"(v) : "l"(p) : "memory"); return v; }
+__device__ __forceinline__ float ld_sys(const float* p) { float v; asm volatile("ld.relaxed.sys.global.f32 %0, [%1];\n" : "=f"(v) : "l"(p) : "memory"); return v; }
 __device__ __forceinline__ void stv(double* p, const double (&a)[2]) { *reinterpret_cast<double2*>(p) = make_double2(a[0], a[1]); }
 __device__ __forceinline__ void stv(float* p, const float (&a)[4]) { *reinterpret_cast<float4*>(p) = make_float4(a[0], a[1], a[2], a[3]); }
 
@@ -141,8 +148,16 @@ __device__ __forceinline__ SorPtrs<REAL> sor_ptrs(const Sys<REAL>& sy, int colou
 	sp.lo_begin = sh.lo_begin; sp.lo_end = sh.lo_end; sp.hi_begin = sh.hi_begin; sp.hi_end = sh.hi_end;
 	return sp;
 }
-template <typename REAL, int VEC, bool PUSH, bool CG = false>
-__device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, REAL one_minus_omega, uint32_t ent) {
+// EDGE (two-plane halos, red entries next to a neighbour): the other colour's values of the neighbour's planes are read from the
+// NEIGHBOUR's array over NVLink (same layout, so the same offsets): sp.peer_lo / peer_hi are its other-colour arrays, sp.lo_begin /
+// hi_begin the first element of this rank's first / last plane.
+template <typename REAL, int VEC>
+__device__ __forceinline__ typename VecT<REAL, VEC>::mtype sor_mask(const SorPtrs<REAL>& sp, uint32_t ent) {
+	return __ldcs(reinterpret_cast<const typename VecT<REAL, VEC>::mtype*>(sp.mask + (size_t)(ent & 0x7fffffffu) * VEC));
+}
+// (mm: the entry's mask word, loaded by the caller -- ahead of time where the loop can)
+template <typename REAL, int VEC, bool PUSH, bool CG = false, bool EDGE = false>
+__device__ __forceinline__ void sor_vector_m(const SorPtrs<REAL>& sp, REAL omega, REAL one_minus_omega, uint32_t ent, typename VecT<REAL, VEC>::mtype mm) {
 	typedef Ops<REAL> O;
 	typedef typename VecT<REAL, VEC>::type V;
 	typedef typename VecT<REAL, VEC>::mtype M;
@@ -150,10 +165,18 @@ __device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, 
 	const M nodiag = VEC == 2 ? (M)0x8080 : (M)0x80808080u;
 	const int s = (int)(ent >> 31);   // x parity of this colour in this row
 	const size_t base = (size_t)(ent & 0x7fffffffu) * VEC;
-	const M mm = __ldcs(reinterpret_cast<const M*>(sp.mask + base));
 	REAL own[VEC], bb[VEC], dd[VEC], xc[VEC], ym[VEC], yp[VEC], zm[VEC], zp[VEC];
 	REAL edge;
-	if (CG) {
+	if (EDGE) {
+		const REAL *oc = o, *ozm = o, *ozp = o;   // in-plane, plane below, plane above
+		if (sp.peer_lo && base < sp.lo_begin + sp.plane) { ozm = sp.peer_lo; if (base < sp.lo_begin) oc = sp.peer_lo; }
+		if (sp.peer_hi && base >= sp.hi_begin) { ozp = sp.peer_hi; if (base >= sp.hi_begin + sp.plane) oc = sp.peer_hi; }
+		ldv_cg(sp.own + base, own);
+		ldv_sys(oc + base, xc);
+		ldv_sys(oc + base - sp.hp, ym); ldv_sys(oc + base + sp.hp, yp);
+		ldv_sys(ozm + base - sp.plane, zm); ldv_sys(ozp + base + sp.plane, zp);
+		edge = ld_sys(s == 0 ? oc + base - 1 : oc + base + VEC);
+	} else if (CG) {
 		ldv_cg(sp.own + base, own);
 		ldv_cg(o + base, xc);
 		ldv_cg(o + base - sp.hp, ym); ldv_cg(o + base + sp.hp, yp);
@@ -193,6 +216,11 @@ __device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, 
 		if (sp.peer_lo && base >= sp.lo_begin && base < sp.lo_end) stv(sp.peer_lo + base, own);
 		if (sp.peer_hi && base >= sp.hi_begin && base < sp.hi_end) stv(sp.peer_hi + base, own);
 	}
+}
+
+template <typename REAL, int VEC, bool PUSH, bool CG = false, bool EDGE = false>
+__device__ __forceinline__ void sor_vector(const SorPtrs<REAL>& sp, REAL omega, REAL one_minus_omega, uint32_t ent) {
+	sor_vector_m<REAL, VEC, PUSH, CG, EDGE>(sp, omega, one_minus_omega, ent, sor_mask<REAL, VEC>(sp, ent));
 }
 
 // SHARD: BOUNDARY FIRST.  The list is in memory order, so the active vectors of the slab's first plane are its first n_lo
@@ -281,6 +309,7 @@ __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_half(Sys<
 // its L2 slice's request rate while other CTAs are still sweeping.  bar[0] = arrivals, bar[32 r], r = 1.., = generation copies;
 // all zero at launch; k counts the barriers of this launch from 0.
 #define FS3_SOR_GEN_LINES 16
+#define FS3_SOR_CHUNK 256   // entries per ticket of the dynamic tail of the one-launch solve's interior sweep
 __device__ __forceinline__ void sor_grid_barrier(uint32_t* bar, uint32_t k, uint32_t G, int* flags) {
 	__syncthreads();
 	if (threadIdx.x == 0) {
@@ -375,17 +404,17 @@ __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_persisten
 // copied once per projection (fs3i_sor_push_system).  Lists: red = slab + one ghost plane per neighbour, black = slab.
 #define FS3_SOR_MAX_NBB 256
 struct SorPersist2 {
-	void* peer_black[2];      // colour-1 array of the lower / upper neighbour (nullptr: no neighbour)
-	uint32_t *peer_B[2], *peer_R[2];   // FS3_SOR_MAX_NBB words each in the neighbour's arena: boundary block i writes word i
-	const uint32_t *my_B[2], *my_R[2]; // [0] written by the lower, [1] by the upper neighbour
+	const void* peer_black[2];   // colour-1 array of the lower / upper neighbour (nullptr: no neighbour)
+	uint32_t *peer_B[2], *peer_R[2];
+	const uint32_t *my_B, *my_R;   // [0] written by the lower, [1] by the upper neighbour
 	uint32_t e0, nbb;
 	int iters;
-	size_t lo_begin, lo_end, hi_begin, hi_end;   // element ranges of the slab's first / last TWO planes in a colour array
+	size_t lo_begin, hi_begin;     // first element of the slab's first / last plane in a colour array
 	const uint32_t *n_lo[2], *n_hi[2], *list[2], *count[2];   // per colour: list entries [0, n_lo) and [n_hi, n) are the edge / boundary entries
-	uint32_t* gbar;
+	uint32_t *done, *gbar;
 	int* flags;
 #ifdef FS3_SOR_TRACE
-	unsigned long long* trace;   // [half sweep 64..95][block 0 / last block][8 time stamps] (tools/sor_trace.py)
+	unsigned long long* trace;   // (tools/sor_trace.py)
 #endif
 };
 #ifdef FS3_SOR_TRACE
@@ -396,10 +425,37 @@ __device__ __forceinline__ unsigned long long fs3_gtime() { unsigned long long t
 #endif
 template <typename REAL, int VEC>
 __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_persistent2(Sys<REAL> sy, REAL omega, REAL one_minus_omega, SorPersist2 P) {
-	const uint32_t G = gridDim.x;
-	const uint32_t nbb = P.nbb;   // blocks that sweep the edge / boundary entries: the SAME number on every rank
+	const uint32_t G = gridDim.x - 1;   // sweeping blocks; the last block is the courier
+	const uint32_t nbb = P.nbb;         // of which the first nbb sweep the edge / boundary entries
+	if (blockIdx.x == G) {
+		// ---- courier: the only CTA that stores to a neighbour.  When the boundary blocks of half sweep k have reported in (local
+		// counter), one system-scope fence orders their stores before the flag it then writes into both neighbours' arenas.
+		if (threadIdx.x == 0) {
+			for (int k = 0; k < 2 * P.iters; k++) {
+				const long long t0 = clock64();
+				for (unsigned itn = 1;; itn++) {
+					uint32_t v;
+					asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(P.done) : "memory");
+					if (v >= nbb * (uint32_t)(k + 1)) break;
+					if ((itn & 1023u) == 0 && (*reinterpret_cast<volatile int*>(P.flags + 2) || clock64() - t0 > 8000000000LL)) { P.flags[2] = 1; return; }
+				}
+				asm volatile("fence.acq_rel.sys;\n" ::: "memory");
+				uint32_t* const f0 = (k & 1) ? P.peer_B[0] : P.peer_R[0];
+				uint32_t* const f1 = (k & 1) ? P.peer_B[1] : P.peer_R[1];
+				if (f0) fs3_st_relaxed_sys(f0, P.e0 + (uint32_t)(k >> 1) + 1u);
+				if (f1) fs3_st_relaxed_sys(f1, P.e0 + (uint32_t)(k >> 1) + 1u);
+#ifdef FS3_SOR_TRACE
+				if (k == 96 || k == 97) { unsigned long long* tr = P.trace + (64 + (size_t)(k - 96) * 1024 + blockIdx.x) * 8; tr[0] = tr[3] = fs3_gtime(); }
+#endif
+			}
+		}
+		return;
+	}
 	const bool bnd = blockIdx.x < nbb;
-	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+	__shared__ uint32_t s_chunk;
+	SorShard sh;
+	sh.peer_p[0] = const_cast<void*>(P.peer_black[0]); sh.peer_p[1] = const_cast<void*>(P.peer_black[1]);
+	sh.lo_begin = P.lo_begin; sh.lo_end = 0; sh.hi_begin = P.hi_begin; sh.hi_end = 0;
 	for (int k = 0; k < 2 * P.iters; k++) {
 		const int c = k & 1, it = k >> 1;
 #ifdef FS3_SOR_TRACE
@@ -408,99 +464,124 @@ __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_persisten
 		                               : (k == 96 || k == 97) ? P.trace + (64 + (size_t)(k - 96) * 1024 + blockIdx.x) * 8 : nullptr;
 #endif
 		SOR_TR(0);
-		SorShard sh;
-		sh.peer_p[0] = P.peer_black[0]; sh.peer_p[1] = P.peer_black[1];
-		sh.lo_begin = P.lo_begin; sh.lo_end = P.lo_end; sh.hi_begin = P.hi_begin; sh.hi_end = P.hi_end;
 		const SorPtrs<REAL> sp = sor_ptrs<REAL>(sy, c, sh);
 		const uint32_t* __restrict__ list = c ? P.list[1] : P.list[0];
 		const uint32_t n = __ldg(c ? P.count[1] : P.count[0]), n_lo = __ldg(c ? P.n_lo[1] : P.n_lo[0]), n_hi = __ldg(c ? P.n_hi[1] : P.n_hi[0]);
 		const uint32_t B = n_lo + (n - n_hi);
 		if (bnd) {
-			// red waits for the blacks of iteration it - 1 (flag B; none at it = 0: the host waited for "system set up"), black for "the
-			// neighbour has read them" (flag R): EVERY boundary block of the neighbour has written the epoch into its word
-			if (k > 0 && warp < 2) {
-				const uint32_t* const w = c ? (warp ? P.my_R[1] : P.my_R[0]) : (warp ? P.my_B[1] : P.my_B[0]);
-				if (w) for (uint32_t i = lane; i < nbb; i += 32) fs3_flag_wait(w + i, P.e0 + (uint32_t)(it + c), P.flags, 0);
+			// red waits for the neighbours' blacks of iteration it - 1 (flag B; none at it = 0: the host waited for "system set up"),
+			// black for "the neighbour has read my blacks of iteration it - 1" (flag R of its red half sweep it)
+			if (k > 0) {
+				const uint32_t* const w = c ? P.my_R : P.my_B;
+				if (threadIdx.x == 0 && P.peer_B[0]) fs3_flag_wait(w, P.e0 + (uint32_t)(it + c), P.flags, 0);
+				if (threadIdx.x == 1 && P.peer_B[1]) fs3_flag_wait(w + 1, P.e0 + (uint32_t)(it + c), P.flags, 0);
 			}
 			__syncthreads();
 			SOR_TR(1);
-			for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < B; t += nbb * blockDim.x)
-				sor_vector<REAL, VEC, false, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
+			if (c) {
+				for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < B; t += nbb * blockDim.x)
+					sor_vector<REAL, VEC, false, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
+			} else {
+				for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < B; t += nbb * blockDim.x)
+					sor_vector<REAL, VEC, false, true, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
+			}
 			SOR_TR(2);
+			// report to the courier right away: the interior work below is not the neighbours' business
+			__syncthreads();
+			if (threadIdx.x == 0) { asm volatile("fence.acq_rel.gpu;\n" ::: "memory"); atomicAdd(P.done, 1u); }
 		}
-		if (!bnd || G == 1) {
-			const uint32_t ib = G == 1 ? 0u : blockIdx.x - nbb, IG = G == 1 ? blockDim.x : (G - nbb) * blockDim.x;
-			for (uint32_t t = ib * blockDim.x + threadIdx.x; t < n - B; t += IG) sor_vector<REAL, VEC, false, true>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
+		// interior.  A static grid-stride split gives every thread floor or ceil of (entries / threads) entries -- 7 or 8 at 256^3
+		// on two ranks: the barrier then waits 4 us for the blocks that got 8 -- and leaves the boundary blocks idle once they have
+		// served the neighbours.  So all but the last two or three entries per interior thread are split statically (the same whole
+		// number for every thread); the tail is handed out through a ticket counter, one entry per thread and ticket (a thread's
+		// entries are serial, ~2 us each under load), to the boundary blocks as well.  Short sweeps (fewer than 4 entries per thread)
+		// stay static: a ticket costs an L2 round trip.
+		{
+			const uint32_t nI = n - B, IT = (G - nbb) * blockDim.x, per = nI / IT;
+			const uint32_t nS = per >= 4u ? (per - 2u) * IT : nI;
+			if (!bnd) {
+				// A thread's entries are serial and each is a chain of dependent loads (list -> mask -> p): the list entry is fetched
+				// two entries ahead and the mask one ahead, so that only the p loads remain on the chain.
+				typedef typename VecT<REAL, VEC>::mtype M;
+				uint32_t t = (blockIdx.x - nbb) * blockDim.x + threadIdx.x;
+				uint32_t e0 = t < nS ? __ldg(list + n_lo + t) : 0u, e1 = t + IT < nS ? __ldg(list + n_lo + t + IT) : 0u;
+				M m0 = t < nS ? sor_mask<REAL, VEC>(sp, e0) : (M)0;
+				for (; t < nS; t += IT) {
+					const uint32_t e2 = t + 2u * IT < nS ? __ldg(list + n_lo + t + 2u * IT) : 0u;
+					const M m1 = t + IT < nS ? sor_mask<REAL, VEC>(sp, e1) : (M)0;
+					sor_vector_m<REAL, VEC, false, true>(sp, omega, one_minus_omega, e0, m0);
+					e0 = e1; e1 = e2; m0 = m1;
+				}
+			}
+			if (nS < nI) {
+				uint32_t* const ticket = P.gbar + 32 * (FS3_SOR_GEN_LINES + 2 + (k & 1));
+				const uint32_t nch = (nI - nS + FS3_SOR_CHUNK - 1) / FS3_SOR_CHUNK;
+				if (threadIdx.x == 0) s_chunk = atomicAdd(ticket, 1u);
+				__syncthreads();
+				uint32_t ch = s_chunk;
+				while (ch < nch) {
+					__syncthreads();   // everybody has read s_chunk
+					uint32_t nxt = 0;
+					if (threadIdx.x == 0) nxt = atomicAdd(ticket, 1u);   // its latency overlaps the chunk's sweep
+					for (uint32_t e = threadIdx.x; e < FS3_SOR_CHUNK; e += blockDim.x) {
+						const uint32_t t = nS + ch * FS3_SOR_CHUNK + e;
+						if (t < nI) sor_vector<REAL, VEC, false, true>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
+					}
+					if (threadIdx.x == 0) s_chunk = nxt;
+					__syncthreads();
+					ch = s_chunk;
+				}
+			}
 		}
-		// ---- grid barrier; the boundary blocks serve the neighbours AFTER they have arrived ----------------------------------------
-		// Any fence of a thread that has stores (or atomics) to a peer in flight waits for their NVLink acknowledgements (4 - 6 us
-		// measured, gpu scope as well as system scope), so such a thread cannot arrive quickly.  Hence: the boundary blocks sweep
-		// their entries into local memory only; thread 0 (which never touches peer memory) arrives; THEN warps 1.. copy the block's
-		// entries from L2 into the neighbours' ghost planes and lane 0 of warp 1 fences at system scope and stores the epoch into
-		// this block's word of the neighbours' flag arrays -- while the other blocks are already in the next half sweep.  (One word
-		// per block: 148 remote atomics on ONE word serialise at the target, 9 us measured.)  Red (flag R) publishes no data, only
-		// "my reads of the ghost blacks are done": they are (their values went into stores that precede the block barrier).
-		__shared__ int s_last;
+		// ---- boundary blocks report to the courier; grid barrier of the sweeping blocks ---------------------------------------------
 		__syncthreads();
 		SOR_TR(4);
 		if (threadIdx.x == 0) {
 			// (acq_rel fences: __threadfence() is the sequentially consistent one, which this protocol does not need)
 			asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
 			const uint32_t old = atomicAdd(P.gbar, 1u);
-			s_last = old == (uint32_t)(k + 1) * G - 1u;
-			if (s_last) {
+			if (old == (uint32_t)(k + 1) * G - 1u) {
+				asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
+				// the ticket counter of the next half sweep's parity was last used two half sweeps ago: reset it before anybody leaves
+				asm volatile("st.relaxed.gpu.global.u32 [%0], %1;\n" ::"l"(P.gbar + 32 * (FS3_SOR_GEN_LINES + 2 + ((k + 1) & 1))), "r"(0u) : "memory");
 				asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
 				for (int r = 1; r <= FS3_SOR_GEN_LINES; r++) asm volatile("st.relaxed.gpu.global.u32 [%0], %1;\n" ::"l"(P.gbar + 32 * r), "r"((uint32_t)k + 1u) : "memory");
+				SOR_TR(5);
+			} else {
+				SOR_TR(5);
+				const uint32_t* const gen = P.gbar + 32 * (1 + (blockIdx.x % FS3_SOR_GEN_LINES));
+				const long long t0 = clock64();
+				for (unsigned itn = 1;; itn++) {
+					uint32_t v;
+					asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(gen) : "memory");
+					if (v >= (uint32_t)k + 1u) break;
+					__nanosleep(100);
+					if ((itn & 1023u) == 0 && (*reinterpret_cast<volatile int*>(P.flags + 2) || clock64() - t0 > 8000000000LL)) { P.flags[2] = 1; break; }
+				}
+				asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
 			}
-			SOR_TR(5);
-		}
-		if (bnd && c) __syncthreads();   // (the copy's peer stores would hold up thread 0's fence)
-		if (bnd && warp >= 1) {
-			if (c) {
-				// this block's entries are t0 + j, j < blockDim.x, for t0 = blockIdx.x * blockDim.x + m * nbb * blockDim.x
-				for (uint32_t t0 = blockIdx.x * blockDim.x; t0 < B; t0 += nbb * blockDim.x)
-					for (uint32_t j = threadIdx.x - 32; j < blockDim.x && t0 + j < B; j += blockDim.x - 32) {
-						const uint32_t t = t0 + j;
-						const size_t base = (size_t)(__ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))) & 0x7fffffffu) * VEC;
-						REAL v[VEC];
-						ldv_cg(sp.own + base, v);
-						if (sp.peer_lo && base >= sp.lo_begin && base < sp.lo_end) stv(sp.peer_lo + base, v);
-						if (sp.peer_hi && base >= sp.hi_begin && base < sp.hi_end) stv(sp.peer_hi + base, v);
-					}
-				asm volatile("bar.sync 1, %0;\n" ::"r"(blockDim.x - 32) : "memory");
-			}
-			if (threadIdx.x == 32) {
-				if (c) asm volatile("fence.acq_rel.sys;\n" ::: "memory");
-				uint32_t* const f0 = c ? P.peer_B[0] : P.peer_R[0];
-				uint32_t* const f1 = c ? P.peer_B[1] : P.peer_R[1];
-				if (f0) fs3_st_relaxed_sys(f0 + blockIdx.x, P.e0 + (uint32_t)it + 1u);
-				if (f1) fs3_st_relaxed_sys(f1 + blockIdx.x, P.e0 + (uint32_t)it + 1u);
-#ifdef FS3_SOR_TRACE
-				if (tr) tr[3] = fs3_gtime();
-#endif
-			}
-		}
-		if (threadIdx.x == 0 && !s_last) {
-			// the generation is replicated over FS3_SOR_GEN_LINES lines (= L2 slices): hundreds of CTAs polling ONE line while the
-			// others are still sweeping take a large share of that slice's request rate, and the sweep is as slow as its slowest slice
-			const uint32_t* const gen = P.gbar + 32 * (1 + (blockIdx.x % FS3_SOR_GEN_LINES));
-			const long long t0 = clock64();
-			for (unsigned itn = 1;; itn++) {
-				uint32_t v;
-				asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(gen) : "memory");
-				if (v >= (uint32_t)k + 1u) break;
-				__nanosleep(100);
-				if ((itn & 1023u) == 0 && (*reinterpret_cast<volatile int*>(P.flags + 2) || clock64() - t0 > 8000000000LL)) { P.flags[2] = 1; break; }
-			}
-			asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
 		}
 		__syncthreads();
 		SOR_TR(6);
 	}
-	// the neighbours' last blacks have landed in the ghost planes when the kernel ends (the gradient reads them)
-	if (blockIdx.x == 0 && warp < 2) {
-		const uint32_t* const w = warp ? P.my_B[1] : P.my_B[0];
-		if (w) for (uint32_t i = lane; i < nbb; i += 32) fs3_flag_wait(w + i, P.e0 + (uint32_t)P.iters, P.flags, 0);
+	// ---- the gradient reads the neighbours' nearest plane of both colours from the local ghost planes: red is there (swept here),
+	// black is fetched now, once the neighbours' last black half sweep has been flagged
+	if (bnd) {
+		if (threadIdx.x == 0 && P.peer_B[0]) fs3_flag_wait(P.my_B, P.e0 + (uint32_t)P.iters, P.flags, 0);
+		if (threadIdx.x == 1 && P.peer_B[1]) fs3_flag_wait(P.my_B + 1, P.e0 + (uint32_t)P.iters, P.flags, 0);
+		__syncthreads();
+		REAL* const black = sy.p[1];
+		const size_t pl = sy.rb.plane;
+		for (int side = 0; side < 2; side++) {
+			const REAL* const src = reinterpret_cast<const REAL*>(side ? P.peer_black[1] : P.peer_black[0]);
+			if (!src) continue;
+			const size_t a = side ? P.hi_begin + pl : P.lo_begin - pl;
+			for (size_t v = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * VEC; v < pl; v += (size_t)nbb * blockDim.x * VEC) {
+				REAL t[VEC];
+				ldv_sys(src + a + v, t);
+				stv(black + a + v, t);
+			}
+		}
 	}
 }
 
@@ -841,36 +922,36 @@ template <typename REAL, int VEC> static int sor_persistent2_t(fs3_sim* s, int i
 	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sor_persistent2<REAL, VEC>, FS3_SOR_THREADS, 0));
 	per_sm = std::max(1, per_sm);
 	const size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * (s->z1 - s->z0 + 2);
-	const int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, FS3_SOR_THREADS)), (long long)s->sm_count * per_sm);
+	// sweeping blocks + the courier, all co-resident
+	const int nb = (int)std::min<long long>(std::max<long long>(2, cdiv((long long)threads, FS3_SOR_THREADS)), (long long)s->sm_count * per_sm - 1);
+	if (nb < 2) { s->err = "device too small for the one-launch sharded solve"; return FS3_ERR_STATE; }
 	SorPersist2 P;
 	const bool lo = s->rank > 0, hi = s->rank < s->world - 1;
 	const size_t pl = s->rb.plane;
-	// flag arrays in sor_done (words): B from below 1024, B from above 1280, R from below 1536, R from above 1792; 256 each
-	uint32_t* const fl_lo = lo ? fs3_peer(s, s->rank - 1, s->sor_done) : nullptr;
-	uint32_t* const fl_hi = hi ? fs3_peer(s, s->rank + 1, s->sor_done) : nullptr;
+	uint32_t* const bar_lo = lo ? fs3_peer(s, s->rank - 1, s->bar) + FS3_MAX_WORLD : nullptr;
+	uint32_t* const bar_hi = hi ? fs3_peer(s, s->rank + 1, s->bar) + FS3_MAX_WORLD : nullptr;
 	P.peer_black[0] = lo ? fs3_peer(s, s->rank - 1, (char*)s->p[1]) : nullptr;
 	P.peer_black[1] = hi ? fs3_peer(s, s->rank + 1, (char*)s->p[1]) : nullptr;
-	P.peer_B[0] = lo ? fl_lo + 1280 : nullptr; P.peer_B[1] = hi ? fl_hi + 1024 : nullptr;
-	P.peer_R[0] = lo ? fl_lo + 1792 : nullptr; P.peer_R[1] = hi ? fl_hi + 1536 : nullptr;
-	P.my_B[0] = lo ? s->sor_done + 1024 : nullptr; P.my_B[1] = hi ? s->sor_done + 1280 : nullptr;
-	P.my_R[0] = lo ? s->sor_done + 1536 : nullptr; P.my_R[1] = hi ? s->sor_done + 1792 : nullptr;
+	// my flags go to the lower neighbour's "from above" slots (+1, +3) and to the upper neighbour's "from below" slots (+0, +2)
+	P.peer_B[0] = lo ? bar_lo + 1 : nullptr; P.peer_B[1] = hi ? bar_hi + 0 : nullptr;
+	P.peer_R[0] = lo ? bar_lo + 3 : nullptr; P.peer_R[1] = hi ? bar_hi + 2 : nullptr;
+	P.my_B = s->bar + FS3_MAX_WORLD; P.my_R = s->bar + FS3_MAX_WORLD + 2;
 	P.e0 = s->sor_e0; P.iters = iters;
 	// Boundary blocks do nothing else (they wait on the neighbours), and the sweep's throughput is proportional to the blocks that
-	// work on it, so their number follows their share of the planes (x 2 for their waits), a function of the grid and the world
-	// size only: every rank must arrive at the same number.  256^3: 139 of 592 blocks at 8 ranks, 36 at 2 ranks.
+	// work on it, so their number follows their share of the planes (x 2 for their waits): 256^3: 139 of 591 blocks at 8 ranks, 36 at 2.
 	P.nbb = (uint32_t)std::min(std::min(std::max(nb / 4, 1), FS3_SOR_MAX_NBB), std::max(8, (int)(2LL * nb * 4 / (s->z1 - s->z0 + 2))));
-	// array plane index of cell plane z is z + 1.  Pushed: the slab's first / last two planes of black
-	P.lo_begin = pl * (size_t)(s->z0 + 1); P.lo_end = pl * (size_t)(s->z0 + 3);
-	P.hi_begin = pl * (size_t)(s->z1 - 1); P.hi_end = pl * (size_t)(s->z1 + 1);
-	// red: planes z0-1, z0 and z1-1, z1 read the neighbours' blacks; black: planes z0, z0+1 and z1-2, z1-1 are pushed.
+	P.nbb = std::min<uint32_t>(P.nbb, (uint32_t)nb - 1u);
+	// array plane index of cell plane z is z + 1
+	P.lo_begin = pl * (size_t)(s->z0 + 1); P.hi_begin = pl * (size_t)s->z1;
+	// red: planes z0-1, z0 and z1-1, z1 read the neighbours' blacks; black: planes z0, z0+1 and z1-2, z1-1 are what the neighbours read.
 	// Without a neighbour the range is empty (the scan is 0 up to the list's first plane and n from its last one on).
 	P.n_lo[0] = s->sor_pos[0] + pl * (size_t)(lo ? s->z0 + 2 : s->z0 + 1) / VEC;
 	P.n_hi[0] = s->sor_pos[0] + pl * (size_t)(hi ? s->z1 : s->z1 + 1) / VEC;
 	P.n_lo[1] = s->sor_pos[1] + pl * (size_t)(lo ? s->z0 + 3 : s->z0 + 1) / VEC;
 	P.n_hi[1] = s->sor_pos[1] + pl * (size_t)(hi ? s->z1 - 1 : s->z1 + 1) / VEC;
 	for (int c = 0; c < 2; c++) { P.list[c] = s->sor_list[c]; P.count[c] = s->sor_count[c]; }
-	P.gbar = s->sor_done + 32; P.flags = s->dev_flags;
-	FS3_CUDA(cudaMemsetAsync(s->sor_done, 0, 4096, s->stream));   // the barrier words; NOT the flag arrays the neighbours write
+	P.done = s->sor_done; P.gbar = s->sor_done + 32; P.flags = s->dev_flags;
+	FS3_CUDA(cudaMemsetAsync(s->sor_done, 0, 4096, s->stream));
 #ifdef FS3_SOR_TRACE
 	static unsigned long long* trace_buf = nullptr;
 	static int trace_calls = 0;
@@ -878,7 +959,7 @@ template <typename REAL, int VEC> static int sor_persistent2_t(fs3_sim* s, int i
 	P.trace = trace_buf;
 #endif
 	void* args[] = {(void*)&sy, (void*)&omega, (void*)&omo, (void*)&P};
-	FS3_CUDA(cudaLaunchCooperativeKernel((const void*)k_sor_persistent2<REAL, VEC>, dim3(nb), dim3(FS3_SOR_THREADS), args, 0, s->stream));
+	FS3_CUDA(cudaLaunchCooperativeKernel((const void*)k_sor_persistent2<REAL, VEC>, dim3(nb + 1), dim3(FS3_SOR_THREADS), args, 0, s->stream));
 	FS3_LAUNCH_CHECK();
 #ifdef FS3_SOR_TRACE
 	if (++trace_calls == 4) {
@@ -896,7 +977,7 @@ template <typename REAL, int VEC> static int sor_persistent2_t(fs3_sim* s, int i
 			const unsigned long long* base = trace_buf + (64 + (size_t)h * 1024) * 8;
 			unsigned long long tmin = ~0ULL;
 			for (int b = 0; b < nb; b++) tmin = std::min(tmin, base[(size_t)b * 8]);
-			for (int b = 0; b < nb; b++) {
+			for (int b = 0; b <= nb; b++) {
 				const unsigned long long* t = base + (size_t)b * 8;
 				snprintf(buf, sizeof buf, "sorblocks rank %d half %d block %d%s", s->rank, 96 + h, b, b < (int)P.nbb ? " B" : ""); out += buf;
 				for (int i = 0; i < 7; i++) { snprintf(buf, sizeof buf, " %6lld", t[i] ? (long long)(t[i] - tmin) : -1LL); out += buf; }
