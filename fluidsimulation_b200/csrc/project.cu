@@ -249,12 +249,17 @@ __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_half(Sys<
 		// previous half sweep has completed and its stores are visible.  The list, the mask and b are constant during
 		// the solve, so the first entry is fetched ahead of the wait.
 		asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
-		uint32_t ent = gtid < n ? __ldg(list + gtid) : 0u;
+		// A thread's entries are serial and each is a chain of dependent loads (list -> mask -> p): the list entry is fetched two
+		// entries ahead and the mask one ahead, so that only the p loads remain on the chain.
+		typedef typename VecT<REAL, VEC>::mtype M;
+		uint32_t e0 = gtid < n ? __ldg(list + gtid) : 0u, e1 = gtid + G < n ? __ldg(list + gtid + G) : 0u;
+		M m0 = gtid < n ? sor_mask<REAL, VEC>(sp, e0) : (M)0;
 		asm volatile("griddepcontrol.wait;\n" ::: "memory");
 		for (uint32_t t = gtid; t < n; t += G) {
-			const uint32_t nxt = t + G < n ? __ldg(list + t + G) : 0u;
-			sor_vector<REAL, VEC, false>(sp, omega, one_minus_omega, ent);
-			ent = nxt;
+			const uint32_t e2 = t + 2u * G < n ? __ldg(list + t + 2u * G) : 0u;
+			const M m1 = t + G < n ? sor_mask<REAL, VEC>(sp, e1) : (M)0;
+			sor_vector_m<REAL, VEC, false>(sp, omega, one_minus_omega, e0, m0);
+			e0 = e1; e1 = e2; m0 = m1;
 		}
 		return;
 	}
