@@ -322,7 +322,7 @@ int fs3i_sor_prepare(fs3_sim* s);
 int fs3i_sor_half_launch(fs3_sim* s, int k);                                // half sweep k of the current projection
 bool fs3i_sor_two_plane(const fs3_sim* s);                                  // sharded solve with two-plane halos (one exchange per iteration)?
 int fs3i_sor_push_system(fs3_sim* s);                                       // two-plane halos: b, diag, mask of my boundary reds to the neighbours
-int fs3i_sor_persistent(fs3_sim* s, int halves);                            // multi-process sharded handle: the whole solve in one cooperative launch
+int fs3i_sor_persistent(fs3_sim* s, int iters);                             // multi-process sharded handle: the whole solve in one cooperative launch
 int fs3i_project_gradient(fs3_sim* s, float dt, bool from_old, bool with_gravity);
 // levelset.cu / p2g.cu pieces
 int fs3i_levelset_seed(fs3_sim* s, cudaStream_t st = nullptr);

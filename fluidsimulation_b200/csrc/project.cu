@@ -298,117 +298,39 @@ __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_half(Sys<
 	for (uint32_t t = ib * blockDim.x + threadIdx.x; t < n - B; t += IG) sor_vector<REAL, VEC, false>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
 }
 
-// ---- sharded solve in ONE launch (multi-process handles) ---------------------------------------------------------------
-// With a slab per GPU a half sweep needs ~4.5 us of memory traffic but cost 13 us as a launch of its own: the launch, and one
-// NVLink flag round trip that could only start once the kernel was running.  Here all 2 * iterations half sweeps are one
-// cooperative launch: a half sweep is the boundary-first schedule of k_sor_half<.., SHARD> followed by a grid barrier (arrive
-// counter in L2), and the neighbours' epoch flags are polled by CTAs that are already resident.  p travels through L2 only
-// (ld.cg / write-through stores): L1 is not coherent across SMs inside a launch.
-// Measured on 2 GPUs at 256^3 (us per half sweep): this arrangement 17.1; boundary CTAs that also take a share of the interior
-// after their two planes 21.0 (they start it late and the grid barrier waits for them); one 1024-thread CTA per SM with
-// shared interior work 22.1.  The disjoint split stays.
-// Grid barrier of the one-launch solves (all CTAs are co-resident: cooperative launch).  Arrivals are atomics on one word; the last
-// arriver publishes the generation in ANOTHER 128-byte line, which is what everybody else polls with relaxed loads: measured with
-// the arrival word polled by acquire loads of all 592 CTAs, a CTA left the barrier 4 us after the last arrival (tools/sor_trace.py).
-// The generation is replicated over FS3_SOR_GEN_LINES lines (block b polls copy b % LINES): one polled line takes a large share of
-// its L2 slice's request rate while other CTAs are still sweeping.  bar[0] = arrivals, bar[32 r], r = 1.., = generation copies;
-// all zero at launch; k counts the barriers of this launch from 0.
+// ---- sharded solve in ONE cooperative launch, two-plane halos (multi-process handles, slabs >= 4 planes) ---------------------
+// Launching every half sweep (round 1) cost 13 us each on 8 GPUs where the slab's memory traffic needs 3.5; one launch with
+// one-plane halos pushed into the neighbours every half sweep (round 2, first version) still 13.8: time stamps taken inside that
+// kernel (tools/sor_trace.py) showed that every half sweep carried  store to peer -> fence -> flag -> flight  and that
+//   * a fence (gpu scope as well as system scope) of a CTA that has stores or atomics to a peer in flight waits for their
+//     NVLink acknowledgements: 4 - 12 us;
+//   * 148 remote atomics on ONE flag word serialise at the target: 9 us;
+//   * sweeping entries whose operands a peer had just written took 4 us instead of 1;
+//   * a CTA left the grid barrier (all CTAs polling the arrival word with acquire loads) 4 us after the last arrival.
+// Hence this arrangement:
+//   * TWO-plane halos, one exchange per ITERATION.  A rank also sweeps the RED cells of each neighbour's nearest plane itself
+//     (the owner's b, diag, mask of that plane are copied once per projection, fs3i_sor_push_system; same inputs, same arithmetic:
+//     bit-identical), so only BLACK values cross the boundary.  Lists: red = slab + one ghost plane per neighbour, black = slab.
+//   * PULL.  The red EDGE entries (ghost plane + own first / last plane) read the neighbours' blacks straight from the
+//     neighbours' arrays (ld.relaxed.sys, same offsets in every arena: sor_vector_m<EDGE>).  No sweeping CTA ever stores to a peer.
+//   * Two flags per neighbour and iteration: B "my boundary blacks (first / last two planes) of iteration i are written", waited
+//     for by the neighbour's red half sweep i + 1, and R "I have read your blacks of iteration i - 1", waited for by the
+//     neighbour's black half sweep i before it overwrites them.  Dedicated boundary blocks sweep these entries FIRST, so both
+//     flags are raised at the start of a half sweep and needed at the start of the next one.
+//   * A COURIER CTA is the only one that writes to a peer: it waits on a local counter the boundary blocks bump, fences once at
+//     system scope and stores the flag into both neighbours' arenas.  It takes no part in the grid barrier.
+//   * Grid barrier of the sweeping CTAs: arrivals are atomics on one word; the last arriver publishes the generation in
+//     FS3_SOR_GEN_LINES separate 128-byte lines (= L2 slices), block b polls copy b % LINES with relaxed loads and back-off: CTAs
+//     polling ONE line while others still sweep take a large share of that slice's request rate.
+//   * After the last iteration the boundary blocks fetch the neighbours' nearest black plane into the local ghost plane: the
+//     gradient reads both colours of it.
+// p travels through L2 only (ld.cg / write-through stores): L1 is not coherent across SMs inside a launch.
+// sor_done (words): [0] boundary blocks that have reported, cumulative; [32] barrier arrivals; [32 r], r = 1..LINES, generation
+// copies; [32 (LINES + 2 + parity)] ticket counters of the interior tail.  All zero at launch.
 #define FS3_SOR_GEN_LINES 16
-#define FS3_SOR_CHUNK 256   // entries per ticket of the dynamic tail of the one-launch solve's interior sweep
-__device__ __forceinline__ void sor_grid_barrier(uint32_t* bar, uint32_t k, uint32_t G, int* flags) {
-	__syncthreads();
-	if (threadIdx.x == 0) {
-		asm volatile("fence.acq_rel.gpu;\n" ::: "memory");   // (__threadfence() is the sequentially consistent fence: not needed here)
-		const uint32_t old = atomicAdd(bar, 1u);
-		if (old == (k + 1u) * G - 1u) {
-			asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
-			for (int r = 1; r <= FS3_SOR_GEN_LINES; r++) asm volatile("st.relaxed.gpu.global.u32 [%0], %1;\n" ::"l"(bar + 32 * r), "r"(k + 1u) : "memory");
-		} else {
-			const uint32_t* const gen = bar + 32 * (1 + (blockIdx.x % FS3_SOR_GEN_LINES));
-			const long long t0 = clock64();
-			for (unsigned it = 1;; it++) {
-				uint32_t v;
-				asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(gen) : "memory");
-				if (v >= k + 1u) break;
-				__nanosleep(100);
-				if ((it & 1023u) == 0 && (*reinterpret_cast<volatile int*>(flags + 2) || clock64() - t0 > 8000000000LL)) { flags[2] = 1; break; }
-			}
-			asm volatile("fence.acq_rel.gpu;\n" ::: "memory");
-		}
-	}
-	__syncthreads();
-}
-struct SorPersist {
-	void* peer_p[2][2];       // [colour][lower / upper neighbour]
-	uint32_t* peer_flag[2];
-	const uint32_t* my_flag;
-	uint32_t e0;              // epoch of "system set up"; half sweep k waits for e0 + k and signals e0 + k + 1
-	int halves;
-	size_t lo_begin, lo_end, hi_begin, hi_end;
-	const uint32_t *n_lo[2], *n_hi[2], *list[2], *count[2];
-	uint32_t *done, *gbar;
-	int* flags;
-};
-template <typename REAL, int VEC>
-__global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_persistent(Sys<REAL> sy, REAL omega, REAL one_minus_omega, SorPersist P) {
-	const uint32_t G = gridDim.x;
-	for (int k = 0; k < P.halves; k++) {
-		const int c = k & 1;
-		SorShard sh;
-		sh.peer_p[0] = P.peer_p[c][0]; sh.peer_p[1] = P.peer_p[c][1];
-		sh.lo_begin = P.lo_begin; sh.lo_end = P.lo_end; sh.hi_begin = P.hi_begin; sh.hi_end = P.hi_end;
-		const SorPtrs<REAL> sp = sor_ptrs<REAL>(sy, c, sh);
-		const uint32_t* __restrict__ list = c ? P.list[1] : P.list[0];
-		const uint32_t n = __ldg(c ? P.count[1] : P.count[0]), n_lo = __ldg(c ? P.n_lo[1] : P.n_lo[0]), n_hi = __ldg(c ? P.n_hi[1] : P.n_hi[0]);
-		const uint32_t B = n_lo + (n - n_hi);
-		const uint32_t nbb = min(max(G / 4u, 1u), max(1u, (B + blockDim.x - 1) / blockDim.x));   // blocks that hold the boundary work
-		if (blockIdx.x < nbb || G == 1) {
-			if (threadIdx.x == 0 && P.peer_flag[0]) fs3_flag_wait(P.my_flag, P.e0 + (uint32_t)k, P.flags, 0);
-			if (threadIdx.x == 1 && P.peer_flag[1]) fs3_flag_wait(P.my_flag + 1, P.e0 + (uint32_t)k, P.flags, 0);
-			__syncthreads();
-			bool pushed = false;
-			for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < B; t += nbb * blockDim.x) {
-				sor_vector<REAL, VEC, true, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
-				pushed = true;
-			}
-			if (pushed) __threadfence_system();   // my peer stores are visible system-wide before the block reports in
-			__syncthreads();
-			if (threadIdx.x == 0) {
-				const uint32_t dn = atomicAdd(P.done, 1u);
-				if (dn == nbb - 1) {
-					*P.done = 0;
-					__threadfence_system();
-					if (P.peer_flag[0]) fs3_st_relaxed_sys(P.peer_flag[0], P.e0 + (uint32_t)k + 1u);
-					if (P.peer_flag[1]) fs3_st_relaxed_sys(P.peer_flag[1], P.e0 + (uint32_t)k + 1u);
-				}
-			}
-		}
-		if (blockIdx.x >= nbb || G == 1) {
-			const uint32_t ib = G == 1 ? 0u : blockIdx.x - nbb, IG = G == 1 ? blockDim.x : (G - nbb) * blockDim.x;
-			for (uint32_t t = ib * blockDim.x + threadIdx.x; t < n - B; t += IG) sor_vector<REAL, VEC, false, true>(sp, omega, one_minus_omega, __ldg(list + n_lo + t));
-		}
-		// ---- grid barrier: the next half sweep reads this colour everywhere -------------------------------------------------
-		sor_grid_barrier(P.gbar, (uint32_t)k, G, P.flags);
-	}
-}
-
-// ---- the same solve with TWO-plane halos: one exchange per ITERATION, both flags off the critical path ----------------------
-// With one-plane halos every half sweep contains a cross-GPU dependency (wait for the neighbour's plane, compute the own boundary,
-// store it over NVLink, system fence, flag, flight: ~7 us), which no schedule inside one rank can hide: at 8 ranks a half sweep
-// took 13.8 us where the memory traffic needs 3.5.  Here a rank also keeps the neighbours' nearest TWO planes: it sweeps the RED
-// cells of the nearest ghost plane itself (same inputs, same arithmetic as the owner: bit-identical), so only BLACK values travel,
-// two planes each way, once per iteration:
-//   red   half sweep: the EDGE entries first (ghost plane + own first plane, the ones that read the neighbour's blacks): wait for
-//                     "blacks of the previous iteration are here" (flag B), sweep them, raise "I have read them" (flag R);
-//                     then the rest;
-//   black half sweep: the BOUNDARY entries first (own first / last two planes): wait for the neighbour's R (it no longer reads
-//                     the ghost blacks I am about to overwrite), sweep them, storing every result into the neighbour's ghost
-//                     planes too, system fence, raise B; then the rest.
-// Both flags are sent at the START of a half sweep and needed at the start of the NEXT one, so the NVLink latency overlaps the
-// interior work; a grid barrier still separates the half sweeps.  The system (b, diag, mask) of the ghost plane is the owner's,
-// copied once per projection (fs3i_sor_push_system).  Lists: red = slab + one ghost plane per neighbour, black = slab.
+#define FS3_SOR_CHUNK 256   // entries per ticket of the dynamic tail of the interior sweep
 #define FS3_SOR_MAX_NBB 256
-struct SorPersist2 {
+struct SorPersist {
 	const void* peer_black[2];   // colour-1 array of the lower / upper neighbour (nullptr: no neighbour)
 	uint32_t *peer_B[2], *peer_R[2];
 	const uint32_t *my_B, *my_R;   // [0] written by the lower, [1] by the upper neighbour
@@ -429,7 +351,7 @@ __device__ __forceinline__ unsigned long long fs3_gtime() { unsigned long long t
 #define SOR_TR(i) do { } while (0)
 #endif
 template <typename REAL, int VEC>
-__global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_persistent2(Sys<REAL> sy, REAL omega, REAL one_minus_omega, SorPersist2 P) {
+__global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_persistent(Sys<REAL> sy, REAL omega, REAL one_minus_omega, SorPersist P) {
 	const uint32_t G = gridDim.x - 1;   // sweeping blocks; the last block is the courier
 	const uint32_t nbb = P.nbb;         // of which the first nbb sweep the edge / boundary entries
 	if (blockIdx.x == G) {
@@ -880,8 +802,10 @@ template <typename REAL, int VEC> static int sor_half_t(fs3_sim* s, int k) {
 }
 int fs3i_sor_half_launch(fs3_sim* s, int k) { return s->alloc_precision ? sor_half_t<float, 4>(s, k) : sor_half_t<double, 2>(s, k); }
 
-// all `halves` half sweeps of a multi-process sharded handle in one cooperative launch
-template <typename REAL, int VEC> static int sor_persistent_t(fs3_sim* s, int halves) {
+// two-plane halos: multi-process handles whose slab has room for two distinct boundary planes on either side
+bool fs3i_sor_two_plane(const fs3_sim* s) { return s->world > 1 && !s->lockstep && s->nz / s->world >= 4; }
+
+template <typename REAL, int VEC> static int sor_persistent_t(fs3_sim* s, int iters) {
 	Sys<REAL> sy = make_sys<REAL>(s);
 	REAL omega = (REAL)fs3_omega(s);
 	if (sizeof(REAL) == 4) omega = (REAL)2 - (REAL)3.16343 / s->nx, omega = s->prm.omega > 0 ? (REAL)s->prm.omega : omega;
@@ -889,48 +813,11 @@ template <typename REAL, int VEC> static int sor_persistent_t(fs3_sim* s, int ha
 	int per_sm = 0;
 	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sor_persistent<REAL, VEC>, FS3_SOR_THREADS, 0));
 	per_sm = std::max(1, per_sm);
-	const size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * (s->z1 - s->z0);
-	const int nb = (int)std::min<long long>(std::max(1, cdiv((long long)threads, FS3_SOR_THREADS)), (long long)s->sm_count * per_sm);
-	SorPersist P;
-	const bool lo = s->rank > 0, hi = s->rank < s->world - 1;
-	for (int c = 0; c < 2; c++) {
-		P.peer_p[c][0] = lo ? fs3_peer(s, s->rank - 1, (char*)s->p[c]) : nullptr;
-		P.peer_p[c][1] = hi ? fs3_peer(s, s->rank + 1, (char*)s->p[c]) : nullptr;
-		P.n_lo[c] = s->sor_pos[c] + s->rb.plane * (size_t)(s->z0 + 2) / VEC;
-		P.n_hi[c] = s->sor_pos[c] + s->rb.plane * (size_t)s->z1 / VEC;
-		P.list[c] = s->sor_list[c]; P.count[c] = s->sor_count[c];
-	}
-	P.peer_flag[0] = lo ? fs3_peer(s, s->rank - 1, s->bar) + FS3_MAX_WORLD + 1 : nullptr;
-	P.peer_flag[1] = hi ? fs3_peer(s, s->rank + 1, s->bar) + FS3_MAX_WORLD + 0 : nullptr;
-	P.my_flag = s->bar + FS3_MAX_WORLD;
-	P.e0 = s->sor_e0; P.halves = halves;
-	P.lo_begin = s->rb.plane * (size_t)(s->z0 + 1); P.lo_end = P.lo_begin + s->rb.plane;
-	P.hi_begin = s->rb.plane * (size_t)s->z1; P.hi_end = P.hi_begin + s->rb.plane;
-	P.done = s->sor_done; P.gbar = s->sor_done + 32; P.flags = s->dev_flags;
-	FS3_CUDA(cudaMemsetAsync(s->sor_done, 0, 4096, s->stream));
-	void* args[] = {(void*)&sy, (void*)&omega, (void*)&omo, (void*)&P};
-	FS3_CUDA(cudaLaunchCooperativeKernel((const void*)k_sor_persistent<REAL, VEC>, dim3(nb), dim3(FS3_SOR_THREADS), args, 0, s->stream));
-	FS3_LAUNCH_CHECK();
-	s->sor_epoch = s->sor_e0 + (uint32_t)halves;
-	return FS3_OK;
-}
-
-// two-plane halos: multi-process handles whose slab has room for two distinct boundary planes on either side
-bool fs3i_sor_two_plane(const fs3_sim* s) { return s->world > 1 && !s->lockstep && s->nz / s->world >= 4; }
-
-template <typename REAL, int VEC> static int sor_persistent2_t(fs3_sim* s, int iters) {
-	Sys<REAL> sy = make_sys<REAL>(s);
-	REAL omega = (REAL)fs3_omega(s);
-	if (sizeof(REAL) == 4) omega = (REAL)2 - (REAL)3.16343 / s->nx, omega = s->prm.omega > 0 ? (REAL)s->prm.omega : omega;
-	REAL omo = (REAL)1 - omega;
-	int per_sm = 0;
-	FS3_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sor_persistent2<REAL, VEC>, FS3_SOR_THREADS, 0));
-	per_sm = std::max(1, per_sm);
 	const size_t threads = (size_t)(s->rb.hp / VEC) * s->ny * (s->z1 - s->z0 + 2);
 	// sweeping blocks + the courier, all co-resident
 	const int nb = (int)std::min<long long>(std::max<long long>(2, cdiv((long long)threads, FS3_SOR_THREADS)), (long long)s->sm_count * per_sm - 1);
 	if (nb < 2) { s->err = "device too small for the one-launch sharded solve"; return FS3_ERR_STATE; }
-	SorPersist2 P;
+	SorPersist P;
 	const bool lo = s->rank > 0, hi = s->rank < s->world - 1;
 	const size_t pl = s->rb.plane;
 	uint32_t* const bar_lo = lo ? fs3_peer(s, s->rank - 1, s->bar) + FS3_MAX_WORLD : nullptr;
@@ -964,7 +851,7 @@ template <typename REAL, int VEC> static int sor_persistent2_t(fs3_sim* s, int i
 	P.trace = trace_buf;
 #endif
 	void* args[] = {(void*)&sy, (void*)&omega, (void*)&omo, (void*)&P};
-	FS3_CUDA(cudaLaunchCooperativeKernel((const void*)k_sor_persistent2<REAL, VEC>, dim3(nb + 1), dim3(FS3_SOR_THREADS), args, 0, s->stream));
+	FS3_CUDA(cudaLaunchCooperativeKernel((const void*)k_sor_persistent<REAL, VEC>, dim3(nb + 1), dim3(FS3_SOR_THREADS), args, 0, s->stream));
 	FS3_LAUNCH_CHECK();
 #ifdef FS3_SOR_TRACE
 	if (++trace_calls == 4) {
@@ -996,9 +883,9 @@ template <typename REAL, int VEC> static int sor_persistent2_t(fs3_sim* s, int i
 	s->sor_epoch = s->sor_e0 + 2u * (uint32_t)iters;   // (the flags end at e0 + iters; the next projection's e0 lies above either scheme's range)
 	return FS3_OK;
 }
-int fs3i_sor_persistent(fs3_sim* s, int halves) {
-	if (fs3i_sor_two_plane(s)) return s->alloc_precision ? sor_persistent2_t<float, 4>(s, halves / 2) : sor_persistent2_t<double, 2>(s, halves / 2);
-	return s->alloc_precision ? sor_persistent_t<float, 4>(s, halves) : sor_persistent_t<double, 2>(s, halves);
+int fs3i_sor_persistent(fs3_sim* s, int iters) {
+	if (!fs3i_sor_two_plane(s)) { s->err = "the one-launch solve needs a multi-process handle with slabs of at least 4 planes"; return FS3_ERR_STATE; }
+	return s->alloc_precision ? sor_persistent_t<float, 4>(s, iters) : sor_persistent_t<double, 2>(s, iters);
 }
 // two-plane halos: the system (b, diag, mask) of the RED cells of my first / last plane goes to the neighbour that sweeps them too
 int fs3i_sor_push_system(fs3_sim* s) {

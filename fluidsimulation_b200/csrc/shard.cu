@@ -4,8 +4,11 @@
 // [z0, z1) and the particles whose cell (int)roundf(n*Z) (S3D.cpp:288) lies there.  All device memory of a rank is one
 // arena exported through ONE CUDA-IPC handle, so rank a reaches array X of rank b at  peer_base[b] + (X - arena).
 // Data moves by stores / copies into the peers' arrays over NVLink (no staging, no library collective):
-//   * SOR: the sweep kernel itself stores its boundary planes into the neighbours' ghost planes and raises their epoch
-//     flag from its last block (project.cu, k_sor_half<.., SHARD>);
+//   * SOR: a multi-process handle solves in ONE cooperative launch with two-plane halos: the neighbours' boundary planes of one
+//     colour are READ in place over NVLink once per iteration, and a courier CTA raises two flags per neighbour and iteration
+//     (project.cu, k_sor_persistent).  A lockstep group (and slabs under 4 planes) launch every half sweep: the sweep kernel
+//     stores its boundary plane into the neighbours' ghost planes and raises their epoch flag from its last block
+//     (k_sor_half<.., SHARD>);
 //   * particle migration: emigrants are packed per destination and copied to the tail of the destination's live range;
 //   * ghost layers for the P2G gather: one cell layer of sorted particles + its cell_start rows is PULLED from each
 //     neighbour and spliced in directly below / above the own range, so the gather kernel is unchanged;
@@ -382,10 +385,10 @@ int fs3i_step_phase(fs3_sim* s, int ph, float dt) {
 	}
 	if (ph < 6 + 2 * I) {   // compute + halo exchange in one kernel
 		s->sor_halves = 2 * I;
-		// one launch per half sweep for a lockstep group (the ranks' kernels take turns on one stream); a multi-process handle runs
-		// the whole solve as ONE cooperative launch whose CTAs exchange halos and epoch flags with the neighbours while resident
-		if (s->lockstep) return fs3i_sor_half_launch(s, ph - 6);
-		return ph == 6 ? fs3i_sor_persistent(s, 2 * I) : FS3_OK;
+		// one launch per half sweep for a lockstep group (the ranks' kernels take turns on one stream) and for slabs too thin for
+		// two-plane halos; a multi-process handle runs the whole solve as ONE cooperative launch
+		if (s->lockstep || !fs3i_sor_two_plane(s)) return fs3i_sor_half_launch(s, ph - 6);
+		return ph == 6 ? fs3i_sor_persistent(s, I) : FS3_OK;
 	}
 	if (ph == 6 + 2 * I) {  // pressure gradient on the slab; the projected field is gathered on every rank
 		// the copies of the previous step's field (stream3) have left before the gradient overwrites their source

@@ -54,7 +54,7 @@ def test_group_reset_bitexact(n, world):
     g.close()
 
 
-@pytest.mark.parametrize("n,world,steps", [(16, 2, 3), (16, 4, 2), (24, 2, 4), (24, 3, 2), (32, 4, 6), (96, 4, 2)])
+@pytest.mark.parametrize("n,world,steps", [(16, 2, 3), (16, 4, 2), (24, 2, 4), (24, 3, 2), (24, 8, 2), (32, 4, 6), (96, 4, 2)])
 def test_group_steps_bitexact_vs_single_gpu(n, world, steps):
     g, one = mkg(n, world), mk(n)
     for k in range(steps):
@@ -189,7 +189,7 @@ def test_group_reset_after_steps_and_hooks_refused():
     g.close()
 
 
-@pytest.mark.parametrize("world,n,steps,zflow", [(2, 24, 3, 0.0), (2, 24, 4, 4.0), (2, 32, 4, 4.0), (4, 64, 4, 4.0), (8, 96, 3, 2.0)])
+@pytest.mark.parametrize("world,n,steps,zflow", [(2, 24, 3, 0.0), (2, 24, 4, 4.0), (2, 32, 4, 4.0), (4, 12, 3, 2.0), (4, 64, 4, 4.0), (8, 96, 3, 2.0)])
 def test_multiprocess_sharded_step(world, n, steps, zflow):
     """One process per GPU over CUDA IPC: the merged result must equal the single-GPU run bit for bit.  With zflow the grid
     velocity W is forced before every step, so particles migrate between slabs and every rank's SOR halo carries fluid.
