@@ -405,12 +405,22 @@ __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_persisten
 			}
 			__syncthreads();
 			SOR_TR(1);
-			if (c) {
-				for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < B; t += nbb * blockDim.x)
-					sor_vector<REAL, VEC, false, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
-			} else {
-				for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < B; t += nbb * blockDim.x)
-					sor_vector<REAL, VEC, false, true, true>(sp, omega, one_minus_omega, __ldg(list + (t < n_lo ? t : n_hi + (t - n_lo))));
+			{
+				// (list two entries ahead, mask one ahead, as in the interior loop below: a thread's entries are serial)
+				typedef typename VecT<REAL, VEC>::mtype M;
+				const uint32_t BT = nbb * blockDim.x;
+				uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+#define SOR_BENT(u) __ldg(list + ((u) < n_lo ? (u) : n_hi + ((u) - n_lo)))
+				uint32_t e0 = t < B ? SOR_BENT(t) : 0u, e1 = t + BT < B ? SOR_BENT(t + BT) : 0u;
+				M m0 = t < B ? sor_mask<REAL, VEC>(sp, e0) : (M)0;
+				for (; t < B; t += BT) {
+					const uint32_t e2 = t + 2u * BT < B ? SOR_BENT(t + 2u * BT) : 0u;
+					const M m1 = t + BT < B ? sor_mask<REAL, VEC>(sp, e1) : (M)0;
+					if (c) sor_vector_m<REAL, VEC, false, true>(sp, omega, one_minus_omega, e0, m0);
+					else sor_vector_m<REAL, VEC, false, true, true>(sp, omega, one_minus_omega, e0, m0);
+					e0 = e1; e1 = e2; m0 = m1;
+				}
+#undef SOR_BENT
 			}
 			SOR_TR(2);
 			// report to the courier right away: the interior work below is not the neighbours' business
@@ -829,9 +839,11 @@ template <typename REAL, int VEC> static int sor_persistent_t(fs3_sim* s, int it
 	P.peer_R[0] = lo ? bar_lo + 3 : nullptr; P.peer_R[1] = hi ? bar_hi + 2 : nullptr;
 	P.my_B = s->bar + FS3_MAX_WORLD; P.my_R = s->bar + FS3_MAX_WORLD + 2;
 	P.e0 = s->sor_e0; P.iters = iters;
-	// Boundary blocks do nothing else (they wait on the neighbours), and the sweep's throughput is proportional to the blocks that
-	// work on it, so their number follows their share of the planes (x 2 for their waits): 256^3: 139 of 591 blocks at 8 ranks, 36 at 2.
-	P.nbb = (uint32_t)std::min(std::min(std::max(nb / 4, 1), FS3_SOR_MAX_NBB), std::max(8, (int)(2LL * nb * 4 / (s->z1 - s->z0 + 2))));
+	// Boundary blocks do little else (they wait on the neighbours, and their entries read remote memory), and the sweep's throughput
+	// is proportional to the blocks that work on it, so their number follows their share of the planes (two per neighbour; x 3 for
+	// the waits and the slower entries): 256^3: 147 of 591 blocks on an inner rank of 8, 107 of 4, 27 at 2 ranks.
+	const int edge_planes = 2 * ((lo ? 1 : 0) + (hi ? 1 : 0));
+	P.nbb = (uint32_t)std::min(std::min(std::max(nb / 4, 1), FS3_SOR_MAX_NBB), std::max(8, (int)(3LL * nb * edge_planes / (s->z1 - s->z0 + 2))));
 	P.nbb = std::min<uint32_t>(P.nbb, (uint32_t)nb - 1u);
 	// array plane index of cell plane z is z + 1
 	P.lo_begin = pl * (size_t)(s->z0 + 1); P.hi_begin = pl * (size_t)s->z1;
