@@ -19,6 +19,7 @@ def main():
     ap.add_argument("steps", type=int, nargs="?", default=3)
     ap.add_argument("--zflow", type=float, default=0.0, help="m/s: W is overwritten with this value before every step, so that particles "
                     "cross slab boundaries (migration) and both SOR neighbours of every interior rank carry fluid")
+    ap.add_argument("--fp32", action="store_true", help="pressure solve in fp32 (set_params precision=1) on the sharded run and on the twin")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
     dist.init_process_group(backend="gloo")
@@ -27,6 +28,8 @@ def main():
     owned0 = sim.num_local_particles
 
     def run(s):
+        if a.fp32:
+            s.set_params(precision=1)
         for _ in range(a.steps):
             if a.zflow:
                 u, v, w = s.get_velocity()

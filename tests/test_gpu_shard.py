@@ -205,3 +205,16 @@ def test_multiprocess_sharded_step(world, n, steps, zflow):
                          capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, "\n".join(l for l in out.stdout.splitlines() if l.startswith("rank 0")) + out.stdout[-1500:] + out.stderr[-1500:]
     assert "SHARD_WORKER_OK" in out.stdout
+
+
+def test_multiprocess_sharded_step_fp32_solve():
+    """The fp32 pressure solve (float4 vectors) of a multi-process handle: the one-launch solve reads the neighbours' planes with
+    16-byte system-scope loads."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                          "--master-port", "29541", os.path.join(ROOT, "tests", "shard_worker.py"), "32", "3", "--zflow", "4.0", "--fp32"],
+                         capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, "\n".join(l for l in out.stdout.splitlines() if l.startswith("rank 0")) + out.stdout[-1500:] + out.stderr[-1500:]
+    assert "SHARD_WORKER_OK" in out.stdout
