@@ -77,7 +77,11 @@ int fs3_destroy(fs3_sim* s);
 /* FluidSim3::ResetSimulation (Simulation3D.cpp:41-99); bit-identical to a libstdc++ build of the
  * reference (minstd_rand0 seed 0, closed-form skip-ahead on the device). */
 int fs3_reset(fs3_sim* s);
-/* FluidSim3::Simulate(dt) (Simulation3D.cpp:101-188).  Asynchronous on the handle's stream. */
+/* FluidSim3::Simulate(dt) (Simulation3D.cpp:101-188).  Queued on the handle's stream; results are complete after fs3_sync or
+ * any getter.  The call itself is NOT free of host waits: the extrapolation reads one bucket size back, a sharded handle reads
+ * the world x world migration counts back, and at grid sizes whose pressure unknowns are held in the persisting L2 carve-out
+ * (about 160^3 to 380^3 on one GPU) the solve is bracketed by two stream synchronisations and cudaDeviceSetLimit calls (the
+ * previous device-wide limit is restored before the call returns).  Do not call it from inside a stream capture. */
 int fs3_step(fs3_sim* s, float dt);
 /* Blocks until all queued work on the handle is complete and reports deferred device errors. */
 int fs3_sync(fs3_sim* s);
