@@ -80,7 +80,7 @@ int fs3_reset(fs3_sim* s);
 /* FluidSim3::Simulate(dt) (Simulation3D.cpp:101-188).  Queued on the handle's stream; results are complete after fs3_sync or
  * any getter.  The call itself is NOT free of host waits: the extrapolation reads one bucket size back, a sharded handle reads
  * the world x world migration counts back, and at grid sizes whose pressure unknowns are held in the persisting L2 carve-out
- * (about 160^3 to 380^3 on one GPU) the solve is bracketed by two stream synchronisations and cudaDeviceSetLimit calls (the
+ * (about 184^3 to 320^3 on one GPU) the solve is bracketed by two stream synchronisations and cudaDeviceSetLimit calls (the
  * previous device-wide limit is restored before the call returns).  Do not call it from inside a stream capture. */
 int fs3_step(fs3_sim* s, float dt);
 /* Blocks until all queued work on the handle is complete and reports deferred device errors. */
