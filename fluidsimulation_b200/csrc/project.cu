@@ -329,7 +329,7 @@ __global__ void __launch_bounds__(FS3_SOR_THREADS, FS3_SOR_MINB) k_sor_half(Sys<
 // copies; [32 (LINES + 2 + parity)] ticket counters of the interior tail.  All zero at launch.
 #define FS3_SOR_GEN_LINES 16
 #define FS3_SOR_CHUNK 256   // entries per ticket of the dynamic tail of the interior sweep
-#define FS3_SOR_MAX_NBB 256
+#define FS3_SOR_MAX_NBB 256   // upper bound of the boundary blocks (a quarter of the grid is the effective one: 147 on a B200)
 struct SorPersist {
 	const void* peer_black[2];   // colour-1 array of the lower / upper neighbour (nullptr: no neighbour)
 	uint32_t *peer_B[2], *peer_R[2];
